@@ -1,0 +1,195 @@
+/*
+ * spu_b200.h -- C-ABI of the B200-native inference hot path (libspu_b200.so).
+ *
+ * Drop-in boundary for ONE path of daxmawal/StarPU-Inference-Server: the body of
+ * the StarPU inference codelet's cuda_func.  In the reference that body is
+ *   InferenceCodelet::cuda_inference_func      src/core/starpu_setup.cpp:807-846
+ *     -> run_codelet_inference                 src/core/starpu_setup.cpp:638-723
+ *       -> run_inference                       src/core/starpu_setup.cpp:594-624
+ *            TensorBuilder::prepare_input_ivalues  src/core/tensor_builder.cpp:148-155
+ *            model->forward(ivalues)               src/core/starpu_setup.cpp:610
+ *            wrapper.copy_(out, non_blocking)      src/core/starpu_setup.cpp:834-844
+ * Everything below replaces "wrap StarPU device buffers as torch tensors, call
+ * LibTorch forward, copy the result into the STARPU_W buffer" with hand-written
+ * sm_100a kernels.  Plain pointers and sizes only; no torch / C++ types; never
+ * throws; every call returns an spu_status and records a message retrievable
+ * with spu_last_error().  All *_async calls only enqueue work on `stream`
+ * (a cudaStream_t passed as void*) -- no allocation, no device/stream
+ * synchronisation, no default-stream use -- which is the STARPU_CUDA_ASYNC
+ * contract (codelet cuda_flags[0] = 1U, src/core/starpu_setup.cpp:559-568).
+ *
+ * There is NO CPU fallback: if no sm_100 device is usable the create calls fail.
+ */
+#ifndef SPU_B200_H
+#define SPU_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SPU_ABI_VERSION 1
+
+typedef enum spu_status {
+  SPU_OK = 0,
+  SPU_ERR_INVALID = 1,     /* bad argument (null pointer, shape out of range)   */
+  SPU_ERR_CUDA = 2,        /* a CUDA runtime / driver call failed               */
+  SPU_ERR_CAPACITY = 3,    /* batch/seq exceeds what the replica was sized for  */
+  SPU_ERR_UNSUPPORTED = 4, /* device is not sm_100, or unsupported model shape  */
+  SPU_ERR_NOMEM = 5
+} spu_status;
+
+/* Opaque per-GPU weight replica + per-worker workspaces.  Replaces one entry of
+ * InferenceParams::models.models_gpu (src/core/inference_params.hpp:46-51), i.e.
+ * one `model_cpu.clone().to(cuda:id)` of clone_model_to_gpus
+ * (src/core/inference_runner.cpp:251-275). */
+typedef struct spu_replica spu_replica;
+
+/* ---- BERT encoder (models/bert.yml: input_ids,attention_mask int64 [B,S] ->
+ *      output0 fp32 [B,S,hidden] = last_hidden_state) ------------------------ */
+typedef struct spu_bert_desc {
+  int32_t layers, hidden, heads, ffn, vocab, max_pos, type_vocab;
+  float ln_eps;
+} spu_bert_desc;
+
+/* precision flags for spu_*_replica_create */
+#define SPU_PREC_BF16 0u
+#define SPU_PREC_FP8_E4M3 1u /* per-tensor scaled FP8 GEMM inputs (QKV/out/FFN) */
+
+/* Number of weight tensors spu_bert_replica_create expects: 5 + 16*layers, in the
+ * order of the HF state dict restated in oracle/bert_oracle.py:weight_names()
+ * (word, position, token_type embeddings, embeddings.LayerNorm.{weight,bias},
+ * then per layer: q.w q.b k.w k.b v.w v.b attn_out.w attn_out.b attn_LN.g
+ * attn_LN.b ffn1.w ffn1.b ffn2.w ffn2.b out_LN.g out_LN.b).  All fp32, host
+ * memory, nn.Linear layout [out_features, in_features]. */
+#define SPU_BERT_NUM_TENSORS(layers) (5 + 16 * (layers))
+
+/* Create one replica on CUDA device `device`: converts the fp32 host tensors to
+ * bf16 (packing q/k/v into one [3H,H] matrix), uploads them, and pre-allocates
+ * `n_workspaces` activation arenas sized for (max_batch, max_seq) -- one per
+ * StarPU CUDA worker that may run on this device (STARPU_NWORKER_PER_CUDA,
+ * models/bert.yml:6-8), so forward calls never allocate.
+ * Replaces load_model + clone_model_to_gpus (src/core/inference_runner.cpp:243-275). */
+spu_status spu_bert_replica_create(const spu_bert_desc *desc,
+                                   const float *const *tensors, int32_t n_tensors,
+                                   int32_t device, int32_t max_batch,
+                                   int32_t max_seq, int32_t n_workspaces,
+                                   uint32_t flags, spu_replica **out);
+
+/* Destroy a replica (synchronises its device). */
+spu_status spu_replica_destroy(spu_replica *r);
+
+/* The forward the codelet enqueues.  ids/mask: DEVICE pointers to contiguous
+ * int64 [batch, seq] (exactly what StarPU hands the reference codelet as
+ * buffers[0..1]->ptr after the host gather, slot_manager_component.cpp:649-727);
+ * mask != 0 means "keep".  out: DEVICE fp32 [batch, seq, hidden] (buffers[2]->ptr).
+ * ws_idx selects the workspace (worker-private; two in-flight calls must not
+ * share one). */
+spu_status spu_bert_forward_async(spu_replica *r, int32_t ws_idx,
+                                  const int64_t *ids, const int64_t *mask,
+                                  int32_t batch, int32_t seq, float *out,
+                                  void *stream);
+
+/* Number of kernel launches one forward of (batch, seq) enqueues. */
+int32_t spu_bert_forward_launch_count(const spu_replica *r);
+
+/* Capture the forward of (batch, seq) on ws_idx into a CUDA graph (warm-up hook,
+ * src/core/warmup.cpp:225-299) so later spu_bert_forward_async calls with the
+ * same (ws_idx, batch, seq, ids, mask, out) pointers replay it. */
+spu_status spu_bert_forward_capture(spu_replica *r, int32_t ws_idx,
+                                    const int64_t *ids, const int64_t *mask,
+                                    int32_t batch, int32_t seq, float *out,
+                                    void *stream);
+
+/* ---- Stage 1: gather + pad + mask (device) --------------------------------
+ * Ragged batch assembly: request i supplies len[i] int64 token ids at
+ * src_ids[i] (and optionally len[i] mask words at src_mask[i]; src_mask or
+ * src_mask[i] may be NULL = all ones).  Writes ids_out/mask_out int64 [n_req,seq]:
+ * tokens then pad_id / 0.  src tables and len are DEVICE arrays of device-visible
+ * pointers (device or pinned-mapped host memory).  With every len == seq this is
+ * byte-identical to SlotManager::copy_job_inputs_to_slot
+ * (src/starpu_task_worker/slot_manager_component.cpp:649-727). */
+spu_status spu_gather_pad_mask_async(const int64_t *const *src_ids,
+                                     const int64_t *const *src_mask,
+                                     const int32_t *len, int32_t n_req,
+                                     int32_t seq, int64_t pad_id,
+                                     int64_t *ids_out, int64_t *mask_out,
+                                     void *stream);
+
+/* Dense byte gather: segment i (nbytes[i] bytes at srcs[i]) is copied to
+ * dst + dst_off[i].  Used for fixed-shape inputs (ViT pixels, full-length ids).
+ * All table arguments are DEVICE arrays. */
+spu_status spu_gather_segments_async(const void *const *srcs,
+                                     const uint64_t *dst_off,
+                                     const uint64_t *nbytes, int32_t n_seg,
+                                     void *dst, void *stream);
+
+/* ---- Stage 4: scatter to per-request buffers ------------------------------
+ * Segment i: nbytes[i] bytes from src + src_off[i] to dsts[i].  Replaces the
+ * dim-0 slicing of ResultDispatcher::propagate_completion_to_sub_jobs
+ * (result_dispatcher_component.cpp:678-739; batching_helpers.hpp:74-127) with a
+ * device-side write into each request's own output buffer. */
+spu_status spu_scatter_segments_async(const void *src, const uint64_t *src_off,
+                                      const uint64_t *nbytes,
+                                      void *const *dsts, int32_t n_seg,
+                                      void *stream);
+
+/* ---- Stage-level entry points (parity tests, benchmarks) ------------------ */
+#define SPU_EPI_BIAS 0        /* out_bf16 = A W^T + bias                       */
+#define SPU_EPI_BIAS_GELU 1   /* out_bf16 = gelu_erf(A W^T + bias)             */
+#define SPU_EPI_BIAS_RESID 2  /* out_f32  = A W^T + bias + resid_f32           */
+
+/* C = A[M,K](bf16,row-major) * W[N,K]^T(bf16,row-major) with fused epilogue on
+ * tcgen05/TMEM, operands staged by TMA.  K % 64 == 0, N % 64 == 0.  `out` is
+ * bf16 [M,N] for BIAS/BIAS_GELU, fp32 [M,N] for BIAS_RESID (resid may alias out).
+ * Creates its tensor maps per call (test path; the replica caches them). */
+spu_status spu_gemm_bf16_async(const void *A, const void *W, const float *bias,
+                               const float *resid, void *out, int32_t M,
+                               int32_t N, int32_t K, int32_t epilogue,
+                               void *stream);
+
+/* Fused masked-softmax attention.  qkv: bf16 [batch*seq, 3*heads*64] (q|k|v);
+ * mask_bias: fp32 [batch, seq] additive (0 keep, large negative drop);
+ * ctx: bf16 [batch*seq, heads*64].  head_dim is 64. */
+spu_status spu_attention_async(const void *qkv, const float *mask_bias, void *ctx,
+                               int32_t batch, int32_t seq, int32_t heads,
+                               void *stream);
+
+/* Row LayerNorm: y = LN(x) * gamma + beta over the last dim (fp32 statistics).
+ * x fp32 [rows, hidden]; writes fp32 out_f32 (may be NULL, may alias x) and bf16
+ * out_bf16 (may be NULL). */
+spu_status spu_layernorm_async(const float *x, const float *gamma,
+                               const float *beta, float eps, float *out_f32,
+                               void *out_bf16, int32_t rows, int32_t hidden,
+                               void *stream);
+
+/* Embedding lookup + LayerNorm + mask-bias builder (BERT stage 1b):
+ * x = LN(word[ids] + pos[t] + type[0]); mask_bias = mask != 0 ? 0 : -1e30.
+ * Tables are fp32 device arrays. */
+spu_status spu_bert_embed_async(const int64_t *ids, const int64_t *mask,
+                                const float *word, const float *pos,
+                                const float *type0, const float *gamma,
+                                const float *beta, float eps, int32_t vocab,
+                                float *x_f32, void *x_bf16, float *mask_bias,
+                                int32_t batch, int32_t seq, int32_t hidden,
+                                void *stream);
+
+/* Toy "model" used by the codelet known-answer tests the reference runs with
+ * TorchScript x+1 / x+1.5 modules (tests/integration/starpu/
+ * integration_starpu_setup.cpp:42-60, tests/unit/core/unit_starpu_setup.cpp:
+ * 2332-2433): out[i] = in[i] * scale + shift, fp32, on the device. */
+spu_status spu_affine_f32_async(const float *in, float *out, uint64_t n,
+                                float scale, float shift, void *stream);
+
+/* ---- Misc ------------------------------------------------------------------ */
+const char *spu_last_error(void);       /* thread-local message of the last failure */
+int32_t spu_abi_version(void);
+int32_t spu_device_count(void);         /* CUDA devices visible (0 without a GPU)   */
+int32_t spu_device_is_sm100(int32_t device);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SPU_B200_H */

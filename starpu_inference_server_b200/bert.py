@@ -1,0 +1,120 @@
+"""Host-side handle of one BERT weight replica (thin wrapper over the C-ABI).
+
+Mirrors the role of one entry of ``InferenceParams::models.models_gpu``
+(/root/reference/src/core/inference_params.hpp:46-51) created by
+``clone_model_to_gpus`` (/root/reference/src/core/inference_runner.cpp:251-275): the
+TorchScript state (or an HF-keyed state dict) is read ONCE at start-up, converted to
+bf16 device buffers by ``spu_bert_replica_create``; afterwards no torch code runs on
+the forward path.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+
+import numpy as np
+
+from . import capi
+
+
+@dataclass(frozen=True)
+class BertConfig:
+    layers: int = 12
+    hidden: int = 768
+    heads: int = 12
+    ffn: int = 3072
+    vocab: int = 30522
+    max_pos: int = 512
+    type_vocab: int = 2
+    ln_eps: float = 1e-12
+
+
+def _tensor_order(layers: int):
+    names = ["embeddings.word_embeddings.weight", "embeddings.position_embeddings.weight",
+             "embeddings.token_type_embeddings.weight", "embeddings.LayerNorm.weight",
+             "embeddings.LayerNorm.bias"]
+    for l in range(layers):
+        p = f"encoder.layer.{l}."
+        names += [p + s for s in (
+            "attention.self.query.weight", "attention.self.query.bias",
+            "attention.self.key.weight", "attention.self.key.bias",
+            "attention.self.value.weight", "attention.self.value.bias",
+            "attention.output.dense.weight", "attention.output.dense.bias",
+            "attention.output.LayerNorm.weight", "attention.output.LayerNorm.bias",
+            "intermediate.dense.weight", "intermediate.dense.bias",
+            "output.dense.weight", "output.dense.bias",
+            "output.LayerNorm.weight", "output.LayerNorm.bias")]
+    return names
+
+
+def config_from_state(state) -> BertConfig:
+    """Infer the architecture from HF-keyed weights (heads = hidden/64)."""
+    word = state["embeddings.word_embeddings.weight"]
+    layers = 0
+    while f"encoder.layer.{layers}.output.dense.weight" in state:
+        layers += 1
+    hidden = word.shape[1]
+    return BertConfig(layers=layers, hidden=hidden, heads=hidden // 64,
+                      ffn=state["encoder.layer.0.intermediate.dense.weight"].shape[0],
+                      vocab=word.shape[0],
+                      max_pos=state["embeddings.position_embeddings.weight"].shape[0],
+                      type_vocab=state["embeddings.token_type_embeddings.weight"].shape[0])
+
+
+def state_from_torchscript(path: str):
+    """Read the weights of a ``bert_libtorch.pt`` produced like
+    /root/reference/models/import_bert-base-uncased.py (keys carry a ``bert.`` prefix
+    from the wrapper module).  Start-up only."""
+    import torch
+
+    sd = torch.jit.load(path, map_location="cpu").state_dict()
+    out = {}
+    for k, v in sd.items():
+        k = k[5:] if k.startswith("bert.") else k
+        out[k] = v.detach().to(torch.float32).contiguous().numpy()
+    return out
+
+
+class BertReplica:
+    """One weight replica on one GPU + ``n_workspaces`` worker-private arenas."""
+
+    def __init__(self, state, cfg: BertConfig | None = None, device: int = 0, max_batch: int = 32,
+                 max_seq: int = 128, n_workspaces: int = 1, flags: int = capi.SPU_PREC_BF16):
+        self.cfg = cfg or config_from_state(state)
+        self.device, self.max_batch, self.max_seq = device, max_batch, max_seq
+        names = _tensor_order(self.cfg.layers)
+        keep = [np.ascontiguousarray(np.asarray(state[n], dtype=np.float32)) for n in names]
+        arr = (C.c_void_p * len(keep))(*[a.ctypes.data for a in keep])
+        desc = capi.BertDesc(self.cfg.layers, self.cfg.hidden, self.cfg.heads, self.cfg.ffn,
+                             self.cfg.vocab, self.cfg.max_pos, self.cfg.type_vocab, self.cfg.ln_eps)
+        h = C.c_void_p()
+        capi.check(capi.lib().spu_bert_replica_create(C.byref(desc), arr, len(keep), device, max_batch,
+                                                      max_seq, n_workspaces, flags, C.byref(h)))
+        self._h = h
+
+    @property
+    def launches_per_forward(self) -> int:
+        return capi.lib().spu_bert_forward_launch_count(self._h)
+
+    def forward_async(self, ids, mask, out, ws: int = 0, stream=None):
+        """ids/mask: int64 CUDA tensors [B,S]; out: fp32 CUDA tensor [B,S,hidden]."""
+        b, s = ids.shape
+        capi.check(capi.lib().spu_bert_forward_async(self._h, ws, capi.ptr(ids), capi.ptr(mask), b, s,
+                                                     capi.ptr(out), capi.stream_ptr(stream)))
+        return out
+
+    def capture(self, ids, mask, out, ws: int = 0, stream=None):
+        b, s = ids.shape
+        capi.check(capi.lib().spu_bert_forward_capture(self._h, ws, capi.ptr(ids), capi.ptr(mask), b, s,
+                                                       capi.ptr(out), capi.stream_ptr(stream)))
+
+    def close(self):
+        if getattr(self, "_h", None):
+            capi.lib().spu_replica_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

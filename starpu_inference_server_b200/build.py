@@ -1,0 +1,98 @@
+"""In-tree build of the native libraries (sm_100a only).
+
+    python -m starpu_inference_server_b200.build [--force]
+
+Produces, next to this file:
+  libspu_b200.so        CUDA kernels + the C-ABI of include/spu_b200.h
+  libspu_host.so        C++ host layer (StarPU-shaped codelet, slot pools, mini runtime)
+nvcc cross-compiles without a GPU, so this runs in the CPU-only build container;
+the .so files travel to the GPU box with the repo snapshot.
+"""
+from __future__ import annotations
+
+import hashlib
+import os
+import subprocess
+import sys
+from concurrent.futures import ThreadPoolExecutor
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+CSRC = os.path.join(HERE, "csrc")
+CORE = os.path.join(HERE, "core")
+OBJ = os.path.join(HERE, "_obj")
+NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+
+ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
+NVCC_FLAGS = ARCH + ["-std=c++17", "-O3", "-lineinfo", "-Xcompiler", "-fPIC",
+                     "--expt-relaxed-constexpr",
+                     "-I", os.path.join(ROOT, "include")]
+
+CUDA_SOURCES = ["replica.cu", "gemm_sm100.cu", "attention.cu", "rowops.cu"]
+HOST_SOURCES = ["inference_codelet.cpp", "slot_pools.cpp", "mini_starpu.cpp", "host_capi.cpp"]
+
+
+def _digest(paths):
+    h = hashlib.sha256()
+    for p in sorted(paths):
+        h.update(p.encode())
+        with open(p, "rb") as f:
+            h.update(f.read())
+    h.update(" ".join(NVCC_FLAGS).encode())
+    return h.hexdigest()
+
+
+def _deps(directory):
+    return [os.path.join(directory, f) for f in os.listdir(directory)
+            if f.endswith((".cu", ".cuh", ".h", ".hpp", ".cpp"))] + \
+           [os.path.join(ROOT, "include", f) for f in os.listdir(os.path.join(ROOT, "include"))]
+
+
+def _run(cmd):
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError("build failed: %s\n%s\n%s" % (" ".join(cmd), r.stdout, r.stderr))
+    return r.stdout + r.stderr
+
+
+def _build_lib(name, directory, sources, extra_link, force):
+    out = os.path.join(HERE, name)
+    stamp = os.path.join(OBJ, name + ".sha256")
+    dig = _digest(_deps(directory) + ([os.path.join(HERE, "libspu_b200.so")] if False else []))
+    if not force and os.path.exists(out) and os.path.exists(stamp) and open(stamp).read() == dig:
+        return out, False
+    os.makedirs(OBJ, exist_ok=True)
+    objs = []
+
+    def compile_one(src):
+        o = os.path.join(OBJ, name + "." + src + ".o")
+        _run([NVCC] + NVCC_FLAGS + ["-x", "cu", "-c", os.path.join(directory, src), "-o", o])
+        return o
+
+    with ThreadPoolExecutor(max_workers=min(8, len(sources))) as ex:
+        objs = list(ex.map(compile_one, sources))
+    _run([NVCC] + ARCH + ["-shared", "-o", out] + objs + ["--cudart", "static"] + extra_link)
+    with open(stamp, "w") as f:
+        f.write(dig)
+    return out, True
+
+
+def build(force: bool = False, verbose: bool = False):
+    """Compile every CUDA/C++ source for sm_100a; returns the library paths."""
+    libs = []
+    p, rebuilt = _build_lib("libspu_b200.so", CSRC, CUDA_SOURCES, [], force)
+    libs.append(p)
+    if verbose:
+        print(("built " if rebuilt else "up to date ") + p)
+    if os.path.isdir(CORE) and all(os.path.exists(os.path.join(CORE, s)) for s in HOST_SOURCES):
+        p2, rebuilt2 = _build_lib("libspu_host.so", CORE, HOST_SOURCES,
+                                  ["-L" + HERE, "-lspu_b200", "-Xlinker", "-rpath=$ORIGIN",
+                                   "-lpthread"], force or rebuilt)
+        libs.append(p2)
+        if verbose:
+            print(("built " if rebuilt2 else "up to date ") + p2)
+    return libs
+
+
+if __name__ == "__main__":
+    build(force="--force" in sys.argv, verbose=True)

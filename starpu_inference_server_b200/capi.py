@@ -1,0 +1,97 @@
+"""ctypes binding of include/spu_b200.h (libspu_b200.so).
+
+This is plumbing for tests/bench: PyTorch supplies device memory and streams, every
+computation goes through the C-ABI.  There is no fallback: a missing library or a
+non-sm_100 device raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libspu_b200.so")
+
+SPU_OK = 0
+SPU_ERR_INVALID, SPU_ERR_CUDA, SPU_ERR_CAPACITY, SPU_ERR_UNSUPPORTED, SPU_ERR_NOMEM = 1, 2, 3, 4, 5
+SPU_EPI_BIAS, SPU_EPI_BIAS_GELU, SPU_EPI_BIAS_RESID = 0, 1, 2
+SPU_PREC_BF16, SPU_PREC_FP8_E4M3 = 0, 1
+
+# every symbol include/spu_b200.h declares (checked by tests/test_capi_symbols.py)
+SYMBOLS = [
+    "spu_bert_replica_create", "spu_replica_destroy", "spu_bert_forward_async",
+    "spu_bert_forward_launch_count", "spu_bert_forward_capture", "spu_gather_pad_mask_async",
+    "spu_gather_segments_async", "spu_scatter_segments_async", "spu_gemm_bf16_async",
+    "spu_attention_async", "spu_layernorm_async", "spu_bert_embed_async", "spu_affine_f32_async",
+    "spu_last_error", "spu_abi_version", "spu_device_count", "spu_device_is_sm100",
+]
+
+
+class SpuError(RuntimeError):
+    def __init__(self, status, msg):
+        super().__init__(f"spu status {status}: {msg}")
+        self.status = status
+
+
+class BertDesc(C.Structure):
+    _fields_ = [("layers", C.c_int32), ("hidden", C.c_int32), ("heads", C.c_int32),
+                ("ffn", C.c_int32), ("vocab", C.c_int32), ("max_pos", C.c_int32),
+                ("type_vocab", C.c_int32), ("ln_eps", C.c_float)]
+
+
+_lib = None
+
+
+def lib():
+    """Load libspu_b200.so (built in-tree by starpu_inference_server_b200.build)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            f"{LIB_PATH} is missing: run `python -m starpu_inference_server_b200.build` "
+            "(there is no CPU or PyTorch fallback for this path)")
+    L = C.CDLL(LIB_PATH)
+    vp, i32, i64, u64, f32 = C.c_void_p, C.c_int32, C.c_int64, C.c_uint64, C.c_float
+    L.spu_bert_replica_create.argtypes = [C.POINTER(BertDesc), C.POINTER(vp), i32, i32, i32, i32, i32,
+                                          C.c_uint32, C.POINTER(vp)]
+    L.spu_replica_destroy.argtypes = [vp]
+    L.spu_bert_forward_async.argtypes = [vp, i32, vp, vp, i32, i32, vp, vp]
+    L.spu_bert_forward_capture.argtypes = [vp, i32, vp, vp, i32, i32, vp, vp]
+    L.spu_bert_forward_launch_count.argtypes = [vp]
+    L.spu_gather_pad_mask_async.argtypes = [vp, vp, vp, i32, i32, i64, vp, vp, vp]
+    L.spu_gather_segments_async.argtypes = [vp, vp, vp, i32, vp, vp]
+    L.spu_scatter_segments_async.argtypes = [vp, vp, vp, vp, i32, vp]
+    L.spu_gemm_bf16_async.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, i32, vp]
+    L.spu_attention_async.argtypes = [vp, vp, vp, i32, i32, i32, vp]
+    L.spu_layernorm_async.argtypes = [vp, vp, vp, f32, vp, vp, i32, i32, vp]
+    L.spu_bert_embed_async.argtypes = [vp, vp, vp, vp, vp, vp, vp, f32, i32, vp, vp, vp, i32, i32, i32, vp]
+    L.spu_affine_f32_async.argtypes = [vp, vp, u64, f32, f32, vp]
+    L.spu_last_error.restype = C.c_char_p
+    for name in SYMBOLS:
+        fn = getattr(L, name)
+        if name not in ("spu_last_error",):
+            fn.restype = i32
+    _lib = L
+    return L
+
+
+def check(status):
+    if status != SPU_OK:
+        raise SpuError(status, lib().spu_last_error().decode(errors="replace"))
+
+
+def ptr(t):
+    """Device/host address of a torch tensor or numpy array (None -> NULL)."""
+    if t is None:
+        return None
+    if hasattr(t, "data_ptr"):
+        return C.c_void_p(t.data_ptr())
+    return C.c_void_p(t.ctypes.data)
+
+
+def stream_ptr(stream=None):
+    import torch
+
+    s = stream if stream is not None else torch.cuda.current_stream()
+    return C.c_void_p(s.cuda_stream)

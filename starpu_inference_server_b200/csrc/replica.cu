@@ -1,0 +1,392 @@
+// Per-GPU weight replica + per-worker workspaces + the forward the codelet enqueues.
+// Replaces load_model/clone_model_to_gpus (/root/reference/src/core/inference_runner.cpp:
+// 243-275) and the body of run_inference (/root/reference/src/core/starpu_setup.cpp:594-624).
+#include <cstring>
+#include <memory>
+#include <mutex>
+#include <vector>
+
+#include "common.cuh"
+#include "gemm_sm100.cuh"
+
+namespace spu {
+
+static thread_local std::string g_last_error;
+void set_error(const std::string &msg) { g_last_error = msg; }
+
+spu_status attention_launch(const void *qkv, const float *mask_bias, void *ctx, int batch, int seq,
+                            int heads, cudaStream_t stream);
+spu_status bert_embed_launch(const int64_t *ids, const int64_t *mask, const float *word,
+                             const float *pos, const float *type0, const float *gamma,
+                             const float *beta, float eps, int vocab, float *x_f32, void *x_bf16,
+                             float *mask_bias, int batch, int seq, int hidden, cudaStream_t stream);
+spu_status layernorm_launch(const float *x, const float *gamma, const float *beta, float eps,
+                            float *out_f32, void *out_bf16, int rows, int hidden,
+                            cudaStream_t stream);
+
+namespace {
+
+uint16_t f32_to_bf16_rne(float f) {
+  uint32_t u;
+  std::memcpy(&u, &f, 4);
+  if ((u & 0x7fffffffu) > 0x7f800000u) return static_cast<uint16_t>((u >> 16) | 0x40u);  // NaN
+  u += 0x7fffu + ((u >> 16) & 1u);
+  return static_cast<uint16_t>(u >> 16);
+}
+
+struct DeviceGuard {
+  int prev = -1;
+  explicit DeviceGuard(int dev) {
+    cudaGetDevice(&prev);
+    if (prev != dev) cudaSetDevice(dev);
+  }
+  ~DeviceGuard() {
+    if (prev >= 0) cudaSetDevice(prev);
+  }
+};
+
+struct LayerWeights {
+  __nv_bfloat16 *w_qkv = nullptr, *w_o = nullptr, *w_1 = nullptr, *w_2 = nullptr;
+  float *b_qkv = nullptr, *b_o = nullptr, *b_1 = nullptr, *b_2 = nullptr;
+  float *ln1_g = nullptr, *ln1_b = nullptr, *ln2_g = nullptr, *ln2_b = nullptr;
+};
+
+struct LayerPlans {
+  GemmPlan qkv, attn_out, ffn1, ffn2;
+};
+
+struct GraphKey {
+  const void *ids = nullptr, *mask = nullptr, *out = nullptr;
+  int batch = 0, seq = 0;
+  bool operator==(const GraphKey &o) const {
+    return ids == o.ids && mask == o.mask && out == o.out && batch == o.batch && seq == o.seq;
+  }
+};
+
+struct CapturedGraph {
+  GraphKey key;
+  cudaGraphExec_t exec = nullptr;
+};
+
+struct Workspace {
+  float *x_f32 = nullptr;
+  __nv_bfloat16 *x_bf16 = nullptr, *qkv = nullptr, *ctx = nullptr, *h = nullptr;
+  float *mask_bias = nullptr;
+  std::vector<LayerPlans> plans;
+  std::vector<CapturedGraph> graphs;
+};
+
+}  // namespace
+}  // namespace spu
+
+struct spu_replica {
+  spu_bert_desc desc{};
+  int device = 0;
+  int max_batch = 0, max_seq = 0, cap_rows = 0;
+  uint32_t flags = 0;
+  float *word = nullptr, *pos = nullptr, *type0 = nullptr, *emb_g = nullptr, *emb_b = nullptr;
+  std::vector<spu::LayerWeights> layers;
+  std::vector<spu::Workspace> ws;
+  std::vector<void *> allocations;
+};
+
+namespace spu {
+namespace {
+
+template <typename T>
+spu_status dev_alloc(spu_replica *r, T **out, size_t count) {
+  void *p = nullptr;
+  cudaError_t e = cudaMalloc(&p, count * sizeof(T));
+  if (e != cudaSuccess) {
+    set_error(std::string("cudaMalloc: ") + cudaGetErrorString(e));
+    return SPU_ERR_NOMEM;
+  }
+  r->allocations.push_back(p);
+  *out = static_cast<T *>(p);
+  return SPU_OK;
+}
+
+spu_status upload_f32(spu_replica *r, float **dst, const float *src, size_t n) {
+  spu_status st = dev_alloc(r, dst, n);
+  if (st != SPU_OK) return st;
+  SPU_CUDA_TRY(cudaMemcpy(*dst, src, n * sizeof(float), cudaMemcpyHostToDevice));
+  return SPU_OK;
+}
+
+// Upload rows [0, n_src) of fp32 host matrices, stacked, as one bf16 device matrix.
+spu_status upload_bf16_stacked(spu_replica *r, __nv_bfloat16 **dst,
+                               std::initializer_list<const float *> srcs, size_t n_each) {
+  const size_t total = n_each * srcs.size();
+  std::vector<uint16_t> tmp(total);
+  size_t o = 0;
+  for (const float *s : srcs)
+    for (size_t i = 0; i < n_each; ++i) tmp[o++] = f32_to_bf16_rne(s[i]);
+  spu_status st = dev_alloc(r, dst, total);
+  if (st != SPU_OK) return st;
+  SPU_CUDA_TRY(cudaMemcpy(*dst, tmp.data(), total * 2, cudaMemcpyHostToDevice));
+  return SPU_OK;
+}
+
+spu_status upload_f32_stacked(spu_replica *r, float **dst, std::initializer_list<const float *> srcs,
+                              size_t n_each) {
+  std::vector<float> tmp;
+  tmp.reserve(n_each * srcs.size());
+  for (const float *s : srcs) tmp.insert(tmp.end(), s, s + n_each);
+  return upload_f32(r, dst, tmp.data(), tmp.size());
+}
+
+#define SPU_TRY(expr)                 \
+  do {                                \
+    spu_status _s = (expr);           \
+    if (_s != SPU_OK) return _s;      \
+  } while (0)
+
+spu_status build(spu_replica *r, const float *const *t) {
+  const spu_bert_desc &d = r->desc;
+  const size_t H = d.hidden, F = d.ffn;
+  SPU_TRY(upload_f32(r, &r->word, t[0], static_cast<size_t>(d.vocab) * H));
+  SPU_TRY(upload_f32(r, &r->pos, t[1], static_cast<size_t>(d.max_pos) * H));
+  SPU_TRY(upload_f32(r, &r->type0, t[2], H));  // token_type_ids are all zero on this path
+  SPU_TRY(upload_f32(r, &r->emb_g, t[3], H));
+  SPU_TRY(upload_f32(r, &r->emb_b, t[4], H));
+  r->layers.resize(d.layers);
+  for (int l = 0; l < d.layers; ++l) {
+    const float *const *p = t + 5 + 16 * l;
+    LayerWeights &w = r->layers[l];
+    SPU_TRY(upload_bf16_stacked(r, &w.w_qkv, {p[0], p[2], p[4]}, H * H));
+    SPU_TRY(upload_f32_stacked(r, &w.b_qkv, {p[1], p[3], p[5]}, H));
+    SPU_TRY(upload_bf16_stacked(r, &w.w_o, {p[6]}, H * H));
+    SPU_TRY(upload_f32(r, &w.b_o, p[7], H));
+    SPU_TRY(upload_f32(r, &w.ln1_g, p[8], H));
+    SPU_TRY(upload_f32(r, &w.ln1_b, p[9], H));
+    SPU_TRY(upload_bf16_stacked(r, &w.w_1, {p[10]}, F * H));
+    SPU_TRY(upload_f32(r, &w.b_1, p[11], F));
+    SPU_TRY(upload_bf16_stacked(r, &w.w_2, {p[12]}, H * F));
+    SPU_TRY(upload_f32(r, &w.b_2, p[13], H));
+    SPU_TRY(upload_f32(r, &w.ln2_g, p[14], H));
+    SPU_TRY(upload_f32(r, &w.ln2_b, p[15], H));
+  }
+  const size_t rows = r->cap_rows;
+  for (Workspace &ws : r->ws) {
+    SPU_TRY(dev_alloc(r, &ws.x_f32, rows * H));
+    SPU_TRY(dev_alloc(r, &ws.x_bf16, rows * H));
+    SPU_TRY(dev_alloc(r, &ws.qkv, rows * 3 * H));
+    SPU_TRY(dev_alloc(r, &ws.ctx, rows * H));
+    SPU_TRY(dev_alloc(r, &ws.h, rows * F));
+    SPU_TRY(dev_alloc(r, &ws.mask_bias, rows));
+    // tail tiles of the last 128-row block read (never store) rows >= M: keep them finite
+    SPU_CUDA_TRY(cudaMemset(ws.x_bf16, 0, rows * H * 2));
+    SPU_CUDA_TRY(cudaMemset(ws.ctx, 0, rows * H * 2));
+    SPU_CUDA_TRY(cudaMemset(ws.h, 0, rows * F * 2));
+    ws.plans.resize(d.layers);
+    for (int l = 0; l < d.layers; ++l) {
+      const LayerWeights &w = r->layers[l];
+      const int R = static_cast<int>(rows);
+      SPU_TRY(gemm_make_plan(&ws.plans[l].qkv, ws.x_bf16, R, w.w_qkv, R, 3 * d.hidden, d.hidden,
+                             SPU_EPI_BIAS, GemmIn::BF16));
+      SPU_TRY(gemm_make_plan(&ws.plans[l].attn_out, ws.ctx, R, w.w_o, R, d.hidden, d.hidden,
+                             SPU_EPI_BIAS_RESID, GemmIn::BF16));
+      SPU_TRY(gemm_make_plan(&ws.plans[l].ffn1, ws.x_bf16, R, w.w_1, R, d.ffn, d.hidden,
+                             SPU_EPI_BIAS_GELU, GemmIn::BF16));
+      SPU_TRY(gemm_make_plan(&ws.plans[l].ffn2, ws.h, R, w.w_2, R, d.hidden, d.ffn,
+                             SPU_EPI_BIAS_RESID, GemmIn::BF16));
+    }
+  }
+  SPU_CUDA_TRY(cudaDeviceSynchronize());
+  return SPU_OK;
+}
+
+spu_status enqueue_forward(spu_replica *r, Workspace &ws, const int64_t *ids, const int64_t *mask,
+                           int batch, int seq, float *out, cudaStream_t stream) {
+  const spu_bert_desc &d = r->desc;
+  const int M = batch * seq;
+  SPU_TRY(bert_embed_launch(ids, mask, r->word, r->pos, r->type0, r->emb_g, r->emb_b, d.ln_eps,
+                            d.vocab, ws.x_f32, ws.x_bf16, ws.mask_bias, batch, seq, d.hidden,
+                            stream));
+  for (int l = 0; l < d.layers; ++l) {
+    const LayerWeights &w = r->layers[l];
+    const LayerPlans &p = ws.plans[l];
+    const bool last = l == d.layers - 1;
+    GemmEpilogueArgs e{};
+    e.acc_scale = 1.f;
+    e.bias = w.b_qkv;
+    e.out = ws.qkv;
+    SPU_TRY(gemm_launch(p.qkv, M, e, stream));
+    SPU_TRY(attention_launch(ws.qkv, ws.mask_bias, ws.ctx, batch, seq, d.heads, stream));
+    e.bias = w.b_o;
+    e.resid = ws.x_f32;
+    e.out = ws.x_f32;  // in place: each element is read then written by the same thread
+    SPU_TRY(gemm_launch(p.attn_out, M, e, stream));
+    SPU_TRY(layernorm_launch(ws.x_f32, w.ln1_g, w.ln1_b, d.ln_eps, ws.x_f32, ws.x_bf16, M,
+                             d.hidden, stream));
+    e.bias = w.b_1;
+    e.resid = nullptr;
+    e.out = ws.h;
+    SPU_TRY(gemm_launch(p.ffn1, M, e, stream));
+    e.bias = w.b_2;
+    e.resid = ws.x_f32;
+    e.out = ws.x_f32;
+    SPU_TRY(gemm_launch(p.ffn2, M, e, stream));
+    // the last LayerNorm writes last_hidden_state straight into the StarPU output buffer
+    SPU_TRY(layernorm_launch(ws.x_f32, w.ln2_g, w.ln2_b, d.ln_eps, last ? out : ws.x_f32,
+                             last ? nullptr : ws.x_bf16, M, d.hidden, stream));
+  }
+  return SPU_OK;
+}
+
+spu_status check_forward_args(spu_replica *r, int ws_idx, const void *ids, const void *mask,
+                              int batch, int seq, const void *out) {
+  SPU_REQUIRE(r != nullptr, SPU_ERR_INVALID, "forward: null replica");
+  SPU_REQUIRE(ids && mask && out, SPU_ERR_INVALID, "forward: null buffer");
+  SPU_REQUIRE(ws_idx >= 0 && ws_idx < static_cast<int>(r->ws.size()), SPU_ERR_INVALID,
+              "forward: workspace index out of range");
+  SPU_REQUIRE(batch >= 1 && seq >= 1, SPU_ERR_INVALID, "forward: empty batch");
+  SPU_REQUIRE(seq <= r->desc.max_pos, SPU_ERR_CAPACITY, "forward: seq exceeds max_position_embeddings");
+  SPU_REQUIRE(static_cast<long long>(batch) * seq <= r->cap_rows, SPU_ERR_CAPACITY,
+              "forward: batch*seq exceeds the workspace the replica was created with");
+  return SPU_OK;
+}
+
+}  // namespace
+}  // namespace spu
+
+using namespace spu;
+
+extern "C" spu_status spu_bert_replica_create(const spu_bert_desc *desc, const float *const *tensors,
+                                              int32_t n_tensors, int32_t device, int32_t max_batch,
+                                              int32_t max_seq, int32_t n_workspaces, uint32_t flags,
+                                              spu_replica **out) {
+  SPU_REQUIRE(desc && tensors && out, SPU_ERR_INVALID, "replica_create: null argument");
+  *out = nullptr;
+  SPU_REQUIRE(desc->layers > 0 && desc->hidden > 0 && desc->heads > 0, SPU_ERR_INVALID,
+              "replica_create: bad descriptor");
+  SPU_REQUIRE(n_tensors == SPU_BERT_NUM_TENSORS(desc->layers), SPU_ERR_INVALID,
+              "replica_create: wrong tensor count");
+  SPU_REQUIRE(desc->hidden == desc->heads * 64, SPU_ERR_UNSUPPORTED,
+              "replica_create: head_dim must be 64");
+  SPU_REQUIRE(desc->hidden % 64 == 0 && desc->ffn % 64 == 0 && desc->hidden <= 1024,
+              SPU_ERR_UNSUPPORTED, "replica_create: hidden/ffn must be multiples of 64, hidden <= 1024");
+  SPU_REQUIRE(max_batch > 0 && max_seq > 0 && max_seq <= desc->max_pos && n_workspaces > 0,
+              SPU_ERR_INVALID, "replica_create: bad capacity");
+  SPU_REQUIRE(flags == SPU_PREC_BF16, SPU_ERR_UNSUPPORTED, "replica_create: unsupported precision flag");
+  for (int i = 0; i < n_tensors; ++i)
+    SPU_REQUIRE(tensors[i] != nullptr, SPU_ERR_INVALID, "replica_create: null weight tensor");
+  SPU_REQUIRE(spu_device_is_sm100(device) == 1, SPU_ERR_UNSUPPORTED,
+              "replica_create: device is not an sm_100 GPU (no CPU fallback exists)");
+  DeviceGuard guard(device);
+  auto r = std::make_unique<spu_replica>();
+  r->desc = *desc;
+  r->device = device;
+  r->max_batch = max_batch;
+  r->max_seq = max_seq;
+  r->flags = flags;
+  r->cap_rows = ((max_batch * max_seq + 127) / 128) * 128;
+  r->ws.resize(n_workspaces);
+  spu_status st = build(r.get(), tensors);
+  if (st != SPU_OK) {
+    for (void *p : r->allocations) cudaFree(p);
+    return st;
+  }
+  *out = r.release();
+  return SPU_OK;
+}
+
+extern "C" spu_status spu_replica_destroy(spu_replica *r) {
+  if (r == nullptr) return SPU_OK;
+  DeviceGuard guard(r->device);
+  cudaDeviceSynchronize();
+  for (Workspace &ws : r->ws)
+    for (CapturedGraph &g : ws.graphs)
+      if (g.exec) cudaGraphExecDestroy(g.exec);
+  for (void *p : r->allocations) cudaFree(p);
+  delete r;
+  return SPU_OK;
+}
+
+extern "C" spu_status spu_bert_forward_async(spu_replica *r, int32_t ws_idx, const int64_t *ids,
+                                             const int64_t *mask, int32_t batch, int32_t seq,
+                                             float *out, void *stream) {
+  SPU_TRY(check_forward_args(r, ws_idx, ids, mask, batch, seq, out));
+  Workspace &ws = r->ws[ws_idx];
+  const GraphKey key{ids, mask, out, batch, seq};
+  for (const CapturedGraph &g : ws.graphs)
+    if (g.key == key) {
+      SPU_CUDA_TRY(cudaGraphLaunch(g.exec, as_stream(stream)));
+      return SPU_OK;
+    }
+  return enqueue_forward(r, ws, ids, mask, batch, seq, out, as_stream(stream));
+}
+
+extern "C" spu_status spu_bert_forward_capture(spu_replica *r, int32_t ws_idx, const int64_t *ids,
+                                               const int64_t *mask, int32_t batch, int32_t seq,
+                                               float *out, void *stream) {
+  SPU_TRY(check_forward_args(r, ws_idx, ids, mask, batch, seq, out));
+  Workspace &ws = r->ws[ws_idx];
+  const GraphKey key{ids, mask, out, batch, seq};
+  for (const CapturedGraph &g : ws.graphs)
+    if (g.key == key) return SPU_OK;
+  cudaStream_t s = as_stream(stream);
+  // one eager pass first: sets kernel attributes and warms caches outside the capture
+  SPU_TRY(enqueue_forward(r, ws, ids, mask, batch, seq, out, s));
+  SPU_CUDA_TRY(cudaStreamSynchronize(s));
+  SPU_CUDA_TRY(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
+  spu_status st = enqueue_forward(r, ws, ids, mask, batch, seq, out, s);
+  cudaGraph_t graph = nullptr;
+  cudaError_t e = cudaStreamEndCapture(s, &graph);
+  if (st != SPU_OK) {
+    if (graph) cudaGraphDestroy(graph);
+    return st;
+  }
+  SPU_CUDA_TRY(e);
+  CapturedGraph cg;
+  cg.key = key;
+  e = cudaGraphInstantiate(&cg.exec, graph, 0);
+  cudaGraphDestroy(graph);
+  SPU_CUDA_TRY(e);
+  ws.graphs.push_back(cg);
+  return SPU_OK;
+}
+
+extern "C" int32_t spu_bert_forward_launch_count(const spu_replica *r) {
+  return r == nullptr ? 0 : 1 + 7 * r->desc.layers;
+}
+
+extern "C" spu_status spu_gemm_bf16_async(const void *A, const void *W, const float *bias,
+                                          const float *resid, void *out, int32_t M, int32_t N,
+                                          int32_t K, int32_t epilogue, void *stream) {
+  GemmPlan plan;
+  SPU_TRY(gemm_make_plan(&plan, A, M, W, M, N, K, epilogue, GemmIn::BF16));
+  GemmEpilogueArgs e{};
+  e.bias = bias;
+  e.resid = resid;
+  e.out = out;
+  e.acc_scale = 1.f;
+  return gemm_launch(plan, M, e, as_stream(stream));
+}
+
+extern "C" spu_status spu_attention_async(const void *qkv, const float *mask_bias, void *ctx,
+                                          int32_t batch, int32_t seq, int32_t heads, void *stream) {
+  return attention_launch(qkv, mask_bias, ctx, batch, seq, heads, as_stream(stream));
+}
+
+extern "C" const char *spu_last_error(void) { return g_last_error.c_str(); }
+extern "C" int32_t spu_abi_version(void) { return SPU_ABI_VERSION; }
+
+extern "C" int32_t spu_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  return n;
+}
+
+extern "C" int32_t spu_device_is_sm100(int32_t device) {
+  int major = 0;
+  if (device < 0 || device >= spu_device_count()) return 0;
+  if (cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, device) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  return major == 10 ? 1 : 0;
+}

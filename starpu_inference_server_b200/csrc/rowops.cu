@@ -1,0 +1,282 @@
+// HBM-bound row kernels of the hot path: embedding+LayerNorm+mask builder,
+// residual LayerNorm, ragged gather/pad/mask, segmented gather/scatter copies, and
+// the toy affine "model".  All are one-pass, 128-bit coalesced, warp-shuffle
+// reductions, no shared-memory staging needed (no reuse across rows).
+#include "common.cuh"
+
+namespace spu {
+namespace {
+
+constexpr int kRowThreads = 256;            // 8 warps = 8 rows per CTA
+constexpr int kMaxChunksPerLane = 8;        // hidden <= 1024 (float4 chunks, 32 lanes)
+
+struct RowStats {
+  float mean, rstd;
+};
+
+// v holds this lane's float4 chunks of one row (chunk c -> lane c % 32).
+__device__ __forceinline__ RowStats row_stats(const float4 (&v)[kMaxChunksPerLane], int nchunk_lane,
+                                              int hidden, float eps) {
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < kMaxChunksPerLane; ++i)
+    if (i < nchunk_lane) s += (v[i].x + v[i].y) + (v[i].z + v[i].w);
+  const float mean = warp_sum(s) / static_cast<float>(hidden);
+  float q = 0.f;
+#pragma unroll
+  for (int i = 0; i < kMaxChunksPerLane; ++i)
+    if (i < nchunk_lane) {
+      const float a = v[i].x - mean, b = v[i].y - mean, c = v[i].z - mean, d = v[i].w - mean;
+      q += (a * a + b * b) + (c * c + d * d);
+    }
+  const float var = warp_sum(q) / static_cast<float>(hidden);
+  return {mean, rsqrtf(var + eps)};
+}
+
+__device__ __forceinline__ void row_normalise_store(const float4 (&v)[kMaxChunksPerLane],
+                                                    int nchunk_lane, RowStats st,
+                                                    const float *__restrict__ gamma,
+                                                    const float *__restrict__ beta,
+                                                    float *out_f32, __nv_bfloat16 *out_bf16,
+                                                    size_t row_off) {
+  const int lane = threadIdx.x & 31;
+#pragma unroll
+  for (int i = 0; i < kMaxChunksPerLane; ++i) {
+    if (i >= nchunk_lane) break;
+    const int c = lane + i * 32;
+    const float4 g = __ldg(reinterpret_cast<const float4 *>(gamma) + c);
+    const float4 b = __ldg(reinterpret_cast<const float4 *>(beta) + c);
+    float4 y;
+    y.x = (v[i].x - st.mean) * st.rstd * g.x + b.x;
+    y.y = (v[i].y - st.mean) * st.rstd * g.y + b.y;
+    y.z = (v[i].z - st.mean) * st.rstd * g.z + b.z;
+    y.w = (v[i].w - st.mean) * st.rstd * g.w + b.w;
+    if (out_f32 != nullptr) reinterpret_cast<float4 *>(out_f32 + row_off)[c] = y;
+    if (out_bf16 != nullptr)
+      reinterpret_cast<uint2 *>(out_bf16 + row_off)[c] =
+          make_uint2(pack_bf16(y.x, y.y), pack_bf16(y.z, y.w));
+  }
+}
+
+// x = LN(word[ids] + pos[t] + type[0]); mask_bias = mask ? 0 : -1e30.
+// Restates BertEmbeddings.forward + the additive mask HF builds (oracle/bert_oracle.py).
+__global__ void __launch_bounds__(kRowThreads)
+bert_embed_ln_kernel(const int64_t *__restrict__ ids, const int64_t *__restrict__ mask,
+                     const float *__restrict__ word, const float *__restrict__ pos,
+                     const float *__restrict__ type0, const float *__restrict__ gamma,
+                     const float *__restrict__ beta, float eps, int vocab, float *x_f32,
+                     __nv_bfloat16 *x_bf16, float *mask_bias, int rows, int seq, int hidden) {
+  const int row = blockIdx.x * (kRowThreads / 32) + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const int lane = threadIdx.x & 31;
+  const int nchunk = hidden >> 2;
+  const int nchunk_lane = (nchunk - lane + 31) >> 5;
+  int64_t id = ids[row];
+  id = id < 0 ? 0 : (id >= vocab ? vocab - 1 : id);  // memory safety; torch would raise
+  const int t = row % seq;
+  const float4 *w4 = reinterpret_cast<const float4 *>(word + static_cast<size_t>(id) * hidden);
+  const float4 *p4 = reinterpret_cast<const float4 *>(pos + static_cast<size_t>(t) * hidden);
+  const float4 *t4 = reinterpret_cast<const float4 *>(type0);
+  float4 v[kMaxChunksPerLane];
+#pragma unroll
+  for (int i = 0; i < kMaxChunksPerLane; ++i) {
+    if (i < nchunk_lane) {
+      const int c = lane + i * 32;
+      const float4 a = __ldg(w4 + c), b = __ldg(p4 + c), d = __ldg(t4 + c);
+      v[i] = make_float4(a.x + b.x + d.x, a.y + b.y + d.y, a.z + b.z + d.z, a.w + b.w + d.w);
+    }
+  }
+  const RowStats st = row_stats(v, nchunk_lane, hidden, eps);
+  row_normalise_store(v, nchunk_lane, st, gamma, beta, x_f32, x_bf16,
+                      static_cast<size_t>(row) * hidden);
+  if (lane == 0) mask_bias[row] = mask[row] != 0 ? 0.f : -1e30f;
+}
+
+__global__ void __launch_bounds__(kRowThreads)
+layernorm_kernel(const float *__restrict__ x, const float *__restrict__ gamma,
+                 const float *__restrict__ beta, float eps, float *out_f32,
+                 __nv_bfloat16 *out_bf16, int rows, int hidden) {
+  const int row = blockIdx.x * (kRowThreads / 32) + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const int lane = threadIdx.x & 31;
+  const int nchunk = hidden >> 2;
+  const int nchunk_lane = (nchunk - lane + 31) >> 5;
+  const size_t off = static_cast<size_t>(row) * hidden;
+  float4 v[kMaxChunksPerLane];
+#pragma unroll
+  for (int i = 0; i < kMaxChunksPerLane; ++i)
+    if (i < nchunk_lane) v[i] = reinterpret_cast<const float4 *>(x + off)[lane + i * 32];
+  const RowStats st = row_stats(v, nchunk_lane, hidden, eps);
+  row_normalise_store(v, nchunk_lane, st, gamma, beta, out_f32, out_bf16, off);
+}
+
+// Ragged gather + pad + mask: one CTA row per request, 8-byte words, coalesced.
+__global__ void __launch_bounds__(256)
+gather_pad_mask_kernel(const int64_t *const *__restrict__ src_ids,
+                       const int64_t *const *__restrict__ src_mask,
+                       const int32_t *__restrict__ len, int seq, int64_t pad_id,
+                       int64_t *__restrict__ ids_out, int64_t *__restrict__ mask_out) {
+  const int r = blockIdx.y;
+  const int L = len[r];
+  const int64_t *sid = src_ids[r];
+  const int64_t *smk = src_mask != nullptr ? src_mask[r] : nullptr;
+  for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < seq; t += gridDim.x * blockDim.x) {
+    const bool in = t < L;
+    const size_t o = static_cast<size_t>(r) * seq + t;
+    ids_out[o] = in ? sid[t] : pad_id;
+    mask_out[o] = in ? (smk != nullptr ? smk[t] : 1) : 0;
+  }
+}
+
+// Segmented byte copy.  Segment i: nbytes[i] bytes from (srcs ? srcs[i] : src_base +
+// src_off[i]) to (dsts ? dsts[i] : dst_base + dst_off[i]).  blockIdx.y = segment;
+// the CTAs of a segment grid-stride over it with 128-bit accesses when all three of
+// source, destination and size are 16-byte aligned.
+__global__ void __launch_bounds__(256)
+segcopy_kernel(const void *const *__restrict__ srcs, const uint8_t *src_base,
+               const uint64_t *__restrict__ src_off, void *const *__restrict__ dsts,
+               uint8_t *dst_base, const uint64_t *__restrict__ dst_off,
+               const uint64_t *__restrict__ nbytes) {
+  const int i = blockIdx.y;
+  const uint8_t *s = srcs != nullptr ? static_cast<const uint8_t *>(srcs[i]) : src_base + src_off[i];
+  uint8_t *d = dsts != nullptr ? static_cast<uint8_t *>(dsts[i]) : dst_base + dst_off[i];
+  const uint64_t n = nbytes[i];
+  const uint64_t tid = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const uint64_t nthr = static_cast<uint64_t>(gridDim.x) * blockDim.x;
+  if (((reinterpret_cast<uintptr_t>(s) | reinterpret_cast<uintptr_t>(d) | n) & 15u) == 0) {
+    const uint4 *s4 = reinterpret_cast<const uint4 *>(s);
+    uint4 *d4 = reinterpret_cast<uint4 *>(d);
+    const uint64_t n4 = n >> 4;
+    uint64_t k = tid;
+    // 4 independent 16-byte loads in flight per thread before the stores
+    for (; k + 3 * nthr < n4; k += 4 * nthr) {
+      const uint4 a = s4[k], b = s4[k + nthr], c = s4[k + 2 * nthr], e = s4[k + 3 * nthr];
+      d4[k] = a;
+      d4[k + nthr] = b;
+      d4[k + 2 * nthr] = c;
+      d4[k + 3 * nthr] = e;
+    }
+    for (; k < n4; k += nthr) d4[k] = s4[k];
+  } else {
+    for (uint64_t k = tid; k < n; k += nthr) d[k] = s[k];
+  }
+}
+
+__global__ void __launch_bounds__(256)
+affine_kernel(const float *__restrict__ in, float *__restrict__ out, uint64_t n, float scale,
+              float shift) {
+  for (uint64_t k = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x; k < n;
+       k += static_cast<uint64_t>(gridDim.x) * blockDim.x)
+    out[k] = in[k] * scale + shift;
+}
+
+constexpr int kSegBlocksPerSegment = 32;
+
+}  // namespace
+
+spu_status bert_embed_launch(const int64_t *ids, const int64_t *mask, const float *word,
+                             const float *pos, const float *type0, const float *gamma,
+                             const float *beta, float eps, int vocab, float *x_f32, void *x_bf16,
+                             float *mask_bias, int batch, int seq, int hidden,
+                             cudaStream_t stream) {
+  SPU_REQUIRE(ids && mask && word && pos && type0 && gamma && beta && mask_bias, SPU_ERR_INVALID,
+              "embed: null argument");
+  SPU_REQUIRE(hidden % 4 == 0 && hidden <= 128 * kMaxChunksPerLane, SPU_ERR_UNSUPPORTED,
+              "embed: hidden must be a multiple of 4 and <= 1024");
+  const int rows = batch * seq;
+  SPU_REQUIRE(rows > 0, SPU_ERR_INVALID, "embed: empty batch");
+  const int grid = (rows + kRowThreads / 32 - 1) / (kRowThreads / 32);
+  bert_embed_ln_kernel<<<grid, kRowThreads, 0, stream>>>(
+      ids, mask, word, pos, type0, gamma, beta, eps, vocab, x_f32,
+      static_cast<__nv_bfloat16 *>(x_bf16), mask_bias, rows, seq, hidden);
+  SPU_CUDA_TRY(cudaGetLastError());
+  return SPU_OK;
+}
+
+spu_status layernorm_launch(const float *x, const float *gamma, const float *beta, float eps,
+                            float *out_f32, void *out_bf16, int rows, int hidden,
+                            cudaStream_t stream) {
+  SPU_REQUIRE(x && gamma && beta, SPU_ERR_INVALID, "layernorm: null argument");
+  SPU_REQUIRE(hidden % 4 == 0 && hidden <= 128 * kMaxChunksPerLane, SPU_ERR_UNSUPPORTED,
+              "layernorm: hidden must be a multiple of 4 and <= 1024");
+  SPU_REQUIRE(rows > 0, SPU_ERR_INVALID, "layernorm: empty input");
+  const int grid = (rows + kRowThreads / 32 - 1) / (kRowThreads / 32);
+  layernorm_kernel<<<grid, kRowThreads, 0, stream>>>(x, gamma, beta, eps, out_f32,
+                                                     static_cast<__nv_bfloat16 *>(out_bf16), rows,
+                                                     hidden);
+  SPU_CUDA_TRY(cudaGetLastError());
+  return SPU_OK;
+}
+
+}  // namespace spu
+
+using namespace spu;
+
+extern "C" spu_status spu_gather_pad_mask_async(const int64_t *const *src_ids,
+                                                const int64_t *const *src_mask,
+                                                const int32_t *len, int32_t n_req, int32_t seq,
+                                                int64_t pad_id, int64_t *ids_out,
+                                                int64_t *mask_out, void *stream) {
+  if (n_req == 0 || seq == 0) return SPU_OK;  // empty batch: nothing to move
+  SPU_REQUIRE(src_ids && len && ids_out && mask_out, SPU_ERR_INVALID, "gather: null argument");
+  SPU_REQUIRE(n_req > 0 && seq > 0 && n_req <= 65535, SPU_ERR_INVALID, "gather: bad shape");
+  dim3 grid((seq + 255) / 256 > 8 ? 8 : (seq + 255) / 256, n_req);
+  gather_pad_mask_kernel<<<grid, 256, 0, as_stream(stream)>>>(src_ids, src_mask, len, seq, pad_id,
+                                                              ids_out, mask_out);
+  SPU_CUDA_TRY(cudaGetLastError());
+  return SPU_OK;
+}
+
+extern "C" spu_status spu_gather_segments_async(const void *const *srcs, const uint64_t *dst_off,
+                                                const uint64_t *nbytes, int32_t n_seg, void *dst,
+                                                void *stream) {
+  if (n_seg == 0) return SPU_OK;
+  SPU_REQUIRE(srcs && dst_off && nbytes && dst, SPU_ERR_INVALID, "gather_segments: null argument");
+  SPU_REQUIRE(n_seg > 0 && n_seg <= 65535, SPU_ERR_INVALID, "gather_segments: bad segment count");
+  dim3 grid(kSegBlocksPerSegment, n_seg);
+  segcopy_kernel<<<grid, 256, 0, as_stream(stream)>>>(srcs, nullptr, nullptr, nullptr,
+                                                      static_cast<uint8_t *>(dst), dst_off, nbytes);
+  SPU_CUDA_TRY(cudaGetLastError());
+  return SPU_OK;
+}
+
+extern "C" spu_status spu_scatter_segments_async(const void *src, const uint64_t *src_off,
+                                                 const uint64_t *nbytes, void *const *dsts,
+                                                 int32_t n_seg, void *stream) {
+  if (n_seg == 0) return SPU_OK;
+  SPU_REQUIRE(src && src_off && nbytes && dsts, SPU_ERR_INVALID, "scatter_segments: null argument");
+  SPU_REQUIRE(n_seg > 0 && n_seg <= 65535, SPU_ERR_INVALID, "scatter_segments: bad segment count");
+  dim3 grid(kSegBlocksPerSegment, n_seg);
+  segcopy_kernel<<<grid, 256, 0, as_stream(stream)>>>(nullptr, static_cast<const uint8_t *>(src),
+                                                      src_off, dsts, nullptr, nullptr, nbytes);
+  SPU_CUDA_TRY(cudaGetLastError());
+  return SPU_OK;
+}
+
+extern "C" spu_status spu_affine_f32_async(const float *in, float *out, uint64_t n, float scale,
+                                           float shift, void *stream) {
+  if (n == 0) return SPU_OK;
+  SPU_REQUIRE(in && out, SPU_ERR_INVALID, "affine: null argument");
+  const uint64_t blocks = (n + 255) / 256;
+  const int grid = static_cast<int>(blocks > 148ull * 8 ? 148ull * 8 : blocks);
+  affine_kernel<<<grid, 256, 0, as_stream(stream)>>>(in, out, n, scale, shift);
+  SPU_CUDA_TRY(cudaGetLastError());
+  return SPU_OK;
+}
+
+extern "C" spu_status spu_layernorm_async(const float *x, const float *gamma, const float *beta,
+                                          float eps, float *out_f32, void *out_bf16, int32_t rows,
+                                          int32_t hidden, void *stream) {
+  return layernorm_launch(x, gamma, beta, eps, out_f32, out_bf16, rows, hidden, as_stream(stream));
+}
+
+extern "C" spu_status spu_bert_embed_async(const int64_t *ids, const int64_t *mask,
+                                           const float *word, const float *pos,
+                                           const float *type0, const float *gamma,
+                                           const float *beta, float eps, int32_t vocab,
+                                           float *x_f32, void *x_bf16, float *mask_bias,
+                                           int32_t batch, int32_t seq, int32_t hidden,
+                                           void *stream) {
+  return bert_embed_launch(ids, mask, word, pos, type0, gamma, beta, eps, vocab, x_f32, x_bf16,
+                           mask_bias, batch, seq, hidden, as_stream(stream));
+}

@@ -1,0 +1,294 @@
+"""Stage-level parity on a real B200: every kernel is called through the C-ABI
+(ctypes -> libspu_b200.so) and compared with the CPU oracle / an fp32 restatement of
+the same op on the same seeded inputs.  Integer/byte stages must be bit-exact."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+torch = pytest.importorskip("torch")
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def spu(built_libs):
+    from starpu_inference_server_b200 import capi
+
+    assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+    L = capi.lib()
+    assert L.spu_device_is_sm100(0) == 1, "device 0 is not sm_100"
+    return capi
+
+
+def _sync():
+    torch.cuda.synchronize()
+
+
+# --------------------------------------------------------------------------- GEMM
+def _gemm_ref(a_bf16, w_bf16, bias, resid, epi):
+    y = a_bf16.float().cpu() @ w_bf16.float().cpu().T + bias.cpu()
+    if epi == 1:
+        y = torch.nn.functional.gelu(y)  # exact erf GELU
+    if epi == 2:
+        y = y + resid.cpu()
+    return y
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 128, 64), (128, 256, 128), (256, 768, 768), (4096, 2304, 768),
+                                   (4096, 768, 3072), (1000, 3072, 768), (77, 384, 128), (640, 512, 128)])
+@pytest.mark.parametrize("epi", [0, 1, 2])
+def test_gemm_tcgen05_matches_fp32(spu, M, N, K, epi):
+    g = torch.Generator(device="cpu").manual_seed(M * 7 + N * 3 + K + epi)
+    a = (torch.randn(M, K, generator=g) * 0.5).to(torch.bfloat16).cuda()
+    w = (torch.randn(N, K, generator=g) * 0.05).to(torch.bfloat16).cuda()
+    bias = torch.randn(N, generator=g).cuda()
+    resid = torch.randn(M, N, generator=g).cuda()
+    out = torch.full((M, N), float("nan"), dtype=torch.float32 if epi == 2 else torch.bfloat16, device="cuda")
+    spu.check(spu.lib().spu_gemm_bf16_async(spu.ptr(a), spu.ptr(w), spu.ptr(bias),
+                                            spu.ptr(resid) if epi == 2 else None, spu.ptr(out),
+                                            M, N, K, epi, spu.stream_ptr()))
+    _sync()
+    ref = _gemm_ref(a, w, bias, resid, epi)
+    got = out.float().cpu()
+    assert torch.isfinite(got).all()
+    # fp32 accumulation of exact bf16 products: only summation order + output rounding differ
+    tol = 2e-3 if epi == 2 else 1.2e-2  # bf16 output rounding (2^-8 relative) dominates for epi 0/1
+    err = (got - ref).abs()
+    bound = tol * (ref.abs() + 1.0)
+    bad = (err > bound).sum().item()
+    assert bad == 0, f"{bad} elements off; max err {err.max().item():.4g} at {np.unravel_index(err.argmax().item(), err.shape)}"
+
+
+def test_gemm_inplace_residual(spu):
+    M, N, K = 512, 768, 768
+    g = torch.Generator().manual_seed(5)
+    a = torch.randn(M, K, generator=g).to(torch.bfloat16).cuda()
+    w = (torch.randn(N, K, generator=g) * 0.03).to(torch.bfloat16).cuda()
+    bias = torch.randn(N, generator=g).cuda()
+    x = torch.randn(M, N, generator=g).cuda()
+    ref = _gemm_ref(a, w, bias, x, 2)
+    spu.check(spu.lib().spu_gemm_bf16_async(spu.ptr(a), spu.ptr(w), spu.ptr(bias), spu.ptr(x), spu.ptr(x),
+                                            M, N, K, 2, spu.stream_ptr()))
+    _sync()
+    assert torch.allclose(x.cpu(), ref, rtol=2e-3, atol=2e-3)
+
+
+def test_gemm_rejects_bad_shapes(spu):
+    a = torch.zeros(128, 100, dtype=torch.bfloat16, device="cuda")
+    st = spu.lib().spu_gemm_bf16_async(spu.ptr(a), spu.ptr(a), None, None, spu.ptr(a), 128, 128, 100, 0,
+                                       spu.stream_ptr())
+    assert st == spu.SPU_ERR_UNSUPPORTED
+    assert b"K must be" in spu.lib().spu_last_error()
+
+
+# ---------------------------------------------------------------------- attention
+def _attn_ref(qkv, mask_bias, B, S, heads):
+    H = heads * 64
+    x = qkv.float().cpu().view(B, S, 3, heads, 64)
+    q, k, v = (x[:, :, i].transpose(1, 2) for i in range(3))
+    s = q @ k.transpose(-1, -2) / 8.0 + mask_bias.cpu().view(B, 1, 1, S)
+    return (torch.softmax(s, -1) @ v).transpose(1, 2).reshape(B * S, H)
+
+
+@pytest.mark.parametrize("B,S,heads", [(2, 128, 12), (1, 64, 2), (3, 200, 4), (2, 512, 12), (5, 16, 2), (1, 37, 1)])
+def test_attention_matches_fp32(spu, B, S, heads):
+    g = torch.Generator().manual_seed(B * 100 + S)
+    H = heads * 64
+    qkv = torch.randn(B * S, 3 * H, generator=g).to(torch.bfloat16).cuda()
+    lens = torch.randint(1, S + 1, (B,), generator=g)
+    keep = torch.arange(S)[None, :] < lens[:, None]
+    keep[0] = True
+    mask_bias = torch.where(keep, 0.0, -1e30).float().cuda()
+    ctx = torch.full((B * S, H), float("nan"), dtype=torch.bfloat16, device="cuda")
+    spu.check(spu.lib().spu_attention_async(spu.ptr(qkv), spu.ptr(mask_bias), spu.ptr(ctx), B, S, heads,
+                                            spu.stream_ptr()))
+    _sync()
+    ref = _attn_ref(qkv, mask_bias, B, S, heads)
+    got = ctx.float().cpu()
+    assert torch.isfinite(got).all()
+    # P is rounded to bf16 before PV and the output is bf16
+    assert (got - ref).abs().max().item() < 3e-2, (got - ref).abs().max().item()
+
+
+def test_attention_fully_masked_row_is_uniform(spu):
+    # HF adds finfo.min to every key of a fully padded sequence -> softmax is uniform
+    B, S, heads = 1, 128, 1
+    g = torch.Generator().manual_seed(3)
+    qkv = torch.randn(B * S, 192, generator=g).to(torch.bfloat16).cuda()
+    mask_bias = torch.full((B, S), -1e30, device="cuda")
+    ctx = torch.zeros(B * S, 64, dtype=torch.bfloat16, device="cuda")
+    spu.check(spu.lib().spu_attention_async(spu.ptr(qkv), spu.ptr(mask_bias), spu.ptr(ctx), B, S, heads,
+                                            spu.stream_ptr()))
+    _sync()
+    v_mean = qkv.float().cpu()[:, 128:].mean(0)
+    assert (ctx.float().cpu() - v_mean[None]).abs().max().item() < 2e-2
+
+
+# --------------------------------------------------------------- LayerNorm / embed
+@pytest.mark.parametrize("rows,hidden", [(4096, 768), (33, 128), (1000, 1024), (1, 768)])
+def test_layernorm_matches_oracle(spu, rows, hidden):
+    from oracle.bert_oracle import _ln
+
+    g = torch.Generator().manual_seed(rows + hidden)
+    x = (torch.randn(rows, hidden, generator=g) * 3 + 0.5)
+    gamma, beta = torch.randn(hidden, generator=g), torch.randn(hidden, generator=g)
+    ref = _ln(x, gamma, beta, 1e-12)
+    xd, gd, bd = x.cuda(), gamma.cuda(), beta.cuda()
+    o32 = torch.empty_like(xd)
+    o16 = torch.empty(rows, hidden, dtype=torch.bfloat16, device="cuda")
+    spu.check(spu.lib().spu_layernorm_async(spu.ptr(xd), spu.ptr(gd), spu.ptr(bd), 1e-12, spu.ptr(o32),
+                                            spu.ptr(o16), rows, hidden, spu.stream_ptr()))
+    _sync()
+    assert torch.allclose(o32.cpu(), ref, rtol=1e-4, atol=1e-4)
+    assert torch.equal(o16.cpu(), o32.cpu().to(torch.bfloat16))
+    # in-place variant
+    spu.check(spu.lib().spu_layernorm_async(spu.ptr(xd), spu.ptr(gd), spu.ptr(bd), 1e-12, spu.ptr(xd),
+                                            None, rows, hidden, spu.stream_ptr()))
+    _sync()
+    assert torch.equal(xd.cpu(), o32.cpu())
+
+
+def test_embed_ln_and_mask_bias(spu):
+    from oracle import bert_oracle as bo
+
+    spec = bo.BERT_TINY
+    w = bo.make_weights(spec, 0)
+    ids, mask = bo.make_inputs(spec, 4, 48, seed=5, min_len=3)
+    mask[1] *= 7  # non-binary mask words mean "keep" (reference warm-up feeds randint(0,10))
+    _, layers = bo.bert_forward(w, spec, ids, mask, return_layers=True)
+    t = {k: torch.from_numpy(v).cuda() for k, v in w.items() if k.startswith("embeddings")}
+    B, S, H = 4, 48, spec.hidden
+    x32 = torch.empty(B * S, H, device="cuda")
+    x16 = torch.empty(B * S, H, dtype=torch.bfloat16, device="cuda")
+    mb = torch.empty(B * S, device="cuda")
+    spu.check(spu.lib().spu_bert_embed_async(
+        spu.ptr(torch.from_numpy(ids).cuda()), spu.ptr(torch.from_numpy(mask).cuda()),
+        spu.ptr(t["embeddings.word_embeddings.weight"]), spu.ptr(t["embeddings.position_embeddings.weight"]),
+        spu.ptr(t["embeddings.token_type_embeddings.weight"]), spu.ptr(t["embeddings.LayerNorm.weight"]),
+        spu.ptr(t["embeddings.LayerNorm.bias"]), spec.ln_eps, spec.vocab, spu.ptr(x32), spu.ptr(x16),
+        spu.ptr(mb), B, S, H, spu.stream_ptr()))
+    _sync()
+    assert np.allclose(x32.cpu().numpy().reshape(B, S, H), layers[0], rtol=1e-4, atol=1e-4)
+    assert torch.equal(x16.cpu(), x32.cpu().to(torch.bfloat16))
+    assert np.array_equal(mb.cpu().numpy().reshape(B, S) == 0.0, mask != 0)
+    assert np.all(mb.cpu().numpy().reshape(B, S)[mask == 0] == np.float32(-1e30))
+
+
+# ------------------------------------------------- gather / scatter: bit-exact
+def _dev_table(ptrs):
+    return torch.tensor(ptrs, dtype=torch.int64).cuda()
+
+
+@pytest.mark.parametrize("lens,seq", [([128] * 8, 128), ([16, 512, 77, 1, 300, 0, 511], 512),
+                                      ([5], 8), ([3, 3, 3], 3)])
+@pytest.mark.parametrize("with_mask", [False, True])
+def test_gather_pad_mask_bit_exact(spu, oracle_gs, lens, seq, with_mask):
+    rng = np.random.Generator(np.random.PCG64(len(lens) * 1000 + seq))
+    n = len(lens)
+    src = [rng.integers(-2**62, 2**62, size=max(L, 1), dtype=np.int64) for L in lens]
+    msk = [rng.integers(0, 10, size=max(L, 1), dtype=np.int64) for L in lens]
+    # oracle
+    ids_o = np.full((n, seq), -1, np.int64)
+    mask_o = np.full((n, seq), -1, np.int64)
+    PP = C.c_void_p * n
+    lens_np = np.asarray(lens, np.int32)
+    rc = oracle_gs.oracle_gather_pad_mask(PP(*[s.ctypes.data for s in src]),
+                                          PP(*[m.ctypes.data for m in msk]) if with_mask else None,
+                                          lens_np.ctypes.data_as(C.c_void_p), C.c_size_t(n), C.c_size_t(seq),
+                                          C.c_int64(0), ids_o.ctypes.data_as(C.c_void_p),
+                                          mask_o.ctypes.data_as(C.c_void_p))
+    assert rc == 0
+    # device
+    dsrc = [torch.from_numpy(s).cuda() for s in src]
+    dmsk = [torch.from_numpy(m).cuda() for m in msk]
+    ids_d = torch.full((n, seq), -1, dtype=torch.int64, device="cuda")
+    mask_d = torch.full((n, seq), -1, dtype=torch.int64, device="cuda")
+    spu.check(spu.lib().spu_gather_pad_mask_async(
+        spu.ptr(_dev_table([t.data_ptr() for t in dsrc])),
+        spu.ptr(_dev_table([t.data_ptr() for t in dmsk])) if with_mask else None,
+        spu.ptr(torch.from_numpy(lens_np).cuda()), n, seq, 0, spu.ptr(ids_d), spu.ptr(mask_d),
+        spu.stream_ptr()))
+    _sync()
+    assert np.array_equal(ids_d.cpu().numpy(), ids_o)
+    assert np.array_equal(mask_d.cpu().numpy(), mask_o)
+
+
+def test_gather_full_length_equals_reference_concat(spu, oracle_gs):
+    """All lens == seq: stage 1 must reproduce copy_job_inputs_to_slot byte for byte."""
+    rng = np.random.Generator(np.random.PCG64(9))
+    n, seq = 6, 128
+    src = [rng.integers(0, 30522, size=seq, dtype=np.int64) for _ in range(n)]
+    slot = np.zeros(n * seq, np.int64)
+    nb = (C.c_size_t * n)(*[s.nbytes for s in src])
+    ne = (C.c_size_t * n)(*[s.size for s in src])
+    nx, by = C.c_size_t(), C.c_size_t()
+    rc = oracle_gs.oracle_gather_concat((C.c_void_p * n)(*[s.ctypes.data for s in src]), nb, ne, C.c_size_t(n),
+                                        slot.ctypes.data_as(C.c_void_p), C.c_size_t(slot.nbytes),
+                                        C.byref(nx), C.byref(by))
+    assert rc == 0 and nx.value == n * seq
+    dsrc = [torch.from_numpy(s).cuda() for s in src]
+    ids_d = torch.empty(n, seq, dtype=torch.int64, device="cuda")
+    mask_d = torch.empty(n, seq, dtype=torch.int64, device="cuda")
+    spu.check(spu.lib().spu_gather_pad_mask_async(
+        spu.ptr(_dev_table([t.data_ptr() for t in dsrc])), None,
+        spu.ptr(torch.full((n,), seq, dtype=torch.int32, device="cuda")), n, seq, 0, spu.ptr(ids_d),
+        spu.ptr(mask_d), spu.stream_ptr()))
+    _sync()
+    assert np.array_equal(ids_d.cpu().numpy().ravel(), slot)
+    assert (mask_d == 1).all()
+
+
+@pytest.mark.parametrize("sizes", [[393216] * 5, [4000, 8000, 4000], [1, 17, 393216 + 3, 0, 64]])
+def test_scatter_and_gather_segments_bit_exact(spu, oracle_gs, sizes):
+    rng = np.random.Generator(np.random.PCG64(sum(sizes)))
+    total = sum(sizes)
+    agg = rng.integers(0, 256, size=total, dtype=np.uint8)
+    offs = np.concatenate([[0], np.cumsum(sizes)[:-1]]).astype(np.uint64)
+    # oracle: contiguous dim-0 slices (rows are bytes here)
+    ref = []
+    for o, s in zip(offs, sizes):
+        d = np.zeros(max(s, 1), np.uint8)
+        got = C.c_int64()
+        if s:
+            rc = oracle_gs.oracle_scatter_slice(agg.ctypes.data_as(C.c_void_p), C.c_size_t(total), C.c_size_t(total),
+                                                C.c_int64(int(o)), C.c_int64(s), d.ctypes.data_as(C.c_void_p),
+                                                C.byref(got))
+            assert rc == 0 and got.value == s
+        ref.append(d[:s])
+    agg_d = torch.from_numpy(agg).cuda()
+    dsts = [torch.zeros(max(s, 1), dtype=torch.uint8, device="cuda") for s in sizes]
+    off_d = torch.from_numpy(offs.astype(np.int64)).cuda()
+    nb_d = torch.tensor(sizes, dtype=torch.int64).cuda()
+    spu.check(spu.lib().spu_scatter_segments_async(spu.ptr(agg_d), spu.ptr(off_d), spu.ptr(nb_d),
+                                                   spu.ptr(_dev_table([t.data_ptr() for t in dsts])),
+                                                   len(sizes), spu.stream_ptr()))
+    _sync()
+    for d, r, s in zip(dsts, ref, sizes):
+        assert np.array_equal(d.cpu().numpy()[:s], r)
+    # and back: gather the per-request buffers into one contiguous batch (round trip)
+    back = torch.zeros(max(total, 1), dtype=torch.uint8, device="cuda")
+    spu.check(spu.lib().spu_gather_segments_async(spu.ptr(_dev_table([t.data_ptr() for t in dsts])),
+                                                  spu.ptr(off_d), spu.ptr(nb_d), len(sizes), spu.ptr(back),
+                                                  spu.stream_ptr()))
+    _sync()
+    assert np.array_equal(back.cpu().numpy()[:total], agg)
+
+
+def test_empty_batches_are_noops(spu):
+    assert spu.lib().spu_gather_pad_mask_async(None, None, None, 0, 128, 0, None, None, spu.stream_ptr()) == 0
+    assert spu.lib().spu_scatter_segments_async(None, None, None, None, 0, spu.stream_ptr()) == 0
+    assert spu.lib().spu_affine_f32_async(None, None, 0, 1.0, 0.0, spu.stream_ptr()) == 0
+
+
+def test_affine_known_answers(spu):
+    """x+1 on {1,2,3} -> {2,3,4} (reference tests/integration/starpu/integration_starpu_setup.cpp:42-60)
+    and x+1.5 (tests/unit/core/unit_starpu_setup.cpp:2332-2433)."""
+    x = torch.tensor([1.0, 2.0, 3.0], device="cuda")
+    y = torch.empty_like(x)
+    spu.check(spu.lib().spu_affine_f32_async(spu.ptr(x), spu.ptr(y), 3, 1.0, 1.0, spu.stream_ptr()))
+    _sync()
+    assert y.cpu().tolist() == [2.0, 3.0, 4.0]
+    spu.check(spu.lib().spu_affine_f32_async(spu.ptr(x), spu.ptr(y), 3, 1.0, 1.5, spu.stream_ptr()))
+    _sync()
+    assert y.cpu().tolist() == [2.5, 3.5, 4.5]
