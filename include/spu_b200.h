@@ -103,6 +103,24 @@ spu_status spu_bert_forward_capture(spu_replica *r, int32_t ws_idx,
                                     int32_t batch, int32_t seq, float *out,
                                     void *stream);
 
+/* Measurement hook (bench.py, not the codelet path): runs one forward with a CUDA
+ * event recorded after every kernel, SYNCHRONISES `stream`, and adds the device time
+ * of each kernel class (summed over layers, milliseconds) into stage_ms[SPU_STAGE_COUNT].
+ * Never replays a captured graph. */
+#define SPU_STAGE_EMBED 0      /* embedding gather + LayerNorm + mask-bias builder   */
+#define SPU_STAGE_GEMM_QKV 1   /* [M,H] x [3H,H]^T + bias                            */
+#define SPU_STAGE_ATTENTION 2  /* fused masked-softmax attention                     */
+#define SPU_STAGE_GEMM_OUT 3   /* [M,H] x [H,H]^T + bias + residual                  */
+#define SPU_STAGE_LN1 4
+#define SPU_STAGE_GEMM_FFN1 5  /* [M,H] x [F,H]^T + bias, erf GELU                   */
+#define SPU_STAGE_GEMM_FFN2 6  /* [M,F] x [H,F]^T + bias + residual                  */
+#define SPU_STAGE_LN2 7        /* last layer: writes fp32 output0                    */
+#define SPU_STAGE_COUNT 8
+spu_status spu_bert_forward_profiled(spu_replica *r, int32_t ws_idx,
+                                     const int64_t *ids, const int64_t *mask,
+                                     int32_t batch, int32_t seq, float *out,
+                                     void *stream, float *stage_ms);
+
 /* ---- Stage 1: gather + pad + mask (device) --------------------------------
  * Ragged batch assembly: request i supplies len[i] int64 token ids at
  * src_ids[i] (and optionally len[i] mask words at src_mask[i]; src_mask or

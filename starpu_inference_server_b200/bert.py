@@ -103,6 +103,15 @@ class BertReplica:
                                                      capi.ptr(out), capi.stream_ptr(stream)))
         return out
 
+    def forward_profiled(self, ids, mask, out, ws: int = 0, stream=None):
+        """Measurement hook: one forward with per-kernel CUDA events; returns
+        {stage name: device ms summed over layers}.  Synchronises the stream."""
+        b, s = ids.shape
+        ms = (C.c_float * len(capi.STAGE_NAMES))()
+        capi.check(capi.lib().spu_bert_forward_profiled(self._h, ws, capi.ptr(ids), capi.ptr(mask), b, s,
+                                                        capi.ptr(out), capi.stream_ptr(stream), ms))
+        return dict(zip(capi.STAGE_NAMES, list(ms)))
+
     def capture(self, ids, mask, out, ws: int = 0, stream=None):
         b, s = ids.shape
         capi.check(capi.lib().spu_bert_forward_capture(self._h, ws, capi.ptr(ids), capi.ptr(mask), b, s,

@@ -178,6 +178,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
         }
       }
     }
+    __syncwarp();  // reconverge before the CTA-wide barrier below
   } else if (warp_idx == 1) {
     // ===================== MMA issuer =====================
     if (lane == 0) {
@@ -215,6 +216,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
         }
       }
     }
+    __syncwarp();
   } else if (warp_idx >= kEpiWarp0) {
     // ===================== epilogue =====================
     const int q = warp_idx - kEpiWarp0;  // == warp_idx % 4: TMEM lane quarter this warp may read

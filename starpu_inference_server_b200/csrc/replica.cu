@@ -68,6 +68,22 @@ struct CapturedGraph {
   cudaGraphExec_t exec = nullptr;
 };
 
+// Optional per-kernel event trail (measurement hook only).
+struct StageTrail {
+  std::vector<cudaEvent_t> ev;  // ev[0] = start, ev[i+1] recorded after launch i
+  std::vector<int> stage;       // stage id of launch i
+  size_t n = 0;
+  spu_status mark(int stage_id, cudaStream_t s) {
+    if (n + 1 >= ev.size()) {
+      set_error("profiling: event trail too short");
+      return SPU_ERR_INVALID;
+    }
+    stage[n] = stage_id;
+    SPU_CUDA_TRY(cudaEventRecord(ev[++n], s));
+    return SPU_OK;
+  }
+};
+
 struct Workspace {
   float *x_f32 = nullptr;
   __nv_bfloat16 *x_bf16 = nullptr, *qkv = nullptr, *ctx = nullptr, *h = nullptr;
@@ -196,13 +212,20 @@ spu_status build(spu_replica *r, const float *const *t) {
   return SPU_OK;
 }
 
+#define SPU_MARK(id)                                  \
+  do {                                                \
+    if (trail != nullptr) SPU_TRY(trail->mark((id), stream)); \
+  } while (0)
+
 spu_status enqueue_forward(spu_replica *r, Workspace &ws, const int64_t *ids, const int64_t *mask,
-                           int batch, int seq, float *out, cudaStream_t stream) {
+                           int batch, int seq, float *out, cudaStream_t stream,
+                           StageTrail *trail = nullptr) {
   const spu_bert_desc &d = r->desc;
   const int M = batch * seq;
   SPU_TRY(bert_embed_launch(ids, mask, r->word, r->pos, r->type0, r->emb_g, r->emb_b, d.ln_eps,
                             d.vocab, ws.x_f32, ws.x_bf16, ws.mask_bias, batch, seq, d.hidden,
                             stream));
+  SPU_MARK(SPU_STAGE_EMBED);
   for (int l = 0; l < d.layers; ++l) {
     const LayerWeights &w = r->layers[l];
     const LayerPlans &p = ws.plans[l];
@@ -212,24 +235,31 @@ spu_status enqueue_forward(spu_replica *r, Workspace &ws, const int64_t *ids, co
     e.bias = w.b_qkv;
     e.out = ws.qkv;
     SPU_TRY(gemm_launch(p.qkv, M, e, stream));
+    SPU_MARK(SPU_STAGE_GEMM_QKV);
     SPU_TRY(attention_launch(ws.qkv, ws.mask_bias, ws.ctx, batch, seq, d.heads, stream));
+    SPU_MARK(SPU_STAGE_ATTENTION);
     e.bias = w.b_o;
     e.resid = ws.x_f32;
     e.out = ws.x_f32;  // in place: each element is read then written by the same thread
     SPU_TRY(gemm_launch(p.attn_out, M, e, stream));
+    SPU_MARK(SPU_STAGE_GEMM_OUT);
     SPU_TRY(layernorm_launch(ws.x_f32, w.ln1_g, w.ln1_b, d.ln_eps, ws.x_f32, ws.x_bf16, M,
                              d.hidden, stream));
+    SPU_MARK(SPU_STAGE_LN1);
     e.bias = w.b_1;
     e.resid = nullptr;
     e.out = ws.h;
     SPU_TRY(gemm_launch(p.ffn1, M, e, stream));
+    SPU_MARK(SPU_STAGE_GEMM_FFN1);
     e.bias = w.b_2;
     e.resid = ws.x_f32;
     e.out = ws.x_f32;
     SPU_TRY(gemm_launch(p.ffn2, M, e, stream));
+    SPU_MARK(SPU_STAGE_GEMM_FFN2);
     // the last LayerNorm writes last_hidden_state straight into the StarPU output buffer
     SPU_TRY(layernorm_launch(ws.x_f32, w.ln2_g, w.ln2_b, d.ln_eps, last ? out : ws.x_f32,
                              last ? nullptr : ws.x_bf16, M, d.hidden, stream));
+    SPU_MARK(SPU_STAGE_LN2);
   }
   return SPU_OK;
 }
@@ -345,6 +375,37 @@ extern "C" spu_status spu_bert_forward_capture(spu_replica *r, int32_t ws_idx, c
   SPU_CUDA_TRY(e);
   ws.graphs.push_back(cg);
   return SPU_OK;
+}
+
+extern "C" spu_status spu_bert_forward_profiled(spu_replica *r, int32_t ws_idx, const int64_t *ids,
+                                                const int64_t *mask, int32_t batch, int32_t seq,
+                                                float *out, void *stream, float *stage_ms) {
+  SPU_TRY(check_forward_args(r, ws_idx, ids, mask, batch, seq, out));
+  SPU_REQUIRE(stage_ms != nullptr, SPU_ERR_INVALID, "profiled: null stage_ms");
+  DeviceGuard guard(r->device);
+  StageTrail trail;
+  const size_t n_launch = static_cast<size_t>(spu_bert_forward_launch_count(r));
+  trail.ev.resize(n_launch + 1, nullptr);
+  trail.stage.resize(n_launch, 0);
+  spu_status st = SPU_OK;
+  for (cudaEvent_t &e : trail.ev)
+    if (cudaEventCreate(&e) != cudaSuccess) st = SPU_ERR_CUDA;
+  cudaStream_t s = as_stream(stream);
+  if (st == SPU_OK && cudaEventRecord(trail.ev[0], s) != cudaSuccess) st = SPU_ERR_CUDA;
+  if (st == SPU_OK) st = enqueue_forward(r, r->ws[ws_idx], ids, mask, batch, seq, out, s, &trail);
+  if (st == SPU_OK && cudaStreamSynchronize(s) != cudaSuccess) {
+    set_error(std::string("profiled forward: ") + cudaGetErrorString(cudaGetLastError()));
+    st = SPU_ERR_CUDA;
+  }
+  if (st == SPU_OK)
+    for (size_t i = 0; i < trail.n; ++i) {
+      float ms = 0.f;
+      if (cudaEventElapsedTime(&ms, trail.ev[i], trail.ev[i + 1]) == cudaSuccess)
+        stage_ms[trail.stage[i]] += ms;
+    }
+  for (cudaEvent_t e : trail.ev)
+    if (e) cudaEventDestroy(e);
+  return st;
 }
 
 extern "C" int32_t spu_bert_forward_launch_count(const spu_replica *r) {

@@ -162,8 +162,9 @@ def test_embed_ln_and_mask_bias(spu):
     x32 = torch.empty(B * S, H, device="cuda")
     x16 = torch.empty(B * S, H, dtype=torch.bfloat16, device="cuda")
     mb = torch.empty(B * S, device="cuda")
+    ids_d, mask_d = torch.from_numpy(ids).cuda(), torch.from_numpy(mask).cuda()  # keep alive
     spu.check(spu.lib().spu_bert_embed_async(
-        spu.ptr(torch.from_numpy(ids).cuda()), spu.ptr(torch.from_numpy(mask).cuda()),
+        spu.ptr(ids_d), spu.ptr(mask_d),
         spu.ptr(t["embeddings.word_embeddings.weight"]), spu.ptr(t["embeddings.position_embeddings.weight"]),
         spu.ptr(t["embeddings.token_type_embeddings.weight"]), spu.ptr(t["embeddings.LayerNorm.weight"]),
         spu.ptr(t["embeddings.LayerNorm.bias"]), spec.ln_eps, spec.vocab, spu.ptr(x32), spu.ptr(x16),
@@ -204,10 +205,11 @@ def test_gather_pad_mask_bit_exact(spu, oracle_gs, lens, seq, with_mask):
     dmsk = [torch.from_numpy(m).cuda() for m in msk]
     ids_d = torch.full((n, seq), -1, dtype=torch.int64, device="cuda")
     mask_d = torch.full((n, seq), -1, dtype=torch.int64, device="cuda")
+    tab_i, tab_m = _dev_table([t.data_ptr() for t in dsrc]), _dev_table([t.data_ptr() for t in dmsk])
+    lens_d = torch.from_numpy(lens_np).cuda()  # device temporaries must outlive the async call
     spu.check(spu.lib().spu_gather_pad_mask_async(
-        spu.ptr(_dev_table([t.data_ptr() for t in dsrc])),
-        spu.ptr(_dev_table([t.data_ptr() for t in dmsk])) if with_mask else None,
-        spu.ptr(torch.from_numpy(lens_np).cuda()), n, seq, 0, spu.ptr(ids_d), spu.ptr(mask_d),
+        spu.ptr(tab_i), spu.ptr(tab_m) if with_mask else None,
+        spu.ptr(lens_d), n, seq, 0, spu.ptr(ids_d), spu.ptr(mask_d),
         spu.stream_ptr()))
     _sync()
     assert np.array_equal(ids_d.cpu().numpy(), ids_o)
@@ -230,9 +232,10 @@ def test_gather_full_length_equals_reference_concat(spu, oracle_gs):
     dsrc = [torch.from_numpy(s).cuda() for s in src]
     ids_d = torch.empty(n, seq, dtype=torch.int64, device="cuda")
     mask_d = torch.empty(n, seq, dtype=torch.int64, device="cuda")
+    tab = _dev_table([t.data_ptr() for t in dsrc])
+    lens_d = torch.full((n,), seq, dtype=torch.int32, device="cuda")
     spu.check(spu.lib().spu_gather_pad_mask_async(
-        spu.ptr(_dev_table([t.data_ptr() for t in dsrc])), None,
-        spu.ptr(torch.full((n,), seq, dtype=torch.int32, device="cuda")), n, seq, 0, spu.ptr(ids_d),
+        spu.ptr(tab), None, spu.ptr(lens_d), n, seq, 0, spu.ptr(ids_d),
         spu.ptr(mask_d), spu.stream_ptr()))
     _sync()
     assert np.array_equal(ids_d.cpu().numpy().ravel(), slot)
@@ -260,17 +263,16 @@ def test_scatter_and_gather_segments_bit_exact(spu, oracle_gs, sizes):
     dsts = [torch.zeros(max(s, 1), dtype=torch.uint8, device="cuda") for s in sizes]
     off_d = torch.from_numpy(offs.astype(np.int64)).cuda()
     nb_d = torch.tensor(sizes, dtype=torch.int64).cuda()
+    tab = _dev_table([t.data_ptr() for t in dsts])
     spu.check(spu.lib().spu_scatter_segments_async(spu.ptr(agg_d), spu.ptr(off_d), spu.ptr(nb_d),
-                                                   spu.ptr(_dev_table([t.data_ptr() for t in dsts])),
-                                                   len(sizes), spu.stream_ptr()))
+                                                   spu.ptr(tab), len(sizes), spu.stream_ptr()))
     _sync()
     for d, r, s in zip(dsts, ref, sizes):
         assert np.array_equal(d.cpu().numpy()[:s], r)
     # and back: gather the per-request buffers into one contiguous batch (round trip)
     back = torch.zeros(max(total, 1), dtype=torch.uint8, device="cuda")
-    spu.check(spu.lib().spu_gather_segments_async(spu.ptr(_dev_table([t.data_ptr() for t in dsts])),
-                                                  spu.ptr(off_d), spu.ptr(nb_d), len(sizes), spu.ptr(back),
-                                                  spu.stream_ptr()))
+    spu.check(spu.lib().spu_gather_segments_async(spu.ptr(tab), spu.ptr(off_d), spu.ptr(nb_d),
+                                                  len(sizes), spu.ptr(back), spu.stream_ptr()))
     _sync()
     assert np.array_equal(back.cpu().numpy()[:total], agg)
 
