@@ -160,13 +160,22 @@ spu_status spu_scatter_segments_async(const void *src, const uint64_t *src_off,
 #define SPU_EPI_BIAS_RESID 2  /* out_f32  = A W^T + bias + resid_f32           */
 
 /* C = A[M,K](bf16,row-major) * W[N,K]^T(bf16,row-major) with fused epilogue on
- * tcgen05/TMEM, operands staged by TMA.  K % 64 == 0, N % 64 == 0.  `out` is
- * bf16 [M,N] for BIAS/BIAS_GELU, fp32 [M,N] for BIAS_RESID (resid may alias out).
- * Creates its tensor maps per call (test path; the replica caches them). */
+ * tcgen05/TMEM, operands staged by TMA, output staged in smem and TMA-stored.
+ * K % 64 == 0, N % 64 == 0, all pointers 16-byte aligned.  `out` is bf16 [M,N] for
+ * BIAS/BIAS_GELU, fp32 [M,N] for BIAS_RESID (resid may alias out).
+ * Creates its tensor maps per call (test path; the replica caches the weight maps). */
 spu_status spu_gemm_bf16_async(const void *A, const void *W, const float *bias,
                                const float *resid, void *out, int32_t M,
                                int32_t N, int32_t K, int32_t epilogue,
                                void *stream);
+
+/* Same GEMM with the tile shape forced (tests / tile sweeps): cta_group 1 = one CTA per
+ * 128 x block_n tile, 2 = a CTA pair per 256 x block_n tile; block_n in {64,128,192,256}
+ * dividing N.  cta_group == 0 lets the library choose as spu_gemm_bf16_async does. */
+spu_status spu_gemm_bf16_cfg_async(const void *A, const void *W, const float *bias,
+                                   const float *resid, void *out, int32_t M,
+                                   int32_t N, int32_t K, int32_t epilogue,
+                                   int32_t cta_group, int32_t block_n, void *stream);
 
 /* Fused masked-softmax attention.  qkv: bf16 [batch*seq, 3*heads*64] (q|k|v);
  * mask_bias: fp32 [batch, seq] additive (0 keep, large negative drop);

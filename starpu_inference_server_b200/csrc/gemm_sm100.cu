@@ -1,140 +1,142 @@
-// tcgen05/TMEM GEMM, TMA operand staging, warp-specialised persistent kernel.
+// tcgen05/TMEM GEMM, TMA operand staging, warp-specialised persistent kernel with a
+// smem-staged, TMA-stored epilogue.  One kernel template covers two tile shapes:
+//   cta_group::1  : one CTA  owns a 128 x BLOCK_N tile  (small M)
+//   cta_group::2  : a CTA pair (cluster of 2, one TPC) owns a 256 x BLOCK_N tile; each
+//                   CTA stages its own 128 A rows and HALF of the B rows, so L2->smem
+//                   traffic per FLOP drops by a third against the 128-row tile.
 //
-// Roles (256 threads, 1 CTA per SM, grid = min(#tiles, #SMs)):
-//   warp 0 lane 0 : TMA producer  (global -> SWIZZLE_128B smem ring, mbarrier tx-count)
-//   warp 1 lane 0 : MMA issuer    (tcgen05.mma 128 x BLOCK_N x 16, fp32 accum in TMEM,
-//                                  tcgen05.commit releases smem stages / publishes tiles)
+// Roles (384 threads, 1 CTA per SM, grid = cta_group x min(#tiles, #SMs / cta_group)):
+//   warp 0 lane 0 : TMA producer  (global -> SWIZZLE_128B smem ring, mbarrier tx-count;
+//                   in a pair both CTAs' loads credit the LEADER CTA's full barrier)
+//   warp 1 lane 0 : MMA issuer    (leader CTA only: tcgen05.mma (128|256) x BLOCK_N x 16,
+//                   fp32 accumulators in TMEM; tcgen05.commit frees smem stages in both
+//                   CTAs and publishes finished accumulators)
 //   warp 2        : TMEM allocator (2 accumulator buffers -> epilogue overlaps next tile)
-//   warps 4..7    : epilogue (tcgen05.ld 32 lanes x 32 cols per warp; thread == output row)
+//   warps 4..11   : epilogue.  Warp w reads TMEM lane quarter w%4; warps 4-7 take the low
+//                   half of the tile's columns, 8-11 the high half.  Per 32-column chunk:
+//                   tcgen05.ld 32x32b.x32 -> bias / GELU / residual in registers ->
+//                   swizzled st.shared (conflict-free) -> one TMA store per 32x32 chunk
+//                   (coalesced, clips the M tail).  The fp32 residual chunk is TMA-loaded
+//                   into the same staging slot two chunks ahead and updated in place.
 //
 // Replaces the cuBLAS/ATen GEMMs LibTorch picks inside Module::forward
 // (/root/reference/src/core/starpu_setup.cpp:610) for the QKV, attention-output and
 // FFN projections of HF BertModel (oracle/bert_oracle.py).
 #include "gemm_sm100.cuh"
 
+#include <cstdlib>
 #include <mutex>
 
 namespace spu {
 
 namespace {
 
-constexpr int kBlockM = 128;
+constexpr int kRowsPerCta = 128;
 constexpr int kTileKBytes = 128;  // one SWIZZLE_128B row: 64 bf16 or 128 e4m3
 constexpr int kUmmaKBytes = 32;   // K=16 bf16 / K=32 e4m3 per tcgen05.mma
-constexpr int kThreads = 256;
 constexpr int kEpiWarp0 = 4;
-constexpr int kABytes = kBlockM * kTileKBytes;  // 16 KiB
-constexpr int kSmemBudget = 227 * 1024 - 2048;  // leave room for alignment + barriers
+constexpr int kNumEpiWarps = 8;
+constexpr int kThreads = (kEpiWarp0 + kNumEpiWarps) * 32;  // 384
+constexpr int kABytes = kRowsPerCta * kTileKBytes;          // 16 KiB
+constexpr int kSmemMax = 227 * 1024;
+constexpr int kBarrierBytes = 512;
+constexpr int kMaxStages = 8;
 
-template <int BLOCK_N>
+template <int EPI>
+struct EpiTraits {
+  // bytes of one staged 32x32 output chunk
+  static constexpr int kElemBytes = EPI == kEpiBiasResid ? 4 : (EPI == kEpiBiasGeluE4m3 ? 1 : 2);
+  static constexpr int kChunkBytes = 32 * 32 * kElemBytes;
+  static constexpr int kWarpBytes = 2 * kChunkBytes;  // double-buffered per warp
+};
+
+template <int BLOCK_N, int CG, int EPI>
 struct TileCfg {
-  static constexpr int kBBytes = BLOCK_N * kTileKBytes;
+  static constexpr int kBRows = BLOCK_N / CG;  // B rows staged by one CTA
+  static constexpr int kBBytes = kBRows * kTileKBytes;
   static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kStagesRaw = kSmemBudget / kStageBytes;
-  static constexpr int kStages = kStagesRaw > 8 ? 8 : kStagesRaw;
+  static constexpr int kStagingBytes = kNumEpiWarps * EpiTraits<EPI>::kWarpBytes;
+  static constexpr int kStagesRaw = (kSmemMax - 1024 - kStagingBytes - kBarrierBytes) / kStageBytes;
+  static constexpr int kStages = kStagesRaw > kMaxStages ? kMaxStages : kStagesRaw;
   static constexpr int kTmemCols = (2 * BLOCK_N <= 32)    ? 32
                                    : (2 * BLOCK_N <= 64)  ? 64
                                    : (2 * BLOCK_N <= 128) ? 128
                                    : (2 * BLOCK_N <= 256) ? 256
                                                           : 512;
-  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align*/ + 256 /*barriers*/;
+  static constexpr int kSmemBytes = 1024 + kStages * kStageBytes + kStagingBytes + kBarrierBytes;
+  static_assert(kStages >= 3, "pipeline too shallow");
+  static_assert((BLOCK_N / 2) % 32 == 0, "each epilogue warp half must be whole 32-column chunks");
 };
 
 struct KernelArgs {
   int M, N, K;
-  GemmEpilogueArgs epi;
+  const float *bias;
+  float acc_scale;
+  float out_inv_scale;
 };
 
-template <int EPI>
-__device__ __forceinline__ void epilogue_chunk(const uint32_t (&v)[32], const KernelArgs &a,
-                                               int row, int col0, bool row_ok) {
-  // 32 consecutive output columns of one row live in this thread.
-  float f[32];
-#pragma unroll
-  for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]) * a.epi.acc_scale;
-  if (a.epi.bias != nullptr) {
-    const float4 *b4 = reinterpret_cast<const float4 *>(a.epi.bias + col0);
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const float4 b = __ldg(b4 + j);
-      f[4 * j + 0] += b.x;
-      f[4 * j + 1] += b.y;
-      f[4 * j + 2] += b.z;
-      f[4 * j + 3] += b.w;
-    }
-  }
-  if constexpr (EPI == SPU_EPI_BIAS_GELU) {
-#pragma unroll
-    for (int j = 0; j < 32; ++j) f[j] = gelu_erf(f[j]);
-  }
-  if (!row_ok) return;
-  const size_t off = static_cast<size_t>(row) * a.N + col0;
-  if constexpr (EPI == SPU_EPI_BIAS_RESID) {
-    const float4 *r4 = reinterpret_cast<const float4 *>(a.epi.resid + off);
-    float4 *o4 = reinterpret_cast<float4 *>(static_cast<float *>(a.epi.out) + off);
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const float4 r = r4[j];
-      o4[j] = make_float4(f[4 * j] + r.x, f[4 * j + 1] + r.y, f[4 * j + 2] + r.z,
-                          f[4 * j + 3] + r.w);
-    }
-  } else {
-    uint4 *o4 = reinterpret_cast<uint4 *>(static_cast<__nv_bfloat16 *>(a.epi.out) + off);
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      o4[j] = make_uint4(pack_bf16(f[8 * j], f[8 * j + 1]), pack_bf16(f[8 * j + 2], f[8 * j + 3]),
-                         pack_bf16(f[8 * j + 4], f[8 * j + 5]),
-                         pack_bf16(f[8 * j + 6], f[8 * j + 7]));
-    }
-    if (a.epi.out_fp8 != nullptr) {
-      // per-tensor scaled e4m3 copy for a following FP8 GEMM
-      uint32_t w[8];
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const float s = a.epi.out_fp8_inv_scale;
-        uint16_t lo, hi;
-        asm("cvt.rn.satfinite.e4m3x2.f32 %0, %1, %2;" : "=h"(lo) : "f"(f[4 * j + 1] * s), "f"(f[4 * j] * s));
-        asm("cvt.rn.satfinite.e4m3x2.f32 %0, %1, %2;" : "=h"(hi) : "f"(f[4 * j + 3] * s), "f"(f[4 * j + 2] * s));
-        w[j] = static_cast<uint32_t>(lo) | (static_cast<uint32_t>(hi) << 16);
-      }
-      uint4 *q4 = reinterpret_cast<uint4 *>(static_cast<uint8_t *>(a.epi.out_fp8) + off);
-      q4[0] = make_uint4(w[0], w[1], w[2], w[3]);
-      q4[1] = make_uint4(w[4], w[5], w[6], w[7]);
-    }
-  }
+__device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c,
+                                             uint32_t d) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d)
+               : "memory");
+}
+__device__ __forceinline__ float4 ld_shared_f4(uint32_t addr) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ uint32_t pack_e4m3x4(float a, float b, float c, float d) {
+  uint16_t lo, hi;
+  asm("cvt.rn.satfinite.e4m3x2.f32 %0, %1, %2;" : "=h"(lo) : "f"(b), "f"(a));
+  asm("cvt.rn.satfinite.e4m3x2.f32 %0, %1, %2;" : "=h"(hi) : "f"(d), "f"(c));
+  return static_cast<uint32_t>(lo) | (static_cast<uint32_t>(hi) << 16);
 }
 
-template <int BLOCK_N, int EPI, int IN_FP8>
+template <int BLOCK_N, int CG, int EPI, int IN_FP8>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
-                    const __grid_constant__ CUtensorMap tmap_b, const KernelArgs args) {
-  using Cfg = TileCfg<BLOCK_N>;
+                    const __grid_constant__ CUtensorMap tmap_b,
+                    const __grid_constant__ CUtensorMap tmap_out,
+                    const __grid_constant__ CUtensorMap tmap_resid, const KernelArgs args) {
+  using Cfg = TileCfg<BLOCK_N, CG, EPI>;
+  using Epi = EpiTraits<EPI>;
   constexpr int kStages = Cfg::kStages;
   constexpr int kStageBytes = Cfg::kStageBytes;
-  constexpr uint32_t kIdesc = make_idesc(IN_FP8 ? 0u : 1u, kBlockM, BLOCK_N);
+  constexpr uint32_t kIdesc = make_idesc(IN_FP8 ? 0u : 1u, kRowsPerCta * CG, BLOCK_N);
   constexpr int kElemsPerKBlock = IN_FP8 ? 128 : 64;
+  constexpr int kTileM = kRowsPerCta * CG;
+  constexpr int kChunksPerWarp = BLOCK_N / 2 / 32;
 
   extern __shared__ uint8_t smem_raw[];
   // SWIZZLE_128B tiles need 1024-byte aligned bases.
   const uint32_t raw_addr = smem_u32(smem_raw);
   uint8_t *smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
-  uint64_t *full_bar = reinterpret_cast<uint64_t *>(smem + kStages * kStageBytes);
-  uint64_t *empty_bar = full_bar + kStages;
-  uint64_t *tmem_full_bar = empty_bar + kStages;
+  uint8_t *staging = smem + kStages * kStageBytes;
+  uint64_t *full_bar = reinterpret_cast<uint64_t *>(staging + Cfg::kStagingBytes);
+  uint64_t *empty_bar = full_bar + kMaxStages;
+  uint64_t *tmem_full_bar = empty_bar + kMaxStages;
   uint64_t *tmem_empty_bar = tmem_full_bar + 2;
-  uint32_t *tmem_ptr_smem = reinterpret_cast<uint32_t *>(tmem_empty_bar + 2);
+  uint64_t *resid_bar = tmem_empty_bar + 2;  // [kNumEpiWarps][2]
+  uint32_t *tmem_ptr_smem = reinterpret_cast<uint32_t *>(resid_bar + 2 * kNumEpiWarps);
 
   const int warp_idx = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  const uint32_t cta_rank = CG == 2 ? cluster_ctarank() : 0u;
+  const int unit = static_cast<int>(blockIdx.x) / CG;       // tile-owning CTA (pair) index
+  const int num_units = static_cast<int>(gridDim.x) / CG;
 
   const int n_blocks = args.N / BLOCK_N;
-  const int m_blocks = (args.M + kBlockM - 1) / kBlockM;
+  const int m_blocks = (args.M + kTileM - 1) / kTileM;
   const int num_tiles = n_blocks * m_blocks;
   const int num_k_blocks = args.K / kElemsPerKBlock;
 
   if (warp_idx == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_a);
     tma_prefetch_desc(&tmap_b);
+    tma_prefetch_desc(&tmap_out);
+    if constexpr (EPI == kEpiBiasResid) tma_prefetch_desc(&tmap_resid);
   }
   if (warp_idx == 1 && lane == 0) {
     for (int s = 0; s < kStages; ++s) {
@@ -143,34 +145,52 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(&tmem_full_bar[s], 1);
-      mbar_init(&tmem_empty_bar[s], 4);  // one arrive per epilogue warp
+      mbar_init(&tmem_empty_bar[s], CG * kNumEpiWarps);  // one arrive per epilogue warp of the pair
     }
+    for (int s = 0; s < 2 * kNumEpiWarps; ++s) mbar_init(&resid_bar[s], 1);
     fence_barrier_init();
   }
   if (warp_idx == 2) {
-    tmem_alloc(tmem_ptr_smem, Cfg::kTmemCols);
-    tmem_relinquish();
+    if constexpr (CG == 2) {
+      tmem_alloc_pair(tmem_ptr_smem, Cfg::kTmemCols);
+      tmem_relinquish_pair();
+    } else {
+      tmem_alloc(tmem_ptr_smem, Cfg::kTmemCols);
+      tmem_relinquish();
+    }
   }
   tcgen05_fence_before();
-  __syncthreads();
+  if constexpr (CG == 2) cluster_sync_all(); else __syncthreads();
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
 
+  // Everything above overlaps the previous kernel's tail under programmatic dependent
+  // launch; global memory written by that kernel is only touched below this line.
+  pdl_wait_prior_grid();
+
   if (warp_idx == 0) {
-    // ===================== TMA producer =====================
+    // ===================== TMA producer (both CTAs of a pair) =====================
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      for (int tile = unit; tile < num_tiles; tile += num_units) {
         const int m_blk = tile / n_blocks;
         const int n_blk = tile % n_blocks;
+        const int a_row = m_blk * kTileM + static_cast<int>(cta_rank) * kRowsPerCta;
+        const int b_row = n_blk * BLOCK_N + static_cast<int>(cta_rank) * Cfg::kBRows;
         for (int kb = 0; kb < num_k_blocks; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1u);
           uint8_t *sa = smem + stage * kStageBytes;
           uint8_t *sb = sa + kABytes;
-          mbar_arrive_expect_tx(&full_bar[stage], kStageBytes);
-          tma_load_2d(sa, &tmap_a, &full_bar[stage], kb * kElemsPerKBlock, m_blk * kBlockM);
-          tma_load_2d(sb, &tmap_b, &full_bar[stage], kb * kElemsPerKBlock, n_blk * BLOCK_N);
+          if constexpr (CG == 2) {
+            if (cta_rank == 0) mbar_arrive_expect_tx(&full_bar[stage], 2 * kStageBytes);
+            tma_load_2d_pair(sa, &tmap_a, &full_bar[stage], kb * kElemsPerKBlock, a_row);
+            tma_load_2d_pair(sb, &tmap_b, &full_bar[stage], kb * kElemsPerKBlock, b_row);
+          } else {
+            mbar_arrive_expect_tx(&full_bar[stage], kStageBytes);
+            tma_load_2d(sa, &tmap_a, &full_bar[stage], kb * kElemsPerKBlock, a_row);
+            tma_load_2d(sb, &tmap_b, &full_bar[stage], kb * kElemsPerKBlock, b_row);
+          }
           if (++stage == kStages) {
             stage = 0;
             phase ^= 1u;
@@ -180,12 +200,12 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
     }
     __syncwarp();  // reconverge before the CTA-wide barrier below
   } else if (warp_idx == 1) {
-    // ===================== MMA issuer =====================
-    if (lane == 0) {
+    // ===================== MMA issuer (leader CTA) =====================
+    if (lane == 0 && cta_rank == 0) {
       int stage = 0;
       uint32_t phase = 0;
       int local_tile = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++local_tile) {
+      for (int tile = unit; tile < num_tiles; tile += num_units, ++local_tile) {
         const int acc = local_tile & 1;
         const uint32_t acc_phase = (local_tile >> 1) & 1u;
         mbar_wait(&tmem_empty_bar[acc], acc_phase ^ 1u);
@@ -202,13 +222,20 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
             // advancing 32 bytes along K inside the 128-byte swizzle row = +2 in the
             // (addr >> 4) start-address field
             const uint64_t adv = static_cast<uint64_t>((k * kUmmaKBytes) >> 4);
-            if constexpr (IN_FP8)
-              umma_f8_ss(tmem_d, desc_a + adv, desc_b + adv, kIdesc, (kb | k) != 0);
-            else
-              umma_f16_ss(tmem_d, desc_a + adv, desc_b + adv, kIdesc, (kb | k) != 0);
+            const uint32_t accumulate = (kb | k) != 0;
+            if constexpr (CG == 2) {
+              if constexpr (IN_FP8) umma_f8_ss_pair(tmem_d, desc_a + adv, desc_b + adv, kIdesc, accumulate);
+              else umma_f16_ss_pair(tmem_d, desc_a + adv, desc_b + adv, kIdesc, accumulate);
+            } else {
+              if constexpr (IN_FP8) umma_f8_ss(tmem_d, desc_a + adv, desc_b + adv, kIdesc, accumulate);
+              else umma_f16_ss(tmem_d, desc_a + adv, desc_b + adv, kIdesc, accumulate);
+            }
           }
-          umma_commit(&empty_bar[stage]);  // smem stage reusable once these MMAs retire
-          if (kb == num_k_blocks - 1) umma_commit(&tmem_full_bar[acc]);
+          // smem stage reusable (in both CTAs) once these MMAs retire
+          if constexpr (CG == 2) umma_commit_pair(&empty_bar[stage]); else umma_commit(&empty_bar[stage]);
+          if (kb == num_k_blocks - 1) {
+            if constexpr (CG == 2) umma_commit_pair(&tmem_full_bar[acc]); else umma_commit(&tmem_full_bar[acc]);
+          }
           if (++stage == kStages) {
             stage = 0;
             phase ^= 1u;
@@ -218,38 +245,149 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
     }
     __syncwarp();
   } else if (warp_idx >= kEpiWarp0) {
-    // ===================== epilogue =====================
-    const int q = warp_idx - kEpiWarp0;  // == warp_idx % 4: TMEM lane quarter this warp may read
+    // ===================== epilogue (all CTAs) =====================
+    const int e = warp_idx - kEpiWarp0;
+    const int q = warp_idx & 3;  // TMEM lane quarter this warp may read
+    const int half = e >> 2;     // which half of the tile's columns
+    const uint32_t stg = smem_u32(staging + e * Epi::kWarpBytes);
+    uint64_t *my_resid_bar = resid_bar + 2 * e;
+    uint32_t chunk_ctr = 0;      // live chunks this warp has staged so far (selects slot + parity)
     int local_tile = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++local_tile) {
+    for (int tile = unit; tile < num_tiles; tile += num_units, ++local_tile) {
       const int m_blk = tile / n_blocks;
       const int n_blk = tile % n_blocks;
       const int acc = local_tile & 1;
       const uint32_t acc_phase = (local_tile >> 1) & 1u;
+      const int row0 = m_blk * kTileM + static_cast<int>(cta_rank) * kRowsPerCta + q * 32;
+      const int colw = n_blk * BLOCK_N + half * (BLOCK_N / 2);  // first column of this warp
+      const bool slab_live = row0 < args.M;  // TMA clips partial slabs; dead ones are skipped
+      if constexpr (EPI == kEpiBiasResid) {
+        // Residual chunks 0 and 1 of this tile: fetched while the main loop still runs.
+        if (lane == 0 && slab_live) {
+          tma_store_wait_read<0>();  // both staging slots are free again
+#pragma unroll
+          for (int c = 0; c < (kChunksPerWarp < 2 ? kChunksPerWarp : 2); ++c) {
+            const uint32_t b = (chunk_ctr + c) & 1u;
+            mbar_arrive_expect_tx(&my_resid_bar[b], Epi::kChunkBytes);
+            tma_load_2d(staging + e * Epi::kWarpBytes + b * Epi::kChunkBytes, &tmap_resid,
+                        &my_resid_bar[b], colw + c * 32, row0);
+          }
+        }
+        __syncwarp();
+      }
       mbar_wait(&tmem_full_bar[acc], acc_phase);
       tcgen05_fence_after();
-      const int row = m_blk * kBlockM + q * 32 + lane;
-      const bool row_ok = row < args.M;
-      const uint32_t taddr =
-          tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(acc * BLOCK_N);
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) +
+                             static_cast<uint32_t>(acc * BLOCK_N + half * (BLOCK_N / 2));
 #pragma unroll 1
-      for (int c = 0; c < BLOCK_N / 32; ++c) {
+      for (int c = 0; c < kChunksPerWarp; ++c) {
+        const int col0 = colw + c * 32;
+        const uint32_t b = chunk_ctr & 1u;
+        const uint32_t sbuf = stg + b * Epi::kChunkBytes;
         uint32_t v[32];
         tmem_ld_32x32b_x32(taddr + static_cast<uint32_t>(c * 32), v);
+        float4 bv[8];
+        if (args.bias != nullptr) {
+          const float4 *b4 = reinterpret_cast<const float4 *>(args.bias + col0);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) bv[j] = __ldg(b4 + j);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) bv[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        if constexpr (EPI != kEpiBiasResid) {
+          // the store issued from this slot two chunks ago must have drained it
+          if (lane == 0) tma_store_wait_read<1>();
+          __syncwarp();
+        }
         tmem_ld_wait();
-        epilogue_chunk<EPI>(v, args, row, n_blk * BLOCK_N + c * 32, row_ok);
+        if (c == kChunksPerWarp - 1) {
+          // accumulator fully read: hand the TMEM buffer back to the MMA issuer
+          tcgen05_fence_before();
+          __syncwarp();
+          if (lane == 0) {
+            if constexpr (CG == 2) mbar_arrive_cluster(&tmem_empty_bar[acc], 0);
+            else mbar_arrive(&tmem_empty_bar[acc]);
+          }
+        }
+        if (!slab_live) continue;
+        float f[32];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          f[4 * j + 0] = fmaf(__uint_as_float(v[4 * j + 0]), args.acc_scale, bv[j].x);
+          f[4 * j + 1] = fmaf(__uint_as_float(v[4 * j + 1]), args.acc_scale, bv[j].y);
+          f[4 * j + 2] = fmaf(__uint_as_float(v[4 * j + 2]), args.acc_scale, bv[j].z);
+          f[4 * j + 3] = fmaf(__uint_as_float(v[4 * j + 3]), args.acc_scale, bv[j].w);
+        }
+        if constexpr (EPI == kEpiBiasGelu || EPI == kEpiBiasGeluE4m3) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) f[j] = gelu_erf(f[j]);
+        }
+        if constexpr (EPI == kEpiBiasResid) {
+          // 32 rows x 128 B, SWIZZLE_128B: 16-byte chunk j of row r sits at j ^ (r & 7)
+          mbar_wait(&my_resid_bar[b], (chunk_ctr >> 1) & 1u);
+          const uint32_t rowa = sbuf + static_cast<uint32_t>(lane) * 128u;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const uint32_t a = rowa + (static_cast<uint32_t>(j ^ (lane & 7)) << 4);
+            const float4 r = ld_shared_f4(a);
+            st_shared_v4(a, __float_as_uint(f[4 * j] + r.x), __float_as_uint(f[4 * j + 1] + r.y),
+                         __float_as_uint(f[4 * j + 2] + r.z), __float_as_uint(f[4 * j + 3] + r.w));
+          }
+        } else if constexpr (EPI == kEpiBiasGeluE4m3) {
+          // 32 rows x 32 B, no swizzle
+          const float s = args.out_inv_scale;
+          const uint32_t rowa = sbuf + static_cast<uint32_t>(lane) * 32u;
+#pragma unroll
+          for (int j = 0; j < 2; ++j) {
+            uint32_t w[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              const int o = 16 * j + 4 * i;
+              w[i] = pack_e4m3x4(f[o] * s, f[o + 1] * s, f[o + 2] * s, f[o + 3] * s);
+            }
+            st_shared_v4(rowa + static_cast<uint32_t>(j << 4), w[0], w[1], w[2], w[3]);
+          }
+        } else {
+          // 32 rows x 64 B, SWIZZLE_64B: 16-byte chunk j of row r sits at j ^ ((r >> 1) & 3)
+          const uint32_t rowa = sbuf + static_cast<uint32_t>(lane) * 64u;
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const uint32_t a = rowa + (static_cast<uint32_t>(j ^ ((lane >> 1) & 3)) << 4);
+            st_shared_v4(a, pack_bf16(f[8 * j], f[8 * j + 1]), pack_bf16(f[8 * j + 2], f[8 * j + 3]),
+                         pack_bf16(f[8 * j + 4], f[8 * j + 5]), pack_bf16(f[8 * j + 6], f[8 * j + 7]));
+          }
+        }
+        fence_proxy_async_smem();  // generic-proxy smem writes -> visible to the TMA engine
+        __syncwarp();
+        if (lane == 0) {
+          tma_store_2d(&tmap_out, staging + e * Epi::kWarpBytes + b * Epi::kChunkBytes, col0, row0);
+          tma_store_commit();
+          if constexpr (EPI == kEpiBiasResid) {
+            if (c + 2 < kChunksPerWarp) {
+              // refill this slot with the residual chunk two ahead once the store has read it
+              tma_store_wait_read<0>();
+              mbar_arrive_expect_tx(&my_resid_bar[b], Epi::kChunkBytes);
+              tma_load_2d(staging + e * Epi::kWarpBytes + b * Epi::kChunkBytes, &tmap_resid,
+                          &my_resid_bar[b], col0 + 64, row0);
+            }
+          }
+        }
+        __syncwarp();
+        ++chunk_ctr;  // counts live chunks only: slot = ctr & 1, residual-barrier parity = ctr >> 1
       }
-      tcgen05_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&tmem_empty_bar[acc]);
     }
+    if (lane == 0) tma_store_wait<0>();  // all bulk stores of this warp are complete
+    __syncwarp();
   }
 
   tcgen05_fence_before();
-  __syncthreads();
+  if constexpr (CG == 2) cluster_sync_all(); else __syncthreads();
+  pdl_launch_dependents();
   if (warp_idx == 2) {
     tcgen05_fence_after();
-    tmem_dealloc(tmem_base, Cfg::kTmemCols);
+    if constexpr (CG == 2) tmem_dealloc_pair(tmem_base, Cfg::kTmemCols);
+    else tmem_dealloc(tmem_base, Cfg::kTmemCols);
   }
 }
 
@@ -273,22 +411,19 @@ EncodeTiledFn get_encode_fn() {
   return fn;
 }
 
-spu_status make_kmajor_tmap(CUtensorMap *map, const void *base, int rows, int k_elems,
-                            int box_rows, GemmIn in) {
+// Row-major [rows, cols] matrix of `esize`-byte elements, box = box_cols x box_rows.
+spu_status make_tmap_2d(CUtensorMap *map, const void *base, int rows, int cols, int esize,
+                        CUtensorMapDataType dtype, int box_cols, int box_rows,
+                        CUtensorMapSwizzle swizzle) {
   EncodeTiledFn enc = get_encode_fn();
   SPU_REQUIRE(enc != nullptr, SPU_ERR_CUDA, "cuTensorMapEncodeTiled entry point unavailable");
-  const int esize = in == GemmIn::FP8_E4M3 ? 1 : 2;
-  cuuint64_t gdim[2] = {static_cast<cuuint64_t>(k_elems), static_cast<cuuint64_t>(rows)};
-  cuuint64_t gstride[1] = {static_cast<cuuint64_t>(k_elems) * esize};
-  cuuint32_t box[2] = {static_cast<cuuint32_t>(kTileKBytes / esize),
-                       static_cast<cuuint32_t>(box_rows)};
+  cuuint64_t gdim[2] = {static_cast<cuuint64_t>(cols), static_cast<cuuint64_t>(rows)};
+  cuuint64_t gstride[1] = {static_cast<cuuint64_t>(cols) * esize};
+  cuuint32_t box[2] = {static_cast<cuuint32_t>(box_cols), static_cast<cuuint32_t>(box_rows)};
   cuuint32_t estride[2] = {1, 1};
-  const CUresult r = enc(map,
-                         in == GemmIn::FP8_E4M3 ? CU_TENSOR_MAP_DATA_TYPE_UINT8
-                                                : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16,
-                         2, const_cast<void *>(base), gdim, gstride, box, estride,
-                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
-                         CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  const CUresult r = enc(map, dtype, 2, const_cast<void *>(base), gdim, gstride, box, estride,
+                         CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     set_error("cuTensorMapEncodeTiled failed with CUresult " + std::to_string(static_cast<int>(r)));
     return SPU_ERR_CUDA;
@@ -296,17 +431,39 @@ spu_status make_kmajor_tmap(CUtensorMap *map, const void *base, int rows, int k_
   return SPU_OK;
 }
 
-int bn_index(int bn) {
-  for (int i = 0; i < kNumBlockN; ++i)
-    if (kBlockNCands[i] == bn) return i;
-  return -1;
+spu_status make_kmajor_tmap(CUtensorMap *map, const void *base, int rows, int k_elems, int box_rows,
+                            GemmIn in) {
+  const int esize = in == GemmIn::FP8_E4M3 ? 1 : 2;
+  return make_tmap_2d(map, base, rows, k_elems, esize,
+                      in == GemmIn::FP8_E4M3 ? CU_TENSOR_MAP_DATA_TYPE_UINT8
+                                             : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16,
+                      kTileKBytes / esize, box_rows, CU_TENSOR_MAP_SWIZZLE_128B);
 }
 
-template <int BLOCK_N, int EPI, int IN_FP8>
-spu_status launch_cfg(const GemmPlan &plan, int M, const GemmEpilogueArgs &epi,
+// 32x32 output chunk map matching the staging layout of the epilogue kind.
+spu_status make_out_tmap(CUtensorMap *map, const void *base, int rows, int cols, int epilogue) {
+  switch (epilogue) {
+    case kEpiBiasResid:
+      return make_tmap_2d(map, base, rows, cols, 4, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 32, 32,
+                          CU_TENSOR_MAP_SWIZZLE_128B);
+    case kEpiBiasGeluE4m3:
+      return make_tmap_2d(map, base, rows, cols, 1, CU_TENSOR_MAP_DATA_TYPE_UINT8, 32, 32,
+                          CU_TENSOR_MAP_SWIZZLE_NONE);
+    default:
+      return make_tmap_2d(map, base, rows, cols, 2, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 32, 32,
+                          CU_TENSOR_MAP_SWIZZLE_64B);
+  }
+}
+
+struct LaunchMaps {
+  CUtensorMap a, out, resid;
+};
+
+template <int BLOCK_N, int CG, int EPI, int IN_FP8>
+spu_status launch_cfg(const GemmPlan &plan, const LaunchMaps &maps, const KernelArgs &a,
                       cudaStream_t stream) {
-  using Cfg = TileCfg<BLOCK_N>;
-  auto kern = gemm_tcgen05_kernel<BLOCK_N, EPI, IN_FP8>;
+  using Cfg = TileCfg<BLOCK_N, CG, EPI>;
+  auto kern = gemm_tcgen05_kernel<BLOCK_N, CG, EPI, IN_FP8>;
   static std::once_flag once;
   static cudaError_t attr_err = cudaSuccess;
   std::call_once(once, [&] {
@@ -314,98 +471,174 @@ spu_status launch_cfg(const GemmPlan &plan, int M, const GemmEpilogueArgs &epi,
                                     Cfg::kSmemBytes);
   });
   SPU_CUDA_TRY(attr_err);
-  KernelArgs a{M, plan.N, plan.K, epi};
-  const int tiles = (plan.N / BLOCK_N) * ((M + kBlockM - 1) / kBlockM);
+  const int tiles = (plan.N / BLOCK_N) * ((a.M + kRowsPerCta * CG - 1) / (kRowsPerCta * CG));
   int dev = 0, sms = kNumSMsB200;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  const int grid = tiles < sms ? tiles : sms;
-  kern<<<grid, kThreads, Cfg::kSmemBytes, stream>>>(plan.tmap_a, plan.tmap_b[bn_index(BLOCK_N)], a);
-  SPU_CUDA_TRY(cudaGetLastError());
+  const int units = sms / CG;
+  const int grid = CG * (tiles < units ? tiles : units);
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(grid, 1, 1);
+  cfg.blockDim = dim3(kThreads, 1, 1);
+  cfg.dynamicSmemBytes = Cfg::kSmemBytes;
+  cfg.stream = stream;
+  cudaLaunchAttribute attrs[2];
+  int n_attr = 0;
+  attrs[n_attr].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attrs[n_attr].val.programmaticStreamSerializationAllowed = 1;
+  ++n_attr;
+  if (CG == 2) {
+    attrs[n_attr].id = cudaLaunchAttributeClusterDimension;
+    attrs[n_attr].val.clusterDim.x = 2;
+    attrs[n_attr].val.clusterDim.y = 1;
+    attrs[n_attr].val.clusterDim.z = 1;
+    ++n_attr;
+  }
+  cfg.attrs = attrs;
+  cfg.numAttrs = n_attr;
+  SPU_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, maps.a, plan.tmap_b[BLOCK_N / CG / 32 - 1], maps.out,
+                                  maps.resid, a));
   return SPU_OK;
 }
 
-template <int BLOCK_N, int IN_FP8>
-spu_status launch_epi(const GemmPlan &plan, int M, const GemmEpilogueArgs &epi,
+template <int BLOCK_N, int CG>
+spu_status launch_epi(const GemmPlan &plan, const LaunchMaps &maps, const KernelArgs &a,
                       cudaStream_t stream) {
+  if (plan.in == GemmIn::FP8_E4M3) {
+    switch (plan.epilogue) {
+      case kEpiBias: return launch_cfg<BLOCK_N, CG, kEpiBias, 1>(plan, maps, a, stream);
+      case kEpiBiasResid: return launch_cfg<BLOCK_N, CG, kEpiBiasResid, 1>(plan, maps, a, stream);
+      case kEpiBiasGeluE4m3: return launch_cfg<BLOCK_N, CG, kEpiBiasGeluE4m3, 1>(plan, maps, a, stream);
+      default: set_error("fp8 gemm: unsupported epilogue"); return SPU_ERR_INVALID;
+    }
+  }
   switch (plan.epilogue) {
-    case SPU_EPI_BIAS: return launch_cfg<BLOCK_N, SPU_EPI_BIAS, IN_FP8>(plan, M, epi, stream);
-    case SPU_EPI_BIAS_GELU: return launch_cfg<BLOCK_N, SPU_EPI_BIAS_GELU, IN_FP8>(plan, M, epi, stream);
-    case SPU_EPI_BIAS_RESID: return launch_cfg<BLOCK_N, SPU_EPI_BIAS_RESID, IN_FP8>(plan, M, epi, stream);
-    default: set_error("unknown epilogue"); return SPU_ERR_INVALID;
+    case kEpiBias: return launch_cfg<BLOCK_N, CG, kEpiBias, 0>(plan, maps, a, stream);
+    case kEpiBiasGelu: return launch_cfg<BLOCK_N, CG, kEpiBiasGelu, 0>(plan, maps, a, stream);
+    case kEpiBiasResid: return launch_cfg<BLOCK_N, CG, kEpiBiasResid, 0>(plan, maps, a, stream);
+    default: set_error("bf16 gemm: unsupported epilogue"); return SPU_ERR_INVALID;
   }
 }
 
-template <int IN_FP8>
-spu_status launch_bn(const GemmPlan &plan, int block_n, int M, const GemmEpilogueArgs &epi,
+template <int CG>
+spu_status launch_bn(const GemmPlan &plan, int block_n, const LaunchMaps &maps, const KernelArgs &a,
                      cudaStream_t stream) {
   switch (block_n) {
-    case 64: return launch_epi<64, IN_FP8>(plan, M, epi, stream);
-    case 128: return launch_epi<128, IN_FP8>(plan, M, epi, stream);
-    case 192: return launch_epi<192, IN_FP8>(plan, M, epi, stream);
-    case 256: return launch_epi<256, IN_FP8>(plan, M, epi, stream);
+    case 64: return launch_epi<64, CG>(plan, maps, a, stream);
+    case 128: return launch_epi<128, CG>(plan, maps, a, stream);
+    case 192: return launch_epi<192, CG>(plan, maps, a, stream);
+    case 256: return launch_epi<256, CG>(plan, maps, a, stream);
     default: set_error("unsupported BLOCK_N"); return SPU_ERR_INVALID;
   }
 }
 
+constexpr int kBlockNCands[4] = {256, 192, 128, 64};
+
 }  // namespace
 
-int choose_block_n(int M, int N) {
-  const int m_blocks = (M + kBlockM - 1) / kBlockM;
-  int best = 0;
-  double best_cost = 1e30;
-  for (int bn : kBlockNCands) {
-    if (N % bn != 0) continue;
-    const int tiles = m_blocks * (N / bn);
-    const int rounds = (tiles + kNumSMsB200 - 1) / kNumSMsB200;
-    // tile cost ~ MMA cycles (proportional to bn) + fixed per-tile overhead
-    const double cost = rounds * (bn + 24.0);
-    if (cost < best_cost) {
-      best_cost = cost;
-      best = bn;
+GemmConfig choose_config(int M, int N, int K, int esize) {
+  GemmConfig best{0, 0};
+  double best_cost = 1e300;
+  const double k_bytes = static_cast<double>(K) * esize;
+  const int k_blocks = static_cast<int>(k_bytes) / kTileKBytes;
+  for (int cg = 2; cg >= 1; --cg) {
+    const int tile_m = kRowsPerCta * cg;
+    const int units = kNumSMsB200 / cg;
+    const int m_blocks = (M + tile_m - 1) / tile_m;
+    for (int bn : kBlockNCands) {
+      if (N % bn != 0) continue;
+      const int tiles = m_blocks * (N / bn);
+      const int rounds = (tiles + units - 1) / units;
+      // cycles one CTA spends per tile on: MMA issue (128 x bn x 16 per bn/2 clocks),
+      // L2->smem operand feed (~40 B/clk/SM), epilogue (8 warps, ~6 clk per column)
+      const double mma = k_blocks * 4.0 * (bn / 2.0);
+      const double feed = (kRowsPerCta + bn / static_cast<double>(cg)) * k_bytes / 40.0;
+      const double epi = bn * 6.0;
+      const double tile = mma > feed ? (mma > epi ? mma : epi) : (feed > epi ? feed : epi);
+      // a pair that owns fewer than 129 valid rows wastes its second CTA
+      const double cost = rounds * tile + epi + 1500.0 + (cg == 2 && M <= kRowsPerCta ? 1.0 : 0.0);
+      if (cost < best_cost) {
+        best_cost = cost;
+        best = GemmConfig{cg, bn};
+      }
     }
   }
   return best;
 }
 
-spu_status gemm_make_plan(GemmPlan *plan, const void *A, int rows_a, const void *W, int M, int N,
-                          int K, int epilogue, GemmIn in, int block_n_override) {
+spu_status gemm_make_plan(GemmPlan *plan, const void *A, int rows_a, const void *W, int N, int K,
+                          int epilogue, GemmIn in, int force_cg, int force_bn) {
   SPU_REQUIRE(plan && A && W, SPU_ERR_INVALID, "gemm: null argument");
   const int kelems = in == GemmIn::FP8_E4M3 ? 128 : 64;
-  SPU_REQUIRE(M > 0 && N > 0 && K > 0, SPU_ERR_INVALID, "gemm: empty shape");
+  SPU_REQUIRE(rows_a > 0 && N > 0 && K > 0, SPU_ERR_INVALID, "gemm: empty shape");
   SPU_REQUIRE(K % kelems == 0, SPU_ERR_UNSUPPORTED, "gemm: K must be a multiple of the 128-byte K tile");
   SPU_REQUIRE(N % 64 == 0, SPU_ERR_UNSUPPORTED, "gemm: N must be a multiple of 64");
-  SPU_REQUIRE(rows_a >= M, SPU_ERR_INVALID, "gemm: A buffer smaller than M");
-  plan->M = rows_a;
+  SPU_REQUIRE((reinterpret_cast<uintptr_t>(A) & 15u) == 0 && (reinterpret_cast<uintptr_t>(W) & 15u) == 0,
+              SPU_ERR_INVALID, "gemm: operands must be 16-byte aligned");
+  plan->A = A;
+  plan->rows_a = rows_a;
   plan->N = N;
   plan->K = K;
   plan->epilogue = epilogue;
   plan->in = in;
-  plan->block_n_override = block_n_override;
-  if (block_n_override)
-    SPU_REQUIRE(bn_index(block_n_override) >= 0 && N % block_n_override == 0, SPU_ERR_UNSUPPORTED,
-                "gemm: BLOCK_N override does not divide N");
-  spu_status st = make_kmajor_tmap(&plan->tmap_a, A, rows_a, K, kBlockM, in);
-  if (st != SPU_OK) return st;
-  for (int i = 0; i < kNumBlockN; ++i) {
-    plan->bn_ok[i] = (N % kBlockNCands[i] == 0);
-    if (!plan->bn_ok[i]) continue;
-    st = make_kmajor_tmap(&plan->tmap_b[i], W, N, K, kBlockNCands[i], in);
+  plan->force_cg = force_cg;
+  plan->force_bn = force_bn;
+  if (const char *env = std::getenv("SPU_GEMM_CFG")) {  // "cg:bn", experiments only
+    int cg = 0, bn = 0;
+    if (std::sscanf(env, "%d:%d", &cg, &bn) == 2 && (cg == 1 || cg == 2) && bn > 0 && N % bn == 0) {
+      plan->force_cg = cg;
+      plan->force_bn = bn;
+    }
+  }
+  if (plan->force_bn)
+    SPU_REQUIRE((plan->force_cg == 1 || plan->force_cg == 2) && N % plan->force_bn == 0 &&
+                    plan->force_bn % 64 == 0 && plan->force_bn <= 256,
+                SPU_ERR_UNSUPPORTED, "gemm: forced tile does not fit N");
+  for (int i = 0; i < kNumBBoxes; ++i) {
+    const int box_rows = 32 * (i + 1);
+    plan->b_ok[i] = false;
+    bool wanted = false;
+    for (int bn : kBlockNCands)
+      if (N % bn == 0 && (bn == box_rows || bn / 2 == box_rows)) wanted = true;
+    if (!wanted) continue;
+    spu_status st = make_kmajor_tmap(&plan->tmap_b[i], W, N, K, box_rows, in);
     if (st != SPU_OK) return st;
+    plan->b_ok[i] = true;
   }
   return SPU_OK;
 }
 
 spu_status gemm_launch(const GemmPlan &plan, int M, const GemmEpilogueArgs &args,
                        cudaStream_t stream) {
-  SPU_REQUIRE(M > 0 && M <= plan.M, SPU_ERR_CAPACITY, "gemm: M exceeds plan capacity");
+  SPU_REQUIRE(M > 0 && M <= plan.rows_a, SPU_ERR_CAPACITY, "gemm: M exceeds plan capacity");
   SPU_REQUIRE(args.out != nullptr, SPU_ERR_INVALID, "gemm: null output");
-  if (plan.epilogue == SPU_EPI_BIAS_RESID)
-    SPU_REQUIRE(args.resid != nullptr, SPU_ERR_INVALID, "gemm: residual epilogue without residual");
-  const int bn = plan.block_n_override ? plan.block_n_override : choose_block_n(M, plan.N);
-  SPU_REQUIRE(bn > 0, SPU_ERR_UNSUPPORTED, "gemm: no BLOCK_N divides N");
-  return plan.in == GemmIn::FP8_E4M3 ? launch_bn<1>(plan, bn, M, args, stream)
-                                     : launch_bn<0>(plan, bn, M, args, stream);
+  SPU_REQUIRE((reinterpret_cast<uintptr_t>(args.out) & 15u) == 0, SPU_ERR_INVALID,
+              "gemm: output must be 16-byte aligned");
+  if (plan.epilogue == kEpiBiasResid)
+    SPU_REQUIRE(args.resid != nullptr && (reinterpret_cast<uintptr_t>(args.resid) & 15u) == 0,
+                SPU_ERR_INVALID, "gemm: residual epilogue needs a 16-byte aligned residual");
+  const int esize = plan.in == GemmIn::FP8_E4M3 ? 1 : 2;
+  GemmConfig cfg = plan.force_bn ? GemmConfig{plan.force_cg, plan.force_bn}
+                                 : choose_config(M, plan.N, plan.K, esize);
+  SPU_REQUIRE(cfg.block_n > 0, SPU_ERR_UNSUPPORTED, "gemm: no BLOCK_N divides N");
+  SPU_REQUIRE(plan.b_ok[cfg.block_n / cfg.cta_group / 32 - 1], SPU_ERR_UNSUPPORTED,
+              "gemm: no weight tensor map for this tile");
+  // Activation-side maps carry the live row count: TMA zero-fills A rows >= M and
+  // clips output rows >= M, so a dynamic batch never reads or writes stale rows.
+  LaunchMaps maps;
+  spu_status st = make_kmajor_tmap(&maps.a, plan.A, M, plan.K, kRowsPerCta, plan.in);
+  if (st != SPU_OK) return st;
+  st = make_out_tmap(&maps.out, args.out, M, plan.N, plan.epilogue);
+  if (st != SPU_OK) return st;
+  if (plan.epilogue == kEpiBiasResid) {
+    st = make_out_tmap(&maps.resid, args.resid, M, plan.N, plan.epilogue);
+    if (st != SPU_OK) return st;
+  } else {
+    maps.resid = maps.out;
+  }
+  KernelArgs a{M, plan.N, plan.K, args.bias, args.acc_scale, args.out_inv_scale};
+  return cfg.cta_group == 2 ? launch_bn<2>(plan, cfg.block_n, maps, a, stream)
+                            : launch_bn<1>(plan, cfg.block_n, maps, a, stream);
 }
 
 }  // namespace spu

@@ -1,4 +1,4 @@
-// tcgen05/TMEM GEMM with TMA-fed operands and fused epilogues (sm_100a).
+// tcgen05/TMEM GEMM with TMA-fed operands and fused, TMA-stored epilogues (sm_100a).
 //   C[M,N] = A[M,K] * W[N,K]^T  (+bias, then GELU | +fp32 residual)
 // Both operands are K-major (activations row-major, nn.Linear weights [out,in]),
 // which is the native TN form of tcgen05.mma with SWIZZLE_128B smem tiles.
@@ -11,36 +11,47 @@ namespace spu {
 
 enum class GemmIn : int { BF16 = 0, FP8_E4M3 = 1 };
 
+// Internal epilogue kinds (the first three are the public SPU_EPI_* values).
+constexpr int kEpiBias = SPU_EPI_BIAS;             // bf16 out
+constexpr int kEpiBiasGelu = SPU_EPI_BIAS_GELU;    // bf16 out
+constexpr int kEpiBiasResid = SPU_EPI_BIAS_RESID;  // fp32 out = acc + bias + fp32 residual
+constexpr int kEpiBiasGeluE4m3 = 3;                // e4m3 out = gelu(acc*s + bias) * out_scale_inv
+
 struct GemmEpilogueArgs {
-  const float *bias;   // [N] fp32 (may be null)
-  const float *resid;  // [M,N] fp32 (EPI_BIAS_RESID)
-  void *out;           // bf16 [M,N] (BIAS, BIAS_GELU) or fp32 [M,N] (BIAS_RESID)
-  void *out_fp8;       // optional e4m3 [M,N] copy of the bf16 result (fp8 pipelines)
-  float acc_scale;     // multiplies the accumulator (fp8: a_scale*w_scale; bf16: 1)
-  float out_fp8_inv_scale;  // 1/scale used when writing out_fp8
+  const float *bias;    // [N] fp32 (may be null)
+  const float *resid;   // [M,N] fp32 (kEpiBiasResid; may alias out)
+  void *out;            // bf16 / fp32 / e4m3 [M,N] according to the epilogue kind
+  float acc_scale;      // multiplies the accumulator (fp8: a_scale*w_scale; bf16: 1)
+  float out_inv_scale;  // kEpiBiasGeluE4m3: 1/scale of the quantised output
 };
 
-constexpr int kNumBlockN = 4;
-constexpr int kBlockNCands[kNumBlockN] = {256, 192, 128, 64};
+// Operand-B TMA boxes come in multiples of 32 rows: BLOCK_N / cta_group in {32..256}.
+constexpr int kNumBBoxes = 8;
 
 struct GemmPlan {
-  CUtensorMap tmap_a;
-  CUtensorMap tmap_b[kNumBlockN];  // one per candidate BLOCK_N that divides N
-  bool bn_ok[kNumBlockN];
-  int M, N, K;                     // M = row capacity of the A buffer
-  int block_n_override;            // 0 = choose per launch from M
+  CUtensorMap tmap_b[kNumBBoxes];  // index = box_rows/32 - 1
+  bool b_ok[kNumBBoxes];
+  const void *A;                   // activation buffer the plan was made for
+  int rows_a;                      // row capacity of A (and of out / resid)
+  int N, K;
   int epilogue;
   GemmIn in;
+  int force_cg, force_bn;          // 0 = choose per launch from M
 };
 
-// Pick BLOCK_N: must divide N; prefer the choice that minimises the number of
-// persistent rounds times tile cost over 148 SMs.
-int choose_block_n(int M, int N);
+struct GemmConfig {
+  int cta_group;  // 1: 128 x BLOCK_N tile per CTA; 2: 256 x BLOCK_N per CTA pair
+  int block_n;
+};
 
-// Encode the two operand tensor maps.  rows_a is the number of rows the A buffer
-// really holds (>= M; tail tiles read but never store rows >= M).
-spu_status gemm_make_plan(GemmPlan *plan, const void *A, int rows_a, const void *W, int M, int N,
-                          int K, int epilogue, GemmIn in, int block_n_override = 0);
+// Pick (cta_group, BLOCK_N) for an [M,N,K] problem: BLOCK_N must divide N; minimise
+// persistent rounds x per-tile cost (MMA issue, L2->smem feed, epilogue) over 148 SMs.
+GemmConfig choose_config(int M, int N, int K, int esize);
+
+// Encode the weight tensor maps.  rows_a is the number of rows the A / out / resid
+// buffers really hold (>= any M later passed to gemm_launch).
+spu_status gemm_make_plan(GemmPlan *plan, const void *A, int rows_a, const void *W, int N, int K,
+                          int epilogue, GemmIn in, int force_cg = 0, int force_bn = 0);
 
 // Enqueue.  Only (M, epilogue pointers) may change between calls with one plan.
 spu_status gemm_launch(const GemmPlan &plan, int M, const GemmEpilogueArgs &args,

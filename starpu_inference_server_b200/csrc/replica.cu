@@ -190,21 +190,17 @@ spu_status build(spu_replica *r, const float *const *t) {
     SPU_TRY(dev_alloc(r, &ws.ctx, rows * H));
     SPU_TRY(dev_alloc(r, &ws.h, rows * F));
     SPU_TRY(dev_alloc(r, &ws.mask_bias, rows));
-    // tail tiles of the last 128-row block read (never store) rows >= M: keep them finite
-    SPU_CUDA_TRY(cudaMemset(ws.x_bf16, 0, rows * H * 2));
-    SPU_CUDA_TRY(cudaMemset(ws.ctx, 0, rows * H * 2));
-    SPU_CUDA_TRY(cudaMemset(ws.h, 0, rows * F * 2));
     ws.plans.resize(d.layers);
     for (int l = 0; l < d.layers; ++l) {
       const LayerWeights &w = r->layers[l];
       const int R = static_cast<int>(rows);
-      SPU_TRY(gemm_make_plan(&ws.plans[l].qkv, ws.x_bf16, R, w.w_qkv, R, 3 * d.hidden, d.hidden,
+      SPU_TRY(gemm_make_plan(&ws.plans[l].qkv, ws.x_bf16, R, w.w_qkv, 3 * d.hidden, d.hidden,
                              SPU_EPI_BIAS, GemmIn::BF16));
-      SPU_TRY(gemm_make_plan(&ws.plans[l].attn_out, ws.ctx, R, w.w_o, R, d.hidden, d.hidden,
+      SPU_TRY(gemm_make_plan(&ws.plans[l].attn_out, ws.ctx, R, w.w_o, d.hidden, d.hidden,
                              SPU_EPI_BIAS_RESID, GemmIn::BF16));
-      SPU_TRY(gemm_make_plan(&ws.plans[l].ffn1, ws.x_bf16, R, w.w_1, R, d.ffn, d.hidden,
+      SPU_TRY(gemm_make_plan(&ws.plans[l].ffn1, ws.x_bf16, R, w.w_1, d.ffn, d.hidden,
                              SPU_EPI_BIAS_GELU, GemmIn::BF16));
-      SPU_TRY(gemm_make_plan(&ws.plans[l].ffn2, ws.h, R, w.w_2, R, d.hidden, d.ffn,
+      SPU_TRY(gemm_make_plan(&ws.plans[l].ffn2, ws.h, R, w.w_2, d.hidden, d.ffn,
                              SPU_EPI_BIAS_RESID, GemmIn::BF16));
     }
   }
@@ -412,17 +408,27 @@ extern "C" int32_t spu_bert_forward_launch_count(const spu_replica *r) {
   return r == nullptr ? 0 : 1 + 7 * r->desc.layers;
 }
 
-extern "C" spu_status spu_gemm_bf16_async(const void *A, const void *W, const float *bias,
-                                          const float *resid, void *out, int32_t M, int32_t N,
-                                          int32_t K, int32_t epilogue, void *stream) {
+extern "C" spu_status spu_gemm_bf16_cfg_async(const void *A, const void *W, const float *bias,
+                                              const float *resid, void *out, int32_t M, int32_t N,
+                                              int32_t K, int32_t epilogue, int32_t cta_group,
+                                              int32_t block_n, void *stream) {
+  SPU_REQUIRE(epilogue >= SPU_EPI_BIAS && epilogue <= SPU_EPI_BIAS_RESID, SPU_ERR_INVALID,
+              "gemm: unknown epilogue");
+  SPU_REQUIRE(M > 0, SPU_ERR_INVALID, "gemm: empty shape");
   GemmPlan plan;
-  SPU_TRY(gemm_make_plan(&plan, A, M, W, M, N, K, epilogue, GemmIn::BF16));
+  SPU_TRY(gemm_make_plan(&plan, A, M, W, N, K, epilogue, GemmIn::BF16, cta_group, block_n));
   GemmEpilogueArgs e{};
   e.bias = bias;
   e.resid = resid;
   e.out = out;
   e.acc_scale = 1.f;
   return gemm_launch(plan, M, e, as_stream(stream));
+}
+
+extern "C" spu_status spu_gemm_bf16_async(const void *A, const void *W, const float *bias,
+                                          const float *resid, void *out, int32_t M, int32_t N,
+                                          int32_t K, int32_t epilogue, void *stream) {
+  return spu_gemm_bf16_cfg_async(A, W, bias, resid, out, M, N, K, epilogue, 0, 0, stream);
 }
 
 extern "C" spu_status spu_attention_async(const void *qkv, const float *mask_bias, void *ctx,

@@ -35,22 +35,21 @@ def _gemm_ref(a_bf16, w_bf16, bias, resid, epi):
     return y
 
 
-@pytest.mark.parametrize("M,N,K", [(128, 128, 64), (128, 256, 128), (256, 768, 768), (4096, 2304, 768),
-                                   (4096, 768, 3072), (1000, 3072, 768), (77, 384, 128), (640, 512, 128)])
-@pytest.mark.parametrize("epi", [0, 1, 2])
-def test_gemm_tcgen05_matches_fp32(spu, M, N, K, epi):
-    g = torch.Generator(device="cpu").manual_seed(M * 7 + N * 3 + K + epi)
+def _check_gemm(spu, M, N, K, epi, cg, bn, seed):
+    g = torch.Generator(device="cpu").manual_seed(seed)
     a = (torch.randn(M, K, generator=g) * 0.5).to(torch.bfloat16).cuda()
     w = (torch.randn(N, K, generator=g) * 0.05).to(torch.bfloat16).cuda()
     bias = torch.randn(N, generator=g).cuda()
     resid = torch.randn(M, N, generator=g).cuda()
-    out = torch.full((M, N), float("nan"), dtype=torch.float32 if epi == 2 else torch.bfloat16, device="cuda")
-    spu.check(spu.lib().spu_gemm_bf16_async(spu.ptr(a), spu.ptr(w), spu.ptr(bias),
-                                            spu.ptr(resid) if epi == 2 else None, spu.ptr(out),
-                                            M, N, K, epi, spu.stream_ptr()))
+    # a guard row after the output catches stores that ignore the M tail
+    out = torch.full((M + 1, N), float("nan"), dtype=torch.float32 if epi == 2 else torch.bfloat16, device="cuda")
+    spu.check(spu.lib().spu_gemm_bf16_cfg_async(spu.ptr(a), spu.ptr(w), spu.ptr(bias),
+                                                spu.ptr(resid) if epi == 2 else None, spu.ptr(out),
+                                                M, N, K, epi, cg, bn, spu.stream_ptr()))
     _sync()
     ref = _gemm_ref(a, w, bias, resid, epi)
-    got = out.float().cpu()
+    assert torch.isnan(out[M]).all(), "GEMM wrote past row M"
+    got = out[:M].float().cpu()
     assert torch.isfinite(got).all()
     # fp32 accumulation of exact bf16 products: only summation order + output rounding differ
     tol = 2e-3 if epi == 2 else 1.2e-2  # bf16 output rounding (2^-8 relative) dominates for epi 0/1
@@ -58,6 +57,43 @@ def test_gemm_tcgen05_matches_fp32(spu, M, N, K, epi):
     bound = tol * (ref.abs() + 1.0)
     bad = (err > bound).sum().item()
     assert bad == 0, f"{bad} elements off; max err {err.max().item():.4g} at {np.unravel_index(err.argmax().item(), err.shape)}"
+
+
+@pytest.mark.parametrize("M,N,K", [(128, 128, 64), (128, 256, 128), (256, 768, 768), (4096, 2304, 768),
+                                   (4096, 768, 3072), (1000, 3072, 768), (77, 384, 128), (640, 512, 128)])
+@pytest.mark.parametrize("epi", [0, 1, 2])
+def test_gemm_tcgen05_matches_fp32(spu, M, N, K, epi):
+    """Library-chosen tile (cta_group, BLOCK_N)."""
+    _check_gemm(spu, M, N, K, epi, 0, 0, M * 7 + N * 3 + K + epi)
+
+
+@pytest.mark.parametrize("cg", [1, 2])
+@pytest.mark.parametrize("bn", [64, 128, 192, 256])
+@pytest.mark.parametrize("epi", [0, 1, 2])
+@pytest.mark.parametrize("M", [4096, 333, 31])
+def test_gemm_every_tile_shape(spu, M, epi, bn, cg):
+    """Every (cta_group, BLOCK_N) instantiation, with full, ragged and sub-slab M; N=768
+    gives 3..12 column blocks and K=320 five k-blocks (pipeline wrap with <= 8 stages
+    needs several tiles per CTA: M=4096 supplies them)."""
+    _check_gemm(spu, M, 768, 320 if M != 4096 else 768, epi, cg, bn, M + 13 * bn + cg + epi)
+
+
+def test_gelu_epilogue_tracks_erf(spu):
+    """The 2^p(|x|) GELU of the epilogue against exact erf over a wide input range
+    (identity weights route A straight into the activation)."""
+    K = N = 256
+    M = 4096
+    x = torch.linspace(-9.0, 9.0, M * K).reshape(M, K)
+    a = x.to(torch.bfloat16).cuda()
+    w = torch.eye(N, K).to(torch.bfloat16).cuda()
+    out = torch.empty(M, N, dtype=torch.bfloat16, device="cuda")
+    spu.check(spu.lib().spu_gemm_bf16_async(spu.ptr(a), spu.ptr(w), None, None, spu.ptr(out), M, N, K, 1,
+                                            spu.stream_ptr()))
+    _sync()
+    xin = a.float().cpu().double()
+    ref = 0.5 * xin * (1.0 + torch.erf(xin / 2 ** 0.5))
+    err = (out.float().cpu().double() - ref).abs()
+    assert (err <= 2.0 ** -8 * ref.abs() + 1e-5).all(), err.max().item()  # one bf16 rounding + 1e-5
 
 
 def test_gemm_inplace_residual(spu):

@@ -1,0 +1,81 @@
+#!/usr/bin/env python
+"""Tile sweep of the tcgen05 GEMM on the BERT-base / ViT-L shapes (GPU box only).
+
+Each (shape, epilogue, cta_group, BLOCK_N) runs `reps` back-to-back launches captured in
+one CUDA graph (so host encode/ctypes time is excluded and programmatic dependent launch
+is in effect, as in the replica's captured forward) and is timed with CUDA events.
+Prints one JSON line per configuration; correctness is tests/test_gpu_stages.py's job.
+"""
+import argparse
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import torch  # noqa: E402
+
+from starpu_inference_server_b200 import capi  # noqa: E402
+
+SHAPES = {  # name: (N, K, epilogue)
+    "qkv": (2304, 768, 0), "attn_out": (768, 768, 2), "ffn1": (3072, 768, 1), "ffn2": (768, 3072, 2),
+}
+
+
+def run(M, N, K, epi, cg, bn, reps, n_buf):
+    L = capi.lib()
+    a = [(torch.randn(M, K, device="cuda") * 0.5).to(torch.bfloat16) for _ in range(n_buf)]
+    w = (torch.randn(N, K, device="cuda") * 0.05).to(torch.bfloat16)
+    bias = torch.randn(N, device="cuda")
+    out = [torch.zeros(M, N, device="cuda", dtype=torch.float32 if epi == 2 else torch.bfloat16) for _ in range(n_buf)]
+    s = torch.cuda.Stream()
+
+    def enqueue():
+        for i in range(reps):
+            o = out[i % n_buf]
+            capi.check(L.spu_gemm_bf16_cfg_async(capi.ptr(a[i % n_buf]), capi.ptr(w), capi.ptr(bias),
+                                                 capi.ptr(o) if epi == 2 else None, capi.ptr(o), M, N, K, epi,
+                                                 cg, bn, capi.stream_ptr(s)))
+    with torch.cuda.stream(s):
+        enqueue()
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g, stream=s):
+        enqueue()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    best = 1e9
+    for _ in range(5):
+        e0.record()
+        g.replay()
+        e1.record()
+        torch.cuda.synchronize()
+        best = min(best, e0.elapsed_time(e1) / reps * 1e3)
+    return best
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--M", type=int, default=4096)
+    ap.add_argument("--reps", type=int, default=40)
+    ap.add_argument("--bufs", type=int, default=1, help="distinct A/out buffers rotated (1 = L2-warm, as in the forward)")
+    ap.add_argument("--shapes", default="qkv,attn_out,ffn1,ffn2")
+    ap.add_argument("--all", action="store_true", help="sweep every tile, not only the chosen one")
+    args = ap.parse_args()
+    for name in args.shapes.split(","):
+        N, K, epi = SHAPES[name]
+        cfgs = [(0, 0)]
+        if args.all:
+            cfgs += [(cg, bn) for cg in (2, 1) for bn in (256, 192, 128, 64) if N % bn == 0]
+        for cg, bn in cfgs:
+            try:
+                us = run(args.M, N, K, epi, cg, bn, args.reps, args.bufs)
+            except Exception as ex:  # keep sweeping
+                print(json.dumps({"shape": name, "cg": cg, "bn": bn, "error": str(ex)}), flush=True)
+                continue
+            tf = 2.0 * args.M * N * K / us / 1e6
+            print(json.dumps({"shape": name, "M": args.M, "N": N, "K": K, "epi": epi, "cg": cg, "bn": bn,
+                              "us": round(us, 2), "tflops": round(tf, 1)}), flush=True)
+
+
+if __name__ == "__main__":
+    main()
