@@ -121,6 +121,37 @@ spu_status spu_bert_forward_profiled(spu_replica *r, int32_t ws_idx,
                                      int32_t batch, int32_t seq, float *out,
                                      void *stream, float *stage_ms);
 
+/* Bytes of output0 for (batch, seq): batch*seq*hidden*4 (0 for a null / non-BERT replica).
+ * The codelet checks the STARPU_W buffer against it, like the reference's
+ * TORCH_CHECK(buffer.size() == out.nbytes()) (src/core/starpu_setup.cpp:840-842). */
+uint64_t spu_bert_output_bytes(const spu_replica *r, int32_t batch, int32_t seq);
+
+/* ---- ViT encoder (models/vit_l_16.yml: input fp32 [B,3,224,224] -> output fp32
+ *      [B,num_classes]; torchvision vit_{b,l}_16 graph, models/import_vit.py:10-13) ---- */
+typedef struct spu_vit_desc {
+  int32_t layers, hidden, heads, mlp, patch, image, channels, classes;
+  float ln_eps;
+} spu_vit_desc;
+
+/* Weight tensors, fp32 host, torchvision state-dict order restated in
+ * oracle/vit_oracle.py:weight_names(): conv_proj.weight [H,C,P,P], conv_proj.bias,
+ * class_token [1,1,H], encoder.pos_embedding [1,S,H], then per layer: ln_1.{weight,bias},
+ * self_attention.in_proj_{weight [3H,H],bias}, self_attention.out_proj.{weight,bias},
+ * ln_2.{weight,bias}, mlp.0.{weight,bias}, mlp.3.{weight,bias}; then encoder.ln.{weight,
+ * bias}, heads.head.{weight [classes,H],bias}. */
+#define SPU_VIT_NUM_TENSORS(layers) (4 + 12 * (layers) + 4)
+
+spu_status spu_vit_replica_create(const spu_vit_desc *desc, const float *const *tensors,
+                                  int32_t n_tensors, int32_t device, int32_t max_batch,
+                                  int32_t n_workspaces, uint32_t flags, spu_replica **out);
+
+/* pixels: DEVICE fp32 [batch, C, image, image] (NCHW, what StarPU hands the codelet as
+ * buffers[0]->ptr); logits: DEVICE fp32 [batch, classes]. */
+spu_status spu_vit_forward_async(spu_replica *r, int32_t ws_idx, const float *pixels,
+                                 int32_t batch, float *logits, void *stream);
+uint64_t spu_vit_input_bytes(const spu_replica *r, int32_t batch);
+uint64_t spu_vit_output_bytes(const spu_replica *r, int32_t batch);
+
 /* ---- Stage 1: gather + pad + mask (device) --------------------------------
  * Ragged batch assembly: request i supplies len[i] int64 token ids at
  * src_ids[i] (and optionally len[i] mask words at src_mask[i]; src_mask or

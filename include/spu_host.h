@@ -1,0 +1,151 @@
+/*
+ * spu_host.h -- C-ABI of libspu_host.so: the C++ host side of the inference path
+ * (StarPU-shaped codelet, slot pools, batch assembly, result slicing) driven through plain
+ * C calls so that tests and bench.py can exercise exactly what a StarPU worker would run.
+ *
+ * What sits behind it mirrors the reference one to one (names kept):
+ *   InferenceCodelet          src/core/starpu_setup.hpp:21-37, starpu_setup.cpp:559-846
+ *   InputSlotPool/OutputSlotPool  src/core/input_slot_pool.cpp:235-328, output_slot_pool.cpp:226-330
+ *   copy_job_inputs_to_slot   src/starpu_task_worker/slot_manager_component.cpp:649-727
+ *   resize_starpu_vector_handle   src/starpu_task_worker/starpu_vector_resize_utils.hpp:19-89
+ *   can_merge_jobs            src/starpu_task_worker/batch_composition_policy.cpp:102-151
+ *   slice_outputs_for_sub_job src/starpu_task_worker/batching_helpers.hpp:74-127
+ *   BatchCollector            src/starpu_task_worker/batch_collector_component.cpp:405-473
+ * The runtime underneath is real StarPU when built with -DSPU_USE_REAL_STARPU, else the
+ * in-repo stand-in (core/mini_starpu.cpp).  Nothing here computes on the CPU: every
+ * inference goes through the codelet's cuda_func -> include/spu_b200.h.
+ */
+#ifndef SPU_HOST_H
+#define SPU_HOST_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#include "spu_b200.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SPU_HOST_MAX_IO 16
+#define SPU_HOST_MAX_DIMS 8
+#define SPU_HOST_MAX_DEVICES 32
+
+/* element types of models/<name>.yml (TYPE_FP32, TYPE_INT64, ...) */
+#define SPU_DT_F32 0
+#define SPU_DT_F64 1
+#define SPU_DT_I32 2
+#define SPU_DT_I64 3
+#define SPU_DT_I8 4
+#define SPU_DT_U8 5
+#define SPU_DT_F16 6
+#define SPU_DT_BF16 7
+#define SPU_DT_BOOL 8
+
+#define SPU_MODEL_BERT 0
+#define SPU_MODEL_VIT 1
+#define SPU_MODEL_AFFINE 2 /* out = in*scale + shift: the reference tests' x+1 / x+1.5 / x*2 toys */
+
+typedef struct spu_tensor_cfg {
+  char name[64];
+  int32_t dtype;
+  int32_t ndims;
+  int64_t dims[SPU_HOST_MAX_DIMS]; /* dims[0] = per-request batch (1 in the shipped configs) */
+} spu_tensor_cfg;
+
+typedef struct spu_server_cfg {
+  /* use_cuda: [{device_ids: [...]}]  (config_loader_device.hpp:104-149) */
+  int32_t n_devices;
+  int32_t device_ids[SPU_HOST_MAX_DEVICES];
+  int32_t nworker_per_cuda; /* STARPU_NWORKER_PER_CUDA (models/bert.yml:6-8); 0 = env / 1 */
+  int32_t cuda_pipeline;    /* STARPU_CUDA_PIPELINE; 0 = env / 2 */
+  /* model + batching (models/bert.yml: max_batch_size, pool_size, batch_coalesce_timeout_ms) */
+  int32_t pool_size;
+  int32_t max_batch_size;
+  int32_t batch_coalesce_timeout_ms;
+  int32_t n_inputs, n_outputs;
+  spu_tensor_cfg inputs[SPU_HOST_MAX_IO], outputs[SPU_HOST_MAX_IO];
+  int32_t model_kind;
+  spu_replica *replicas[SPU_HOST_MAX_DEVICES]; /* replicas[i] serves device_ids[i] (BERT / ViT) */
+  int32_t n_workspaces;                        /* arenas each replica was created with */
+  float affine_scale, affine_shift;
+} spu_server_cfg;
+
+typedef struct spu_request {
+  int32_t request_id;
+  int64_t batch;                         /* rows this request carries (dims[0]) */
+  const void *inputs[SPU_HOST_MAX_IO];   /* host, contiguous [batch, ...] per model input */
+  void *outputs[SPU_HOST_MAX_IO];        /* host destination per model output (may be NULL) */
+} spu_request;
+
+typedef struct spu_result {
+  int32_t request_id;
+  int32_t ok;           /* 1 = outputs delivered */
+  int64_t rows;         /* processed_length of this request's slice */
+  int64_t batch_rows;   /* effective batch of the task it rode in */
+  int32_t worker_id, device_id, executed_on; /* executed_on: 0 CPU, 1 CUDA, 2 unknown */
+  double codelet_ms;    /* codelet_end - codelet_start (host time of the async enqueue) */
+  double task_ms;       /* before_starpu_submitted -> callback_start (task latency) */
+  double latency_ms;    /* enqueued -> callback_end */
+  char error[192];
+} spu_result;
+
+typedef struct spu_server spu_server;
+
+/* starpu_init + codelet + slot pools + replica table.  One server per process (StarPU is a
+ * process-wide singleton). */
+int32_t spu_server_create(const spu_server_cfg *cfg, spu_server **out);
+void spu_server_destroy(spu_server *s);
+
+/* One StarPU task from reqs[0] (master) + reqs[1..n) (aggregated sub-jobs, row order =
+ * request order).  fixed_worker >= 0 pins the task (warm-up).  Returns a ticket >= 0, or
+ * -1 with spu_host_last_error() set. */
+int64_t spu_server_submit_batch(spu_server *s, const spu_request *reqs, int32_t n, int32_t fixed_worker);
+/* Dynamic batching: the collector thread merges compatible requests up to max_batch_size
+ * rows or batch_coalesce_timeout_ms.  Ticket covers this one request. */
+int64_t spu_server_enqueue(spu_server *s, const spu_request *req);
+/* Blocks until every request of the ticket has completed; fills up to cap results (in
+ * request order) and returns how many the ticket held.  A ticket can be waited once. */
+int32_t spu_server_wait(spu_server *s, int64_t ticket, spu_result *results, int32_t cap);
+int32_t spu_server_wait_all(spu_server *s);
+/* counters: [0] tasks submitted, [1] requests completed, [2] free input slots, [3] free
+ * output slots, [4] StarPU workers, [5] codelet failures */
+void spu_server_stats(spu_server *s, int64_t out[6]);
+
+const char *spu_host_last_error(void);
+
+/* ---- unit-test seams (no runtime needed; mirror the reference's unit tests) ---------- */
+/* InferenceCodelet field values (unit_starpu_setup.cpp:4065-4074):
+ * out = {nbuffers, type, max_parallelism, cpu_funcs[0]!=0, cuda_funcs[0]!=0, cuda_flags[0], where} */
+void spu_host_codelet_fields(int64_t out[7]);
+/* buffer_byte_size (starpu_setup.cpp:515-542); returns 0 ok, 1 exception (message in last_error) */
+int32_t spu_host_buffer_byte_size(int32_t interface_id, uint32_t nx, uint64_t elemsize, int32_t null_buffer,
+                                  uint64_t *out);
+/* select_gpu_module (starpu_setup.cpp:725-778) over a table of n_models dummy replicas:
+ * returns the chosen index, or -1 on StarPUCodeletException (message in last_error). */
+int32_t spu_host_select_replica(const int32_t *device_ids, int32_t n_device_ids, const int32_t *worker_ids,
+                                int32_t n_worker_ids, int32_t n_models, int32_t worker_id, int32_t device_id);
+/* copy_job_inputs_to_slot over one input: n_jobs host arrays back to back into a slot of
+ * `capacity` bytes registered with elemsize; returns 0 ok / 1 exception.  nx_out = the
+ * handle's nx afterwards on node 0. */
+int32_t spu_host_gather_to_slot(const void *const *srcs, const uint64_t *nbytes, int32_t n_jobs, uint64_t elemsize,
+                                void *slot, uint64_t capacity, uint64_t *nx_out, uint64_t *bytes_out);
+/* slice_outputs_for_sub_job over one aggregated [rows, row_bytes] output: returns the byte
+ * offset and length of the view through *off_out / *len_out and the processed length. */
+int64_t spu_host_slice_rows(uint64_t rows, uint64_t row_bytes, int64_t offset, int64_t batch_size, uint64_t *off_out,
+                            uint64_t *len_out);
+/* can_merge_jobs over two single-input requests described by dims/dtype */
+int32_t spu_host_can_merge(const int64_t *dims_a, int32_t nd_a, int32_t dt_a, const int64_t *dims_b, int32_t nd_b,
+                           int32_t dt_b);
+/* Calls codelet.cuda_funcs[0] directly, like unit_starpu_setup.cpp:2332-2433: DEVICE fp32
+ * in/out of n elements, an affine "model" on `device`, mocked worker id / device id / stream.
+ * rec = {device_id, worker_id, executed_on, start!=0, end!=0, inflight gauge after}.
+ * Returns 0, or 1 when the codelet threw (message in last_error). */
+int32_t spu_host_call_cuda_func_affine(const float *in_dev, float *out_dev, uint64_t n, float scale, float shift,
+                                       int32_t device, int32_t worker_id, void *stream, int32_t n_models,
+                                       int32_t use_vector_iface, int64_t rec[6]);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SPU_HOST_H */

@@ -28,8 +28,13 @@ NVCC_FLAGS = ARCH + ["-std=c++17", "-O3", "-lineinfo", "-Xcompiler", "-fPIC",
                      "--expt-relaxed-constexpr",
                      "-I", os.path.join(ROOT, "include")]
 
-CUDA_SOURCES = ["replica.cu", "gemm_sm100.cu", "attention.cu", "rowops.cu"]
-HOST_SOURCES = ["inference_codelet.cpp", "slot_pools.cpp", "mini_starpu.cpp", "host_capi.cpp"]
+CUDA_SOURCES = ["replica.cu", "gemm_sm100.cu", "attention.cu", "rowops.cu", "vit.cu"]
+HOST_SOURCES = ["inference_codelet.cpp", "slot_pools.cpp", "task_runner.cpp", "mini_starpu.cpp", "host_capi.cpp",
+                "host_test_hooks.cpp"]
+CXX = os.environ.get("CXX", "g++")
+CUDA_HOME = os.environ.get("CUDA_HOME", "/usr/local/cuda")
+CXX_FLAGS = ["-std=c++20", "-O2", "-g", "-fPIC", "-Wall", "-Wextra", "-pthread",
+             "-I", os.path.join(ROOT, "include"), "-I", os.path.join(CUDA_HOME, "include")]
 
 
 def _digest(paths):
@@ -38,7 +43,7 @@ def _digest(paths):
         h.update(p.encode())
         with open(p, "rb") as f:
             h.update(f.read())
-    h.update(" ".join(NVCC_FLAGS).encode())
+    h.update(" ".join(NVCC_FLAGS + CXX_FLAGS).encode())
     return h.hexdigest()
 
 
@@ -66,7 +71,10 @@ def _build_lib(name, directory, sources, extra_link, force):
 
     def compile_one(src):
         o = os.path.join(OBJ, name + "." + src + ".o")
-        _run([NVCC] + NVCC_FLAGS + ["-x", "cu", "-c", os.path.join(directory, src), "-o", o])
+        if src.endswith(".cu"):
+            _run([NVCC] + NVCC_FLAGS + ["-c", os.path.join(directory, src), "-o", o])
+        else:  # plain C++ host code: no device code, C++20 (std::span)
+            _run([CXX] + CXX_FLAGS + ["-c", os.path.join(directory, src), "-o", o])
         return o
 
     with ThreadPoolExecutor(max_workers=min(8, len(sources))) as ex:

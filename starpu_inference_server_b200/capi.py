@@ -25,6 +25,8 @@ SYMBOLS = [
     "spu_gather_segments_async", "spu_scatter_segments_async", "spu_gemm_bf16_async", "spu_gemm_bf16_cfg_async",
     "spu_attention_async", "spu_layernorm_async", "spu_bert_embed_async", "spu_affine_f32_async",
     "spu_last_error", "spu_abi_version", "spu_device_count", "spu_device_is_sm100",
+    "spu_bert_output_bytes", "spu_vit_replica_create", "spu_vit_forward_async", "spu_vit_input_bytes",
+    "spu_vit_output_bytes",
 ]
 
 
@@ -38,6 +40,12 @@ class BertDesc(C.Structure):
     _fields_ = [("layers", C.c_int32), ("hidden", C.c_int32), ("heads", C.c_int32),
                 ("ffn", C.c_int32), ("vocab", C.c_int32), ("max_pos", C.c_int32),
                 ("type_vocab", C.c_int32), ("ln_eps", C.c_float)]
+
+
+class VitDesc(C.Structure):
+    _fields_ = [("layers", C.c_int32), ("hidden", C.c_int32), ("heads", C.c_int32), ("mlp", C.c_int32),
+                ("patch", C.c_int32), ("image", C.c_int32), ("channels", C.c_int32), ("classes", C.c_int32),
+                ("ln_eps", C.c_float)]
 
 
 _lib = None
@@ -70,10 +78,18 @@ def lib():
     L.spu_layernorm_async.argtypes = [vp, vp, vp, f32, vp, vp, i32, i32, vp]
     L.spu_bert_embed_async.argtypes = [vp, vp, vp, vp, vp, vp, vp, f32, i32, vp, vp, vp, i32, i32, i32, vp]
     L.spu_affine_f32_async.argtypes = [vp, vp, u64, f32, f32, vp]
+    L.spu_vit_replica_create.argtypes = [C.POINTER(VitDesc), C.POINTER(vp), i32, i32, i32, i32, C.c_uint32,
+                                         C.POINTER(vp)]
+    L.spu_vit_forward_async.argtypes = [vp, i32, vp, i32, vp, vp]
+    L.spu_bert_output_bytes.argtypes = [vp, i32, i32]
+    L.spu_vit_input_bytes.argtypes = [vp, i32]
+    L.spu_vit_output_bytes.argtypes = [vp, i32]
     L.spu_last_error.restype = C.c_char_p
     for name in SYMBOLS:
         fn = getattr(L, name)
-        if name not in ("spu_last_error",):
+        if name.endswith("_bytes"):
+            fn.restype = u64
+        elif name not in ("spu_last_error",):
             fn.restype = i32
     _lib = L
     return L

@@ -1,0 +1,365 @@
+// extern "C" surface of libspu_host.so (include/spu_host.h): server object = StarPU runtime
+// + TaskRunner + BatchCollector; tickets instead of foreign-thread callbacks into Python.
+#include <chrono>
+#include <condition_variable>
+#include <cstring>
+#include <deque>
+#include <map>
+#include <mutex>
+#include <thread>
+
+#include "../../include/spu_host.h"
+#include "task_runner.hpp"
+
+#if !defined(SPU_USE_REAL_STARPU)
+extern "C" long spu_mini_starpu_codelet_failures(void);
+#endif
+
+using namespace starpu_server;
+
+namespace {
+thread_local std::string g_host_error;
+void set_host_error(const std::string &m) { g_host_error = m; }
+
+ScalarType to_scalar(int32_t dt) {
+  switch (dt) {
+    case SPU_DT_F32: return ScalarType::Float32;
+    case SPU_DT_F64: return ScalarType::Float64;
+    case SPU_DT_I32: return ScalarType::Int32;
+    case SPU_DT_I64: return ScalarType::Int64;
+    case SPU_DT_I8: return ScalarType::Int8;
+    case SPU_DT_U8: return ScalarType::UInt8;
+    case SPU_DT_F16: return ScalarType::Float16;
+    case SPU_DT_BF16: return ScalarType::BFloat16;
+    default: return ScalarType::Bool;
+  }
+}
+
+TensorConfig to_cfg(const spu_tensor_cfg &c) {
+  TensorConfig t;
+  t.name = c.name;
+  t.type = to_scalar(c.dtype);
+  for (int i = 0; i < c.ndims && i < SPU_HOST_MAX_DIMS; ++i) t.dims.push_back(c.dims[i]);
+  return t;
+}
+
+double ms_between(MonotonicClock::time_point a, MonotonicClock::time_point b) {
+  if (a == MonotonicClock::time_point{} || b == MonotonicClock::time_point{}) return 0.0;
+  return std::chrono::duration<double, std::milli>(b - a).count();
+}
+
+struct Ticket {
+  int expected = 0, done = 0;
+  std::vector<spu_result> results;
+};
+}  // namespace
+
+struct spu_server {
+  std::vector<std::unique_ptr<DeviceModel>> models;
+  std::unique_ptr<TaskRunner> runner;
+  ModelConfig model;
+  bool starpu_up = false;
+  // tickets
+  std::mutex tmu;
+  std::condition_variable tcv;
+  std::map<int64_t, Ticket> tickets;
+  int64_t next_ticket = 0;
+  std::atomic<long> completed{0};
+  // BatchCollector (batch_collector_component.cpp): one thread forming batches
+  std::mutex qmu;
+  std::condition_variable qcv;
+  std::deque<std::shared_ptr<InferenceJob>> queue;
+  std::thread collector;
+  bool stop = false;
+  int coalesce_ms = 0;
+  int forming = 0;  // batches popped from the queue but not yet submitted (guarded by qmu)
+
+  std::shared_ptr<InferenceJob> make_job(const spu_request &rq, int64_t ticket, int index) {
+    auto job = std::make_shared<InferenceJob>();
+    job->request_id = rq.request_id;
+    job->timing.enqueued_time = MonotonicClock::now();
+    for (size_t i = 0; i < model.inputs.size(); ++i) {
+      HostTensor t;
+      t.data = static_cast<std::byte *>(const_cast<void *>(rq.inputs[i]));
+      t.type = model.inputs[i].type;
+      t.dims = model.inputs[i].dims;
+      if (t.dims.empty()) t.dims.push_back(rq.batch);
+      else t.dims[0] = rq.batch;
+      job->inputs.push_back(std::move(t));
+    }
+    std::vector<void *> dsts(rq.outputs, rq.outputs + model.outputs.size());
+    job->on_complete = [this, ticket, index, dsts](const JobResult &res) {
+      spu_result out{};
+      out.request_id = res.request_id;
+      out.ok = res.ok ? 1 : 0;
+      out.rows = res.rows;
+      out.batch_rows = res.batch_rows;
+      out.worker_id = res.worker_id;
+      out.device_id = res.device_id;
+      out.executed_on = static_cast<int32_t>(res.executed_on);
+      out.codelet_ms = ms_between(res.timing.codelet_start_time, res.timing.codelet_end_time);
+      out.task_ms = ms_between(res.timing.before_starpu_submitted_time, res.timing.callback_start_time);
+      std::snprintf(out.error, sizeof(out.error), "%s", res.error.c_str());
+      if (res.ok)
+        // the response copy the reference makes per request (fill_output_tensor,
+        // src/grpc/server/inference_service_io.cpp:377-419): slot view -> caller's buffer
+        for (size_t o = 0; o < res.outputs.size() && o < dsts.size(); ++o)
+          if (dsts[o] && res.outputs[o].defined()) std::memcpy(dsts[o], res.outputs[o].data, res.outputs[o].nbytes());
+      out.latency_ms = ms_between(res.timing.enqueued_time, MonotonicClock::now());
+      {
+        std::lock_guard<std::mutex> lk(tmu);
+        Ticket &t = tickets[ticket];
+        if (static_cast<int>(t.results.size()) <= index) t.results.resize(static_cast<size_t>(index) + 1);
+        t.results[static_cast<size_t>(index)] = out;
+        ++t.done;
+      }
+      ++completed;
+      tcv.notify_all();
+    };
+    return job;
+  }
+
+  int64_t open_ticket(int n) {
+    std::lock_guard<std::mutex> lk(tmu);
+    const int64_t id = next_ticket++;
+    tickets[id].expected = n;
+    tickets[id].results.resize(static_cast<size_t>(n));
+    return id;
+  }
+
+  void fail_ticket_entry(int64_t ticket, int index, int request_id, const std::string &why) {
+    {
+      std::lock_guard<std::mutex> lk(tmu);
+      Ticket &t = tickets[ticket];
+      spu_result r{};
+      r.request_id = request_id;
+      r.ok = 0;
+      r.worker_id = r.device_id = -1;
+      r.executed_on = 2;
+      std::snprintf(r.error, sizeof(r.error), "%s", why.c_str());
+      t.results[static_cast<size_t>(index)] = r;
+      ++t.done;
+    }
+    tcv.notify_all();
+  }
+
+  void collector_loop() {
+    for (;;) {
+      std::vector<std::shared_ptr<InferenceJob>> batch;
+      {
+        std::unique_lock<std::mutex> lk(qmu);
+        qcv.wait(lk, [&] { return stop || !queue.empty(); });
+        if (queue.empty()) return;
+        batch.push_back(queue.front());
+        queue.pop_front();
+        ++forming;
+        int64_t rows = batch[0]->batch_size();
+        const auto deadline = std::chrono::steady_clock::now() + std::chrono::milliseconds(coalesce_ms);
+        while (rows < model.max_batch_size) {
+          if (queue.empty()) {
+            if (coalesce_ms <= 0 || stop) break;
+            if (qcv.wait_until(lk, deadline) == std::cv_status::timeout && queue.empty()) break;
+            if (queue.empty()) continue;
+          }
+          auto &cand = queue.front();
+          if (!can_merge_jobs(batch[0].get(), cand.get())) break;  // incompatible: starts the next batch
+          if (rows + cand->batch_size() > model.max_batch_size) break;
+          rows += cand->batch_size();
+          batch.push_back(cand);
+          queue.pop_front();
+        }
+      }
+      try {
+        runner->submit_batch(batch);
+      } catch (const std::exception &e) {
+        for (auto &j : batch) {
+          JobResult r;
+          r.request_id = j->request_id;
+          r.ok = false;
+          r.error = e.what();
+          r.timing.enqueued_time = j->timing.enqueued_time;
+          if (j->on_complete) j->on_complete(r);
+        }
+      }
+      {
+        std::lock_guard<std::mutex> lk(qmu);
+        --forming;
+      }
+    }
+  }
+};
+
+extern "C" {
+
+const char *spu_host_last_error(void) { return g_host_error.c_str(); }
+void spu_host_set_error_for_hooks(const char *m) { set_host_error(m ? m : ""); }
+
+int32_t spu_server_create(const spu_server_cfg *cfg, spu_server **out) {
+  if (!cfg || !out) {
+    set_host_error("server_create: null argument");
+    return 1;
+  }
+  *out = nullptr;
+  try {
+    if (cfg->n_devices < 0 || cfg->n_devices > SPU_HOST_MAX_DEVICES) throw std::invalid_argument("bad device count");
+    if (cfg->n_inputs <= 0 || cfg->n_inputs > SPU_HOST_MAX_IO || cfg->n_outputs <= 0 ||
+        cfg->n_outputs > SPU_HOST_MAX_IO)
+      throw std::invalid_argument("bad tensor count");
+    auto s = std::make_unique<spu_server>();
+    starpu_conf conf;
+    starpu_conf_init(&conf);
+    conf.sched_policy_name = "eager";
+    conf.ncpus = 0;
+    conf.ncuda = cfg->n_devices;
+    conf.use_explicit_workers_cuda_gpuid = 1;
+    for (int i = 0; i < cfg->n_devices; ++i) conf.workers_cuda_gpuid[i] = static_cast<unsigned>(cfg->device_ids[i]);
+#if !defined(SPU_USE_REAL_STARPU)
+    conf.nworker_per_cuda = cfg->nworker_per_cuda;
+    conf.cuda_pipeline = cfg->cuda_pipeline;
+#endif
+    const int rc = starpu_init(&conf);
+    if (rc != 0) throw std::runtime_error("starpu_init failed with code " + std::to_string(rc));
+    s->starpu_up = true;
+    try {
+      s->model.name = "model";
+      for (int i = 0; i < cfg->n_inputs; ++i) s->model.inputs.push_back(to_cfg(cfg->inputs[i]));
+      for (int i = 0; i < cfg->n_outputs; ++i) s->model.outputs.push_back(to_cfg(cfg->outputs[i]));
+      s->model.max_batch_size = cfg->max_batch_size > 0 ? cfg->max_batch_size : 1;
+      s->model.pool_size = cfg->pool_size > 0 ? cfg->pool_size : 12;
+      s->coalesce_ms = cfg->batch_coalesce_timeout_ms;
+      std::vector<int> dev_ids;
+      std::vector<DeviceModel *> models;
+      for (int i = 0; i < cfg->n_devices; ++i) {
+        auto m = std::make_unique<DeviceModel>();
+        m->kind = cfg->model_kind == SPU_MODEL_BERT  ? DeviceModel::Kind::Bert
+                  : cfg->model_kind == SPU_MODEL_VIT ? DeviceModel::Kind::Vit
+                                                     : DeviceModel::Kind::Affine;
+        m->replica = cfg->replicas[i];
+        m->n_workspaces = cfg->n_workspaces;
+        m->scale = cfg->affine_scale;
+        m->shift = cfg->affine_shift;
+        m->device_id = cfg->device_ids[i];
+        if (m->kind != DeviceModel::Kind::Affine && m->replica == nullptr)
+          throw std::invalid_argument("missing replica for device " + std::to_string(cfg->device_ids[i]));
+        dev_ids.push_back(cfg->device_ids[i]);
+        models.push_back(m.get());
+        s->models.push_back(std::move(m));
+      }
+      s->runner = std::make_unique<TaskRunner>(s->model, dev_ids, models);
+      spu_server *raw = s.get();
+      s->collector = std::thread([raw] { raw->collector_loop(); });
+    } catch (...) {
+      s->runner.reset();
+      starpu_shutdown();
+      throw;
+    }
+    *out = s.release();
+    return 0;
+  } catch (const std::exception &e) {
+    set_host_error(e.what());
+    return 1;
+  }
+}
+
+void spu_server_destroy(spu_server *s) {
+  if (!s) return;
+  {
+    std::lock_guard<std::mutex> lk(s->qmu);
+    s->stop = true;
+  }
+  s->qcv.notify_all();
+  if (s->collector.joinable()) s->collector.join();
+  if (s->runner) s->runner->wait_for_all();
+  for (auto &m : s->models)
+    if (m->replica) forget_replica_workspaces(m->replica);
+  s->runner.reset();  // unregisters the slot handles while the runtime is still up
+  if (s->starpu_up) starpu_shutdown();
+  delete s;
+}
+
+int64_t spu_server_submit_batch(spu_server *s, const spu_request *reqs, int32_t n, int32_t fixed_worker) {
+  if (!s || !reqs || n <= 0) {
+    set_host_error("submit_batch: bad argument");
+    return -1;
+  }
+  const int64_t ticket = s->open_ticket(n);
+  std::vector<std::shared_ptr<InferenceJob>> jobs;
+  for (int i = 0; i < n; ++i) jobs.push_back(s->make_job(reqs[i], ticket, i));
+  if (fixed_worker >= 0) jobs[0]->fixed_worker_id = fixed_worker;
+  try {
+    s->runner->submit_batch(jobs);
+  } catch (const std::exception &e) {
+    set_host_error(e.what());
+    std::lock_guard<std::mutex> lk(s->tmu);
+    s->tickets.erase(ticket);
+    return -1;
+  }
+  return ticket;
+}
+
+int64_t spu_server_enqueue(spu_server *s, const spu_request *req) {
+  if (!s || !req) {
+    set_host_error("enqueue: bad argument");
+    return -1;
+  }
+  if (req->batch < 1 || req->batch > s->model.max_batch_size) {
+    set_host_error("enqueue: request batch exceeds max_batch_size");
+    return -1;
+  }
+  const int64_t ticket = s->open_ticket(1);
+  auto job = s->make_job(*req, ticket, 0);
+  {
+    std::lock_guard<std::mutex> lk(s->qmu);
+    s->queue.push_back(std::move(job));
+  }
+  s->qcv.notify_all();
+  return ticket;
+}
+
+int32_t spu_server_wait(spu_server *s, int64_t ticket, spu_result *results, int32_t cap) {
+  if (!s) return -1;
+  std::unique_lock<std::mutex> lk(s->tmu);
+  auto it = s->tickets.find(ticket);
+  if (it == s->tickets.end()) {
+    set_host_error("wait: unknown ticket");
+    return -1;
+  }
+  s->tcv.wait(lk, [&] {
+    auto f = s->tickets.find(ticket);
+    return f != s->tickets.end() && f->second.done >= f->second.expected;
+  });
+  it = s->tickets.find(ticket);
+  const int n = it->second.expected;
+  for (int i = 0; i < n && i < cap && results; ++i) results[i] = it->second.results[static_cast<size_t>(i)];
+  s->tickets.erase(it);
+  return n;
+}
+
+int32_t spu_server_wait_all(spu_server *s) {
+  if (!s) return -1;
+  for (;;) {
+    {
+      std::lock_guard<std::mutex> lk(s->qmu);
+      if (s->queue.empty() && s->forming == 0) break;
+    }
+    std::this_thread::sleep_for(std::chrono::microseconds(200));
+  }
+  s->runner->wait_for_all();
+  return 0;
+}
+
+void spu_server_stats(spu_server *s, int64_t out[6]) {
+  if (!s || !out) return;
+  out[0] = s->runner->tasks_submitted();
+  out[1] = s->completed.load();
+  out[2] = s->runner->input_pool().free_slots();
+  out[3] = s->runner->output_pool().free_slots();
+  out[4] = starpu_worker_get_count();
+#if !defined(SPU_USE_REAL_STARPU)
+  out[5] = spu_mini_starpu_codelet_failures();
+#else
+  out[5] = 0;
+#endif
+}
+
+}  // extern "C"

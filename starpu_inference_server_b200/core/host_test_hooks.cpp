@@ -1,0 +1,223 @@
+// Unit-test seams of libspu_host.so (second half of include/spu_host.h): each one drives a
+// single host-side function the way the reference's own unit tests do, so that
+// tests/test_host_*.py read like tests/unit/core/unit_starpu_setup.cpp and
+// tests/unit/starpu/unit_starpu_task_runner_*.cpp.
+#include <cstring>
+
+#include "../../include/spu_host.h"
+#include "task_runner.hpp"
+
+using namespace starpu_server;
+
+// shares the thread-local error slot of host_capi.cpp
+extern "C" void spu_host_set_error_for_hooks(const char *m);
+
+namespace {
+void fail(const std::exception &e) { spu_host_set_error_for_hooks(e.what()); }
+
+int g_mock_worker = 0, g_mock_device = 0;
+void *g_mock_stream = nullptr;
+int mock_worker_id() { return g_mock_worker; }
+int mock_worker_devid(int) { return g_mock_device; }
+void *mock_stream() { return g_mock_stream; }
+}  // namespace
+
+extern "C" {
+
+void spu_host_codelet_fields(int64_t out[7]) {
+  InferenceCodelet cl;
+  starpu_codelet *c = cl.get_codelet();
+  out[0] = c->nbuffers;
+  out[1] = static_cast<int64_t>(c->type);
+  out[2] = c->max_parallelism;
+  out[3] = c->cpu_funcs[0] != nullptr;
+  out[4] = c->cuda_funcs[0] != nullptr;
+  out[5] = static_cast<int64_t>(c->cuda_flags[0]);
+  out[6] = static_cast<int64_t>(c->where);
+}
+
+int32_t spu_host_buffer_byte_size(int32_t interface_id, uint32_t nx, uint64_t elemsize, int32_t null_buffer,
+                                  uint64_t *out) {
+  try {
+    if (null_buffer) {
+      *out = buffer_byte_size(nullptr);
+      return 0;
+    }
+    if (interface_id == STARPU_VECTOR_INTERFACE_ID) {
+      starpu_vector_interface v{};
+      v.id = STARPU_VECTOR_INTERFACE_ID;
+      v.nx = nx;
+      v.elemsize = static_cast<size_t>(elemsize);
+      *out = buffer_byte_size(reinterpret_cast<const StarpuBufferInterface *>(&v));
+      return 0;
+    }
+    starpu_variable_interface v{};
+    v.id = static_cast<starpu_data_interface_id>(interface_id);
+    v.elemsize = static_cast<size_t>(elemsize);
+    *out = buffer_byte_size(&v);
+    return 0;
+  } catch (const std::exception &e) {
+    fail(e);
+    return 1;
+  }
+}
+
+int32_t spu_host_select_replica(const int32_t *device_ids, int32_t n_device_ids, const int32_t *worker_ids,
+                                int32_t n_worker_ids, int32_t n_models, int32_t worker_id, int32_t device_id) {
+  InferenceParams p;
+  std::vector<DeviceModel> models(static_cast<size_t>(n_models > 0 ? n_models : 0));
+  for (auto &m : models) p.models.models_gpu.push_back(&m);
+  for (int i = 0; i < n_device_ids; ++i) p.models.device_ids.push_back(device_ids[i]);
+  for (int i = 0; i < n_worker_ids; ++i) p.models.worker_ids.push_back(worker_ids[i]);
+  try {
+    DeviceModel *m = select_gpu_module(p, worker_id, device_id);
+    return static_cast<int32_t>(m - models.data());
+  } catch (const StarPUCodeletException &e) {
+    fail(e);
+    return -1;
+  }
+}
+
+int32_t spu_host_gather_to_slot(const void *const *srcs, const uint64_t *nbytes, int32_t n_jobs, uint64_t elemsize,
+                                void *slot, uint64_t capacity, uint64_t *nx_out, uint64_t *bytes_out) {
+  // a slot of one input registered exactly like InputSlotPool does (input_slot_pool.cpp:195-214)
+  starpu_data_handle_t h = nullptr;
+  starpu_vector_data_register(&h, STARPU_MAIN_RAM, reinterpret_cast<uintptr_t>(slot),
+                              static_cast<uint32_t>(capacity / (elemsize ? elemsize : 1)), static_cast<size_t>(elemsize));
+  std::vector<InferenceJob> jobs(static_cast<size_t>(n_jobs));
+  for (int j = 0; j < n_jobs; ++j) {
+    HostTensor t;
+    t.data = static_cast<std::byte *>(const_cast<void *>(srcs[j]));
+    t.type = elemsize == 8 ? ScalarType::Int64 : (elemsize == 4 ? ScalarType::Float32 : ScalarType::UInt8);
+    t.dims = {static_cast<int64_t>(nbytes[j] / (elemsize ? elemsize : 1))};
+    jobs[static_cast<size_t>(j)].inputs.push_back(std::move(t));
+  }
+  std::vector<const InferenceJob *> pending;
+  for (int j = 1; j < n_jobs; ++j) pending.push_back(&jobs[static_cast<size_t>(j)]);
+  int32_t rc = 0;
+  try {
+    HostBufferInfo info;
+    info.bytes = static_cast<size_t>(capacity);
+    const size_t copied = copy_job_inputs_to_slot(n_jobs > 0 ? &jobs[0] : nullptr, pending, {h},
+                                                  {static_cast<std::byte *>(slot)}, {info});
+    if (bytes_out) *bytes_out = copied;
+    if (nx_out) *nx_out = static_cast<starpu_vector_interface *>(starpu_data_get_interface_on_node(h, 0))->nx;
+  } catch (const std::exception &e) {
+    fail(e);
+    rc = 1;
+  }
+  starpu_data_unregister(h);
+  return rc;
+}
+
+int64_t spu_host_slice_rows(uint64_t rows, uint64_t row_bytes, int64_t offset, int64_t batch_size, uint64_t *off_out,
+                            uint64_t *len_out) {
+  static std::byte base_byte;
+  HostTensor t;
+  t.data = &base_byte;  // only address arithmetic is performed
+  t.type = ScalarType::UInt8;
+  t.dims = {static_cast<int64_t>(rows), static_cast<int64_t>(row_bytes)};
+  std::vector<HostTensor> agg;
+  if (rows > 0) agg.push_back(t);
+  const SubJobSliceResult r = slice_outputs_for_sub_job(agg, offset, batch_size);
+  *off_out = 0;
+  *len_out = 0;
+  if (!r.outputs.empty() && r.outputs[0].defined()) {
+    *off_out = static_cast<uint64_t>(r.outputs[0].data - &base_byte);
+    *len_out = r.outputs[0].nbytes();
+  }
+  return r.processed_length;
+}
+
+int32_t spu_host_can_merge(const int64_t *dims_a, int32_t nd_a, int32_t dt_a, const int64_t *dims_b, int32_t nd_b,
+                           int32_t dt_b) {
+  static std::byte dummy;
+  auto mk = [](const int64_t *d, int32_t nd, int32_t dt) {
+    InferenceJob j;
+    HostTensor t;
+    t.data = &dummy;
+    t.type = static_cast<ScalarType>(dt);
+    t.dims.assign(d, d + nd);
+    j.inputs.push_back(std::move(t));
+    return j;
+  };
+  const InferenceJob a = mk(dims_a, nd_a, dt_a), b = mk(dims_b, nd_b, dt_b);
+  return can_merge_jobs(&a, &b) ? 1 : 0;
+}
+
+int32_t spu_host_call_cuda_func_affine(const float *in_dev, float *out_dev, uint64_t n, float scale, float shift,
+                                       int32_t device, int32_t worker_id, void *stream, int32_t n_models,
+                                       int32_t use_vector_iface, int64_t rec[6]) {
+  g_mock_worker = worker_id;
+  g_mock_device = device;
+  g_mock_stream = stream;
+  WorkerContextHooks hooks;
+  hooks.worker_get_id = &mock_worker_id;
+  hooks.worker_get_devid = &mock_worker_devid;
+  hooks.cuda_get_local_stream = &mock_stream;
+  set_worker_context_hooks(hooks);
+
+  DeviceModel model;
+  model.kind = DeviceModel::Kind::Affine;
+  model.scale = scale;
+  model.shift = shift;
+  model.device_id = device;
+  InferenceParams params;  // make_basic_params(n) of the reference tests
+  params.num_inputs = 1;
+  params.num_outputs = 1;
+  params.layout.dims = {{static_cast<int64_t>(n)}};
+  params.layout.num_dims = {1};
+  params.layout.input_types = {ScalarType::Float32};
+  params.limits.max_inputs = InferLimits::MaxInputs;
+  params.limits.max_dims = InferLimits::MaxDims;
+  params.models.models_gpu.resize(static_cast<size_t>(n_models > 0 ? n_models : 0), nullptr);
+  if (device >= 0 && device < n_models) params.models.models_gpu[static_cast<size_t>(device)] = &model;
+
+  int rec_dev = -1, rec_worker = -1;
+  DeviceType rec_on = DeviceType::Unknown;
+  MonotonicClock::time_point t0{}, t1{};
+  params.device.device_id = &rec_dev;
+  params.device.worker_id = &rec_worker;
+  params.device.executed_on = &rec_on;
+  params.timing.codelet_start_time = &t0;
+  params.timing.codelet_end_time = &t1;
+
+  starpu_variable_interface vin{}, vout{};
+  starpu_vector_interface win{}, wout{};
+  void *buffers[2];
+  if (use_vector_iface) {
+    win.id = wout.id = STARPU_VECTOR_INTERFACE_ID;
+    win.ptr = reinterpret_cast<uintptr_t>(in_dev);
+    wout.ptr = reinterpret_cast<uintptr_t>(out_dev);
+    win.nx = wout.nx = static_cast<uint32_t>(n);
+    win.elemsize = wout.elemsize = sizeof(float);
+    buffers[0] = &win;
+    buffers[1] = &wout;
+  } else {
+    // make_variable_interface (tests/common/test_utils.hpp:88-135): elemsize = n * sizeof(T)
+    vin.id = vout.id = STARPU_VARIABLE_INTERFACE_ID;
+    vin.ptr = reinterpret_cast<uintptr_t>(in_dev);
+    vout.ptr = reinterpret_cast<uintptr_t>(out_dev);
+    vin.elemsize = vout.elemsize = static_cast<size_t>(n) * sizeof(float);
+    buffers[0] = &vin;
+    buffers[1] = &vout;
+  }
+  InferenceCodelet codelet;
+  int32_t rc = 0;
+  try {
+    codelet.get_codelet()->cuda_funcs[0](buffers, &params);
+  } catch (const StarPUCodeletException &e) {
+    fail(e);
+    rc = 1;
+  }
+  rec[0] = rec_dev;
+  rec[1] = rec_worker;
+  rec[2] = static_cast<int64_t>(rec_on);
+  rec[3] = t0.time_since_epoch().count() != 0;
+  rec[4] = t1.time_since_epoch().count() != 0;
+  rec[5] = worker_inflight_gauge(worker_id);
+  set_worker_context_hooks(WorkerContextHooks{});
+  return rc;
+}
+
+}  // extern "C"

@@ -1,0 +1,358 @@
+#include "task_runner.hpp"
+
+#include <algorithm>
+#include <cstdlib>
+#include <cstring>
+#include <limits>
+#include <mutex>
+
+namespace starpu_server {
+
+auto can_merge_jobs(const InferenceJob *lhs, const InferenceJob *rhs) -> bool {
+  if (!lhs || !rhs) return false;
+  if (lhs->inputs.size() != rhs->inputs.size()) return false;
+  for (size_t i = 0; i < lhs->inputs.size(); ++i)
+    if (lhs->inputs[i].type != rhs->inputs[i].type) return false;
+  for (size_t i = 0; i < lhs->inputs.size(); ++i) {
+    const HostTensor &a = lhs->inputs[i], &b = rhs->inputs[i];
+    if (!a.defined() || !b.defined()) return false;
+    if (a.dims.size() != b.dims.size()) return false;
+    if (a.dims.empty()) return false;
+    for (size_t d = 1; d < a.dims.size(); ++d)
+      if (a.dims[d] != b.dims[d]) return false;
+  }
+  return true;
+}
+
+void resize_starpu_vector_interface(starpu_vector_interface *vi, VectorResizeSpec spec, bool is_input_handle) {
+  if (vi == nullptr) return;
+  const auto elem_size = vi->elemsize;
+  if (elem_size == 0) throw StarPUDataAcquireException("StarPU vector interface reported zero element size");
+  if (spec.byte_count % elem_size != 0) {
+    const std::string msg = std::string(is_input_handle ? "Input" : "Output") + " tensor byte size (" +
+                            std::to_string(spec.byte_count) + ") is not divisible by element size (" +
+                            std::to_string(elem_size) + ")";
+    if (is_input_handle) throw InvalidInputTensorException(msg);
+    throw InvalidInferenceJobException(msg);
+  }
+  spec.element_count = spec.byte_count / elem_size;
+  const auto alloc_size = vi->allocsize;
+  if (alloc_size != std::numeric_limits<size_t>::max() && alloc_size != 0 && spec.byte_count > alloc_size) {
+    const std::string msg = std::string(is_input_handle ? "Input" : "Output") + " tensor requires " +
+                            std::to_string(spec.byte_count) + " bytes but slot capacity is " +
+                            std::to_string(alloc_size) + " bytes";
+    if (is_input_handle) throw InputPoolCapacityException(msg);
+    throw InvalidInferenceJobException(msg);
+  }
+  vi->nx = static_cast<uint32_t>(spec.element_count);
+}
+
+void resize_starpu_vector_handle(starpu_data_handle_t handle, VectorResizeSpec spec, bool is_input_handle) {
+  if (handle == nullptr) throw StarPUDataAcquireException("StarPU vector handle is null");
+  if (starpu_data_get_interface_id(handle) != STARPU_VECTOR_INTERFACE_ID)
+    throw StarPUDataAcquireException("Expected StarPU vector interface for handle");
+  const unsigned memory_nodes = starpu_memory_nodes_get_count();
+  for (unsigned node = 0; node < memory_nodes; ++node) {
+    auto *raw = starpu_data_get_interface_on_node(handle, node);
+    if (raw == nullptr) continue;
+    resize_starpu_vector_interface(static_cast<starpu_vector_interface *>(raw), spec, is_input_handle);
+  }
+}
+
+auto copy_job_inputs_to_slot(const InferenceJob *job, const std::vector<const InferenceJob *> &pending_jobs,
+                             const std::vector<starpu_data_handle_t> &handles,
+                             const std::vector<std::byte *> &base_ptrs,
+                             const std::vector<HostBufferInfo> &buffer_infos) -> std::size_t {
+  if (!job) return 0;
+  std::size_t total_bytes_copied = 0;
+  for (std::size_t input_idx = 0; input_idx < job->inputs.size(); ++input_idx) {
+    std::byte *dst = base_ptrs[input_idx];
+    const std::size_t capacity = buffer_infos[input_idx].bytes;
+    std::size_t offset = 0, total_numel = 0, total_bytes = 0;
+    auto copy_tensor = [&](const HostTensor &t) {
+      if (!t.defined())
+        throw InvalidInputTensorException("input[" + std::to_string(input_idx) + "] is not a defined host tensor");
+      const size_t bytes = t.nbytes();
+      if (capacity < offset + bytes)
+        throw InputPoolCapacityException("Input tensor exceeds allocated slot buffer capacity");
+      std::memcpy(dst + offset, t.data, bytes);
+      offset += bytes;
+      total_bytes += bytes;
+      total_numel += t.numel();
+      total_bytes_copied += bytes;
+    };
+    copy_tensor(job->inputs[input_idx]);
+    for (const InferenceJob *pending : pending_jobs) {
+      if (!pending) continue;
+      if (input_idx >= pending->inputs.size())
+        throw InconsistentInputTensorCountException("Inconsistent input tensor count");
+      copy_tensor(pending->inputs[input_idx]);
+    }
+    resize_starpu_vector_handle(handles[input_idx], VectorResizeSpec{total_numel, total_bytes}, true);
+  }
+  return total_bytes_copied;
+}
+
+auto slice_outputs_for_sub_job(const std::vector<HostTensor> &aggregated_outputs, int64_t offset,
+                               int64_t batch_size) -> SubJobSliceResult {
+  SubJobSliceResult result;
+  const int64_t slice_size = std::max<int64_t>(1, batch_size);
+  result.processed_length = slice_size;
+  if (aggregated_outputs.empty()) return result;
+  bool determined_length = false;
+  for (const HostTensor &t : aggregated_outputs) {
+    if (!t.defined() || t.dims.empty()) {
+      result.outputs.push_back(t);
+      continue;
+    }
+    const int64_t available = t.dims[0];
+    const int64_t slice_end = std::min<int64_t>(available, offset + slice_size);
+    const int64_t length = std::max<int64_t>(0, slice_end - offset);
+    if (length <= 0 || offset < 0) {
+      result.outputs.emplace_back();
+      continue;
+    }
+    if (!determined_length) {
+      result.processed_length = length;
+      determined_length = true;
+    }
+    const size_t sample_bytes = t.nbytes() / static_cast<size_t>(available);
+    HostTensor view = t;
+    view.data = t.data + static_cast<size_t>(offset) * sample_bytes;
+    view.dims[0] = length;
+    result.outputs.push_back(std::move(view));
+  }
+  return result;
+}
+
+// ---------------------------------------------------------------------------------
+struct TaskRunner::CallbackContext {
+  TaskRunner *runner = nullptr;
+  std::vector<std::shared_ptr<InferenceJob>> jobs;  // [0] = master
+  std::unique_ptr<InferenceParams> params;
+  int input_slot = -1, output_slot = -1;
+  std::vector<starpu_data_handle_t> outputs_handles;
+  int64_t effective_batch = 0;
+  int worker_id = -1, device_id = -1;
+  DeviceType executed_on = DeviceType::Unknown;
+  JobTiming timing;
+  std::vector<bool> acquired;
+};
+
+TaskRunner::TaskRunner(ModelConfig model, std::vector<int> device_ids, std::vector<DeviceModel *> models_gpu)
+    : model_(std::move(model)), device_ids_(std::move(device_ids)), models_gpu_(std::move(models_gpu)) {
+  if (models_gpu_.size() > InferLimits::MaxModelsGPU) throw std::invalid_argument("too many GPU replicas");
+  if (model_.inputs.empty() || model_.inputs.size() > InferLimits::MaxInputs)
+    throw std::invalid_argument("model must declare 1..16 inputs");
+  if (model_.outputs.empty()) throw std::invalid_argument("model must declare outputs");
+  const bool pinned = !device_ids_.empty();
+  input_pool_ = std::make_unique<InputSlotPool>(model_.inputs, model_.max_batch_size, model_.pool_size, pinned);
+  output_pool_ = std::make_unique<OutputSlotPool>(model_.outputs, model_.max_batch_size, model_.pool_size, pinned);
+}
+
+TaskRunner::~TaskRunner() { wait_for_all(); }
+
+void TaskRunner::wait_for_all() { starpu_task_wait_for_all(); }
+
+void TaskRunner::submit_batch(const std::vector<std::shared_ptr<InferenceJob>> &jobs) {
+  if (jobs.empty() || !jobs.front()) throw InvalidInferenceJobException("empty batch");
+  const InferenceJob *master = jobs.front().get();
+  if (master->inputs.size() != model_.inputs.size())
+    throw InputPoolMismatchException("Input count mismatch between job and slot");
+  int64_t effective_batch = 0;
+  std::vector<const InferenceJob *> pending;
+  for (size_t k = 0; k < jobs.size(); ++k) {
+    if (!jobs[k]) continue;
+    if (k > 0) {
+      if (!can_merge_jobs(master, jobs[k].get()))
+        throw InvalidInferenceJobException("sub-job cannot be merged with the master job (shape/type mismatch)");
+      pending.push_back(jobs[k].get());
+    }
+    effective_batch += jobs[k]->batch_size();  // aggregate_batch_metadata: sum of sub batch sizes
+  }
+  if (effective_batch < 1 || effective_batch > input_pool_->max_batch_size())
+    throw InputPoolCapacityException("Batch size exceeds input pool capacity");
+
+  auto ctx = std::make_unique<CallbackContext>();
+  ctx->runner = this;
+  ctx->jobs = jobs;
+  ctx->effective_batch = effective_batch;
+  ctx->input_slot = input_pool_->acquire();
+  ctx->output_slot = output_pool_->acquire();
+  struct SlotGuard {
+    TaskRunner *r;
+    CallbackContext *c;
+    bool armed = true;
+    ~SlotGuard() {
+      if (!armed) return;
+      r->input_pool_->release(c->input_slot);
+      r->output_pool_->release(c->output_slot);
+    }
+  } guard{this, ctx.get()};
+
+  const auto &in_handles = input_pool_->handles(ctx->input_slot);
+  const auto &out_handles = output_pool_->handles(ctx->output_slot);
+  // SlotHandleLease(handles, STARPU_W) around the host gather (slot_manager_component.cpp:425)
+  size_t leased = 0;
+  try {
+    for (; leased < in_handles.size(); ++leased)
+      if (starpu_data_acquire(in_handles[leased], STARPU_W) != 0)
+        throw StarPUDataAcquireException("starpu_data_acquire failed");
+    copy_job_inputs_to_slot(master, pending, in_handles, input_pool_->base_ptrs(ctx->input_slot),
+                            input_pool_->host_buffer_infos(ctx->input_slot));
+  } catch (...) {
+    for (size_t i = 0; i < leased; ++i) starpu_data_release(in_handles[i]);
+    throw;
+  }
+  for (size_t i = 0; i < leased; ++i) starpu_data_release(in_handles[i]);
+
+  // outputs: prototype resized to [effective_batch, ...] (resize_outputs_for_batch)
+  for (size_t o = 0; o < out_handles.size(); ++o) {
+    const size_t numel = output_pool_->per_sample_numel(o) * static_cast<size_t>(effective_batch);
+    resize_starpu_vector_handle(out_handles[o],
+                                VectorResizeSpec{numel, numel * element_size(output_pool_->tensor_type(o))}, false);
+  }
+
+  auto params = std::make_unique<InferenceParams>();
+  params->models.device_ids = device_ids_;
+  params->models.models_gpu = models_gpu_;
+  params->num_inputs = model_.inputs.size();
+  params->num_outputs = model_.outputs.size();
+  params->batch_size = effective_batch;
+  params->request_id = master->request_id;
+  params->limits.max_inputs = InferLimits::MaxInputs;
+  params->limits.max_dims = InferLimits::MaxDims;
+  for (size_t i = 0; i < master->inputs.size(); ++i) {
+    std::vector<int64_t> dims = master->inputs[i].dims;
+    if (!dims.empty()) dims[0] = effective_batch;  // inference_task.cpp:606-613
+    params->layout.num_dims.push_back(static_cast<int64_t>(dims.size()));
+    params->layout.dims.push_back(std::move(dims));
+    params->layout.input_types.push_back(master->inputs[i].type);
+  }
+  CallbackContext *raw = ctx.get();
+  params->device.device_id = &raw->device_id;
+  params->device.worker_id = &raw->worker_id;
+  params->device.executed_on = &raw->executed_on;
+  params->timing.codelet_start_time = &raw->timing.codelet_start_time;
+  params->timing.codelet_end_time = &raw->timing.codelet_end_time;
+  params->timing.inference_start_time = &raw->timing.inference_start_time;
+  ctx->params = std::move(params);
+  ctx->outputs_handles = out_handles;
+
+  starpu_task *task = starpu_task_create();
+  if (task == nullptr) throw StarPUTaskCreationException("Failed to create StarPU task.");
+  const size_t num_inputs = in_handles.size(), num_buffers = num_inputs + out_handles.size();
+  task->nbuffers = static_cast<int>(num_buffers);
+  task->cl = codelet_.get_codelet();
+  task->synchronous = 0;
+  task->cl_arg = ctx->params.get();
+  task->cl_arg_size = sizeof(InferenceParams);
+  task->priority = std::max(starpu_sched_get_min_priority(), starpu_sched_get_max_priority() - master->request_id);
+  task->destroy = 1;
+  task->dyn_handles = static_cast<starpu_data_handle_t *>(std::malloc(num_buffers * sizeof(starpu_data_handle_t)));
+  task->dyn_modes =
+      static_cast<starpu_data_access_mode *>(std::malloc(num_buffers * sizeof(starpu_data_access_mode)));
+  for (size_t i = 0; i < num_inputs; ++i) {
+    task->dyn_handles[i] = in_handles[i];
+    task->dyn_modes[i] = STARPU_R;
+  }
+  for (size_t o = 0; o < out_handles.size(); ++o) {
+    task->dyn_handles[num_inputs + o] = out_handles[o];
+    task->dyn_modes[num_inputs + o] = STARPU_W;
+  }
+  if (master->fixed_worker_id.has_value()) {
+    const int wid = *master->fixed_worker_id;
+    if (wid < 0) {
+      starpu_task_destroy(task);
+      throw std::invalid_argument("Fixed worker ID must be non-negative");
+    }
+    if (wid >= static_cast<int>(starpu_worker_get_count())) {
+      starpu_task_destroy(task);
+      throw std::out_of_range("Fixed worker ID exceeds available workers");
+    }
+    task->workerid = static_cast<unsigned>(wid);
+    task->execute_on_a_specific_worker = 1;
+  }
+  task->callback_func = &TaskRunner::starpu_output_callback;
+  task->callback_arg = raw;
+  raw->timing.before_starpu_submitted_time = MonotonicClock::now();
+  const int ret = starpu_task_submit(task);
+  if (ret != 0) {
+    starpu_task_destroy(task);
+    throw StarPUTaskSubmissionException("[ERROR] StarPU task submission failed (code " + std::to_string(ret) + ")");
+  }
+  guard.armed = false;
+  (void)ctx.release();  // owned by the callback from here on
+  ++submitted_;
+}
+
+void TaskRunner::starpu_output_callback(void *arg) {
+  auto *ctx = static_cast<CallbackContext *>(arg);
+  if (ctx == nullptr) return;
+  ctx->timing.callback_start_time = MonotonicClock::now();
+  ctx->acquired.assign(ctx->outputs_handles.size(), false);
+  // acquire every STARPU_W handle on the host: this is what lands the D2H copy into the
+  // pinned output slot (inference_task.cpp:907-935)
+  bool ok = true;
+  for (size_t i = 0; i < ctx->outputs_handles.size(); ++i) {
+    if (starpu_data_acquire(ctx->outputs_handles[i], STARPU_R) != 0) {
+      ok = false;
+      break;
+    }
+    ctx->acquired[i] = true;
+  }
+  (void)ok;
+  finalize(ctx);
+}
+
+void TaskRunner::finalize(CallbackContext *ctx) {
+  TaskRunner *r = ctx->runner;
+  const bool all_acquired = std::all_of(ctx->acquired.begin(), ctx->acquired.end(), [](bool b) { return b; });
+  // the codelet stamps codelet_end only on success (starpu_setup.cpp:709-722)
+  const bool codelet_ok = ctx->timing.codelet_end_time != MonotonicClock::time_point{};
+  // bind_output_views_from_pool (inference_task.cpp:949-989): slot buffers viewed as [B, ...]
+  std::vector<HostTensor> aggregated;
+  const auto &bases = r->output_pool_->base_ptrs(ctx->output_slot);
+  for (size_t o = 0; o < bases.size(); ++o) {
+    HostTensor t;
+    t.data = bases[o];
+    t.type = r->output_pool_->tensor_type(o);
+    t.dims = r->model_.outputs[o].dims;
+    if (t.dims.empty()) t.dims.push_back(ctx->effective_batch);
+    else t.dims[0] = ctx->effective_batch;
+    aggregated.push_back(std::move(t));
+  }
+  ctx->timing.callback_end_time = MonotonicClock::now();
+  // propagate_completion_to_sub_jobs (result_dispatcher_component.cpp:678-739)
+  int64_t offset = 0;
+  for (const auto &job : ctx->jobs) {
+    if (!job) continue;
+    JobResult res;
+    res.request_id = job->request_id;
+    res.worker_id = ctx->worker_id;
+    res.device_id = ctx->device_id;
+    res.executed_on = ctx->executed_on;
+    res.batch_rows = ctx->effective_batch;
+    res.timing = ctx->timing;
+    res.timing.enqueued_time = job->timing.enqueued_time;
+    if (codelet_ok && all_acquired) {
+      auto slice = slice_outputs_for_sub_job(aggregated, offset, job->batch_size());
+      res.outputs = std::move(slice.outputs);
+      res.rows = slice.processed_length;
+      res.ok = true;
+      offset += slice.processed_length;
+    } else {
+      res.ok = false;
+      res.error = codelet_ok ? "Failed to acquire output data handle from StarPU." : "Inference failed";
+      offset += job->batch_size();
+    }
+    if (job->on_complete) job->on_complete(res);
+  }
+  for (size_t i = 0; i < ctx->outputs_handles.size(); ++i)
+    if (ctx->acquired[i]) starpu_data_release(ctx->outputs_handles[i]);
+  r->input_pool_->release(ctx->input_slot);
+  r->output_pool_->release(ctx->output_slot);
+  delete ctx;
+}
+
+}  // namespace starpu_server

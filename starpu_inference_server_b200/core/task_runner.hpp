@@ -1,0 +1,134 @@
+// Batch assembly (host gather), task submission and result slicing (host scatter): the
+// callers either side of the codelet.  Restates, without torch::Tensor:
+//   SlotManager::validate_batch_and_copy_inputs / copy_job_inputs_to_slot
+//       /root/reference/src/starpu_task_worker/slot_manager_component.cpp:392-515, 649-727
+//   resize_starpu_vector_handle   starpu_vector_resize_utils.hpp:19-89
+//   can_merge_jobs                batch_composition_policy.cpp:102-151
+//   aggregate_batch_metadata / resize_outputs_for_batch   batching_helpers.hpp:129-191
+//   InferenceTask::create_task / fill_task_buffers        src/core/inference_task.cpp:690-822
+//   starpu_output_callback -> acquire -> finalize          inference_task.cpp:850-1037
+//   propagate_completion_to_sub_jobs / slice_outputs_for_sub_job
+//       result_dispatcher_component.cpp:678-739, batching_helpers.hpp:74-127
+#pragma once
+
+#include <algorithm>
+#include <atomic>
+#include <functional>
+#include <memory>
+#include <optional>
+#include <string>
+#include <vector>
+
+#include "inference_codelet.hpp"
+#include "slot_pools.hpp"
+
+namespace starpu_server {
+
+// A borrowed, contiguous, row-major host array (what at::Tensor is to the reference here).
+struct HostTensor {
+  std::byte *data = nullptr;
+  std::vector<int64_t> dims;
+  ScalarType type = ScalarType::Float32;
+  [[nodiscard]] auto numel() const -> size_t {
+    size_t n = 1;
+    for (int64_t d : dims) n *= static_cast<size_t>(d);
+    return dims.empty() ? 0 : n;
+  }
+  [[nodiscard]] auto nbytes() const -> size_t { return numel() * element_size(type); }
+  [[nodiscard]] auto defined() const -> bool { return data != nullptr; }
+};
+
+struct JobTiming {  // detail::TimingInfo subset (inference_job.hpp)
+  MonotonicClock::time_point enqueued_time{}, before_starpu_submitted_time{}, codelet_start_time{},
+      inference_start_time{}, codelet_end_time{}, callback_start_time{}, callback_end_time{};
+};
+
+struct JobResult {
+  int request_id = 0;
+  bool ok = false;
+  std::string error;                // failure_info message
+  std::vector<HostTensor> outputs;  // views of rows [off, off+b) of the output slot; valid inside on_complete
+  int64_t rows = 0;                 // processed_length
+  int worker_id = -1, device_id = -1;
+  DeviceType executed_on = DeviceType::Unknown;
+  JobTiming timing;
+  int64_t batch_rows = 0;  // effective batch size of the task this request rode in
+};
+
+struct InferenceJob {
+  int request_id = 0;
+  std::vector<HostTensor> inputs;  // inputs[i].dims[0] = this request's batch
+  std::optional<int> fixed_worker_id;
+  std::function<void(const JobResult &)> on_complete;
+  JobTiming timing;
+  [[nodiscard]] auto batch_size() const -> int64_t {
+    return inputs.empty() || inputs[0].dims.empty() ? 1 : std::max<int64_t>(1, inputs[0].dims[0]);
+  }
+};
+
+// batch_composition_policy.cpp:102-151
+auto can_merge_jobs(const InferenceJob *lhs, const InferenceJob *rhs) -> bool;
+
+struct VectorResizeSpec {
+  std::size_t element_count;
+  std::size_t byte_count;
+};
+void resize_starpu_vector_interface(starpu_vector_interface *vi, VectorResizeSpec spec, bool is_input_handle);
+void resize_starpu_vector_handle(starpu_data_handle_t handle, VectorResizeSpec spec, bool is_input_handle);
+
+// Host gather of a master job + pending sub-jobs into a slot; returns bytes copied and
+// resizes every handle to nx = sum(numel).
+auto copy_job_inputs_to_slot(const InferenceJob *job, const std::vector<const InferenceJob *> &pending_jobs,
+                             const std::vector<starpu_data_handle_t> &handles,
+                             const std::vector<std::byte *> &base_ptrs,
+                             const std::vector<HostBufferInfo> &buffer_infos) -> std::size_t;
+
+struct SubJobSliceResult {
+  std::vector<HostTensor> outputs;
+  int64_t processed_length = 0;
+};
+// batching_helpers.hpp:74-127 (zero-copy views into the aggregated outputs)
+auto slice_outputs_for_sub_job(const std::vector<HostTensor> &aggregated_outputs, int64_t offset,
+                               int64_t batch_size) -> SubJobSliceResult;
+
+struct ModelConfig {  // the slice of models/*.yml the path needs (config_loader.cpp)
+  std::string name;
+  std::vector<TensorConfig> inputs, outputs;
+  int max_batch_size = 1;
+  int pool_size = 12;  // models/bert.yml: pool_size
+};
+
+// StarPUSetup + StarPUTaskRunner rolled into what the path needs: owns the codelet and the
+// slot pools, knows the per-device replicas, submits one StarPU task per batch.
+class TaskRunner {
+ public:
+  // models_gpu[i] serves device_ids[i] (build_gpu_replica_assignments, inference_runner.cpp:128-183)
+  TaskRunner(ModelConfig model, std::vector<int> device_ids, std::vector<DeviceModel *> models_gpu);
+  ~TaskRunner();
+
+  // One task from jobs[0] (master) + jobs[1..] (aggregated sub-jobs, in order).  Blocks while
+  // no slot is free.  Throws the reference's exception types on contract violations.
+  void submit_batch(const std::vector<std::shared_ptr<InferenceJob>> &jobs);
+  void wait_for_all();
+
+  [[nodiscard]] auto codelet() -> starpu_codelet * { return codelet_.get_codelet(); }
+  [[nodiscard]] auto input_pool() -> InputSlotPool & { return *input_pool_; }
+  [[nodiscard]] auto output_pool() -> OutputSlotPool & { return *output_pool_; }
+  [[nodiscard]] auto model() const -> const ModelConfig & { return model_; }
+  [[nodiscard]] auto tasks_submitted() const -> long { return submitted_.load(); }
+
+ private:
+  struct CallbackContext;
+  static void starpu_output_callback(void *arg);
+  static void finalize(CallbackContext *ctx);
+
+  ModelConfig model_;
+  std::vector<int> device_ids_;
+  std::vector<DeviceModel *> models_gpu_;
+  InferenceCodelet codelet_;
+  std::unique_ptr<InputSlotPool> input_pool_;
+  std::unique_ptr<OutputSlotPool> output_pool_;
+  std::atomic<long> submitted_{0};
+};
+
+}  // namespace starpu_server

@@ -404,6 +404,11 @@ extern "C" spu_status spu_bert_forward_profiled(spu_replica *r, int32_t ws_idx, 
   return st;
 }
 
+extern "C" uint64_t spu_bert_output_bytes(const spu_replica *r, int32_t batch, int32_t seq) {
+  if (r == nullptr || batch <= 0 || seq <= 0) return 0;
+  return static_cast<uint64_t>(batch) * static_cast<uint64_t>(seq) * static_cast<uint64_t>(r->desc.hidden) * 4u;
+}
+
 extern "C" int32_t spu_bert_forward_launch_count(const spu_replica *r) {
   return r == nullptr ? 0 : 1 + 7 * r->desc.layers;
 }

@@ -1,0 +1,182 @@
+"""CPU: host-side contract of the codelet wrapper (libspu_host.so) checked against the
+reference's own known answers and the C oracle.  No CUDA call is made here.
+
+Reference tests mirrored:
+  codelet field values           tests/unit/core/unit_starpu_setup.cpp:4065-4074
+  buffer_byte_size               src/core/starpu_setup.cpp:515-542 (+ unit tests around :4180)
+  select_gpu_module              tests/unit/core/unit_starpu_setup.cpp:4106-4183
+  gather bytes + nx              tests/unit/starpu/unit_starpu_task_runner_submission_and_slots.cpp:607-666
+  scatter slices                 tests/unit/starpu/unit_starpu_task_runner_batching_and_internal.cpp:1514-1606
+  can_merge_jobs                 src/starpu_task_worker/batch_composition_policy.cpp:102-151
+"""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def host(built_libs):
+    from starpu_inference_server_b200 import hostapi
+
+    hostapi.lib()
+    return hostapi
+
+
+def test_host_header_symbols_all_exported(host):
+    src = open(os.path.join(ROOT, "include", "spu_host.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    declared = sorted(set(re.findall(r"\b(spu_(?:server|host)_[a-z0-9_]+)\s*\(", src)))
+    assert sorted(host.SYMBOLS) == declared
+    for name in declared:
+        assert hasattr(host.lib(), name), name
+
+
+def test_codelet_fields_are_initialized(host):
+    out = (C.c_int64 * 7)()
+    host.lib().spu_host_codelet_fields(out)
+    nbuffers, ctype, max_par, has_cpu, has_cuda, cuda_flags, where = list(out)
+    assert nbuffers == -1          # STARPU_VARIABLE_NBUFFERS
+    assert ctype == 2              # STARPU_FORKJOIN
+    assert max_par == 2**31 - 1    # INT_MAX
+    assert has_cuda == 1
+    assert cuda_flags == 1         # STARPU_CUDA_ASYNC
+    # deliberate difference from the reference (EXPECT_NE(cpu_funcs[0], nullptr)): the new
+    # codelet has no CPU implementation to fall back to
+    assert has_cpu == 0
+    assert where == (1 << 3)       # STARPU_CUDA
+
+
+@pytest.mark.parametrize("iface,nx,es", [(2, 4, 8), (2, 0, 4), (2, 4096 * 768, 4), (5, 123, 12), (5, 0, 0)])
+def test_buffer_byte_size_matches_oracle(host, oracle_gs, iface, nx, es):
+    got, want = C.c_uint64(), C.c_uint64()
+    assert host.lib().spu_host_buffer_byte_size(iface, nx, es, 0, C.byref(got)) == 0
+    oracle_gs.oracle_buffer_byte_size.argtypes = [C.c_int, C.c_uint64, C.c_uint64, C.POINTER(C.c_uint64)]
+    assert oracle_gs.oracle_buffer_byte_size(iface, nx, es, C.byref(want)) == 0
+    assert got.value == want.value
+
+
+def test_buffer_byte_size_errors(host):
+    out = C.c_uint64()
+    assert host.lib().spu_host_buffer_byte_size(2, 1, 1, 1, C.byref(out)) == 1
+    assert "StarPU buffer is null" in host.last_error()
+    assert host.lib().spu_host_buffer_byte_size(0, 1, 1, 0, C.byref(out)) == 1  # matrix interface
+    assert "Unsupported StarPU buffer interface id 0" in host.last_error()
+
+
+def _select(host, device_ids, worker_ids, n_models, worker_id, device_id):
+    d = (C.c_int32 * max(1, len(device_ids)))(*device_ids)
+    w = (C.c_int32 * max(1, len(worker_ids)))(*worker_ids)
+    return host.lib().spu_host_select_replica(d, len(device_ids), w, len(worker_ids), n_models, worker_id, device_id)
+
+
+def test_select_gpu_module_lookup_order(host):
+    # device id used as index when no table is given
+    assert _select(host, [], [], 3, 0, 2) == 2
+    # device_ids table: replica i serves device_ids[i]
+    assert _select(host, [4, 7], [], 2, 0, 7) == 1
+    assert _select(host, [4, 7], [], 2, 0, 4) == 0
+    # per-worker table wins over the device table
+    assert _select(host, [0], [10, 11, 12], 3, 11, 0) == 1
+
+
+def test_select_gpu_module_throws_when_replica_missing(host):
+    assert _select(host, [], [], 1, 0, 3) == -1
+    assert "No GPU model replica available for device 3" in host.last_error()
+    assert _select(host, [4], [], 1, 0, 5) == -1
+    assert _select(host, [], [10, 11], 2, 12, 0) == -1
+    assert "No GPU model replica available for worker 12 on device 0" in host.last_error()
+    assert _select(host, [], [], 2, 0, -1) == -1
+
+
+def _gather(host, arrays, elemsize, capacity):
+    n = len(arrays)
+    srcs = (C.c_void_p * max(1, n))(*[a.ctypes.data for a in arrays])
+    nbytes = (C.c_uint64 * max(1, n))(*[a.nbytes for a in arrays])
+    slot = np.full(capacity, 0xEE, np.uint8)
+    nx, total = C.c_uint64(), C.c_uint64()
+    rc = host.lib().spu_host_gather_to_slot(srcs, nbytes, n, elemsize, slot.ctypes.data, capacity, C.byref(nx),
+                                            C.byref(total))
+    return rc, slot, nx.value, total.value
+
+
+def test_gather_known_answer(host):
+    """jobs {1,2} + {3,4} -> slot 1,2,3,4 and nx == 4 (reference test :607-666)."""
+    a, b = np.array([1, 2], np.float32), np.array([3, 4], np.float32)
+    rc, slot, nx, total = _gather(host, [a, b], 4, 64)
+    assert rc == 0 and nx == 4 and total == 16
+    assert slot[:16].view(np.float32).tolist() == [1, 2, 3, 4]
+    assert (slot[16:] == 0xEE).all()
+
+
+def test_gather_matches_oracle_bytes(host, oracle_gs):
+    rng = np.random.default_rng(5)
+    arrays = [rng.integers(0, 30522, size=(b, 128), dtype=np.int64) for b in (1, 3, 1, 2, 1)]
+    cap = 32 * 128 * 8
+    rc, slot, nx, total = _gather(host, arrays, 8, cap)
+    assert rc == 0
+    n = len(arrays)
+    srcs = (C.c_void_p * n)(*[a.ctypes.data for a in arrays])
+    nbytes = (C.c_size_t * n)(*[a.nbytes for a in arrays])
+    numel = (C.c_size_t * n)(*[a.size for a in arrays])
+    want = np.full(cap, 0xEE, np.uint8)
+    onx, obytes = C.c_size_t(), C.c_size_t()
+    oracle_gs.oracle_gather_concat.argtypes = [C.POINTER(C.c_void_p), C.POINTER(C.c_size_t), C.POINTER(C.c_size_t),
+                                               C.c_size_t, C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t),
+                                               C.POINTER(C.c_size_t)]
+    assert oracle_gs.oracle_gather_concat(srcs, nbytes, numel, n, want.ctypes.data, cap, C.byref(onx),
+                                          C.byref(obytes)) == 0
+    assert (slot == want).all() and nx == onx.value == 8 * 128 and total == obytes.value
+
+
+def test_gather_capacity_exception(host):
+    a = np.zeros(8, np.float32)
+    rc, _, _, _ = _gather(host, [a, a, a], 4, 64)
+    assert rc == 1 and "exceeds allocated slot buffer capacity" in host.last_error()
+
+
+@pytest.mark.parametrize("rows,off,bs", [(3, 0, 1), (3, 1, 2), (3, 2, 5), (3, 3, 1), (32, 7, 0), (1, 0, 1), (0, 0, 1)])
+def test_slice_rows_matches_oracle(host, oracle_gs, rows, off, bs):
+    row_bytes = 4000
+    o, ln = C.c_uint64(), C.c_uint64()
+    processed = host.lib().spu_host_slice_rows(rows, row_bytes, off, bs, C.byref(o), C.byref(ln))
+    agg = np.arange(max(rows, 1) * row_bytes, dtype=np.uint8)
+    dst = np.zeros(max(rows, 1) * row_bytes + 8, np.uint8)
+    got_rows = C.c_int64()
+    oracle_gs.oracle_scatter_slice.argtypes = [C.c_void_p, C.c_size_t, C.c_size_t, C.c_int64, C.c_int64, C.c_void_p,
+                                               C.POINTER(C.c_int64)]
+    assert oracle_gs.oracle_scatter_slice(agg.ctypes.data, rows, rows * row_bytes, off, bs, dst.ctypes.data,
+                                          C.byref(got_rows)) == 0
+    assert ln.value == got_rows.value * row_bytes
+    if got_rows.value > 0:
+        assert processed == got_rows.value and o.value == off * row_bytes
+        assert (dst[:ln.value] == agg[o.value:o.value + ln.value]).all()
+    else:
+        assert processed == max(1, bs)  # reference: processed_length stays slice_size when nothing is cut
+
+
+def test_slice_known_answer(host):
+    """batch sizes 1 + 2 over 3 rows -> rows [0,1) and [1,3) (reference test :1514-1606)."""
+    o, ln = C.c_uint64(), C.c_uint64()
+    assert host.lib().spu_host_slice_rows(3, 8, 0, 1, C.byref(o), C.byref(ln)) == 1 and (o.value, ln.value) == (0, 8)
+    assert host.lib().spu_host_slice_rows(3, 8, 1, 2, C.byref(o), C.byref(ln)) == 2 and (o.value, ln.value) == (8, 16)
+
+
+def _merge(host, da, ta, db, tb):
+    a, b = (C.c_int64 * len(da))(*da), (C.c_int64 * len(db))(*db)
+    return host.lib().spu_host_can_merge(a, len(da), ta, b, len(db), tb)
+
+
+def test_can_merge_jobs(host):
+    I64, F32 = 3, 0
+    assert _merge(host, [1, 128], I64, [1, 128], I64) == 1
+    assert _merge(host, [1, 128], I64, [4, 128], I64) == 1    # batch dim is free
+    assert _merge(host, [1, 128], I64, [1, 64], I64) == 0     # trailing dims must match
+    assert _merge(host, [1, 128], I64, [1, 128], F32) == 0    # dtype must match
+    assert _merge(host, [1, 3, 224, 224], F32, [2, 3, 224, 224], F32) == 1
+    assert _merge(host, [1, 128], I64, [1, 128, 1], I64) == 0  # rank must match
+    assert _merge(host, [5], F32, [9], F32) == 1              # rank 1: nothing but dim 0
