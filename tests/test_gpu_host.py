@@ -1,0 +1,156 @@
+"""GPU: the codelet wrapper and the task path around it (libspu_host.so), through the same
+entry a StarPU CUDA worker uses: codelet.cuda_funcs[0](buffers, cl_arg).
+
+Reference tests mirrored:
+  cuda_func x+1.5 on device buffers + side effects   tests/unit/core/unit_starpu_setup.cpp:2332-2433
+  missing replica -> StarPUCodeletException          tests/unit/core/unit_starpu_setup.cpp:4106-4183
+  cpu/cuda_func x+1 on {1,2,3} -> {2,3,4}            tests/integration/starpu/integration_starpu_setup.cpp:42-60
+  x*2 through the runner                             tests/integration/core/integration_inference_runner.cpp:72-120
+  batched sub-jobs sliced back in order              tests/unit/starpu/unit_starpu_task_runner_batching_and_internal.cpp:1514-1606
+"""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+torch = pytest.importorskip("torch")
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def host(built_libs):
+    from starpu_inference_server_b200 import capi, hostapi
+
+    assert torch.cuda.is_available() and capi.lib().spu_device_is_sm100(0) == 1
+    hostapi.lib()
+    return hostapi
+
+
+@pytest.mark.parametrize("vector_iface", [0, 1])
+def test_cuda_func_copies_results_to_device_buffer(host, vector_iface):
+    x = torch.tensor([1.0, 2.0, 3.0], device="cuda")
+    y = torch.zeros(3, device="cuda")
+    s = torch.cuda.Stream()
+    rec = (C.c_int64 * 6)()
+    rc = host.lib().spu_host_call_cuda_func_affine(x.data_ptr(), y.data_ptr(), 3, 1.0, 1.5, 0, 77, s.cuda_stream, 1,
+                                                   vector_iface, rec)
+    assert rc == 0, host.last_error()
+    s.synchronize()
+    assert y.cpu().tolist() == [2.5, 3.5, 4.5]
+    device_id, worker_id, executed_on, start_set, end_set, gauge = list(rec)
+    assert (device_id, worker_id, executed_on) == (0, 77, 1)  # DeviceType::CUDA
+    assert start_set == 1 and end_set == 1 and gauge == 0
+
+
+def test_cuda_func_wraps_missing_replica(host):
+    x = torch.ones(3, device="cuda")
+    y = torch.zeros(3, device="cuda")
+    rec = (C.c_int64 * 6)()
+    rc = host.lib().spu_host_call_cuda_func_affine(x.data_ptr(), y.data_ptr(), 3, 1.0, 1.0, 0, 5,
+                                                   torch.cuda.current_stream().cuda_stream, 0, 0, rec)
+    assert rc == 1 and "No GPU model replica available for device 0" in host.last_error()
+    torch.cuda.synchronize()
+    assert y.cpu().tolist() == [0, 0, 0]
+
+
+def _affine_server(host, scale, shift, **kw):
+    return host.Server(inputs=[("x", "f32", [1, 3])], outputs=[("y", "f32", [1, 3])], model_kind=host.MODEL_AFFINE,
+                       affine=(scale, shift), **kw)
+
+
+def test_task_path_x_plus_one(host):
+    with _affine_server(host, 1.0, 1.0, max_batch_size=4, pool_size=2) as srv:
+        x = np.array([[1, 2, 3]], np.float32)
+        y = np.zeros((1, 3), np.float32)
+        (r,) = srv.wait(srv.submit_batch([(7, 1, [x], [y])]))
+        assert r.ok == 1 and r.request_id == 7 and r.rows == 1 and r.batch_rows == 1
+        assert y.tolist() == [[2, 3, 4]]
+        assert r.executed_on == 1 and r.device_id == 0 and r.worker_id >= 0
+        assert r.codelet_ms > 0 and r.task_ms > 0 and r.latency_ms >= r.task_ms
+        st = srv.stats()
+        assert st["tasks"] == 1 and st["completed"] == 1 and st["free_in"] == 2 and st["free_out"] == 2
+
+
+def test_batched_sub_jobs_are_gathered_and_sliced_in_order(host):
+    """master b=1 + sub-jobs b=2, b=1: rows are concatenated in request order and each
+    request gets exactly its own rows back (x*2, the reference's integration toy)."""
+    with _affine_server(host, 2.0, 0.0, max_batch_size=8, pool_size=3, nworker_per_cuda=2) as srv:
+        rng = np.random.default_rng(0)
+        xs = [rng.standard_normal((b, 3)).astype(np.float32) for b in (1, 2, 1)]
+        ys = [np.zeros_like(x) for x in xs]
+        res = srv.wait(srv.submit_batch([(10 + i, x.shape[0], [x], [y]) for i, (x, y) in enumerate(zip(xs, ys))]))
+        assert [r.request_id for r in res] == [10, 11, 12]
+        assert [r.rows for r in res] == [1, 2, 1] and all(r.batch_rows == 4 and r.ok == 1 for r in res)
+        for x, y in zip(xs, ys):
+            assert (y == x * 2).all()
+
+
+def test_batch_over_capacity_is_rejected(host):
+    with _affine_server(host, 1.0, 0.0, max_batch_size=2, pool_size=1) as srv:
+        x = np.zeros((3, 3), np.float32)
+        with pytest.raises(host.HostError, match="exceeds input pool capacity"):
+            srv.submit_batch([(0, 3, [x], [np.zeros_like(x)])])
+        assert srv.stats()["free_in"] == 1  # the slot went back
+
+
+def test_dynamic_batching_and_many_workers(host):
+    with _affine_server(host, 1.0, 0.5, max_batch_size=8, pool_size=4, nworker_per_cuda=4, cuda_pipeline=4,
+                        batch_coalesce_timeout_ms=2) as srv:
+        n = 200
+        xs = [np.full((1, 3), float(i), np.float32) for i in range(n)]
+        ys = [np.zeros((1, 3), np.float32) for _ in range(n)]
+        tickets = [srv.enqueue(i, 1, [xs[i]], [ys[i]]) for i in range(n)]
+        workers, sizes = set(), []
+        for i, t in enumerate(tickets):
+            (r,) = srv.wait(t)
+            assert r.ok == 1 and r.request_id == i
+            workers.add(r.worker_id)
+            sizes.append(r.batch_rows)
+            assert (ys[i] == i + 0.5).all()
+        st = srv.stats()
+        assert st["completed"] == n and st["tasks"] <= n and st["workers"] == 4
+        assert max(sizes) > 1 and max(sizes) <= 8  # the collector did coalesce
+        assert st["free_in"] == 4 and st["free_out"] == 4 and st["codelet_failures"] == 0
+
+
+@pytest.fixture(scope="module")
+def bert_tiny(host):
+    from oracle import bert_oracle as bo
+    from starpu_inference_server_b200.bert import BertReplica
+
+    spec = bo.BERT_TINY
+    w = bo.make_weights(spec, 0)
+    rep = BertReplica(w, max_batch=8, max_seq=32, n_workspaces=2)
+    yield bo, spec, w, rep
+    rep.close()
+
+
+def test_bert_through_the_task_path(host, bert_tiny):
+    """gRPC-shaped requests ([1,S] ids+mask each) -> host gather -> StarPU task -> codelet ->
+    C-ABI kernels -> D2H -> slices.  Must equal the direct C-ABI forward bit for bit and the
+    fp32 oracle within the bf16 tolerance."""
+    bo, spec, w, rep = bert_tiny
+    S, H = 32, spec.hidden
+    ids, mask = bo.make_inputs(spec, 5, S, seed=3, min_len=4)
+    ref = bo.bert_forward(w, spec, ids, mask)
+    direct = torch.empty(5, S, H, device="cuda")
+    rep.forward_async(torch.from_numpy(ids).cuda(), torch.from_numpy(mask).cuda(), direct, ws=1)
+    torch.cuda.synchronize()
+    with host.Server(inputs=[("input_ids", "i64", [1, S]), ("attention_mask", "i64", [1, S])],
+                     outputs=[("output0", "f32", [1, S, H])], replicas=[rep], model_kind=host.MODEL_BERT,
+                     max_batch_size=8, pool_size=2, n_workspaces=2) as srv:
+        outs = [np.zeros((1, S, H), np.float32) for _ in range(5)]
+        reqs = [(i, 1, [ids[i:i + 1].copy(), mask[i:i + 1].copy()], [outs[i]]) for i in range(5)]
+        res = srv.wait(srv.submit_batch(reqs))
+        assert all(r.ok == 1 and r.batch_rows == 5 for r in res)
+        got = np.concatenate(outs, 0)
+        assert (got == direct.cpu().numpy()).all()
+        assert np.abs(got - ref).max() / np.abs(ref).max() < 2e-2
+        # wrong sequence length for this server's config: the codelet's size check fires and
+        # the failure reaches the request as ok == 0 (gRPC INTERNAL in the reference)
+    with host.Server(inputs=[("input_ids", "i64", [1, S]), ("attention_mask", "i64", [1, S])],
+                     outputs=[("output0", "f32", [1, S, H + 8])], replicas=[rep], model_kind=host.MODEL_BERT,
+                     max_batch_size=8, pool_size=2, n_workspaces=2) as srv:
+        out = np.zeros((1, S, H + 8), np.float32)
+        (r,) = srv.wait(srv.submit_batch([(0, 1, [ids[:1].copy(), mask[:1].copy()], [out])]))
+        assert r.ok == 0 and srv.stats()["codelet_failures"] == 1
