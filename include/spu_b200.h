@@ -121,6 +121,16 @@ spu_status spu_bert_forward_profiled(spu_replica *r, int32_t ws_idx,
                                      int32_t batch, int32_t seq, float *out,
                                      void *stream, float *stage_ms);
 
+/* Measurement hook: device time (ms per forward) of ONLY the kernel classes whose bit
+ * (1u << SPU_STAGE_*) is set in stage_mask, run as `reps` forwards' worth of launches back
+ * to back inside one CUDA graph (no host gaps, programmatic dependent launch in effect) and
+ * bracketed by two CUDA events on `stream`.  Synchronises the stream.  stage_mask = ~0u
+ * times the whole forward. */
+spu_status spu_bert_stage_chain_ms(spu_replica *r, int32_t ws_idx, const int64_t *ids,
+                                   const int64_t *mask, int32_t batch, int32_t seq, float *out,
+                                   uint32_t stage_mask, int32_t reps, void *stream,
+                                   float *ms_per_forward);
+
 /* Bytes of output0 for (batch, seq): batch*seq*hidden*4 (0 for a null / non-BERT replica).
  * The codelet checks the STARPU_W buffer against it, like the reference's
  * TORCH_CHECK(buffer.size() == out.nbytes()) (src/core/starpu_setup.cpp:840-842). */

@@ -112,6 +112,16 @@ class BertReplica:
                                                         capi.ptr(out), capi.stream_ptr(stream), ms))
         return dict(zip(capi.STAGE_NAMES, list(ms)))
 
+    def stage_chain_ms(self, ids, mask, out, stages=None, reps=5, ws: int = 0, stream=None) -> float:
+        """Device ms per forward of only the named kernel classes (None = all), launched back to
+        back in one CUDA graph and bracketed by CUDA events (measurement hook)."""
+        b, s = ids.shape
+        m = 0xFFFFFFFF if stages is None else sum(1 << capi.STAGE_NAMES.index(n) for n in stages)
+        ms = C.c_float()
+        capi.check(capi.lib().spu_bert_stage_chain_ms(self._h, ws, capi.ptr(ids), capi.ptr(mask), b, s, capi.ptr(out),
+                                                      m, reps, capi.stream_ptr(stream), C.byref(ms)))
+        return ms.value
+
     def capture(self, ids, mask, out, ws: int = 0, stream=None):
         b, s = ids.shape
         capi.check(capi.lib().spu_bert_forward_capture(self._h, ws, capi.ptr(ids), capi.ptr(mask), b, s,

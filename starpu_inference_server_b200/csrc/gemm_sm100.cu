@@ -164,43 +164,72 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
   tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
 
-  // Everything above overlaps the previous kernel's tail under programmatic dependent
-  // launch; global memory written by that kernel is only touched below this line.
-  pdl_wait_prior_grid();
+  // Programmatic dependent launch: everything above, plus the producer's first WEIGHT-tile
+  // loads below, overlaps the previous kernel's tail; memory written by that kernel (the
+  // activations, the residual) is only touched after griddepcontrol.wait.  Dependents are
+  // released at once: their CTAs start their own prologue as soon as an SM frees up.
+  pdl_launch_dependents();
 
   if (warp_idx == 0) {
     // ===================== TMA producer (both CTAs of a pair) =====================
     if (lane == 0) {
+      auto issue_expect = [&](int stage) {
+        if constexpr (CG == 2) {
+          if (cta_rank == 0) mbar_arrive_expect_tx(&full_bar[stage], 2 * kStageBytes);
+        } else {
+          mbar_arrive_expect_tx(&full_bar[stage], kStageBytes);
+        }
+      };
+      auto load_a = [&](int stage, int kb, int a_row) {
+        uint8_t *sa = smem + stage * kStageBytes;
+        if constexpr (CG == 2) tma_load_2d_pair(sa, &tmap_a, &full_bar[stage], kb * kElemsPerKBlock, a_row);
+        else tma_load_2d(sa, &tmap_a, &full_bar[stage], kb * kElemsPerKBlock, a_row);
+      };
+      auto load_b = [&](int stage, int kb, int b_row) {
+        uint8_t *sb = smem + stage * kStageBytes + kABytes;
+        if constexpr (CG == 2) tma_load_2d_pair(sb, &tmap_b, &full_bar[stage], kb * kElemsPerKBlock, b_row);
+        else tma_load_2d(sb, &tmap_b, &full_bar[stage], kb * kElemsPerKBlock, b_row);
+      };
+      // weights of the first tile's first stages: independent of the previous kernel
+      const int n_pre = unit < num_tiles ? (num_k_blocks < kStages ? num_k_blocks : kStages) : 0;
+      {
+        const int n_blk = unit % n_blocks;
+        const int b_row = n_blk * BLOCK_N + static_cast<int>(cta_rank) * Cfg::kBRows;
+        for (int kb = 0; kb < n_pre; ++kb) {
+          issue_expect(kb);
+          load_b(kb, kb, b_row);
+        }
+      }
+      pdl_wait_prior_grid();
       int stage = 0;
       uint32_t phase = 0;
+      bool first = true;
       for (int tile = unit; tile < num_tiles; tile += num_units) {
         const int m_blk = tile / n_blocks;
         const int n_blk = tile % n_blocks;
         const int a_row = m_blk * kTileM + static_cast<int>(cta_rank) * kRowsPerCta;
         const int b_row = n_blk * BLOCK_N + static_cast<int>(cta_rank) * Cfg::kBRows;
         for (int kb = 0; kb < num_k_blocks; ++kb) {
-          mbar_wait(&empty_bar[stage], phase ^ 1u);
-          uint8_t *sa = smem + stage * kStageBytes;
-          uint8_t *sb = sa + kABytes;
-          if constexpr (CG == 2) {
-            if (cta_rank == 0) mbar_arrive_expect_tx(&full_bar[stage], 2 * kStageBytes);
-            tma_load_2d_pair(sa, &tmap_a, &full_bar[stage], kb * kElemsPerKBlock, a_row);
-            tma_load_2d_pair(sb, &tmap_b, &full_bar[stage], kb * kElemsPerKBlock, b_row);
+          if (first && kb < n_pre) {
+            load_a(stage, kb, a_row);  // barrier armed and B already in flight
           } else {
-            mbar_arrive_expect_tx(&full_bar[stage], kStageBytes);
-            tma_load_2d(sa, &tmap_a, &full_bar[stage], kb * kElemsPerKBlock, a_row);
-            tma_load_2d(sb, &tmap_b, &full_bar[stage], kb * kElemsPerKBlock, b_row);
+            mbar_wait(&empty_bar[stage], phase ^ 1u);
+            issue_expect(stage);
+            load_a(stage, kb, a_row);
+            load_b(stage, kb, b_row);
           }
           if (++stage == kStages) {
             stage = 0;
             phase ^= 1u;
           }
         }
+        first = false;
       }
     }
     __syncwarp();  // reconverge before the CTA-wide barrier below
   } else if (warp_idx == 1) {
     // ===================== MMA issuer (leader CTA) =====================
+    pdl_wait_prior_grid();
     if (lane == 0 && cta_rank == 0) {
       int stage = 0;
       uint32_t phase = 0;
@@ -246,6 +275,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
     __syncwarp();
   } else if (warp_idx >= kEpiWarp0) {
     // ===================== epilogue (all CTAs) =====================
+    pdl_wait_prior_grid();
     const int e = warp_idx - kEpiWarp0;
     const int q = warp_idx & 3;  // TMEM lane quarter this warp may read
     const int half = e >> 2;     // which half of the tile's columns
@@ -383,7 +413,6 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
 
   tcgen05_fence_before();
   if constexpr (CG == 2) cluster_sync_all(); else __syncthreads();
-  pdl_launch_dependents();
   if (warp_idx == 2) {
     tcgen05_fence_after();
     if constexpr (CG == 2) tmem_dealloc_pair(tmem_base, Cfg::kTmemCols);
@@ -556,7 +585,11 @@ GemmConfig choose_config(int M, int N, int K, int esize) {
       const double epi = bn * 6.0;
       const double tile = mma > feed ? (mma > epi ? mma : epi) : (feed > epi ? feed : epi);
       // a pair that owns fewer than 129 valid rows wastes its second CTA
-      const double cost = rounds * tile + epi + 1500.0 + (cg == 2 && M <= kRowsPerCta ? 1.0 : 0.0);
+      // measured in situ (profiles/r02_tile_sweep_in_situ.md): at every BERT/ViT problem size a
+      // CTA pair is 5-15 % slower than two independent CTAs with the same BLOCK_N (cluster
+      // launch + cross-CTA barrier latency outweigh the saved operand traffic), so the
+      // automatic choice stays on cta_group::1; pairs remain available when forced.
+      const double cost = rounds * tile + epi + 1500.0 + (cg == 2 ? 1e12 : 0.0);
       if (cost < best_cost) {
         best_cost = cost;
         best = GemmConfig{cg, bn};

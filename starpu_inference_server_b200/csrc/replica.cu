@@ -212,13 +212,14 @@ spu_status build(spu_replica *r, const float *const *t) {
   do {                                                \
     if (trail != nullptr) SPU_TRY(trail->mark((id), stream)); \
   } while (0)
+#define SPU_ON(id) ((stage_mask >> (id)) & 1u)
 
 spu_status enqueue_forward(spu_replica *r, Workspace &ws, const int64_t *ids, const int64_t *mask,
                            int batch, int seq, float *out, cudaStream_t stream,
-                           StageTrail *trail = nullptr) {
+                           StageTrail *trail = nullptr, uint32_t stage_mask = 0xffffffffu) {
   const spu_bert_desc &d = r->desc;
   const int M = batch * seq;
-  SPU_TRY(bert_embed_launch(ids, mask, r->word, r->pos, r->type0, r->emb_g, r->emb_b, d.ln_eps,
+  if (SPU_ON(SPU_STAGE_EMBED)) SPU_TRY(bert_embed_launch(ids, mask, r->word, r->pos, r->type0, r->emb_g, r->emb_b, d.ln_eps,
                             d.vocab, ws.x_f32, ws.x_bf16, ws.mask_bias, batch, seq, d.hidden,
                             stream));
   SPU_MARK(SPU_STAGE_EMBED);
@@ -230,30 +231,30 @@ spu_status enqueue_forward(spu_replica *r, Workspace &ws, const int64_t *ids, co
     e.acc_scale = 1.f;
     e.bias = w.b_qkv;
     e.out = ws.qkv;
-    SPU_TRY(gemm_launch(p.qkv, M, e, stream));
+    if (SPU_ON(SPU_STAGE_GEMM_QKV)) SPU_TRY(gemm_launch(p.qkv, M, e, stream));
     SPU_MARK(SPU_STAGE_GEMM_QKV);
-    SPU_TRY(attention_launch(ws.qkv, ws.mask_bias, ws.ctx, batch, seq, d.heads, stream));
+    if (SPU_ON(SPU_STAGE_ATTENTION)) SPU_TRY(attention_launch(ws.qkv, ws.mask_bias, ws.ctx, batch, seq, d.heads, stream));
     SPU_MARK(SPU_STAGE_ATTENTION);
     e.bias = w.b_o;
     e.resid = ws.x_f32;
     e.out = ws.x_f32;  // in place: each element is read then written by the same thread
-    SPU_TRY(gemm_launch(p.attn_out, M, e, stream));
+    if (SPU_ON(SPU_STAGE_GEMM_OUT)) SPU_TRY(gemm_launch(p.attn_out, M, e, stream));
     SPU_MARK(SPU_STAGE_GEMM_OUT);
-    SPU_TRY(layernorm_launch(ws.x_f32, w.ln1_g, w.ln1_b, d.ln_eps, ws.x_f32, ws.x_bf16, M,
+    if (SPU_ON(SPU_STAGE_LN1)) SPU_TRY(layernorm_launch(ws.x_f32, w.ln1_g, w.ln1_b, d.ln_eps, ws.x_f32, ws.x_bf16, M,
                              d.hidden, stream));
     SPU_MARK(SPU_STAGE_LN1);
     e.bias = w.b_1;
     e.resid = nullptr;
     e.out = ws.h;
-    SPU_TRY(gemm_launch(p.ffn1, M, e, stream));
+    if (SPU_ON(SPU_STAGE_GEMM_FFN1)) SPU_TRY(gemm_launch(p.ffn1, M, e, stream));
     SPU_MARK(SPU_STAGE_GEMM_FFN1);
     e.bias = w.b_2;
     e.resid = ws.x_f32;
     e.out = ws.x_f32;
-    SPU_TRY(gemm_launch(p.ffn2, M, e, stream));
+    if (SPU_ON(SPU_STAGE_GEMM_FFN2)) SPU_TRY(gemm_launch(p.ffn2, M, e, stream));
     SPU_MARK(SPU_STAGE_GEMM_FFN2);
     // the last LayerNorm writes last_hidden_state straight into the StarPU output buffer
-    SPU_TRY(layernorm_launch(ws.x_f32, w.ln2_g, w.ln2_b, d.ln_eps, last ? out : ws.x_f32,
+    if (SPU_ON(SPU_STAGE_LN2)) SPU_TRY(layernorm_launch(ws.x_f32, w.ln2_g, w.ln2_b, d.ln_eps, last ? out : ws.x_f32,
                              last ? nullptr : ws.x_bf16, M, d.hidden, stream));
     SPU_MARK(SPU_STAGE_LN2);
   }
@@ -402,6 +403,51 @@ extern "C" spu_status spu_bert_forward_profiled(spu_replica *r, int32_t ws_idx, 
   for (cudaEvent_t e : trail.ev)
     if (e) cudaEventDestroy(e);
   return st;
+}
+
+extern "C" spu_status spu_bert_stage_chain_ms(spu_replica *r, int32_t ws_idx, const int64_t *ids,
+                                              const int64_t *mask, int32_t batch, int32_t seq, float *out,
+                                              uint32_t stage_mask, int32_t reps, void *stream, float *ms_per_forward) {
+  SPU_TRY(check_forward_args(r, ws_idx, ids, mask, batch, seq, out));
+  SPU_REQUIRE(ms_per_forward != nullptr && reps > 0, SPU_ERR_INVALID, "stage_chain: bad argument");
+  DeviceGuard guard(r->device);
+  cudaStream_t s = as_stream(stream);
+  Workspace &ws = r->ws[ws_idx];
+  // capture `reps` forwards' worth of the selected kernel classes into one graph so the
+  // chain runs back to back (programmatic dependent launch in effect, no host gaps)
+  SPU_TRY(enqueue_forward(r, ws, ids, mask, batch, seq, out, s, nullptr, stage_mask));  // warm-up, attributes
+  SPU_CUDA_TRY(cudaStreamSynchronize(s));
+  SPU_CUDA_TRY(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
+  spu_status st = SPU_OK;
+  for (int i = 0; i < reps && st == SPU_OK; ++i)
+    st = enqueue_forward(r, ws, ids, mask, batch, seq, out, s, nullptr, stage_mask);
+  cudaGraph_t graph = nullptr;
+  cudaError_t e = cudaStreamEndCapture(s, &graph);
+  if (st != SPU_OK) {
+    if (graph) cudaGraphDestroy(graph);
+    return st;
+  }
+  SPU_CUDA_TRY(e);
+  cudaGraphExec_t exec = nullptr;
+  e = cudaGraphInstantiate(&exec, graph, 0);
+  cudaGraphDestroy(graph);
+  SPU_CUDA_TRY(e);
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  cudaEventCreate(&e0);
+  cudaEventCreate(&e1);
+  cudaGraphLaunch(exec, s);  // warm
+  cudaEventRecord(e0, s);
+  cudaGraphLaunch(exec, s);
+  cudaEventRecord(e1, s);
+  e = cudaStreamSynchronize(s);
+  float ms = 0.f;
+  if (e == cudaSuccess) cudaEventElapsedTime(&ms, e0, e1);
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  cudaGraphExecDestroy(exec);
+  SPU_CUDA_TRY(e);
+  *ms_per_forward = ms / static_cast<float>(reps);
+  return SPU_OK;
 }
 
 extern "C" uint64_t spu_bert_output_bytes(const spu_replica *r, int32_t batch, int32_t seq) {

@@ -1,0 +1,24 @@
+#!/usr/bin/env python
+"""Target for `ncu`: two eager BERT-base forwards (batch 32 x seq 128 by default) through the
+C-ABI.  Skip the first forward's launches and capture the second's."""
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import torch  # noqa: E402
+
+from starpu_inference_server_b200 import synthetic  # noqa: E402
+from starpu_inference_server_b200.bert import BertConfig, BertReplica  # noqa: E402
+
+B = int(sys.argv[1]) if len(sys.argv) > 1 else 32
+S = int(sys.argv[2]) if len(sys.argv) > 2 else 128
+spec = BertConfig()
+rep = BertReplica(synthetic.make_weights(spec, 0), max_batch=B, max_seq=S)
+ids, mask = synthetic.make_requests(spec, B, S, seed=1)
+ids, mask = torch.from_numpy(ids).cuda(), torch.from_numpy(mask).cuda()
+out = torch.empty(B, S, spec.hidden, device="cuda")
+for _ in range(2):
+    rep.forward_async(ids, mask, out)
+    torch.cuda.synchronize()
+rep.close()
