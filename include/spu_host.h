@@ -87,6 +87,7 @@ typedef struct spu_result {
   double codelet_ms;    /* codelet_end - codelet_start (host time of the async enqueue) */
   double task_ms;       /* before_starpu_submitted -> callback_start (task latency) */
   double latency_ms;    /* enqueued -> callback_end */
+  float first_value;    /* outputs[0] row 0 element 0 read from the landed slot (fp32 outputs) */
   char error[192];
 } spu_result;
 

@@ -100,6 +100,8 @@ struct spu_server {
       out.codelet_ms = ms_between(res.timing.codelet_start_time, res.timing.codelet_end_time);
       out.task_ms = ms_between(res.timing.before_starpu_submitted_time, res.timing.callback_start_time);
       std::snprintf(out.error, sizeof(out.error), "%s", res.error.c_str());
+      if (res.ok && !res.outputs.empty() && res.outputs[0].defined() && res.outputs[0].type == ScalarType::Float32)
+        std::memcpy(&out.first_value, res.outputs[0].data, sizeof(float));
       if (res.ok)
         // the response copy the reference makes per request (fill_output_tensor,
         // src/grpc/server/inference_service_io.cpp:377-419): slot view -> caller's buffer

@@ -48,7 +48,7 @@ class Result(C.Structure):
     _fields_ = [("request_id", C.c_int32), ("ok", C.c_int32), ("rows", C.c_int64), ("batch_rows", C.c_int64),
                 ("worker_id", C.c_int32), ("device_id", C.c_int32), ("executed_on", C.c_int32),
                 ("codelet_ms", C.c_double), ("task_ms", C.c_double), ("latency_ms", C.c_double),
-                ("error", C.c_char * 192)]
+                ("first_value", C.c_float), ("error", C.c_char * 192)]
 
 
 _lib = None
@@ -164,6 +164,17 @@ class Server:
         """requests: list of (request_id, batch, [input arrays], [output arrays]).  One StarPU task."""
         arr = (Request * len(requests))(*[self._request(*r) for r in requests])
         t = lib().spu_server_submit_batch(self._h, arr, len(requests), fixed_worker)
+        if t < 0:
+            raise HostError(last_error())
+        return t
+
+    def prepare_batch(self, requests):
+        """Build the request table once (pointer table reuse across steps)."""
+        return (Request * len(requests))(*[self._request(*r) for r in requests]), len(requests)
+
+    def submit_prepared(self, prepared, fixed_worker=-1):
+        arr, n = prepared
+        t = lib().spu_server_submit_batch(self._h, arr, n, fixed_worker)
         if t < 0:
             raise HostError(last_error())
         return t
