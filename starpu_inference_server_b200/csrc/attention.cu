@@ -98,7 +98,8 @@ attention_kernel(const __nv_bfloat16 *__restrict__ qkv, const float *__restrict_
       // keys past the sequence end never contribute (-inf); masked keys get the
       // additive bias the mask builder wrote (HF: (1-mask)*finfo.min)
       s_bias[buf][threadIdx.x] =
-          key < seq ? mask_bias[static_cast<size_t>(b) * seq + key] * kLog2e : -INFINITY;
+          key < seq ? (mask_bias != nullptr ? mask_bias[static_cast<size_t>(b) * seq + key] * kLog2e : 0.f)
+                    : -INFINITY;
     }
   };
 
@@ -239,7 +240,7 @@ attention_kernel(const __nv_bfloat16 *__restrict__ qkv, const float *__restrict_
 
 spu_status attention_launch(const void *qkv, const float *mask_bias, void *ctx, int batch, int seq,
                             int heads, cudaStream_t stream) {
-  SPU_REQUIRE(qkv && mask_bias && ctx, SPU_ERR_INVALID, "attention: null argument");
+  SPU_REQUIRE(qkv && ctx, SPU_ERR_INVALID, "attention: null argument");  // mask_bias may be null (no mask)
   SPU_REQUIRE(batch > 0 && seq > 0 && heads > 0, SPU_ERR_INVALID, "attention: empty shape");
   SPU_REQUIRE(batch <= 65535 && heads <= 65535, SPU_ERR_CAPACITY, "attention: grid too large");
   dim3 grid((seq + kQTile - 1) / kQTile, heads, batch);

@@ -6,67 +6,14 @@
 #include <mutex>
 #include <vector>
 
-#include "common.cuh"
-#include "gemm_sm100.cuh"
+#include "replica.cuh"
 
 namespace spu {
 
 static thread_local std::string g_last_error;
 void set_error(const std::string &msg) { g_last_error = msg; }
 
-spu_status attention_launch(const void *qkv, const float *mask_bias, void *ctx, int batch, int seq,
-                            int heads, cudaStream_t stream);
-spu_status bert_embed_launch(const int64_t *ids, const int64_t *mask, const float *word,
-                             const float *pos, const float *type0, const float *gamma,
-                             const float *beta, float eps, int vocab, float *x_f32, void *x_bf16,
-                             float *mask_bias, int batch, int seq, int hidden, cudaStream_t stream);
-spu_status layernorm_launch(const float *x, const float *gamma, const float *beta, float eps,
-                            float *out_f32, void *out_bf16, int rows, int hidden,
-                            cudaStream_t stream);
-
 namespace {
-
-uint16_t f32_to_bf16_rne(float f) {
-  uint32_t u;
-  std::memcpy(&u, &f, 4);
-  if ((u & 0x7fffffffu) > 0x7f800000u) return static_cast<uint16_t>((u >> 16) | 0x40u);  // NaN
-  u += 0x7fffu + ((u >> 16) & 1u);
-  return static_cast<uint16_t>(u >> 16);
-}
-
-struct DeviceGuard {
-  int prev = -1;
-  explicit DeviceGuard(int dev) {
-    cudaGetDevice(&prev);
-    if (prev != dev) cudaSetDevice(dev);
-  }
-  ~DeviceGuard() {
-    if (prev >= 0) cudaSetDevice(prev);
-  }
-};
-
-struct LayerWeights {
-  __nv_bfloat16 *w_qkv = nullptr, *w_o = nullptr, *w_1 = nullptr, *w_2 = nullptr;
-  float *b_qkv = nullptr, *b_o = nullptr, *b_1 = nullptr, *b_2 = nullptr;
-  float *ln1_g = nullptr, *ln1_b = nullptr, *ln2_g = nullptr, *ln2_b = nullptr;
-};
-
-struct LayerPlans {
-  GemmPlan qkv, attn_out, ffn1, ffn2;
-};
-
-struct GraphKey {
-  const void *ids = nullptr, *mask = nullptr, *out = nullptr;
-  int batch = 0, seq = 0;
-  bool operator==(const GraphKey &o) const {
-    return ids == o.ids && mask == o.mask && out == o.out && batch == o.batch && seq == o.seq;
-  }
-};
-
-struct CapturedGraph {
-  GraphKey key;
-  cudaGraphExec_t exec = nullptr;
-};
 
 // Optional per-kernel event trail (measurement hook only).
 struct StageTrail {
@@ -83,79 +30,6 @@ struct StageTrail {
     return SPU_OK;
   }
 };
-
-struct Workspace {
-  float *x_f32 = nullptr;
-  __nv_bfloat16 *x_bf16 = nullptr, *qkv = nullptr, *ctx = nullptr, *h = nullptr;
-  float *mask_bias = nullptr;
-  std::vector<LayerPlans> plans;
-  std::vector<CapturedGraph> graphs;
-};
-
-}  // namespace
-}  // namespace spu
-
-struct spu_replica {
-  spu_bert_desc desc{};
-  int device = 0;
-  int max_batch = 0, max_seq = 0, cap_rows = 0;
-  uint32_t flags = 0;
-  float *word = nullptr, *pos = nullptr, *type0 = nullptr, *emb_g = nullptr, *emb_b = nullptr;
-  std::vector<spu::LayerWeights> layers;
-  std::vector<spu::Workspace> ws;
-  std::vector<void *> allocations;
-};
-
-namespace spu {
-namespace {
-
-template <typename T>
-spu_status dev_alloc(spu_replica *r, T **out, size_t count) {
-  void *p = nullptr;
-  cudaError_t e = cudaMalloc(&p, count * sizeof(T));
-  if (e != cudaSuccess) {
-    set_error(std::string("cudaMalloc: ") + cudaGetErrorString(e));
-    return SPU_ERR_NOMEM;
-  }
-  r->allocations.push_back(p);
-  *out = static_cast<T *>(p);
-  return SPU_OK;
-}
-
-spu_status upload_f32(spu_replica *r, float **dst, const float *src, size_t n) {
-  spu_status st = dev_alloc(r, dst, n);
-  if (st != SPU_OK) return st;
-  SPU_CUDA_TRY(cudaMemcpy(*dst, src, n * sizeof(float), cudaMemcpyHostToDevice));
-  return SPU_OK;
-}
-
-// Upload rows [0, n_src) of fp32 host matrices, stacked, as one bf16 device matrix.
-spu_status upload_bf16_stacked(spu_replica *r, __nv_bfloat16 **dst,
-                               std::initializer_list<const float *> srcs, size_t n_each) {
-  const size_t total = n_each * srcs.size();
-  std::vector<uint16_t> tmp(total);
-  size_t o = 0;
-  for (const float *s : srcs)
-    for (size_t i = 0; i < n_each; ++i) tmp[o++] = f32_to_bf16_rne(s[i]);
-  spu_status st = dev_alloc(r, dst, total);
-  if (st != SPU_OK) return st;
-  SPU_CUDA_TRY(cudaMemcpy(*dst, tmp.data(), total * 2, cudaMemcpyHostToDevice));
-  return SPU_OK;
-}
-
-spu_status upload_f32_stacked(spu_replica *r, float **dst, std::initializer_list<const float *> srcs,
-                              size_t n_each) {
-  std::vector<float> tmp;
-  tmp.reserve(n_each * srcs.size());
-  for (const float *s : srcs) tmp.insert(tmp.end(), s, s + n_each);
-  return upload_f32(r, dst, tmp.data(), tmp.size());
-}
-
-#define SPU_TRY(expr)                 \
-  do {                                \
-    spu_status _s = (expr);           \
-    if (_s != SPU_OK) return _s;      \
-  } while (0)
 
 spu_status build(spu_replica *r, const float *const *t) {
   const spu_bert_desc &d = r->desc;
@@ -264,6 +138,7 @@ spu_status enqueue_forward(spu_replica *r, Workspace &ws, const int64_t *ids, co
 spu_status check_forward_args(spu_replica *r, int ws_idx, const void *ids, const void *mask,
                               int batch, int seq, const void *out) {
   SPU_REQUIRE(r != nullptr, SPU_ERR_INVALID, "forward: null replica");
+  SPU_REQUIRE(r->kind == 0, SPU_ERR_INVALID, "forward: not a BERT replica");
   SPU_REQUIRE(ids && mask && out, SPU_ERR_INVALID, "forward: null buffer");
   SPU_REQUIRE(ws_idx >= 0 && ws_idx < static_cast<int>(r->ws.size()), SPU_ERR_INVALID,
               "forward: workspace index out of range");
@@ -325,6 +200,7 @@ extern "C" spu_status spu_replica_destroy(spu_replica *r) {
   for (Workspace &ws : r->ws)
     for (CapturedGraph &g : ws.graphs)
       if (g.exec) cudaGraphExecDestroy(g.exec);
+  if (r->vit != nullptr && r->vit_destroy != nullptr) r->vit_destroy(r->vit);
   for (void *p : r->allocations) cudaFree(p);
   delete r;
   return SPU_OK;
@@ -451,7 +327,7 @@ extern "C" spu_status spu_bert_stage_chain_ms(spu_replica *r, int32_t ws_idx, co
 }
 
 extern "C" uint64_t spu_bert_output_bytes(const spu_replica *r, int32_t batch, int32_t seq) {
-  if (r == nullptr || batch <= 0 || seq <= 0) return 0;
+  if (r == nullptr || r->kind != 0 || batch <= 0 || seq <= 0) return 0;
   return static_cast<uint64_t>(batch) * static_cast<uint64_t>(seq) * static_cast<uint64_t>(r->desc.hidden) * 4u;
 }
 

@@ -1,0 +1,144 @@
+// Shared definitions of the weight replica (BERT fields here; the ViT state hangs off
+// `vit`, owned by vit.cu).  Internal header of libspu_b200.so.
+#pragma once
+#include <cstring>
+#include <initializer_list>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "common.cuh"
+#include "gemm_sm100.cuh"
+
+namespace spu {
+
+spu_status attention_launch(const void *qkv, const float *mask_bias, void *ctx, int batch, int seq,
+                            int heads, cudaStream_t stream);
+spu_status bert_embed_launch(const int64_t *ids, const int64_t *mask, const float *word,
+                             const float *pos, const float *type0, const float *gamma,
+                             const float *beta, float eps, int vocab, float *x_f32, void *x_bf16,
+                             float *mask_bias, int batch, int seq, int hidden, cudaStream_t stream);
+// in_row_stride: elements between consecutive input rows (0 = hidden, i.e. contiguous)
+spu_status layernorm_launch(const float *x, const float *gamma, const float *beta, float eps,
+                            float *out_f32, void *out_bf16, int rows, int hidden,
+                            cudaStream_t stream, long long in_row_stride = 0);
+
+inline uint16_t f32_to_bf16_rne(float f) {
+  uint32_t u;
+  std::memcpy(&u, &f, 4);
+  if ((u & 0x7fffffffu) > 0x7f800000u) return static_cast<uint16_t>((u >> 16) | 0x40u);  // NaN
+  u += 0x7fffu + ((u >> 16) & 1u);
+  return static_cast<uint16_t>(u >> 16);
+}
+
+struct DeviceGuard {
+  int prev = -1;
+  explicit DeviceGuard(int dev) {
+    cudaGetDevice(&prev);
+    if (prev != dev) cudaSetDevice(dev);
+  }
+  ~DeviceGuard() {
+    if (prev >= 0) cudaSetDevice(prev);
+  }
+};
+
+struct LayerWeights {
+  __nv_bfloat16 *w_qkv = nullptr, *w_o = nullptr, *w_1 = nullptr, *w_2 = nullptr;
+  float *b_qkv = nullptr, *b_o = nullptr, *b_1 = nullptr, *b_2 = nullptr;
+  float *ln1_g = nullptr, *ln1_b = nullptr, *ln2_g = nullptr, *ln2_b = nullptr;
+};
+
+struct LayerPlans {
+  GemmPlan qkv, attn_out, ffn1, ffn2;
+};
+
+struct GraphKey {
+  const void *ids = nullptr, *mask = nullptr, *out = nullptr;
+  int batch = 0, seq = 0;
+  bool operator==(const GraphKey &o) const {
+    return ids == o.ids && mask == o.mask && out == o.out && batch == o.batch && seq == o.seq;
+  }
+};
+
+struct CapturedGraph {
+  GraphKey key;
+  cudaGraphExec_t exec = nullptr;
+};
+
+struct Workspace {
+  float *x_f32 = nullptr;
+  __nv_bfloat16 *x_bf16 = nullptr, *qkv = nullptr, *ctx = nullptr, *h = nullptr;
+  float *mask_bias = nullptr;
+  std::vector<LayerPlans> plans;
+  std::vector<CapturedGraph> graphs;
+};
+
+struct VitState;  // vit.cu
+
+}  // namespace spu
+
+struct spu_replica {
+  int kind = 0;  // 0 = BERT, 1 = ViT
+  spu_bert_desc desc{};
+  int device = 0;
+  int max_batch = 0, max_seq = 0, cap_rows = 0;
+  uint32_t flags = 0;
+  float *word = nullptr, *pos = nullptr, *type0 = nullptr, *emb_g = nullptr, *emb_b = nullptr;
+  std::vector<spu::LayerWeights> layers;
+  std::vector<spu::Workspace> ws;
+  std::vector<void *> allocations;
+  spu::VitState *vit = nullptr;
+  void (*vit_destroy)(spu::VitState *) = nullptr;
+};
+
+namespace spu {
+
+template <typename T>
+spu_status dev_alloc(spu_replica *r, T **out, size_t count) {
+  void *p = nullptr;
+  cudaError_t e = cudaMalloc(&p, (count ? count : 1) * sizeof(T));
+  if (e != cudaSuccess) {
+    set_error(std::string("cudaMalloc: ") + cudaGetErrorString(e));
+    return SPU_ERR_NOMEM;
+  }
+  r->allocations.push_back(p);
+  *out = static_cast<T *>(p);
+  return SPU_OK;
+}
+
+inline spu_status upload_f32(spu_replica *r, float **dst, const float *src, size_t n) {
+  spu_status st = dev_alloc(r, dst, n);
+  if (st != SPU_OK) return st;
+  SPU_CUDA_TRY(cudaMemcpy(*dst, src, n * sizeof(float), cudaMemcpyHostToDevice));
+  return SPU_OK;
+}
+
+// Upload fp32 host matrices, stacked, as one bf16 device matrix.
+inline spu_status upload_bf16_stacked(spu_replica *r, __nv_bfloat16 **dst,
+                                      std::initializer_list<const float *> srcs, size_t n_each) {
+  const size_t total = n_each * srcs.size();
+  std::vector<uint16_t> tmp(total);
+  size_t o = 0;
+  for (const float *s : srcs)
+    for (size_t i = 0; i < n_each; ++i) tmp[o++] = f32_to_bf16_rne(s[i]);
+  spu_status st = dev_alloc(r, dst, total);
+  if (st != SPU_OK) return st;
+  SPU_CUDA_TRY(cudaMemcpy(*dst, tmp.data(), total * 2, cudaMemcpyHostToDevice));
+  return SPU_OK;
+}
+
+inline spu_status upload_f32_stacked(spu_replica *r, float **dst, std::initializer_list<const float *> srcs,
+                                     size_t n_each) {
+  std::vector<float> tmp;
+  tmp.reserve(n_each * srcs.size());
+  for (const float *s : srcs) tmp.insert(tmp.end(), s, s + n_each);
+  return upload_f32(r, dst, tmp.data(), tmp.size());
+}
+
+#define SPU_TRY(expr)                 \
+  do {                                \
+    spu_status _s = (expr);           \
+    if (_s != SPU_OK) return _s;      \
+  } while (0)
+
+}  // namespace spu

@@ -2,7 +2,7 @@
 // residual LayerNorm, ragged gather/pad/mask, segmented gather/scatter copies, and
 // the toy affine "model".  All are one-pass, 128-bit coalesced, warp-shuffle
 // reductions, no shared-memory staging needed (no reuse across rows).
-#include "common.cuh"
+#include "replica.cuh"
 
 namespace spu {
 namespace {
@@ -95,17 +95,18 @@ bert_embed_ln_kernel(const int64_t *__restrict__ ids, const int64_t *__restrict_
 __global__ void __launch_bounds__(kRowThreads)
 layernorm_kernel(const float *__restrict__ x, const float *__restrict__ gamma,
                  const float *__restrict__ beta, float eps, float *out_f32,
-                 __nv_bfloat16 *out_bf16, int rows, int hidden) {
+                 __nv_bfloat16 *out_bf16, int rows, int hidden, long long in_row_stride) {
   const int row = blockIdx.x * (kRowThreads / 32) + (threadIdx.x >> 5);
   if (row >= rows) return;
   const int lane = threadIdx.x & 31;
   const int nchunk = hidden >> 2;
   const int nchunk_lane = (nchunk - lane + 31) >> 5;
   const size_t off = static_cast<size_t>(row) * hidden;
+  const size_t in_off = static_cast<size_t>(row) * static_cast<size_t>(in_row_stride);
   float4 v[kMaxChunksPerLane];
 #pragma unroll
   for (int i = 0; i < kMaxChunksPerLane; ++i)
-    if (i < nchunk_lane) v[i] = reinterpret_cast<const float4 *>(x + off)[lane + i * 32];
+    if (i < nchunk_lane) v[i] = reinterpret_cast<const float4 *>(x + in_off)[lane + i * 32];
   const RowStats st = row_stats(v, nchunk_lane, hidden, eps);
   row_normalise_store(v, nchunk_lane, st, gamma, beta, out_f32, out_bf16, off);
 }
@@ -195,15 +196,17 @@ spu_status bert_embed_launch(const int64_t *ids, const int64_t *mask, const floa
 
 spu_status layernorm_launch(const float *x, const float *gamma, const float *beta, float eps,
                             float *out_f32, void *out_bf16, int rows, int hidden,
-                            cudaStream_t stream) {
+                            cudaStream_t stream, long long in_row_stride) {
   SPU_REQUIRE(x && gamma && beta, SPU_ERR_INVALID, "layernorm: null argument");
+  if (in_row_stride == 0) in_row_stride = hidden;
+  SPU_REQUIRE(in_row_stride % 4 == 0, SPU_ERR_INVALID, "layernorm: row stride must keep 16-byte alignment");
   SPU_REQUIRE(hidden % 4 == 0 && hidden <= 128 * kMaxChunksPerLane, SPU_ERR_UNSUPPORTED,
               "layernorm: hidden must be a multiple of 4 and <= 1024");
   SPU_REQUIRE(rows > 0, SPU_ERR_INVALID, "layernorm: empty input");
   const int grid = (rows + kRowThreads / 32 - 1) / (kRowThreads / 32);
   layernorm_kernel<<<grid, kRowThreads, 0, stream>>>(x, gamma, beta, eps, out_f32,
                                                      static_cast<__nv_bfloat16 *>(out_bf16), rows,
-                                                     hidden);
+                                                     hidden, in_row_stride);
   SPU_CUDA_TRY(cudaGetLastError());
   return SPU_OK;
 }
@@ -267,7 +270,7 @@ extern "C" spu_status spu_affine_f32_async(const float *in, float *out, uint64_t
 extern "C" spu_status spu_layernorm_async(const float *x, const float *gamma, const float *beta,
                                           float eps, float *out_f32, void *out_bf16, int32_t rows,
                                           int32_t hidden, void *stream) {
-  return layernorm_launch(x, gamma, beta, eps, out_f32, out_bf16, rows, hidden, as_stream(stream));
+  return layernorm_launch(x, gamma, beta, eps, out_f32, out_bf16, rows, hidden, as_stream(stream), 0);
 }
 
 extern "C" spu_status spu_bert_embed_async(const int64_t *ids, const int64_t *mask,

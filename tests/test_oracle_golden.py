@@ -150,3 +150,40 @@ def test_ragged_gather_scatter_roundtrip(oracle_gs):
     assert rc == 0
     for s, d, L in zip(src, dst, lens):
         assert np.array_equal(s[:L], d[:L])
+
+
+@pytest.mark.parametrize("name,spec_name", [("vit_tiny.npz", "VIT_TINY"), ("vit_l16.npz", "VIT_L_16")])
+def test_vit_oracle_matches_torchvision(name, spec_name):
+    """oracle/vit_oracle.py restatement vs the torchvision fp32 logits (oracle/make_golden_vit.py)."""
+    import hashlib
+    import json
+
+    from oracle import vit_oracle as vo
+
+    man = json.load(open(os.path.join(GOLD, "MANIFEST_VIT.json")))
+    assert hashlib.sha256(open(os.path.join(GOLD, name), "rb").read()).hexdigest() == man["files"][name]
+    spec = getattr(vo, spec_name)
+    z = np.load(os.path.join(GOLD, name))
+    if spec_name == "VIT_L_16" and (os.cpu_count() or 1) < 4:
+        pytest.skip("ViT-L on the CPU needs a few cores")
+    x = vo.make_inputs(spec, int(z["batch"]), int(z["seed"]))
+    got = vo.vit_forward(vo.make_weights(spec, 0), spec, x)
+    assert np.abs(got - z["logits"]).max() < 2e-5 * max(1.0, float(np.abs(z["logits"]).max()))
+    assert (got.argmax(-1) == z["logits"].argmax(-1)).all()
+
+
+def test_vit_im2col_is_conv_proj():
+    """The patch embedding written as a GEMM over im2col rows equals nn.Conv2d(stride=patch)."""
+    import torch
+
+    from oracle import vit_oracle as vo
+
+    spec = vo.VIT_TINY
+    w = vo.make_weights(spec, 3)
+    x = torch.from_numpy(vo.make_inputs(spec, 2, seed=9))
+    conv = torch.nn.functional.conv2d(x, torch.from_numpy(w["conv_proj.weight"]), torch.from_numpy(w["conv_proj.bias"]),
+                                      stride=spec.patch)
+    ref = conv.reshape(2, spec.hidden, -1).permute(0, 2, 1).reshape(-1, spec.hidden)
+    got = vo.im2col(spec, x) @ torch.from_numpy(w["conv_proj.weight"]).reshape(spec.hidden, -1).T + \
+        torch.from_numpy(w["conv_proj.bias"])
+    assert torch.allclose(got, ref, atol=1e-5)
