@@ -57,6 +57,8 @@ typedef struct spu_bert_desc {
 /* precision flags for spu_*_replica_create */
 #define SPU_PREC_BF16 0u
 #define SPU_PREC_FP8_E4M3 1u /* per-tensor scaled FP8 GEMM inputs (QKV/out/FFN) */
+/* FP8 in the first n encoder layers only, bf16 GEMMs in the rest (n = 0 or >= layers: all) */
+#define SPU_PREC_FP8_LAYERS(n) (SPU_PREC_FP8_E4M3 | ((uint32_t)(n) << 8))
 
 /* Number of weight tensors spu_bert_replica_create expects: 5 + 16*layers, in the
  * order of the HF state dict restated in oracle/bert_oracle.py:weight_names()
@@ -120,6 +122,18 @@ spu_status spu_bert_forward_profiled(spu_replica *r, int32_t ws_idx,
                                      const int64_t *ids, const int64_t *mask,
                                      int32_t batch, int32_t seq, float *out,
                                      void *stream, float *stage_ms);
+
+/* FP8 E4M3 variant (replica created with SPU_PREC_FP8_E4M3): per-tensor weight scales are
+ * fixed at creation (amax/448); the per-tensor activation scales of the four GEMM inputs of
+ * every layer come from this calibration pass: it runs the bf16 forward of (ids, mask) with
+ * an amax probe after each such tensor, SYNCHRONISES the stream and installs scale =
+ * running amax / 448.  May be called several times (maxima accumulate); must be called at
+ * least once before spu_bert_forward_async.  Start-up only (warm-up, warmup.cpp:225-299). */
+spu_status spu_bert_calibrate_fp8(spu_replica *r, int32_t ws_idx, const int64_t *ids,
+                                  const int64_t *mask, int32_t batch, int32_t seq, void *stream);
+/* Scales of an FP8 replica, 8 per layer: activation x, ctx, x1, h then weight qkv, out,
+ * ffn1, ffn2.  Returns the count (0 for a bf16 replica). */
+int32_t spu_bert_fp8_scales(const spu_replica *r, float *out, int32_t cap);
 
 /* Measurement hook: device time (ms per forward) of ONLY the kernel classes whose bit
  * (1u << SPU_STAGE_*) is set in stage_mask, run as `reps` forwards' worth of launches back
@@ -209,6 +223,18 @@ spu_status spu_gemm_bf16_async(const void *A, const void *W, const float *bias,
                                const float *resid, void *out, int32_t M,
                                int32_t N, int32_t K, int32_t epilogue,
                                void *stream);
+
+/* FP8 E4M3 GEMM: A [M,K] and W [N,K] hold e4m3 bytes; C = (A W^T) * acc_scale + bias with
+ * epilogue SPU_EPI_BIAS (bf16 out), SPU_EPI_BIAS_RESID (fp32 out = ... + resid) or
+ * SPU_EPI_BIAS_GELU_E4M3 (e4m3 out = gelu(...) * out_inv_scale).  K % 128 == 0. */
+#define SPU_EPI_BIAS_GELU_E4M3 3
+spu_status spu_gemm_fp8_async(const void *A, const void *W, const float *bias,
+                              const float *resid, void *out, int32_t M, int32_t N,
+                              int32_t K, int32_t epilogue, float acc_scale,
+                              float out_inv_scale, void *stream);
+/* out_e4m3[i] = sat(in[i] * inv_scale), n % 4 == 0 (round to nearest even, saturating at 448) */
+spu_status spu_quantize_e4m3_async(const float *in_f32, void *out, uint64_t n, float inv_scale,
+                                   void *stream);
 
 /* Same GEMM with the tile shape forced (tests / tile sweeps): cta_group 1 = one CTA per
  * 128 x block_n tile, 2 = a CTA pair per 256 x block_n tile; block_n in {64,128,192,256}

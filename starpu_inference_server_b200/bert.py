@@ -122,6 +122,18 @@ class BertReplica:
                                                       m, reps, capi.stream_ptr(stream), C.byref(ms)))
         return ms.value
 
+    def calibrate_fp8(self, ids, mask, ws: int = 0, stream=None):
+        """FP8 replicas: install per-tensor activation scales from this calibration batch."""
+        b, s = ids.shape
+        capi.check(capi.lib().spu_bert_calibrate_fp8(self._h, ws, capi.ptr(ids), capi.ptr(mask), b, s,
+                                                     capi.stream_ptr(stream)))
+
+    def fp8_scales(self):
+        n = capi.lib().spu_bert_fp8_scales(self._h, None, 0)
+        buf = (C.c_float * max(n, 1))()
+        capi.lib().spu_bert_fp8_scales(self._h, buf, n)
+        return np.array(buf[:n], dtype=np.float32).reshape(-1, 8)
+
     def capture(self, ids, mask, out, ws: int = 0, stream=None):
         b, s = ids.shape
         capi.check(capi.lib().spu_bert_forward_capture(self._h, ws, capi.ptr(ids), capi.ptr(mask), b, s,

@@ -26,7 +26,8 @@ SYMBOLS = [
     "spu_attention_async", "spu_layernorm_async", "spu_bert_embed_async", "spu_affine_f32_async",
     "spu_last_error", "spu_abi_version", "spu_device_count", "spu_device_is_sm100",
     "spu_bert_output_bytes", "spu_vit_replica_create", "spu_vit_forward_async", "spu_vit_input_bytes",
-    "spu_vit_output_bytes", "spu_bert_stage_chain_ms",
+    "spu_vit_output_bytes", "spu_bert_stage_chain_ms", "spu_bert_calibrate_fp8", "spu_bert_fp8_scales",
+    "spu_gemm_fp8_async", "spu_quantize_e4m3_async",
 ]
 
 
@@ -82,6 +83,10 @@ def lib():
                                          C.POINTER(vp)]
     L.spu_vit_forward_async.argtypes = [vp, i32, vp, i32, vp, vp]
     L.spu_bert_stage_chain_ms.argtypes = [vp, i32, vp, vp, i32, i32, vp, C.c_uint32, i32, vp, C.POINTER(f32)]
+    L.spu_bert_calibrate_fp8.argtypes = [vp, i32, vp, vp, i32, i32, vp]
+    L.spu_bert_fp8_scales.argtypes = [vp, C.POINTER(f32), i32]
+    L.spu_gemm_fp8_async.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, i32, f32, f32, vp]
+    L.spu_quantize_e4m3_async.argtypes = [vp, vp, u64, f32, vp]
     L.spu_bert_output_bytes.argtypes = [vp, i32, i32]
     L.spu_vit_input_bytes.argtypes = [vp, i32]
     L.spu_vit_output_bytes.argtypes = [vp, i32]

@@ -9,7 +9,7 @@
 // Restates the attention block of HF BertSelfAttention that LibTorch executes
 // inside Module::forward (/root/reference/src/core/starpu_setup.cpp:610); oracle:
 // oracle/bert_oracle.py:bert_forward (scores/softmax/ctx lines).
-#include "common.cuh"
+#include "replica.cuh"
 
 namespace spu {
 namespace {
@@ -73,9 +73,16 @@ __device__ __forceinline__ void load_tile_async(uint8_t *smem_tile, const __nv_b
   }
 }
 
+__device__ __forceinline__ uint16_t pack_e4m3x2(float lo, float hi) {
+  uint16_t r;
+  asm("cvt.rn.satfinite.e4m3x2.f32 %0, %1, %2;" : "=h"(r) : "f"(hi), "f"(lo));
+  return r;
+}
+
+template <bool OUT_E4M3>
 __global__ void __launch_bounds__(kThreads)
 attention_kernel(const __nv_bfloat16 *__restrict__ qkv, const float *__restrict__ mask_bias,
-                 __nv_bfloat16 *__restrict__ ctx, int seq, int heads) {
+                 void *__restrict__ ctx_out, int seq, int heads, float q_inv_scale) {
   __shared__ __align__(128) uint8_t s_q[kQTile * 128];
   __shared__ __align__(128) uint8_t s_k[2][kKTile * 128];
   __shared__ __align__(128) uint8_t s_v[2][kKTile * 128];
@@ -215,23 +222,47 @@ attention_kernel(const __nv_bfloat16 *__restrict__ qkv, const float *__restrict_
     l_run[r] += __shfl_xor_sync(0xffffffffu, l_run[r], 2);
   }
   const float inv0 = 1.f / l_run[0], inv1 = 1.f / l_run[1];
+  if constexpr (OUT_E4M3) {
+    // per-tensor scaled e4m3 operand of the attention-output GEMM: 64 rows x 64 bytes staged
+    // in this warp's part of s_q, then one 16-byte store per row quarter
+    uint8_t *ctx = static_cast<uint8_t *>(ctx_out);
+    const float s0 = inv0 * q_inv_scale, s1 = inv1 * q_inv_scale;
 #pragma unroll
-  for (int i = 0; i < 8; ++i) {
-    const int r0 = warp * 16 + g, r1 = r0 + 8;
-    *reinterpret_cast<uint32_t *>(s_q + tile_off(r0, i) + t * 4) =
-        pack_bf16(o[i][0] * inv0, o[i][1] * inv0);
-    *reinterpret_cast<uint32_t *>(s_q + tile_off(r1, i) + t * 4) =
-        pack_bf16(o[i][2] * inv1, o[i][3] * inv1);
-  }
-  __syncwarp();
+    for (int i = 0; i < 8; ++i) {
+      const int r0 = warp * 16 + g, r1 = r0 + 8;
+      *reinterpret_cast<uint16_t *>(s_q + r0 * 64 + i * 8 + t * 2) = pack_e4m3x2(o[i][0] * s0, o[i][1] * s0);
+      *reinterpret_cast<uint16_t *>(s_q + r1 * 64 + i * 8 + t * 2) = pack_e4m3x2(o[i][2] * s1, o[i][3] * s1);
+    }
+    __syncwarp();
 #pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const int idx = lane + i * 32;
-    const int r = warp * 16 + (idx >> 3), c = idx & 7;
-    const int q_row = qt * kQTile + r;
-    if (q_row < seq) {
-      const uint4 v = *reinterpret_cast<const uint4 *>(s_q + tile_off(r, c));
-      *reinterpret_cast<uint4 *>(ctx + (tok0 + q_row) * hidden + h * kHeadDim + c * 8) = v;
+    for (int i = 0; i < 2; ++i) {
+      const int idx = lane + i * 32;
+      const int r = warp * 16 + (idx >> 2), c = idx & 3;
+      const int q_row = qt * kQTile + r;
+      if (q_row < seq)
+        *reinterpret_cast<uint4 *>(ctx + (tok0 + q_row) * hidden + h * kHeadDim + c * 16) =
+            *reinterpret_cast<const uint4 *>(s_q + r * 64 + c * 16);
+    }
+  } else {
+    __nv_bfloat16 *ctx = static_cast<__nv_bfloat16 *>(ctx_out);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int r0 = warp * 16 + g, r1 = r0 + 8;
+      *reinterpret_cast<uint32_t *>(s_q + tile_off(r0, i) + t * 4) =
+          pack_bf16(o[i][0] * inv0, o[i][1] * inv0);
+      *reinterpret_cast<uint32_t *>(s_q + tile_off(r1, i) + t * 4) =
+          pack_bf16(o[i][2] * inv1, o[i][3] * inv1);
+    }
+    __syncwarp();
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int idx = lane + i * 32;
+      const int r = warp * 16 + (idx >> 3), c = idx & 7;
+      const int q_row = qt * kQTile + r;
+      if (q_row < seq) {
+        const uint4 v = *reinterpret_cast<const uint4 *>(s_q + tile_off(r, c));
+        *reinterpret_cast<uint4 *>(ctx + (tok0 + q_row) * hidden + h * kHeadDim + c * 8) = v;
+      }
     }
   }
 }
@@ -239,13 +270,17 @@ attention_kernel(const __nv_bfloat16 *__restrict__ qkv, const float *__restrict_
 }  // namespace
 
 spu_status attention_launch(const void *qkv, const float *mask_bias, void *ctx, int batch, int seq,
-                            int heads, cudaStream_t stream) {
+                            int heads, cudaStream_t stream, bool out_e4m3, float q_inv_scale) {
   SPU_REQUIRE(qkv && ctx, SPU_ERR_INVALID, "attention: null argument");  // mask_bias may be null (no mask)
   SPU_REQUIRE(batch > 0 && seq > 0 && heads > 0, SPU_ERR_INVALID, "attention: empty shape");
   SPU_REQUIRE(batch <= 65535 && heads <= 65535, SPU_ERR_CAPACITY, "attention: grid too large");
   dim3 grid((seq + kQTile - 1) / kQTile, heads, batch);
-  attention_kernel<<<grid, kThreads, 0, stream>>>(static_cast<const __nv_bfloat16 *>(qkv), mask_bias,
-                                                  static_cast<__nv_bfloat16 *>(ctx), seq, heads);
+  if (out_e4m3)
+    attention_kernel<true><<<grid, kThreads, 0, stream>>>(static_cast<const __nv_bfloat16 *>(qkv), mask_bias, ctx,
+                                                          seq, heads, q_inv_scale);
+  else
+    attention_kernel<false><<<grid, kThreads, 0, stream>>>(static_cast<const __nv_bfloat16 *>(qkv), mask_bias, ctx,
+                                                           seq, heads, 1.f);
   SPU_CUDA_TRY(cudaGetLastError());
   return SPU_OK;
 }

@@ -1,6 +1,7 @@
 // Per-GPU weight replica + per-worker workspaces + the forward the codelet enqueues.
 // Replaces load_model/clone_model_to_gpus (/root/reference/src/core/inference_runner.cpp:
 // 243-275) and the body of run_inference (/root/reference/src/core/starpu_setup.cpp:594-624).
+#include <cmath>
 #include <cstring>
 #include <memory>
 #include <mutex>
@@ -31,6 +32,19 @@ struct StageTrail {
   }
 };
 
+constexpr float kE4m3Max = 448.f;
+
+spu_status quantize_weight(spu_replica *r, uint8_t **dst, float *scale, const __nv_bfloat16 *w_bf16,
+                           std::initializer_list<const float *> srcs, size_t n_each) {
+  float amax = 0.f;
+  for (const float *s : srcs)
+    for (size_t i = 0; i < n_each; ++i) amax = std::fmax(amax, std::fabs(s[i]));
+  *scale = (amax > 0.f ? amax : 1.f) / kE4m3Max;
+  const size_t total = n_each * srcs.size();
+  SPU_TRY(dev_alloc(r, dst, total));
+  return quantize_e4m3_launch(nullptr, w_bf16, *dst, total, 1.f / *scale, nullptr);
+}
+
 spu_status build(spu_replica *r, const float *const *t) {
   const spu_bert_desc &d = r->desc;
   const size_t H = d.hidden, F = d.ffn;
@@ -55,6 +69,18 @@ spu_status build(spu_replica *r, const float *const *t) {
     SPU_TRY(upload_f32(r, &w.b_2, p[13], H));
     SPU_TRY(upload_f32(r, &w.ln2_g, p[14], H));
     SPU_TRY(upload_f32(r, &w.ln2_b, p[15], H));
+    if (r->flags & SPU_PREC_FP8_E4M3) {
+      // per-tensor weight scale = amax / 448 (E4M3 max finite), quantised on the device
+      // from the bf16 copy (which the calibration pass also uses)
+      SPU_TRY(quantize_weight(r, &w.q_qkv, &w.sw_qkv, w.w_qkv, {p[0], p[2], p[4]}, H * H));
+      SPU_TRY(quantize_weight(r, &w.q_o, &w.sw_o, w.w_o, {p[6]}, H * H));
+      SPU_TRY(quantize_weight(r, &w.q_1, &w.sw_1, w.w_1, {p[10]}, F * H));
+      SPU_TRY(quantize_weight(r, &w.q_2, &w.sw_2, w.w_2, {p[12]}, H * F));
+    }
+  }
+  if (r->flags & SPU_PREC_FP8_E4M3) {
+    SPU_TRY(dev_alloc(r, &r->amax, static_cast<size_t>(d.layers) * 4));
+    SPU_CUDA_TRY(cudaMemset(r->amax, 0, static_cast<size_t>(d.layers) * 4 * sizeof(float)));
   }
   const size_t rows = r->cap_rows;
   for (Workspace &ws : r->ws) {
@@ -64,6 +90,24 @@ spu_status build(spu_replica *r, const float *const *t) {
     SPU_TRY(dev_alloc(r, &ws.ctx, rows * H));
     SPU_TRY(dev_alloc(r, &ws.h, rows * F));
     SPU_TRY(dev_alloc(r, &ws.mask_bias, rows));
+    if (r->flags & SPU_PREC_FP8_E4M3) {
+      SPU_TRY(dev_alloc(r, &ws.x_q, rows * H));
+      SPU_TRY(dev_alloc(r, &ws.ctx_q, rows * H));
+      SPU_TRY(dev_alloc(r, &ws.h_q, rows * F));
+      ws.plans8.resize(d.layers);
+      for (int l = 0; l < d.layers; ++l) {
+        const LayerWeights &w = r->layers[l];
+        const int R = static_cast<int>(rows);
+        SPU_TRY(gemm_make_plan(&ws.plans8[l].qkv, ws.x_q, R, w.q_qkv, 3 * d.hidden, d.hidden, kEpiBias,
+                               GemmIn::FP8_E4M3));
+        SPU_TRY(gemm_make_plan(&ws.plans8[l].attn_out, ws.ctx_q, R, w.q_o, d.hidden, d.hidden, kEpiBiasResid,
+                               GemmIn::FP8_E4M3));
+        SPU_TRY(gemm_make_plan(&ws.plans8[l].ffn1, ws.x_q, R, w.q_1, d.ffn, d.hidden, kEpiBiasGeluE4m3,
+                               GemmIn::FP8_E4M3));
+        SPU_TRY(gemm_make_plan(&ws.plans8[l].ffn2, ws.h_q, R, w.q_2, d.hidden, d.ffn, kEpiBiasResid,
+                               GemmIn::FP8_E4M3));
+      }
+    }
     ws.plans.resize(d.layers);
     for (int l = 0; l < d.layers; ++l) {
       const LayerWeights &w = r->layers[l];
@@ -88,9 +132,18 @@ spu_status build(spu_replica *r, const float *const *t) {
   } while (0)
 #define SPU_ON(id) ((stage_mask >> (id)) & 1u)
 
+spu_status enqueue_forward_fp8(spu_replica *r, Workspace &ws, const int64_t *ids, const int64_t *mask,
+                               int batch, int seq, float *out, cudaStream_t stream, uint32_t stage_mask);
+
 spu_status enqueue_forward(spu_replica *r, Workspace &ws, const int64_t *ids, const int64_t *mask,
                            int batch, int seq, float *out, cudaStream_t stream,
                            StageTrail *trail = nullptr, uint32_t stage_mask = 0xffffffffu) {
+  if (r->flags & SPU_PREC_FP8_E4M3) {
+    SPU_REQUIRE(r->fp8_calibrated, SPU_ERR_INVALID,
+                "forward: FP8 replica has no activation scales yet (call spu_bert_calibrate_fp8 first)");
+    SPU_REQUIRE(trail == nullptr, SPU_ERR_UNSUPPORTED, "profiled forward: use spu_bert_stage_chain_ms for FP8");
+    return enqueue_forward_fp8(r, ws, ids, mask, batch, seq, out, stream, stage_mask);
+  }
   const spu_bert_desc &d = r->desc;
   const int M = batch * seq;
   if (SPU_ON(SPU_STAGE_EMBED)) SPU_TRY(bert_embed_launch(ids, mask, r->word, r->pos, r->type0, r->emb_g, r->emb_b, d.ln_eps,
@@ -135,6 +188,101 @@ spu_status enqueue_forward(spu_replica *r, Workspace &ws, const int64_t *ids, co
   return SPU_OK;
 }
 
+// FP8 E4M3 variant of enqueue_forward: same kernels, e4m3 GEMM operands with per-tensor
+// scales folded into the epilogue (acc * sa * sw + bias); attention, LayerNorm statistics and
+// the residual stream stay bf16 / fp32.  Layers >= r->fp8_layers run the bf16 GEMMs (the
+// late layers' quantisation noise is the part LayerNorm never attenuates).
+spu_status enqueue_forward_fp8(spu_replica *r, Workspace &ws, const int64_t *ids, const int64_t *mask,
+                               int batch, int seq, float *out, cudaStream_t stream, uint32_t stage_mask) {
+  const spu_bert_desc &d = r->desc;
+  const int M = batch * seq;
+  auto is8 = [&](int l) { return l < r->fp8_layers; };
+  if (SPU_ON(SPU_STAGE_EMBED))
+    SPU_TRY(bert_embed_launch(ids, mask, r->word, r->pos, r->type0, r->emb_g, r->emb_b, d.ln_eps, d.vocab,
+                              ws.x_f32, is8(0) ? nullptr : ws.x_bf16, ws.mask_bias, batch, seq, d.hidden, stream,
+                              is8(0) ? ws.x_q : nullptr, 1.f / r->layers[0].sa_x));
+  for (int l = 0; l < d.layers; ++l) {
+    const LayerWeights &w = r->layers[l];
+    const bool f8 = is8(l);
+    const LayerPlans &p = f8 ? ws.plans8[l] : ws.plans[l];
+    const bool last = l == d.layers - 1;
+    GemmEpilogueArgs e{};
+    e.bias = w.b_qkv;
+    e.out = ws.qkv;
+    e.acc_scale = f8 ? w.sa_x * w.sw_qkv : 1.f;
+    if (SPU_ON(SPU_STAGE_GEMM_QKV)) SPU_TRY(gemm_launch(p.qkv, M, e, stream));
+    if (SPU_ON(SPU_STAGE_ATTENTION))
+      SPU_TRY(attention_launch(ws.qkv, ws.mask_bias, f8 ? static_cast<void *>(ws.ctx_q) : ws.ctx, batch, seq,
+                               d.heads, stream, f8, 1.f / w.sa_ctx));
+    e.bias = w.b_o;
+    e.resid = ws.x_f32;
+    e.out = ws.x_f32;
+    e.acc_scale = f8 ? w.sa_ctx * w.sw_o : 1.f;
+    if (SPU_ON(SPU_STAGE_GEMM_OUT)) SPU_TRY(gemm_launch(p.attn_out, M, e, stream));
+    if (SPU_ON(SPU_STAGE_LN1))
+      SPU_TRY(layernorm_launch(ws.x_f32, w.ln1_g, w.ln1_b, d.ln_eps, ws.x_f32, f8 ? nullptr : ws.x_bf16, M,
+                               d.hidden, stream, 0, f8 ? ws.x_q : nullptr, 1.f / w.sa_x1));
+    e.bias = w.b_1;
+    e.resid = nullptr;
+    e.out = f8 ? static_cast<void *>(ws.h_q) : ws.h;
+    e.acc_scale = f8 ? w.sa_x1 * w.sw_1 : 1.f;
+    e.out_inv_scale = 1.f / w.sa_h;
+    if (SPU_ON(SPU_STAGE_GEMM_FFN1)) SPU_TRY(gemm_launch(p.ffn1, M, e, stream));
+    e.bias = w.b_2;
+    e.resid = ws.x_f32;
+    e.out = ws.x_f32;
+    e.acc_scale = f8 ? w.sa_h * w.sw_2 : 1.f;
+    if (SPU_ON(SPU_STAGE_GEMM_FFN2)) SPU_TRY(gemm_launch(p.ffn2, M, e, stream));
+    if (SPU_ON(SPU_STAGE_LN2)) {
+      const bool n8 = !last && is8(l + 1);
+      SPU_TRY(layernorm_launch(ws.x_f32, w.ln2_g, w.ln2_b, d.ln_eps, last ? out : ws.x_f32,
+                               (last || n8) ? nullptr : ws.x_bf16, M, d.hidden, stream, 0, n8 ? ws.x_q : nullptr,
+                               n8 ? 1.f / r->layers[l + 1].sa_x : 1.f));
+    }
+  }
+  return SPU_OK;
+}
+
+// bf16 forward with an amax probe after every tensor that feeds an FP8 GEMM.
+spu_status enqueue_calibration(spu_replica *r, Workspace &ws, const int64_t *ids, const int64_t *mask, int batch,
+                               int seq, cudaStream_t stream) {
+  const spu_bert_desc &d = r->desc;
+  const int M = batch * seq;
+  const uint64_t nH = static_cast<uint64_t>(M) * d.hidden, nF = static_cast<uint64_t>(M) * d.ffn;
+  SPU_TRY(bert_embed_launch(ids, mask, r->word, r->pos, r->type0, r->emb_g, r->emb_b, d.ln_eps, d.vocab, ws.x_f32,
+                            ws.x_bf16, ws.mask_bias, batch, seq, d.hidden, stream));
+  for (int l = 0; l < d.layers; ++l) {
+    const LayerWeights &w = r->layers[l];
+    const LayerPlans &p = ws.plans[l];
+    float *am = r->amax + 4 * l;
+    SPU_TRY(amax_launch(nullptr, ws.x_bf16, nH, am + 0, stream));
+    GemmEpilogueArgs e{};
+    e.acc_scale = 1.f;
+    e.bias = w.b_qkv;
+    e.out = ws.qkv;
+    SPU_TRY(gemm_launch(p.qkv, M, e, stream));
+    SPU_TRY(attention_launch(ws.qkv, ws.mask_bias, ws.ctx, batch, seq, d.heads, stream));
+    SPU_TRY(amax_launch(nullptr, ws.ctx, nH, am + 1, stream));
+    e.bias = w.b_o;
+    e.resid = ws.x_f32;
+    e.out = ws.x_f32;
+    SPU_TRY(gemm_launch(p.attn_out, M, e, stream));
+    SPU_TRY(layernorm_launch(ws.x_f32, w.ln1_g, w.ln1_b, d.ln_eps, ws.x_f32, ws.x_bf16, M, d.hidden, stream));
+    SPU_TRY(amax_launch(nullptr, ws.x_bf16, nH, am + 2, stream));
+    e.bias = w.b_1;
+    e.resid = nullptr;
+    e.out = ws.h;
+    SPU_TRY(gemm_launch(p.ffn1, M, e, stream));
+    SPU_TRY(amax_launch(nullptr, ws.h, nF, am + 3, stream));
+    e.bias = w.b_2;
+    e.resid = ws.x_f32;
+    e.out = ws.x_f32;
+    SPU_TRY(gemm_launch(p.ffn2, M, e, stream));
+    SPU_TRY(layernorm_launch(ws.x_f32, w.ln2_g, w.ln2_b, d.ln_eps, ws.x_f32, ws.x_bf16, M, d.hidden, stream));
+  }
+  return SPU_OK;
+}
+
 spu_status check_forward_args(spu_replica *r, int ws_idx, const void *ids, const void *mask,
                               int batch, int seq, const void *out) {
   SPU_REQUIRE(r != nullptr, SPU_ERR_INVALID, "forward: null replica");
@@ -170,7 +318,11 @@ extern "C" spu_status spu_bert_replica_create(const spu_bert_desc *desc, const f
               SPU_ERR_UNSUPPORTED, "replica_create: hidden/ffn must be multiples of 64, hidden <= 1024");
   SPU_REQUIRE(max_batch > 0 && max_seq > 0 && max_seq <= desc->max_pos && n_workspaces > 0,
               SPU_ERR_INVALID, "replica_create: bad capacity");
-  SPU_REQUIRE(flags == SPU_PREC_BF16, SPU_ERR_UNSUPPORTED, "replica_create: unsupported precision flag");
+  SPU_REQUIRE((flags & ~(SPU_PREC_FP8_E4M3 | 0xff00u)) == 0 && ((flags & SPU_PREC_FP8_E4M3) || flags == 0),
+              SPU_ERR_UNSUPPORTED, "replica_create: unsupported precision flag");
+  if (flags & SPU_PREC_FP8_E4M3)
+    SPU_REQUIRE(desc->hidden % 128 == 0 && desc->ffn % 128 == 0, SPU_ERR_UNSUPPORTED,
+                "replica_create: FP8 needs hidden/ffn multiples of 128 (one 128-byte K tile)");
   for (int i = 0; i < n_tensors; ++i)
     SPU_REQUIRE(tensors[i] != nullptr, SPU_ERR_INVALID, "replica_create: null weight tensor");
   SPU_REQUIRE(spu_device_is_sm100(device) == 1, SPU_ERR_UNSUPPORTED,
@@ -182,6 +334,10 @@ extern "C" spu_status spu_bert_replica_create(const spu_bert_desc *desc, const f
   r->max_batch = max_batch;
   r->max_seq = max_seq;
   r->flags = flags;
+  {
+    const int n8 = static_cast<int>((flags >> 8) & 0xffu);
+    r->fp8_layers = (flags & SPU_PREC_FP8_E4M3) ? ((n8 == 0 || n8 > desc->layers) ? desc->layers : n8) : 0;
+  }
   r->cap_rows = ((max_batch * max_seq + 127) / 128) * 128;
   r->ws.resize(n_workspaces);
   spu_status st = build(r.get(), tensors);
@@ -279,6 +435,64 @@ extern "C" spu_status spu_bert_forward_profiled(spu_replica *r, int32_t ws_idx, 
   for (cudaEvent_t e : trail.ev)
     if (e) cudaEventDestroy(e);
   return st;
+}
+
+extern "C" spu_status spu_bert_calibrate_fp8(spu_replica *r, int32_t ws_idx, const int64_t *ids,
+                                             const int64_t *mask, int32_t batch, int32_t seq, void *stream) {
+  float dummy = 0.f;
+  SPU_TRY(check_forward_args(r, ws_idx, ids, mask, batch, seq, &dummy));
+  SPU_REQUIRE(r->flags & SPU_PREC_FP8_E4M3, SPU_ERR_INVALID, "calibrate: not an FP8 replica");
+  DeviceGuard guard(r->device);
+  cudaStream_t s = as_stream(stream);
+  SPU_TRY(enqueue_calibration(r, r->ws[ws_idx], ids, mask, batch, seq, s));
+  std::vector<float> am(static_cast<size_t>(r->desc.layers) * 4);
+  SPU_CUDA_TRY(cudaMemcpyAsync(am.data(), r->amax, am.size() * sizeof(float), cudaMemcpyDeviceToHost, s));
+  SPU_CUDA_TRY(cudaStreamSynchronize(s));
+  for (int l = 0; l < r->desc.layers; ++l) {
+    LayerWeights &w = r->layers[l];
+    auto scale = [](float a) { return (a > 1e-12f ? a : 1.f) / kE4m3Max; };
+    w.sa_x = scale(am[4 * l + 0]);
+    w.sa_ctx = scale(am[4 * l + 1]);
+    w.sa_x1 = scale(am[4 * l + 2]);
+    w.sa_h = scale(am[4 * l + 3]);
+  }
+  r->fp8_calibrated = true;
+  // captured graphs bake the scales in: drop them
+  for (Workspace &ws : r->ws) {
+    for (CapturedGraph &g : ws.graphs)
+      if (g.exec) cudaGraphExecDestroy(g.exec);
+    ws.graphs.clear();
+  }
+  return SPU_OK;
+}
+
+extern "C" int32_t spu_bert_fp8_scales(const spu_replica *r, float *out, int32_t cap) {
+  if (r == nullptr || r->kind != 0 || !(r->flags & SPU_PREC_FP8_E4M3)) return 0;
+  const int n = r->desc.layers * 8;
+  for (int l = 0; l < r->desc.layers && out != nullptr; ++l) {
+    const LayerWeights &w = r->layers[l];
+    const float v[8] = {w.sa_x, w.sa_ctx, w.sa_x1, w.sa_h, w.sw_qkv, w.sw_o, w.sw_1, w.sw_2};
+    for (int i = 0; i < 8; ++i)
+      if (l * 8 + i < cap) out[l * 8 + i] = v[i];
+  }
+  return n;
+}
+
+extern "C" spu_status spu_gemm_fp8_async(const void *A, const void *W, const float *bias, const float *resid,
+                                         void *out, int32_t M, int32_t N, int32_t K, int32_t epilogue,
+                                         float acc_scale, float out_inv_scale, void *stream) {
+  SPU_REQUIRE(epilogue == SPU_EPI_BIAS || epilogue == SPU_EPI_BIAS_RESID || epilogue == SPU_EPI_BIAS_GELU_E4M3,
+              SPU_ERR_INVALID, "fp8 gemm: unknown epilogue");
+  SPU_REQUIRE(M > 0, SPU_ERR_INVALID, "gemm: empty shape");
+  GemmPlan plan;
+  SPU_TRY(gemm_make_plan(&plan, A, M, W, N, K, epilogue, GemmIn::FP8_E4M3));
+  GemmEpilogueArgs e{};
+  e.bias = bias;
+  e.resid = resid;
+  e.out = out;
+  e.acc_scale = acc_scale;
+  e.out_inv_scale = out_inv_scale;
+  return gemm_launch(plan, M, e, as_stream(stream));
 }
 
 extern "C" spu_status spu_bert_stage_chain_ms(spu_replica *r, int32_t ws_idx, const int64_t *ids,

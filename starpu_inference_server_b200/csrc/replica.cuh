@@ -12,16 +12,26 @@
 
 namespace spu {
 
+// ctx is bf16 [rows, heads*64], or e4m3 of ctx * q_inv_scale when out_e4m3 is set
 spu_status attention_launch(const void *qkv, const float *mask_bias, void *ctx, int batch, int seq,
-                            int heads, cudaStream_t stream);
+                            int heads, cudaStream_t stream, bool out_e4m3 = false,
+                            float q_inv_scale = 1.f);
 spu_status bert_embed_launch(const int64_t *ids, const int64_t *mask, const float *word,
                              const float *pos, const float *type0, const float *gamma,
                              const float *beta, float eps, int vocab, float *x_f32, void *x_bf16,
-                             float *mask_bias, int batch, int seq, int hidden, cudaStream_t stream);
+                             float *mask_bias, int batch, int seq, int hidden, cudaStream_t stream,
+                             void *x_q = nullptr, float q_inv_scale = 1.f);
 // in_row_stride: elements between consecutive input rows (0 = hidden, i.e. contiguous)
 spu_status layernorm_launch(const float *x, const float *gamma, const float *beta, float eps,
                             float *out_f32, void *out_bf16, int rows, int hidden,
-                            cudaStream_t stream, long long in_row_stride = 0);
+                            cudaStream_t stream, long long in_row_stride = 0, void *out_q = nullptr,
+                            float q_inv_scale = 1.f);
+// e4m3 = sat(in * inv_scale); exactly one of in_f32 / in_bf16 is non-null; n % 4 == 0
+spu_status quantize_e4m3_launch(const float *in_f32, const void *in_bf16, void *out, uint64_t n,
+                                float inv_scale, cudaStream_t stream);
+// amax[0] = max(amax[0], max|in|)
+spu_status amax_launch(const float *in_f32, const void *in_bf16, uint64_t n, float *amax,
+                       cudaStream_t stream);
 
 inline uint16_t f32_to_bf16_rne(float f) {
   uint32_t u;
@@ -46,6 +56,11 @@ struct LayerWeights {
   __nv_bfloat16 *w_qkv = nullptr, *w_o = nullptr, *w_1 = nullptr, *w_2 = nullptr;
   float *b_qkv = nullptr, *b_o = nullptr, *b_1 = nullptr, *b_2 = nullptr;
   float *ln1_g = nullptr, *ln1_b = nullptr, *ln2_g = nullptr, *ln2_b = nullptr;
+  // FP8 E4M3 variant: per-tensor scaled weights (value = q * sw) and the calibrated
+  // per-tensor activation scales of the four GEMM inputs of this layer
+  uint8_t *q_qkv = nullptr, *q_o = nullptr, *q_1 = nullptr, *q_2 = nullptr;
+  float sw_qkv = 1.f, sw_o = 1.f, sw_1 = 1.f, sw_2 = 1.f;
+  float sa_x = 1.f, sa_ctx = 1.f, sa_x1 = 1.f, sa_h = 1.f;
 };
 
 struct LayerPlans {
@@ -69,7 +84,9 @@ struct Workspace {
   float *x_f32 = nullptr;
   __nv_bfloat16 *x_bf16 = nullptr, *qkv = nullptr, *ctx = nullptr, *h = nullptr;
   float *mask_bias = nullptr;
+  uint8_t *x_q = nullptr, *ctx_q = nullptr, *h_q = nullptr;  // FP8 variant operands
   std::vector<LayerPlans> plans;
+  std::vector<LayerPlans> plans8;
   std::vector<CapturedGraph> graphs;
 };
 
@@ -87,6 +104,9 @@ struct spu_replica {
   std::vector<spu::LayerWeights> layers;
   std::vector<spu::Workspace> ws;
   std::vector<void *> allocations;
+  float *amax = nullptr;      // [layers * 4] running calibration maxima (FP8 variant)
+  bool fp8_calibrated = false;
+  int fp8_layers = 0;         // leading layers whose GEMMs run in FP8 (rest bf16)
   spu::VitState *vit = nullptr;
   void (*vit_destroy)(spu::VitState *) = nullptr;
 };

@@ -33,12 +33,20 @@ __device__ __forceinline__ RowStats row_stats(const float4 (&v)[kMaxChunksPerLan
   return {mean, rsqrtf(var + eps)};
 }
 
+__device__ __forceinline__ uint32_t pack_e4m3x4(float a, float b, float c, float d) {
+  uint16_t lo, hi;
+  asm("cvt.rn.satfinite.e4m3x2.f32 %0, %1, %2;" : "=h"(lo) : "f"(b), "f"(a));
+  asm("cvt.rn.satfinite.e4m3x2.f32 %0, %1, %2;" : "=h"(hi) : "f"(d), "f"(c));
+  return static_cast<uint32_t>(lo) | (static_cast<uint32_t>(hi) << 16);
+}
+
 __device__ __forceinline__ void row_normalise_store(const float4 (&v)[kMaxChunksPerLane],
                                                     int nchunk_lane, RowStats st,
                                                     const float *__restrict__ gamma,
                                                     const float *__restrict__ beta,
                                                     float *out_f32, __nv_bfloat16 *out_bf16,
-                                                    size_t row_off) {
+                                                    size_t row_off, uint8_t *out_q = nullptr,
+                                                    float q_inv_scale = 1.f) {
   const int lane = threadIdx.x & 31;
 #pragma unroll
   for (int i = 0; i < kMaxChunksPerLane; ++i) {
@@ -55,6 +63,9 @@ __device__ __forceinline__ void row_normalise_store(const float4 (&v)[kMaxChunks
     if (out_bf16 != nullptr)
       reinterpret_cast<uint2 *>(out_bf16 + row_off)[c] =
           make_uint2(pack_bf16(y.x, y.y), pack_bf16(y.z, y.w));
+    if (out_q != nullptr)  // per-tensor scaled FP8 E4M3 operand of the next GEMM
+      reinterpret_cast<uint32_t *>(out_q + row_off)[c] =
+          pack_e4m3x4(y.x * q_inv_scale, y.y * q_inv_scale, y.z * q_inv_scale, y.w * q_inv_scale);
   }
 }
 
@@ -65,7 +76,8 @@ bert_embed_ln_kernel(const int64_t *__restrict__ ids, const int64_t *__restrict_
                      const float *__restrict__ word, const float *__restrict__ pos,
                      const float *__restrict__ type0, const float *__restrict__ gamma,
                      const float *__restrict__ beta, float eps, int vocab, float *x_f32,
-                     __nv_bfloat16 *x_bf16, float *mask_bias, int rows, int seq, int hidden) {
+                     __nv_bfloat16 *x_bf16, float *mask_bias, int rows, int seq, int hidden,
+                     uint8_t *x_q, float q_inv_scale) {
   const int row = blockIdx.x * (kRowThreads / 32) + (threadIdx.x >> 5);
   if (row >= rows) return;
   const int lane = threadIdx.x & 31;
@@ -88,14 +100,15 @@ bert_embed_ln_kernel(const int64_t *__restrict__ ids, const int64_t *__restrict_
   }
   const RowStats st = row_stats(v, nchunk_lane, hidden, eps);
   row_normalise_store(v, nchunk_lane, st, gamma, beta, x_f32, x_bf16,
-                      static_cast<size_t>(row) * hidden);
+                      static_cast<size_t>(row) * hidden, x_q, q_inv_scale);
   if (lane == 0) mask_bias[row] = mask[row] != 0 ? 0.f : -1e30f;
 }
 
 __global__ void __launch_bounds__(kRowThreads)
 layernorm_kernel(const float *__restrict__ x, const float *__restrict__ gamma,
                  const float *__restrict__ beta, float eps, float *out_f32,
-                 __nv_bfloat16 *out_bf16, int rows, int hidden, long long in_row_stride) {
+                 __nv_bfloat16 *out_bf16, int rows, int hidden, long long in_row_stride,
+                 uint8_t *out_q, float q_inv_scale) {
   const int row = blockIdx.x * (kRowThreads / 32) + (threadIdx.x >> 5);
   if (row >= rows) return;
   const int lane = threadIdx.x & 31;
@@ -108,7 +121,40 @@ layernorm_kernel(const float *__restrict__ x, const float *__restrict__ gamma,
   for (int i = 0; i < kMaxChunksPerLane; ++i)
     if (i < nchunk_lane) v[i] = reinterpret_cast<const float4 *>(x + in_off)[lane + i * 32];
   const RowStats st = row_stats(v, nchunk_lane, hidden, eps);
-  row_normalise_store(v, nchunk_lane, st, gamma, beta, out_f32, out_bf16, off);
+  row_normalise_store(v, nchunk_lane, st, gamma, beta, out_f32, out_bf16, off, out_q, q_inv_scale);
+}
+
+// out = sat_e4m3(in * inv_scale): weights at replica creation, stage tests.
+__global__ void __launch_bounds__(256)
+quantize_e4m3_kernel(const float *__restrict__ in_f32, const __nv_bfloat16 *__restrict__ in_bf16,
+                     uint8_t *__restrict__ out, uint64_t n4, float inv_scale) {
+  for (uint64_t k = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x; k < n4;
+       k += static_cast<uint64_t>(gridDim.x) * blockDim.x) {
+    float4 v;
+    if (in_f32 != nullptr) {
+      v = reinterpret_cast<const float4 *>(in_f32)[k];
+    } else {
+      const uint2 u = reinterpret_cast<const uint2 *>(in_bf16)[k];
+      const __nv_bfloat162 a = *reinterpret_cast<const __nv_bfloat162 *>(&u.x);
+      const __nv_bfloat162 b = *reinterpret_cast<const __nv_bfloat162 *>(&u.y);
+      v = make_float4(__low2float(a), __high2float(a), __low2float(b), __high2float(b));
+    }
+    reinterpret_cast<uint32_t *>(out)[k] =
+        pack_e4m3x4(v.x * inv_scale, v.y * inv_scale, v.z * inv_scale, v.w * inv_scale);
+  }
+}
+
+// amax[0] = max(amax[0], max |x|) over a bf16 / fp32 buffer (FP8 calibration).  Values are
+// non-negative floats, so the integer max of their bit patterns is the float max.
+__global__ void __launch_bounds__(256)
+amax_kernel(const float *__restrict__ in_f32, const __nv_bfloat16 *__restrict__ in_bf16, uint64_t n,
+            float *amax) {
+  float m = 0.f;
+  for (uint64_t k = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x; k < n;
+       k += static_cast<uint64_t>(gridDim.x) * blockDim.x)
+    m = fmaxf(m, fabsf(in_f32 != nullptr ? in_f32[k] : __bfloat162float(in_bf16[k])));
+  m = warp_max(m);
+  if ((threadIdx.x & 31) == 0 && m > 0.f) atomicMax(reinterpret_cast<int *>(amax), __float_as_int(m));
 }
 
 // Ragged gather + pad + mask: one CTA row per request, 8-byte words, coalesced.
@@ -179,7 +225,7 @@ spu_status bert_embed_launch(const int64_t *ids, const int64_t *mask, const floa
                              const float *pos, const float *type0, const float *gamma,
                              const float *beta, float eps, int vocab, float *x_f32, void *x_bf16,
                              float *mask_bias, int batch, int seq, int hidden,
-                             cudaStream_t stream) {
+                             cudaStream_t stream, void *x_q, float q_inv_scale) {
   SPU_REQUIRE(ids && mask && word && pos && type0 && gamma && beta && mask_bias, SPU_ERR_INVALID,
               "embed: null argument");
   SPU_REQUIRE(hidden % 4 == 0 && hidden <= 128 * kMaxChunksPerLane, SPU_ERR_UNSUPPORTED,
@@ -189,14 +235,16 @@ spu_status bert_embed_launch(const int64_t *ids, const int64_t *mask, const floa
   const int grid = (rows + kRowThreads / 32 - 1) / (kRowThreads / 32);
   bert_embed_ln_kernel<<<grid, kRowThreads, 0, stream>>>(
       ids, mask, word, pos, type0, gamma, beta, eps, vocab, x_f32,
-      static_cast<__nv_bfloat16 *>(x_bf16), mask_bias, rows, seq, hidden);
+      static_cast<__nv_bfloat16 *>(x_bf16), mask_bias, rows, seq, hidden, static_cast<uint8_t *>(x_q),
+      q_inv_scale);
   SPU_CUDA_TRY(cudaGetLastError());
   return SPU_OK;
 }
 
 spu_status layernorm_launch(const float *x, const float *gamma, const float *beta, float eps,
                             float *out_f32, void *out_bf16, int rows, int hidden,
-                            cudaStream_t stream, long long in_row_stride) {
+                            cudaStream_t stream, long long in_row_stride, void *out_q,
+                            float q_inv_scale) {
   SPU_REQUIRE(x && gamma && beta, SPU_ERR_INVALID, "layernorm: null argument");
   if (in_row_stride == 0) in_row_stride = hidden;
   SPU_REQUIRE(in_row_stride % 4 == 0, SPU_ERR_INVALID, "layernorm: row stride must keep 16-byte alignment");
@@ -206,7 +254,34 @@ spu_status layernorm_launch(const float *x, const float *gamma, const float *bet
   const int grid = (rows + kRowThreads / 32 - 1) / (kRowThreads / 32);
   layernorm_kernel<<<grid, kRowThreads, 0, stream>>>(x, gamma, beta, eps, out_f32,
                                                      static_cast<__nv_bfloat16 *>(out_bf16), rows,
-                                                     hidden, in_row_stride);
+                                                     hidden, in_row_stride,
+                                                     static_cast<uint8_t *>(out_q), q_inv_scale);
+  SPU_CUDA_TRY(cudaGetLastError());
+  return SPU_OK;
+}
+
+spu_status quantize_e4m3_launch(const float *in_f32, const void *in_bf16, void *out, uint64_t n,
+                                float inv_scale, cudaStream_t stream) {
+  SPU_REQUIRE((in_f32 != nullptr) != (in_bf16 != nullptr) && out != nullptr, SPU_ERR_INVALID,
+              "quantize: exactly one input and an output are required");
+  SPU_REQUIRE(n % 4 == 0, SPU_ERR_INVALID, "quantize: element count must be a multiple of 4");
+  if (n == 0) return SPU_OK;
+  const uint64_t blocks = (n / 4 + 255) / 256;
+  const int grid = static_cast<int>(blocks > 148ull * 8 ? 148ull * 8 : blocks);
+  quantize_e4m3_kernel<<<grid, 256, 0, stream>>>(in_f32, static_cast<const __nv_bfloat16 *>(in_bf16),
+                                                 static_cast<uint8_t *>(out), n / 4, inv_scale);
+  SPU_CUDA_TRY(cudaGetLastError());
+  return SPU_OK;
+}
+
+spu_status amax_launch(const float *in_f32, const void *in_bf16, uint64_t n, float *amax,
+                       cudaStream_t stream) {
+  SPU_REQUIRE((in_f32 != nullptr) != (in_bf16 != nullptr) && amax != nullptr, SPU_ERR_INVALID,
+              "amax: exactly one input and an output are required");
+  if (n == 0) return SPU_OK;
+  const uint64_t blocks = (n + 255) / 256;
+  const int grid = static_cast<int>(blocks > 148ull * 4 ? 148ull * 4 : blocks);
+  amax_kernel<<<grid, 256, 0, stream>>>(in_f32, static_cast<const __nv_bfloat16 *>(in_bf16), n, amax);
   SPU_CUDA_TRY(cudaGetLastError());
   return SPU_OK;
 }
@@ -270,7 +345,8 @@ extern "C" spu_status spu_affine_f32_async(const float *in, float *out, uint64_t
 extern "C" spu_status spu_layernorm_async(const float *x, const float *gamma, const float *beta,
                                           float eps, float *out_f32, void *out_bf16, int32_t rows,
                                           int32_t hidden, void *stream) {
-  return layernorm_launch(x, gamma, beta, eps, out_f32, out_bf16, rows, hidden, as_stream(stream), 0);
+  return layernorm_launch(x, gamma, beta, eps, out_f32, out_bf16, rows, hidden, as_stream(stream), 0, nullptr,
+                          1.f);
 }
 
 extern "C" spu_status spu_bert_embed_async(const int64_t *ids, const int64_t *mask,
@@ -281,5 +357,10 @@ extern "C" spu_status spu_bert_embed_async(const int64_t *ids, const int64_t *ma
                                            int32_t batch, int32_t seq, int32_t hidden,
                                            void *stream) {
   return bert_embed_launch(ids, mask, word, pos, type0, gamma, beta, eps, vocab, x_f32, x_bf16,
-                           mask_bias, batch, seq, hidden, as_stream(stream));
+                           mask_bias, batch, seq, hidden, as_stream(stream), nullptr, 1.f);
+}
+
+extern "C" spu_status spu_quantize_e4m3_async(const float *in_f32, void *out, uint64_t n, float inv_scale,
+                                              void *stream) {
+  return quantize_e4m3_launch(in_f32, nullptr, out, n, inv_scale, as_stream(stream));
 }
