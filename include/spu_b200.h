@@ -277,6 +277,10 @@ spu_status spu_bert_embed_async(const int64_t *ids, const int64_t *mask,
 spu_status spu_affine_f32_async(const float *in, float *out, uint64_t n,
                                 float scale, float shift, void *stream);
 
+/* Debug (tools/gemm_trace.py): CTA `cta` of every following GEMM launch writes 65 u64
+ * %globaltimer stamps of its pipeline to device_buf; NULL switches it off.  Not thread-safe. */
+void spu_debug_gemm_trace(void *device_buf, int32_t cta);
+
 /* ---- Misc ------------------------------------------------------------------ */
 const char *spu_last_error(void);       /* thread-local message of the last failure */
 int32_t spu_abi_version(void);

@@ -45,7 +45,8 @@ constexpr int kMaxStages = 8;
 template <int EPI>
 struct EpiTraits {
   // bytes of one staged 32x32 output chunk
-  static constexpr int kElemBytes = EPI == kEpiBiasResid ? 4 : (EPI == kEpiBiasGeluE4m3 ? 1 : 2);
+  static constexpr int kElemBytes =
+      (EPI == kEpiBiasResid || EPI == kEpiBiasAccum) ? 4 : (EPI == kEpiBiasGeluE4m3 ? 1 : 2);
   static constexpr int kChunkBytes = 32 * 32 * kElemBytes;
   static constexpr int kWarpBytes = 2 * kChunkBytes;  // double-buffered per warp
 };
@@ -73,6 +74,13 @@ struct KernelArgs {
   const float *bias;
   float acc_scale;
   float out_inv_scale;
+  // Debug trace (tools/gemm_trace.py): when non-null, CTA `trace_cta` writes %globaltimer
+  // stamps: [0] kernel entry, [1] after griddepcontrol.wait (MMA thread), [2+kb] full
+  // barrier of k-block kb of its first tile observed by the MMA thread (kb < 60),
+  // [62] accumulator of the first tile ready (epilogue warp 4), [63] that warp's last store
+  // of the first tile issued, [64] kernel exit.
+  unsigned long long *trace;
+  int trace_cta;
 };
 
 __device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c,
@@ -132,6 +140,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
   const int num_tiles = n_blocks * m_blocks;
   const int num_k_blocks = args.K / kElemsPerKBlock;
 
+  const bool tracing = args.trace != nullptr && static_cast<int>(blockIdx.x) == args.trace_cta;
+  if (tracing && threadIdx.x == 0) args.trace[0] = global_timer_ns();
   if (warp_idx == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_a);
     tma_prefetch_desc(&tmap_b);
@@ -230,6 +240,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
   } else if (warp_idx == 1) {
     // ===================== MMA issuer (leader CTA) =====================
     pdl_wait_prior_grid();
+    if (tracing && lane == 0) args.trace[1] = global_timer_ns();
     if (lane == 0 && cta_rank == 0) {
       int stage = 0;
       uint32_t phase = 0;
@@ -243,6 +254,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
         for (int kb = 0; kb < num_k_blocks; ++kb) {
           mbar_wait(&full_bar[stage], phase);
           tcgen05_fence_after();
+          if (tracing && local_tile == 0 && kb < 60) args.trace[2 + kb] = global_timer_ns();
           const uint32_t sa = smem_u32(smem + stage * kStageBytes);
           const uint64_t desc_a = make_sw128_kmajor_desc(sa);
           const uint64_t desc_b = make_sw128_kmajor_desc(sa + kABytes);
@@ -291,6 +303,20 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
       const int row0 = m_blk * kTileM + static_cast<int>(cta_rank) * kRowsPerCta + q * 32;
       const int colw = n_blk * BLOCK_N + half * (BLOCK_N / 2);  // first column of this warp
       const bool slab_live = row0 < args.M;  // TMA clips partial slabs; dead ones are skipped
+      // bias of chunk 0 -> registers while the main loop still runs; every later chunk's
+      // bias is fetched one chunk ahead (warp-uniform addresses: one broadcast per load)
+      float4 bv[8];
+      auto load_bias = [&](float4 (&dst)[8], int col) {
+        if (args.bias != nullptr) {
+          const float4 *b4 = reinterpret_cast<const float4 *>(args.bias + col);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) dst[j] = __ldg(b4 + j);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) dst[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+      };
+      load_bias(bv, colw);
       if constexpr (EPI == kEpiBiasResid) {
         // Residual chunks 0 and 1 of this tile: fetched while the main loop still runs.
         if (lane == 0 && slab_live) {
@@ -307,6 +333,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
       }
       mbar_wait(&tmem_full_bar[acc], acc_phase);
       tcgen05_fence_after();
+      if (tracing && local_tile == 0 && e == 0 && lane == 0) args.trace[62] = global_timer_ns();
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) +
                              static_cast<uint32_t>(acc * BLOCK_N + half * (BLOCK_N / 2));
 #pragma unroll 1
@@ -316,21 +343,18 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
         const uint32_t sbuf = stg + b * Epi::kChunkBytes;
         uint32_t v[32];
         tmem_ld_32x32b_x32(taddr + static_cast<uint32_t>(c * 32), v);
-        float4 bv[8];
-        if (args.bias != nullptr) {
-          const float4 *b4 = reinterpret_cast<const float4 *>(args.bias + col0);
-#pragma unroll
-          for (int j = 0; j < 8; ++j) bv[j] = __ldg(b4 + j);
-        } else {
-#pragma unroll
-          for (int j = 0; j < 8; ++j) bv[j] = make_float4(0.f, 0.f, 0.f, 0.f);
-        }
+        float4 bn[8];
+        if (c + 1 < kChunksPerWarp) load_bias(bn, col0 + 32);
+        const bool tr_chunk = tracing && local_tile == 0 && e == 0 && lane == 0 && c < 8;
+        if (tr_chunk) args.trace[66 + 4 * c] = global_timer_ns();
         if constexpr (EPI != kEpiBiasResid) {
           // the store issued from this slot two chunks ago must have drained it
           if (lane == 0) tma_store_wait_read<1>();
           __syncwarp();
         }
+        if (tr_chunk) args.trace[67 + 4 * c] = global_timer_ns();
         tmem_ld_wait();
+        if (tr_chunk) args.trace[68 + 4 * c] = global_timer_ns();
         if (c == kChunksPerWarp - 1) {
           // accumulator fully read: hand the TMEM buffer back to the MMA issuer
           tcgen05_fence_before();
@@ -340,7 +364,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
             else mbar_arrive(&tmem_empty_bar[acc]);
           }
         }
-        if (!slab_live) continue;
+        if (!slab_live) continue;  // dead slab: bias registers are never consumed
         float f[32];
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
@@ -363,6 +387,15 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
             const float4 r = ld_shared_f4(a);
             st_shared_v4(a, __float_as_uint(f[4 * j] + r.x), __float_as_uint(f[4 * j + 1] + r.y),
                          __float_as_uint(f[4 * j + 2] + r.z), __float_as_uint(f[4 * j + 3] + r.w));
+          }
+        } else if constexpr (EPI == kEpiBiasAccum) {
+          // 32 rows x 128 B, SWIZZLE_128B; added to the output in place by the TMA reduce below
+          const uint32_t rowa = sbuf + static_cast<uint32_t>(lane) * 128u;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const uint32_t a = rowa + (static_cast<uint32_t>(j ^ (lane & 7)) << 4);
+            st_shared_v4(a, __float_as_uint(f[4 * j]), __float_as_uint(f[4 * j + 1]), __float_as_uint(f[4 * j + 2]),
+                         __float_as_uint(f[4 * j + 3]));
           }
         } else if constexpr (EPI == kEpiBiasGeluE4m3) {
           // 32 rows x 32 B, no swizzle
@@ -390,8 +423,12 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
         }
         fence_proxy_async_smem();  // generic-proxy smem writes -> visible to the TMA engine
         __syncwarp();
+        if (tr_chunk) args.trace[69 + 4 * c] = global_timer_ns();
         if (lane == 0) {
-          tma_store_2d(&tmap_out, staging + e * Epi::kWarpBytes + b * Epi::kChunkBytes, col0, row0);
+          if constexpr (EPI == kEpiBiasAccum)
+            tma_reduce_add_2d(&tmap_out, staging + e * Epi::kWarpBytes + b * Epi::kChunkBytes, col0, row0);
+          else
+            tma_store_2d(&tmap_out, staging + e * Epi::kWarpBytes + b * Epi::kChunkBytes, col0, row0);
           tma_store_commit();
           if constexpr (EPI == kEpiBiasResid) {
             if (c + 2 < kChunksPerWarp) {
@@ -404,8 +441,13 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
           }
         }
         __syncwarp();
+        if (c + 1 < kChunksPerWarp) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) bv[j] = bn[j];
+        }
         ++chunk_ctr;  // counts live chunks only: slot = ctr & 1, residual-barrier parity = ctr >> 1
       }
+      if (tracing && local_tile == 0 && e == 0 && lane == 0) args.trace[63] = global_timer_ns();
     }
     if (lane == 0) tma_store_wait<0>();  // all bulk stores of this warp are complete
     __syncwarp();
@@ -413,6 +455,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
 
   tcgen05_fence_before();
   if constexpr (CG == 2) cluster_sync_all(); else __syncthreads();
+  if (tracing && threadIdx.x == 0) args.trace[64] = global_timer_ns();
   if (warp_idx == 2) {
     tcgen05_fence_after();
     if constexpr (CG == 2) tmem_dealloc_pair(tmem_base, Cfg::kTmemCols);
@@ -473,6 +516,7 @@ spu_status make_kmajor_tmap(CUtensorMap *map, const void *base, int rows, int k_
 spu_status make_out_tmap(CUtensorMap *map, const void *base, int rows, int cols, int epilogue) {
   switch (epilogue) {
     case kEpiBiasResid:
+    case kEpiBiasAccum:
       return make_tmap_2d(map, base, rows, cols, 4, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 32, 32,
                           CU_TENSOR_MAP_SWIZZLE_128B);
     case kEpiBiasGeluE4m3:
@@ -532,11 +576,13 @@ spu_status launch_cfg(const GemmPlan &plan, const LaunchMaps &maps, const Kernel
 
 template <int BLOCK_N, int CG>
 spu_status launch_epi(const GemmPlan &plan, const LaunchMaps &maps, const KernelArgs &a,
-                      cudaStream_t stream) {
+                      cudaStream_t stream, bool inplace) {
   if (plan.in == GemmIn::FP8_E4M3) {
     switch (plan.epilogue) {
       case kEpiBias: return launch_cfg<BLOCK_N, CG, kEpiBias, 1>(plan, maps, a, stream);
-      case kEpiBiasResid: return launch_cfg<BLOCK_N, CG, kEpiBiasResid, 1>(plan, maps, a, stream);
+      case kEpiBiasResid:
+        return inplace ? launch_cfg<BLOCK_N, CG, kEpiBiasAccum, 1>(plan, maps, a, stream)
+                       : launch_cfg<BLOCK_N, CG, kEpiBiasResid, 1>(plan, maps, a, stream);
       case kEpiBiasGeluE4m3: return launch_cfg<BLOCK_N, CG, kEpiBiasGeluE4m3, 1>(plan, maps, a, stream);
       default: set_error("fp8 gemm: unsupported epilogue"); return SPU_ERR_INVALID;
     }
@@ -544,26 +590,36 @@ spu_status launch_epi(const GemmPlan &plan, const LaunchMaps &maps, const Kernel
   switch (plan.epilogue) {
     case kEpiBias: return launch_cfg<BLOCK_N, CG, kEpiBias, 0>(plan, maps, a, stream);
     case kEpiBiasGelu: return launch_cfg<BLOCK_N, CG, kEpiBiasGelu, 0>(plan, maps, a, stream);
-    case kEpiBiasResid: return launch_cfg<BLOCK_N, CG, kEpiBiasResid, 0>(plan, maps, a, stream);
+    case kEpiBiasResid:
+      return inplace ? launch_cfg<BLOCK_N, CG, kEpiBiasAccum, 0>(plan, maps, a, stream)
+                     : launch_cfg<BLOCK_N, CG, kEpiBiasResid, 0>(plan, maps, a, stream);
     default: set_error("bf16 gemm: unsupported epilogue"); return SPU_ERR_INVALID;
   }
 }
 
 template <int CG>
 spu_status launch_bn(const GemmPlan &plan, int block_n, const LaunchMaps &maps, const KernelArgs &a,
-                     cudaStream_t stream) {
+                     cudaStream_t stream, bool inplace) {
   switch (block_n) {
-    case 64: return launch_epi<64, CG>(plan, maps, a, stream);
-    case 128: return launch_epi<128, CG>(plan, maps, a, stream);
-    case 192: return launch_epi<192, CG>(plan, maps, a, stream);
-    case 256: return launch_epi<256, CG>(plan, maps, a, stream);
+    case 64: return launch_epi<64, CG>(plan, maps, a, stream, inplace);
+    case 128: return launch_epi<128, CG>(plan, maps, a, stream, inplace);
+    case 192: return launch_epi<192, CG>(plan, maps, a, stream, inplace);
+    case 256: return launch_epi<256, CG>(plan, maps, a, stream, inplace);
     default: set_error("unsupported BLOCK_N"); return SPU_ERR_INVALID;
   }
 }
 
 constexpr int kBlockNCands[4] = {256, 192, 128, 64};
 
+unsigned long long *g_trace_buf = nullptr;  // debug only, see KernelArgs::trace
+int g_trace_cta = 0;
+
 }  // namespace
+
+void gemm_set_trace(unsigned long long *device_buf, int cta) {
+  g_trace_buf = device_buf;
+  g_trace_cta = cta;
+}
 
 GemmConfig choose_config(int M, int N, int K, int esize) {
   GemmConfig best{0, 0};
@@ -669,9 +725,11 @@ spu_status gemm_launch(const GemmPlan &plan, int M, const GemmEpilogueArgs &args
   } else {
     maps.resid = maps.out;
   }
-  KernelArgs a{M, plan.N, plan.K, args.bias, args.acc_scale, args.out_inv_scale};
-  return cfg.cta_group == 2 ? launch_bn<2>(plan, cfg.block_n, maps, a, stream)
-                            : launch_bn<1>(plan, cfg.block_n, maps, a, stream);
+  KernelArgs a{M, plan.N, plan.K, args.bias, args.acc_scale, args.out_inv_scale, g_trace_buf, g_trace_cta};
+  // residual == output: accumulate in place with a TMA reduce-add instead of load + add + store
+  const bool inplace = plan.epilogue == kEpiBiasResid && args.resid == args.out;
+  return cfg.cta_group == 2 ? launch_bn<2>(plan, cfg.block_n, maps, a, stream, inplace)
+                            : launch_bn<1>(plan, cfg.block_n, maps, a, stream, inplace);
 }
 
 }  // namespace spu

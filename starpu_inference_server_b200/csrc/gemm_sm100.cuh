@@ -15,7 +15,8 @@ enum class GemmIn : int { BF16 = 0, FP8_E4M3 = 1 };
 constexpr int kEpiBias = SPU_EPI_BIAS;             // bf16 out
 constexpr int kEpiBiasGelu = SPU_EPI_BIAS_GELU;    // bf16 out
 constexpr int kEpiBiasResid = SPU_EPI_BIAS_RESID;  // fp32 out = acc + bias + fp32 residual
-constexpr int kEpiBiasGeluE4m3 = 3;                // e4m3 out = gelu(acc*s + bias) * out_scale_inv
+constexpr int kEpiBiasGeluE4m3 = 3;
+constexpr int kEpiBiasAccum = 4;  // fp32 out += acc*s + bias by TMA reduce-add: BIAS_RESID when resid == out                // e4m3 out = gelu(acc*s + bias) * out_scale_inv
 
 struct GemmEpilogueArgs {
   const float *bias;    // [N] fp32 (may be null)
@@ -56,5 +57,9 @@ spu_status gemm_make_plan(GemmPlan *plan, const void *A, int rows_a, const void 
 // Enqueue.  Only (M, epilogue pointers) may change between calls with one plan.
 spu_status gemm_launch(const GemmPlan &plan, int M, const GemmEpilogueArgs &args,
                        cudaStream_t stream);
+
+// Debug: have CTA `cta` of every following launch write its pipeline time stamps (65 x u64,
+// %globaltimer ns) to device_buf; nullptr switches tracing off.  Not thread-safe, tools only.
+void gemm_set_trace(unsigned long long *device_buf, int cta);
 
 }  // namespace spu

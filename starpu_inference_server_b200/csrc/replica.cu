@@ -577,6 +577,10 @@ extern "C" spu_status spu_attention_async(const void *qkv, const float *mask_bia
   return attention_launch(qkv, mask_bias, ctx, batch, seq, heads, as_stream(stream));
 }
 
+extern "C" void spu_debug_gemm_trace(void *device_buf, int32_t cta) {
+  gemm_set_trace(static_cast<unsigned long long *>(device_buf), cta);
+}
+
 extern "C" const char *spu_last_error(void) { return g_last_error.c_str(); }
 extern "C" int32_t spu_abi_version(void) { return SPU_ABI_VERSION; }
 

@@ -16,11 +16,18 @@ def main():
     B = int(sys.argv[1]) if len(sys.argv) > 1 else 32
     S = int(sys.argv[2]) if len(sys.argv) > 2 else 128
     spec = BertConfig()
-    rep = BertReplica(synthetic.make_weights(spec, 0), max_batch=B, max_seq=S)
+    fp8 = len(sys.argv) > 3 and sys.argv[3].startswith("fp8")
+    flags = 0
+    if fp8:
+        n8 = int(sys.argv[3][3:] or 0)
+        flags = capi.SPU_PREC_FP8_E4M3 | (n8 << 8)
+    rep = BertReplica(synthetic.make_weights(spec, 0), max_batch=B, max_seq=S, flags=flags)
     ids, mask = synthetic.make_requests(spec, B, S, seed=1)
     ids, mask = torch.from_numpy(ids).cuda(), torch.from_numpy(mask).cuda()
+    if fp8:
+        rep.calibrate_fp8(ids[:32].contiguous(), mask[:32].contiguous())
     out = torch.empty(B, S, spec.hidden, device="cuda")
-    res = {"B": B, "S": S}
+    res = {"B": B, "S": S, "prec": sys.argv[3] if fp8 else "bf16"}
     st = torch.cuda.Stream()
     for name in capi.STAGE_NAMES:
         res[name] = min(rep.stage_chain_ms(ids, mask, out, [name], stream=st) for _ in range(3))
