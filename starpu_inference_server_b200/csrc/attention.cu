@@ -88,6 +88,8 @@ attention_kernel(const __nv_bfloat16 *__restrict__ qkv, const float *__restrict_
   __shared__ __align__(128) uint8_t s_v[2][kKTile * 128];
   __shared__ float s_bias[2][kKTile];
 
+  pdl_wait_prior_grid();
+  pdl_launch_dependents();
   const int qt = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
   const int hidden = heads * kHeadDim;
   const int ld = 3 * hidden;
@@ -275,12 +277,13 @@ spu_status attention_launch(const void *qkv, const float *mask_bias, void *ctx, 
   SPU_REQUIRE(batch > 0 && seq > 0 && heads > 0, SPU_ERR_INVALID, "attention: empty shape");
   SPU_REQUIRE(batch <= 65535 && heads <= 65535, SPU_ERR_CAPACITY, "attention: grid too large");
   dim3 grid((seq + kQTile - 1) / kQTile, heads, batch);
+  const __nv_bfloat16 *q16 = static_cast<const __nv_bfloat16 *>(qkv);
   if (out_e4m3)
-    attention_kernel<true><<<grid, kThreads, 0, stream>>>(static_cast<const __nv_bfloat16 *>(qkv), mask_bias, ctx,
-                                                          seq, heads, q_inv_scale);
+    SPU_CUDA_TRY(launch_pdl(attention_kernel<true>, grid, dim3(kThreads), 0, stream, q16, mask_bias, ctx, seq, heads,
+                            q_inv_scale));
   else
-    attention_kernel<false><<<grid, kThreads, 0, stream>>>(static_cast<const __nv_bfloat16 *>(qkv), mask_bias, ctx,
-                                                           seq, heads, 1.f);
+    SPU_CUDA_TRY(launch_pdl(attention_kernel<false>, grid, dim3(kThreads), 0, stream, q16, mask_bias, ctx, seq, heads,
+                            1.f));
   SPU_CUDA_TRY(cudaGetLastError());
   return SPU_OK;
 }

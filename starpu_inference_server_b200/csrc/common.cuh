@@ -5,6 +5,7 @@
 #include <stdint.h>
 
 #include <cstdio>
+#include <cstdlib>
 #include <string>
 
 #include "../../include/spu_b200.h"
@@ -34,6 +35,30 @@ void set_error(const std::string &msg);
 static inline cudaStream_t as_stream(void *s) { return reinterpret_cast<cudaStream_t>(s); }
 
 constexpr int kNumSMsB200 = 148;
+
+#ifdef __CUDACC__
+// Launch helper for the row / attention kernels.  With SPU_ROW_PDL=1 they are launched with
+// programmatic stream serialisation (they execute griddepcontrol.wait first thing, so that is
+// safe); measured on B200 it LOSES 1-3 % at every batch size (profiles/r04_pdl_row_kernels.md:
+// early-resident secondaries take registers from the multi-wave primaries), so the default
+// is a plain launch and only the GEMMs use PDL.
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                              Args... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  static const bool on = std::getenv("SPU_ROW_PDL") != nullptr;  // experiments only
+  cfg.numAttrs = on ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+#endif
 
 #ifdef __CUDACC__
 // ---- small device utilities ---------------------------------------------------

@@ -78,6 +78,8 @@ bert_embed_ln_kernel(const int64_t *__restrict__ ids, const int64_t *__restrict_
                      const float *__restrict__ beta, float eps, int vocab, float *x_f32,
                      __nv_bfloat16 *x_bf16, float *mask_bias, int rows, int seq, int hidden,
                      uint8_t *x_q, float q_inv_scale) {
+  pdl_wait_prior_grid();
+  pdl_launch_dependents();
   const int row = blockIdx.x * (kRowThreads / 32) + (threadIdx.x >> 5);
   if (row >= rows) return;
   const int lane = threadIdx.x & 31;
@@ -109,6 +111,8 @@ layernorm_kernel(const float *__restrict__ x, const float *__restrict__ gamma,
                  const float *__restrict__ beta, float eps, float *out_f32,
                  __nv_bfloat16 *out_bf16, int rows, int hidden, long long in_row_stride,
                  uint8_t *out_q, float q_inv_scale) {
+  pdl_wait_prior_grid();
+  pdl_launch_dependents();
   const int row = blockIdx.x * (kRowThreads / 32) + (threadIdx.x >> 5);
   if (row >= rows) return;
   const int lane = threadIdx.x & 31;
@@ -233,11 +237,9 @@ spu_status bert_embed_launch(const int64_t *ids, const int64_t *mask, const floa
   const int rows = batch * seq;
   SPU_REQUIRE(rows > 0, SPU_ERR_INVALID, "embed: empty batch");
   const int grid = (rows + kRowThreads / 32 - 1) / (kRowThreads / 32);
-  bert_embed_ln_kernel<<<grid, kRowThreads, 0, stream>>>(
-      ids, mask, word, pos, type0, gamma, beta, eps, vocab, x_f32,
-      static_cast<__nv_bfloat16 *>(x_bf16), mask_bias, rows, seq, hidden, static_cast<uint8_t *>(x_q),
-      q_inv_scale);
-  SPU_CUDA_TRY(cudaGetLastError());
+  SPU_CUDA_TRY(launch_pdl(bert_embed_ln_kernel, dim3(grid), dim3(kRowThreads), 0, stream, ids, mask, word, pos,
+                          type0, gamma, beta, eps, vocab, x_f32, static_cast<__nv_bfloat16 *>(x_bf16), mask_bias,
+                          rows, seq, hidden, static_cast<uint8_t *>(x_q), q_inv_scale));
   return SPU_OK;
 }
 
@@ -252,11 +254,9 @@ spu_status layernorm_launch(const float *x, const float *gamma, const float *bet
               "layernorm: hidden must be a multiple of 4 and <= 1024");
   SPU_REQUIRE(rows > 0, SPU_ERR_INVALID, "layernorm: empty input");
   const int grid = (rows + kRowThreads / 32 - 1) / (kRowThreads / 32);
-  layernorm_kernel<<<grid, kRowThreads, 0, stream>>>(x, gamma, beta, eps, out_f32,
-                                                     static_cast<__nv_bfloat16 *>(out_bf16), rows,
-                                                     hidden, in_row_stride,
-                                                     static_cast<uint8_t *>(out_q), q_inv_scale);
-  SPU_CUDA_TRY(cudaGetLastError());
+  SPU_CUDA_TRY(launch_pdl(layernorm_kernel, dim3(grid), dim3(kRowThreads), 0, stream, x, gamma, beta, eps, out_f32,
+                          static_cast<__nv_bfloat16 *>(out_bf16), rows, hidden, in_row_stride,
+                          static_cast<uint8_t *>(out_q), q_inv_scale));
   return SPU_OK;
 }
 

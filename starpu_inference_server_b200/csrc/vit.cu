@@ -77,6 +77,8 @@ vit_assemble_ln_kernel(const float *__restrict__ patch_out, const float *__restr
                        const float *__restrict__ gamma, const float *__restrict__ beta, float eps,
                        float *__restrict__ x_f32, __nv_bfloat16 *__restrict__ y_bf16, int rows, int seq,
                        int hidden) {
+  pdl_wait_prior_grid();
+  pdl_launch_dependents();
   const int row = blockIdx.x * (kRowThreads / 32) + (threadIdx.x >> 5);
   if (row >= rows) return;
   const int lane = threadIdx.x & 31;
@@ -229,10 +231,9 @@ spu_status vit_enqueue(spu_replica *r, VitState *v, VitWorkspace &ws, const floa
   SPU_TRY(gemm_launch(ws.patch_plan, MP, e, stream));
   {
     const int grid = (M + kRowThreads / 32 - 1) / (kRowThreads / 32);
-    vit_assemble_ln_kernel<<<grid, kRowThreads, 0, stream>>>(ws.patch_out, v->cls_pos0, v->layers[0].ln1_g,
-                                                              v->layers[0].ln1_b, d.ln_eps, ws.x_f32, ws.y_bf16, M, S,
-                                                              d.hidden);
-    SPU_CUDA_TRY(cudaGetLastError());
+    SPU_CUDA_TRY(launch_pdl(vit_assemble_ln_kernel, dim3(grid), dim3(kRowThreads), 0, stream, ws.patch_out,
+                            v->cls_pos0, v->layers[0].ln1_g, v->layers[0].ln1_b, d.ln_eps, ws.x_f32, ws.y_bf16, M, S,
+                            d.hidden));
   }
   for (int l = 0; l < d.layers; ++l) {
     const LayerWeights &w = v->layers[l];
