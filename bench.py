@@ -164,6 +164,24 @@ def run_reference(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
+def reduce_max_over_ranks(values, device):
+    """Slowest rank's time for each entry (the contract's max-over-ranks); identity at N=1.
+    Ranks are independent replicas: this all-reduce of a few scalars is the only collective
+    of the whole benchmark and it is outside every timed region."""
+    import torch.distributed as dist
+
+    t = torch.tensor(list(values), device=device, dtype=torch.float64)
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return [float(v) for v in t]
+
+
+def whole_job_rate(units_per_rank_step, steps, world, slowest_ms):
+    """Weak scaling: every rank processes its own `units_per_rank_step` x steps; the job's
+    throughput is all ranks' units over the slowest rank's time."""
+    return world * units_per_rank_step * steps / (slowest_ms / 1e3)
+
+
 # ---------------------------------------------------------------------- B200 arm
 def run_b200(args, rank, local_rank, world):
     import torch.distributed as dist
@@ -181,16 +199,25 @@ def run_b200(args, rank, local_rank, world):
 
     spec = BertConfig()
     B, S = args.batch, args.seq
-    n_pipe = 4  # workspaces / streams in flight, like STARPU_CUDA_PIPELINE=4 (models/bert.yml:6-8)
+    n_pipe = 4  # workspaces / CUDA workers, like STARPU_NWORKER_PER_CUDA=4 (models/bert.yml:6-8)
+    flags = {"bf16": capi.SPU_PREC_BF16, "fp8": capi.SPU_PREC_FP8_E4M3,
+             "fp8x6": capi.SPU_PREC_FP8_E4M3 | (6 << 8)}[args.precision]
     w = synthetic.make_weights(spec, 0)
-    rep = BertReplica(w, device=local_rank, max_batch=B, max_seq=S, n_workspaces=n_pipe)
+    rep = BertReplica(w, device=local_rank, max_batch=B, max_seq=S, n_workspaces=n_pipe, flags=flags)
     del w
     n_sets = 4
-    host = make_batches(spec, B, S, n_sets, seed0=1234 + 100 * rank)
+    from starpu_inference_server_b200 import synthetic as syn
+
+    host = [syn.make_requests(spec, B, S, seed=1234 + 100 * rank + i, min_len=args.min_len) for i in range(n_sets)]
+    true_tokens = float(np.mean([m.sum() for _, m in host]))  # FLOPs are charged on unpadded tokens
     ids_d = [torch.from_numpy(i).to(dev) for i, _ in host]
     mask_d = [torch.from_numpy(m).to(dev) for _, m in host]
     out_d = [torch.empty(B, S, spec.hidden, device=dev) for _ in range(n_pipe)]
     stream = torch.cuda.Stream(device=dev)
+    if flags & capi.SPU_PREC_FP8_E4M3:
+        # per-tensor activation scales from a 32-sequence calibration draw
+        ci, cm = syn.make_requests(spec, min(32, B), S, seed=999, min_len=args.min_len)
+        rep.calibrate_fp8(torch.from_numpy(ci).to(dev), torch.from_numpy(cm).to(dev), stream=stream)
 
     def barrier():
         if world > 1:
@@ -198,26 +225,35 @@ def run_b200(args, rank, local_rank, world):
         torch.cuda.synchronize(dev)
 
     # ---------------- device-resident throughput (value) ----------------
-    # warm-up hook (src/core/warmup.cpp:225-299): one CUDA graph per (input set) pointer tuple
-    with torch.cuda.stream(stream):
-        for i in range(n_sets):
-            rep.capture(ids_d[i], mask_d[i], out_d[0], ws=0, stream=stream)
+    # warm-up hook (src/core/warmup.cpp:225-299): one CUDA graph per (worker, input set)
+    # pointer tuple; `--streams` workers issue tasks round-robin like StarPU's CUDA workers
+    n_str = max(1, min(args.streams, n_pipe))
+    wstreams = [stream] + [torch.cuda.Stream(device=dev) for _ in range(n_str - 1)]
+    for k, st in enumerate(wstreams):
+        with torch.cuda.stream(st):
+            for i in range(n_sets):
+                rep.capture(ids_d[i], mask_d[i], out_d[k], ws=k, stream=st)
+    torch.cuda.synchronize(dev)
 
-    def step_resident(i):
-        rep.forward_async(ids_d[i % n_sets], mask_d[i % n_sets], out_d[0], ws=0, stream=stream)
+    def step_resident(i, k=0):
+        rep.forward_async(ids_d[i % n_sets], mask_d[i % n_sets], out_d[k], ws=k, stream=wstreams[k])
 
-    with torch.cuda.stream(stream):
-        for i in range(args.warmup):
-            step_resident(i)
+    for i in range(args.warmup):
+        step_resident(i, i % n_str)
     barrier()
     sampler = ClockSampler(local_rank)
     sampler.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    with torch.cuda.stream(stream):
-        e0.record(stream)
-        for i in range(args.steps):
-            step_resident(i)
-        e1.record(stream)
+    e0.record(stream)
+    for st in wstreams[1:]:
+        st.wait_event(e0)
+    for i in range(args.steps):
+        step_resident(i, i % n_str)
+    for st in wstreams[1:]:
+        ev = torch.cuda.Event()
+        ev.record(st)
+        stream.wait_event(ev)
+    e1.record(stream)
     barrier()
     clocks = sampler.stop()
     ms_total = e0.elapsed_time(e1)
@@ -280,26 +316,29 @@ def run_b200(args, rank, local_rank, world):
         raise SystemExit(f"bench.py: {fails} requests failed on the e2e path")
 
     # ---------------- reduce over ranks ----------------
-    t = torch.tensor([ms_total, e2e_s * 1e3], device=dev, dtype=torch.float64)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_total, e2e_ms = float(t[0]), float(t[1])
+    ms_total, e2e_ms = reduce_max_over_ranks([ms_total, e2e_s * 1e3], dev)
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
 
     peaks = load_peaks()
-    value = world * B * args.steps / (ms_total / 1e3)
-    e2e_value = world * B * args.steps / (e2e_ms / 1e3)
-    gemm_tflops = gemm_flops_per_seq(S) * B / (gemm_ms / 1e3) / 1e12
+    value = whole_job_rate(B, args.steps, world, ms_total)
+    e2e_value = whole_job_rate(B, args.steps, world, e2e_ms)
+    gemm_flop_step = LAYERS * 24 * true_tokens * HIDDEN * HIDDEN  # charged on true lengths
+    gemm_tflops = gemm_flop_step / (gemm_ms / 1e3) / 1e12
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-        "config": {"workload": f"BERT-base seq{S} dynamic batch at cap {B}, bf16, one CUDA worker/replica per B200 "
-                               "(BASELINE configs[1]); random-init weights seed 0, ids U[0,30522), all-ones mask",
-                   "batch": B, "seq_len": S, "replicas": world,
+        "scaling": "weak", "vs_baseline": None, "dtype": "bf16" if args.precision == "bf16" else "fp8_e4m3",
+        "data": "synthetic",
+        "config": {"workload": f"BERT-base seq{S} dynamic batch at cap {B}, {args.precision}, one weight replica per B200 "
+                               + ("(BASELINE configs[1])" if (B, S, args.precision, args.min_len) == (32, 128, "bf16", None)
+                                  else "(variant of BASELINE configs[1])")
+                               + "; random-init weights seed 0, ids U[0,30522), "
+                               + ("all-ones mask" if args.min_len is None else f"lengths U[{args.min_len},{S}] padded+masked"),
+                   "batch": B, "seq_len": S, "replicas": world, "resident_streams": n_str,
+                   "mean_true_tokens_per_batch": true_tokens,
                    "l2": "no explicit flush: each step streams 170 MB of bf16 weights plus ~110 MB of activations "
                          "(> 126 MB L2) and input batches rotate over 4 distinct buffers"},
         "clocks": clocks,
@@ -316,7 +355,7 @@ def run_b200(args, rank, local_rank, world):
         "roofline": {"bound": "tensor", "kernel": "gemm_tcgen05_kernel (QKV, attn-out, FFN1, FFN2; 48 launches/step)",
                      "achieved": gemm_tflops, "peak": peaks["tflops"], "unit": "TFLOP/s",
                      "frac": gemm_tflops / peaks["tflops"], "peak_source": peaks["source"], "traffic": None,
-                     "flops_per_step": gemm_flops_per_seq(S) * B, "kernel_ms_per_step": gemm_ms,
+                     "flops_per_step": gemm_flop_step, "kernel_ms_per_step": gemm_ms,
                      "how": "48 GEMM launches x 5 forwards back to back in one CUDA graph, CUDA events on the launch stream"},
         "stage_ms_per_step": stage_ms,
     }
@@ -338,6 +377,9 @@ def main():
     ap.add_argument("--batch", type=int, default=32)
     ap.add_argument("--seq", type=int, default=128)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--precision", default="bf16", choices=["bf16", "fp8", "fp8x6"])
+    ap.add_argument("--min-len", type=int, default=None, help="variable-length requests: lengths U[min_len, seq]")
+    ap.add_argument("--streams", type=int, default=2, help="CUDA workers issuing resident tasks round-robin")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)

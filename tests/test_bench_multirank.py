@@ -1,0 +1,58 @@
+"""CPU, world_size 2 over gloo: the N>1 logic of bench.py -- ranks are independent replicas,
+the only collective is the max-over-ranks of the timed intervals, value = all ranks' units
+over the slowest rank's time, and the reference arm prints on rank 0 only."""
+import json
+import os
+import subprocess
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+WORKER = r"""
+import json, os, sys
+sys.path.insert(0, %r)
+import torch, torch.distributed as dist
+import bench
+dist.init_process_group("gloo")
+rank, world = dist.get_rank(), dist.get_world_size()
+# rank r "measured" (10 + 5 r) ms for the resident loop and (20 - 3 r) ms end to end
+vals = bench.reduce_max_over_ranks([10.0 + 5 * rank, 20.0 - 3 * rank], torch.device("cpu"))
+rate = bench.whole_job_rate(32, 100, world, vals[0])
+print(json.dumps({"rank": rank, "vals": vals, "rate": rate}), flush=True)
+dist.destroy_process_group()
+""" % ROOT
+
+
+def test_max_over_ranks_and_weak_scaling_rate(tmp_path):
+    script = tmp_path / "worker.py"
+    script.write_text(WORKER)
+    env = dict(os.environ, MASTER_ADDR="127.0.0.1")
+    out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+                          "--master-addr", "127.0.0.1", "--master-port", "29731", str(script)],
+                         capture_output=True, text=True, env=env, timeout=240)
+    assert out.returncode == 0, out.stderr[-2000:]
+    lines = [json.loads(l) for l in out.stdout.splitlines() if l.startswith("{")]
+    assert sorted(l["rank"] for l in lines) == [0, 1]
+    for l in lines:
+        assert l["vals"] == [15.0, 20.0]                      # slowest rank of each interval
+        assert l["rate"] == pytest.approx(2 * 32 * 100 / 0.015)  # both replicas' units / slowest time
+
+
+def test_single_rank_is_identity():
+    import torch
+
+    sys.path.insert(0, ROOT)
+    import bench
+
+    assert bench.reduce_max_over_ranks([1.5, 2.5], torch.device("cpu")) == [1.5, 2.5]
+    assert bench.whole_job_rate(32, 10, 1, 1000.0) == 320.0
+
+
+def test_reference_arm_other_ranks_exit_quietly():
+    """bench.py --impl reference under torchrun: ranks != 0 print nothing and exit 0."""
+    env = dict(os.environ, RANK="1", LOCAL_RANK="1", WORLD_SIZE="2")
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--gpus", "2",
+                          "--steps", "1", "--warmup", "1"], capture_output=True, text=True, env=env, timeout=240)
+    assert out.returncode == 0 and out.stdout.strip() == ""
