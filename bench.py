@@ -194,7 +194,10 @@ def run_b200(args, rank, local_rank, world):
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
+        # replicas only: the ranks never exchange data, so the rendezvous is a
+        # host-side gloo group used for the barrier and the max-over-ranks of a few scalars;
+        # NCCL is deliberately not initialised (and cannot pollute stdout with its banner)
+        dist.init_process_group("gloo")
     assert capi.lib().spu_device_is_sm100(local_rank) == 1, "device is not sm_100"
 
     spec = BertConfig()
@@ -316,7 +319,7 @@ def run_b200(args, rank, local_rank, world):
         raise SystemExit(f"bench.py: {fails} requests failed on the e2e path")
 
     # ---------------- reduce over ranks ----------------
-    ms_total, e2e_ms = reduce_max_over_ranks([ms_total, e2e_s * 1e3], dev)
+    ms_total, e2e_ms = reduce_max_over_ranks([ms_total, e2e_s * 1e3], torch.device("cpu"))
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()

@@ -161,7 +161,9 @@ amax_kernel(const float *__restrict__ in_f32, const __nv_bfloat16 *__restrict__ 
   if ((threadIdx.x & 31) == 0 && m > 0.f) atomicMax(reinterpret_cast<int *>(amax), __float_as_int(m));
 }
 
-// Ragged gather + pad + mask: one CTA row per request, 8-byte words, coalesced.
+// Ragged gather + pad + mask: blockIdx.y = request; each thread moves TWO consecutive tokens
+// per step (two 8-byte loads in flight per table, one 16-byte store per output row when the
+// row is 16-byte aligned), grid-striding over the padded row.
 __global__ void __launch_bounds__(256)
 gather_pad_mask_kernel(const int64_t *const *__restrict__ src_ids,
                        const int64_t *const *__restrict__ src_mask,
@@ -171,18 +173,33 @@ gather_pad_mask_kernel(const int64_t *const *__restrict__ src_ids,
   const int L = len[r];
   const int64_t *sid = src_ids[r];
   const int64_t *smk = src_mask != nullptr ? src_mask[r] : nullptr;
-  for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < seq; t += gridDim.x * blockDim.x) {
-    const bool in = t < L;
-    const size_t o = static_cast<size_t>(r) * seq + t;
-    ids_out[o] = in ? sid[t] : pad_id;
-    mask_out[o] = in ? (smk != nullptr ? smk[t] : 1) : 0;
+  const size_t row = static_cast<size_t>(r) * seq;
+  const bool vec = ((row | static_cast<size_t>(seq)) & 1u) == 0;  // 16-byte aligned pairs
+  for (int t = 2 * (blockIdx.x * blockDim.x + threadIdx.x); t < seq; t += 2 * gridDim.x * blockDim.x) {
+    const bool in0 = t < L, in1 = t + 1 < L;
+    const int64_t i0 = in0 ? sid[t] : pad_id;
+    const int64_t i1 = in1 ? sid[t + 1] : pad_id;
+    const int64_t m0 = in0 ? (smk != nullptr ? smk[t] : 1) : 0;
+    const int64_t m1 = in1 ? (smk != nullptr ? smk[t + 1] : 1) : 0;
+    if (vec) {
+      *reinterpret_cast<longlong2 *>(ids_out + row + t) = make_longlong2(i0, i1);
+      *reinterpret_cast<longlong2 *>(mask_out + row + t) = make_longlong2(m0, m1);
+    } else {
+      ids_out[row + t] = i0;
+      mask_out[row + t] = m0;
+      if (t + 1 < seq) {
+        ids_out[row + t + 1] = i1;
+        mask_out[row + t + 1] = m1;
+      }
+    }
   }
 }
 
 // Segmented byte copy.  Segment i: nbytes[i] bytes from (srcs ? srcs[i] : src_base +
-// src_off[i]) to (dsts ? dsts[i] : dst_base + dst_off[i]).  blockIdx.y = segment;
-// the CTAs of a segment grid-stride over it with 128-bit accesses when all three of
-// source, destination and size are 16-byte aligned.
+// src_off[i]) to (dsts ? dsts[i] : dst_base + dst_off[i]).  blockIdx.y = segment; block b of
+// the gridDim.x blocks of a segment owns one contiguous span of it, and every thread keeps up
+// to four independent 16-byte loads in flight before its stores (128-bit path when source,
+// destination and size are all 16-byte aligned; byte path otherwise).
 __global__ void __launch_bounds__(256)
 segcopy_kernel(const void *const *__restrict__ srcs, const uint8_t *src_base,
                const uint64_t *__restrict__ src_off, void *const *__restrict__ dsts,
@@ -192,23 +209,25 @@ segcopy_kernel(const void *const *__restrict__ srcs, const uint8_t *src_base,
   const uint8_t *s = srcs != nullptr ? static_cast<const uint8_t *>(srcs[i]) : src_base + src_off[i];
   uint8_t *d = dsts != nullptr ? static_cast<uint8_t *>(dsts[i]) : dst_base + dst_off[i];
   const uint64_t n = nbytes[i];
-  const uint64_t tid = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
-  const uint64_t nthr = static_cast<uint64_t>(gridDim.x) * blockDim.x;
   if (((reinterpret_cast<uintptr_t>(s) | reinterpret_cast<uintptr_t>(d) | n) & 15u) == 0) {
+    const uint64_t n4 = n >> 4;
+    const uint64_t span = (n4 + gridDim.x - 1) / gridDim.x;
+    const uint64_t lo = span * blockIdx.x;
+    const uint64_t hi = lo + span < n4 ? lo + span : n4;
     const uint4 *s4 = reinterpret_cast<const uint4 *>(s);
     uint4 *d4 = reinterpret_cast<uint4 *>(d);
-    const uint64_t n4 = n >> 4;
-    uint64_t k = tid;
-    // 4 independent 16-byte loads in flight per thread before the stores
-    for (; k + 3 * nthr < n4; k += 4 * nthr) {
-      const uint4 a = s4[k], b = s4[k + nthr], c = s4[k + 2 * nthr], e = s4[k + 3 * nthr];
-      d4[k] = a;
-      d4[k + nthr] = b;
-      d4[k + 2 * nthr] = c;
-      d4[k + 3 * nthr] = e;
+    for (uint64_t base = lo + threadIdx.x; base < hi; base += 4 * 256) {
+      uint4 v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (base + u * 256 < hi) v[u] = __ldcs(s4 + base + u * 256);
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (base + u * 256 < hi) __stcs(d4 + base + u * 256, v[u]);
     }
-    for (; k < n4; k += nthr) d4[k] = s4[k];
   } else {
+    const uint64_t tid = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    const uint64_t nthr = static_cast<uint64_t>(gridDim.x) * blockDim.x;
     for (uint64_t k = tid; k < n; k += nthr) d[k] = s[k];
   }
 }
@@ -298,7 +317,7 @@ extern "C" spu_status spu_gather_pad_mask_async(const int64_t *const *src_ids,
   if (n_req == 0 || seq == 0) return SPU_OK;  // empty batch: nothing to move
   SPU_REQUIRE(src_ids && len && ids_out && mask_out, SPU_ERR_INVALID, "gather: null argument");
   SPU_REQUIRE(n_req > 0 && seq > 0 && n_req <= 65535, SPU_ERR_INVALID, "gather: bad shape");
-  dim3 grid((seq + 255) / 256 > 8 ? 8 : (seq + 255) / 256, n_req);
+  dim3 grid((seq + 511) / 512 > 8 ? 8 : (seq + 511) / 512, n_req);
   gather_pad_mask_kernel<<<grid, 256, 0, as_stream(stream)>>>(src_ids, src_mask, len, seq, pad_id,
                                                               ids_out, mask_out);
   SPU_CUDA_TRY(cudaGetLastError());
