@@ -20,7 +20,9 @@ rank, world = dist.get_rank(), dist.get_world_size()
 # rank r "measured" (10 + 5 r) ms for the resident loop and (20 - 3 r) ms end to end
 vals = bench.reduce_max_over_ranks([10.0 + 5 * rank, 20.0 - 3 * rank], torch.device("cpu"))
 rate = bench.whole_job_rate(32, 100, world, vals[0])
-print(json.dumps({"rank": rank, "vals": vals, "rate": rate}), flush=True)
+# one file per rank: two ranks writing to the same stdout pipe can interleave mid-line
+with open(os.path.join(os.environ["SPU_TEST_OUT"], "rank" + str(rank) + ".json"), "w") as f:
+    json.dump({"rank": rank, "vals": vals, "rate": rate}, f)
 dist.destroy_process_group()
 """ % ROOT
 
@@ -28,12 +30,12 @@ dist.destroy_process_group()
 def test_max_over_ranks_and_weak_scaling_rate(tmp_path):
     script = tmp_path / "worker.py"
     script.write_text(WORKER)
-    env = dict(os.environ, MASTER_ADDR="127.0.0.1")
+    env = dict(os.environ, MASTER_ADDR="127.0.0.1", SPU_TEST_OUT=str(tmp_path))
     out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
                           "--master-addr", "127.0.0.1", "--master-port", "29731", str(script)],
                          capture_output=True, text=True, env=env, timeout=240)
     assert out.returncode == 0, out.stderr[-2000:]
-    lines = [json.loads(l) for l in out.stdout.splitlines() if l.startswith("{")]
+    lines = [json.loads((tmp_path / f"rank{r}.json").read_text()) for r in range(2)]
     assert sorted(l["rank"] for l in lines) == [0, 1]
     for l in lines:
         assert l["vals"] == [15.0, 20.0]                      # slowest rank of each interval
