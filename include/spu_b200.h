@@ -280,6 +280,9 @@ spu_status spu_affine_f32_async(const float *in, float *out, uint64_t n,
 /* Debug (tools/gemm_trace.py): CTA `cta` of every following GEMM launch writes 65 u64
  * %globaltimer stamps of its pipeline to device_buf; NULL switches it off.  Not thread-safe. */
 void spu_debug_gemm_trace(void *device_buf, int32_t cta);
+/* Debug (tools/gemm_rates.py): 0 = normal, 1 = GEMM launches skip their TMA operand loads,
+ * 2 = skip their MMAs.  Results are garbage; isolates the MMA rate from the feed rate. */
+void spu_debug_gemm_mode(int32_t mode);
 
 /* ---- Misc ------------------------------------------------------------------ */
 const char *spu_last_error(void);       /* thread-local message of the last failure */

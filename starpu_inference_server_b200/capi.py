@@ -28,6 +28,7 @@ SYMBOLS = [
     "spu_bert_output_bytes", "spu_vit_replica_create", "spu_vit_forward_async", "spu_vit_input_bytes",
     "spu_vit_output_bytes", "spu_bert_stage_chain_ms", "spu_bert_calibrate_fp8", "spu_bert_fp8_scales",
     "spu_gemm_fp8_async", "spu_quantize_e4m3_async", "spu_debug_gemm_trace",
+    "spu_debug_gemm_mode",
 ]
 
 
@@ -88,6 +89,7 @@ def lib():
     L.spu_gemm_fp8_async.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, i32, f32, f32, vp]
     L.spu_quantize_e4m3_async.argtypes = [vp, vp, u64, f32, vp]
     L.spu_debug_gemm_trace.argtypes = [vp, i32]
+    L.spu_debug_gemm_mode.argtypes = [i32]
     L.spu_bert_output_bytes.argtypes = [vp, i32, i32]
     L.spu_vit_input_bytes.argtypes = [vp, i32]
     L.spu_vit_output_bytes.argtypes = [vp, i32]
@@ -96,7 +98,7 @@ def lib():
         fn = getattr(L, name)
         if name.endswith("_bytes"):
             fn.restype = u64
-        elif name == "spu_debug_gemm_trace":
+        elif name in ("spu_debug_gemm_trace", "spu_debug_gemm_mode"):
             fn.restype = None
         elif name not in ("spu_last_error",):
             fn.restype = i32

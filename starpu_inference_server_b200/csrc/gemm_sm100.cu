@@ -41,6 +41,7 @@ constexpr int kABytes = kRowsPerCta * kTileKBytes;          // 16 KiB
 constexpr int kSmemMax = 227 * 1024;
 constexpr int kBarrierBytes = 512;
 constexpr int kMaxStages = 8;
+constexpr int kTraceTile = 0;  // which of the traced CTA's tiles the epilogue stamps describe
 
 template <int EPI>
 struct EpiTraits {
@@ -78,9 +79,14 @@ struct KernelArgs {
   // stamps: [0] kernel entry, [1] after griddepcontrol.wait (MMA thread), [2+kb] full
   // barrier of k-block kb of its first tile observed by the MMA thread (kb < 60),
   // [62] accumulator of the first tile ready (epilogue warp 4), [63] that warp's last store
-  // of the first tile issued, [64] kernel exit.
+  // of the first tile issued, [64] kernel exit, [66 + 8c + i] chunk c < 4 of that warp:
+  // i = 0 loop top, 1 tcgen05.ld + bias loads issued, 2 staging slot free, 3 tcgen05.ld
+  // landed, 4 math + st.shared issued, 5 proxy fence done, 6 TMA store issued, 7 iteration end.
   unsigned long long *trace;
   int trace_cta;
+  // Experiments only (spu_debug_gemm_mode): 1 = producer skips the TMA loads (pure MMA +
+  // barrier rate on whatever smem holds), 2 = issuer skips the MMAs (pure operand feed rate).
+  int dbg;
 };
 
 __device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c,
@@ -129,7 +135,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
   uint64_t *resid_bar = tmem_empty_bar + 2;  // [kNumEpiWarps][2]
   uint32_t *tmem_ptr_smem = reinterpret_cast<uint32_t *>(resid_bar + 2 * kNumEpiWarps);
 
-  const int warp_idx = threadIdx.x >> 5;
+  // warp-uniform by construction AND provably so for the compiler (shuffle from lane 0)
+  const int warp_idx = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
   const int lane = threadIdx.x & 31;
   const uint32_t cta_rank = CG == 2 ? cluster_ctarank() : 0u;
   const int unit = static_cast<int>(blockIdx.x) / CG;       // tile-owning CTA (pair) index
@@ -140,6 +147,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
   const int num_tiles = n_blocks * m_blocks;
   const int num_k_blocks = args.K / kElemsPerKBlock;
 
+  // experiments (spu_debug_gemm_mode bits 8..11): use fewer ring stages than fit
+  const int n_stages = (args.dbg >> 8) > 0 && (args.dbg >> 8) < kStages ? (args.dbg >> 8) : kStages;
+  const int dbg_mode = args.dbg & 0xff;
   const bool tracing = args.trace != nullptr && static_cast<int>(blockIdx.x) == args.trace_cta;
   if (tracing && threadIdx.x == 0) args.trace[0] = global_timer_ns();
   if (warp_idx == 0 && lane == 0) {
@@ -172,7 +182,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
   tcgen05_fence_before();
   if constexpr (CG == 2) cluster_sync_all(); else __syncthreads();
   tcgen05_fence_after();
-  const uint32_t tmem_base = *tmem_ptr_smem;
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_ptr_smem, 0);
+  const uint32_t smem_base_u32 = smem_u32(smem);
 
   // Programmatic dependent launch: everything above, plus the producer's first WEIGHT-tile
   // loads below, overlaps the previous kernel's tail; memory written by that kernel (the
@@ -182,109 +193,130 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
 
   if (warp_idx == 0) {
     // ===================== TMA producer (both CTAs of a pair) =====================
-    if (lane == 0) {
-      auto issue_expect = [&](int stage) {
-        if constexpr (CG == 2) {
-          if (cta_rank == 0) mbar_arrive_expect_tx(&full_bar[stage], 2 * kStageBytes);
-        } else {
-          mbar_arrive_expect_tx(&full_bar[stage], kStageBytes);
-        }
-      };
-      auto load_a = [&](int stage, int kb, int a_row) {
-        uint8_t *sa = smem + stage * kStageBytes;
-        if constexpr (CG == 2) tma_load_2d_pair(sa, &tmap_a, &full_bar[stage], kb * kElemsPerKBlock, a_row);
-        else tma_load_2d(sa, &tmap_a, &full_bar[stage], kb * kElemsPerKBlock, a_row);
-      };
-      auto load_b = [&](int stage, int kb, int b_row) {
-        uint8_t *sb = smem + stage * kStageBytes + kABytes;
-        if constexpr (CG == 2) tma_load_2d_pair(sb, &tmap_b, &full_bar[stage], kb * kElemsPerKBlock, b_row);
-        else tma_load_2d(sb, &tmap_b, &full_bar[stage], kb * kElemsPerKBlock, b_row);
-      };
-      // weights of the first tile's first stages: independent of the previous kernel
-      const int n_pre = unit < num_tiles ? (num_k_blocks < kStages ? num_k_blocks : kStages) : 0;
-      {
-        const int n_blk = unit % n_blocks;
-        const int b_row = n_blk * BLOCK_N + static_cast<int>(cta_rank) * Cfg::kBRows;
+    // Whole warp in the loop (uniform control flow -> uniform-register TMA operands), one
+    // elected lane issues.
+    const bool no_tma = dbg_mode == 1 || dbg_mode == 3;
+    auto issue_expect = [&](int stage) {
+      if (no_tma) {
+        if (cta_rank == 0) mbar_arrive(&full_bar[stage]);
+        return;
+      }
+      if constexpr (CG == 2) {
+        if (cta_rank == 0) mbar_arrive_expect_tx(&full_bar[stage], 2 * kStageBytes);
+      } else {
+        mbar_arrive_expect_tx(&full_bar[stage], kStageBytes);
+      }
+    };
+    auto load_a = [&](int stage, int kb, int a_row) {
+      if (no_tma) return;
+      uint8_t *sa = smem + stage * kStageBytes;
+      if constexpr (CG == 2) tma_load_2d_pair(sa, &tmap_a, &full_bar[stage], kb * kElemsPerKBlock, a_row);
+      else tma_load_2d(sa, &tmap_a, &full_bar[stage], kb * kElemsPerKBlock, a_row);
+    };
+    auto load_b = [&](int stage, int kb, int b_row) {
+      if (no_tma) return;
+      uint8_t *sb = smem + stage * kStageBytes + kABytes;
+      if constexpr (CG == 2) tma_load_2d_pair(sb, &tmap_b, &full_bar[stage], kb * kElemsPerKBlock, b_row);
+      else tma_load_2d(sb, &tmap_b, &full_bar[stage], kb * kElemsPerKBlock, b_row);
+    };
+    // weights of the first tile's first stages: independent of the previous kernel
+    const int n_pre = unit < num_tiles ? (num_k_blocks < n_stages ? num_k_blocks : n_stages) : 0;
+    {
+      const int n_blk = unit % n_blocks;
+      const int b_row = n_blk * BLOCK_N + static_cast<int>(cta_rank) * Cfg::kBRows;
+      if (elect_one()) {
         for (int kb = 0; kb < n_pre; ++kb) {
           issue_expect(kb);
           load_b(kb, kb, b_row);
         }
       }
-      pdl_wait_prior_grid();
-      int stage = 0;
-      uint32_t phase = 0;
-      bool first = true;
-      for (int tile = unit; tile < num_tiles; tile += num_units) {
-        const int m_blk = tile / n_blocks;
-        const int n_blk = tile % n_blocks;
-        const int a_row = m_blk * kTileM + static_cast<int>(cta_rank) * kRowsPerCta;
-        const int b_row = n_blk * BLOCK_N + static_cast<int>(cta_rank) * Cfg::kBRows;
-        for (int kb = 0; kb < num_k_blocks; ++kb) {
-          if (first && kb < n_pre) {
-            load_a(stage, kb, a_row);  // barrier armed and B already in flight
-          } else {
-            mbar_wait(&empty_bar[stage], phase ^ 1u);
+      __syncwarp();
+    }
+    pdl_wait_prior_grid();
+    int stage = 0;
+    uint32_t phase = 0;
+    bool first = true;
+    for (int tile = unit; tile < num_tiles; tile += num_units) {
+      const int m_blk = tile / n_blocks;
+      const int n_blk = tile % n_blocks;
+      const int a_row = m_blk * kTileM + static_cast<int>(cta_rank) * kRowsPerCta;
+      const int b_row = n_blk * BLOCK_N + static_cast<int>(cta_rank) * Cfg::kBRows;
+      for (int kb = 0; kb < num_k_blocks; ++kb) {
+        if (first && kb < n_pre) {
+          if (elect_one()) load_a(stage, kb, a_row);  // barrier armed and B already in flight
+        } else {
+          mbar_wait_warp(&empty_bar[stage], phase ^ 1u);
+          if (elect_one()) {
             issue_expect(stage);
             load_a(stage, kb, a_row);
             load_b(stage, kb, b_row);
           }
-          if (++stage == kStages) {
-            stage = 0;
-            phase ^= 1u;
-          }
         }
-        first = false;
+        __syncwarp();
+        if (++stage == n_stages) {
+          stage = 0;
+          phase ^= 1u;
+        }
       }
+      first = false;
     }
-    __syncwarp();  // reconverge before the CTA-wide barrier below
   } else if (warp_idx == 1) {
     // ===================== MMA issuer (leader CTA) =====================
+    // The WHOLE warp runs the loop (warp-uniform control flow and operands, so ptxas keeps
+    // descriptors in uniform registers); one elected lane issues the MMAs and commits.
     pdl_wait_prior_grid();
     if (tracing && lane == 0) args.trace[1] = global_timer_ns();
-    if (lane == 0 && cta_rank == 0) {
+    if (cta_rank == 0) {
       int stage = 0;
       uint32_t phase = 0;
       int local_tile = 0;
+      const int dbg = dbg_mode;
       for (int tile = unit; tile < num_tiles; tile += num_units, ++local_tile) {
         const int acc = local_tile & 1;
         const uint32_t acc_phase = (local_tile >> 1) & 1u;
-        mbar_wait(&tmem_empty_bar[acc], acc_phase ^ 1u);
+        mbar_wait_warp(&tmem_empty_bar[acc], acc_phase ^ 1u);
         tcgen05_fence_after();
         const uint32_t tmem_d = tmem_base + static_cast<uint32_t>(acc * BLOCK_N);
         for (int kb = 0; kb < num_k_blocks; ++kb) {
-          mbar_wait(&full_bar[stage], phase);
+          mbar_wait_warp(&full_bar[stage], phase);
           tcgen05_fence_after();
-          if (tracing && local_tile == 0 && kb < 60) args.trace[2 + kb] = global_timer_ns();
-          const uint32_t sa = smem_u32(smem + stage * kStageBytes);
+          if (tracing && lane == 0 && local_tile == 0 && kb < 60) args.trace[2 + kb] = global_timer_ns();
+          const uint32_t sa = smem_base_u32 + static_cast<uint32_t>(stage * kStageBytes);
           const uint64_t desc_a = make_sw128_kmajor_desc(sa);
           const uint64_t desc_b = make_sw128_kmajor_desc(sa + kABytes);
+          if (elect_one()) {
+            auto issue_kblock = [&](uint32_t first_accumulates) {
 #pragma unroll
-          for (int k = 0; k < kTileKBytes / kUmmaKBytes; ++k) {
-            // advancing 32 bytes along K inside the 128-byte swizzle row = +2 in the
-            // (addr >> 4) start-address field
-            const uint64_t adv = static_cast<uint64_t>((k * kUmmaKBytes) >> 4);
-            const uint32_t accumulate = (kb | k) != 0;
-            if constexpr (CG == 2) {
-              if constexpr (IN_FP8) umma_f8_ss_pair(tmem_d, desc_a + adv, desc_b + adv, kIdesc, accumulate);
-              else umma_f16_ss_pair(tmem_d, desc_a + adv, desc_b + adv, kIdesc, accumulate);
-            } else {
-              if constexpr (IN_FP8) umma_f8_ss(tmem_d, desc_a + adv, desc_b + adv, kIdesc, accumulate);
-              else umma_f16_ss(tmem_d, desc_a + adv, desc_b + adv, kIdesc, accumulate);
+              for (int k = 0; k < kTileKBytes / kUmmaKBytes; ++k) {
+                // advancing 32 bytes along K inside the 128-byte swizzle row = +2 in the
+                // (addr >> 4) start-address field
+                const uint64_t adv = static_cast<uint64_t>((k * kUmmaKBytes) >> 4);
+                const uint32_t accumulate = k != 0 ? 1u : first_accumulates;
+                if constexpr (CG == 2) {
+                  if constexpr (IN_FP8) umma_f8_ss_pair(tmem_d, desc_a + adv, desc_b + adv, kIdesc, accumulate);
+                  else umma_f16_ss_pair(tmem_d, desc_a + adv, desc_b + adv, kIdesc, accumulate);
+                } else {
+                  if constexpr (IN_FP8) umma_f8_ss(tmem_d, desc_a + adv, desc_b + adv, kIdesc, accumulate);
+                  else umma_f16_ss(tmem_d, desc_a + adv, desc_b + adv, kIdesc, accumulate);
+                }
+              }
+            };
+            if (dbg != 2) issue_kblock(kb != 0);
+            if (dbg == 3) issue_kblock(1u);  // experiments: twice the MMAs per barrier round
+            // smem stage reusable (in both CTAs) once these MMAs retire
+            if constexpr (CG == 2) umma_commit_pair(&empty_bar[stage]); else umma_commit(&empty_bar[stage]);
+            if (kb == num_k_blocks - 1) {
+              if constexpr (CG == 2) umma_commit_pair(&tmem_full_bar[acc]); else umma_commit(&tmem_full_bar[acc]);
             }
           }
-          // smem stage reusable (in both CTAs) once these MMAs retire
-          if constexpr (CG == 2) umma_commit_pair(&empty_bar[stage]); else umma_commit(&empty_bar[stage]);
-          if (kb == num_k_blocks - 1) {
-            if constexpr (CG == 2) umma_commit_pair(&tmem_full_bar[acc]); else umma_commit(&tmem_full_bar[acc]);
-          }
-          if (++stage == kStages) {
+          __syncwarp();
+          if (++stage == n_stages) {
             stage = 0;
             phase ^= 1u;
           }
         }
       }
     }
-    __syncwarp();
   } else if (warp_idx >= kEpiWarp0) {
     // ===================== epilogue (all CTAs) =====================
     pdl_wait_prior_grid();
@@ -333,7 +365,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
       }
       mbar_wait(&tmem_full_bar[acc], acc_phase);
       tcgen05_fence_after();
-      if (tracing && local_tile == 0 && e == 0 && lane == 0) args.trace[62] = global_timer_ns();
+      if (tracing && local_tile == kTraceTile && e == 0 && lane == 0) args.trace[62] = global_timer_ns();
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) +
                              static_cast<uint32_t>(acc * BLOCK_N + half * (BLOCK_N / 2));
 #pragma unroll 1
@@ -342,19 +374,20 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
         const uint32_t b = chunk_ctr & 1u;
         const uint32_t sbuf = stg + b * Epi::kChunkBytes;
         uint32_t v[32];
+        const bool tr_chunk = tracing && local_tile == kTraceTile && e == 0 && lane == 0 && c < 4;
+        if (tr_chunk) args.trace[66 + 8 * c] = global_timer_ns();
         tmem_ld_32x32b_x32(taddr + static_cast<uint32_t>(c * 32), v);
         float4 bn[8];
         if (c + 1 < kChunksPerWarp) load_bias(bn, col0 + 32);
-        const bool tr_chunk = tracing && local_tile == 0 && e == 0 && lane == 0 && c < 8;
-        if (tr_chunk) args.trace[66 + 4 * c] = global_timer_ns();
+        if (tr_chunk) args.trace[67 + 8 * c] = global_timer_ns();
         if constexpr (EPI != kEpiBiasResid) {
           // the store issued from this slot two chunks ago must have drained it
           if (lane == 0) tma_store_wait_read<1>();
           __syncwarp();
         }
-        if (tr_chunk) args.trace[67 + 4 * c] = global_timer_ns();
+        if (tr_chunk) args.trace[68 + 8 * c] = global_timer_ns();
         tmem_ld_wait();
-        if (tr_chunk) args.trace[68 + 4 * c] = global_timer_ns();
+        if (tr_chunk) args.trace[69 + 8 * c] = global_timer_ns();
         if (c == kChunksPerWarp - 1) {
           // accumulator fully read: hand the TMEM buffer back to the MMA issuer
           tcgen05_fence_before();
@@ -421,9 +454,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
                          pack_bf16(f[8 * j + 4], f[8 * j + 5]), pack_bf16(f[8 * j + 6], f[8 * j + 7]));
           }
         }
+        if (tr_chunk) args.trace[70 + 8 * c] = global_timer_ns();
         fence_proxy_async_smem();  // generic-proxy smem writes -> visible to the TMA engine
         __syncwarp();
-        if (tr_chunk) args.trace[69 + 4 * c] = global_timer_ns();
+        if (tr_chunk) args.trace[71 + 8 * c] = global_timer_ns();
         if (lane == 0) {
           if constexpr (EPI == kEpiBiasAccum)
             tma_reduce_add_2d(&tmap_out, staging + e * Epi::kWarpBytes + b * Epi::kChunkBytes, col0, row0);
@@ -441,13 +475,15 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
           }
         }
         __syncwarp();
+        if (tr_chunk) args.trace[72 + 8 * c] = global_timer_ns();
         if (c + 1 < kChunksPerWarp) {
 #pragma unroll
           for (int j = 0; j < 8; ++j) bv[j] = bn[j];
         }
+        if (tr_chunk) args.trace[73 + 8 * c] = global_timer_ns();
         ++chunk_ctr;  // counts live chunks only: slot = ctr & 1, residual-barrier parity = ctr >> 1
       }
-      if (tracing && local_tile == 0 && e == 0 && lane == 0) args.trace[63] = global_timer_ns();
+      if (tracing && local_tile == kTraceTile && e == 0 && lane == 0) args.trace[63] = global_timer_ns();
     }
     if (lane == 0) tma_store_wait<0>();  // all bulk stores of this warp are complete
     __syncwarp();
@@ -557,9 +593,12 @@ spu_status launch_cfg(const GemmPlan &plan, const LaunchMaps &maps, const Kernel
   cfg.stream = stream;
   cudaLaunchAttribute attrs[2];
   int n_attr = 0;
-  attrs[n_attr].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-  attrs[n_attr].val.programmaticStreamSerializationAllowed = 1;
-  ++n_attr;
+  static const bool pdl = std::getenv("SPU_GEMM_NO_PDL") == nullptr;  // experiments only
+  if (pdl) {
+    attrs[n_attr].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attrs[n_attr].val.programmaticStreamSerializationAllowed = 1;
+    ++n_attr;
+  }
   if (CG == 2) {
     attrs[n_attr].id = cudaLaunchAttributeClusterDimension;
     attrs[n_attr].val.clusterDim.x = 2;
@@ -613,6 +652,7 @@ constexpr int kBlockNCands[4] = {256, 192, 128, 64};
 
 unsigned long long *g_trace_buf = nullptr;  // debug only, see KernelArgs::trace
 int g_trace_cta = 0;
+int g_dbg_mode = 0;
 
 }  // namespace
 
@@ -620,32 +660,30 @@ void gemm_set_trace(unsigned long long *device_buf, int cta) {
   g_trace_buf = device_buf;
   g_trace_cta = cta;
 }
+void gemm_set_debug_mode(int mode) { g_dbg_mode = mode; }
 
 GemmConfig choose_config(int M, int N, int K, int esize) {
+  // Cost model fitted to in-situ measurements on B200 (profiles/r05_gemm_issue_path.md):
+  // one persistent round costs k_blocks x t_kb(cta_group, BLOCK_N); the last tile's epilogue
+  // and the launch / pipeline-fill cost are paid once.  A CTA pair halves the B bytes each SM
+  // stages and reads per MMA, and shared-memory bandwidth (TMA fill + MMA operand reads) is
+  // what bounds the main loop, so pairs win at every size measured.
+  static const double t_kb_ns[2][4] = {{560.0, 480.0, 390.0, 300.0},   // cta_group::1, BLOCK_N 256/192/128/64
+                                       {350.0, 290.0, 270.0, 260.0}};  // cta_group::2
   GemmConfig best{0, 0};
   double best_cost = 1e300;
-  const double k_bytes = static_cast<double>(K) * esize;
-  const int k_blocks = static_cast<int>(k_bytes) / kTileKBytes;
+  const int k_blocks = static_cast<int>(static_cast<long long>(K) * esize / kTileKBytes);
   for (int cg = 2; cg >= 1; --cg) {
     const int tile_m = kRowsPerCta * cg;
     const int units = kNumSMsB200 / cg;
     const int m_blocks = (M + tile_m - 1) / tile_m;
-    for (int bn : kBlockNCands) {
+    for (int i = 0; i < 4; ++i) {
+      const int bn = kBlockNCands[i];
       if (N % bn != 0) continue;
       const int tiles = m_blocks * (N / bn);
       const int rounds = (tiles + units - 1) / units;
-      // cycles one CTA spends per tile on: MMA issue (128 x bn x 16 per bn/2 clocks),
-      // L2->smem operand feed (~40 B/clk/SM), epilogue (8 warps, ~6 clk per column)
-      const double mma = k_blocks * 4.0 * (bn / 2.0);
-      const double feed = (kRowsPerCta + bn / static_cast<double>(cg)) * k_bytes / 40.0;
-      const double epi = bn * 6.0;
-      const double tile = mma > feed ? (mma > epi ? mma : epi) : (feed > epi ? feed : epi);
-      // a pair that owns fewer than 129 valid rows wastes its second CTA
-      // measured in situ (profiles/r02_tile_sweep_in_situ.md): at every BERT/ViT problem size a
-      // CTA pair is 5-15 % slower than two independent CTAs with the same BLOCK_N (cluster
-      // launch + cross-CTA barrier latency outweigh the saved operand traffic), so the
-      // automatic choice stays on cta_group::1; pairs remain available when forced.
-      const double cost = rounds * tile + epi + 1500.0 + (cg == 2 ? 1e12 : 0.0);
+      const double tail_ns = 600.0 + 10.0 * bn;
+      const double cost = rounds * k_blocks * t_kb_ns[cg - 1][i] + tail_ns + 2500.0;
       if (cost < best_cost) {
         best_cost = cost;
         best = GemmConfig{cg, bn};
@@ -725,7 +763,7 @@ spu_status gemm_launch(const GemmPlan &plan, int M, const GemmEpilogueArgs &args
   } else {
     maps.resid = maps.out;
   }
-  KernelArgs a{M, plan.N, plan.K, args.bias, args.acc_scale, args.out_inv_scale, g_trace_buf, g_trace_cta};
+  KernelArgs a{M, plan.N, plan.K, args.bias, args.acc_scale, args.out_inv_scale, g_trace_buf, g_trace_cta, g_dbg_mode};
   // residual == output: accumulate in place with a TMA reduce-add instead of load + add + store
   const bool inplace = plan.epilogue == kEpiBiasResid && args.resid == args.out;
   return cfg.cta_group == 2 ? launch_bn<2>(plan, cfg.block_n, maps, a, stream, inplace)

@@ -61,5 +61,7 @@ spu_status gemm_launch(const GemmPlan &plan, int M, const GemmEpilogueArgs &args
 // Debug: have CTA `cta` of every following launch write its pipeline time stamps (65 x u64,
 // %globaltimer ns) to device_buf; nullptr switches tracing off.  Not thread-safe, tools only.
 void gemm_set_trace(unsigned long long *device_buf, int cta);
+// Debug: 0 = normal; 1 = no TMA operand loads; 2 = no MMAs (results are garbage; rate experiments only).
+void gemm_set_debug_mode(int mode);
 
 }  // namespace spu

@@ -581,6 +581,8 @@ extern "C" void spu_debug_gemm_trace(void *device_buf, int32_t cta) {
   gemm_set_trace(static_cast<unsigned long long *>(device_buf), cta);
 }
 
+extern "C" void spu_debug_gemm_mode(int32_t mode) { gemm_set_debug_mode(mode); }
+
 extern "C" const char *spu_last_error(void) { return g_last_error.c_str(); }
 extern "C" int32_t spu_abi_version(void) { return SPU_ABI_VERSION; }
 

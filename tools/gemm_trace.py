@@ -41,8 +41,8 @@ def main():
                               "kb_gap_ns_mean": sum(gaps) / max(1, len(gaps)), "kb_gaps_head": gaps[:14],
                               "last_full": kb[-1], "acc_ready": t[62] - t0, "epi_done": t[63] - t0,
                               "exit": t[64] - t0,
-                              "chunks(start,after_wait_read,after_tmem_ld,after_stage)":
-                                  [[t[66 + 4 * c + i] - t0 for i in range(4)] for c in range(8) if t[66 + 4 * c]]}))
+                              "chunks(top,ld_issued,slot_free,ld_landed,staged,fenced,stored,end)":
+                                  [[t[66 + 8 * c + i] - t0 for i in range(8)] for c in range(4) if t[66 + 8 * c]]}))
 
 
 if __name__ == "__main__":
