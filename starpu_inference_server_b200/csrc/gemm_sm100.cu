@@ -41,7 +41,6 @@ constexpr int kABytes = kRowsPerCta * kTileKBytes;          // 16 KiB
 constexpr int kSmemMax = 227 * 1024;
 constexpr int kBarrierBytes = 512;
 constexpr int kMaxStages = 8;
-constexpr int kTraceTile = 0;  // which of the traced CTA's tiles the epilogue stamps describe
 
 template <int EPI>
 struct EpiTraits {
@@ -150,7 +149,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
   // experiments (spu_debug_gemm_mode bits 8..11): use fewer ring stages than fit
   const int n_stages = (args.dbg >> 8) > 0 && (args.dbg >> 8) < kStages ? (args.dbg >> 8) : kStages;
   const int dbg_mode = args.dbg & 0xff;
-  const bool tracing = args.trace != nullptr && static_cast<int>(blockIdx.x) == args.trace_cta;
+  // trace_cta = cta index | (local tile whose epilogue is stamped << 16)
+  const bool tracing = args.trace != nullptr && static_cast<int>(blockIdx.x) == (args.trace_cta & 0xffff);
+  const int kTraceTile = args.trace_cta >> 16;
   if (tracing && threadIdx.x == 0) args.trace[0] = global_timer_ns();
   if (warp_idx == 0 && lane == 0) {
     tma_prefetch_desc(&tmap_a);
@@ -335,9 +336,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
       const int row0 = m_blk * kTileM + static_cast<int>(cta_rank) * kRowsPerCta + q * 32;
       const int colw = n_blk * BLOCK_N + half * (BLOCK_N / 2);  // first column of this warp
       const bool slab_live = row0 < args.M;  // TMA clips partial slabs; dead ones are skipped
-      // bias of chunk 0 -> registers while the main loop still runs; every later chunk's
-      // bias is fetched one chunk ahead (warp-uniform addresses: one broadcast per load)
-      float4 bv[8];
+      // Bias: warp-uniform 128-bit loads (one broadcast each) issued at the top of every
+      // chunk; the tile's whole bias slice is pulled into L1 here, while the main loop runs.
       auto load_bias = [&](float4 (&dst)[8], int col) {
         if (args.bias != nullptr) {
           const float4 *b4 = reinterpret_cast<const float4 *>(args.bias + col);
@@ -348,7 +348,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
           for (int j = 0; j < 8; ++j) dst[j] = make_float4(0.f, 0.f, 0.f, 0.f);
         }
       };
-      load_bias(bv, colw);
+      if (args.bias != nullptr && lane < kChunksPerWarp)
+        asm volatile("prefetch.global.L1 [%0];" ::"l"(args.bias + colw + lane * 32));
       if constexpr (EPI == kEpiBiasResid) {
         // Residual chunks 0 and 1 of this tile: fetched while the main loop still runs.
         if (lane == 0 && slab_live) {
@@ -368,17 +369,21 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
       if (tracing && local_tile == kTraceTile && e == 0 && lane == 0) args.trace[62] = global_timer_ns();
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) +
                              static_cast<uint32_t>(acc * BLOCK_N + half * (BLOCK_N / 2));
-#pragma unroll 1
+      // TMEM -> registers is software-pipelined: chunk c+1's tcgen05.ld is in flight while
+      // chunk c is converted, staged and stored (fully unrolled: the two register sets are
+      // named statically).
+      uint32_t vv[2][32];
+      tmem_ld_32x32b_x32(taddr, vv[0]);
+#pragma unroll
       for (int c = 0; c < kChunksPerWarp; ++c) {
+        uint32_t(&v)[32] = vv[c & 1];
         const int col0 = colw + c * 32;
         const uint32_t b = chunk_ctr & 1u;
         const uint32_t sbuf = stg + b * Epi::kChunkBytes;
-        uint32_t v[32];
         const bool tr_chunk = tracing && local_tile == kTraceTile && e == 0 && lane == 0 && c < 4;
         if (tr_chunk) args.trace[66 + 8 * c] = global_timer_ns();
-        tmem_ld_32x32b_x32(taddr + static_cast<uint32_t>(c * 32), v);
-        float4 bn[8];
-        if (c + 1 < kChunksPerWarp) load_bias(bn, col0 + 32);
+        float4 bv[8];
+        load_bias(bv, col0);
         if (tr_chunk) args.trace[67 + 8 * c] = global_timer_ns();
         if constexpr (EPI != kEpiBiasResid) {
           // the store issued from this slot two chunks ago must have drained it
@@ -388,7 +393,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
         if (tr_chunk) args.trace[68 + 8 * c] = global_timer_ns();
         tmem_ld_wait();
         if (tr_chunk) args.trace[69 + 8 * c] = global_timer_ns();
-        if (c == kChunksPerWarp - 1) {
+        if (c + 1 < kChunksPerWarp) {
+          tmem_ld_32x32b_x32(taddr + static_cast<uint32_t>((c + 1) * 32), vv[(c + 1) & 1]);
+        } else {
           // accumulator fully read: hand the TMEM buffer back to the MMA issuer
           tcgen05_fence_before();
           __syncwarp();
@@ -397,95 +404,93 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
             else mbar_arrive(&tmem_empty_bar[acc]);
           }
         }
-        if (!slab_live) continue;  // dead slab: bias registers are never consumed
-        float f[32];
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          f[4 * j + 0] = fmaf(__uint_as_float(v[4 * j + 0]), args.acc_scale, bv[j].x);
-          f[4 * j + 1] = fmaf(__uint_as_float(v[4 * j + 1]), args.acc_scale, bv[j].y);
-          f[4 * j + 2] = fmaf(__uint_as_float(v[4 * j + 2]), args.acc_scale, bv[j].z);
-          f[4 * j + 3] = fmaf(__uint_as_float(v[4 * j + 3]), args.acc_scale, bv[j].w);
-        }
-        if constexpr (EPI == kEpiBiasGelu || EPI == kEpiBiasGeluE4m3) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) f[j] = gelu_erf(f[j]);
-        }
-        if constexpr (EPI == kEpiBiasResid) {
-          // 32 rows x 128 B, SWIZZLE_128B: 16-byte chunk j of row r sits at j ^ (r & 7)
-          mbar_wait(&my_resid_bar[b], (chunk_ctr >> 1) & 1u);
-          const uint32_t rowa = sbuf + static_cast<uint32_t>(lane) * 128u;
+        if (slab_live) {  // dead slab (rows >= M): nothing to convert or store
+          float f[32];
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
-            const uint32_t a = rowa + (static_cast<uint32_t>(j ^ (lane & 7)) << 4);
-            const float4 r = ld_shared_f4(a);
-            st_shared_v4(a, __float_as_uint(f[4 * j] + r.x), __float_as_uint(f[4 * j + 1] + r.y),
-                         __float_as_uint(f[4 * j + 2] + r.z), __float_as_uint(f[4 * j + 3] + r.w));
+            f[4 * j + 0] = fmaf(__uint_as_float(v[4 * j + 0]), args.acc_scale, bv[j].x);
+            f[4 * j + 1] = fmaf(__uint_as_float(v[4 * j + 1]), args.acc_scale, bv[j].y);
+            f[4 * j + 2] = fmaf(__uint_as_float(v[4 * j + 2]), args.acc_scale, bv[j].z);
+            f[4 * j + 3] = fmaf(__uint_as_float(v[4 * j + 3]), args.acc_scale, bv[j].w);
           }
-        } else if constexpr (EPI == kEpiBiasAccum) {
-          // 32 rows x 128 B, SWIZZLE_128B; added to the output in place by the TMA reduce below
-          const uint32_t rowa = sbuf + static_cast<uint32_t>(lane) * 128u;
+          if constexpr (EPI == kEpiBiasGelu || EPI == kEpiBiasGeluE4m3) {
 #pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const uint32_t a = rowa + (static_cast<uint32_t>(j ^ (lane & 7)) << 4);
-            st_shared_v4(a, __float_as_uint(f[4 * j]), __float_as_uint(f[4 * j + 1]), __float_as_uint(f[4 * j + 2]),
-                         __float_as_uint(f[4 * j + 3]));
+            for (int j = 0; j < 32; ++j) f[j] = gelu_erf(f[j]);
           }
-        } else if constexpr (EPI == kEpiBiasGeluE4m3) {
-          // 32 rows x 32 B, no swizzle
-          const float s = args.out_inv_scale;
-          const uint32_t rowa = sbuf + static_cast<uint32_t>(lane) * 32u;
-#pragma unroll
-          for (int j = 0; j < 2; ++j) {
-            uint32_t w[4];
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-              const int o = 16 * j + 4 * i;
-              w[i] = pack_e4m3x4(f[o] * s, f[o + 1] * s, f[o + 2] * s, f[o + 3] * s);
-            }
-            st_shared_v4(rowa + static_cast<uint32_t>(j << 4), w[0], w[1], w[2], w[3]);
-          }
-        } else {
-          // 32 rows x 64 B, SWIZZLE_64B: 16-byte chunk j of row r sits at j ^ ((r >> 1) & 3)
-          const uint32_t rowa = sbuf + static_cast<uint32_t>(lane) * 64u;
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            const uint32_t a = rowa + (static_cast<uint32_t>(j ^ ((lane >> 1) & 3)) << 4);
-            st_shared_v4(a, pack_bf16(f[8 * j], f[8 * j + 1]), pack_bf16(f[8 * j + 2], f[8 * j + 3]),
-                         pack_bf16(f[8 * j + 4], f[8 * j + 5]), pack_bf16(f[8 * j + 6], f[8 * j + 7]));
-          }
-        }
-        if (tr_chunk) args.trace[70 + 8 * c] = global_timer_ns();
-        fence_proxy_async_smem();  // generic-proxy smem writes -> visible to the TMA engine
-        __syncwarp();
-        if (tr_chunk) args.trace[71 + 8 * c] = global_timer_ns();
-        if (lane == 0) {
-          if constexpr (EPI == kEpiBiasAccum)
-            tma_reduce_add_2d(&tmap_out, staging + e * Epi::kWarpBytes + b * Epi::kChunkBytes, col0, row0);
-          else
-            tma_store_2d(&tmap_out, staging + e * Epi::kWarpBytes + b * Epi::kChunkBytes, col0, row0);
-          tma_store_commit();
           if constexpr (EPI == kEpiBiasResid) {
-            if (c + 2 < kChunksPerWarp) {
-              // refill this slot with the residual chunk two ahead once the store has read it
-              tma_store_wait_read<0>();
-              mbar_arrive_expect_tx(&my_resid_bar[b], Epi::kChunkBytes);
-              tma_load_2d(staging + e * Epi::kWarpBytes + b * Epi::kChunkBytes, &tmap_resid,
-                          &my_resid_bar[b], col0 + 64, row0);
+            // 32 rows x 128 B, SWIZZLE_128B: 16-byte chunk j of row r sits at j ^ (r & 7)
+            mbar_wait(&my_resid_bar[b], (chunk_ctr >> 1) & 1u);
+            const uint32_t rowa = sbuf + static_cast<uint32_t>(lane) * 128u;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const uint32_t a = rowa + (static_cast<uint32_t>(j ^ (lane & 7)) << 4);
+              const float4 r = ld_shared_f4(a);
+              st_shared_v4(a, __float_as_uint(f[4 * j] + r.x), __float_as_uint(f[4 * j + 1] + r.y),
+                           __float_as_uint(f[4 * j + 2] + r.z), __float_as_uint(f[4 * j + 3] + r.w));
+            }
+          } else if constexpr (EPI == kEpiBiasAccum) {
+            // 32 rows x 128 B, SWIZZLE_128B; added to the output in place by the TMA reduce below
+            const uint32_t rowa = sbuf + static_cast<uint32_t>(lane) * 128u;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const uint32_t a = rowa + (static_cast<uint32_t>(j ^ (lane & 7)) << 4);
+              st_shared_v4(a, __float_as_uint(f[4 * j]), __float_as_uint(f[4 * j + 1]), __float_as_uint(f[4 * j + 2]),
+                           __float_as_uint(f[4 * j + 3]));
+            }
+          } else if constexpr (EPI == kEpiBiasGeluE4m3) {
+            // 32 rows x 32 B, no swizzle
+            const float sc = args.out_inv_scale;
+            const uint32_t rowa = sbuf + static_cast<uint32_t>(lane) * 32u;
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+              uint32_t w[4];
+#pragma unroll
+              for (int i = 0; i < 4; ++i) {
+                const int o = 16 * j + 4 * i;
+                w[i] = pack_e4m3x4(f[o] * sc, f[o + 1] * sc, f[o + 2] * sc, f[o + 3] * sc);
+              }
+              st_shared_v4(rowa + static_cast<uint32_t>(j << 4), w[0], w[1], w[2], w[3]);
+            }
+          } else {
+            // 32 rows x 64 B, SWIZZLE_64B: 16-byte chunk j of row r sits at j ^ ((r >> 1) & 3)
+            const uint32_t rowa = sbuf + static_cast<uint32_t>(lane) * 64u;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const uint32_t a = rowa + (static_cast<uint32_t>(j ^ ((lane >> 1) & 3)) << 4);
+              st_shared_v4(a, pack_bf16(f[8 * j], f[8 * j + 1]), pack_bf16(f[8 * j + 2], f[8 * j + 3]),
+                           pack_bf16(f[8 * j + 4], f[8 * j + 5]), pack_bf16(f[8 * j + 6], f[8 * j + 7]));
             }
           }
+          if (tr_chunk) args.trace[70 + 8 * c] = global_timer_ns();
+          fence_proxy_async_smem();  // generic-proxy smem writes -> visible to the TMA engine
+          __syncwarp();
+          if (tr_chunk) args.trace[71 + 8 * c] = global_timer_ns();
+          if (lane == 0) {
+            if constexpr (EPI == kEpiBiasAccum)
+              tma_reduce_add_2d(&tmap_out, staging + e * Epi::kWarpBytes + b * Epi::kChunkBytes, col0, row0);
+            else
+              tma_store_2d(&tmap_out, staging + e * Epi::kWarpBytes + b * Epi::kChunkBytes, col0, row0);
+            tma_store_commit();
+            if constexpr (EPI == kEpiBiasResid) {
+              if (c + 2 < kChunksPerWarp) {
+                // refill this slot with the residual chunk two ahead once the store has read it
+                tma_store_wait_read<0>();
+                mbar_arrive_expect_tx(&my_resid_bar[b], Epi::kChunkBytes);
+                tma_load_2d(staging + e * Epi::kWarpBytes + b * Epi::kChunkBytes, &tmap_resid,
+                            &my_resid_bar[b], col0 + 64, row0);
+              }
+            }
+          }
+          __syncwarp();
+          if (tr_chunk) args.trace[72 + 8 * c] = global_timer_ns();
+          ++chunk_ctr;  // counts live chunks only: slot = ctr & 1, residual-barrier parity = ctr >> 1
         }
-        __syncwarp();
-        if (tr_chunk) args.trace[72 + 8 * c] = global_timer_ns();
-        if (c + 1 < kChunksPerWarp) {
-#pragma unroll
-          for (int j = 0; j < 8; ++j) bv[j] = bn[j];
-        }
-        if (tr_chunk) args.trace[73 + 8 * c] = global_timer_ns();
-        ++chunk_ctr;  // counts live chunks only: slot = ctr & 1, residual-barrier parity = ctr >> 1
       }
       if (tracing && local_tile == kTraceTile && e == 0 && lane == 0) args.trace[63] = global_timer_ns();
     }
-    if (lane == 0) tma_store_wait<0>();  // all bulk stores of this warp are complete
+    // the staging slots must outlive the bulk stores' smem reads; their global writes are
+    // complete (and visible) at grid completion like any other store
+    if (lane == 0) tma_store_wait_read<0>();
     __syncwarp();
   }
 

@@ -13,11 +13,14 @@ from starpu_inference_server_b200 import capi  # noqa: E402
 SHAPES = {"qkv": (2304, 768, 0), "attn_out": (768, 768, 2), "ffn1": (3072, 768, 1), "ffn2": (768, 3072, 2)}
 
 
+TILE = int(sys.argv[1]) if len(sys.argv) > 1 else 0  # local tile whose epilogue is stamped
+
+
 def main():
     L = capi.lib()
     M = 4096
     for name, (N, K, epi) in SHAPES.items():
-        for cg, bn in ((1, 256 if N != 768 else 192), (2, 256)):
+        for cg, bn in ((2, 256 if N != 768 else 192),):
             a = (torch.randn(M, K, device="cuda") * 0.5).to(torch.bfloat16)
             w = (torch.randn(N, K, device="cuda") * 0.05).to(torch.bfloat16)
             bias = torch.randn(N, device="cuda")
@@ -26,7 +29,7 @@ def main():
             s = torch.cuda.Stream()
             with torch.cuda.stream(s):
                 for it in range(6):  # last launch is the traced one, after 5 back-to-back warm launches
-                    L.spu_debug_gemm_trace(tr.data_ptr() if it == 5 else None, 2 * (cg == 2) + 4)
+                    L.spu_debug_gemm_trace(tr.data_ptr() if it == 5 else None, (2 * (cg == 2) + 4) | (TILE << 16))
                     capi.check(L.spu_gemm_bf16_cfg_async(capi.ptr(a), capi.ptr(w), capi.ptr(bias),
                                                          capi.ptr(out) if epi == 2 else None, capi.ptr(out), M, N, K,
                                                          epi, cg, bn, capi.stream_ptr(s)))
