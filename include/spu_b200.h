@@ -59,6 +59,13 @@ typedef struct spu_bert_desc {
 #define SPU_PREC_FP8_E4M3 1u /* per-tensor scaled FP8 GEMM inputs (QKV/out/FFN) */
 /* FP8 in the first n encoder layers only, bf16 GEMMs in the rest (n = 0 or >= layers: all) */
 #define SPU_PREC_FP8_LAYERS(n) (SPU_PREC_FP8_E4M3 | ((uint32_t)(n) << 8))
+/* Warm-up capture in place (src/core/warmup.cpp:225-299 runs fixed-worker jobs so that every
+ * worker has executed once before traffic arrives): with this flag spu_bert_forward_async
+ * captures a CUDA graph the second time it sees the same (workspace, ids, mask, out, batch,
+ * seq) tuple -- StarPU hands a worker the same device buffers for the same slot handles, so
+ * tuples recur -- and replays it from then on.  Capture is thread-local stream capture on the
+ * caller's stream: no synchronisation, no allocation visible to other workers. */
+#define SPU_FORWARD_AUTO_GRAPH (1u << 16)
 
 /* Number of weight tensors spu_bert_replica_create expects: 5 + 16*layers, in the
  * order of the HF state dict restated in oracle/bert_oracle.py:weight_names()

@@ -16,6 +16,7 @@ SPU_OK = 0
 SPU_ERR_INVALID, SPU_ERR_CUDA, SPU_ERR_CAPACITY, SPU_ERR_UNSUPPORTED, SPU_ERR_NOMEM = 1, 2, 3, 4, 5
 SPU_EPI_BIAS, SPU_EPI_BIAS_GELU, SPU_EPI_BIAS_RESID = 0, 1, 2
 SPU_PREC_BF16, SPU_PREC_FP8_E4M3 = 0, 1
+SPU_FORWARD_AUTO_GRAPH = 1 << 16  # capture a CUDA graph on the second sighting of a pointer tuple
 STAGE_NAMES = ["embed_ln", "gemm_qkv", "attention", "gemm_attn_out", "ln1", "gemm_ffn1", "gemm_ffn2", "ln2"]
 
 # every symbol include/spu_b200.h declares (checked by tests/test_capi_symbols.py)

@@ -336,8 +336,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
       const int row0 = m_blk * kTileM + static_cast<int>(cta_rank) * kRowsPerCta + q * 32;
       const int colw = n_blk * BLOCK_N + half * (BLOCK_N / 2);  // first column of this warp
       const bool slab_live = row0 < args.M;  // TMA clips partial slabs; dead ones are skipped
-      // Bias: warp-uniform 128-bit loads (one broadcast each) issued at the top of every
-      // chunk; the tile's whole bias slice is pulled into L1 here, while the main loop runs.
+      // Bias: warp-uniform 128-bit loads (one broadcast each).  Chunk c+1's bias is requested
+      // into the same registers right after chunk c's FMAs consumed them, so its L2 latency
+      // hides behind the staging / fence / store of chunk c.
       auto load_bias = [&](float4 (&dst)[8], int col) {
         if (args.bias != nullptr) {
           const float4 *b4 = reinterpret_cast<const float4 *>(args.bias + col);
@@ -348,8 +349,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
           for (int j = 0; j < 8; ++j) dst[j] = make_float4(0.f, 0.f, 0.f, 0.f);
         }
       };
-      if (args.bias != nullptr && lane < kChunksPerWarp)
-        asm volatile("prefetch.global.L1 [%0];" ::"l"(args.bias + colw + lane * 32));
+      float4 bv[8];
+      load_bias(bv, colw);  // chunk 0, while the main loop still runs
       if constexpr (EPI == kEpiBiasResid) {
         // Residual chunks 0 and 1 of this tile: fetched while the main loop still runs.
         if (lane == 0 && slab_live) {
@@ -382,8 +383,6 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
         const uint32_t sbuf = stg + b * Epi::kChunkBytes;
         const bool tr_chunk = tracing && local_tile == kTraceTile && e == 0 && lane == 0 && c < 4;
         if (tr_chunk) args.trace[66 + 8 * c] = global_timer_ns();
-        float4 bv[8];
-        load_bias(bv, col0);
         if (tr_chunk) args.trace[67 + 8 * c] = global_timer_ns();
         if constexpr (EPI != kEpiBiasResid) {
           // the store issued from this slot two chunks ago must have drained it
@@ -413,6 +412,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
             f[4 * j + 2] = fmaf(__uint_as_float(v[4 * j + 2]), args.acc_scale, bv[j].z);
             f[4 * j + 3] = fmaf(__uint_as_float(v[4 * j + 3]), args.acc_scale, bv[j].w);
           }
+          if (c + 1 < kChunksPerWarp) load_bias(bv, col0 + 32);
           if constexpr (EPI == kEpiBiasGelu || EPI == kEpiBiasGeluE4m3) {
 #pragma unroll
             for (int j = 0; j < 32; ++j) f[j] = gelu_erf(f[j]);

@@ -318,7 +318,8 @@ extern "C" spu_status spu_bert_replica_create(const spu_bert_desc *desc, const f
               SPU_ERR_UNSUPPORTED, "replica_create: hidden/ffn must be multiples of 64, hidden <= 1024");
   SPU_REQUIRE(max_batch > 0 && max_seq > 0 && max_seq <= desc->max_pos && n_workspaces > 0,
               SPU_ERR_INVALID, "replica_create: bad capacity");
-  SPU_REQUIRE((flags & ~(SPU_PREC_FP8_E4M3 | 0xff00u)) == 0 && ((flags & SPU_PREC_FP8_E4M3) || flags == 0),
+  SPU_REQUIRE((flags & ~(SPU_PREC_FP8_E4M3 | 0xff00u | SPU_FORWARD_AUTO_GRAPH)) == 0 &&
+                  ((flags & SPU_PREC_FP8_E4M3) || (flags & 0xff00u) == 0),
               SPU_ERR_UNSUPPORTED, "replica_create: unsupported precision flag");
   if (flags & SPU_PREC_FP8_E4M3)
     SPU_REQUIRE(desc->hidden % 128 == 0 && desc->ffn % 128 == 0, SPU_ERR_UNSUPPORTED,
@@ -362,6 +363,8 @@ extern "C" spu_status spu_replica_destroy(spu_replica *r) {
   return SPU_OK;
 }
 
+constexpr size_t kMaxAutoGraphs = 64;  // per workspace (a worker sees pool_size slot tuples)
+
 extern "C" spu_status spu_bert_forward_async(spu_replica *r, int32_t ws_idx, const int64_t *ids,
                                              const int64_t *mask, int32_t batch, int32_t seq,
                                              float *out, void *stream) {
@@ -373,6 +376,32 @@ extern "C" spu_status spu_bert_forward_async(spu_replica *r, int32_t ws_idx, con
       SPU_CUDA_TRY(cudaGraphLaunch(g.exec, as_stream(stream)));
       return SPU_OK;
     }
+  if ((r->flags & SPU_FORWARD_AUTO_GRAPH) != 0 && ws.graphs.size() < kMaxAutoGraphs) {
+    bool seen = false;
+    for (const GraphKey &k : ws.seen) seen = seen || k == key;
+    if (seen) {
+      // second sighting: kernel attributes are set and caches warm from the eager pass
+      cudaStream_t s = as_stream(stream);
+      SPU_CUDA_TRY(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
+      spu_status st = enqueue_forward(r, ws, ids, mask, batch, seq, out, s);
+      cudaGraph_t graph = nullptr;
+      cudaError_t e = cudaStreamEndCapture(s, &graph);
+      if (st != SPU_OK) {
+        if (graph) cudaGraphDestroy(graph);
+        return st;
+      }
+      SPU_CUDA_TRY(e);
+      CapturedGraph cg;
+      cg.key = key;
+      e = cudaGraphInstantiate(&cg.exec, graph, 0);
+      cudaGraphDestroy(graph);
+      SPU_CUDA_TRY(e);
+      ws.graphs.push_back(cg);
+      SPU_CUDA_TRY(cudaGraphLaunch(cg.exec, s));
+      return SPU_OK;
+    }
+    if (ws.seen.size() < 4 * kMaxAutoGraphs) ws.seen.push_back(key);
+  }
   return enqueue_forward(r, ws, ids, mask, batch, seq, out, as_stream(stream));
 }
 

@@ -88,6 +88,7 @@ struct Workspace {
   std::vector<LayerPlans> plans;
   std::vector<LayerPlans> plans8;
   std::vector<CapturedGraph> graphs;
+  std::vector<GraphKey> seen;  // SPU_FORWARD_AUTO_GRAPH: tuples run eagerly once so far
 };
 
 struct VitState;  // vit.cu

@@ -174,6 +174,34 @@ def test_graph_capture_replays_identically(base):
     assert torch.equal(out, eager)
 
 
+def test_auto_graph_on_second_sighting(spu):
+    """SPU_FORWARD_AUTO_GRAPH: first call eager, second call captures + replays, later calls
+    replay; new input CONTENT in the same buffers is honoured; every result bit-equals eager."""
+    from oracle import bert_oracle as bo
+    from starpu_inference_server_b200.bert import BertReplica
+
+    w = bo.make_weights(bo.BERT_TINY, 0)
+    plain = BertReplica(w, max_batch=4, max_seq=128)
+    auto = BertReplica(w, max_batch=4, max_seq=128, flags=spu.SPU_FORWARD_AUTO_GRAPH)
+    ids_d = torch.zeros(4, 128, dtype=torch.int64, device="cuda")
+    mask_d = torch.ones(4, 128, dtype=torch.int64, device="cuda")
+    out_a = torch.zeros(4, 128, bo.BERT_TINY.hidden, device="cuda")
+    out_p = torch.zeros_like(out_a)
+    s = torch.cuda.Stream()
+    for it in range(4):
+        ids, mask = bo.make_inputs(bo.BERT_TINY, 4, 128, seed=300 + it, min_len=16)
+        with torch.cuda.stream(s):
+            ids_d.copy_(torch.from_numpy(ids).cuda(), non_blocking=False)
+            mask_d.copy_(torch.from_numpy(mask).cuda(), non_blocking=False)
+            out_a.fill_(float("nan"))
+            auto.forward_async(ids_d, mask_d, out_a, stream=s)
+            plain.forward_async(ids_d, mask_d, out_p, stream=s)
+        torch.cuda.synchronize()
+        assert torch.equal(out_a, out_p), f"iteration {it}"
+    plain.close()
+    auto.close()
+
+
 def test_capacity_and_argument_errors(base, spu):
     bo, w, r = base
     ids = torch.zeros(65, 512, dtype=torch.int64, device="cuda")
