@@ -257,6 +257,12 @@ spu_status spu_gemm_bf16_cfg_async(const void *A, const void *W, const float *bi
 spu_status spu_attention_async(const void *qkv, const float *mask_bias, void *ctx,
                                int32_t batch, int32_t seq, int32_t heads,
                                void *stream);
+/* Same, with the implementation and output format selectable (tests / tools):
+ * impl 0 = default, 1 = tcgen05/TMEM kernel, 2 = mma.sync kernel; out_e4m3 != 0 writes
+ * ctx as e4m3 bytes of ctx * q_inv_scale (the FP8 variant's attention-output operand). */
+spu_status spu_attention_cfg_async(const void *qkv, const float *mask_bias, void *ctx,
+                                   int32_t batch, int32_t seq, int32_t heads, int32_t impl,
+                                   int32_t out_e4m3, float q_inv_scale, void *stream);
 
 /* Row LayerNorm: y = LN(x) * gamma + beta over the last dim (fp32 statistics).
  * x fp32 [rows, hidden]; writes fp32 out_f32 (may be NULL, may alias x) and bf16

@@ -28,7 +28,7 @@ NVCC_FLAGS = ARCH + ["-std=c++17", "-O3", "-lineinfo", "-Xcompiler", "-fPIC",
                      "--expt-relaxed-constexpr",
                      "-I", os.path.join(ROOT, "include")]
 
-CUDA_SOURCES = ["replica.cu", "gemm_sm100.cu", "attention.cu", "rowops.cu", "vit.cu"]
+CUDA_SOURCES = ["replica.cu", "gemm_sm100.cu", "attention.cu", "attention_sm100.cu", "rowops.cu", "vit.cu"]
 HOST_SOURCES = ["inference_codelet.cpp", "slot_pools.cpp", "task_runner.cpp", "mini_starpu.cpp", "host_capi.cpp",
                 "host_test_hooks.cpp"]
 CXX = os.environ.get("CXX", "g++")

@@ -24,7 +24,7 @@ SYMBOLS = [
     "spu_bert_replica_create", "spu_replica_destroy", "spu_bert_forward_async",
     "spu_bert_forward_launch_count", "spu_bert_forward_capture", "spu_bert_forward_profiled", "spu_gather_pad_mask_async",
     "spu_gather_segments_async", "spu_scatter_segments_async", "spu_gemm_bf16_async", "spu_gemm_bf16_cfg_async",
-    "spu_attention_async", "spu_layernorm_async", "spu_bert_embed_async", "spu_affine_f32_async",
+    "spu_attention_async", "spu_attention_cfg_async", "spu_layernorm_async", "spu_bert_embed_async", "spu_affine_f32_async",
     "spu_last_error", "spu_abi_version", "spu_device_count", "spu_device_is_sm100",
     "spu_bert_output_bytes", "spu_vit_replica_create", "spu_vit_forward_async", "spu_vit_input_bytes",
     "spu_vit_output_bytes", "spu_bert_stage_chain_ms", "spu_bert_calibrate_fp8", "spu_bert_fp8_scales",
@@ -78,6 +78,7 @@ def lib():
     L.spu_gemm_bf16_async.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, i32, vp]
     L.spu_gemm_bf16_cfg_async.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp]
     L.spu_attention_async.argtypes = [vp, vp, vp, i32, i32, i32, vp]
+    L.spu_attention_cfg_async.argtypes = [vp, vp, vp, i32, i32, i32, i32, i32, f32, vp]
     L.spu_layernorm_async.argtypes = [vp, vp, vp, f32, vp, vp, i32, i32, vp]
     L.spu_bert_embed_async.argtypes = [vp, vp, vp, vp, vp, vp, vp, f32, i32, vp, vp, vp, i32, i32, i32, vp]
     L.spu_affine_f32_async.argtypes = [vp, vp, u64, f32, f32, vp]

@@ -271,8 +271,8 @@ attention_kernel(const __nv_bfloat16 *__restrict__ qkv, const float *__restrict_
 
 }  // namespace
 
-spu_status attention_launch(const void *qkv, const float *mask_bias, void *ctx, int batch, int seq,
-                            int heads, cudaStream_t stream, bool out_e4m3, float q_inv_scale) {
+spu_status attention_mma_launch(const void *qkv, const float *mask_bias, void *ctx, int batch, int seq,
+                                int heads, cudaStream_t stream, bool out_e4m3, float q_inv_scale) {
   SPU_REQUIRE(qkv && ctx, SPU_ERR_INVALID, "attention: null argument");  // mask_bias may be null (no mask)
   SPU_REQUIRE(batch > 0 && seq > 0 && heads > 0, SPU_ERR_INVALID, "attention: empty shape");
   SPU_REQUIRE(batch <= 65535 && heads <= 65535, SPU_ERR_CAPACITY, "attention: grid too large");
@@ -286,6 +286,21 @@ spu_status attention_launch(const void *qkv, const float *mask_bias, void *ctx, 
                             1.f));
   SPU_CUDA_TRY(cudaGetLastError());
   return SPU_OK;
+}
+
+// Default: the tcgen05/TMEM kernel (attention_sm100.cu) wherever it is the faster one on B200
+// (profiles/r06_attention.md): single-tile sequences (S <= 128); longer sequences stay on this
+// file's mma.sync kernel.  SPU_ATTN=mma / SPU_ATTN=tc force one implementation for every shape.
+spu_status attention_launch(const void *qkv, const float *mask_bias, void *ctx, int batch, int seq,
+                            int heads, cudaStream_t stream, bool out_e4m3, float q_inv_scale) {
+  static const int forced = [] {
+    const char *e = std::getenv("SPU_ATTN");
+    if (e == nullptr) return 0;
+    return std::string(e) == "mma" ? 2 : (std::string(e) == "tc" ? 1 : 0);
+  }();
+  const bool tc = forced == 1 || (forced == 0 && seq <= 128);
+  return tc ? attention_tc_launch(qkv, mask_bias, ctx, batch, seq, heads, stream, out_e4m3, q_inv_scale)
+            : attention_mma_launch(qkv, mask_bias, ctx, batch, seq, heads, stream, out_e4m3, q_inv_scale);
 }
 
 }  // namespace spu

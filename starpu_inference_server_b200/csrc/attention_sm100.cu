@@ -1,0 +1,416 @@
+// tcgen05/TMEM fused masked-softmax attention for head_dim 64 (BERT-base / ViT-L heads), sm_100a.
+//   ctx[b, q, h, :] = softmax_k( q.k / 8 + mask_bias[b, k] ) . v
+// One CTA = 128 query rows of one (batch, head), 128 threads.  Q, K and V tiles arrive by TMA
+// (3-D map over qkv viewed as [B, S, 3H]: rows past the end of a sequence are zero-filled, so
+// ragged S needs no special load path) into 128B-swizzled smem.  S = Q K^T is ONE 128x128x64
+// tcgen05.mma chain into TMEM; each thread then owns one query row (tcgen05.ld 32x32b), so the
+// row max / row sum need no shuffles at all; P goes back to smem as a K-major bf16 operand and
+// O = P V runs as a second tcgen05.mma chain whose B operand is V as loaded (MN-major
+// descriptor, no transpose pass).  Scores and probabilities never touch HBM.
+//   SINGLE (S <= 128): P overwrites the dead Q|K tiles and O reuses the TMEM columns of S:
+//          48 KB smem + 128 TMEM columns per CTA -> 4 CTAs per SM, all (b, h) of a b<=49
+//          batch resident at once (the kernel is latency-bound there, not throughput-bound).
+//   MULTI  (S  > 128): K/V double-buffered (next tile's TMA overlaps this tile's softmax),
+//          online softmax with the running O in registers; 2 CTAs per SM.
+//
+// Restates the attention block of HF BertSelfAttention / torchvision MultiheadAttention that
+// LibTorch executes inside Module::forward (/root/reference/src/core/starpu_setup.cpp:610);
+// oracle: oracle/bert_oracle.py:bert_forward (scores/softmax/ctx lines).
+#include <cuda.h>
+
+#include <mutex>
+
+#include "replica.cuh"
+
+namespace spu {
+namespace {
+
+constexpr int kHeadDim = 64;
+constexpr int kTile = 128;            // query rows per CTA == keys per KV tile
+constexpr int kThreads = 128;
+constexpr int kTileBytes = kTile * kHeadDim * 2;  // 16 KB: 128 rows x 128 B, SWIZZLE_128B
+constexpr float kLog2e = 1.4426950408889634f;
+
+template <bool MULTI>
+struct AttnCfg {
+  static constexpr int kBufs = MULTI ? 2 : 1;
+  static constexpr int kOffQ = 0;
+  static constexpr int kOffK = kTileBytes;
+  static constexpr int kOffV = kOffK + kBufs * kTileBytes;
+  // SINGLE: P (2 x 16 KB, keys 0-63 | 64-127) overwrites Q|K once S has been read out of TMEM
+  static constexpr int kOffP = MULTI ? kOffV + kBufs * kTileBytes : 0;
+  static constexpr int kTiles = MULTI ? kOffP + 2 * kTileBytes : kOffV + kTileBytes;
+  static constexpr int kOffBias = kTiles;                       // kBufs x 128 fp32
+  static constexpr int kOffBars = kOffBias + kBufs * kTile * 4;  // 6 mbarriers + tmem slot
+  static constexpr int kSmemBytes = kOffBars + 64 + 1024;        // + 1024-alignment slack
+  static constexpr uint32_t kTmemCols = MULTI ? 256 : 128;
+  static constexpr uint32_t kTmemO = MULTI ? 128 : 0;            // SINGLE: O aliases S
+};
+
+__device__ __forceinline__ void tma_load_3d(void *smem_dst, const void *tmap, uint64_t *bar, int32_t c0,
+                                            int32_t c1, int32_t c2) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4, %5}], [%2];" ::"r"(smem_u32(smem_dst)),
+      "l"(reinterpret_cast<uint64_t>(tmap)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
+      : "memory");
+}
+
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+__device__ __forceinline__ uint16_t pack_e4m3x2(float lo, float hi) {
+  uint16_t r;
+  asm("cvt.rn.satfinite.e4m3x2.f32 %0, %1, %2;" : "=h"(r) : "f"(hi), "f"(lo));
+  return r;
+}
+
+// byte offset of 16-byte chunk `chunk` of row `row` inside a 128-row x 128 B SWIZZLE_128B tile
+__device__ __forceinline__ uint32_t sw128_off(int row, int chunk) {
+  return static_cast<uint32_t>(row * 128 + ((chunk ^ (row & 7)) << 4));
+}
+
+// Instruction descriptor: bf16 x bf16 -> fp32, M x N, B operand MN-major when b_mn (bit 16).
+__host__ __device__ constexpr uint32_t attn_idesc(uint32_t m, uint32_t n, bool b_mn) {
+  return make_idesc(1u, m, n) | (b_mn ? (1u << 16) : 0u);
+}
+
+// One thread = one query row of S in TMEM (128 fp32 columns), read in four 32-column chunks with the
+// next chunk's tcgen05.ld in flight while the current one is consumed.
+template <typename F>
+__device__ __forceinline__ void for_each_chunk(uint32_t tmem_row, F &&f) {
+  uint32_t va[32], vb[32];
+  tmem_ld_32x32b_x32(tmem_row, va);
+  tmem_ld_wait();
+  tmem_ld_32x32b_x32(tmem_row + 32, vb);
+  f(0, va);
+  tmem_ld_wait();
+  tmem_ld_32x32b_x32(tmem_row + 64, va);
+  f(1, vb);
+  tmem_ld_wait();
+  tmem_ld_32x32b_x32(tmem_row + 96, vb);
+  f(2, va);
+  tmem_ld_wait();
+  f(3, vb);
+}
+
+// max_k (s*scale + bias_k); four independent accumulators keep the FMNMX chain short
+template <bool BIAS>
+__device__ __forceinline__ float row_max(uint32_t tmem_row, const float *bias, float scale) {
+  float m0 = -INFINITY, m1 = -INFINITY, m2 = -INFINITY, m3 = -INFINITY;
+  for_each_chunk(tmem_row, [&](int c, const uint32_t(&v)[32]) {
+#pragma unroll
+    for (int i = 0; i < 32; i += 4) {
+      if constexpr (BIAS) {
+        const float4 bz = *reinterpret_cast<const float4 *>(bias + c * 32 + i);
+        m0 = fmaxf(m0, fmaf(__uint_as_float(v[i + 0]), scale, bz.x));
+        m1 = fmaxf(m1, fmaf(__uint_as_float(v[i + 1]), scale, bz.y));
+        m2 = fmaxf(m2, fmaf(__uint_as_float(v[i + 2]), scale, bz.z));
+        m3 = fmaxf(m3, fmaf(__uint_as_float(v[i + 3]), scale, bz.w));
+      } else {
+        m0 = fmaxf(m0, __uint_as_float(v[i + 0]));
+        m1 = fmaxf(m1, __uint_as_float(v[i + 1]));
+        m2 = fmaxf(m2, __uint_as_float(v[i + 2]));
+        m3 = fmaxf(m3, __uint_as_float(v[i + 3]));
+      }
+    }
+  });
+  const float m = fmaxf(fmaxf(m0, m1), fmaxf(m2, m3));
+  return BIAS ? m : m * scale;  // scale > 0
+}
+
+// p_k = 2^(s*scale + bias_k - m) -> bf16 into the two 64-key K-major SWIZZLE_128B tiles at s_p;
+// returns the fp32 row sum
+template <bool BIAS>
+__device__ __forceinline__ float row_exp(uint32_t tmem_row, const float *bias, float scale, float m, uint8_t *s_p,
+                                         int row) {
+  float l0 = 0.f, l1 = 0.f, l2 = 0.f, l3 = 0.f;
+  const float neg_m = -m;
+  for_each_chunk(tmem_row, [&](int c, const uint32_t(&v)[32]) {
+    uint8_t *p_half = s_p + (c >> 1) * kTileBytes;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      float p[8];
+#pragma unroll
+      for (int e = 0; e < 8; e += 4) {
+        const int i = q * 8 + e;
+        if constexpr (BIAS) {
+          const float4 bz = *reinterpret_cast<const float4 *>(bias + c * 32 + i);
+          p[e + 0] = ex2_approx(fmaf(__uint_as_float(v[i + 0]), scale, bz.x) - m);
+          p[e + 1] = ex2_approx(fmaf(__uint_as_float(v[i + 1]), scale, bz.y) - m);
+          p[e + 2] = ex2_approx(fmaf(__uint_as_float(v[i + 2]), scale, bz.z) - m);
+          p[e + 3] = ex2_approx(fmaf(__uint_as_float(v[i + 3]), scale, bz.w) - m);
+        } else {
+          p[e + 0] = ex2_approx(fmaf(__uint_as_float(v[i + 0]), scale, neg_m));
+          p[e + 1] = ex2_approx(fmaf(__uint_as_float(v[i + 1]), scale, neg_m));
+          p[e + 2] = ex2_approx(fmaf(__uint_as_float(v[i + 2]), scale, neg_m));
+          p[e + 3] = ex2_approx(fmaf(__uint_as_float(v[i + 3]), scale, neg_m));
+        }
+        l0 += p[e + 0];
+        l1 += p[e + 1];
+        l2 += p[e + 2];
+        l3 += p[e + 3];
+      }
+      *reinterpret_cast<uint4 *>(p_half + sw128_off(row, (c & 1) * 4 + q)) =
+          make_uint4(pack_bf16(p[0], p[1]), pack_bf16(p[2], p[3]), pack_bf16(p[4], p[5]), pack_bf16(p[6], p[7]));
+    }
+  });
+  return (l0 + l1) + (l2 + l3);
+}
+
+template <bool MULTI, bool OUT_E4M3>
+__global__ void __launch_bounds__(kThreads, MULTI ? 2 : 4)
+attention_tc_kernel(const __grid_constant__ CUtensorMap tm_qkv, const float *__restrict__ mask_bias,
+                    void *__restrict__ ctx_out, int seq, int heads, float q_inv_scale) {
+  using Cfg = AttnCfg<MULTI>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t *s_q = smem + Cfg::kOffQ;
+  uint8_t *s_k = smem + Cfg::kOffK;
+  uint8_t *s_v = smem + Cfg::kOffV;
+  uint8_t *s_p = smem + Cfg::kOffP;
+  float *s_bias = reinterpret_cast<float *>(smem + Cfg::kOffBias);
+  uint64_t *bars = reinterpret_cast<uint64_t *>(smem + Cfg::kOffBars);
+  uint64_t *bar_k = bars, *bar_v = bars + 2, *bar_s = bars + 4, *bar_o = bars + 5;
+  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 6);
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int qt = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
+  const int hidden = heads * kHeadDim;
+  const int n_kv = MULTI ? (seq + kTile - 1) / kTile : 1;
+
+  // thread 0 gets the first loads in flight before anything else; warp 1 allocates TMEM meanwhile
+  if (tid == 0) {
+#pragma unroll
+    for (int i = 0; i < 6; ++i) mbar_init(bars + i, 1);
+    fence_barrier_init();
+    pdl_wait_prior_grid();  // qkv is written by the preceding GEMM
+    mbar_arrive_expect_tx(&bar_k[0], 2 * kTileBytes);
+    tma_load_3d(s_q, &tm_qkv, &bar_k[0], h * kHeadDim, qt * kTile, b);
+    tma_load_3d(s_k, &tm_qkv, &bar_k[0], hidden + h * kHeadDim, 0, b);
+    mbar_arrive_expect_tx(&bar_v[0], kTileBytes);
+    tma_load_3d(s_v, &tm_qkv, &bar_v[0], 2 * hidden + h * kHeadDim, 0, b);
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_slot, Cfg::kTmemCols);
+    tmem_relinquish();
+  }
+  pdl_wait_prior_grid();
+  pdl_launch_dependents();
+  tcgen05_fence_before();
+  __syncthreads();
+  tcgen05_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t tmem_row = tmem_base + (static_cast<uint32_t>(warp * 32) << 16);
+
+  constexpr uint32_t kIdescQK = attn_idesc(kTile, kTile, false);
+  constexpr uint32_t kIdescPV = attn_idesc(kTile, kHeadDim, true);
+  const float scale_log2 = 0.125f * kLog2e;  // 1/sqrt(64) folded into exp2
+  float m_run = -INFINITY, l_run = 0.f;
+  float o_run[kHeadDim];
+#pragma unroll
+  for (int i = 0; i < kHeadDim; ++i) o_run[i] = 0.f;
+
+  for (int j = 0; j < n_kv; ++j) {
+    const int buf = MULTI ? (j & 1) : 0;
+    float *bias = s_bias + buf * kTile;
+    // keys past the sequence end never contribute (-inf); masked keys get the additive bias
+    // the mask builder wrote (HF: (1-mask)*finfo.min), pre-multiplied by log2(e)
+    const int key = j * kTile + tid;
+    const float my_bias =
+        key < seq ? (mask_bias != nullptr ? mask_bias[static_cast<size_t>(b) * seq + key] * kLog2e : 0.f) : -INFINITY;
+    bias[tid] = my_bias;
+    if (tid == 0) {
+      if (MULTI && j + 1 < n_kv) {  // buffers of tile j-1 are free: its PV chain completed (bar_o)
+        const int nb = buf ^ 1;
+        mbar_arrive_expect_tx(&bar_k[nb], kTileBytes);
+        tma_load_3d(s_k + nb * kTileBytes, &tm_qkv, &bar_k[nb], hidden + h * kHeadDim, (j + 1) * kTile, b);
+        mbar_arrive_expect_tx(&bar_v[nb], kTileBytes);
+        tma_load_3d(s_v + nb * kTileBytes, &tm_qkv, &bar_v[nb], 2 * hidden + h * kHeadDim, (j + 1) * kTile, b);
+      }
+      // ---- S = Q K^T : 128 x 128 x 64 as four K=16 steps (32 B inside the swizzle atom) ----
+      mbar_wait(&bar_k[buf], (j >> 1) & 1);
+      tcgen05_fence_after();
+      const uint64_t dq = make_sw128_kmajor_desc(smem_u32(s_q));
+      const uint64_t dk = make_sw128_kmajor_desc(smem_u32(s_k + buf * kTileBytes));
+#pragma unroll
+      for (int k = 0; k < 4; ++k) umma_f16_ss(tmem_base, dq + 2 * k, dk + 2 * k, kIdescQK, k > 0);
+      umma_commit(bar_s);
+    }
+    // bias visible to every row owner; a tile without any bias (no padding, no tail) takes the
+    // cheaper softmax path below (block-uniform branch)
+    const bool has_bias = __syncthreads_or(my_bias != 0.f) != 0;
+    mbar_wait_warp(bar_s, j & 1);
+    tcgen05_fence_after();
+
+    // ---- pass 1: row max of s' = s*scale + bias (this thread owns query row `tid`) ----
+    const float mx = has_bias ? row_max<true>(tmem_row, bias, scale_log2) : row_max<false>(tmem_row, bias, scale_log2);
+    const float m_new = fmaxf(m_run, mx);
+    const float m_use = m_new == -INFINITY ? 0.f : m_new;
+    const float corr = ex2_approx(m_run - m_use);  // first tile: 2^-inf = 0
+    m_run = m_new;
+    // ---- pass 2: p = 2^(s' - m), row sum, P -> smem as the K-major bf16 A operand of P V ----
+    const float l_tile = has_bias ? row_exp<true>(tmem_row, bias, scale_log2, m_use, s_p, tid)
+                                  : row_exp<false>(tmem_row, bias, scale_log2, m_use, s_p, tid);
+    l_run = fmaf(l_run, corr, l_tile);
+    fence_proxy_async_smem();  // generic-proxy P stores -> visible to the tensor core's async proxy
+    tcgen05_fence_before();
+    __syncthreads();           // all of S read out of TMEM, all of P in smem
+
+    // ---- O_tile = P V : 128 x 64 x 128, V consumed as loaded (MN-major B, 16 keys = 2 KB per step) ----
+    if (tid == 0) {
+      tcgen05_fence_after();
+      mbar_wait(&bar_v[buf], (j >> 1) & 1);
+      const uint32_t v_addr = smem_u32(s_v + buf * kTileBytes);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const uint64_t dp = make_sw128_kmajor_desc(smem_u32(s_p + (k >> 2) * kTileBytes)) + 2 * (k & 3);
+        const uint64_t dv = make_sw128_kmajor_desc(v_addr + k * 2048);
+        umma_f16_ss(tmem_base + Cfg::kTmemO, dp, dv, kIdescPV, k > 0);
+      }
+      umma_commit(bar_o);
+    }
+    mbar_wait_warp(bar_o, j & 1);
+    tcgen05_fence_after();
+    {
+      uint32_t va[32], vb[32];
+      tmem_ld_32x32b_x32(tmem_row + Cfg::kTmemO, va);
+      tmem_ld_32x32b_x32(tmem_row + Cfg::kTmemO + 32, vb);
+      tmem_ld_wait();
+#pragma unroll
+      for (int i = 0; i < 32; ++i) {
+        o_run[i] = MULTI ? fmaf(o_run[i], corr, __uint_as_float(va[i])) : __uint_as_float(va[i]);
+        o_run[32 + i] = MULTI ? fmaf(o_run[32 + i], corr, __uint_as_float(vb[i])) : __uint_as_float(vb[i]);
+      }
+    }
+    tcgen05_fence_before();  // ordered before the next tile's MMAs overwrite S / O
+  }
+
+  // ---- normalise and store this thread's query row ----
+  const float inv = 1.f / l_run;
+  const int q_row = qt * kTile + tid;
+  const size_t tok0 = static_cast<size_t>(b) * seq;
+  if constexpr (OUT_E4M3) {
+    // per-tensor scaled e4m3 operand of the attention-output GEMM: 64 contiguous bytes per row
+    if (q_row < seq) {
+      uint8_t *dst = static_cast<uint8_t *>(ctx_out) + (tok0 + q_row) * hidden + h * kHeadDim;
+      const float s = inv * q_inv_scale;
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        uint32_t w[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const int i = c * 16 + e * 4;
+          const uint32_t lo = pack_e4m3x2(o_run[i] * s, o_run[i + 1] * s);
+          const uint32_t hi = pack_e4m3x2(o_run[i + 2] * s, o_run[i + 3] * s);
+          w[e] = lo | (hi << 16);
+        }
+        *reinterpret_cast<uint4 *>(dst + c * 16) = make_uint4(w[0], w[1], w[2], w[3]);
+      }
+    }
+  } else {
+    // stage this warp's 32 rows in the (dead) first P tile, then 128-bit coalesced stores:
+    // 4 full 128-byte rows per warp instruction
+    uint8_t *stage = s_p;
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+      const uint4 w = make_uint4(pack_bf16(o_run[c * 8 + 0] * inv, o_run[c * 8 + 1] * inv),
+                                 pack_bf16(o_run[c * 8 + 2] * inv, o_run[c * 8 + 3] * inv),
+                                 pack_bf16(o_run[c * 8 + 4] * inv, o_run[c * 8 + 5] * inv),
+                                 pack_bf16(o_run[c * 8 + 6] * inv, o_run[c * 8 + 7] * inv));
+      *reinterpret_cast<uint4 *>(stage + sw128_off(tid, c)) = w;
+    }
+    __syncwarp();
+    __nv_bfloat16 *ctx = static_cast<__nv_bfloat16 *>(ctx_out);
+#pragma unroll
+    for (int it = 0; it < 8; ++it) {
+      const int idx = lane + it * 32;
+      const int r = warp * 32 + (idx >> 3), c = idx & 7;
+      const int row = qt * kTile + r;
+      if (row < seq)
+        *reinterpret_cast<uint4 *>(ctx + (tok0 + row) * hidden + h * kHeadDim + c * 8) =
+            *reinterpret_cast<const uint4 *>(stage + sw128_off(r, c));
+    }
+  }
+
+  tcgen05_fence_before();
+  __syncthreads();
+  if (warp == 0) {
+    tcgen05_fence_after();
+    tmem_dealloc(tmem_base, Cfg::kTmemCols);
+  }
+}
+
+// ---- host side -----------------------------------------------------------------
+using EncodeTiledFn = CUresult (*)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                   const cuuint64_t *, const cuuint32_t *, const cuuint32_t *,
+                                   CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                   CUtensorMapFloatOOBfill);
+
+EncodeTiledFn attn_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void *p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  });
+  return fn;
+}
+
+template <bool MULTI, bool OUT_E4M3>
+spu_status launch_tc(const CUtensorMap &map, const float *mask_bias, void *ctx, int batch, int seq, int heads,
+                     cudaStream_t stream, float q_inv_scale) {
+  using Cfg = AttnCfg<MULTI>;
+  auto kern = attention_tc_kernel<MULTI, OUT_E4M3>;
+  static std::once_flag once;
+  static cudaError_t attr_err = cudaSuccess;
+  std::call_once(once, [&] {
+    attr_err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes);
+  });
+  SPU_CUDA_TRY(attr_err);
+  dim3 grid((seq + kTile - 1) / kTile, heads, batch);
+  SPU_CUDA_TRY(launch_pdl(kern, grid, dim3(kThreads), Cfg::kSmemBytes, stream, map, mask_bias, ctx, seq, heads,
+                          q_inv_scale));
+  SPU_CUDA_TRY(cudaGetLastError());
+  return SPU_OK;
+}
+
+}  // namespace
+
+// qkv: bf16 [batch*seq, 3*heads*64] (Q | K | V column blocks), ctx: bf16 or e4m3 [batch*seq, heads*64].
+spu_status attention_tc_launch(const void *qkv, const float *mask_bias, void *ctx, int batch, int seq, int heads,
+                               cudaStream_t stream, bool out_e4m3, float q_inv_scale) {
+  SPU_REQUIRE(qkv && ctx, SPU_ERR_INVALID, "attention: null argument");  // mask_bias may be null (no mask)
+  SPU_REQUIRE(batch > 0 && seq > 0 && heads > 0, SPU_ERR_INVALID, "attention: empty shape");
+  SPU_REQUIRE(batch <= 65535 && heads <= 65535, SPU_ERR_CAPACITY, "attention: grid too large");
+  SPU_REQUIRE((reinterpret_cast<uintptr_t>(qkv) & 15) == 0, SPU_ERR_INVALID, "attention: qkv must be 16-byte aligned");
+  EncodeTiledFn enc = attn_encode_fn();
+  SPU_REQUIRE(enc != nullptr, SPU_ERR_CUDA, "cuTensorMapEncodeTiled entry point unavailable");
+  // qkv viewed as [batch, seq, 3H]: a 128-row box that runs past a sequence end is zero-filled
+  const cuuint64_t ld = static_cast<cuuint64_t>(3) * heads * kHeadDim;
+  cuuint64_t gdim[3] = {ld, static_cast<cuuint64_t>(seq), static_cast<cuuint64_t>(batch)};
+  cuuint64_t gstride[2] = {ld * 2, ld * 2 * static_cast<cuuint64_t>(seq)};
+  cuuint32_t box[3] = {kHeadDim, kTile, 1};
+  cuuint32_t estride[3] = {1, 1, 1};
+  CUtensorMap map;
+  const CUresult r = enc(&map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void *>(qkv), gdim, gstride, box,
+                         estride, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                         CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("attention: cuTensorMapEncodeTiled failed with CUresult " + std::to_string(static_cast<int>(r)));
+    return SPU_ERR_CUDA;
+  }
+  if (seq <= kTile)
+    return out_e4m3 ? launch_tc<false, true>(map, mask_bias, ctx, batch, seq, heads, stream, q_inv_scale)
+                    : launch_tc<false, false>(map, mask_bias, ctx, batch, seq, heads, stream, 1.f);
+  return out_e4m3 ? launch_tc<true, true>(map, mask_bias, ctx, batch, seq, heads, stream, q_inv_scale)
+                  : launch_tc<true, false>(map, mask_bias, ctx, batch, seq, heads, stream, 1.f);
+}
+
+}  // namespace spu

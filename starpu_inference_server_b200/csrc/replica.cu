@@ -606,6 +606,16 @@ extern "C" spu_status spu_attention_async(const void *qkv, const float *mask_bia
   return attention_launch(qkv, mask_bias, ctx, batch, seq, heads, as_stream(stream));
 }
 
+extern "C" spu_status spu_attention_cfg_async(const void *qkv, const float *mask_bias, void *ctx,
+                                              int32_t batch, int32_t seq, int32_t heads, int32_t impl,
+                                              int32_t out_e4m3, float q_inv_scale, void *stream) {
+  if (impl == 1)
+    return attention_tc_launch(qkv, mask_bias, ctx, batch, seq, heads, as_stream(stream), out_e4m3 != 0, q_inv_scale);
+  if (impl == 2)
+    return attention_mma_launch(qkv, mask_bias, ctx, batch, seq, heads, as_stream(stream), out_e4m3 != 0, q_inv_scale);
+  return attention_launch(qkv, mask_bias, ctx, batch, seq, heads, as_stream(stream), out_e4m3 != 0, q_inv_scale);
+}
+
 extern "C" void spu_debug_gemm_trace(void *device_buf, int32_t cta) {
   gemm_set_trace(static_cast<unsigned long long *>(device_buf), cta);
 }

@@ -16,6 +16,11 @@ namespace spu {
 spu_status attention_launch(const void *qkv, const float *mask_bias, void *ctx, int batch, int seq,
                             int heads, cudaStream_t stream, bool out_e4m3 = false,
                             float q_inv_scale = 1.f);
+// the two implementations behind attention_launch (attention_sm100.cu: tcgen05; attention.cu: mma.sync)
+spu_status attention_tc_launch(const void *qkv, const float *mask_bias, void *ctx, int batch, int seq,
+                               int heads, cudaStream_t stream, bool out_e4m3, float q_inv_scale);
+spu_status attention_mma_launch(const void *qkv, const float *mask_bias, void *ctx, int batch, int seq,
+                                int heads, cudaStream_t stream, bool out_e4m3, float q_inv_scale);
 spu_status bert_embed_launch(const int64_t *ids, const int64_t *mask, const float *word,
                              const float *pos, const float *type0, const float *gamma,
                              const float *beta, float eps, int vocab, float *x_f32, void *x_bf16,

@@ -127,8 +127,12 @@ def _attn_ref(qkv, mask_bias, B, S, heads):
     return (torch.softmax(s, -1) @ v).transpose(1, 2).reshape(B * S, H)
 
 
-@pytest.mark.parametrize("B,S,heads", [(2, 128, 12), (1, 64, 2), (3, 200, 4), (2, 512, 12), (5, 16, 2), (1, 37, 1)])
-def test_attention_matches_fp32(spu, B, S, heads):
+_ATTN_IMPLS = [(1, "tcgen05"), (2, "mma.sync")]
+_ATTN_SHAPES = [(2, 128, 12), (1, 64, 2), (3, 200, 4), (2, 512, 12), (5, 16, 2), (1, 37, 1), (2, 129, 3), (3, 197, 16),
+                (2, 256, 2), (1, 389, 2), (1, 1, 1), (33, 128, 12)]
+
+
+def _attn_inputs(B, S, heads):
     g = torch.Generator().manual_seed(B * 100 + S)
     H = heads * 64
     qkv = torch.randn(B * S, 3 * H, generator=g).to(torch.bfloat16).cuda()
@@ -136,9 +140,17 @@ def test_attention_matches_fp32(spu, B, S, heads):
     keep = torch.arange(S)[None, :] < lens[:, None]
     keep[0] = True
     mask_bias = torch.where(keep, 0.0, -1e30).float().cuda()
+    return qkv, mask_bias
+
+
+@pytest.mark.parametrize("impl,_name", _ATTN_IMPLS)
+@pytest.mark.parametrize("B,S,heads", _ATTN_SHAPES)
+def test_attention_matches_fp32(spu, B, S, heads, impl, _name):
+    H = heads * 64
+    qkv, mask_bias = _attn_inputs(B, S, heads)
     ctx = torch.full((B * S, H), float("nan"), dtype=torch.bfloat16, device="cuda")
-    spu.check(spu.lib().spu_attention_async(spu.ptr(qkv), spu.ptr(mask_bias), spu.ptr(ctx), B, S, heads,
-                                            spu.stream_ptr()))
+    spu.check(spu.lib().spu_attention_cfg_async(spu.ptr(qkv), spu.ptr(mask_bias), spu.ptr(ctx), B, S, heads, impl, 0,
+                                                1.0, spu.stream_ptr()))
     _sync()
     ref = _attn_ref(qkv, mask_bias, B, S, heads)
     got = ctx.float().cpu()
@@ -147,15 +159,61 @@ def test_attention_matches_fp32(spu, B, S, heads):
     assert (got - ref).abs().max().item() < 3e-2, (got - ref).abs().max().item()
 
 
-def test_attention_fully_masked_row_is_uniform(spu):
+@pytest.mark.parametrize("B,S,heads", [(2, 128, 12), (3, 197, 16), (2, 512, 4)])
+def test_attention_no_mask_pointer(spu, B, S, heads):
+    # ViT path: mask_bias == NULL; rows of a neighbouring sequence must never leak into a ragged tile
+    H = heads * 64
+    qkv, _ = _attn_inputs(B, S, heads)
+    ctx = torch.full((B * S, H), float("nan"), dtype=torch.bfloat16, device="cuda")
+    spu.check(spu.lib().spu_attention_cfg_async(spu.ptr(qkv), None, spu.ptr(ctx), B, S, heads, 1, 0, 1.0,
+                                                spu.stream_ptr()))
+    _sync()
+    ref = _attn_ref(qkv, torch.zeros(B, S), B, S, heads)
+    assert (ctx.float().cpu() - ref).abs().max().item() < 3e-2
+
+
+@pytest.mark.parametrize("B,S,heads", [(2, 128, 12), (2, 300, 4)])
+def test_attention_tcgen05_tracks_mma_sync(spu, B, S, heads):
+    # two independent implementations of the same bf16 pipeline: agree to bf16 rounding of the output
+    H = heads * 64
+    qkv, mask_bias = _attn_inputs(B, S, heads)
+    outs = []
+    for impl in (1, 2):
+        ctx = torch.zeros(B * S, H, dtype=torch.bfloat16, device="cuda")
+        spu.check(spu.lib().spu_attention_cfg_async(spu.ptr(qkv), spu.ptr(mask_bias), spu.ptr(ctx), B, S, heads, impl,
+                                                    0, 1.0, spu.stream_ptr()))
+        _sync()
+        outs.append(ctx.float().cpu())
+    assert (outs[0] - outs[1]).abs().max().item() < 1.6e-2
+
+
+@pytest.mark.parametrize("impl,_name", _ATTN_IMPLS)
+@pytest.mark.parametrize("B,S,heads", [(2, 128, 12), (2, 200, 4)])
+def test_attention_e4m3_output(spu, B, S, heads, impl, _name):
+    H = heads * 64
+    qkv, mask_bias = _attn_inputs(B, S, heads)
+    ref = _attn_ref(qkv, mask_bias, B, S, heads)
+    scale = ref.abs().max().item() / 448.0
+    ctx = torch.zeros(B * S, H, dtype=torch.uint8, device="cuda")
+    spu.check(spu.lib().spu_attention_cfg_async(spu.ptr(qkv), spu.ptr(mask_bias), spu.ptr(ctx), B, S, heads, impl, 1,
+                                                1.0 / scale, spu.stream_ptr()))
+    _sync()
+    got = ctx.view(torch.float8_e4m3fn).float().cpu() * scale
+    # e4m3 has 3 mantissa bits: half-ulp relative error 2^-4, plus the bf16 pipeline error
+    err = (got - ref).abs()
+    assert (err <= 0.0625 * ref.abs() + 3e-2).all(), err.max().item()
+
+
+@pytest.mark.parametrize("impl,_name", _ATTN_IMPLS)
+def test_attention_fully_masked_row_is_uniform(spu, impl, _name):
     # HF adds finfo.min to every key of a fully padded sequence -> softmax is uniform
     B, S, heads = 1, 128, 1
     g = torch.Generator().manual_seed(3)
     qkv = torch.randn(B * S, 192, generator=g).to(torch.bfloat16).cuda()
     mask_bias = torch.full((B, S), -1e30, device="cuda")
     ctx = torch.zeros(B * S, 64, dtype=torch.bfloat16, device="cuda")
-    spu.check(spu.lib().spu_attention_async(spu.ptr(qkv), spu.ptr(mask_bias), spu.ptr(ctx), B, S, heads,
-                                            spu.stream_ptr()))
+    spu.check(spu.lib().spu_attention_cfg_async(spu.ptr(qkv), spu.ptr(mask_bias), spu.ptr(ctx), B, S, heads, impl, 0,
+                                                1.0, spu.stream_ptr()))
     _sync()
     v_mean = qkv.float().cpu()[:, 128:].mean(0)
     assert (ctx.float().cpu() - v_mean[None]).abs().max().item() < 2e-2
