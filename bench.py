@@ -361,7 +361,7 @@ def run_b200(args, rank, local_rank, world):
                        "what": "device time of one task (batch) = codelet_start..codelet_end"},
         "roofline": {"bound": "tensor", "kernel": "gemm_tcgen05_kernel (QKV, attn-out, FFN1, FFN2; 48 launches/step)",
                      "achieved": gemm_tflops, "peak": peaks["tflops"], "unit": "TFLOP/s",
-                     "frac": gemm_tflops / peaks["tflops"], "peak_source": peaks["source"], "traffic": None,
+                     "frac": gemm_tflops / peaks["tflops"], "peak_source": peaks["source"], **gemm_traffic(B, S, args.precision),
                      "flops_per_step": gemm_flop_step, "kernel_ms_per_step": gemm_ms,
                      "how": "48 GEMM launches x 5 forwards back to back in one CUDA graph, CUDA events on the launch stream"},
         "stage_ms_per_step": stage_ms,
@@ -374,6 +374,21 @@ def run_b200(args, rank, local_rank, world):
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+def gemm_traffic(B, S, precision):
+    """roofline.traffic: dram__bytes_read+write per GEMM launch (mean of the four GEMMs of a layer) from the committed
+    `ncu --set full` capture, when this run is the workload the capture was taken on; else null."""
+    p = os.path.join(ROOT, "profiles", "gemm_traffic.json")
+    try:
+        t = json.load(open(p))
+        w = t["workload"]
+        if (w["batch"], w["seq_len"], w["precision"]) == (B, S, precision):
+            return {"traffic": t["mean_dram_bytes_per_launch"], "traffic_unit": "bytes per GEMM launch (ncu dram read+write, cold)",
+                    "traffic_source": t["source"]}
+    except (OSError, KeyError, ValueError):
+        pass
+    return {"traffic": None}
 
 
 def main():
