@@ -288,9 +288,9 @@ spu_status attention_mma_launch(const void *qkv, const float *mask_bias, void *c
   return SPU_OK;
 }
 
-// Default: the tcgen05/TMEM kernel (attention_sm100.cu) wherever it is the faster one on B200
-// (profiles/r06_attention.md): single-tile sequences (S <= 128); longer sequences stay on this
-// file's mma.sync kernel.  SPU_ATTN=mma / SPU_ATTN=tc force one implementation for every shape.
+// Default: the tcgen05/TMEM kernel (attention_sm100.cu), faster than this file's mma.sync kernel at
+// every shape of the path on B200 (profiles/r06_attention.md: 1.4-2.2x from S=128 to S=512 and on
+// ViT's ragged S=197).  SPU_ATTN=mma keeps the mma.sync kernel selectable as the measured baseline.
 spu_status attention_launch(const void *qkv, const float *mask_bias, void *ctx, int batch, int seq,
                             int heads, cudaStream_t stream, bool out_e4m3, float q_inv_scale) {
   static const int forced = [] {
@@ -298,7 +298,7 @@ spu_status attention_launch(const void *qkv, const float *mask_bias, void *ctx, 
     if (e == nullptr) return 0;
     return std::string(e) == "mma" ? 2 : (std::string(e) == "tc" ? 1 : 0);
   }();
-  const bool tc = forced == 1 || (forced == 0 && seq <= 128);
+  const bool tc = forced != 2;
   return tc ? attention_tc_launch(qkv, mask_bias, ctx, batch, seq, heads, stream, out_e4m3, q_inv_scale)
             : attention_mma_launch(qkv, mask_bias, ctx, batch, seq, heads, stream, out_e4m3, q_inv_scale);
 }

@@ -27,7 +27,6 @@ namespace {
 
 constexpr int kHeadDim = 64;
 constexpr int kTile = 128;            // query rows per CTA == keys per KV tile
-constexpr int kThreads = 128;
 constexpr int kTileBytes = kTile * kHeadDim * 2;  // 16 KB: 128 rows x 128 B, SWIZZLE_128B
 constexpr float kLog2e = 1.4426950408889634f;
 
@@ -38,13 +37,24 @@ struct AttnCfg {
   static constexpr int kOffK = kTileBytes;
   static constexpr int kOffV = kOffK + kBufs * kTileBytes;
   // SINGLE: P (2 x 16 KB, keys 0-63 | 64-127) overwrites Q|K once S has been read out of TMEM
-  static constexpr int kOffP = MULTI ? kOffV + kBufs * kTileBytes : 0;
+  // V is single-buffered in both variants (two CTAs of 97 KB per SM): V_j is fetched while pass 2 of tile j
+  // runs, right after O_{j-1} has been collected
+  static constexpr int kOffP = MULTI ? kOffV + kTileBytes : 0;
   static constexpr int kTiles = MULTI ? kOffP + 2 * kTileBytes : kOffV + kTileBytes;
   static constexpr int kOffBias = kTiles;                       // kBufs x 128 fp32
-  static constexpr int kOffBars = kOffBias + kBufs * kTile * 4;  // 6 mbarriers + tmem slot
-  static constexpr int kSmemBytes = kOffBars + 64 + 1024;        // + 1024-alignment slack
+  static constexpr int kOffRed = kOffBias + kBufs * kTile * 4;   // 2 x 128 fp32: max / sum exchange (MULTI)
+  static constexpr int kOffBars = kOffRed + 2 * kTile * 4;       // 6 mbarriers + tmem slot
+  static constexpr int kSmemBytes = kOffBars + 96 + 1024;        // + 1024-alignment slack
+  // S buffers of 128 fp32 columns (MULTI: two, tile j in buffer j&1); O of tile j overwrites
+  // columns [0,64) of its own S buffer once every row owner has read S out
   static constexpr uint32_t kTmemCols = MULTI ? 256 : 128;
-  static constexpr uint32_t kTmemO = MULTI ? 128 : 0;            // SINGLE: O aliases S
+  // SINGLE: one thread per query row (128 threads, <=128 registers -> 4 CTAs/SM).
+  // MULTI : two threads per row, each owning 64 of a tile's 128 key columns and 32 of the 64
+  //         output columns (256 threads x 2 CTAs/SM = the same 16 warps/SM with half the
+  //         per-thread softmax chain and register footprint).
+  static constexpr int kTpr = MULTI ? 2 : 1;
+  static constexpr int kThreads = kTile * kTpr;
+  static constexpr int kOCols = kHeadDim / kTpr;
 };
 
 __device__ __forceinline__ void tma_load_3d(void *smem_dst, const void *tmap, uint64_t *bar, int32_t c0,
@@ -78,30 +88,47 @@ __host__ __device__ constexpr uint32_t attn_idesc(uint32_t m, uint32_t n, bool b
   return make_idesc(1u, m, n) | (b_mn ? (1u << 16) : 0u);
 }
 
-// One thread = one query row of S in TMEM (128 fp32 columns), read in four 32-column chunks with the
+// One thread = one query row of S in TMEM (up to 128 fp32 columns), read in up to four 32-column chunks with the
 // next chunk's tcgen05.ld in flight while the current one is consumed.
-template <typename F>
-__device__ __forceinline__ void for_each_chunk(uint32_t tmem_row, F &&f) {
+// PIPELINED = false (MULTI, 128-register budget with the running O resident): one chunk at a time.
+template <bool PIPELINED, typename F>
+__device__ __forceinline__ void for_each_chunk(uint32_t tmem_row, int nch, F &&f) {
+  if (nch <= 0) return;  // warp-uniform
+  if constexpr (!PIPELINED) {
+    for (int c = 0; c < nch; ++c) {
+      uint32_t v[32];
+      tmem_ld_32x32b_x32(tmem_row + c * 32, v);
+      tmem_ld_wait();
+      f(c, v);
+    }
+    return;
+  }
   uint32_t va[32], vb[32];
   tmem_ld_32x32b_x32(tmem_row, va);
   tmem_ld_wait();
-  tmem_ld_32x32b_x32(tmem_row + 32, vb);
+  if (nch > 1) tmem_ld_32x32b_x32(tmem_row + 32, vb);
   f(0, va);
-  tmem_ld_wait();
-  tmem_ld_32x32b_x32(tmem_row + 64, va);
-  f(1, vb);
-  tmem_ld_wait();
-  tmem_ld_32x32b_x32(tmem_row + 96, vb);
-  f(2, va);
-  tmem_ld_wait();
-  f(3, vb);
+  if (nch > 1) {
+    tmem_ld_wait();
+    if (nch > 2) tmem_ld_32x32b_x32(tmem_row + 64, va);
+    f(1, vb);
+    if (nch > 2) {
+      tmem_ld_wait();
+      if (nch > 3) tmem_ld_32x32b_x32(tmem_row + 96, vb);
+      f(2, va);
+      if (nch > 3) {
+        tmem_ld_wait();
+        f(3, vb);
+      }
+    }
+  }
 }
 
 // max_k (s*scale + bias_k); four independent accumulators keep the FMNMX chain short
-template <bool BIAS>
-__device__ __forceinline__ float row_max(uint32_t tmem_row, const float *bias, float scale) {
+template <bool BIAS, bool PIPELINED>
+__device__ __forceinline__ float row_max(uint32_t tmem_row, int nch, const float *bias, float scale) {
   float m0 = -INFINITY, m1 = -INFINITY, m2 = -INFINITY, m3 = -INFINITY;
-  for_each_chunk(tmem_row, [&](int c, const uint32_t(&v)[32]) {
+  for_each_chunk<PIPELINED>(tmem_row, nch, [&](int c, const uint32_t(&v)[32]) {
 #pragma unroll
     for (int i = 0; i < 32; i += 4) {
       if constexpr (BIAS) {
@@ -122,14 +149,15 @@ __device__ __forceinline__ float row_max(uint32_t tmem_row, const float *bias, f
   return BIAS ? m : m * scale;  // scale > 0
 }
 
-// p_k = 2^(s*scale + bias_k - m) -> bf16 into the two 64-key K-major SWIZZLE_128B tiles at s_p;
+// p_k = 2^(s*scale + bias_k - m) for chunks [c0, c0+nch) -> bf16 into the two 64-key K-major SWIZZLE_128B tiles at s_p;
 // returns the fp32 row sum
-template <bool BIAS>
-__device__ __forceinline__ float row_exp(uint32_t tmem_row, const float *bias, float scale, float m, uint8_t *s_p,
-                                         int row) {
+template <bool BIAS, bool PIPELINED>
+__device__ __forceinline__ float row_exp(uint32_t tmem_row, int nch, int c0, const float *bias, float scale, float m,
+                                         uint8_t *s_p, int row) {
   float l0 = 0.f, l1 = 0.f, l2 = 0.f, l3 = 0.f;
   const float neg_m = -m;
-  for_each_chunk(tmem_row, [&](int c, const uint32_t(&v)[32]) {
+  for_each_chunk<PIPELINED>(tmem_row, nch, [&](int cl, const uint32_t(&v)[32]) {
+    const int c = c0 + cl;  // chunk index inside the 128-key tile; `bias` and `tmem_row` are already offset by c0
     uint8_t *p_half = s_p + (c >> 1) * kTileBytes;
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
@@ -138,7 +166,7 @@ __device__ __forceinline__ float row_exp(uint32_t tmem_row, const float *bias, f
       for (int e = 0; e < 8; e += 4) {
         const int i = q * 8 + e;
         if constexpr (BIAS) {
-          const float4 bz = *reinterpret_cast<const float4 *>(bias + c * 32 + i);
+          const float4 bz = *reinterpret_cast<const float4 *>(bias + cl * 32 + i);
           p[e + 0] = ex2_approx(fmaf(__uint_as_float(v[i + 0]), scale, bz.x) - m);
           p[e + 1] = ex2_approx(fmaf(__uint_as_float(v[i + 1]), scale, bz.y) - m);
           p[e + 2] = ex2_approx(fmaf(__uint_as_float(v[i + 2]), scale, bz.z) - m);
@@ -162,10 +190,11 @@ __device__ __forceinline__ float row_exp(uint32_t tmem_row, const float *bias, f
 }
 
 template <bool MULTI, bool OUT_E4M3>
-__global__ void __launch_bounds__(kThreads, MULTI ? 2 : 4)
+__global__ void __launch_bounds__(AttnCfg<MULTI>::kThreads, MULTI ? 2 : 4)
 attention_tc_kernel(const __grid_constant__ CUtensorMap tm_qkv, const float *__restrict__ mask_bias,
                     void *__restrict__ ctx_out, int seq, int heads, float q_inv_scale) {
   using Cfg = AttnCfg<MULTI>;
+  constexpr int kOCols = Cfg::kOCols;
   extern __shared__ uint8_t smem_raw[];
   uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t *s_q = smem + Cfg::kOffQ;
@@ -173,14 +202,17 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm_qkv, const float *__r
   uint8_t *s_v = smem + Cfg::kOffV;
   uint8_t *s_p = smem + Cfg::kOffP;
   float *s_bias = reinterpret_cast<float *>(smem + Cfg::kOffBias);
+  float *s_red = reinterpret_cast<float *>(smem + Cfg::kOffRed);
   uint64_t *bars = reinterpret_cast<uint64_t *>(smem + Cfg::kOffBars);
   uint64_t *bar_k = bars, *bar_v = bars + 2, *bar_s = bars + 4, *bar_o = bars + 5;
   uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 6);
+  int *s_live = reinterpret_cast<int *>(bars + 7);  // one per warp (<= 8)
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int row = tid & (kTile - 1);          // query row of the tile this thread works on
+  const int half = MULTI ? (tid >> 7) : 0;    // which half of the key / output columns (MULTI)
   const int qt = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
   const int hidden = heads * kHeadDim;
-  const int n_kv = MULTI ? (seq + kTile - 1) / kTile : 1;
 
   // thread 0 gets the first loads in flight before anything else; warp 1 allocates TMEM meanwhile
   if (tid == 0) {
@@ -200,106 +232,180 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm_qkv, const float *__r
   }
   pdl_wait_prior_grid();
   pdl_launch_dependents();
+  // Hard-masked tail (padding): keys after the last live one add exactly 0 to every row sum and to
+  // O, so whole 32-key chunks / KV tiles behind it are skipped.  "Live" = bias above -1e29 (the
+  // mask builder writes -1e30); softer additive masks are never skipped.  No live key at all
+  // (fully padded sequence -> uniform softmax, as HF) keeps the full length.
+  {
+    int last = -1;
+    if (mask_bias != nullptr)
+      for (int k = tid; k < seq; k += Cfg::kThreads)
+        if (__ldg(mask_bias + static_cast<size_t>(b) * seq + k) > -1e29f) last = k;
+    last = __reduce_max_sync(0xffffffffu, last);
+    if (lane == 0) s_live[warp] = last;
+  }
   tcgen05_fence_before();
   __syncthreads();
   tcgen05_fence_after();
+  int live_end = -1;
+#pragma unroll
+  for (int w = 0; w < Cfg::kThreads / 32; ++w) live_end = max(live_end, s_live[w]);
+  live_end = (mask_bias == nullptr || live_end < 0) ? seq : live_end + 1;
+  const int n_kv = MULTI ? (live_end + kTile - 1) / kTile : 1;
   const uint32_t tmem_base = *tmem_slot;
-  const uint32_t tmem_row = tmem_base + (static_cast<uint32_t>(warp * 32) << 16);
+  // a warp may only touch TMEM lanes 32*(warp%4) .. +31: warps w and w+4 share the rows, split the columns
+  const uint32_t tmem_row = tmem_base + (static_cast<uint32_t>((warp & 3) * 32) << 16);
 
   constexpr uint32_t kIdescQK = attn_idesc(kTile, kTile, false);
   constexpr uint32_t kIdescPV = attn_idesc(kTile, kHeadDim, true);
   const float scale_log2 = 0.125f * kLog2e;  // 1/sqrt(64) folded into exp2
-  float m_run = -INFINITY, l_run = 0.f;
-  float o_run[kHeadDim];
+  float m_run = -INFINITY, l_run = 0.f;      // l_run: this thread's share of the row sum
+  float o_run[kOCols];
 #pragma unroll
-  for (int i = 0; i < kHeadDim; ++i) o_run[i] = 0.f;
+  for (int i = 0; i < kOCols; ++i) o_run[i] = 0.f;
 
+  // MMA issue helpers (thread 0 only)
+  auto issue_qk = [&](int j) {  // S_j = Q K_j^T : 128 x 128 x 64 as four K=16 steps (32 B inside the swizzle atom)
+    const int kb = MULTI ? (j & 1) : 0;
+    mbar_wait(&bar_k[kb], (j >> 1) & 1);
+    tcgen05_fence_after();
+    const uint64_t dq = make_sw128_kmajor_desc(smem_u32(s_q));
+    const uint64_t dk = make_sw128_kmajor_desc(smem_u32(s_k + kb * kTileBytes));
+#pragma unroll
+    for (int k = 0; k < 4; ++k) umma_f16_ss(tmem_base + kb * kTile, dq + 2 * k, dk + 2 * k, kIdescQK, k > 0);
+    umma_commit(bar_s);
+  };
+  // o_run = o_run * corr + this thread's columns of O_tile (tile in S buffer sb)
+  auto load_o = [&](int sb, float corr) {
+    if constexpr (MULTI) {
+      uint32_t va[32];
+      tmem_ld_32x32b_x32(tmem_row + sb * kTile + half * 32, va);
+      tmem_ld_wait();
+#pragma unroll
+      for (int i = 0; i < 32; ++i) o_run[i] = fmaf(o_run[i], corr, __uint_as_float(va[i]));
+    } else {
+      uint32_t va[32], vb[32];
+      tmem_ld_32x32b_x32(tmem_row, va);
+      tmem_ld_32x32b_x32(tmem_row + 32, vb);
+      tmem_ld_wait();
+#pragma unroll
+      for (int i = 0; i < 32; ++i) {
+        o_run[i] = __uint_as_float(va[i]);
+        o_run[32 + i] = __uint_as_float(vb[i]);
+      }
+    }
+  };
+
+  if (tid == 0) {
+    if (MULTI && n_kv > 1) {  // second K tile: in flight before the first softmax starts
+      mbar_arrive_expect_tx(&bar_k[1], kTileBytes);
+      tma_load_3d(s_k + kTileBytes, &tm_qkv, &bar_k[1], hidden + h * kHeadDim, kTile, b);
+    }
+    issue_qk(0);
+  }
+
+  // Software pipeline over KV tiles (MULTI): while the row owners run pass 2 of tile j the tensor
+  // core computes S_{j+1}; O_{j-1} = P V of the previous tile is collected one tile late, after
+  // pass 1 of tile j, so neither MMA round trip is exposed.
+  // keys past the sequence end never contribute (-inf); masked keys get the additive bias
+  // the mask builder wrote (HF: (1-mask)*finfo.min), pre-multiplied by log2(e)
+  auto load_bias = [&](int j) -> float {
+    if (tid >= kTile) return 0.f;
+    const int key = j * kTile + tid;
+    return key < seq ? (mask_bias != nullptr ? __ldg(mask_bias + static_cast<size_t>(b) * seq + key) * kLog2e : 0.f)
+                     : -INFINITY;
+  };
+  float next_bias = load_bias(0);
+  float corr_prev = 0.f;
   for (int j = 0; j < n_kv; ++j) {
     const int buf = MULTI ? (j & 1) : 0;
     float *bias = s_bias + buf * kTile;
-    // keys past the sequence end never contribute (-inf); masked keys get the additive bias
-    // the mask builder wrote (HF: (1-mask)*finfo.min), pre-multiplied by log2(e)
-    const int key = j * kTile + tid;
-    const float my_bias =
-        key < seq ? (mask_bias != nullptr ? mask_bias[static_cast<size_t>(b) * seq + key] * kLog2e : 0.f) : -INFINITY;
-    bias[tid] = my_bias;
-    if (tid == 0) {
-      if (MULTI && j + 1 < n_kv) {  // buffers of tile j-1 are free: its PV chain completed (bar_o)
-        const int nb = buf ^ 1;
-        mbar_arrive_expect_tx(&bar_k[nb], kTileBytes);
-        tma_load_3d(s_k + nb * kTileBytes, &tm_qkv, &bar_k[nb], hidden + h * kHeadDim, (j + 1) * kTile, b);
-        mbar_arrive_expect_tx(&bar_v[nb], kTileBytes);
-        tma_load_3d(s_v + nb * kTileBytes, &tm_qkv, &bar_v[nb], 2 * hidden + h * kHeadDim, (j + 1) * kTile, b);
-      }
-      // ---- S = Q K^T : 128 x 128 x 64 as four K=16 steps (32 B inside the swizzle atom) ----
-      mbar_wait(&bar_k[buf], (j >> 1) & 1);
-      tcgen05_fence_after();
-      const uint64_t dq = make_sw128_kmajor_desc(smem_u32(s_q));
-      const uint64_t dk = make_sw128_kmajor_desc(smem_u32(s_k + buf * kTileBytes));
-#pragma unroll
-      for (int k = 0; k < 4; ++k) umma_f16_ss(tmem_base, dq + 2 * k, dk + 2 * k, kIdescQK, k > 0);
-      umma_commit(bar_s);
-    }
-    // bias visible to every row owner; a tile without any bias (no padding, no tail) takes the
-    // cheaper softmax path below (block-uniform branch)
-    const bool has_bias = __syncthreads_or(my_bias != 0.f) != 0;
+    const float my_bias = next_bias;
+    if (tid < kTile) bias[tid] = my_bias;
+    if (MULTI && j + 1 < n_kv) next_bias = load_bias(j + 1);  // L2 latency hidden behind this tile's work
+    const int valid = min(kTile, live_end - j * kTile);
+    const int nch = (valid + 31) >> 5;  // 32-key chunks that hold any live key (ragged last tile)
+    const int c0 = MULTI ? half * 2 : 0;               // first chunk of this thread's key columns
+    const int my_nch = MULTI ? min(2, nch - c0) : nch;  // may be <= 0 for the upper half of a short tail
+    const uint32_t s_row = tmem_row + buf * kTile + c0 * 32;
+    // bias visible to every row owner; a tile whose processed chunks carry no bias (no padding, no
+    // tail inside them) takes the cheaper softmax path below (block-uniform branch)
+    const bool has_bias = __syncthreads_or(my_bias != 0.f && tid < nch * 32) != 0;
     mbar_wait_warp(bar_s, j & 1);
     tcgen05_fence_after();
+    if (MULTI && tid == 0 && j + 2 < n_kv) {  // S_j done: its K buffer takes tile j+2
+      mbar_arrive_expect_tx(&bar_k[buf], kTileBytes);
+      tma_load_3d(s_k + buf * kTileBytes, &tm_qkv, &bar_k[buf], hidden + h * kHeadDim, (j + 2) * kTile, b);
+    }
 
-    // ---- pass 1: row max of s' = s*scale + bias (this thread owns query row `tid`) ----
-    const float mx = has_bias ? row_max<true>(tmem_row, bias, scale_log2) : row_max<false>(tmem_row, bias, scale_log2);
+    // ---- pass 1: max of s' = s*scale + bias over this thread's columns of query row `row` ----
+    float mx = has_bias ? row_max<true, !MULTI>(s_row, my_nch, bias + c0 * 32, scale_log2)
+                        : row_max<false, !MULTI>(s_row, my_nch, bias + c0 * 32, scale_log2);
+    if (MULTI) {
+      if (j > 0) {  // collect O_{j-1} (long complete): frees its S buffer, its V buffer and the P tile
+        mbar_wait_warp(bar_o, (j - 1) & 1);
+        tcgen05_fence_after();
+        load_o(buf ^ 1, corr_prev);
+      }
+      s_red[half * kTile + row] = mx;
+      tcgen05_fence_before();
+      __syncthreads();
+      mx = fmaxf(mx, s_red[(half ^ 1) * kTile + row]);
+      if (tid == 0) {
+        if (j > 0) {  // P V of tile j-1 has completed: the V buffer takes tile j
+          mbar_arrive_expect_tx(&bar_v[0], kTileBytes);
+          tma_load_3d(s_v, &tm_qkv, &bar_v[0], 2 * hidden + h * kHeadDim, j * kTile, b);
+        }
+        if (j + 1 < n_kv) issue_qk(j + 1);  // runs under pass 2 of tile j
+      }
+    }
     const float m_new = fmaxf(m_run, mx);
     const float m_use = m_new == -INFINITY ? 0.f : m_new;
     const float corr = ex2_approx(m_run - m_use);  // first tile: 2^-inf = 0
     m_run = m_new;
+    corr_prev = corr;
+
     // ---- pass 2: p = 2^(s' - m), row sum, P -> smem as the K-major bf16 A operand of P V ----
-    const float l_tile = has_bias ? row_exp<true>(tmem_row, bias, scale_log2, m_use, s_p, tid)
-                                  : row_exp<false>(tmem_row, bias, scale_log2, m_use, s_p, tid);
+    const float l_tile = has_bias ? row_exp<true, !MULTI>(s_row, my_nch, c0, bias + c0 * 32, scale_log2, m_use, s_p, row)
+                                  : row_exp<false, !MULTI>(s_row, my_nch, c0, bias + c0 * 32, scale_log2, m_use, s_p, row);
     l_run = fmaf(l_run, corr, l_tile);
     fence_proxy_async_smem();  // generic-proxy P stores -> visible to the tensor core's async proxy
     tcgen05_fence_before();
-    __syncthreads();           // all of S read out of TMEM, all of P in smem
+    __syncthreads();           // all of S_j read out of TMEM, all of P_j in smem
 
-    // ---- O_tile = P V : 128 x 64 x 128, V consumed as loaded (MN-major B, 16 keys = 2 KB per step) ----
+    // ---- O_j = P V : 128 x 64 x (32*nch), V consumed as loaded (MN-major B, 16 keys = 2 KB per step) ----
     if (tid == 0) {
       tcgen05_fence_after();
-      mbar_wait(&bar_v[buf], (j >> 1) & 1);
-      const uint32_t v_addr = smem_u32(s_v + buf * kTileBytes);
-#pragma unroll
-      for (int k = 0; k < 8; ++k) {
+      mbar_wait(&bar_v[0], j & 1);
+      const uint32_t v_addr = smem_u32(s_v);
+      for (int k = 0; k < 2 * nch; ++k) {
         const uint64_t dp = make_sw128_kmajor_desc(smem_u32(s_p + (k >> 2) * kTileBytes)) + 2 * (k & 3);
         const uint64_t dv = make_sw128_kmajor_desc(v_addr + k * 2048);
-        umma_f16_ss(tmem_base + Cfg::kTmemO, dp, dv, kIdescPV, k > 0);
+        umma_f16_ss(tmem_base + buf * kTile, dp, dv, kIdescPV, k > 0);
       }
       umma_commit(bar_o);
     }
-    mbar_wait_warp(bar_o, j & 1);
-    tcgen05_fence_after();
-    {
-      uint32_t va[32], vb[32];
-      tmem_ld_32x32b_x32(tmem_row + Cfg::kTmemO, va);
-      tmem_ld_32x32b_x32(tmem_row + Cfg::kTmemO + 32, vb);
-      tmem_ld_wait();
-#pragma unroll
-      for (int i = 0; i < 32; ++i) {
-        o_run[i] = MULTI ? fmaf(o_run[i], corr, __uint_as_float(va[i])) : __uint_as_float(va[i]);
-        o_run[32 + i] = MULTI ? fmaf(o_run[32 + i], corr, __uint_as_float(vb[i])) : __uint_as_float(vb[i]);
-      }
-    }
-    tcgen05_fence_before();  // ordered before the next tile's MMAs overwrite S / O
+  }
+  mbar_wait_warp(bar_o, (n_kv - 1) & 1);
+  tcgen05_fence_after();
+  load_o(MULTI ? ((n_kv - 1) & 1) : 0, corr_prev);
+  if (MULTI) {  // the two column owners of a row add their partial sums
+    s_red[half * kTile + row] = l_run;
+    __syncthreads();
+    l_run += s_red[(half ^ 1) * kTile + row];
   }
 
-  // ---- normalise and store this thread's query row ----
+  // ---- normalise and store: this thread holds kOCols columns of query row `row` ----
   const float inv = 1.f / l_run;
-  const int q_row = qt * kTile + tid;
+  const int q_row = qt * kTile + row;
   const size_t tok0 = static_cast<size_t>(b) * seq;
   if constexpr (OUT_E4M3) {
     // per-tensor scaled e4m3 operand of the attention-output GEMM: 64 contiguous bytes per row
     if (q_row < seq) {
-      uint8_t *dst = static_cast<uint8_t *>(ctx_out) + (tok0 + q_row) * hidden + h * kHeadDim;
+      uint8_t *dst = static_cast<uint8_t *>(ctx_out) + (tok0 + q_row) * hidden + h * kHeadDim + half * kOCols;
       const float s = inv * q_inv_scale;
 #pragma unroll
-      for (int c = 0; c < 4; ++c) {
+      for (int c = 0; c < kOCols / 16; ++c) {
         uint32_t w[4];
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
@@ -312,33 +418,35 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm_qkv, const float *__r
       }
     }
   } else {
-    // stage this warp's 32 rows in the (dead) first P tile, then 128-bit coalesced stores:
-    // 4 full 128-byte rows per warp instruction
+    // stage the rows in the (dead) first P tile, then 128-bit coalesced stores: 4 full 128-byte
+    // rows per warp instruction
     uint8_t *stage = s_p;
 #pragma unroll
-    for (int c = 0; c < 8; ++c) {
+    for (int c = 0; c < kOCols / 8; ++c) {
       const uint4 w = make_uint4(pack_bf16(o_run[c * 8 + 0] * inv, o_run[c * 8 + 1] * inv),
                                  pack_bf16(o_run[c * 8 + 2] * inv, o_run[c * 8 + 3] * inv),
                                  pack_bf16(o_run[c * 8 + 4] * inv, o_run[c * 8 + 5] * inv),
                                  pack_bf16(o_run[c * 8 + 6] * inv, o_run[c * 8 + 7] * inv));
-      *reinterpret_cast<uint4 *>(stage + sw128_off(tid, c)) = w;
+      *reinterpret_cast<uint4 *>(stage + sw128_off(row, half * (kOCols / 8) + c)) = w;
     }
-    __syncwarp();
     __nv_bfloat16 *ctx = static_cast<__nv_bfloat16 *>(ctx_out);
+    if (MULTI) __syncthreads();  // a row's two halves come from different warps
+    else __syncwarp();           // a warp stores exactly the 32 rows it staged
+    constexpr int kIters = kTile * 8 / Cfg::kThreads;
 #pragma unroll
-    for (int it = 0; it < 8; ++it) {
-      const int idx = lane + it * 32;
-      const int r = warp * 32 + (idx >> 3), c = idx & 7;
-      const int row = qt * kTile + r;
-      if (row < seq)
-        *reinterpret_cast<uint4 *>(ctx + (tok0 + row) * hidden + h * kHeadDim + c * 8) =
+    for (int it = 0; it < kIters; ++it) {
+      const int idx = MULTI ? tid + it * Cfg::kThreads : warp * 256 + lane + it * 32;
+      const int r = idx >> 3, c = idx & 7;
+      const int grow = qt * kTile + r;
+      if (grow < seq)
+        *reinterpret_cast<uint4 *>(ctx + (tok0 + grow) * hidden + h * kHeadDim + c * 8) =
             *reinterpret_cast<const uint4 *>(stage + sw128_off(r, c));
     }
   }
 
   tcgen05_fence_before();
   __syncthreads();
-  if (warp == 0) {
+  if (warp == 1) {
     tcgen05_fence_after();
     tmem_dealloc(tmem_base, Cfg::kTmemCols);
   }
@@ -375,7 +483,7 @@ spu_status launch_tc(const CUtensorMap &map, const float *mask_bias, void *ctx, 
   });
   SPU_CUDA_TRY(attr_err);
   dim3 grid((seq + kTile - 1) / kTile, heads, batch);
-  SPU_CUDA_TRY(launch_pdl(kern, grid, dim3(kThreads), Cfg::kSmemBytes, stream, map, mask_bias, ctx, seq, heads,
+  SPU_CUDA_TRY(launch_pdl(kern, grid, dim3(Cfg::kThreads), Cfg::kSmemBytes, stream, map, mask_bias, ctx, seq, heads,
                           q_inv_scale));
   SPU_CUDA_TRY(cudaGetLastError());
   return SPU_OK;
