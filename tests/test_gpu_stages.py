@@ -219,6 +219,46 @@ def test_attention_fully_masked_row_is_uniform(spu, impl, _name):
     assert (ctx.float().cpu() - v_mean[None]).abs().max().item() < 2e-2
 
 
+@pytest.mark.parametrize("B,S,heads", [(256, 128, 12), (64, 512, 12), (64, 197, 16)])
+def test_attention_full_size_properties(spu, B, S, heads):
+    """BASELINE.json's full sizes, checked through size-independent properties instead of an O(B*S*S) oracle:
+    (1) softmax rows sum to one: with every V row of a head equal to a constant vector c the output is c;
+    (2) padded keys are inert: garbage in the K/V rows of hard-masked keys does not change any output row;
+    (3) sequences are independent: permuting the batch permutes the output."""
+    H = heads * 64
+    g = torch.Generator().manual_seed(S + B)
+    qkv = torch.randn(B, S, 3 * H, generator=g).to(torch.bfloat16)
+    c = torch.randn(H, generator=g).to(torch.bfloat16)
+    lens = torch.randint(1, S + 1, (B,), generator=g)
+    lens[0] = S
+    keep = torch.arange(S)[None, :] < lens[:, None]
+    mask_bias = torch.where(keep, 0.0, -1e30).float().cuda()
+
+    def run(x, mb):
+        x = x.reshape(B * S, 3 * H).contiguous().cuda()
+        ctx = torch.full((B * S, H), float("nan"), dtype=torch.bfloat16, device="cuda")
+        spu.check(spu.lib().spu_attention_cfg_async(spu.ptr(x), spu.ptr(mb), spu.ptr(ctx), B, S, heads, 1, 0, 1.0,
+                                                    spu.stream_ptr()))
+        _sync()
+        return ctx.cpu().view(B, S, H)
+
+    const_v = qkv.clone()
+    const_v[:, :, 2 * H:] = c
+    out = run(const_v, mask_bias).float()
+    assert torch.isfinite(out).all()
+    # P is rounded to bf16 (rel 2^-9) while the row sum is kept in fp32
+    assert (out - c.float()).abs().max().item() <= 2e-2 * max(1.0, c.float().abs().max().item())
+
+    base = run(qkv, mask_bias)
+    noisy = qkv.clone()
+    pad = ~keep
+    noisy[:, :, H:][pad] = (torch.randn(int(pad.sum()), 2 * H, generator=g) * 50).to(torch.bfloat16)
+    assert torch.equal(run(noisy, mask_bias), base)
+
+    perm = torch.randperm(B, generator=g)
+    assert torch.equal(run(qkv[perm], mask_bias[perm.cuda()].contiguous()), base[perm])
+
+
 # --------------------------------------------------------------- LayerNorm / embed
 @pytest.mark.parametrize("rows,hidden", [(4096, 768), (33, 128), (1000, 1024), (1, 768)])
 def test_layernorm_matches_oracle(spu, rows, hidden):
