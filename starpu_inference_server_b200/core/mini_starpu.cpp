@@ -177,6 +177,15 @@ void finish_task(Runtime *rt, starpu_task *task) {
   rt->idle_cv.notify_all();
 }
 
+// Completion waits (one completer thread per worker, one per output acquire) sleep on the event
+// instead of spinning: with one process per GPU and 4 workers each, 8 ranks would otherwise keep
+// 32+ host cores busy polling, which is what capped the end-to-end rate at 8 GPUs.  SPU_SPIN_SYNC=1
+// restores the spinning waits (lowest latency when cores are plentiful).
+unsigned sync_event_flags() {
+  static const bool spin = std::getenv("SPU_SPIN_SYNC") != nullptr;
+  return spin ? cudaEventDisableTiming : (cudaEventDisableTiming | cudaEventBlockingSync);
+}
+
 void completer_loop(Runtime *rt, Worker *w) {
   tls_worker = -1;  // callbacks do not run "on" a worker (starpu_worker_get_id() == -1)
   if (w->type == STARPU_CUDA_WORKER) cudaSetDevice(w->devid);
@@ -266,7 +275,7 @@ void worker_loop(Runtime *rt, Worker *w) {
     if (w->type == STARPU_CUDA_WORKER) {
       const bool async = task->cl->cuda_flags[0] & STARPU_CUDA_ASYNC;
       if (!async) cudaStreamSynchronize(w->stream);
-      cudaEventCreateWithFlags(&ev, cudaEventDisableTiming);
+      cudaEventCreateWithFlags(&ev, sync_event_flags());
       cudaEventRecord(ev, w->stream);
     }
     {
@@ -306,7 +315,18 @@ int fetch_to_host_locked(Runtime *rt, _starpu_data_state *h) {
     cudaError_t e = cudaMemcpyAsync(reinterpret_cast<void *>(host.iface.ptr),
                                     reinterpret_cast<void *>(src.iface.ptr), live_bytes(src.iface),
                                     cudaMemcpyDeviceToHost, s);
-    if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+    if (e == cudaSuccess) {
+      // wait on an event so the wait can block (see sync_event_flags) instead of spinning in
+      // cudaStreamSynchronize for the whole D2H
+      cudaEvent_t done = nullptr;
+      if (cudaEventCreateWithFlags(&done, sync_event_flags()) == cudaSuccess) {
+        e = cudaEventRecord(done, s);
+        if (e == cudaSuccess) e = cudaEventSynchronize(done);
+        cudaEventDestroy(done);
+      } else {
+        e = cudaStreamSynchronize(s);
+      }
+    }
     if (mine) cudaStreamDestroy(mine);
     if (prev >= 0) cudaSetDevice(prev);
     if (e != cudaSuccess) {

@@ -19,22 +19,27 @@ from starpu_inference_server_b200 import capi  # noqa: E402
 
 SHAPES = {  # name: (N, K, epilogue)
     "qkv": (2304, 768, 0), "attn_out": (768, 768, 2), "ffn1": (3072, 768, 1), "ffn2": (768, 3072, 2),
+    # epilogue-cost probes: the N=768 shapes with the plain bf16 epilogue / with a separate residual buffer
+    "attn_out_bf16": (768, 768, 0), "ffn2_bf16": (768, 3072, 0), "attn_out_sep": (768, 768, 12), "ffn2_sep": (768, 3072, 12),
 }
 
 
 def run(M, N, K, epi, cg, bn, reps, n_buf):
     L = capi.lib()
+    separate = epi == 12  # BIAS_RESID reading the residual from a different buffer (no in-place reduce-add)
+    epi = 2 if separate else epi
     a = [(torch.randn(M, K, device="cuda") * 0.5).to(torch.bfloat16) for _ in range(n_buf)]
     w = (torch.randn(N, K, device="cuda") * 0.05).to(torch.bfloat16)
     bias = torch.randn(N, device="cuda")
     out = [torch.zeros(M, N, device="cuda", dtype=torch.float32 if epi == 2 else torch.bfloat16) for _ in range(n_buf)]
+    res = [torch.zeros(M, N, device="cuda") for _ in range(n_buf)] if separate else out
     s = torch.cuda.Stream()
 
     def enqueue():
         for i in range(reps):
             o = out[i % n_buf]
             capi.check(L.spu_gemm_bf16_cfg_async(capi.ptr(a[i % n_buf]), capi.ptr(w), capi.ptr(bias),
-                                                 capi.ptr(o) if epi == 2 else None, capi.ptr(o), M, N, K, epi,
+                                                 capi.ptr(res[i % n_buf]) if epi == 2 else None, capi.ptr(o), M, N, K, epi,
                                                  cg, bn, capi.stream_ptr(s)))
     with torch.cuda.stream(s):
         enqueue()
