@@ -66,6 +66,9 @@ typedef struct spu_bert_desc {
  * tuples recur -- and replays it from then on.  Capture is thread-local stream capture on the
  * caller's stream: no synchronisation, no allocation visible to other workers. */
 #define SPU_FORWARD_AUTO_GRAPH (1u << 16)
+/* Allocate the per-workspace staging (ids, mask, batched output) that
+ * spu_bert_forward_requests_async needs.  Without it that call returns SPU_ERR_UNSUPPORTED. */
+#define SPU_REQUEST_IO (1u << 17)
 
 /* Number of weight tensors spu_bert_replica_create expects: 5 + 16*layers, in the
  * order of the HF state dict restated in oracle/bert_oracle.py:weight_names()
@@ -103,6 +106,25 @@ spu_status spu_bert_forward_async(spu_replica *r, int32_t ws_idx,
 
 /* Number of kernel launches one forward of (batch, seq) enqueues. */
 int32_t spu_bert_forward_launch_count(const spu_replica *r);
+
+/* Stages 1-4 in one call, on PER-REQUEST buffers (SURVEY 8(f) rows 1+2 at the codelet level;
+ * replaces the host staging copy of SlotManager::copy_job_inputs_to_slot,
+ * slot_manager_component.cpp:649-727, and the slot slicing of batching_helpers.hpp:74-127).
+ * Request i supplies len[i] <= seq token ids at src_ids[i] (and optionally len[i] mask words at
+ * src_mask[i]; src_mask or src_mask[i] NULL = all ones).  Stage 1 pads every row to `seq` with
+ * id 0 / mask 0 on the device; stages 2-3 run the encoder on the assembled [n_req, seq] batch
+ * (identical to spu_bert_forward_async on that batch); stage 4 writes request i's hidden states
+ * straight into dsts[i]: `seq` rows when full_rows != 0 (the reference's fixed [1, seq, H]
+ * output), else only its len[i] live rows.  src tables, len and dsts are DEVICE arrays of
+ * device-visible pointers (device memory or pinned, mapped host memory: the kernels then read
+ * the requests and write the responses over PCIe directly, with no staging copy at all).
+ * The replica must have been created with SPU_REQUEST_IO. */
+spu_status spu_bert_forward_requests_async(spu_replica *r, int32_t ws_idx,
+                                           const int64_t *const *src_ids,
+                                           const int64_t *const *src_mask,
+                                           const int32_t *len, int32_t n_req, int32_t seq,
+                                           float *const *dsts, int32_t full_rows,
+                                           void *stream);
 
 /* Capture the forward of (batch, seq) on ws_idx into a CUDA graph (warm-up hook,
  * src/core/warmup.cpp:225-299) so later spu_bert_forward_async calls with the

@@ -103,6 +103,14 @@ class BertReplica:
                                                      capi.ptr(out), capi.stream_ptr(stream)))
         return out
 
+    def forward_requests_async(self, src_ids_table, src_mask_table, len_dev, n_req: int, seq: int, dst_table,
+                               full_rows: bool = True, ws: int = 0, stream=None):
+        """Stages 1-4 on per-request buffers (replica created with capi.SPU_REQUEST_IO).  The tables are int64 CUDA
+        tensors of device-visible addresses (src_mask_table may be None), len_dev an int32 CUDA tensor."""
+        capi.check(capi.lib().spu_bert_forward_requests_async(
+            self._h, ws, capi.ptr(src_ids_table), None if src_mask_table is None else capi.ptr(src_mask_table),
+            capi.ptr(len_dev), n_req, seq, capi.ptr(dst_table), 1 if full_rows else 0, capi.stream_ptr(stream)))
+
     def forward_profiled(self, ids, mask, out, ws: int = 0, stream=None):
         """Measurement hook: one forward with per-kernel CUDA events; returns
         {stage name: device ms summed over layers}.  Synchronises the stream."""

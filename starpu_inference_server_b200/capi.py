@@ -17,12 +17,13 @@ SPU_ERR_INVALID, SPU_ERR_CUDA, SPU_ERR_CAPACITY, SPU_ERR_UNSUPPORTED, SPU_ERR_NO
 SPU_EPI_BIAS, SPU_EPI_BIAS_GELU, SPU_EPI_BIAS_RESID = 0, 1, 2
 SPU_PREC_BF16, SPU_PREC_FP8_E4M3 = 0, 1
 SPU_FORWARD_AUTO_GRAPH = 1 << 16  # capture a CUDA graph on the second sighting of a pointer tuple
+SPU_REQUEST_IO = 1 << 17  # allocate the staging spu_bert_forward_requests_async needs
 STAGE_NAMES = ["embed_ln", "gemm_qkv", "attention", "gemm_attn_out", "ln1", "gemm_ffn1", "gemm_ffn2", "ln2"]
 
 # every symbol include/spu_b200.h declares (checked by tests/test_capi_symbols.py)
 SYMBOLS = [
     "spu_bert_replica_create", "spu_replica_destroy", "spu_bert_forward_async",
-    "spu_bert_forward_launch_count", "spu_bert_forward_capture", "spu_bert_forward_profiled", "spu_gather_pad_mask_async",
+    "spu_bert_forward_launch_count", "spu_bert_forward_requests_async", "spu_bert_forward_capture", "spu_bert_forward_profiled", "spu_gather_pad_mask_async",
     "spu_gather_segments_async", "spu_scatter_segments_async", "spu_gemm_bf16_async", "spu_gemm_bf16_cfg_async",
     "spu_attention_async", "spu_attention_cfg_async", "spu_layernorm_async", "spu_bert_embed_async", "spu_affine_f32_async",
     "spu_last_error", "spu_abi_version", "spu_device_count", "spu_device_is_sm100",
@@ -78,6 +79,7 @@ def lib():
     L.spu_gemm_bf16_async.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, i32, vp]
     L.spu_gemm_bf16_cfg_async.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp]
     L.spu_attention_async.argtypes = [vp, vp, vp, i32, i32, i32, vp]
+    L.spu_bert_forward_requests_async.argtypes = [vp, i32, vp, vp, vp, i32, i32, vp, i32, vp]
     L.spu_attention_cfg_async.argtypes = [vp, vp, vp, i32, i32, i32, i32, i32, f32, vp]
     L.spu_layernorm_async.argtypes = [vp, vp, vp, f32, vp, vp, i32, i32, vp]
     L.spu_bert_embed_async.argtypes = [vp, vp, vp, vp, vp, vp, vp, f32, i32, vp, vp, vp, i32, i32, i32, vp]

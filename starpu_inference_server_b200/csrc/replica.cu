@@ -90,6 +90,11 @@ spu_status build(spu_replica *r, const float *const *t) {
     SPU_TRY(dev_alloc(r, &ws.ctx, rows * H));
     SPU_TRY(dev_alloc(r, &ws.h, rows * F));
     SPU_TRY(dev_alloc(r, &ws.mask_bias, rows));
+    if (r->flags & SPU_REQUEST_IO) {
+      SPU_TRY(dev_alloc(r, &ws.req_ids, rows));
+      SPU_TRY(dev_alloc(r, &ws.req_mask, rows));
+      SPU_TRY(dev_alloc(r, &ws.req_out, rows * H));
+    }
     if (r->flags & SPU_PREC_FP8_E4M3) {
       SPU_TRY(dev_alloc(r, &ws.x_q, rows * H));
       SPU_TRY(dev_alloc(r, &ws.ctx_q, rows * H));
@@ -318,7 +323,7 @@ extern "C" spu_status spu_bert_replica_create(const spu_bert_desc *desc, const f
               SPU_ERR_UNSUPPORTED, "replica_create: hidden/ffn must be multiples of 64, hidden <= 1024");
   SPU_REQUIRE(max_batch > 0 && max_seq > 0 && max_seq <= desc->max_pos && n_workspaces > 0,
               SPU_ERR_INVALID, "replica_create: bad capacity");
-  SPU_REQUIRE((flags & ~(SPU_PREC_FP8_E4M3 | 0xff00u | SPU_FORWARD_AUTO_GRAPH)) == 0 &&
+  SPU_REQUIRE((flags & ~(SPU_PREC_FP8_E4M3 | 0xff00u | SPU_FORWARD_AUTO_GRAPH | SPU_REQUEST_IO)) == 0 &&
                   ((flags & SPU_PREC_FP8_E4M3) || (flags & 0xff00u) == 0),
               SPU_ERR_UNSUPPORTED, "replica_create: unsupported precision flag");
   if (flags & SPU_PREC_FP8_E4M3)
@@ -403,6 +408,25 @@ extern "C" spu_status spu_bert_forward_async(spu_replica *r, int32_t ws_idx, con
     if (ws.seen.size() < 4 * kMaxAutoGraphs) ws.seen.push_back(key);
   }
   return enqueue_forward(r, ws, ids, mask, batch, seq, out, as_stream(stream));
+}
+
+extern "C" spu_status spu_bert_forward_requests_async(spu_replica *r, int32_t ws_idx,
+                                                      const int64_t *const *src_ids,
+                                                      const int64_t *const *src_mask, const int32_t *len,
+                                                      int32_t n_req, int32_t seq, float *const *dsts,
+                                                      int32_t full_rows, void *stream) {
+  SPU_REQUIRE(r != nullptr && r->kind == 0, SPU_ERR_INVALID, "forward_requests: not a BERT replica");
+  SPU_REQUIRE((r->flags & SPU_REQUEST_IO) != 0, SPU_ERR_UNSUPPORTED,
+              "forward_requests: replica was created without SPU_REQUEST_IO");
+  SPU_REQUIRE(ws_idx >= 0 && ws_idx < static_cast<int>(r->ws.size()), SPU_ERR_INVALID,
+              "forward_requests: workspace index out of range");
+  SPU_REQUIRE(src_ids && len && dsts, SPU_ERR_INVALID, "forward_requests: null table");
+  Workspace &ws = r->ws[ws_idx];
+  SPU_TRY(check_forward_args(r, ws_idx, ws.req_ids, ws.req_mask, n_req, seq, ws.req_out));
+  cudaStream_t s = as_stream(stream);
+  SPU_TRY(spu_gather_pad_mask_async(src_ids, src_mask, len, n_req, seq, 0, ws.req_ids, ws.req_mask, stream));
+  SPU_TRY(enqueue_forward(r, ws, ws.req_ids, ws.req_mask, n_req, seq, ws.req_out, s));
+  return scatter_requests_launch(ws.req_out, len, n_req, seq, r->desc.hidden, full_rows != 0, dsts, s);
 }
 
 extern "C" spu_status spu_bert_forward_capture(spu_replica *r, int32_t ws_idx, const int64_t *ids,

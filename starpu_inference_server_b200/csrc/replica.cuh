@@ -31,6 +31,9 @@ spu_status layernorm_launch(const float *x, const float *gamma, const float *bet
                             float *out_f32, void *out_bf16, int rows, int hidden,
                             cudaStream_t stream, long long in_row_stride = 0, void *out_q = nullptr,
                             float q_inv_scale = 1.f);
+// request i <- rows [i*seq, i*seq + (full_rows ? seq : len[i])) of src [n_req*seq, hidden]
+spu_status scatter_requests_launch(const float *src, const int32_t *len, int n_req, int seq, int hidden,
+                                   bool full_rows, float *const *dsts, cudaStream_t stream);
 // e4m3 = sat(in * inv_scale); exactly one of in_f32 / in_bf16 is non-null; n % 4 == 0
 spu_status quantize_e4m3_launch(const float *in_f32, const void *in_bf16, void *out, uint64_t n,
                                 float inv_scale, cudaStream_t stream);
@@ -90,6 +93,10 @@ struct Workspace {
   __nv_bfloat16 *x_bf16 = nullptr, *qkv = nullptr, *ctx = nullptr, *h = nullptr;
   float *mask_bias = nullptr;
   uint8_t *x_q = nullptr, *ctx_q = nullptr, *h_q = nullptr;  // FP8 variant operands
+  // SPU_REQUEST_IO: the assembled [batch, seq] ids / mask and the batched output of
+  // spu_bert_forward_requests_async (stage 1 writes, stage 4 reads)
+  int64_t *req_ids = nullptr, *req_mask = nullptr;
+  float *req_out = nullptr;
   std::vector<LayerPlans> plans;
   std::vector<LayerPlans> plans8;
   std::vector<CapturedGraph> graphs;

@@ -232,6 +232,41 @@ segcopy_kernel(const void *const *__restrict__ srcs, const uint8_t *src_base,
   }
 }
 
+// Stage 4 on per-request buffers: request i receives rows [i*seq, i*seq + rows_i) of the batched
+// [n_req*seq, hidden] fp32 output, rows_i = seq (fixed-shape contract) or len[i] (live rows only).
+// blockIdx.y = request, the gridDim.x blocks of a request split its bytes; four independent
+// 16-byte streaming loads in flight per thread (the output is read once, written once).
+__global__ void __launch_bounds__(256)
+scatter_requests_kernel(const float *__restrict__ src, const int32_t *__restrict__ len, int seq, int hidden,
+                        int full_rows, float *const *__restrict__ dsts) {
+  const int i = blockIdx.y;
+  const int rows = full_rows ? seq : min(max(len[i], 0), seq);
+  const float *s = src + static_cast<size_t>(i) * seq * hidden;
+  float *d = dsts[i];
+  const uint64_t n = static_cast<uint64_t>(rows) * hidden;  // floats
+  if (((reinterpret_cast<uintptr_t>(d) | (n * 4)) & 15u) == 0) {
+    const uint64_t n4 = n >> 2;
+    const uint64_t span = (n4 + gridDim.x - 1) / gridDim.x;
+    const uint64_t lo = span * blockIdx.x;
+    const uint64_t hi = lo + span < n4 ? lo + span : n4;
+    const uint4 *s4 = reinterpret_cast<const uint4 *>(s);
+    uint4 *d4 = reinterpret_cast<uint4 *>(d);
+    for (uint64_t base = lo + threadIdx.x; base < hi; base += 4 * 256) {
+      uint4 v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (base + u * 256 < hi) v[u] = __ldcs(s4 + base + u * 256);
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (base + u * 256 < hi) __stcs(d4 + base + u * 256, v[u]);
+    }
+  } else {
+    const uint64_t tid = static_cast<uint64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    const uint64_t nthr = static_cast<uint64_t>(gridDim.x) * blockDim.x;
+    for (uint64_t k = tid; k < n; k += nthr) d[k] = s[k];
+  }
+}
+
 __global__ void __launch_bounds__(256)
 affine_kernel(const float *__restrict__ in, float *__restrict__ out, uint64_t n, float scale,
               float shift) {
@@ -289,6 +324,17 @@ spu_status quantize_e4m3_launch(const float *in_f32, const void *in_bf16, void *
   const int grid = static_cast<int>(blocks > 148ull * 8 ? 148ull * 8 : blocks);
   quantize_e4m3_kernel<<<grid, 256, 0, stream>>>(in_f32, static_cast<const __nv_bfloat16 *>(in_bf16),
                                                  static_cast<uint8_t *>(out), n / 4, inv_scale);
+  SPU_CUDA_TRY(cudaGetLastError());
+  return SPU_OK;
+}
+
+spu_status scatter_requests_launch(const float *src, const int32_t *len, int n_req, int seq, int hidden,
+                                   bool full_rows, float *const *dsts, cudaStream_t stream) {
+  SPU_REQUIRE(src && len && dsts, SPU_ERR_INVALID, "scatter_requests: null argument");
+  SPU_REQUIRE(n_req > 0 && n_req <= 65535 && seq > 0 && hidden > 0 && hidden % 4 == 0, SPU_ERR_INVALID,
+              "scatter_requests: bad shape");
+  dim3 grid(kSegBlocksPerSegment, n_req);
+  scatter_requests_kernel<<<grid, 256, 0, stream>>>(src, len, seq, hidden, full_rows ? 1 : 0, dsts);
   SPU_CUDA_TRY(cudaGetLastError());
   return SPU_OK;
 }

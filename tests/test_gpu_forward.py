@@ -202,6 +202,61 @@ def test_auto_graph_on_second_sighting(spu):
     auto.close()
 
 
+@pytest.mark.parametrize("where", ["device", "pinned_host"])
+@pytest.mark.parametrize("full_rows", [True, False])
+def test_forward_requests_stages_1_to_4(spu, where, full_rows):
+    """spu_bert_forward_requests_async: ragged per-request buffers -> device gather/pad/mask -> encoder -> per-request
+    outputs.  Bit-identical to spu_bert_forward_async on the host-assembled padded batch (the reference's gather,
+    slot_manager_component.cpp:649-727, then its dim-0 slices, batching_helpers.hpp:74-127), for requests living in
+    device memory and for requests / responses living in pinned host memory the kernels reach over PCIe."""
+    from oracle import bert_oracle as bo
+    from starpu_inference_server_b200.bert import BertReplica
+
+    cfg = bo.BERT_TINY
+    w = bo.make_weights(cfg, 0)
+    n_req, seq, H = 7, 96, cfg.hidden
+    rep = BertReplica(w, max_batch=8, max_seq=128, flags=spu.SPU_REQUEST_IO)
+    rng = np.random.default_rng(11)
+    lens = rng.integers(1, seq + 1, size=n_req).astype(np.int32)
+    lens[0], lens[1] = seq, 1
+
+    def alloc(shape, dtype):
+        t = torch.zeros(shape, dtype=dtype)
+        return t.pin_memory() if where == "pinned_host" else t.cuda()
+
+    ids_req, mask_req, out_req = [], [], []
+    ids_pad = np.zeros((n_req, seq), np.int64)
+    mask_pad = np.zeros((n_req, seq), np.int64)
+    for i, n in enumerate(lens):
+        a = rng.integers(0, cfg.vocab, size=int(n)).astype(np.int64)
+        m = np.ones(int(n), np.int64)
+        if i == 3 and n > 4:
+            m[2] = 0  # a request may carry its own mask words
+        ids_pad[i, :n], mask_pad[i, :n] = a, m
+        ti, tm = alloc((int(n),), torch.int64), alloc((int(n),), torch.int64)
+        ti.copy_(torch.from_numpy(a))
+        tm.copy_(torch.from_numpy(m))
+        ids_req.append(ti)
+        mask_req.append(tm)
+        to = alloc(((seq if full_rows else int(n)), H), torch.float32)
+        to.fill_(float("nan"))
+        out_req.append(to)
+    table = lambda ts: torch.tensor([t.data_ptr() for t in ts], dtype=torch.int64, device="cuda")  # noqa: E731
+    rep.forward_requests_async(table(ids_req), table(mask_req), torch.from_numpy(lens).cuda(), n_req, seq,
+                               table(out_req), full_rows=full_rows)
+    torch.cuda.synchronize()
+    ref = torch.from_numpy(_run(rep, ids_pad, mask_pad, H))
+    for i, n in enumerate(lens):
+        rows = seq if full_rows else int(n)
+        assert torch.equal(out_req[i].cpu(), ref[i, :rows]), f"request {i}"
+    # without the flag the entry point refuses instead of touching unallocated staging
+    plain = BertReplica(w, max_batch=8, max_seq=128)
+    with pytest.raises(spu.SpuError):
+        plain.forward_requests_async(table(ids_req), None, torch.from_numpy(lens).cuda(), n_req, seq, table(out_req))
+    plain.close()
+    rep.close()
+
+
 def test_capacity_and_argument_errors(base, spu):
     bo, w, r = base
     ids = torch.zeros(65, 512, dtype=torch.int64, device="cuda")
