@@ -290,9 +290,10 @@ def run_b200(args, rank, local_rank, world):
     # output slot -> per-request slices; everything inside the timed region.
     from starpu_inference_server_b200 import hostapi
 
-    # defaults follow models/bert.yml (4 workers per CUDA device, pool 12); the env knobs are for sweeps only
-    e2e_workers = min(n_pipe, int(os.environ.get("SPU_BENCH_WORKERS", n_pipe)))
-    e2e_pipeline = int(os.environ.get("SPU_BENCH_PIPELINE", 2))
+    # pool 12 as models/bert.yml; 2 CUDA workers x STARPU_CUDA_PIPELINE 4 (the reference's pipeline depth) measured
+    # best of the swept (workers, pipeline) pairs at N=1 and N=8 (profiles/r06_e2e_config.md); env knobs: sweeps only
+    e2e_workers = min(n_pipe, int(os.environ.get("SPU_BENCH_WORKERS", 2)))
+    e2e_pipeline = int(os.environ.get("SPU_BENCH_PIPELINE", 4))
     e2e_pool = int(os.environ.get("SPU_BENCH_POOL", 12))
     io = dict(inputs=[("input_ids", "i64", [1, S]), ("attention_mask", "i64", [1, S])],
               outputs=[("output0", "f32", [1, S, spec.hidden])])
@@ -314,7 +315,8 @@ def run_b200(args, rank, local_rank, world):
                     checksum += float(r.first_value)
                     task_ms.append(r.task_ms)
 
-    run_e2e(max(args.warmup, 120 if args.auto_graph else 20), False)  # auto-graph: most (worker, slot) tuples captured
+    # auto-graph: every (worker, slot) tuple has to be seen twice before it replays a graph
+    run_e2e(max(args.warmup, 6 * e2e_workers * e2e_pool if args.auto_graph else 20), False)
     # three back-to-back segments of K steps each, the MEDIAN segment is reported: one host-side hiccup
     # (a descheduled worker thread) inside a 0.2 s region otherwise moves the number by 20 %
     e2e_segments = []
@@ -361,7 +363,8 @@ def run_b200(args, rank, local_rank, world):
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 2 * B * S * 8,
                 "d2h_bytes_per_step": B * S * HIDDEN * 4, "checksum": checksum,
                 "path": "libspu_host.so: per-request host buffers -> host gather -> task -> H2D -> codelet -> D2H -> "
-                        f"slices ({e2e_workers} CUDA workers x pipeline {e2e_pipeline}, pool {e2e_pool})",
+                        f"slices ({e2e_workers} CUDA workers x pipeline {e2e_pipeline}, pool {e2e_pool}, "
+                        + ("CUDA-graph replay per (worker, slot) tuple)" if args.auto_graph else "eager launches)"),
                 "tasks": int(host_stats["tasks"]),
                 "how": f"median of 3 segments of {args.steps} steps (rank 0 segments, inferences/s: "
                        + ", ".join(f"{B * args.steps * world / t:.0f}" for t in e2e_segments) + ")",
@@ -414,8 +417,10 @@ def main():
     ap.add_argument("--min-len", type=int, default=None, help="variable-length requests: lengths U[min_len, seq]")
     ap.add_argument("--streams", type=int, default=2, help="CUDA workers issuing resident tasks round-robin")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--auto-graph", action="store_true",
-                    help="e2e path replays CUDA graphs (SPU_FORWARD_AUTO_GRAPH); measured neutral: 30.7k vs 31.1k inf/s")
+    ap.add_argument("--no-auto-graph", dest="auto_graph", action="store_false",
+                    help="e2e path launches every kernel eagerly instead of replaying CUDA graphs captured on the second "
+                         "sighting of a (worker, slot) tuple (SPU_FORWARD_AUTO_GRAPH; profiles/r06_e2e_config.md: "
+                         "33.7k vs 32.2k inf/s at N=1, 259k vs 220k at N=8 where host cores are scarce)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     rank = int(os.environ.get("RANK", "0"))
