@@ -69,6 +69,11 @@ typedef struct spu_server_cfg {
   spu_replica *replicas[SPU_HOST_MAX_DEVICES]; /* replicas[i] serves device_ids[i] (BERT / ViT) */
   int32_t n_workspaces;                        /* arenas each replica was created with */
   float affine_scale, affine_shift;
+  /* SURVEY 8(f) row 1 (variable-length admission): != 0 lets a request carry any sequence length
+   * 1 <= seq_len <= inputs[*].dims[1]; requests of different lengths merge into one batch that the host
+   * gather pads with zeros (token id 0 = [PAD], mask 0) to its longest request, slots stay sized by the
+   * configured dims[1], and a single-sample request gets only its own seq_len rows back. */
+  int32_t variable_length;
 } spu_server_cfg;
 
 typedef struct spu_request {
@@ -76,6 +81,8 @@ typedef struct spu_request {
   int64_t batch;                         /* rows this request carries (dims[0]) */
   const void *inputs[SPU_HOST_MAX_IO];   /* host, contiguous [batch, ...] per model input */
   void *outputs[SPU_HOST_MAX_IO];        /* host destination per model output (may be NULL) */
+  int64_t seq_len;                       /* variable_length servers: dims[1] of this request's inputs
+                                            (0 = the configured length); ignored otherwise */
 } spu_request;
 
 typedef struct spu_result {
@@ -138,6 +145,13 @@ int64_t spu_host_slice_rows(uint64_t rows, uint64_t row_bytes, int64_t offset, i
 /* can_merge_jobs over two single-input requests described by dims/dtype */
 int32_t spu_host_can_merge(const int64_t *dims_a, int32_t nd_a, int32_t dt_a, const int64_t *dims_b, int32_t nd_b,
                            int32_t dt_b);
+/* the same with the variable-length relaxation (dims[1] may differ) */
+int32_t spu_host_can_merge_varlen(const int64_t *dims_a, int32_t nd_a, int32_t dt_a, const int64_t *dims_b,
+                                  int32_t nd_b, int32_t dt_b);
+/* copy_job_inputs_to_slot_padded over one int64 input: request j is one [1, len[j]] row, every row is padded
+ * to `seq`; returns 0 ok / 1 exception; nx_out = the handle's nx afterwards. */
+int32_t spu_host_gather_padded(const int64_t *const *srcs, const int64_t *len, int32_t n_jobs, int64_t seq,
+                               int64_t *slot, uint64_t capacity_bytes, uint64_t *nx_out);
 /* Calls codelet.cuda_funcs[0] directly, like unit_starpu_setup.cpp:2332-2433: DEVICE fp32
  * in/out of n elements, an affine "model" on `device`, mocked worker id / device id / stream.
  * rec = {device_id, worker_id, executed_on, start!=0, end!=0, inflight gauge after}.

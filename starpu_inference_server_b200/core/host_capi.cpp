@@ -85,6 +85,8 @@ struct spu_server {
       t.dims = model.inputs[i].dims;
       if (t.dims.empty()) t.dims.push_back(rq.batch);
       else t.dims[0] = rq.batch;
+      // variable-length admission: the request states its own sequence length (checked in submit_batch)
+      if (model.variable_length && rq.seq_len > 0 && t.dims.size() >= 2) t.dims[1] = rq.seq_len;
       job->inputs.push_back(std::move(t));
     }
     std::vector<void *> dsts(rq.outputs, rq.outputs + model.outputs.size());
@@ -164,7 +166,7 @@ struct spu_server {
             if (queue.empty()) continue;
           }
           auto &cand = queue.front();
-          if (!can_merge_jobs(batch[0].get(), cand.get())) break;  // incompatible: starts the next batch
+          if (!can_merge_jobs(batch[0].get(), cand.get(), model.variable_length)) break;  // incompatible: starts the next batch
           if (rows + cand->batch_size() > model.max_batch_size) break;
           rows += cand->batch_size();
           batch.push_back(cand);
@@ -228,6 +230,7 @@ int32_t spu_server_create(const spu_server_cfg *cfg, spu_server **out) {
       for (int i = 0; i < cfg->n_outputs; ++i) s->model.outputs.push_back(to_cfg(cfg->outputs[i]));
       s->model.max_batch_size = cfg->max_batch_size > 0 ? cfg->max_batch_size : 1;
       s->model.pool_size = cfg->pool_size > 0 ? cfg->pool_size : 12;
+      s->model.variable_length = cfg->variable_length != 0;
       s->coalesce_ms = cfg->batch_coalesce_timeout_ms;
       std::vector<int> dev_ids;
       std::vector<DeviceModel *> models;

@@ -145,6 +145,52 @@ int32_t spu_host_can_merge(const int64_t *dims_a, int32_t nd_a, int32_t dt_a, co
   return can_merge_jobs(&a, &b) ? 1 : 0;
 }
 
+int32_t spu_host_can_merge_varlen(const int64_t *dims_a, int32_t nd_a, int32_t dt_a, const int64_t *dims_b,
+                                  int32_t nd_b, int32_t dt_b) {
+  static std::byte dummy;
+  auto mk = [](const int64_t *d, int32_t nd, int32_t dt) {
+    InferenceJob j;
+    HostTensor t;
+    t.data = &dummy;
+    t.type = static_cast<ScalarType>(dt);
+    t.dims.assign(d, d + nd);
+    j.inputs.push_back(std::move(t));
+    return j;
+  };
+  const InferenceJob a = mk(dims_a, nd_a, dt_a), b = mk(dims_b, nd_b, dt_b);
+  return can_merge_jobs(&a, &b, true) ? 1 : 0;
+}
+
+int32_t spu_host_gather_padded(const int64_t *const *srcs, const int64_t *len, int32_t n_jobs, int64_t seq,
+                               int64_t *slot, uint64_t capacity_bytes, uint64_t *nx_out) {
+  starpu_data_handle_t h = nullptr;
+  starpu_vector_data_register(&h, STARPU_MAIN_RAM, reinterpret_cast<uintptr_t>(slot),
+                              static_cast<uint32_t>(capacity_bytes / 8), 8);
+  std::vector<InferenceJob> jobs(static_cast<size_t>(n_jobs));
+  for (int j = 0; j < n_jobs; ++j) {
+    HostTensor t;
+    t.data = reinterpret_cast<std::byte *>(const_cast<int64_t *>(srcs[j]));
+    t.type = ScalarType::Int64;
+    t.dims = {1, len[j]};
+    jobs[static_cast<size_t>(j)].inputs.push_back(std::move(t));
+  }
+  std::vector<const InferenceJob *> pending;
+  for (int j = 1; j < n_jobs; ++j) pending.push_back(&jobs[static_cast<size_t>(j)]);
+  int32_t rc = 0;
+  try {
+    HostBufferInfo info;
+    info.bytes = static_cast<size_t>(capacity_bytes);
+    copy_job_inputs_to_slot_padded(n_jobs > 0 ? &jobs[0] : nullptr, pending, {h},
+                                   {reinterpret_cast<std::byte *>(slot)}, {info}, seq);
+    if (nx_out) *nx_out = static_cast<starpu_vector_interface *>(starpu_data_get_interface_on_node(h, 0))->nx;
+  } catch (const std::exception &e) {
+    fail(e);
+    rc = 1;
+  }
+  starpu_data_unregister(h);
+  return rc;
+}
+
 int32_t spu_host_call_cuda_func_affine(const float *in_dev, float *out_dev, uint64_t n, float scale, float shift,
                                        int32_t device, int32_t worker_id, void *stream, int32_t n_models,
                                        int32_t use_vector_iface, int64_t rec[6]) {

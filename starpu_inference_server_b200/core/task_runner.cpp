@@ -8,7 +8,7 @@
 
 namespace starpu_server {
 
-auto can_merge_jobs(const InferenceJob *lhs, const InferenceJob *rhs) -> bool {
+auto can_merge_jobs(const InferenceJob *lhs, const InferenceJob *rhs, bool variable_length) -> bool {
   if (!lhs || !rhs) return false;
   if (lhs->inputs.size() != rhs->inputs.size()) return false;
   for (size_t i = 0; i < lhs->inputs.size(); ++i)
@@ -19,7 +19,7 @@ auto can_merge_jobs(const InferenceJob *lhs, const InferenceJob *rhs) -> bool {
     if (a.dims.size() != b.dims.size()) return false;
     if (a.dims.empty()) return false;
     for (size_t d = 1; d < a.dims.size(); ++d)
-      if (a.dims[d] != b.dims[d]) return false;
+      if (a.dims[d] != b.dims[d] && !(variable_length && d == 1)) return false;
   }
   return true;
 }
@@ -93,6 +93,47 @@ auto copy_job_inputs_to_slot(const InferenceJob *job, const std::vector<const In
   return total_bytes_copied;
 }
 
+auto copy_job_inputs_to_slot_padded(const InferenceJob *job, const std::vector<const InferenceJob *> &pending_jobs,
+                                    const std::vector<starpu_data_handle_t> &handles,
+                                    const std::vector<std::byte *> &base_ptrs,
+                                    const std::vector<HostBufferInfo> &buffer_infos, int64_t seq) -> std::size_t {
+  if (!job) return 0;
+  std::size_t total_bytes_copied = 0;
+  for (std::size_t input_idx = 0; input_idx < job->inputs.size(); ++input_idx) {
+    std::byte *dst = base_ptrs[input_idx];
+    const std::size_t capacity = buffer_infos[input_idx].bytes;
+    std::size_t offset = 0, total_numel = 0;
+    auto copy_tensor = [&](const HostTensor &t) {
+      if (!t.defined())
+        throw InvalidInputTensorException("input[" + std::to_string(input_idx) + "] is not a defined host tensor");
+      if (t.dims.size() < 2 || t.dims[0] < 1 || t.dims[1] < 1 || t.dims[1] > seq)
+        throw InvalidInputTensorException("variable-length input needs dims [batch, seq <= " + std::to_string(seq) +
+                                          ", ...]");
+      const size_t samples = static_cast<size_t>(t.dims[0]);
+      const size_t row_bytes = t.nbytes() / samples;                                  // L * rest * elem
+      const size_t padded_bytes = row_bytes / static_cast<size_t>(t.dims[1]) * static_cast<size_t>(seq);
+      if (capacity < offset + samples * padded_bytes)
+        throw InputPoolCapacityException("Input tensor exceeds allocated slot buffer capacity");
+      for (size_t r = 0; r < samples; ++r) {
+        std::memcpy(dst + offset, t.data + r * row_bytes, row_bytes);
+        std::memset(dst + offset + row_bytes, 0, padded_bytes - row_bytes);
+        offset += padded_bytes;
+      }
+      total_numel += padded_bytes / element_size(t.type) * samples;
+      total_bytes_copied += samples * row_bytes;
+    };
+    copy_tensor(job->inputs[input_idx]);
+    for (const InferenceJob *pending : pending_jobs) {
+      if (!pending) continue;
+      if (input_idx >= pending->inputs.size())
+        throw InconsistentInputTensorCountException("Inconsistent input tensor count");
+      copy_tensor(pending->inputs[input_idx]);
+    }
+    resize_starpu_vector_handle(handles[input_idx], VectorResizeSpec{total_numel, offset}, true);
+  }
+  return total_bytes_copied;
+}
+
 auto slice_outputs_for_sub_job(const std::vector<HostTensor> &aggregated_outputs, int64_t offset,
                                int64_t batch_size) -> SubJobSliceResult {
   SubJobSliceResult result;
@@ -133,6 +174,7 @@ struct TaskRunner::CallbackContext {
   int input_slot = -1, output_slot = -1;
   std::vector<starpu_data_handle_t> outputs_handles;
   int64_t effective_batch = 0;
+  int64_t seq = 0;  // variable_length: the padded sequence length of this batch (0 = fixed shapes)
   int worker_id = -1, device_id = -1;
   DeviceType executed_on = DeviceType::Unknown;
   JobTiming timing;
@@ -164,7 +206,7 @@ void TaskRunner::submit_batch(const std::vector<std::shared_ptr<InferenceJob>> &
   for (size_t k = 0; k < jobs.size(); ++k) {
     if (!jobs[k]) continue;
     if (k > 0) {
-      if (!can_merge_jobs(master, jobs[k].get()))
+      if (!can_merge_jobs(master, jobs[k].get(), model_.variable_length))
         throw InvalidInferenceJobException("sub-job cannot be merged with the master job (shape/type mismatch)");
       pending.push_back(jobs[k].get());
     }
@@ -172,11 +214,27 @@ void TaskRunner::submit_batch(const std::vector<std::shared_ptr<InferenceJob>> &
   }
   if (effective_batch < 1 || effective_batch > input_pool_->max_batch_size())
     throw InputPoolCapacityException("Batch size exceeds input pool capacity");
+  // variable_length: the batch is padded to its longest request; the configured dims[1] is the cap
+  int64_t seq = 0, seq_cap = 0;
+  if (model_.variable_length) {
+    if (model_.inputs[0].dims.size() < 2) throw std::invalid_argument("variable_length needs inputs of rank >= 2");
+    seq_cap = model_.inputs[0].dims[1];
+    for (const auto &j : jobs) {
+      if (!j) continue;
+      for (const HostTensor &t : j->inputs) {
+        if (t.dims.size() < 2 || t.dims[1] < 1 || t.dims[1] > seq_cap || t.dims[1] != j->inputs[0].dims[1])
+          throw InvalidInputTensorException("variable-length request: every input needs the same seq in [1, " +
+                                            std::to_string(seq_cap) + "]");
+      }
+      seq = std::max(seq, j->inputs[0].dims[1]);
+    }
+  }
 
   auto ctx = std::make_unique<CallbackContext>();
   ctx->runner = this;
   ctx->jobs = jobs;
   ctx->effective_batch = effective_batch;
+  ctx->seq = seq;
   ctx->input_slot = input_pool_->acquire();
   ctx->output_slot = output_pool_->acquire();
   struct SlotGuard {
@@ -198,8 +256,12 @@ void TaskRunner::submit_batch(const std::vector<std::shared_ptr<InferenceJob>> &
     for (; leased < in_handles.size(); ++leased)
       if (starpu_data_acquire(in_handles[leased], STARPU_W) != 0)
         throw StarPUDataAcquireException("starpu_data_acquire failed");
-    copy_job_inputs_to_slot(master, pending, in_handles, input_pool_->base_ptrs(ctx->input_slot),
-                            input_pool_->host_buffer_infos(ctx->input_slot));
+    if (model_.variable_length)
+      copy_job_inputs_to_slot_padded(master, pending, in_handles, input_pool_->base_ptrs(ctx->input_slot),
+                                     input_pool_->host_buffer_infos(ctx->input_slot), seq);
+    else
+      copy_job_inputs_to_slot(master, pending, in_handles, input_pool_->base_ptrs(ctx->input_slot),
+                              input_pool_->host_buffer_infos(ctx->input_slot));
   } catch (...) {
     for (size_t i = 0; i < leased; ++i) starpu_data_release(in_handles[i]);
     throw;
@@ -208,7 +270,10 @@ void TaskRunner::submit_batch(const std::vector<std::shared_ptr<InferenceJob>> &
 
   // outputs: prototype resized to [effective_batch, ...] (resize_outputs_for_batch)
   for (size_t o = 0; o < out_handles.size(); ++o) {
-    const size_t numel = output_pool_->per_sample_numel(o) * static_cast<size_t>(effective_batch);
+    size_t numel = output_pool_->per_sample_numel(o) * static_cast<size_t>(effective_batch);
+    // variable_length: an output whose dims[1] is the configured sequence length shrinks with the batch's seq
+    if (seq > 0 && model_.outputs[o].dims.size() >= 2 && model_.outputs[o].dims[1] == seq_cap)
+      numel = numel / static_cast<size_t>(seq_cap) * static_cast<size_t>(seq);
     resize_starpu_vector_handle(out_handles[o],
                                 VectorResizeSpec{numel, numel * element_size(output_pool_->tensor_type(o))}, false);
   }
@@ -225,6 +290,7 @@ void TaskRunner::submit_batch(const std::vector<std::shared_ptr<InferenceJob>> &
   for (size_t i = 0; i < master->inputs.size(); ++i) {
     std::vector<int64_t> dims = master->inputs[i].dims;
     if (!dims.empty()) dims[0] = effective_batch;  // inference_task.cpp:606-613
+    if (seq > 0 && dims.size() >= 2) dims[1] = seq;
     params->layout.num_dims.push_back(static_cast<int64_t>(dims.size()));
     params->layout.dims.push_back(std::move(dims));
     params->layout.input_types.push_back(master->inputs[i].type);
@@ -320,6 +386,7 @@ void TaskRunner::finalize(CallbackContext *ctx) {
     t.dims = r->model_.outputs[o].dims;
     if (t.dims.empty()) t.dims.push_back(ctx->effective_batch);
     else t.dims[0] = ctx->effective_batch;
+    if (ctx->seq > 0 && t.dims.size() >= 2 && t.dims[1] == r->model_.inputs[0].dims[1]) t.dims[1] = ctx->seq;
     aggregated.push_back(std::move(t));
   }
   ctx->timing.callback_end_time = MonotonicClock::now();
@@ -338,6 +405,10 @@ void TaskRunner::finalize(CallbackContext *ctx) {
     if (codelet_ok && all_acquired) {
       auto slice = slice_outputs_for_sub_job(aggregated, offset, job->batch_size());
       res.outputs = std::move(slice.outputs);
+      // variable_length: a single-sample request gets its own L rows (a contiguous prefix of its padded sample)
+      if (ctx->seq > 0 && job->batch_size() == 1 && !job->inputs.empty() && job->inputs[0].dims.size() >= 2)
+        for (HostTensor &v : res.outputs)
+          if (v.defined() && v.dims.size() >= 2 && v.dims[1] == ctx->seq) v.dims[1] = job->inputs[0].dims[1];
       res.rows = slice.processed_length;
       res.ok = true;
       offset += slice.processed_length;

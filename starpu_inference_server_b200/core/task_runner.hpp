@@ -66,8 +66,9 @@ struct InferenceJob {
   }
 };
 
-// batch_composition_policy.cpp:102-151
-auto can_merge_jobs(const InferenceJob *lhs, const InferenceJob *rhs) -> bool;
+// batch_composition_policy.cpp:102-151.  variable_length: dims[1], the sequence
+// length, may differ between the two requests; every other rule of the reference stands.
+auto can_merge_jobs(const InferenceJob *lhs, const InferenceJob *rhs, bool variable_length = false) -> bool;
 
 struct VectorResizeSpec {
   std::size_t element_count;
@@ -83,6 +84,14 @@ auto copy_job_inputs_to_slot(const InferenceJob *job, const std::vector<const In
                              const std::vector<std::byte *> &base_ptrs,
                              const std::vector<HostBufferInfo> &buffer_infos) -> std::size_t;
 
+// Variable-length host gather: like copy_job_inputs_to_slot, but every sample row of
+// every request (dims [b, L, ...], L <= seq) is padded with zero bytes to `seq` (token id 0 = [PAD], mask 0),
+// so the slot holds one contiguous [sum b, seq, ...] array per input; nx := sum(b) * seq * rest.
+auto copy_job_inputs_to_slot_padded(const InferenceJob *job, const std::vector<const InferenceJob *> &pending_jobs,
+                                    const std::vector<starpu_data_handle_t> &handles,
+                                    const std::vector<std::byte *> &base_ptrs,
+                                    const std::vector<HostBufferInfo> &buffer_infos, int64_t seq) -> std::size_t;
+
 struct SubJobSliceResult {
   std::vector<HostTensor> outputs;
   int64_t processed_length = 0;
@@ -96,6 +105,10 @@ struct ModelConfig {  // the slice of models/*.yml the path needs (config_loader
   std::vector<TensorConfig> inputs, outputs;
   int max_batch_size = 1;
   int pool_size = 12;  // models/bert.yml: pool_size
+  // requests may carry any sequence length L <= inputs[*].dims[1]; a batch is padded to
+  // the longest request it holds (mask synthesised by the zero padding), slots stay sized by the configured
+  // dims[1] (= max_seq), and a single-sample request gets only its own L rows back.
+  bool variable_length = false;
 };
 
 // StarPUSetup + StarPUTaskRunner rolled into what the path needs: owns the codelet and the

@@ -22,7 +22,7 @@ SYMBOLS = [
     "spu_server_create", "spu_server_destroy", "spu_server_submit_batch", "spu_server_enqueue", "spu_server_wait",
     "spu_server_wait_all", "spu_server_stats", "spu_host_last_error", "spu_host_codelet_fields",
     "spu_host_buffer_byte_size", "spu_host_select_replica", "spu_host_gather_to_slot", "spu_host_slice_rows",
-    "spu_host_can_merge", "spu_host_call_cuda_func_affine",
+    "spu_host_can_merge", "spu_host_call_cuda_func_affine", "spu_host_can_merge_varlen", "spu_host_gather_padded",
 ]
 
 
@@ -36,12 +36,12 @@ class ServerCfg(C.Structure):
                 ("batch_coalesce_timeout_ms", C.c_int32), ("n_inputs", C.c_int32), ("n_outputs", C.c_int32),
                 ("inputs", TensorCfg * MAX_IO), ("outputs", TensorCfg * MAX_IO), ("model_kind", C.c_int32),
                 ("replicas", C.c_void_p * MAX_DEV), ("n_workspaces", C.c_int32), ("affine_scale", C.c_float),
-                ("affine_shift", C.c_float)]
+                ("affine_shift", C.c_float), ("variable_length", C.c_int32)]
 
 
 class Request(C.Structure):
     _fields_ = [("request_id", C.c_int32), ("batch", C.c_int64), ("inputs", C.c_void_p * MAX_IO),
-                ("outputs", C.c_void_p * MAX_IO)]
+                ("outputs", C.c_void_p * MAX_IO), ("seq_len", C.c_int64)]
 
 
 class Result(C.Structure):
@@ -91,6 +91,10 @@ def lib():
     L.spu_host_slice_rows.restype = i64
     L.spu_host_can_merge.argtypes = [C.POINTER(i64), i32, i32, C.POINTER(i64), i32, i32]
     L.spu_host_can_merge.restype = i32
+    L.spu_host_can_merge_varlen.argtypes = [C.POINTER(i64), i32, i32, C.POINTER(i64), i32, i32]
+    L.spu_host_can_merge_varlen.restype = i32
+    L.spu_host_gather_padded.argtypes = [C.POINTER(vp), C.POINTER(i64), i32, i64, vp, u64, C.POINTER(u64)]
+    L.spu_host_gather_padded.restype = i32
     L.spu_host_call_cuda_func_affine.argtypes = [vp, vp, u64, f32, f32, i32, i32, vp, i32, i32, C.POINTER(i64)]
     L.spu_host_call_cuda_func_affine.restype = i32
     _lib = L
@@ -125,8 +129,10 @@ class Server:
 
     def __init__(self, inputs, outputs, device_ids=(0,), replicas=(), model_kind=MODEL_BERT, max_batch_size=32,
                  pool_size=12, nworker_per_cuda=1, cuda_pipeline=2, batch_coalesce_timeout_ms=0, n_workspaces=1,
-                 affine=(1.0, 0.0)):
+                 affine=(1.0, 0.0), variable_length=False):
         cfg = ServerCfg()
+        cfg.variable_length = 1 if variable_length else 0
+        self.variable_length = bool(variable_length)
         cfg.n_devices = len(device_ids)
         for i, d in enumerate(device_ids):
             cfg.device_ids[i] = d
@@ -154,6 +160,8 @@ class Server:
     def _request(self, request_id, batch, in_arrays, out_arrays):
         rq = Request()
         rq.request_id, rq.batch = request_id, batch
+        # variable-length servers: the request's own sequence length is dims[1] of its first input array
+        rq.seq_len = int(in_arrays[0].shape[1]) if self.variable_length and len(in_arrays[0].shape) >= 2 else 0
         for i, a in enumerate(in_arrays):
             rq.inputs[i] = a.ctypes.data if hasattr(a, "ctypes") else a.data_ptr()
         for i, a in enumerate(out_arrays):

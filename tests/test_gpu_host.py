@@ -154,3 +154,54 @@ def test_bert_through_the_task_path(host, bert_tiny):
         out = np.zeros((1, S, H + 8), np.float32)
         (r,) = srv.wait(srv.submit_batch([(0, 1, [ids[:1].copy(), mask[:1].copy()], [out])]))
         assert r.ok == 0 and srv.stats()["codelet_failures"] == 1
+
+
+def test_variable_length_requests_through_the_task_path(host, bert_tiny):
+    """SURVEY 8(f) row 1 on the served path: requests of different lengths merge into one task, the host gather pads
+    them to the batch's longest request (mask synthesised by the zero padding), the codelet runs [B, S_batch], and
+    every request gets exactly its own rows back.  Each response equals the direct C-ABI forward on the padded batch
+    bit for bit, and the fp32 oracle run on THAT REQUEST ALONE (its own length, no padding) within the tolerance."""
+    bo, spec, w, rep = bert_tiny
+    S_max, H = 32, spec.hidden
+    rng = np.random.default_rng(21)
+    lens = [17, 32, 1, 9, 24]
+    ids = [rng.integers(1, spec.vocab, size=(1, n), dtype=np.int64) for n in lens]
+    ones = [np.ones((1, n), np.int64) for n in lens]
+    S_b = max(lens)
+    ids_pad, mask_pad = np.zeros((len(lens), S_b), np.int64), np.zeros((len(lens), S_b), np.int64)
+    for i, n in enumerate(lens):
+        ids_pad[i, :n], mask_pad[i, :n] = ids[i][0], 1
+    direct = torch.empty(len(lens), S_b, H, device="cuda")
+    rep.forward_async(torch.from_numpy(ids_pad).cuda(), torch.from_numpy(mask_pad).cuda(), direct, ws=1)
+    torch.cuda.synchronize()
+    direct = direct.cpu().numpy()
+    with host.Server(inputs=[("input_ids", "i64", [1, S_max]), ("attention_mask", "i64", [1, S_max])],
+                     outputs=[("output0", "f32", [1, S_max, H])], replicas=[rep], model_kind=host.MODEL_BERT,
+                     max_batch_size=8, pool_size=2, n_workspaces=2, variable_length=True) as srv:
+        outs = [np.full((1, n, H), np.nan, np.float32) for n in lens]
+        reqs = [(i, 1, [ids[i], ones[i]], [outs[i]]) for i in range(len(lens))]
+        res = srv.wait(srv.submit_batch(reqs))
+        assert all(r.ok == 1 and r.batch_rows == len(lens) for r in res)
+        for i, n in enumerate(lens):
+            assert (outs[i][0] == direct[i, :n]).all(), f"request {i}"
+            alone = bo.bert_forward(w, spec, ids[i], ones[i])
+            assert np.abs(outs[i] - alone).max() / np.abs(alone).max() < 2e-2, f"request {i} vs oracle"
+        # a shorter batch lands a smaller D2H: second task holds only short requests
+        short = [np.full((1, n, H), np.nan, np.float32) for n in (3, 5)]
+        res = srv.wait(srv.submit_batch([(10, 1, [ids[0][:, :3].copy(), ones[0][:, :3].copy()], [short[0]]),
+                                         (11, 1, [ids[1][:, :5].copy(), ones[1][:, :5].copy()], [short[1]])]))
+        assert all(r.ok == 1 for r in res) and np.isfinite(short[0]).all() and np.isfinite(short[1]).all()
+        # dynamic batching merges different lengths too
+        outs2 = [np.full((1, n, H), np.nan, np.float32) for n in lens]
+        tickets = [srv.enqueue(100 + i, 1, [ids[i], ones[i]], [outs2[i]]) for i in range(len(lens))]
+        for t in tickets:
+            (r,) = srv.wait(t)
+            assert r.ok == 1
+        for i in range(len(lens)):
+            alone = bo.bert_forward(w, spec, ids[i], ones[i])
+            assert np.abs(outs2[i] - alone).max() / np.abs(alone).max() < 2e-2
+        # longer than the configured cap: refused before anything is copied
+        too_long = np.ones((1, S_max + 1), np.int64)
+        with pytest.raises(host.HostError):
+            srv.wait(srv.submit_batch([(0, 1, [too_long, too_long], [None])]))
+

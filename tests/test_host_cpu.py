@@ -133,6 +133,63 @@ def test_gather_matches_oracle_bytes(host, oracle_gs):
     assert (slot == want).all() and nx == onx.value == 8 * 128 and total == obytes.value
 
 
+def _gather_padded(host, rows, seq, cap_rows):
+    n = len(rows)
+    srcs = (C.c_void_p * n)(*[r.ctypes.data for r in rows])
+    lens = (C.c_int64 * n)(*[r.size for r in rows])
+    slot = np.full(cap_rows * seq, -77, np.int64)
+    nx = C.c_uint64()
+    rc = host.lib().spu_host_gather_padded(srcs, lens, n, seq, slot.ctypes.data, slot.nbytes, C.byref(nx))
+    return rc, slot, nx.value
+
+
+def test_varlen_gather_known_answer(host):
+    """requests {1,2,3} + {4} padded to the batch max 3 -> 1,2,3,4,0,0 and nx == 6."""
+    rc, slot, nx = _gather_padded(host, [np.array([1, 2, 3], np.int64), np.array([4], np.int64)], 3, 4)
+    assert rc == 0 and nx == 6
+    assert slot[:6].tolist() == [1, 2, 3, 4, 0, 0] and (slot[6:] == -77).all()
+
+
+def test_varlen_gather_matches_oracle(host, oracle_gs):
+    """The padded host gather of ids and of an all-ones mask equals the C oracle's gather+pad+mask."""
+    rng = np.random.default_rng(9)
+    lens = [128, 1, 77, 16, 100]
+    seq = max(lens)
+    ids = [rng.integers(1, 30522, size=n, dtype=np.int64) for n in lens]
+    ones = [np.ones(n, np.int64) for n in lens]
+    rc, got_ids, nx = _gather_padded(host, ids, seq, 8)
+    rc2, got_mask, _ = _gather_padded(host, ones, seq, 8)
+    assert rc == 0 and rc2 == 0 and nx == len(lens) * seq
+    n = len(lens)
+    PP = C.c_void_p * n
+    want_ids, want_mask = np.zeros((n, seq), np.int64), np.zeros((n, seq), np.int64)
+    oracle_gs.oracle_gather_pad_mask.argtypes = [C.POINTER(C.c_void_p), C.c_void_p, C.POINTER(C.c_int32), C.c_size_t,
+                                                 C.c_size_t, C.c_int64, C.c_void_p, C.c_void_p]
+    assert oracle_gs.oracle_gather_pad_mask(PP(*[a.ctypes.data for a in ids]), None, (C.c_int32 * n)(*lens), n, seq, 0,
+                                            want_ids.ctypes.data, want_mask.ctypes.data) == 0
+    assert (got_ids[:n * seq].reshape(n, seq) == want_ids).all()
+    assert (got_mask[:n * seq].reshape(n, seq) == want_mask).all()
+
+
+def test_varlen_gather_rejects_long_and_overflow(host):
+    rc, _, _ = _gather_padded(host, [np.arange(5, dtype=np.int64)], 4, 4)   # request longer than the batch seq
+    assert rc == 1 and "variable-length input" in host.last_error()
+    rc, _, _ = _gather_padded(host, [np.arange(4, dtype=np.int64)] * 3, 4, 2)  # 3 rows into a 2-row slot
+    assert rc == 1 and "exceeds allocated slot buffer capacity" in host.last_error()
+
+
+def test_can_merge_jobs_variable_length(host):
+    I64 = 3
+    m = lambda da, db, tb=I64: host.lib().spu_host_can_merge_varlen(  # noqa: E731
+        (C.c_int64 * len(da))(*da), len(da), I64, (C.c_int64 * len(db))(*db), len(db), tb)
+    assert m([1, 128], [1, 64]) == 1          # only the sequence dim is relaxed
+    assert m([1, 128], [3, 17]) == 1
+    assert m([1, 128, 4], [1, 64, 4]) == 1
+    assert m([1, 128, 4], [1, 64, 5]) == 0    # trailing dims past the sequence still have to match
+    assert m([1, 128], [1, 64], 0) == 0       # dtype
+    assert m([1, 128], [1, 64, 1]) == 0       # rank
+
+
 def test_gather_capacity_exception(host):
     a = np.zeros(8, np.float32)
     rc, _, _, _ = _gather(host, [a, a, a], 4, 64)
