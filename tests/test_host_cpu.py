@@ -163,10 +163,12 @@ def test_varlen_gather_matches_oracle(host, oracle_gs):
     n = len(lens)
     PP = C.c_void_p * n
     want_ids, want_mask = np.zeros((n, seq), np.int64), np.zeros((n, seq), np.int64)
-    oracle_gs.oracle_gather_pad_mask.argtypes = [C.POINTER(C.c_void_p), C.c_void_p, C.POINTER(C.c_int32), C.c_size_t,
-                                                 C.c_size_t, C.c_int64, C.c_void_p, C.c_void_p]
-    assert oracle_gs.oracle_gather_pad_mask(PP(*[a.ctypes.data for a in ids]), None, (C.c_int32 * n)(*lens), n, seq, 0,
-                                            want_ids.ctypes.data, want_mask.ctypes.data) == 0
+    lens32 = np.array(lens, np.int32)
+    # no argtypes on the shared oracle handle (other tests call it with explicit ctypes values)
+    assert oracle_gs.oracle_gather_pad_mask(PP(*[a.ctypes.data for a in ids]), None, lens32.ctypes.data_as(C.c_void_p),
+                                            C.c_size_t(n), C.c_size_t(seq), C.c_int64(0),
+                                            want_ids.ctypes.data_as(C.c_void_p),
+                                            want_mask.ctypes.data_as(C.c_void_p)) == 0
     assert (got_ids[:n * seq].reshape(n, seq) == want_ids).all()
     assert (got_mask[:n * seq].reshape(n, seq) == want_mask).all()
 
