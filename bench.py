@@ -205,6 +205,8 @@ def run_b200(args, rank, local_rank, world):
     n_pipe = 4  # workspaces / CUDA workers, like STARPU_NWORKER_PER_CUDA=4 (models/bert.yml:6-8)
     flags = {"bf16": capi.SPU_PREC_BF16, "fp8": capi.SPU_PREC_FP8_E4M3,
              "fp8x6": capi.SPU_PREC_FP8_E4M3 | (6 << 8)}[args.precision]
+    if args.output_bf16:
+        flags |= capi.SPU_OUTPUT_BF16
     if args.auto_graph:
         # the codelet path replays a CUDA graph from the second sighting of a slot's device
         # buffers on (warm-up capture, src/core/warmup.cpp:225-299)
@@ -219,7 +221,8 @@ def run_b200(args, rank, local_rank, world):
     true_tokens = float(np.mean([m.sum() for _, m in host]))  # FLOPs are charged on unpadded tokens
     ids_d = [torch.from_numpy(i).to(dev) for i, _ in host]
     mask_d = [torch.from_numpy(m).to(dev) for _, m in host]
-    out_d = [torch.empty(B, S, spec.hidden, device=dev) for _ in range(n_pipe)]
+    out_d = [torch.empty(B, S, spec.hidden, device=dev, dtype=torch.bfloat16 if args.output_bf16 else torch.float32)
+             for _ in range(n_pipe)]
     stream = torch.cuda.Stream(device=dev)
     if flags & capi.SPU_PREC_FP8_E4M3:
         # per-tensor activation scales from a 32-sequence calibration draw
@@ -296,7 +299,7 @@ def run_b200(args, rank, local_rank, world):
     e2e_pipeline = int(os.environ.get("SPU_BENCH_PIPELINE", 4))
     e2e_pool = int(os.environ.get("SPU_BENCH_POOL", 12))
     io = dict(inputs=[("input_ids", "i64", [1, S]), ("attention_mask", "i64", [1, S])],
-              outputs=[("output0", "f32", [1, S, spec.hidden])])
+              outputs=[("output0", "bf16" if args.output_bf16 else "f32", [1, S, spec.hidden])])
     srv = hostapi.Server(**io, replicas=[rep], device_ids=[local_rank], model_kind=hostapi.MODEL_BERT,
                          max_batch_size=B, pool_size=e2e_pool, nworker_per_cuda=e2e_workers, cuda_pipeline=e2e_pipeline,
                          n_workspaces=n_pipe)
@@ -359,13 +362,13 @@ def run_b200(args, rank, local_rank, world):
                                   else "(variant of BASELINE configs[1])")
                                + "; random-init weights seed 0, ids U[0,30522), "
                                + ("all-ones mask" if args.min_len is None else f"lengths U[{args.min_len},{S}] padded+masked"),
-                   "batch": B, "seq_len": S, "replicas": world, "resident_streams": n_str,
+                   "batch": B, "seq_len": S, "replicas": world, "output_dtype": "bf16" if args.output_bf16 else "f32", "resident_streams": n_str,
                    "mean_true_tokens_per_batch": true_tokens,
                    "l2": "no explicit flush: each step streams 170 MB of bf16 weights plus ~110 MB of activations "
                          "(> 126 MB L2) and input batches rotate over 4 distinct buffers"},
         "clocks": clocks,
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 2 * B * S * 8,
-                "d2h_bytes_per_step": B * S * HIDDEN * 4, "checksum": checksum,
+                "d2h_bytes_per_step": B * S * HIDDEN * (2 if args.output_bf16 else 4), "checksum": checksum,
                 "path": "libspu_host.so: per-request host buffers -> host gather -> task -> H2D -> codelet -> D2H -> "
                         f"slices ({e2e_workers} CUDA workers x pipeline {e2e_pipeline}, pool {e2e_pool}, "
                         + ("CUDA-graph replay per (worker, slot) tuple)" if args.auto_graph else "eager launches)"),
@@ -421,6 +424,8 @@ def main():
     ap.add_argument("--min-len", type=int, default=None, help="variable-length requests: lengths U[min_len, seq]")
     ap.add_argument("--streams", type=int, default=2, help="CUDA workers issuing resident tasks round-robin")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--output-bf16", action="store_true",
+                    help="variant: output0 as bf16 (SPU_OUTPUT_BF16, SURVEY 8(f) row 3): half the response bytes")
     ap.add_argument("--no-auto-graph", dest="auto_graph", action="store_false",
                     help="e2e path launches every kernel eagerly instead of replaying CUDA graphs captured on the second "
                          "sighting of a (worker, slot) tuple (SPU_FORWARD_AUTO_GRAPH; profiles/r06_e2e_config.md: "

@@ -69,6 +69,11 @@ typedef struct spu_bert_desc {
 /* Allocate the per-workspace staging (ids, mask, batched output) that
  * spu_bert_forward_requests_async needs.  Without it that call returns SPU_ERR_UNSUPPORTED. */
 #define SPU_REQUEST_IO (1u << 17)
+/* SURVEY 8(f) row 3 (response path): output0 of spu_bert_forward_async / _capture is bf16
+ * [batch, seq, hidden] (the fp32 last_hidden_state rounded to nearest even by the last LayerNorm)
+ * instead of fp32: half the D2H and response bytes.  spu_bert_output_bytes follows.  Declare the
+ * model's output as TYPE_BF16 in models/<name>.yml.  Not combinable with SPU_REQUEST_IO. */
+#define SPU_OUTPUT_BF16 (1u << 18)
 
 /* Number of weight tensors spu_bert_replica_create expects: 5 + 16*layers, in the
  * order of the HF state dict restated in oracle/bert_oracle.py:weight_names()

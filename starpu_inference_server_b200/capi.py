@@ -17,6 +17,7 @@ SPU_ERR_INVALID, SPU_ERR_CUDA, SPU_ERR_CAPACITY, SPU_ERR_UNSUPPORTED, SPU_ERR_NO
 SPU_EPI_BIAS, SPU_EPI_BIAS_GELU, SPU_EPI_BIAS_RESID = 0, 1, 2
 SPU_PREC_BF16, SPU_PREC_FP8_E4M3 = 0, 1
 SPU_FORWARD_AUTO_GRAPH = 1 << 16  # capture a CUDA graph on the second sighting of a pointer tuple
+SPU_OUTPUT_BF16 = 1 << 18  # output0 is bf16 [B,S,H] (response path)
 SPU_REQUEST_IO = 1 << 17  # allocate the staging spu_bert_forward_requests_async needs
 STAGE_NAMES = ["embed_ln", "gemm_qkv", "attention", "gemm_attn_out", "ln1", "gemm_ffn1", "gemm_ffn2", "ln2"]
 

@@ -104,6 +104,13 @@ struct spu_server {
       std::snprintf(out.error, sizeof(out.error), "%s", res.error.c_str());
       if (res.ok && !res.outputs.empty() && res.outputs[0].defined() && res.outputs[0].type == ScalarType::Float32)
         std::memcpy(&out.first_value, res.outputs[0].data, sizeof(float));
+      else if (res.ok && !res.outputs.empty() && res.outputs[0].defined() &&
+               res.outputs[0].type == ScalarType::BFloat16) {
+        uint16_t h = 0;
+        std::memcpy(&h, res.outputs[0].data, sizeof(h));
+        const uint32_t u = static_cast<uint32_t>(h) << 16;
+        std::memcpy(&out.first_value, &u, sizeof(float));
+      }
       if (res.ok)
         // the response copy the reference makes per request (fill_output_tensor,
         // src/grpc/server/inference_service_io.cpp:377-419): slot view -> caller's buffer

@@ -186,8 +186,10 @@ spu_status enqueue_forward(spu_replica *r, Workspace &ws, const int64_t *ids, co
     if (SPU_ON(SPU_STAGE_GEMM_FFN2)) SPU_TRY(gemm_launch(p.ffn2, M, e, stream));
     SPU_MARK(SPU_STAGE_GEMM_FFN2);
     // the last LayerNorm writes last_hidden_state straight into the StarPU output buffer
-    if (SPU_ON(SPU_STAGE_LN2)) SPU_TRY(layernorm_launch(ws.x_f32, w.ln2_g, w.ln2_b, d.ln_eps, last ? out : ws.x_f32,
-                             last ? nullptr : ws.x_bf16, M, d.hidden, stream));
+    const bool out16 = last && (r->flags & SPU_OUTPUT_BF16) != 0;  // `out` is a bf16 buffer then
+    if (SPU_ON(SPU_STAGE_LN2)) SPU_TRY(layernorm_launch(ws.x_f32, w.ln2_g, w.ln2_b, d.ln_eps,
+                             out16 ? nullptr : (last ? out : ws.x_f32),
+                             out16 ? static_cast<void *>(out) : (last ? nullptr : ws.x_bf16), M, d.hidden, stream));
     SPU_MARK(SPU_STAGE_LN2);
   }
   return SPU_OK;
@@ -240,8 +242,10 @@ spu_status enqueue_forward_fp8(spu_replica *r, Workspace &ws, const int64_t *ids
     if (SPU_ON(SPU_STAGE_GEMM_FFN2)) SPU_TRY(gemm_launch(p.ffn2, M, e, stream));
     if (SPU_ON(SPU_STAGE_LN2)) {
       const bool n8 = !last && is8(l + 1);
-      SPU_TRY(layernorm_launch(ws.x_f32, w.ln2_g, w.ln2_b, d.ln_eps, last ? out : ws.x_f32,
-                               (last || n8) ? nullptr : ws.x_bf16, M, d.hidden, stream, 0, n8 ? ws.x_q : nullptr,
+      const bool out16 = last && (r->flags & SPU_OUTPUT_BF16) != 0;
+      SPU_TRY(layernorm_launch(ws.x_f32, w.ln2_g, w.ln2_b, d.ln_eps, out16 ? nullptr : (last ? out : ws.x_f32),
+                               out16 ? static_cast<void *>(out) : ((last || n8) ? nullptr : ws.x_bf16), M, d.hidden,
+                               stream, 0, n8 ? ws.x_q : nullptr,
                                n8 ? 1.f / r->layers[l + 1].sa_x : 1.f));
     }
   }
@@ -323,7 +327,7 @@ extern "C" spu_status spu_bert_replica_create(const spu_bert_desc *desc, const f
               SPU_ERR_UNSUPPORTED, "replica_create: hidden/ffn must be multiples of 64, hidden <= 1024");
   SPU_REQUIRE(max_batch > 0 && max_seq > 0 && max_seq <= desc->max_pos && n_workspaces > 0,
               SPU_ERR_INVALID, "replica_create: bad capacity");
-  SPU_REQUIRE((flags & ~(SPU_PREC_FP8_E4M3 | 0xff00u | SPU_FORWARD_AUTO_GRAPH | SPU_REQUEST_IO)) == 0 &&
+  SPU_REQUIRE((flags & ~(SPU_PREC_FP8_E4M3 | 0xff00u | SPU_FORWARD_AUTO_GRAPH | SPU_REQUEST_IO | SPU_OUTPUT_BF16)) == 0 &&
                   ((flags & SPU_PREC_FP8_E4M3) || (flags & 0xff00u) == 0),
               SPU_ERR_UNSUPPORTED, "replica_create: unsupported precision flag");
   if (flags & SPU_PREC_FP8_E4M3)
@@ -418,6 +422,8 @@ extern "C" spu_status spu_bert_forward_requests_async(spu_replica *r, int32_t ws
   SPU_REQUIRE(r != nullptr && r->kind == 0, SPU_ERR_INVALID, "forward_requests: not a BERT replica");
   SPU_REQUIRE((r->flags & SPU_REQUEST_IO) != 0, SPU_ERR_UNSUPPORTED,
               "forward_requests: replica was created without SPU_REQUEST_IO");
+  SPU_REQUIRE((r->flags & SPU_OUTPUT_BF16) == 0, SPU_ERR_UNSUPPORTED,
+              "forward_requests: fp32 responses only (SPU_OUTPUT_BF16 is set)");
   SPU_REQUIRE(ws_idx >= 0 && ws_idx < static_cast<int>(r->ws.size()), SPU_ERR_INVALID,
               "forward_requests: workspace index out of range");
   SPU_REQUIRE(src_ids && len && dsts, SPU_ERR_INVALID, "forward_requests: null table");
@@ -595,7 +601,8 @@ extern "C" spu_status spu_bert_stage_chain_ms(spu_replica *r, int32_t ws_idx, co
 
 extern "C" uint64_t spu_bert_output_bytes(const spu_replica *r, int32_t batch, int32_t seq) {
   if (r == nullptr || r->kind != 0 || batch <= 0 || seq <= 0) return 0;
-  return static_cast<uint64_t>(batch) * static_cast<uint64_t>(seq) * static_cast<uint64_t>(r->desc.hidden) * 4u;
+  return static_cast<uint64_t>(batch) * static_cast<uint64_t>(seq) * static_cast<uint64_t>(r->desc.hidden) *
+         ((r->flags & SPU_OUTPUT_BF16) ? 2u : 4u);
 }
 
 extern "C" int32_t spu_bert_forward_launch_count(const spu_replica *r) {

@@ -257,6 +257,32 @@ def test_forward_requests_stages_1_to_4(spu, where, full_rows):
     rep.close()
 
 
+def test_bf16_output_option(spu):
+    """SPU_OUTPUT_BF16: output0 is the fp32 last_hidden_state rounded to bf16 by the last
+    LayerNorm -- bit-identical to rounding the fp32 output, half the bytes."""
+    from oracle import bert_oracle as bo
+    from starpu_inference_server_b200.bert import BertReplica
+
+    cfg = bo.BERT_TINY
+    w = bo.make_weights(cfg, 0)
+    ids, mask = bo.make_inputs(cfg, 3, 40, seed=8, min_len=5)
+    ids_d, mask_d = torch.from_numpy(ids).cuda(), torch.from_numpy(mask).cuda()
+    r32 = BertReplica(w, max_batch=4, max_seq=64)
+    r16 = BertReplica(w, max_batch=4, max_seq=64, flags=spu.SPU_OUTPUT_BF16)
+    o32 = torch.empty(3, 40, cfg.hidden, device="cuda")
+    o16 = torch.full((3, 40, cfg.hidden), float("nan"), dtype=torch.bfloat16, device="cuda")
+    guard = torch.full((16,), 7.0, dtype=torch.bfloat16, device="cuda")  # a bf16-sized output must not be overrun
+    r32.forward_async(ids_d, mask_d, o32)
+    r16.forward_async(ids_d, mask_d, o16)
+    torch.cuda.synchronize()
+    assert torch.equal(o16, o32.to(torch.bfloat16))
+    assert (guard == 7.0).all()
+    lib = spu.lib()
+    assert lib.spu_bert_output_bytes(r16._h, 3, 40) * 2 == lib.spu_bert_output_bytes(r32._h, 3, 40)
+    r32.close()
+    r16.close()
+
+
 def test_capacity_and_argument_errors(base, spu):
     bo, w, r = base
     ids = torch.zeros(65, 512, dtype=torch.int64, device="cuda")

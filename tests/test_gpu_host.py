@@ -205,3 +205,28 @@ def test_variable_length_requests_through_the_task_path(host, bert_tiny):
         with pytest.raises(host.HostError):
             srv.wait(srv.submit_batch([(0, 1, [too_long, too_long], [None])]))
 
+
+def test_bf16_response_through_the_task_path(host, bert_tiny):
+    """models/<name>.yml output declared TYPE_BF16 + a replica created with SPU_OUTPUT_BF16: the slot, the D2H and
+    the per-request slices carry 2 bytes per element; values = the fp32 path's rounded to bf16."""
+    from starpu_inference_server_b200 import capi
+    from starpu_inference_server_b200.bert import BertReplica
+
+    bo, spec, w, rep32 = bert_tiny
+    S, H = 32, spec.hidden
+    ids, mask = bo.make_inputs(spec, 4, S, seed=5, min_len=4)
+    direct = torch.empty(4, S, H, device="cuda")
+    rep32.forward_async(torch.from_numpy(ids).cuda(), torch.from_numpy(mask).cuda(), direct, ws=1)
+    torch.cuda.synchronize()
+    want = direct.to(torch.bfloat16).cpu().view(torch.int16).numpy()
+    rep16 = BertReplica(w, max_batch=8, max_seq=32, n_workspaces=2, flags=capi.SPU_OUTPUT_BF16)
+    with host.Server(inputs=[("input_ids", "i64", [1, S]), ("attention_mask", "i64", [1, S])],
+                     outputs=[("output0", "bf16", [1, S, H])], replicas=[rep16], model_kind=host.MODEL_BERT,
+                     max_batch_size=8, pool_size=2, n_workspaces=2) as srv:
+        outs = [np.zeros((1, S, H), np.int16) for _ in range(4)]
+        res = srv.wait(srv.submit_batch([(i, 1, [ids[i:i + 1].copy(), mask[i:i + 1].copy()], [outs[i]])
+                                         for i in range(4)]))
+        assert all(r.ok == 1 for r in res)
+        assert (np.concatenate(outs, 0) == want).all()
+    rep16.close()
+
