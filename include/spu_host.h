@@ -74,6 +74,12 @@ typedef struct spu_server_cfg {
    * gather pads with zeros (token id 0 = [PAD], mask 0) to its longest request, slots stay sized by the
    * configured dims[1], and a single-sample request gets only its own seq_len rows back. */
   int32_t variable_length;
+  /* variable_length servers, dynamic batching (spu_server_enqueue): > 0 buckets requests by
+   * ceil(seq_len / length_bucket): a batch only takes requests of its oldest request's bucket (the collector
+   * looks past other buckets' requests instead of closing the batch at the first one), so a batch pads to at
+   * most length_bucket - 1 extra tokens per row instead of to the longest request in arrival order.  The oldest
+   * queued request always opens the next batch, so no bucket starves.  0 = arrival order (the reference). */
+  int32_t length_bucket;
 } spu_server_cfg;
 
 typedef struct spu_request {
@@ -96,6 +102,7 @@ typedef struct spu_result {
   double latency_ms;    /* enqueued -> callback_end */
   float first_value;    /* outputs[0] row 0 element 0 read from the landed slot (fp32 outputs) */
   char error[192];
+  int64_t batch_seq;    /* variable_length servers: padded sequence length of the task it rode in (else 0) */
 } spu_result;
 
 typedef struct spu_server spu_server;

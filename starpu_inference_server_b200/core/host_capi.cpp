@@ -72,6 +72,7 @@ struct spu_server {
   std::thread collector;
   bool stop = false;
   int coalesce_ms = 0;
+  int length_bucket = 0;  // variable_length: requests per ceil(L / length_bucket) bucket batch together
   int forming = 0;  // batches popped from the queue but not yet submitted (guarded by qmu)
 
   std::shared_ptr<InferenceJob> make_job(const spu_request &rq, int64_t ticket, int index) {
@@ -96,6 +97,7 @@ struct spu_server {
       out.ok = res.ok ? 1 : 0;
       out.rows = res.rows;
       out.batch_rows = res.batch_rows;
+      out.batch_seq = res.batch_seq;
       out.worker_id = res.worker_id;
       out.device_id = res.device_id;
       out.executed_on = static_cast<int32_t>(res.executed_on);
@@ -166,7 +168,30 @@ struct spu_server {
         ++forming;
         int64_t rows = batch[0]->batch_size();
         const auto deadline = std::chrono::steady_clock::now() + std::chrono::milliseconds(coalesce_ms);
-        while (rows < model.max_batch_size) {
+        // variable-length bucketing: the batch belongs to the bucket of its oldest request; the collector
+        // looks past other buckets' requests (they keep their queue order and open later batches)
+        const bool bucketing = model.variable_length && length_bucket > 0 && !batch[0]->inputs.empty() &&
+                               batch[0]->inputs[0].dims.size() >= 2;
+        auto bucket_of = [&](const InferenceJob &j) {
+          return j.inputs.empty() || j.inputs[0].dims.size() < 2 ? int64_t{-1}
+                                                                 : (j.inputs[0].dims[1] - 1) / length_bucket;
+        };
+        while (bucketing && rows < model.max_batch_size) {
+          const int64_t mine = bucket_of(*batch[0]);
+          for (auto it = queue.begin(); it != queue.end() && rows < model.max_batch_size;) {
+            if (bucket_of(**it) == mine && can_merge_jobs(batch[0].get(), it->get(), true) &&
+                rows + (*it)->batch_size() <= model.max_batch_size) {
+              rows += (*it)->batch_size();
+              batch.push_back(*it);
+              it = queue.erase(it);
+            } else {
+              ++it;
+            }
+          }
+          if (rows >= model.max_batch_size || coalesce_ms <= 0 || stop) break;
+          if (qcv.wait_until(lk, deadline) == std::cv_status::timeout) break;  // else: new arrivals, rescan
+        }
+        while (!bucketing && rows < model.max_batch_size) {
           if (queue.empty()) {
             if (coalesce_ms <= 0 || stop) break;
             if (qcv.wait_until(lk, deadline) == std::cv_status::timeout && queue.empty()) break;
@@ -238,6 +263,7 @@ int32_t spu_server_create(const spu_server_cfg *cfg, spu_server **out) {
       s->model.max_batch_size = cfg->max_batch_size > 0 ? cfg->max_batch_size : 1;
       s->model.pool_size = cfg->pool_size > 0 ? cfg->pool_size : 12;
       s->model.variable_length = cfg->variable_length != 0;
+      s->length_bucket = cfg->length_bucket > 0 ? cfg->length_bucket : 0;
       s->coalesce_ms = cfg->batch_coalesce_timeout_ms;
       std::vector<int> dev_ids;
       std::vector<DeviceModel *> models;

@@ -400,6 +400,7 @@ void TaskRunner::finalize(CallbackContext *ctx) {
     res.device_id = ctx->device_id;
     res.executed_on = ctx->executed_on;
     res.batch_rows = ctx->effective_batch;
+    res.batch_seq = ctx->seq;
     res.timing = ctx->timing;
     res.timing.enqueued_time = job->timing.enqueued_time;
     if (codelet_ok && all_acquired) {

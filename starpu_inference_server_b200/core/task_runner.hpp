@@ -53,6 +53,7 @@ struct JobResult {
   DeviceType executed_on = DeviceType::Unknown;
   JobTiming timing;
   int64_t batch_rows = 0;  // effective batch size of the task this request rode in
+  int64_t batch_seq = 0;   // variable_length: padded sequence length of that task (0 = fixed shapes)
 };
 
 struct InferenceJob {

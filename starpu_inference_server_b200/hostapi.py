@@ -36,7 +36,8 @@ class ServerCfg(C.Structure):
                 ("batch_coalesce_timeout_ms", C.c_int32), ("n_inputs", C.c_int32), ("n_outputs", C.c_int32),
                 ("inputs", TensorCfg * MAX_IO), ("outputs", TensorCfg * MAX_IO), ("model_kind", C.c_int32),
                 ("replicas", C.c_void_p * MAX_DEV), ("n_workspaces", C.c_int32), ("affine_scale", C.c_float),
-                ("affine_shift", C.c_float), ("variable_length", C.c_int32)]
+                ("affine_shift", C.c_float), ("variable_length", C.c_int32),
+                ("length_bucket", C.c_int32)]
 
 
 class Request(C.Structure):
@@ -48,7 +49,7 @@ class Result(C.Structure):
     _fields_ = [("request_id", C.c_int32), ("ok", C.c_int32), ("rows", C.c_int64), ("batch_rows", C.c_int64),
                 ("worker_id", C.c_int32), ("device_id", C.c_int32), ("executed_on", C.c_int32),
                 ("codelet_ms", C.c_double), ("task_ms", C.c_double), ("latency_ms", C.c_double),
-                ("first_value", C.c_float), ("error", C.c_char * 192)]
+                ("first_value", C.c_float), ("error", C.c_char * 192), ("batch_seq", C.c_int64)]
 
 
 _lib = None
@@ -129,9 +130,10 @@ class Server:
 
     def __init__(self, inputs, outputs, device_ids=(0,), replicas=(), model_kind=MODEL_BERT, max_batch_size=32,
                  pool_size=12, nworker_per_cuda=1, cuda_pipeline=2, batch_coalesce_timeout_ms=0, n_workspaces=1,
-                 affine=(1.0, 0.0), variable_length=False):
+                 affine=(1.0, 0.0), variable_length=False, length_bucket=0):
         cfg = ServerCfg()
         cfg.variable_length = 1 if variable_length else 0
+        cfg.length_bucket = int(length_bucket)
         self.variable_length = bool(variable_length)
         cfg.n_devices = len(device_ids)
         for i, d in enumerate(device_ids):

@@ -230,3 +230,29 @@ def test_bf16_response_through_the_task_path(host, bert_tiny):
         assert (np.concatenate(outs, 0) == want).all()
     rep16.close()
 
+
+def test_length_bucketing_in_the_collector(host, bert_tiny):
+    """variable_length + length_bucket: requests arriving short/long interleaved are batched per bucket of
+    ceil(L / 16) (each task pads to its own bucket's longest request), every response still equals the fp32 oracle
+    on that request alone, and the oldest request always opens the next batch."""
+    bo, spec, w, rep = bert_tiny
+    S_max, H = 32, spec.hidden
+    rng = np.random.default_rng(4)
+    lens = [5, 30, 6, 29, 7, 31, 4, 28]
+    ids = [rng.integers(1, spec.vocab, size=(1, n), dtype=np.int64) for n in lens]
+    ones = [np.ones((1, n), np.int64) for n in lens]
+    with host.Server(inputs=[("input_ids", "i64", [1, S_max]), ("attention_mask", "i64", [1, S_max])],
+                     outputs=[("output0", "f32", [1, S_max, H])], replicas=[rep], model_kind=host.MODEL_BERT,
+                     max_batch_size=4, pool_size=2, n_workspaces=2, batch_coalesce_timeout_ms=200,
+                     variable_length=True, length_bucket=16) as srv:
+        outs = [np.full((1, n, H), np.nan, np.float32) for n in lens]
+        tickets = [srv.enqueue(i, 1, [ids[i], ones[i]], [outs[i]]) for i in range(len(lens))]
+        res = [srv.wait(t)[0] for t in tickets]
+        assert all(r.ok == 1 for r in res)
+        for i, (n, r) in enumerate(zip(lens, res)):
+            assert r.batch_rows == 4, (i, r.batch_rows)
+            assert r.batch_seq == (7 if n <= 16 else 31), (i, n, r.batch_seq)  # padded to its own bucket's longest
+            alone = bo.bert_forward(w, spec, ids[i], ones[i])
+            assert np.abs(outs[i] - alone).max() / np.abs(alone).max() < 2e-2
+        assert srv.stats()["tasks"] == 2
+
