@@ -1,17 +1,21 @@
 // tcgen05/TMEM fused masked-softmax attention for head_dim 64 (BERT-base / ViT-L heads), sm_100a.
 //   ctx[b, q, h, :] = softmax_k( q.k / 8 + mask_bias[b, k] ) . v
-// One CTA = 128 query rows of one (batch, head), 128 threads.  Q, K and V tiles arrive by TMA
+// One CTA = 128 query rows of one (batch, head).  Q, K and V tiles arrive by TMA
 // (3-D map over qkv viewed as [B, S, 3H]: rows past the end of a sequence are zero-filled, so
 // ragged S needs no special load path) into 128B-swizzled smem.  S = Q K^T is ONE 128x128x64
-// tcgen05.mma chain into TMEM; each thread then owns one query row (tcgen05.ld 32x32b), so the
+// tcgen05.mma chain into TMEM; a thread then owns (half of) one query row (tcgen05.ld 32x32b), so the
 // row max / row sum need no shuffles at all; P goes back to smem as a K-major bf16 operand and
 // O = P V runs as a second tcgen05.mma chain whose B operand is V as loaded (MN-major
 // descriptor, no transpose pass).  Scores and probabilities never touch HBM.
-//   SINGLE (S <= 128): P overwrites the dead Q|K tiles and O reuses the TMEM columns of S:
-//          48 KB smem + 128 TMEM columns per CTA -> 4 CTAs per SM, all (b, h) of a b<=49
-//          batch resident at once (the kernel is latency-bound there, not throughput-bound).
-//   MULTI  (S  > 128): K/V double-buffered (next tile's TMA overlaps this tile's softmax),
-//          online softmax with the running O in registers; 2 CTAs per SM.
+//   SINGLE (S <= 128): one thread per query row (128 threads); P overwrites the dead Q|K tiles and O reuses
+//          the TMEM columns of S: 48 KB smem + 128 TMEM columns + <=128 registers per CTA -> 4 CTAs per
+//          SM, all (b, h) of a b<=49 batch resident at once (the kernel is latency-bound there).
+//   MULTI  (S  > 128): KV loop with online softmax, TWO threads per query row (256 threads, each owning
+//          64 of a tile's 128 key columns and 32 output columns; max / sum exchanged through smem), K
+//          double-buffered, S_(j+1) issued under pass 2 of tile j into the second TMEM buffer, O_(j-1)
+//          collected one tile late; V single-buffered so that a CTA needs 97 KB -> 2 CTAs per SM.
+// Chunks / KV tiles behind the last live key of a hard-masked (padded) sequence are skipped: they add
+// exactly 0 to every row sum and to O.
 //
 // Restates the attention block of HF BertSelfAttention / torchvision MultiheadAttention that
 // LibTorch executes inside Module::forward (/root/reference/src/core/starpu_setup.cpp:610);
