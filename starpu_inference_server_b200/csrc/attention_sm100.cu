@@ -480,12 +480,7 @@ spu_status launch_tc(const CUtensorMap &map, const float *mask_bias, void *ctx, 
                      cudaStream_t stream, float q_inv_scale) {
   using Cfg = AttnCfg<MULTI>;
   auto kern = attention_tc_kernel<MULTI, OUT_E4M3>;
-  static std::once_flag once;
-  static cudaError_t attr_err = cudaSuccess;
-  std::call_once(once, [&] {
-    attr_err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes);
-  });
-  SPU_CUDA_TRY(attr_err);
+  SPU_CUDA_TRY((ensure_dynamic_smem<attention_tc_kernel<MULTI, OUT_E4M3>>(Cfg::kSmemBytes)));
   dim3 grid((seq + kTile - 1) / kTile, heads, batch);
   SPU_CUDA_TRY(launch_pdl(kern, grid, dim3(Cfg::kThreads), Cfg::kSmemBytes, stream, map, mask_bias, ctx, seq, heads,
                           q_inv_scale));

@@ -61,6 +61,22 @@ inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, s
 #endif
 
 #ifdef __CUDACC__
+// Opt a kernel into > 48 KB of dynamic shared memory.  The attribute is PER DEVICE, and one process may drive
+// several GPUs (spu_server with several device_ids): remember it per (kernel instantiation, device ordinal).
+template <auto Kern>
+inline cudaError_t ensure_dynamic_smem(int bytes) {
+  static unsigned long long done = 0;  // bit d = set on device d (ordinals < 64)
+  int dev = 0;
+  cudaGetDevice(&dev);
+  const unsigned long long bit = 1ull << (dev & 63);
+  if (__atomic_load_n(&done, __ATOMIC_ACQUIRE) & bit) return cudaSuccess;
+  const cudaError_t e = cudaFuncSetAttribute(Kern, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  if (e == cudaSuccess) __atomic_fetch_or(&done, bit, __ATOMIC_RELEASE);
+  return e;
+}
+#endif
+
+#ifdef __CUDACC__
 // ---- small device utilities ---------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void *p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));

@@ -578,13 +578,7 @@ spu_status launch_cfg(const GemmPlan &plan, const LaunchMaps &maps, const Kernel
                       cudaStream_t stream) {
   using Cfg = TileCfg<BLOCK_N, CG, EPI>;
   auto kern = gemm_tcgen05_kernel<BLOCK_N, CG, EPI, IN_FP8>;
-  static std::once_flag once;
-  static cudaError_t attr_err = cudaSuccess;
-  std::call_once(once, [&] {
-    attr_err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                    Cfg::kSmemBytes);
-  });
-  SPU_CUDA_TRY(attr_err);
+  SPU_CUDA_TRY((ensure_dynamic_smem<gemm_tcgen05_kernel<BLOCK_N, CG, EPI, IN_FP8>>(Cfg::kSmemBytes)));
   const int tiles = (plan.N / BLOCK_N) * ((a.M + kRowsPerCta * CG - 1) / (kRowsPerCta * CG));
   int dev = 0, sms = kNumSMsB200;
   cudaGetDevice(&dev);

@@ -256,3 +256,36 @@ def test_length_bucketing_in_the_collector(host, bert_tiny):
             assert np.abs(outs[i] - alone).max() / np.abs(alone).max() < 2e-2
         assert srv.stats()["tasks"] == 2
 
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs in one process")
+def test_two_devices_in_one_process(host):
+    """use_cuda: [{device_ids: [0, 1]}] (config_loader_device.hpp:104-149): one replica per device, one server; tasks
+    land on both devices and every response equals the single-device result bit for bit (kernel attributes such as
+    the dynamic shared-memory opt-in are per device)."""
+    from oracle import bert_oracle as bo
+    from starpu_inference_server_b200.bert import BertReplica
+
+    spec = bo.BERT_TINY
+    w = bo.make_weights(spec, 0)
+    S, H = 160, spec.hidden  # > 128: the KV-loop attention variant (101 KB of dynamic smem) on both devices
+    reps = [BertReplica(w, device=d, max_batch=4, max_seq=S, n_workspaces=1) for d in (0, 1)]
+    ids, mask = bo.make_inputs(spec, 4, S, seed=13, min_len=20)
+    direct = torch.empty(4, S, H, device="cuda:0")
+    reps[0].forward_async(torch.from_numpy(ids).cuda(0), torch.from_numpy(mask).cuda(0), direct)
+    torch.cuda.synchronize(0)
+    want = direct.cpu().numpy()
+    with host.Server(inputs=[("input_ids", "i64", [1, S]), ("attention_mask", "i64", [1, S])],
+                     outputs=[("output0", "f32", [1, S, H])], replicas=reps, device_ids=[0, 1],
+                     model_kind=host.MODEL_BERT, max_batch_size=4, pool_size=4, n_workspaces=1) as srv:
+        devices = set()
+        for rnd in range(8):
+            outs = [np.zeros((1, S, H), np.float32) for _ in range(4)]
+            res = srv.wait(srv.submit_batch([(i, 1, [ids[i:i + 1].copy(), mask[i:i + 1].copy()], [outs[i]])
+                                             for i in range(4)], fixed_worker=rnd % 2))
+            assert all(r.ok == 1 for r in res), res[0].error
+            devices.add(res[0].device_id)
+            assert (np.concatenate(outs, 0) == want).all(), f"round {rnd} on device {res[0].device_id}"
+        assert devices == {0, 1}
+    for r in reps:
+        r.close()
+
