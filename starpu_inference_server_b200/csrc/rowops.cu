@@ -113,7 +113,7 @@ layernorm_kernel(const float *__restrict__ x, const float *__restrict__ gamma,
                  uint8_t *out_q, float q_inv_scale) {
   pdl_wait_prior_grid();
   pdl_launch_dependents();
-  const int row = blockIdx.x * (kRowThreads / 32) + (threadIdx.x >> 5);
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (row >= rows) return;
   const int lane = threadIdx.x & 31;
   const int nchunk = hidden >> 2;
@@ -307,8 +307,14 @@ spu_status layernorm_launch(const float *x, const float *gamma, const float *bet
   SPU_REQUIRE(hidden % 4 == 0 && hidden <= 128 * kMaxChunksPerLane, SPU_ERR_UNSUPPORTED,
               "layernorm: hidden must be a multiple of 4 and <= 1024");
   SPU_REQUIRE(rows > 0, SPU_ERR_INVALID, "layernorm: empty input");
-  const int grid = (rows + kRowThreads / 32 - 1) / (kRowThreads / 32);
-  SPU_CUDA_TRY(launch_pdl(layernorm_kernel, dim3(grid), dim3(kRowThreads), 0, stream, x, gamma, beta, eps, out_f32,
+  // rows per CTA: SPU_LN_THREADS (64..256, experiments) / 32; default 8 rows
+  static const int threads = [] {
+    const char *e = std::getenv("SPU_LN_THREADS");
+    const int t = e ? std::atoi(e) : 0;
+    return (t == 64 || t == 128 || t == 256) ? t : kRowThreads;
+  }();
+  const int grid = (rows + threads / 32 - 1) / (threads / 32);
+  SPU_CUDA_TRY(launch_pdl(layernorm_kernel, dim3(grid), dim3(threads), 0, stream, x, gamma, beta, eps, out_f32,
                           static_cast<__nv_bfloat16 *>(out_bf16), rows, hidden, in_row_stride,
                           static_cast<uint8_t *>(out_q), q_inv_scale));
   return SPU_OK;
