@@ -63,8 +63,26 @@ def make_weights(cfg, seed=0):
 def main():
     B = int(sys.argv[1]) if len(sys.argv) > 1 else 64
     steps = int(sys.argv[2]) if len(sys.argv) > 2 else 30
+    # under torchrun: one replica + process per GPU, no collective on the data path (gloo barrier + max of times)
+    import torch.distributed as dist
+    world, rank, local = (int(os.environ.get(k, d)) for k, d in (("WORLD_SIZE", 1), ("RANK", 0), ("LOCAL_RANK", 0)))
+    if world > 1:
+        dist.init_process_group("gloo")
+    torch.cuda.set_device(local)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+
+    def slowest(v):
+        t = torch.tensor([v], dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t[0])
+
     cfg = VitConfig()
-    rep = VitReplica(make_weights(cfg), cfg, max_batch=B, n_workspaces=4)
+    rep = VitReplica(make_weights(cfg), cfg, device=local, max_batch=B, n_workspaces=4)
     rng = np.random.Generator(np.random.PCG64(7))
     host = [rng.random((B, 3, 224, 224), dtype=np.float32) for _ in range(2)]
     x = [torch.from_numpy(h).cuda() for h in host]
@@ -74,33 +92,40 @@ def main():
     with torch.cuda.stream(s):
         for i in range(3):
             rep.forward_async(x[i % 2], out, stream=s)
+    barrier()
+    with torch.cuda.stream(s):
         e0.record(s)
         for i in range(steps):
             rep.forward_async(x[i % 2], out, stream=s)
         e1.record(s)
-    torch.cuda.synchronize()
-    ms = e0.elapsed_time(e1) / steps
+    barrier()
+    ms = slowest(e0.elapsed_time(e1)) / steps
     gemm_flop = (2 * 196 * 768 * 1024 + 24 * 24 * 197 * 1024 * 1024 + 2 * 1024 * 1000) * B
     res = {"workload": f"ViT-L/16 224x224 batch {B} bf16 (BASELINE configs[4])", "ms_per_step": ms,
-           "images_per_s": B / (ms / 1e3), "dense_tflops_whole_forward": gemm_flop / (ms / 1e3) / 1e12,
+           "images_per_s": world * B / (ms / 1e3), "n_gpus": world,
+           "dense_tflops_whole_forward_per_gpu": gemm_flop / (ms / 1e3) / 1e12,
            "launches_per_forward": rep.launches_per_forward}
     # end to end: [1,3,224,224] host requests -> gather -> task -> H2D -> codelet -> D2H -> slices
-    srv = hostapi.Server(**hostapi.VIT_L_IO, replicas=[rep], model_kind=hostapi.MODEL_VIT, max_batch_size=B,
+    srv = hostapi.Server(**hostapi.VIT_L_IO, replicas=[rep], device_ids=[local], model_kind=hostapi.MODEL_VIT, max_batch_size=B,
                          pool_size=6, nworker_per_cuda=4, cuda_pipeline=2, n_workspaces=4)
     rows = [[np.ascontiguousarray(h[r:r + 1]) for r in range(B)] for h in host]
     prepared = [srv.prepare_batch([(r, 1, [a], [None]) for r, a in enumerate(rr)]) for rr in rows]
     for t in [srv.submit_prepared(prepared[i % 2]) for i in range(4)]:
         srv.wait(t, cap=B)
+    barrier()
     t0 = time.perf_counter()
     tickets = [srv.submit_prepared(prepared[i % 2]) for i in range(steps)]
     ok = all(r.ok == 1 for t in tickets for r in srv.wait(t, cap=B))
-    dt = time.perf_counter() - t0
-    res["e2e_images_per_s"] = B * steps / dt
+    dt = slowest(time.perf_counter() - t0)
+    res["e2e_images_per_s"] = world * B * steps / dt
     res["e2e_ok"] = ok
     res["h2d_bytes_per_step"] = B * 3 * 224 * 224 * 4
     srv.close()
     rep.close()
-    print(json.dumps(res))
+    if rank == 0:
+        print(json.dumps(res))
+    if world > 1:
+        dist.destroy_process_group()
 
 
 if __name__ == "__main__":
