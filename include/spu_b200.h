@@ -165,6 +165,18 @@ spu_status spu_bert_forward_profiled(spu_replica *r, int32_t ws_idx,
  * least once before spu_bert_forward_async.  Start-up only (warm-up, warmup.cpp:225-299). */
 spu_status spu_bert_calibrate_fp8(spu_replica *r, int32_t ws_idx, const int64_t *ids,
                                   const int64_t *mask, int32_t batch, int32_t seq, void *stream);
+/* Which GEMMs of which encoder layer run on FP8 operands (the rest run in bf16): one byte per
+ * layer, OR of SPU_FP8_GEMM_*.  Replaces the mask the creation flags implied.  Start-up only:
+ * synchronises the device and drops captured graphs.  The producer of each GEMM operand
+ * (embedding, LayerNorm, attention, the FFN1 GELU epilogue) emits the format its consumer wants. */
+#define SPU_FP8_GEMM_QKV 1u
+#define SPU_FP8_GEMM_OUT 2u
+#define SPU_FP8_GEMM_FFN1 4u
+#define SPU_FP8_GEMM_FFN2 8u
+#define SPU_FP8_GEMM_ALL 15u
+spu_status spu_bert_set_fp8_mask(spu_replica *r, const uint8_t *layer_masks, int32_t n_layers);
+/* Current mask into out[0..cap); returns the layer count (0 for a bf16 replica). */
+int32_t spu_bert_get_fp8_mask(const spu_replica *r, uint8_t *out, int32_t cap);
 /* Scales of an FP8 replica, 8 per layer: activation x, ctx, x1, h then weight qkv, out,
  * ffn1, ffn2.  Returns the count (0 for a bf16 replica). */
 int32_t spu_bert_fp8_scales(const spu_replica *r, float *out, int32_t cap);

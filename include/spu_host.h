@@ -86,7 +86,10 @@ typedef struct spu_request {
   int32_t request_id;
   int64_t batch;                         /* rows this request carries (dims[0]) */
   const void *inputs[SPU_HOST_MAX_IO];   /* host, contiguous [batch, ...] per model input */
-  void *outputs[SPU_HOST_MAX_IO];        /* host destination per model output (may be NULL) */
+  void *outputs[SPU_HOST_MAX_IO];        /* host destination per model output (may be NULL); sized by THIS
+                                            request's shape: [batch, seq_len, ...] on a variable_length server
+                                            (the response is compacted to the request's own seq_len even when
+                                            it rode in a longer padded batch), [batch, dims[1..]] otherwise */
   int64_t seq_len;                       /* variable_length servers: dims[1] of this request's inputs
                                             (0 = the configured length); ignored otherwise */
 } spu_request;

@@ -136,6 +136,17 @@ class BertReplica:
         capi.check(capi.lib().spu_bert_calibrate_fp8(self._h, ws, capi.ptr(ids), capi.ptr(mask), b, s,
                                                      capi.stream_ptr(stream)))
 
+    def set_fp8_mask(self, masks):
+        """One byte per layer (OR of capi.FP8_GEMM_*): which GEMMs run on e4m3 operands.  Start-up only."""
+        m = np.ascontiguousarray(np.asarray(masks, dtype=np.uint8))
+        capi.check(capi.lib().spu_bert_set_fp8_mask(self._h, capi.ptr(m), len(m)))
+
+    def fp8_mask(self):
+        n = capi.lib().spu_bert_get_fp8_mask(self._h, None, 0)
+        m = np.zeros(max(n, 1), dtype=np.uint8)
+        capi.lib().spu_bert_get_fp8_mask(self._h, capi.ptr(m), n)
+        return m[:n]
+
     def fp8_scales(self):
         n = capi.lib().spu_bert_fp8_scales(self._h, None, 0)
         buf = (C.c_float * max(n, 1))()

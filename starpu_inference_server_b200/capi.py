@@ -19,6 +19,7 @@ SPU_PREC_BF16, SPU_PREC_FP8_E4M3 = 0, 1
 SPU_FORWARD_AUTO_GRAPH = 1 << 16  # capture a CUDA graph on the second sighting of a pointer tuple
 SPU_OUTPUT_BF16 = 1 << 18  # output0 is bf16 [B,S,H] (response path)
 SPU_REQUEST_IO = 1 << 17  # allocate the staging spu_bert_forward_requests_async needs
+FP8_GEMM_QKV, FP8_GEMM_OUT, FP8_GEMM_FFN1, FP8_GEMM_FFN2, FP8_GEMM_ALL = 1, 2, 4, 8, 15
 STAGE_NAMES = ["embed_ln", "gemm_qkv", "attention", "gemm_attn_out", "ln1", "gemm_ffn1", "gemm_ffn2", "ln2"]
 
 # every symbol include/spu_b200.h declares (checked by tests/test_capi_symbols.py)
@@ -30,7 +31,8 @@ SYMBOLS = [
     "spu_last_error", "spu_abi_version", "spu_device_count", "spu_device_is_sm100",
     "spu_bert_output_bytes", "spu_vit_replica_create", "spu_vit_forward_async", "spu_vit_input_bytes",
     "spu_vit_output_bytes", "spu_bert_stage_chain_ms", "spu_bert_calibrate_fp8", "spu_bert_fp8_scales",
-    "spu_gemm_fp8_async", "spu_quantize_e4m3_async", "spu_debug_gemm_trace",
+    "spu_gemm_fp8_async", "spu_quantize_e4m3_async", "spu_bert_set_fp8_mask", "spu_bert_get_fp8_mask",
+    "spu_debug_gemm_trace",
     "spu_debug_gemm_mode",
 ]
 
@@ -91,6 +93,8 @@ def lib():
     L.spu_bert_stage_chain_ms.argtypes = [vp, i32, vp, vp, i32, i32, vp, C.c_uint32, i32, vp, C.POINTER(f32)]
     L.spu_bert_calibrate_fp8.argtypes = [vp, i32, vp, vp, i32, i32, vp]
     L.spu_bert_fp8_scales.argtypes = [vp, C.POINTER(f32), i32]
+    L.spu_bert_set_fp8_mask.argtypes = [vp, vp, i32]
+    L.spu_bert_get_fp8_mask.argtypes = [vp, vp, i32]
     L.spu_gemm_fp8_async.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, i32, f32, f32, vp]
     L.spu_quantize_e4m3_async.argtypes = [vp, vp, u64, f32, vp]
     L.spu_debug_gemm_trace.argtypes = [vp, i32]

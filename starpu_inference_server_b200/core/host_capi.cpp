@@ -91,7 +91,11 @@ struct spu_server {
       job->inputs.push_back(std::move(t));
     }
     std::vector<void *> dsts(rq.outputs, rq.outputs + model.outputs.size());
-    job->on_complete = [this, ticket, index, dsts](const JobResult &res) {
+    // variable_length: the sequence length this request's response is laid out with
+    const int64_t own_seq = model.variable_length && !job->inputs.empty() && job->inputs[0].dims.size() >= 2
+                                ? job->inputs[0].dims[1]
+                                : 0;
+    job->on_complete = [this, ticket, index, dsts, own_seq](const JobResult &res) {
       spu_result out{};
       out.request_id = res.request_id;
       out.ok = res.ok ? 1 : 0;
@@ -115,9 +119,22 @@ struct spu_server {
       }
       if (res.ok)
         // the response copy the reference makes per request (fill_output_tensor,
-        // src/grpc/server/inference_service_io.cpp:377-419): slot view -> caller's buffer
-        for (size_t o = 0; o < res.outputs.size() && o < dsts.size(); ++o)
-          if (dsts[o] && res.outputs[o].defined()) std::memcpy(dsts[o], res.outputs[o].data, res.outputs[o].nbytes());
+        // src/grpc/server/inference_service_io.cpp:377-419): slot view -> caller's buffer.  The caller sizes
+        // its buffer by its OWN shape: on a variable_length server a multi-sample request that rode in a longer
+        // batch is compacted sample by sample to [batch, own_seq, ...], never the padded [batch, batch_seq, ...].
+        for (size_t o = 0; o < res.outputs.size() && o < dsts.size(); ++o) {
+          const HostTensor &v = res.outputs[o];
+          if (!dsts[o] || !v.defined()) continue;
+          if (own_seq > 0 && res.batch_seq > own_seq && v.dims.size() >= 2 && v.dims[1] == res.batch_seq) {
+            const size_t samples = static_cast<size_t>(v.dims[0]);
+            const size_t padded = v.nbytes() / samples;
+            const size_t live = padded / static_cast<size_t>(res.batch_seq) * static_cast<size_t>(own_seq);
+            for (size_t r = 0; r < samples; ++r)
+              std::memcpy(static_cast<std::byte *>(dsts[o]) + r * live, v.data + r * padded, live);
+          } else {
+            std::memcpy(dsts[o], v.data, v.nbytes());
+          }
+        }
       out.latency_ms = ms_between(res.timing.enqueued_time, MonotonicClock::now());
       {
         std::lock_guard<std::mutex> lk(tmu);

@@ -51,6 +51,7 @@ struct _starpu_data_state {
   int pending = 0;              // submitted, not yet completed tasks using this handle
   bool acquired = false;
   bool host_pinned_by_us = false;
+  uint32_t wt_mask = 0;         // starpu_data_set_wt_mask: nodes every write is propagated to
 };
 
 namespace {
@@ -66,16 +67,33 @@ struct Worker {
   int dev_index = 0;  // index into Runtime::gpuids (CUDA) / cpu index
   int devid = 0;      // CUDA ordinal
   cudaStream_t stream = nullptr;
-  cudaStream_t xfer = nullptr;  // D2H on acquire from this worker's completion thread
+  cudaStream_t xfer = nullptr;  // write-through D2H of STARPU_W buffers, behind the compute event
   std::thread thread, completer;
   std::mutex cmu;
   std::condition_variable ccv;
   struct InFlight {
-    starpu_task *task;
-    cudaEvent_t ev;
+    starpu_task *task = nullptr;
+    cudaEvent_t compute = nullptr;  // recorded on `stream` after the codelet returned
+    cudaEvent_t landed = nullptr;   // recorded on `xfer` after the write-through copies (null: none issued)
+    std::vector<_starpu_data_state *> written_through;
   };
   std::deque<InFlight> inflight;
+  std::vector<cudaEvent_t> free_events;  // created once, recycled (guarded by cmu)
   bool cstop = false;
+
+  cudaEvent_t take_event();
+  void give_event(cudaEvent_t e) {
+    if (e == nullptr) return;
+    std::lock_guard<std::mutex> lk(cmu);
+    free_events.push_back(e);
+  }
+};
+
+// (stream, event) pairs for transfers issued by non-worker threads (starpu_data_acquire from a
+// callback or the submitter): created on first use, recycled, one free list per device.
+struct XferSlot {
+  cudaStream_t stream = nullptr;
+  cudaEvent_t done = nullptr;
 };
 
 struct Runtime {
@@ -90,7 +108,7 @@ struct Runtime {
   std::atomic<long> codelet_failures{0};
   std::string last_failure;
   std::mutex xfer_mu;
-  std::vector<cudaStream_t> host_xfer;  // per device: transfers issued by non-worker threads
+  std::vector<std::vector<XferSlot>> host_xfer;  // per device: free transfer slots
 };
 
 unsigned node_of_dev(int dev_index) { return 1u + static_cast<unsigned>(dev_index); }
@@ -186,6 +204,23 @@ unsigned sync_event_flags() {
   return spin ? cudaEventDisableTiming : (cudaEventDisableTiming | cudaEventBlockingSync);
 }
 
+cudaEvent_t Worker::take_event() {
+  {
+    std::lock_guard<std::mutex> lk(cmu);
+    if (!free_events.empty()) {
+      cudaEvent_t e = free_events.back();
+      free_events.pop_back();
+      return e;
+    }
+  }
+  cudaEvent_t e = nullptr;  // pool exhausted (never in steady state: 2 per in-flight task are pre-created)
+  if (cudaEventCreateWithFlags(&e, sync_event_flags()) != cudaSuccess) {
+    cudaGetLastError();
+    return nullptr;
+  }
+  return e;
+}
+
 void completer_loop(Runtime *rt, Worker *w) {
   tls_worker = -1;  // callbacks do not run "on" a worker (starpu_worker_get_id() == -1)
   if (w->type == STARPU_CUDA_WORKER) cudaSetDevice(w->devid);
@@ -197,10 +232,24 @@ void completer_loop(Runtime *rt, Worker *w) {
       if (w->inflight.empty()) return;
       f = w->inflight.front();
     }
-    if (f.ev) {
-      cudaEventSynchronize(f.ev);
-      cudaEventDestroy(f.ev);
+    cudaError_t e = cudaSuccess;
+    if (f.landed) e = cudaEventSynchronize(f.landed);  // implies the compute event
+    else if (f.compute) e = cudaEventSynchronize(f.compute);
+    if (e != cudaSuccess) {
+      // an asynchronous fault of the task's kernels or copies: count it as a codelet failure and leave
+      // the host copies invalid, so the output acquire of the callback reports the task as failed
+      cudaGetLastError();
+      ++rt->codelet_failures;
+      std::lock_guard<std::mutex> lk(rt->qmu);
+      rt->last_failure = std::string("asynchronous CUDA failure after the codelet: ") + cudaGetErrorString(e);
+    } else {
+      for (_starpu_data_state *h : f.written_through) {
+        std::lock_guard<std::mutex> lk(h->mu);
+        h->nodes[0].valid = true;  // shared: the device copy stays valid too
+      }
     }
+    w->give_event(f.compute);
+    w->give_event(f.landed);
     {
       std::lock_guard<std::mutex> lk(w->cmu);
       w->inflight.pop_front();
@@ -215,6 +264,12 @@ void worker_loop(Runtime *rt, Worker *w) {
   if (w->type == STARPU_CUDA_WORKER) cudaSetDevice(w->devid);
   for (;;) {
     starpu_task *task = nullptr;
+    // pipeline back-pressure BEFORE taking a task: a task must not wait behind this worker's full
+    // pipeline while another worker is idle (only this thread adds to `inflight`, so room stays room)
+    {
+      std::unique_lock<std::mutex> lk(w->cmu);
+      w->ccv.wait(lk, [&] { return static_cast<int>(w->inflight.size()) < rt->pipeline; });
+    }
     {
       std::unique_lock<std::mutex> lk(rt->qmu);
       for (;;) {
@@ -232,11 +287,6 @@ void worker_loop(Runtime *rt, Worker *w) {
         if (task) break;
         rt->qcv.wait(lk);
       }
-    }
-    // pipeline back-pressure
-    {
-      std::unique_lock<std::mutex> lk(w->cmu);
-      w->ccv.wait(lk, [&] { return static_cast<int>(w->inflight.size()) < rt->pipeline; });
     }
     const int nb = task_nbuffers(task);
     starpu_data_handle_t *hs = task_handles(task);
@@ -271,16 +321,49 @@ void worker_loop(Runtime *rt, Worker *w) {
       std::lock_guard<std::mutex> lk(rt->qmu);
       rt->last_failure = err;
     }
-    cudaEvent_t ev = nullptr;
+    Worker::InFlight f{};
+    f.task = task;
     if (w->type == STARPU_CUDA_WORKER) {
       const bool async = task->cl->cuda_flags[0] & STARPU_CUDA_ASYNC;
       if (!async) cudaStreamSynchronize(w->stream);
-      cudaEventCreateWithFlags(&ev, sync_event_flags());
-      cudaEventRecord(ev, w->stream);
+      f.compute = w->take_event();
+      if (f.compute) cudaEventRecord(f.compute, w->stream);
+      // write-through (starpu_data_set_wt_mask with the main-RAM bit): the D2H of every STARPU_W buffer is
+      // enqueued on the worker's transfer stream behind the compute event right here, so it overlaps the
+      // next task's kernels and the callback's acquire finds the host copy valid instead of issuing it
+      if (ok && f.compute) {
+        const unsigned node = node_of_dev(w->dev_index);
+        bool waited = false;
+        for (int i = 0; i < nb; ++i) {
+          _starpu_data_state *h = hs[i];
+          if (!(task_mode(task, i) & STARPU_W)) continue;
+          std::lock_guard<std::mutex> lk(h->mu);
+          if (!(h->wt_mask & (1u << STARPU_MAIN_RAM))) continue;
+          NodeCopy &src = h->nodes[node];
+          NodeCopy &host = h->nodes[0];
+          if (!src.valid || host.iface.ptr == 0) continue;
+          if (!waited) {
+            cudaStreamWaitEvent(w->xfer, f.compute, 0);
+            waited = true;
+          }
+          if (cudaMemcpyAsync(reinterpret_cast<void *>(host.iface.ptr), reinterpret_cast<void *>(src.iface.ptr),
+                              live_bytes(src.iface), cudaMemcpyDeviceToHost, w->xfer) == cudaSuccess) {
+            host.iface.nx = src.iface.nx;
+            f.written_through.push_back(h);
+          } else {
+            cudaGetLastError();
+          }
+        }
+        if (!f.written_through.empty()) {
+          f.landed = w->take_event();
+          if (f.landed) cudaEventRecord(f.landed, w->xfer);
+          else f.written_through.clear();  // no event to wait on: fall back to fetch-on-acquire
+        }
+      }
     }
     {
       std::lock_guard<std::mutex> lk(w->cmu);
-      w->inflight.push_back({task, ev});
+      w->inflight.push_back(std::move(f));
     }
     w->ccv.notify_all();
   }
@@ -304,30 +387,35 @@ int fetch_to_host_locked(Runtime *rt, _starpu_data_state *h) {
     int prev = -1;
     cudaGetDevice(&prev);
     cudaSetDevice(static_cast<int>(rt->gpuids[dev_index]));
-    cudaStream_t s;
+    // a recycled (stream, event) pair per concurrent acquire: concurrent acquires do not serialise on one
+    // stream, and nothing is created or destroyed per call in steady state
+    XferSlot slot;
     {
       std::lock_guard<std::mutex> lk(rt->xfer_mu);
-      s = rt->host_xfer[dev_index];
-    }
-    // a private stream per call keeps concurrent acquires from serialising on one stream
-    cudaStream_t mine = nullptr;
-    if (cudaStreamCreateWithFlags(&mine, cudaStreamNonBlocking) == cudaSuccess) s = mine;
-    cudaError_t e = cudaMemcpyAsync(reinterpret_cast<void *>(host.iface.ptr),
-                                    reinterpret_cast<void *>(src.iface.ptr), live_bytes(src.iface),
-                                    cudaMemcpyDeviceToHost, s);
-    if (e == cudaSuccess) {
-      // wait on an event so the wait can block (see sync_event_flags) instead of spinning in
-      // cudaStreamSynchronize for the whole D2H
-      cudaEvent_t done = nullptr;
-      if (cudaEventCreateWithFlags(&done, sync_event_flags()) == cudaSuccess) {
-        e = cudaEventRecord(done, s);
-        if (e == cudaSuccess) e = cudaEventSynchronize(done);
-        cudaEventDestroy(done);
-      } else {
-        e = cudaStreamSynchronize(s);
+      auto &pool = rt->host_xfer[dev_index];
+      if (!pool.empty()) {
+        slot = pool.back();
+        pool.pop_back();
       }
     }
-    if (mine) cudaStreamDestroy(mine);
+    cudaError_t e = cudaSuccess;
+    if (slot.stream == nullptr) {
+      e = cudaStreamCreateWithFlags(&slot.stream, cudaStreamNonBlocking);
+      if (e == cudaSuccess) e = cudaEventCreateWithFlags(&slot.done, sync_event_flags());
+    }
+    if (e == cudaSuccess)
+      e = cudaMemcpyAsync(reinterpret_cast<void *>(host.iface.ptr), reinterpret_cast<void *>(src.iface.ptr),
+                          live_bytes(src.iface), cudaMemcpyDeviceToHost, slot.stream);
+    // wait on an event so the wait can block (see sync_event_flags) instead of spinning for the whole D2H
+    if (e == cudaSuccess) e = cudaEventRecord(slot.done, slot.stream);
+    if (e == cudaSuccess) e = cudaEventSynchronize(slot.done);
+    if (slot.stream != nullptr && slot.done != nullptr) {
+      std::lock_guard<std::mutex> lk(rt->xfer_mu);
+      rt->host_xfer[dev_index].push_back(slot);
+    } else {
+      if (slot.done) cudaEventDestroy(slot.done);
+      if (slot.stream) cudaStreamDestroy(slot.stream);
+    }
     if (prev >= 0) cudaSetDevice(prev);
     if (e != cudaSuccess) {
       cudaGetLastError();
@@ -380,9 +468,7 @@ int starpu_init(struct starpu_conf *conf) {
   int next_id = 0;
   for (size_t d = 0; d < rt->gpuids.size(); ++d) {
     cudaSetDevice(static_cast<int>(rt->gpuids[d]));
-    cudaStream_t hx = nullptr;
-    cudaStreamCreateWithFlags(&hx, cudaStreamNonBlocking);
-    rt->host_xfer.push_back(hx);
+    rt->host_xfer.emplace_back();
     for (int k = 0; k < per; ++k) {
       auto w = std::make_unique<Worker>();
       w->id = next_id++;
@@ -391,6 +477,10 @@ int starpu_init(struct starpu_conf *conf) {
       w->devid = static_cast<int>(rt->gpuids[d]);
       cudaStreamCreateWithFlags(&w->stream, cudaStreamNonBlocking);
       cudaStreamCreateWithFlags(&w->xfer, cudaStreamNonBlocking);
+      for (int e = 0; e < 2 * (rt->pipeline + 1); ++e) {
+        cudaEvent_t ev = nullptr;
+        if (cudaEventCreateWithFlags(&ev, sync_event_flags()) == cudaSuccess) w->free_events.push_back(ev);
+      }
       rt->workers.push_back(std::move(w));
     }
   }
@@ -450,13 +540,16 @@ void starpu_shutdown(void) {
       cudaSetDevice(w->devid);
       if (w->stream) cudaStreamDestroy(w->stream);
       if (w->xfer) cudaStreamDestroy(w->xfer);
+      for (cudaEvent_t e : w->free_events) cudaEventDestroy(e);
     }
   }
-  for (size_t d = 0; d < rt->host_xfer.size(); ++d)
-    if (rt->host_xfer[d]) {
-      cudaSetDevice(static_cast<int>(rt->gpuids[d]));
-      cudaStreamDestroy(rt->host_xfer[d]);
+  for (size_t d = 0; d < rt->host_xfer.size(); ++d) {
+    cudaSetDevice(static_cast<int>(rt->gpuids[d]));
+    for (XferSlot &x : rt->host_xfer[d]) {
+      cudaEventDestroy(x.done);
+      cudaStreamDestroy(x.stream);
     }
+  }
   {
     std::lock_guard<std::mutex> lk(g_rt_mu);
     g_rt = nullptr;
@@ -594,6 +687,12 @@ int starpu_data_acquire_cb(starpu_data_handle_t h, enum starpu_data_access_mode 
   if (rc != 0) return rc;
   if (callback) callback(arg);
   return 0;
+}
+
+void starpu_data_set_wt_mask(starpu_data_handle_t h, uint32_t wt_mask) {
+  if (!h) return;
+  std::lock_guard<std::mutex> lk(h->mu);
+  h->wt_mask = wt_mask;
 }
 
 void starpu_data_release(starpu_data_handle_t h) {

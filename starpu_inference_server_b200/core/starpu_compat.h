@@ -142,6 +142,8 @@ int starpu_data_acquire(starpu_data_handle_t handle, enum starpu_data_access_mod
 int starpu_data_acquire_cb(starpu_data_handle_t handle, enum starpu_data_access_mode mode,
                            void (*callback)(void *), void *arg);
 void starpu_data_release(starpu_data_handle_t handle);
+/* write-through: every write to the handle is propagated to the memory nodes whose bit is set */
+void starpu_data_set_wt_mask(starpu_data_handle_t handle, uint32_t wt_mask);
 enum starpu_data_interface_id starpu_data_get_interface_id(starpu_data_handle_t handle);
 void *starpu_data_get_interface_on_node(starpu_data_handle_t handle, unsigned node);
 unsigned starpu_memory_nodes_get_count(void);

@@ -190,6 +190,12 @@ TaskRunner::TaskRunner(ModelConfig model, std::vector<int> device_ids, std::vect
   const bool pinned = !device_ids_.empty();
   input_pool_ = std::make_unique<InputSlotPool>(model_.inputs, model_.max_batch_size, model_.pool_size, pinned);
   output_pool_ = std::make_unique<OutputSlotPool>(model_.outputs, model_.max_batch_size, model_.pool_size, pinned);
+  // Output slots are only ever consumed on the host (starpu_output_callback acquires them, inference_task.cpp:
+  // 907-935): mark them write-through to main RAM, so the runtime starts the D2H as soon as the codelet's
+  // kernels finish instead of when the callback asks for it.  SPU_NO_WRITE_THROUGH=1 restores fetch-on-acquire.
+  if (pinned && std::getenv("SPU_NO_WRITE_THROUGH") == nullptr)
+    for (int s = 0; s < output_pool_->num_slots(); ++s)
+      for (starpu_data_handle_t h : output_pool_->handles(s)) starpu_data_set_wt_mask(h, 1u << STARPU_MAIN_RAM);
 }
 
 TaskRunner::~TaskRunner() { wait_for_all(); }

@@ -337,6 +337,21 @@ __device__ __forceinline__ void mbar_arrive_cluster(uint64_t *bar, uint32_t cta)
       "r"(cta)
       : "memory");
 }
+// Address of the same shared-memory offset in CTA `cta` of this cluster.
+__device__ __forceinline__ uint32_t mapa_u32(uint32_t smem_addr, uint32_t cta) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(smem_addr), "r"(cta));
+  return r;
+}
+// Store 8 bytes into a peer CTA's shared memory and credit them to that CTA's mbarrier (both addresses
+// are shared::cluster addresses from mapa_u32).  No fence: the data is visible to whoever observes the
+// barrier's phase completion.
+__device__ __forceinline__ void st_async_f32x2(uint32_t remote_addr, float a, float b, uint32_t remote_bar) {
+  asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v2.f32 [%0], {%1, %2}, [%3];" ::"r"(
+                   remote_addr),
+               "f"(a), "f"(b), "r"(remote_bar)
+               : "memory");
+}
 // TMA load issued by either CTA of a pair; the transaction bytes are credited to the
 // barrier at the same smem offset in the pair's EVEN (leader) CTA.
 __device__ __forceinline__ void tma_load_2d_pair(void *smem_dst, const void *tmap, uint64_t *bar,
@@ -385,8 +400,8 @@ __device__ __forceinline__ void umma_f8_ss_pair(uint32_t tmem_d, uint64_t desc_a
       : "memory");
 }
 // Commit of the pair's MMAs, arriving on the barrier at this offset in BOTH CTAs.
-__device__ __forceinline__ void umma_commit_pair(uint64_t *bar) {
-  const uint16_t mask = 0x3;
+__device__ __forceinline__ void umma_commit_pair(uint64_t *bar, uint32_t pair_base = 0) {
+  const uint16_t mask = static_cast<uint16_t>(0x3u << pair_base);  // the pair's two CTAs inside the cluster
   asm volatile(
       "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 "
       "[%0], %1;" ::"r"(smem_u32(bar)),

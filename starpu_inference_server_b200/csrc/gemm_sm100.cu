@@ -42,13 +42,21 @@ constexpr int kSmemMax = 227 * 1024;
 constexpr int kBarrierBytes = 512;
 constexpr int kMaxStages = 8;
 
+constexpr int kLnMaxNBlocks = 4;  // LayerNorm-fused epilogue: column blocks (CTAs or CTA pairs) per row block
+constexpr int kLnChunk2Bytes = 32 * 32 * 2;  // second (bf16 / e4m3) output chunk of the LayerNorm epilogue
+
 template <int EPI>
 struct EpiTraits {
   // bytes of one staged 32x32 output chunk
   static constexpr int kElemBytes =
-      (EPI == kEpiBiasResid || EPI == kEpiBiasAccum) ? 4 : (EPI == kEpiBiasGeluE4m3 ? 1 : 2);
+      (EPI == kEpiBiasResid || EPI == kEpiBiasAccum || EPI == kEpiBiasResidLN) ? 4
+                                                                               : (EPI == kEpiBiasGeluE4m3 ? 1 : 2);
   static constexpr int kChunkBytes = 32 * 32 * kElemBytes;
-  static constexpr int kWarpBytes = 2 * kChunkBytes;  // double-buffered per warp
+  // double-buffered per warp; the LayerNorm epilogue adds two slots for its second (bf16 / e4m3) output
+  static constexpr int kWarpBytes = 2 * kChunkBytes + (EPI == kEpiBiasResidLN ? 2 * kLnChunk2Bytes : 0);
+  // LayerNorm epilogue: per-row (mean, M2) contributions of every column half of every column block,
+  // double-buffered across tiles: [2][2 * kLnMaxNBlocks][128 rows] float2
+  static constexpr int kStatsBytes = EPI == kEpiBiasResidLN ? 2 * 2 * kLnMaxNBlocks * kRowsPerCta * 8 : 0;
 };
 
 template <int BLOCK_N, int CG, int EPI>
@@ -57,14 +65,15 @@ struct TileCfg {
   static constexpr int kBBytes = kBRows * kTileKBytes;
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kStagingBytes = kNumEpiWarps * EpiTraits<EPI>::kWarpBytes;
-  static constexpr int kStagesRaw = (kSmemMax - 1024 - kStagingBytes - kBarrierBytes) / kStageBytes;
+  static constexpr int kStatsBytes = EpiTraits<EPI>::kStatsBytes;
+  static constexpr int kStagesRaw = (kSmemMax - 1024 - kStagingBytes - kStatsBytes - kBarrierBytes) / kStageBytes;
   static constexpr int kStages = kStagesRaw > kMaxStages ? kMaxStages : kStagesRaw;
   static constexpr int kTmemCols = (2 * BLOCK_N <= 32)    ? 32
                                    : (2 * BLOCK_N <= 64)  ? 64
                                    : (2 * BLOCK_N <= 128) ? 128
                                    : (2 * BLOCK_N <= 256) ? 256
                                                           : 512;
-  static constexpr int kSmemBytes = 1024 + kStages * kStageBytes + kStagingBytes + kBarrierBytes;
+  static constexpr int kSmemBytes = 1024 + kStages * kStageBytes + kStagingBytes + kStatsBytes + kBarrierBytes;
   static_assert(kStages >= 3, "pipeline too shallow");
   static_assert((BLOCK_N / 2) % 32 == 0, "each epilogue warp half must be whole 32-column chunks");
 };
@@ -86,6 +95,11 @@ struct KernelArgs {
   // Experiments only (spu_debug_gemm_mode): 1 = producer skips the TMA loads (pure MMA +
   // barrier rate on whatever smem holds), 2 = issuer skips the MMAs (pure operand feed rate).
   int dbg;
+  // LayerNorm-fused epilogue (kEpiBiasResidLN): y = LN(acc*s + bias + resid) * gamma + beta over the N columns
+  const float *gamma, *beta;
+  float ln_eps;
+  int ln_write_f32;  // y -> tmap_out (fp32)
+  int ln_out2;       // 0 none, 1 bf16 y -> tmap_out2, 2 e4m3 (y * out_inv_scale) -> tmap_out2
 };
 
 __device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c,
@@ -622,12 +636,14 @@ spu_status launch_epi(const GemmPlan &plan, const LaunchMaps &maps, const Kernel
         return inplace ? launch_cfg<BLOCK_N, CG, kEpiBiasAccum, 1>(plan, maps, a, stream)
                        : launch_cfg<BLOCK_N, CG, kEpiBiasResid, 1>(plan, maps, a, stream);
       case kEpiBiasGeluE4m3: return launch_cfg<BLOCK_N, CG, kEpiBiasGeluE4m3, 1>(plan, maps, a, stream);
+      case kEpiBiasGelu: return launch_cfg<BLOCK_N, CG, kEpiBiasGelu, 1>(plan, maps, a, stream);
       default: set_error("fp8 gemm: unsupported epilogue"); return SPU_ERR_INVALID;
     }
   }
   switch (plan.epilogue) {
     case kEpiBias: return launch_cfg<BLOCK_N, CG, kEpiBias, 0>(plan, maps, a, stream);
     case kEpiBiasGelu: return launch_cfg<BLOCK_N, CG, kEpiBiasGelu, 0>(plan, maps, a, stream);
+    case kEpiBiasGeluE4m3: return launch_cfg<BLOCK_N, CG, kEpiBiasGeluE4m3, 0>(plan, maps, a, stream);
     case kEpiBiasResid:
       return inplace ? launch_cfg<BLOCK_N, CG, kEpiBiasAccum, 0>(plan, maps, a, stream)
                      : launch_cfg<BLOCK_N, CG, kEpiBiasResid, 0>(plan, maps, a, stream);

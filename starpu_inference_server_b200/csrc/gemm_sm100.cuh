@@ -15,16 +15,29 @@ enum class GemmIn : int { BF16 = 0, FP8_E4M3 = 1 };
 constexpr int kEpiBias = SPU_EPI_BIAS;             // bf16 out
 constexpr int kEpiBiasGelu = SPU_EPI_BIAS_GELU;    // bf16 out
 constexpr int kEpiBiasResid = SPU_EPI_BIAS_RESID;  // fp32 out = acc + bias + fp32 residual
-constexpr int kEpiBiasGeluE4m3 = 3;
-constexpr int kEpiBiasAccum = 4;  // fp32 out += acc*s + bias by TMA reduce-add: BIAS_RESID when resid == out                // e4m3 out = gelu(acc*s + bias) * out_scale_inv
+constexpr int kEpiBiasGeluE4m3 = 3;   // e4m3 out = gelu(acc*s + bias) * out_inv_scale
+constexpr int kEpiBiasAccum = 4;  // fp32 out += acc*s + bias by TMA reduce-add: BIAS_RESID when resid == out
+// y = LayerNorm(acc*s + bias + resid) * gamma + beta over the N columns of a row, fused: the CTAs (or CTA
+// pairs) that hold the column blocks of one row block form a thread-block cluster and exchange per-row
+// (mean, M2) over distributed shared memory.  Writes y as fp32 (out) and / or bf16 / e4m3 (out2).
+constexpr int kEpiBiasResidLN = 5;
 
 struct GemmEpilogueArgs {
   const float *bias;    // [N] fp32 (may be null)
   const float *resid;   // [M,N] fp32 (kEpiBiasResid; may alias out)
   void *out;            // bf16 / fp32 / e4m3 [M,N] according to the epilogue kind
   float acc_scale;      // multiplies the accumulator (fp8: a_scale*w_scale; bf16: 1)
-  float out_inv_scale;  // kEpiBiasGeluE4m3: 1/scale of the quantised output
+  float out_inv_scale;  // kEpiBiasGeluE4m3 / LN e4m3 output: 1/scale of the quantised output
+  // kEpiBiasResidLN only
+  const float *gamma = nullptr, *beta = nullptr;  // [N] fp32
+  float ln_eps = 0.f;
+  void *out2 = nullptr;  // bf16 (out2_e4m3 == 0) or e4m3 [M,N] copy of y; null = none
+  int out2_e4m3 = 0;
+  // out may be null (no fp32 y) when out2 is given
 };
+
+// Can the LayerNorm-fused epilogue serve an output width of N columns (cluster of <= 8 CTAs spanning N)?
+bool gemm_ln_supported(int N);
 
 // Operand-B TMA boxes come in multiples of 32 rows: BLOCK_N / cta_group in {32..256}.
 constexpr int kNumBBoxes = 8;

@@ -111,6 +111,10 @@ spu_status build(spu_replica *r, const float *const *t) {
                                GemmIn::FP8_E4M3));
         SPU_TRY(gemm_make_plan(&ws.plans8[l].ffn2, ws.h_q, R, w.q_2, d.hidden, d.ffn, kEpiBiasResid,
                                GemmIn::FP8_E4M3));
+        SPU_TRY(gemm_make_plan(&ws.plans8[l].ffn1_b2q, ws.x_bf16, R, w.w_1, d.ffn, d.hidden, kEpiBiasGeluE4m3,
+                               GemmIn::BF16));
+        SPU_TRY(gemm_make_plan(&ws.plans8[l].ffn1_q2b, ws.x_q, R, w.q_1, d.ffn, d.hidden, kEpiBiasGelu,
+                               GemmIn::FP8_E4M3));
       }
     }
     ws.plans.resize(d.layers);
@@ -195,53 +199,62 @@ spu_status enqueue_forward(spu_replica *r, Workspace &ws, const int64_t *ids, co
   return SPU_OK;
 }
 
-// FP8 E4M3 variant of enqueue_forward: same kernels, e4m3 GEMM operands with per-tensor
-// scales folded into the epilogue (acc * sa * sw + bias); attention, LayerNorm statistics and
-// the residual stream stay bf16 / fp32.  Layers >= r->fp8_layers run the bf16 GEMMs (the
-// late layers' quantisation noise is the part LayerNorm never attenuates).
+// FP8 E4M3 variant of enqueue_forward: same kernels; each of a layer's four GEMMs runs either on
+// e4m3 operands with per-tensor scales folded into the epilogue (acc * sa * sw + bias) or in bf16,
+// as r->fp8_mask[l] says (SPU_FP8_GEMM_* bits).  The producer of every GEMM operand (embedding,
+// LayerNorm, attention, the FFN1 GELU epilogue) emits the format its consumer wants; attention,
+// LayerNorm statistics and the residual stream stay bf16 / fp32.
 spu_status enqueue_forward_fp8(spu_replica *r, Workspace &ws, const int64_t *ids, const int64_t *mask,
                                int batch, int seq, float *out, cudaStream_t stream, uint32_t stage_mask) {
   const spu_bert_desc &d = r->desc;
   const int M = batch * seq;
-  auto is8 = [&](int l) { return l < r->fp8_layers; };
-  if (SPU_ON(SPU_STAGE_EMBED))
-    SPU_TRY(bert_embed_launch(ids, mask, r->word, r->pos, r->type0, r->emb_g, r->emb_b, d.ln_eps, d.vocab,
-                              ws.x_f32, is8(0) ? nullptr : ws.x_bf16, ws.mask_bias, batch, seq, d.hidden, stream,
-                              is8(0) ? ws.x_q : nullptr, 1.f / r->layers[0].sa_x));
+  auto on = [&](int l, int bit) { return l < d.layers && (r->fp8_mask[l] & bit) != 0; };
+  {
+    const bool q = on(0, SPU_FP8_GEMM_QKV);
+    if (SPU_ON(SPU_STAGE_EMBED))
+      SPU_TRY(bert_embed_launch(ids, mask, r->word, r->pos, r->type0, r->emb_g, r->emb_b, d.ln_eps, d.vocab,
+                                ws.x_f32, q ? nullptr : ws.x_bf16, ws.mask_bias, batch, seq, d.hidden, stream,
+                                q ? ws.x_q : nullptr, 1.f / r->layers[0].sa_x));
+  }
   for (int l = 0; l < d.layers; ++l) {
     const LayerWeights &w = r->layers[l];
-    const bool f8 = is8(l);
-    const LayerPlans &p = f8 ? ws.plans8[l] : ws.plans[l];
+    const LayerPlans &p8 = ws.plans8[l];
+    const LayerPlans &p16 = ws.plans[l];
+    const bool q_qkv = on(l, SPU_FP8_GEMM_QKV), q_out = on(l, SPU_FP8_GEMM_OUT);
+    const bool q_f1 = on(l, SPU_FP8_GEMM_FFN1), q_f2 = on(l, SPU_FP8_GEMM_FFN2);
     const bool last = l == d.layers - 1;
     GemmEpilogueArgs e{};
     e.bias = w.b_qkv;
     e.out = ws.qkv;
-    e.acc_scale = f8 ? w.sa_x * w.sw_qkv : 1.f;
-    if (SPU_ON(SPU_STAGE_GEMM_QKV)) SPU_TRY(gemm_launch(p.qkv, M, e, stream));
+    e.acc_scale = q_qkv ? w.sa_x * w.sw_qkv : 1.f;
+    if (SPU_ON(SPU_STAGE_GEMM_QKV)) SPU_TRY(gemm_launch(q_qkv ? p8.qkv : p16.qkv, M, e, stream));
     if (SPU_ON(SPU_STAGE_ATTENTION))
-      SPU_TRY(attention_launch(ws.qkv, ws.mask_bias, f8 ? static_cast<void *>(ws.ctx_q) : ws.ctx, batch, seq,
-                               d.heads, stream, f8, 1.f / w.sa_ctx));
+      SPU_TRY(attention_launch(ws.qkv, ws.mask_bias, q_out ? static_cast<void *>(ws.ctx_q) : ws.ctx, batch, seq,
+                               d.heads, stream, q_out, 1.f / w.sa_ctx));
     e.bias = w.b_o;
     e.resid = ws.x_f32;
     e.out = ws.x_f32;
-    e.acc_scale = f8 ? w.sa_ctx * w.sw_o : 1.f;
-    if (SPU_ON(SPU_STAGE_GEMM_OUT)) SPU_TRY(gemm_launch(p.attn_out, M, e, stream));
+    e.acc_scale = q_out ? w.sa_ctx * w.sw_o : 1.f;
+    if (SPU_ON(SPU_STAGE_GEMM_OUT)) SPU_TRY(gemm_launch(q_out ? p8.attn_out : p16.attn_out, M, e, stream));
     if (SPU_ON(SPU_STAGE_LN1))
-      SPU_TRY(layernorm_launch(ws.x_f32, w.ln1_g, w.ln1_b, d.ln_eps, ws.x_f32, f8 ? nullptr : ws.x_bf16, M,
-                               d.hidden, stream, 0, f8 ? ws.x_q : nullptr, 1.f / w.sa_x1));
+      SPU_TRY(layernorm_launch(ws.x_f32, w.ln1_g, w.ln1_b, d.ln_eps, ws.x_f32, q_f1 ? nullptr : ws.x_bf16, M,
+                               d.hidden, stream, 0, q_f1 ? ws.x_q : nullptr, 1.f / w.sa_x1));
     e.bias = w.b_1;
     e.resid = nullptr;
-    e.out = f8 ? static_cast<void *>(ws.h_q) : ws.h;
-    e.acc_scale = f8 ? w.sa_x1 * w.sw_1 : 1.f;
+    e.out = q_f2 ? static_cast<void *>(ws.h_q) : ws.h;
+    e.acc_scale = q_f1 ? w.sa_x1 * w.sw_1 : 1.f;
     e.out_inv_scale = 1.f / w.sa_h;
-    if (SPU_ON(SPU_STAGE_GEMM_FFN1)) SPU_TRY(gemm_launch(p.ffn1, M, e, stream));
+    if (SPU_ON(SPU_STAGE_GEMM_FFN1)) {
+      const GemmPlan &pf1 = q_f1 ? (q_f2 ? p8.ffn1 : p8.ffn1_q2b) : (q_f2 ? p8.ffn1_b2q : p16.ffn1);
+      SPU_TRY(gemm_launch(pf1, M, e, stream));
+    }
     e.bias = w.b_2;
     e.resid = ws.x_f32;
     e.out = ws.x_f32;
-    e.acc_scale = f8 ? w.sa_h * w.sw_2 : 1.f;
-    if (SPU_ON(SPU_STAGE_GEMM_FFN2)) SPU_TRY(gemm_launch(p.ffn2, M, e, stream));
+    e.acc_scale = q_f2 ? w.sa_h * w.sw_2 : 1.f;
+    if (SPU_ON(SPU_STAGE_GEMM_FFN2)) SPU_TRY(gemm_launch(q_f2 ? p8.ffn2 : p16.ffn2, M, e, stream));
     if (SPU_ON(SPU_STAGE_LN2)) {
-      const bool n8 = !last && is8(l + 1);
+      const bool n8 = !last && on(l + 1, SPU_FP8_GEMM_QKV);
       const bool out16 = last && (r->flags & SPU_OUTPUT_BF16) != 0;
       SPU_TRY(layernorm_launch(ws.x_f32, w.ln2_g, w.ln2_b, d.ln_eps, out16 ? nullptr : (last ? out : ws.x_f32),
                                out16 ? static_cast<void *>(out) : ((last || n8) ? nullptr : ws.x_bf16), M, d.hidden,
@@ -347,6 +360,8 @@ extern "C" spu_status spu_bert_replica_create(const spu_bert_desc *desc, const f
   {
     const int n8 = static_cast<int>((flags >> 8) & 0xffu);
     r->fp8_layers = (flags & SPU_PREC_FP8_E4M3) ? ((n8 == 0 || n8 > desc->layers) ? desc->layers : n8) : 0;
+    r->fp8_mask.assign(desc->layers, 0);
+    for (int l = 0; l < r->fp8_layers; ++l) r->fp8_mask[l] = SPU_FP8_GEMM_ALL;
   }
   r->cap_rows = ((max_batch * max_seq + 127) / 128) * 128;
   r->ws.resize(n_workspaces);
@@ -523,6 +538,31 @@ extern "C" spu_status spu_bert_calibrate_fp8(spu_replica *r, int32_t ws_idx, con
     ws.graphs.clear();
   }
   return SPU_OK;
+}
+
+extern "C" spu_status spu_bert_set_fp8_mask(spu_replica *r, const uint8_t *layer_masks, int32_t n_layers) {
+  SPU_REQUIRE(r != nullptr && r->kind == 0 && (r->flags & SPU_PREC_FP8_E4M3), SPU_ERR_INVALID,
+              "set_fp8_mask: not an FP8 BERT replica");
+  SPU_REQUIRE(layer_masks != nullptr && n_layers == r->desc.layers, SPU_ERR_INVALID,
+              "set_fp8_mask: one mask byte per encoder layer is required");
+  for (int l = 0; l < n_layers; ++l)
+    SPU_REQUIRE((layer_masks[l] & ~SPU_FP8_GEMM_ALL) == 0, SPU_ERR_INVALID, "set_fp8_mask: unknown GEMM bit");
+  DeviceGuard guard(r->device);
+  SPU_CUDA_TRY(cudaDeviceSynchronize());  // start-up only: no forward of the old plan may be in flight
+  r->fp8_mask.assign(layer_masks, layer_masks + n_layers);
+  for (Workspace &ws : r->ws) {  // captured graphs bake the plan in: drop them
+    for (CapturedGraph &g : ws.graphs)
+      if (g.exec) cudaGraphExecDestroy(g.exec);
+    ws.graphs.clear();
+    ws.seen.clear();
+  }
+  return SPU_OK;
+}
+
+extern "C" int32_t spu_bert_get_fp8_mask(const spu_replica *r, uint8_t *out, int32_t cap) {
+  if (r == nullptr || r->kind != 0 || !(r->flags & SPU_PREC_FP8_E4M3)) return 0;
+  for (int l = 0; l < r->desc.layers && out != nullptr && l < cap; ++l) out[l] = r->fp8_mask[l];
+  return r->desc.layers;
 }
 
 extern "C" int32_t spu_bert_fp8_scales(const spu_replica *r, float *out, int32_t cap) {

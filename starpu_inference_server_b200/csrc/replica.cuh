@@ -73,6 +73,9 @@ struct LayerWeights {
 
 struct LayerPlans {
   GemmPlan qkv, attn_out, ffn1, ffn2;
+  // FP8 plan set only: FFN1 with mixed operand / output formats (per-GEMM FP8 mask)
+  GemmPlan ffn1_b2q;  // bf16 operands -> e4m3 GELU output (FFN2 runs in FP8, FFN1 does not)
+  GemmPlan ffn1_q2b;  // e4m3 operands -> bf16 GELU output (FFN1 runs in FP8, FFN2 does not)
 };
 
 struct GraphKey {
@@ -120,6 +123,8 @@ struct spu_replica {
   float *amax = nullptr;      // [layers * 4] running calibration maxima (FP8 variant)
   bool fp8_calibrated = false;
   int fp8_layers = 0;         // leading layers whose GEMMs run in FP8 (rest bf16)
+  // per layer: which of its four GEMMs run in FP8 (SPU_FP8_GEMM_* bits); others run in bf16
+  std::vector<uint8_t> fp8_mask;
   spu::VitState *vit = nullptr;
   void (*vit_destroy)(spu::VitState *) = nullptr;
 };

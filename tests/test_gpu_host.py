@@ -206,6 +206,32 @@ def test_variable_length_requests_through_the_task_path(host, bert_tiny):
             srv.wait(srv.submit_batch([(0, 1, [too_long, too_long], [None])]))
 
 
+def test_variable_length_multi_sample_request_is_compacted_to_its_own_shape(host, bert_tiny):
+    """A request carrying 2 samples of length 9 merged with a length-30 request: its response buffer is sized by ITS
+    shape [2, 9, H]; the copy must be compact (sample by sample), never the padded [2, 30, H] -- a sentinel right
+    behind the buffer stays untouched (heap overflow in the response memcpy)."""
+    bo, spec, w, rep = bert_tiny
+    S_max, H = 32, spec.hidden
+    rng = np.random.default_rng(8)
+    ids2 = rng.integers(1, spec.vocab, size=(2, 9), dtype=np.int64)
+    ids1 = rng.integers(1, spec.vocab, size=(1, 30), dtype=np.int64)
+    with host.Server(inputs=[("input_ids", "i64", [1, S_max]), ("attention_mask", "i64", [1, S_max])],
+                     outputs=[("output0", "f32", [1, S_max, H])], replicas=[rep], model_kind=host.MODEL_BERT,
+                     max_batch_size=8, pool_size=2, n_workspaces=2, variable_length=True) as srv:
+        backing = np.full(2 * 9 * H + 4096, -7.0, np.float32)
+        out2 = backing[: 2 * 9 * H].reshape(2, 9, H)
+        out1 = np.full((1, 30, H), np.nan, np.float32)
+        res = srv.wait(srv.submit_batch([(0, 2, [ids2, np.ones_like(ids2)], [out2]),
+                                         (1, 1, [ids1, np.ones_like(ids1)], [out1])]))
+        assert all(r.ok == 1 for r in res) and res[0].batch_seq == 30 and res[0].rows == 2
+        assert (backing[2 * 9 * H:] == -7.0).all(), "response copy ran past the request's own [2, 9, H] buffer"
+        for k in range(2):
+            alone = bo.bert_forward(w, spec, ids2[k:k + 1], np.ones((1, 9), np.int64))
+            assert np.abs(out2[k:k + 1] - alone).max() / np.abs(alone).max() < 2e-2, k
+        alone = bo.bert_forward(w, spec, ids1, np.ones_like(ids1))
+        assert np.abs(out1 - alone).max() / np.abs(alone).max() < 2e-2
+
+
 def test_bf16_response_through_the_task_path(host, bert_tiny):
     """models/<name>.yml output declared TYPE_BF16 + a replica created with SPU_OUTPUT_BF16: the slot, the D2H and
     the per-request slices carry 2 bytes per element; values = the fp32 path's rounded to bf16."""
