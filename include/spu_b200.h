@@ -56,8 +56,12 @@ typedef struct spu_bert_desc {
 
 /* precision flags for spu_*_replica_create */
 #define SPU_PREC_BF16 0u
-#define SPU_PREC_FP8_E4M3 1u /* per-tensor scaled FP8 GEMM inputs (QKV/out/FFN) */
-/* FP8 in the first n encoder layers only, bf16 GEMMs in the rest (n = 0 or >= layers: all) */
+/* Per-tensor scaled FP8 E4M3 GEMM operands.  Alone, this selects the default FP8 plan: the QKV projection of
+ * every layer and both FFN GEMMs of the first half of the encoder run in FP8, the rest in bf16 -- the largest
+ * measured plan inside the 6e-2 gate on BERT-base (58 % of the GEMM FLOPs; profiles/r2_fp8_plan.md). */
+#define SPU_PREC_FP8_E4M3 1u
+/* All four GEMMs of the first n encoder layers in FP8, bf16 GEMMs in the rest (n >= layers: every GEMM,
+ * which sits at the E4M3 floor of 7.6e-2 on BERT-base, outside the gate).  spu_bert_set_fp8_mask sets any plan. */
 #define SPU_PREC_FP8_LAYERS(n) (SPU_PREC_FP8_E4M3 | ((uint32_t)(n) << 8))
 /* Warm-up capture in place (src/core/warmup.cpp:225-299 runs fixed-worker jobs so that every
  * worker has executed once before traffic arrives): with this flag spu_bert_forward_async
@@ -74,6 +78,11 @@ typedef struct spu_bert_desc {
  * instead of fp32: half the D2H and response bytes.  spu_bert_output_bytes follows.  Declare the
  * model's output as TYPE_BF16 in models/<name>.yml.  Not combinable with SPU_REQUEST_IO. */
 #define SPU_OUTPUT_BF16 (1u << 18)
+
+/* BERT replicas: fuse the residual add + LayerNorm that follow the attention-output and FFN2 projections into
+ * those GEMMs' epilogues (see spu_gemm_ln_bf16_async): 5 launches per layer instead of 7.  Ignored when no
+ * cluster tiling spans the hidden size.  Results differ from the unfused path only by fp32 summation order. */
+#define SPU_LN_FUSED (1u << 19)
 
 /* Number of weight tensors spu_bert_replica_create expects: 5 + 16*layers, in the
  * order of the HF state dict restated in oracle/bert_oracle.py:weight_names()
@@ -289,6 +298,18 @@ spu_status spu_gemm_bf16_cfg_async(const void *A, const void *W, const float *bi
                                    const float *resid, void *out, int32_t M,
                                    int32_t N, int32_t K, int32_t epilogue,
                                    int32_t cta_group, int32_t block_n, void *stream);
+
+/* GEMM with the residual add AND the row LayerNorm fused into its epilogue (BERT's attention-output and FFN2
+ * projections): y = LayerNorm(A W^T + bias + resid) * gamma + beta over the N columns of every row.  The CTAs
+ * (cta_group 1) or CTA pairs (cta_group 2) that hold the N / block_n column blocks of one row block form ONE
+ * thread-block cluster and exchange per-row (mean, M2) over distributed shared memory, so the pre-LayerNorm sum
+ * never reaches HBM.  Writes y as fp32 (out_f32, may alias resid, may be NULL) and as bf16 (out_bf16, may be
+ * NULL).  N / block_n <= 4 and block_n in {64,128,192} (cta_group 0 / block_n 0: the library chooses);
+ * SPU_ERR_UNSUPPORTED when no such tiling spans N. */
+spu_status spu_gemm_ln_bf16_async(const void *A, const void *W, const float *bias, const float *resid,
+                                  const float *gamma, const float *beta, float eps, float *out_f32,
+                                  void *out_bf16, int32_t M, int32_t N, int32_t K, int32_t cta_group,
+                                  int32_t block_n, void *stream);
 
 /* Fused masked-softmax attention.  qkv: bf16 [batch*seq, 3*heads*64] (q|k|v);
  * mask_bias: fp32 [batch, seq] additive (0 keep, large negative drop);

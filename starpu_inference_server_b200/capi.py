@@ -18,6 +18,7 @@ SPU_EPI_BIAS, SPU_EPI_BIAS_GELU, SPU_EPI_BIAS_RESID = 0, 1, 2
 SPU_PREC_BF16, SPU_PREC_FP8_E4M3 = 0, 1
 SPU_FORWARD_AUTO_GRAPH = 1 << 16  # capture a CUDA graph on the second sighting of a pointer tuple
 SPU_OUTPUT_BF16 = 1 << 18  # output0 is bf16 [B,S,H] (response path)
+SPU_LN_FUSED = 1 << 19  # residual + LayerNorm in the N = hidden GEMM epilogues
 SPU_REQUEST_IO = 1 << 17  # allocate the staging spu_bert_forward_requests_async needs
 FP8_GEMM_QKV, FP8_GEMM_OUT, FP8_GEMM_FFN1, FP8_GEMM_FFN2, FP8_GEMM_ALL = 1, 2, 4, 8, 15
 STAGE_NAMES = ["embed_ln", "gemm_qkv", "attention", "gemm_attn_out", "ln1", "gemm_ffn1", "gemm_ffn2", "ln2"]
@@ -32,6 +33,7 @@ SYMBOLS = [
     "spu_bert_output_bytes", "spu_vit_replica_create", "spu_vit_forward_async", "spu_vit_input_bytes",
     "spu_vit_output_bytes", "spu_bert_stage_chain_ms", "spu_bert_calibrate_fp8", "spu_bert_fp8_scales",
     "spu_gemm_fp8_async", "spu_quantize_e4m3_async", "spu_bert_set_fp8_mask", "spu_bert_get_fp8_mask",
+    "spu_gemm_ln_bf16_async",
     "spu_debug_gemm_trace",
     "spu_debug_gemm_mode",
 ]
@@ -80,6 +82,7 @@ def lib():
     L.spu_gather_segments_async.argtypes = [vp, vp, vp, i32, vp, vp]
     L.spu_scatter_segments_async.argtypes = [vp, vp, vp, vp, i32, vp]
     L.spu_gemm_bf16_async.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, i32, vp]
+    L.spu_gemm_ln_bf16_async.argtypes = [vp, vp, vp, vp, vp, vp, f32, vp, vp, i32, i32, i32, i32, i32, vp]
     L.spu_gemm_bf16_cfg_async.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp]
     L.spu_attention_async.argtypes = [vp, vp, vp, i32, i32, i32, vp]
     L.spu_bert_forward_requests_async.argtypes = [vp, i32, vp, vp, vp, i32, i32, vp, i32, vp]

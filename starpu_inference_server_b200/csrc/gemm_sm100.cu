@@ -56,7 +56,10 @@ struct EpiTraits {
   static constexpr int kWarpBytes = 2 * kChunkBytes + (EPI == kEpiBiasResidLN ? 2 * kLnChunk2Bytes : 0);
   // LayerNorm epilogue: per-row (mean, M2) contributions of every column half of every column block,
   // double-buffered across tiles: [2][2 * kLnMaxNBlocks][128 rows] float2
-  static constexpr int kStatsBytes = EPI == kEpiBiasResidLN ? 2 * 2 * kLnMaxNBlocks * kRowsPerCta * 8 : 0;
+  static constexpr int kLnStatsOnly = 2 * 2 * kLnMaxNBlocks * kRowsPerCta * 8;
+  // this CTA's column slices of gamma | beta (with the bias too, <192, 2> would drop from 4 to 3 ring stages)
+  static constexpr int kLnVecBytes = 2 * 192 * 4;
+  static constexpr int kStatsBytes = EPI == kEpiBiasResidLN ? kLnStatsOnly + kLnVecBytes : 0;
 };
 
 template <int BLOCK_N, int CG, int EPI>
@@ -126,7 +129,8 @@ __global__ void __launch_bounds__(kThreads, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
                     const __grid_constant__ CUtensorMap tmap_b,
                     const __grid_constant__ CUtensorMap tmap_out,
-                    const __grid_constant__ CUtensorMap tmap_resid, const KernelArgs args) {
+                    const __grid_constant__ CUtensorMap tmap_resid,
+                    const __grid_constant__ CUtensorMap tmap_out2, const KernelArgs args) {
   using Cfg = TileCfg<BLOCK_N, CG, EPI>;
   using Epi = EpiTraits<EPI>;
   constexpr int kStages = Cfg::kStages;
@@ -135,30 +139,42 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
   constexpr int kElemsPerKBlock = IN_FP8 ? 128 : 64;
   constexpr int kTileM = kRowsPerCta * CG;
   constexpr int kChunksPerWarp = BLOCK_N / 2 / 32;
+  // LayerNorm-fused epilogue: the CG * (N / BLOCK_N) CTAs holding one row block's columns form a cluster
+  constexpr bool kLN = EPI == kEpiBiasResidLN;
+  constexpr bool kClustered = CG == 2 || kLN;
 
   extern __shared__ uint8_t smem_raw[];
   // SWIZZLE_128B tiles need 1024-byte aligned bases.
   const uint32_t raw_addr = smem_u32(smem_raw);
   uint8_t *smem = smem_raw + ((1024u - (raw_addr & 1023u)) & 1023u);
   uint8_t *staging = smem + kStages * kStageBytes;
-  uint64_t *full_bar = reinterpret_cast<uint64_t *>(staging + Cfg::kStagingBytes);
+  uint8_t *stats_base = staging + Cfg::kStagingBytes;
+  uint64_t *full_bar = reinterpret_cast<uint64_t *>(stats_base + Cfg::kStatsBytes);
   uint64_t *empty_bar = full_bar + kMaxStages;
   uint64_t *tmem_full_bar = empty_bar + kMaxStages;
   uint64_t *tmem_empty_bar = tmem_full_bar + 2;
   uint64_t *resid_bar = tmem_empty_bar + 2;  // [kNumEpiWarps][2]
-  uint32_t *tmem_ptr_smem = reinterpret_cast<uint32_t *>(resid_bar + 2 * kNumEpiWarps);
+  uint64_t *stats_bar = resid_bar + 2 * kNumEpiWarps;  // [2], LayerNorm epilogue only
+  uint32_t *tmem_ptr_smem = reinterpret_cast<uint32_t *>(stats_bar + 2);
 
   // warp-uniform by construction AND provably so for the compiler (shuffle from lane 0)
   const int warp_idx = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
   const int lane = threadIdx.x & 31;
-  const uint32_t cta_rank = CG == 2 ? cluster_ctarank() : 0u;
-  const int unit = static_cast<int>(blockIdx.x) / CG;       // tile-owning CTA (pair) index
-  const int num_units = static_cast<int>(gridDim.x) / CG;
-
   const int n_blocks = args.N / BLOCK_N;
   const int m_blocks = (args.M + kTileM - 1) / kTileM;
-  const int num_tiles = n_blocks * m_blocks;
+  const uint32_t crank = kClustered ? cluster_ctarank() : 0u;
+  const uint32_t cta_rank = crank & static_cast<uint32_t>(CG - 1);      // rank inside the CTA pair
+  const uint32_t pair_base = crank & ~static_cast<uint32_t>(CG - 1);    // cluster rank of the pair's leader
+  // A "unit" owns tiles: a CTA (pair) striding over all (m, n) tiles, or -- LayerNorm epilogue -- a whole
+  // cluster striding over row blocks while each of its CTAs (pairs) keeps ONE column block.
+  const int unit_ctas = kLN ? CG * n_blocks : CG;
+  const int unit = static_cast<int>(blockIdx.x) / unit_ctas;
+  const int num_units = static_cast<int>(gridDim.x) / unit_ctas;
+  const int ln_n_blk = static_cast<int>(crank) / CG;
+  const int num_tiles = kLN ? m_blocks : n_blocks * m_blocks;
   const int num_k_blocks = args.K / kElemsPerKBlock;
+  auto tile_m = [&](int tile) { return kLN ? tile : tile / n_blocks; };
+  auto tile_n = [&](int tile) { return kLN ? ln_n_blk : tile % n_blocks; };
 
   // experiments (spu_debug_gemm_mode bits 8..11): use fewer ring stages than fit
   const int n_stages = (args.dbg >> 8) > 0 && (args.dbg >> 8) < kStages ? (args.dbg >> 8) : kStages;
@@ -171,7 +187,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
     tma_prefetch_desc(&tmap_a);
     tma_prefetch_desc(&tmap_b);
     tma_prefetch_desc(&tmap_out);
-    if constexpr (EPI == kEpiBiasResid) tma_prefetch_desc(&tmap_resid);
+    if constexpr (EPI == kEpiBiasResid || kLN) tma_prefetch_desc(&tmap_resid);
+    if constexpr (kLN) tma_prefetch_desc(&tmap_out2);
   }
   if (warp_idx == 1 && lane == 0) {
     for (int s = 0; s < kStages; ++s) {
@@ -183,6 +200,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
       mbar_init(&tmem_empty_bar[s], CG * kNumEpiWarps);  // one arrive per epilogue warp of the pair
     }
     for (int s = 0; s < 2 * kNumEpiWarps; ++s) mbar_init(&resid_bar[s], 1);
+    for (int s = 0; s < 2; ++s) mbar_init(&stats_bar[s], 1);
     fence_barrier_init();
   }
   if (warp_idx == 2) {
@@ -195,7 +213,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
     }
   }
   tcgen05_fence_before();
-  if constexpr (CG == 2) cluster_sync_all(); else __syncthreads();
+  if constexpr (kClustered) cluster_sync_all(); else __syncthreads();
   tcgen05_fence_after();
   const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_ptr_smem, 0);
   const uint32_t smem_base_u32 = smem_u32(smem);
@@ -237,7 +255,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
     // weights of the first tile's first stages: independent of the previous kernel
     const int n_pre = unit < num_tiles ? (num_k_blocks < n_stages ? num_k_blocks : n_stages) : 0;
     {
-      const int n_blk = unit % n_blocks;
+      const int n_blk = tile_n(unit);
       const int b_row = n_blk * BLOCK_N + static_cast<int>(cta_rank) * Cfg::kBRows;
       if (elect_one()) {
         for (int kb = 0; kb < n_pre; ++kb) {
@@ -252,8 +270,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
     uint32_t phase = 0;
     bool first = true;
     for (int tile = unit; tile < num_tiles; tile += num_units) {
-      const int m_blk = tile / n_blocks;
-      const int n_blk = tile % n_blocks;
+      const int m_blk = tile_m(tile);
+      const int n_blk = tile_n(tile);
       const int a_row = m_blk * kTileM + static_cast<int>(cta_rank) * kRowsPerCta;
       const int b_row = n_blk * BLOCK_N + static_cast<int>(cta_rank) * Cfg::kBRows;
       for (int kb = 0; kb < num_k_blocks; ++kb) {
@@ -319,9 +337,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
             if (dbg != 2) issue_kblock(kb != 0);
             if (dbg == 3) issue_kblock(1u);  // experiments: twice the MMAs per barrier round
             // smem stage reusable (in both CTAs) once these MMAs retire
-            if constexpr (CG == 2) umma_commit_pair(&empty_bar[stage]); else umma_commit(&empty_bar[stage]);
+            if constexpr (CG == 2) umma_commit_pair(&empty_bar[stage], pair_base); else umma_commit(&empty_bar[stage]);
             if (kb == num_k_blocks - 1) {
-              if constexpr (CG == 2) umma_commit_pair(&tmem_full_bar[acc]); else umma_commit(&tmem_full_bar[acc]);
+              if constexpr (CG == 2) umma_commit_pair(&tmem_full_bar[acc], pair_base);
+              else umma_commit(&tmem_full_bar[acc]);
             }
           }
           __syncwarp();
@@ -333,6 +352,212 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
       }
     }
   } else if (warp_idx >= kEpiWarp0) {
+    // ============ epilogue with fused residual + LayerNorm (all CTAs of the cluster) ============
+    // Thread (warp w, lane l) owns row q*32+l of this CTA's 128-row slab and kVals = BLOCK_N/2 consecutive
+    // columns of it.  Pass 1: x = acc*s + bias + resid for those columns, kept in registers (the TMEM buffer is
+    // handed back at once); local (mean, M2) of the kVals values.  Exchange: the pair is sent with st.async to
+    // every CTA of the cluster that holds the same rows (one per column block), which credits that CTA's
+    // statistics mbarrier; Chan's formula merges the 2 * n_blocks contributions.  Pass 2: normalise from
+    // registers, stage and TMA-store y as fp32 (next residual) and / or bf16 / e4m3 (next GEMM operand).
+    if constexpr (kLN) {
+      constexpr int kVals = BLOCK_N / 2;
+      constexpr int kChunks = kVals / 32;
+      const int e = warp_idx - kEpiWarp0;
+      const int q = warp_idx & 3;
+      const int half = e >> 2;
+      uint8_t *wstage = staging + e * Epi::kWarpBytes;  // [2][4096] fp32 slots, then [2][2048] second-output slots
+      const uint32_t stg = smem_u32(wstage);
+      const uint32_t stg2 = stg + 2 * Epi::kChunkBytes;
+      uint64_t *my_resid_bar = resid_bar + 2 * e;
+      const int n_contrib = 2 * n_blocks;
+      const int my_contrib = 2 * ln_n_blk + half;
+      const int row_in_cta = q * 32 + lane;
+      const uint32_t stats_u32 = smem_u32(stats_base);
+      // gamma | beta of this CTA's BLOCK_N columns -> shared memory once (weights: independent of the previous
+      // kernel, so this runs under its tail), read back as warp-wide broadcasts in pass 2; the bias slice of this
+      // warp is pulled into L1 now and read with broadcast loads in pass 1
+      float *vecs = reinterpret_cast<float *>(stats_base + Epi::kLnStatsOnly);
+      {
+        const int t = static_cast<int>(threadIdx.x) - kEpiWarp0 * 32;
+        const int c0 = ln_n_blk * BLOCK_N;
+        if (t < BLOCK_N) {
+          vecs[t] = __ldg(args.gamma + c0 + t);
+          vecs[BLOCK_N + t] = __ldg(args.beta + c0 + t);
+        }
+        if (lane < kVals / 32)
+          asm volatile("prefetch.global.L1 [%0];" ::"l"(args.bias + c0 + half * kVals + lane * 32));
+        asm volatile("bar.sync 1, %0;" ::"n"(kNumEpiWarps * 32) : "memory");
+      }
+      const uint32_t vec_u32 = smem_u32(vecs) + static_cast<uint32_t>(half * kVals * 4);
+      pdl_wait_prior_grid();
+      // residual slot of chunk c: the two fp32 slots, then (third chunk) the 4 KiB of the second-output slots,
+      // which pass 1 does not use -- every residual chunk of the tile is in flight before the main loop ends
+      auto resid_slot = [&](int c) { return c < 2 ? c * Epi::kChunkBytes : 2 * Epi::kChunkBytes; };
+      static_assert(kChunks <= 3, "three residual slots");
+      uint32_t resid_par = 0u;
+      int local_tile = 0;
+      for (int tile = unit; tile < num_tiles; tile += num_units, ++local_tile) {
+        const int acc = local_tile & 1;
+        const uint32_t acc_phase = (local_tile >> 1) & 1u;
+        const int buf = local_tile & 1;
+        const int row0 = tile * kTileM + static_cast<int>(cta_rank) * kRowsPerCta + q * 32;
+        const int colw = ln_n_blk * BLOCK_N + half * kVals;
+        if (e == 0 && lane == 0)  // this tile's statistics: 8 bytes per row from every contribution
+          mbar_arrive_expect_tx(&stats_bar[buf], static_cast<uint32_t>(n_contrib * kRowsPerCta * 8));
+        if (lane == 0) {
+          tma_store_wait_read<0>();  // the previous tile's stores have read the staging slots
+#pragma unroll
+          mbar_arrive_expect_tx(&my_resid_bar[0], kChunks * Epi::kChunkBytes);
+#pragma unroll
+          for (int c = 0; c < kChunks; ++c)
+            tma_load_2d(wstage + resid_slot(c), &tmap_resid, &my_resid_bar[0], colw + c * 32, row0);
+        }
+        __syncwarp();
+        mbar_wait(&tmem_full_bar[acc], acc_phase);
+        tcgen05_fence_after();
+        const bool tr = tracing && local_tile == kTraceTile && e == 0 && lane == 0;
+        if (tr) args.trace[62] = global_timer_ns();
+        const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) +
+                               static_cast<uint32_t>(acc * BLOCK_N + half * kVals);
+        uint32_t v[kChunks][32];
+#pragma unroll
+        for (int c = 0; c < kChunks; ++c) tmem_ld_32x32b_x32(taddr + static_cast<uint32_t>(c * 32), v[c]);
+        tmem_ld_wait();
+        tcgen05_fence_before();
+        __syncwarp();
+        if (lane == 0) {  // accumulator is in registers: the MMA issuer may start the next tile into it
+          if constexpr (CG == 2) mbar_arrive_cluster(&tmem_empty_bar[acc], pair_base);
+          else mbar_arrive(&tmem_empty_bar[acc]);
+        }
+        if (tr) args.trace[70] = global_timer_ns();
+        // ---- pass 1 ----
+        float sum = 0.f;
+#pragma unroll
+        for (int c = 0; c < kChunks; ++c) {
+          if (c == 0) {
+            mbar_wait(&my_resid_bar[0], resid_par);
+            resid_par ^= 1u;
+          }
+          const uint32_t rowa = stg + static_cast<uint32_t>(resid_slot(c)) + static_cast<uint32_t>(lane) * 128u;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float4 bj = __ldg(reinterpret_cast<const float4 *>(args.bias + colw + c * 32) + j);
+            const float4 r = ld_shared_f4(rowa + (static_cast<uint32_t>(j ^ (lane & 7)) << 4));
+            const float x0 = fmaf(__uint_as_float(v[c][4 * j + 0]), args.acc_scale, bj.x) + r.x;
+            const float x1 = fmaf(__uint_as_float(v[c][4 * j + 1]), args.acc_scale, bj.y) + r.y;
+            const float x2 = fmaf(__uint_as_float(v[c][4 * j + 2]), args.acc_scale, bj.z) + r.z;
+            const float x3 = fmaf(__uint_as_float(v[c][4 * j + 3]), args.acc_scale, bj.w) + r.w;
+            v[c][4 * j + 0] = __float_as_uint(x0);
+            v[c][4 * j + 1] = __float_as_uint(x1);
+            v[c][4 * j + 2] = __float_as_uint(x2);
+            v[c][4 * j + 3] = __float_as_uint(x3);
+            sum += (x0 + x1) + (x2 + x3);
+          }
+        }
+        const float mean_i = sum * (1.f / static_cast<float>(kVals));
+        float m2_i = 0.f;
+#pragma unroll
+        for (int c = 0; c < kChunks; ++c)
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            const float d = __uint_as_float(v[c][j]) - mean_i;
+            m2_i = fmaf(d, d, m2_i);
+          }
+        if (tr) args.trace[71] = global_timer_ns();
+        // ---- exchange ----
+        {
+          const uint32_t slot_addr =
+              stats_u32 + static_cast<uint32_t>(((buf * 2 * kLnMaxNBlocks + my_contrib) * kRowsPerCta + row_in_cta) * 8);
+          const uint32_t bar_addr = smem_u32(&stats_bar[buf]);
+          for (int nb = 0; nb < n_blocks; ++nb) {
+            const uint32_t dst = static_cast<uint32_t>(nb * CG) + cta_rank;
+            st_async_f32x2(mapa_u32(slot_addr, dst), mean_i, m2_i, mapa_u32(bar_addr, dst));
+          }
+        }
+        if (tr) args.trace[72] = global_timer_ns();
+        mbar_wait_warp(&stats_bar[buf], (local_tile >> 1) & 1u);
+        if (tr) args.trace[73] = global_timer_ns();
+        float mean = 0.f, rstd;
+        {
+          const float2 *st = reinterpret_cast<const float2 *>(stats_base) +
+                             (buf * 2 * kLnMaxNBlocks) * kRowsPerCta + row_in_cta;
+#pragma unroll
+          for (int i = 0; i < 2 * kLnMaxNBlocks; ++i)
+            if (i < n_contrib) mean += st[i * kRowsPerCta].x;
+          mean *= 1.f / static_cast<float>(n_contrib);
+          float m2 = 0.f;
+#pragma unroll
+          for (int i = 0; i < 2 * kLnMaxNBlocks; ++i)
+            if (i < n_contrib) {  // re-read from shared memory rather than keep 16 registers live
+              const float2 p = st[i * kRowsPerCta];
+              const float d = p.x - mean;
+              m2 += p.y + static_cast<float>(kVals) * d * d;
+            }
+          rstd = rsqrtf(m2 / static_cast<float>(args.N) + args.ln_eps);
+        }
+        // ---- pass 2 ----
+#pragma unroll
+        for (int c = 0; c < kChunks; ++c) {
+          const int slot = c & 1;
+          const int col0 = colw + c * 32;
+          if (c >= 2) {  // the stores issued from this slot pair two chunks ago must have read them
+            if (lane == 0) tma_store_wait_read<1>();
+            __syncwarp();
+          }
+          float y[32];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float4 g = ld_shared_f4(vec_u32 + static_cast<uint32_t>((c * 32 + 4 * j) * 4));
+            const float4 be = ld_shared_f4(vec_u32 + static_cast<uint32_t>((BLOCK_N + c * 32 + 4 * j) * 4));
+            y[4 * j + 0] = fmaf((__uint_as_float(v[c][4 * j + 0]) - mean) * rstd, g.x, be.x);
+            y[4 * j + 1] = fmaf((__uint_as_float(v[c][4 * j + 1]) - mean) * rstd, g.y, be.y);
+            y[4 * j + 2] = fmaf((__uint_as_float(v[c][4 * j + 2]) - mean) * rstd, g.z, be.z);
+            y[4 * j + 3] = fmaf((__uint_as_float(v[c][4 * j + 3]) - mean) * rstd, g.w, be.w);
+          }
+          if (args.ln_write_f32) {  // 32 rows x 128 B, SWIZZLE_128B
+            const uint32_t rowa = stg + static_cast<uint32_t>(slot * Epi::kChunkBytes) + static_cast<uint32_t>(lane) * 128u;
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+              st_shared_v4(rowa + (static_cast<uint32_t>(j ^ (lane & 7)) << 4), __float_as_uint(y[4 * j]),
+                           __float_as_uint(y[4 * j + 1]), __float_as_uint(y[4 * j + 2]), __float_as_uint(y[4 * j + 3]));
+          }
+          if (args.ln_out2 == 1) {  // bf16: 32 rows x 64 B, SWIZZLE_64B
+            const uint32_t rowa = stg2 + static_cast<uint32_t>(slot * kLnChunk2Bytes) + static_cast<uint32_t>(lane) * 64u;
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+              st_shared_v4(rowa + (static_cast<uint32_t>(j ^ ((lane >> 1) & 3)) << 4), pack_bf16(y[8 * j], y[8 * j + 1]),
+                           pack_bf16(y[8 * j + 2], y[8 * j + 3]), pack_bf16(y[8 * j + 4], y[8 * j + 5]),
+                           pack_bf16(y[8 * j + 6], y[8 * j + 7]));
+          } else if (args.ln_out2 == 2) {  // e4m3: 32 rows x 32 B, no swizzle
+            const float sc = args.out_inv_scale;
+            const uint32_t rowa = stg2 + static_cast<uint32_t>(slot * kLnChunk2Bytes) + static_cast<uint32_t>(lane) * 32u;
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+              uint32_t w[4];
+#pragma unroll
+              for (int i = 0; i < 4; ++i) {
+                const int o = 16 * j + 4 * i;
+                w[i] = pack_e4m3x4(y[o] * sc, y[o + 1] * sc, y[o + 2] * sc, y[o + 3] * sc);
+              }
+              st_shared_v4(rowa + static_cast<uint32_t>(j << 4), w[0], w[1], w[2], w[3]);
+            }
+          }
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            if (args.ln_write_f32) tma_store_2d(&tmap_out, wstage + slot * Epi::kChunkBytes, col0, row0);
+            if (args.ln_out2 != 0)
+              tma_store_2d(&tmap_out2, wstage + 2 * Epi::kChunkBytes + slot * kLnChunk2Bytes, col0, row0);
+            tma_store_commit();
+          }
+          __syncwarp();
+          if (tr) args.trace[74 + c] = global_timer_ns();
+        }
+        if (tr) args.trace[63] = global_timer_ns();
+      }
+      if (lane == 0) tma_store_wait_read<0>();
+      __syncwarp();
+    } else {
     // ===================== epilogue (all CTAs) =====================
     pdl_wait_prior_grid();
     const int e = warp_idx - kEpiWarp0;
@@ -413,7 +638,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
           tcgen05_fence_before();
           __syncwarp();
           if (lane == 0) {
-            if constexpr (CG == 2) mbar_arrive_cluster(&tmem_empty_bar[acc], 0);
+            if constexpr (CG == 2) mbar_arrive_cluster(&tmem_empty_bar[acc], pair_base);
             else mbar_arrive(&tmem_empty_bar[acc]);
           }
         }
@@ -506,10 +731,11 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
     // complete (and visible) at grid completion like any other store
     if (lane == 0) tma_store_wait_read<0>();
     __syncwarp();
+    }  // !kLN
   }
 
   tcgen05_fence_before();
-  if constexpr (CG == 2) cluster_sync_all(); else __syncthreads();
+  if constexpr (kClustered) cluster_sync_all(); else __syncthreads();
   if (tracing && threadIdx.x == 0) args.trace[64] = global_timer_ns();
   if (warp_idx == 2) {
     tcgen05_fence_after();
@@ -584,7 +810,7 @@ spu_status make_out_tmap(CUtensorMap *map, const void *base, int rows, int cols,
 }
 
 struct LaunchMaps {
-  CUtensorMap a, out, resid;
+  CUtensorMap a, out, resid, out2;
 };
 
 template <int BLOCK_N, int CG, int EPI, int IN_FP8>
@@ -593,14 +819,13 @@ spu_status launch_cfg(const GemmPlan &plan, const LaunchMaps &maps, const Kernel
   using Cfg = TileCfg<BLOCK_N, CG, EPI>;
   auto kern = gemm_tcgen05_kernel<BLOCK_N, CG, EPI, IN_FP8>;
   SPU_CUDA_TRY((ensure_dynamic_smem<gemm_tcgen05_kernel<BLOCK_N, CG, EPI, IN_FP8>>(Cfg::kSmemBytes)));
-  const int tiles = (plan.N / BLOCK_N) * ((a.M + kRowsPerCta * CG - 1) / (kRowsPerCta * CG));
-  int dev = 0, sms = kNumSMsB200;
+  constexpr bool kLN = EPI == kEpiBiasResidLN;
+  const int n_blocks = plan.N / BLOCK_N;
+  const int m_blocks = (a.M + kRowsPerCta * CG - 1) / (kRowsPerCta * CG);
+  const int cluster = kLN ? CG * n_blocks : CG;
+  int dev = 0;
   cudaGetDevice(&dev);
-  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  const int units = sms / CG;
-  const int grid = CG * (tiles < units ? tiles : units);
   cudaLaunchConfig_t cfg{};
-  cfg.gridDim = dim3(grid, 1, 1);
   cfg.blockDim = dim3(kThreads, 1, 1);
   cfg.dynamicSmemBytes = Cfg::kSmemBytes;
   cfg.stream = stream;
@@ -612,23 +837,63 @@ spu_status launch_cfg(const GemmPlan &plan, const LaunchMaps &maps, const Kernel
     attrs[n_attr].val.programmaticStreamSerializationAllowed = 1;
     ++n_attr;
   }
-  if (CG == 2) {
+  if (cluster > 1 || kLN) {
     attrs[n_attr].id = cudaLaunchAttributeClusterDimension;
-    attrs[n_attr].val.clusterDim.x = 2;
+    attrs[n_attr].val.clusterDim.x = static_cast<unsigned>(cluster);
     attrs[n_attr].val.clusterDim.y = 1;
     attrs[n_attr].val.clusterDim.z = 1;
     ++n_attr;
   }
   cfg.attrs = attrs;
   cfg.numAttrs = n_attr;
+  int grid;
+  if constexpr (kLN) {
+    // one cluster per row block; persistent over row blocks when more exist than clusters fit the device
+    static int max_clusters[64][9] = {};  // [device][cluster size], 0 = not asked yet
+    int &cached = max_clusters[dev & 63][cluster];
+    int fit = __atomic_load_n(&cached, __ATOMIC_RELAXED);
+    if (fit == 0) {
+      cfg.gridDim = dim3(static_cast<unsigned>(cluster), 1, 1);
+      SPU_CUDA_TRY(cudaOccupancyMaxActiveClusters(&fit, kern, &cfg));
+      SPU_REQUIRE(fit > 0, SPU_ERR_UNSUPPORTED, "gemm: the LayerNorm-fused cluster does not fit this device");
+      if (const char *env = std::getenv("SPU_LN_MAX_CLUSTERS")) {  // experiments: trust the hardware, not the query
+        const int forced = std::atoi(env);
+        if (forced > 0) fit = forced;
+      }
+      __atomic_store_n(&cached, fit, __ATOMIC_RELAXED);
+    }
+    grid = cluster * (m_blocks < fit ? m_blocks : fit);
+  } else {
+    static int sm_count[64] = {};
+    int sms = __atomic_load_n(&sm_count[dev & 63], __ATOMIC_RELAXED);
+    if (sms == 0) {
+      sms = kNumSMsB200;
+      cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+      __atomic_store_n(&sm_count[dev & 63], sms, __ATOMIC_RELAXED);
+    }
+    const int tiles = n_blocks * m_blocks;
+    const int units = sms / CG;
+    grid = CG * (tiles < units ? tiles : units);
+  }
+  cfg.gridDim = dim3(static_cast<unsigned>(grid), 1, 1);
   SPU_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, maps.a, plan.tmap_b[BLOCK_N / CG / 32 - 1], maps.out,
-                                  maps.resid, a));
+                                  maps.resid, maps.out2, a));
   return SPU_OK;
 }
 
 template <int BLOCK_N, int CG>
 spu_status launch_epi(const GemmPlan &plan, const LaunchMaps &maps, const KernelArgs &a,
                       cudaStream_t stream, bool inplace) {
+  if (plan.epilogue == kEpiBiasResidLN) {
+    // BLOCK_N / 2 values of a row live in registers per thread; a lone CTA stages all of B (3 stages need <= 128)
+    if constexpr (BLOCK_N <= 192 && (CG == 2 || BLOCK_N <= 128)) {
+      return plan.in == GemmIn::FP8_E4M3 ? launch_cfg<BLOCK_N, CG, kEpiBiasResidLN, 1>(plan, maps, a, stream)
+                                         : launch_cfg<BLOCK_N, CG, kEpiBiasResidLN, 0>(plan, maps, a, stream);
+    } else {
+      set_error("gemm: the LayerNorm-fused epilogue needs BLOCK_N <= 192 (<= 128 without a CTA pair)");
+      return SPU_ERR_UNSUPPORTED;
+    }
+  }
   if (plan.in == GemmIn::FP8_E4M3) {
     switch (plan.epilogue) {
       case kEpiBias: return launch_cfg<BLOCK_N, CG, kEpiBias, 1>(plan, maps, a, stream);
@@ -676,6 +941,15 @@ void gemm_set_trace(unsigned long long *device_buf, int cta) {
   g_trace_cta = cta;
 }
 void gemm_set_debug_mode(int mode) { g_dbg_mode = mode; }
+
+// LayerNorm-fused epilogue: the widest column block whose count per row stays within the cluster.
+static GemmConfig choose_ln_config(int M, int N) {
+  for (int bn : {192, 128, 64})
+    if (N % bn == 0 && N / bn <= kLnMaxNBlocks) return GemmConfig{(M > kRowsPerCta || bn > 128) ? 2 : 1, bn};
+  return GemmConfig{0, 0};
+}
+
+bool gemm_ln_supported(int N) { return choose_ln_config(1024, N).block_n != 0; }
 
 GemmConfig choose_config(int M, int N, int K, int esize) {
   // Cost model fitted to in-situ measurements on B200 (profiles/r05_gemm_issue_path.md):
@@ -736,6 +1010,13 @@ spu_status gemm_make_plan(GemmPlan *plan, const void *A, int rows_a, const void 
     SPU_REQUIRE((plan->force_cg == 1 || plan->force_cg == 2) && N % plan->force_bn == 0 &&
                     plan->force_bn % 64 == 0 && plan->force_bn <= 256,
                 SPU_ERR_UNSUPPORTED, "gemm: forced tile does not fit N");
+  if (epilogue == kEpiBiasResidLN) {
+    SPU_REQUIRE(gemm_ln_supported(N), SPU_ERR_UNSUPPORTED,
+                "gemm: no LayerNorm-fused tiling spans N with a cluster of <= 8 CTAs");
+    if (plan->force_bn)
+      SPU_REQUIRE(plan->force_bn <= 192 && N / plan->force_bn <= kLnMaxNBlocks, SPU_ERR_UNSUPPORTED,
+                  "gemm: forced tile does not fit the LayerNorm-fused epilogue");
+  }
   for (int i = 0; i < kNumBBoxes; ++i) {
     const int box_rows = 32 * (i + 1);
     plan->b_ok[i] = false;
@@ -753,14 +1034,20 @@ spu_status gemm_make_plan(GemmPlan *plan, const void *A, int rows_a, const void 
 spu_status gemm_launch(const GemmPlan &plan, int M, const GemmEpilogueArgs &args,
                        cudaStream_t stream) {
   SPU_REQUIRE(M > 0 && M <= plan.rows_a, SPU_ERR_CAPACITY, "gemm: M exceeds plan capacity");
-  SPU_REQUIRE(args.out != nullptr, SPU_ERR_INVALID, "gemm: null output");
   SPU_REQUIRE((reinterpret_cast<uintptr_t>(args.out) & 15u) == 0, SPU_ERR_INVALID,
               "gemm: output must be 16-byte aligned");
-  if (plan.epilogue == kEpiBiasResid)
+  const bool ln = plan.epilogue == kEpiBiasResidLN;
+  SPU_REQUIRE(args.out != nullptr || (ln && args.out2 != nullptr), SPU_ERR_INVALID, "gemm: null output");
+  if (plan.epilogue == kEpiBiasResid || ln)
     SPU_REQUIRE(args.resid != nullptr && (reinterpret_cast<uintptr_t>(args.resid) & 15u) == 0,
                 SPU_ERR_INVALID, "gemm: residual epilogue needs a 16-byte aligned residual");
+  if (ln)
+    SPU_REQUIRE(args.gamma != nullptr && args.beta != nullptr && args.bias != nullptr &&
+                    (reinterpret_cast<uintptr_t>(args.out2) & 15u) == 0,
+                SPU_ERR_INVALID, "gemm: the LayerNorm-fused epilogue needs bias, gamma, beta and aligned outputs");
   const int esize = plan.in == GemmIn::FP8_E4M3 ? 1 : 2;
   GemmConfig cfg = plan.force_bn ? GemmConfig{plan.force_cg, plan.force_bn}
+                   : ln          ? choose_ln_config(M, plan.N)
                                  : choose_config(M, plan.N, plan.K, esize);
   SPU_REQUIRE(cfg.block_n > 0, SPU_ERR_UNSUPPORTED, "gemm: no BLOCK_N divides N");
   SPU_REQUIRE(plan.b_ok[cfg.block_n / cfg.cta_group / 32 - 1], SPU_ERR_UNSUPPORTED,
@@ -770,15 +1057,35 @@ spu_status gemm_launch(const GemmPlan &plan, int M, const GemmEpilogueArgs &args
   LaunchMaps maps;
   spu_status st = make_kmajor_tmap(&maps.a, plan.A, M, plan.K, kRowsPerCta, plan.in);
   if (st != SPU_OK) return st;
-  st = make_out_tmap(&maps.out, args.out, M, plan.N, plan.epilogue);
-  if (st != SPU_OK) return st;
-  if (plan.epilogue == kEpiBiasResid) {
-    st = make_out_tmap(&maps.resid, args.resid, M, plan.N, plan.epilogue);
+  if (ln) {
+    st = make_out_tmap(&maps.resid, args.resid, M, plan.N, kEpiBiasResid);
     if (st != SPU_OK) return st;
+    if (args.out != nullptr) {
+      st = make_out_tmap(&maps.out, args.out, M, plan.N, kEpiBiasResid);
+      if (st != SPU_OK) return st;
+    } else {
+      maps.out = maps.resid;
+    }
+    if (args.out2 != nullptr) {
+      st = make_out_tmap(&maps.out2, args.out2, M, plan.N, args.out2_e4m3 ? kEpiBiasGeluE4m3 : kEpiBias);
+      if (st != SPU_OK) return st;
+    } else {
+      maps.out2 = maps.out;
+    }
   } else {
-    maps.resid = maps.out;
+    st = make_out_tmap(&maps.out, args.out, M, plan.N, plan.epilogue);
+    if (st != SPU_OK) return st;
+    if (plan.epilogue == kEpiBiasResid) {
+      st = make_out_tmap(&maps.resid, args.resid, M, plan.N, plan.epilogue);
+      if (st != SPU_OK) return st;
+    } else {
+      maps.resid = maps.out;
+    }
+    maps.out2 = maps.out;
   }
-  KernelArgs a{M, plan.N, plan.K, args.bias, args.acc_scale, args.out_inv_scale, g_trace_buf, g_trace_cta, g_dbg_mode};
+  KernelArgs a{M, plan.N, plan.K, args.bias, args.acc_scale, args.out_inv_scale, g_trace_buf, g_trace_cta, g_dbg_mode,
+               args.gamma, args.beta, args.ln_eps, args.out != nullptr ? 1 : 0,
+               args.out2 == nullptr ? 0 : (args.out2_e4m3 ? 2 : 1)};
   // residual == output: accumulate in place with a TMA reduce-add instead of load + add + store
   const bool inplace = plan.epilogue == kEpiBiasResid && args.resid == args.out;
   return cfg.cta_group == 2 ? launch_bn<2>(plan, cfg.block_n, maps, a, stream, inplace)

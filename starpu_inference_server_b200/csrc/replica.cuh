@@ -76,6 +76,8 @@ struct LayerPlans {
   // FP8 plan set only: FFN1 with mixed operand / output formats (per-GEMM FP8 mask)
   GemmPlan ffn1_b2q;  // bf16 operands -> e4m3 GELU output (FFN2 runs in FP8, FFN1 does not)
   GemmPlan ffn1_q2b;  // e4m3 operands -> bf16 GELU output (FFN1 runs in FP8, FFN2 does not)
+  // residual + LayerNorm fused into the epilogue (replica.ln_fused): replace attn_out / ffn2 + layernorm_kernel
+  GemmPlan attn_out_ln, ffn2_ln;
 };
 
 struct GraphKey {
@@ -122,6 +124,7 @@ struct spu_replica {
   std::vector<void *> allocations;
   float *amax = nullptr;      // [layers * 4] running calibration maxima (FP8 variant)
   bool fp8_calibrated = false;
+  bool ln_fused = false;      // N = hidden GEMMs carry the residual + LayerNorm in their epilogue
   int fp8_layers = 0;         // leading layers whose GEMMs run in FP8 (rest bf16)
   // per layer: which of its four GEMMs run in FP8 (SPU_FP8_GEMM_* bits); others run in bf16
   std::vector<uint8_t> fp8_mask;

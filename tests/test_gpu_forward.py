@@ -283,6 +283,44 @@ def test_bf16_output_option(spu):
     r16.close()
 
 
+@pytest.mark.parametrize("spec_name,B,S", [("BERT_TINY", 5, 40), ("BERT_BASE", 30, 128), ("BERT_BASE", 32, 128),
+                                           ("BERT_BASE", 3, 200)])
+def test_fused_layernorm_forward_vs_oracle(spu, spec_name, B, S):
+    """SPU_LN_FUSED: residual + LayerNorm ride in the attention-output / FFN2 GEMM epilogues (5 launches per layer
+    instead of 7).  Same gate against the fp32 oracle as the default path; against the default path itself only fp32
+    summation order differs (row statistics merged across the cluster instead of inside one warp)."""
+    from oracle import bert_oracle as bo
+    from starpu_inference_server_b200.bert import BertReplica
+
+    spec = getattr(bo, spec_name)
+    w = bo.make_weights(spec, 0)
+    ids, mask = bo.make_inputs(spec, B, S, seed=41 + B, min_len=7)
+    ref = bo.bert_forward(w, spec, ids, mask)
+    plain = BertReplica(w, max_batch=B, max_seq=S)
+    fused = BertReplica(w, max_batch=B, max_seq=S, flags=spu.SPU_LN_FUSED)
+    assert fused.launches_per_forward == 1 + 5 * spec.layers and plain.launches_per_forward == 1 + 7 * spec.layers
+    a, b = _run(plain, ids, mask, spec.hidden), _run(fused, ids, mask, spec.hidden)
+    e = rel_err(b, ref)
+    print(f"{spec_name} B={B} S={S} fused LN: rel_err {e:.3e} (unfused {rel_err(a, ref):.3e}), "
+          f"fused vs unfused {rel_err(b, a):.3e}")
+    assert np.isfinite(b).all() and e < BF16_TOL
+    assert rel_err(b, a) < 5e-3
+    if B * S <= 1024:  # like the unfused tests: a 1e-2 margin decides every token only on small batches
+        check_top1(b, ref)
+    else:
+        tm, ts = top1_agreement(b, ref, TOP1_MARGIN), top1_agreement(b, ref)
+        print(f"  top-1 beyond the 1e-2 margin {tm:.5f} (unfused {top1_agreement(a, ref, TOP1_MARGIN):.5f}), strict {ts:.4f}")
+        assert tm >= 0.995 and ts >= 0.97
+    # bf16 output option through the fused epilogue
+    f16 = BertReplica(w, max_batch=B, max_seq=S, flags=spu.SPU_LN_FUSED | spu.SPU_OUTPUT_BF16)
+    o16 = torch.full((B, S, spec.hidden), float("nan"), dtype=torch.bfloat16, device="cuda")
+    f16.forward_async(torch.from_numpy(ids).cuda(), torch.from_numpy(mask).cuda(), o16)
+    torch.cuda.synchronize()
+    assert torch.equal(o16.cpu(), torch.from_numpy(b).to(torch.bfloat16))
+    for r in (plain, fused, f16):
+        r.close()
+
+
 def test_capacity_and_argument_errors(base, spu):
     bo, w, r = base
     ids = torch.zeros(65, 512, dtype=torch.int64, device="cuda")

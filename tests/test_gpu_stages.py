@@ -110,6 +110,75 @@ def test_gemm_inplace_residual(spu):
     assert torch.allclose(x.cpu(), ref, rtol=2e-3, atol=2e-3)
 
 
+# ------------------------------------------- GEMM with fused residual + LayerNorm epilogue
+def _check_gemm_ln(spu, M, N, K, cg, bn, seed, inplace=True, want_f32=True, want_bf16=True):
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    a = (torch.randn(M, K, generator=g) * 0.5).to(torch.bfloat16).cuda()
+    w = (torch.randn(N, K, generator=g) * 0.05).to(torch.bfloat16).cuda()
+    bias, gamma, beta = (torch.randn(N, generator=g).cuda() for _ in range(3))
+    # a non-zero row mean and unequal column scales: the merged (mean, M2) must handle both
+    resid = (torch.randn(M, N, generator=g) * torch.linspace(0.2, 3.0, N) + 1.5).cuda()
+    x = a.float().cpu() @ w.float().cpu().T + bias.cpu() + resid.cpu()
+    ref = torch.nn.functional.layer_norm(x.double(), (N,), gamma.cpu().double(), beta.cpu().double(), 1e-12).float()
+    guard = torch.full((M + 1, N), float("nan"), device="cuda")
+    if inplace:
+        guard[:M] = resid
+        resid_arg = guard
+    else:
+        resid_arg = resid
+    out16 = torch.full((M + 1, N), float("nan"), dtype=torch.bfloat16, device="cuda")
+    spu.check(spu.lib().spu_gemm_ln_bf16_async(
+        spu.ptr(a), spu.ptr(w), spu.ptr(bias), spu.ptr(resid_arg), spu.ptr(gamma), spu.ptr(beta), 1e-12,
+        spu.ptr(guard) if want_f32 else None, spu.ptr(out16) if want_bf16 else None, M, N, K, cg, bn,
+        spu.stream_ptr()))
+    _sync()
+    if want_f32:
+        assert torch.isnan(guard[M]).all(), "fused LayerNorm GEMM wrote fp32 past row M"
+        got = guard[:M].cpu()
+        assert torch.isfinite(got).all()
+        err = (got - ref).abs().max().item()
+        assert err < 5e-4, f"fp32 y: max err {err:.3g}"
+    if want_bf16:
+        assert torch.isnan(out16[M].float()).all(), "fused LayerNorm GEMM wrote bf16 past row M"
+        got16 = out16[:M].cpu()
+        if want_f32:  # the bf16 copy is the fp32 result rounded to nearest even, bit for bit
+            assert torch.equal(got16.view(torch.int16), guard[:M].cpu().to(torch.bfloat16).view(torch.int16))
+        else:
+            assert ((got16.float() - ref).abs() <= 2.0 ** -8 * ref.abs() + 5e-4).all()
+
+
+@pytest.mark.parametrize("M,N,K,cg,bn", [
+    (4096, 768, 768, 0, 0),     # BERT-base attention-output: 16 clusters of 4 CTA pairs x 192 columns
+    (4096, 768, 3072, 0, 0),    # BERT-base FFN2
+    (5000, 768, 768, 0, 0),     # more row blocks than resident clusters: persistent loop, ragged tail
+    (333, 768, 320, 0, 0),
+    (64, 768, 768, 0, 0),       # a single slab: the second CTA of each pair holds dead rows
+    (1024, 768, 768, 2, 192),
+    (512, 128, 128, 1, 64), (512, 128, 128, 2, 64), (512, 128, 128, 1, 128), (300, 128, 512, 2, 128),
+    (700, 256, 128, 2, 64), (700, 256, 128, 1, 64), (700, 256, 256, 2, 128),
+    (1111, 512, 128, 2, 128), (1111, 512, 192, 1, 128), (8192, 384, 128, 2, 192),
+])
+def test_gemm_fused_residual_layernorm(spu, M, N, K, cg, bn):
+    """y = LayerNorm(A W^T + bias + resid) with the row statistics merged across the cluster that spans the N
+    columns (st.async over distributed shared memory), against a float64 LayerNorm of the fp32 product."""
+    _check_gemm_ln(spu, M, N, K, cg, bn, seed=M + N + K + cg + bn)
+
+
+def test_gemm_fused_layernorm_output_variants(spu):
+    _check_gemm_ln(spu, 600, 768, 768, 0, 0, seed=1, inplace=False)
+    _check_gemm_ln(spu, 600, 768, 768, 0, 0, seed=2, want_bf16=False)
+    _check_gemm_ln(spu, 600, 768, 768, 0, 0, seed=3, want_f32=False, inplace=False)
+    # hidden sizes no cluster of <= 8 CTAs spans are refused (the forward then keeps the separate LayerNorm kernel)
+    a = torch.zeros(128, 1024, dtype=torch.bfloat16, device="cuda")
+    st = spu.lib().spu_gemm_ln_bf16_async(spu.ptr(a), spu.ptr(a), spu.ptr(a), spu.ptr(a), spu.ptr(a), spu.ptr(a), 1e-12,
+                                          spu.ptr(a), None, 128, 1024, 1024, 0, 0, spu.stream_ptr())
+    assert st == spu.SPU_ERR_UNSUPPORTED
+    # 768 = 6 x 128: more column blocks than the cluster holds
+    st = spu.lib().spu_gemm_ln_bf16_async(spu.ptr(a), spu.ptr(a), spu.ptr(a), spu.ptr(a), spu.ptr(a), spu.ptr(a), 1e-12,
+                                          spu.ptr(a), None, 128, 768, 768, 2, 128, spu.stream_ptr())
+    assert st == spu.SPU_ERR_UNSUPPORTED
+
+
 def test_gemm_rejects_bad_shapes(spu):
     a = torch.zeros(128, 100, dtype=torch.bfloat16, device="cuda")
     st = spu.lib().spu_gemm_bf16_async(spu.ptr(a), spu.ptr(a), None, None, spu.ptr(a), 128, 128, 100, 0,

@@ -20,6 +20,8 @@ from starpu_inference_server_b200 import capi  # noqa: E402
 SHAPES = {  # name: (N, K, epilogue)
     "qkv": (2304, 768, 0), "attn_out": (768, 768, 2), "ffn1": (3072, 768, 1), "ffn2": (768, 3072, 2),
     # epilogue-cost probes: the N=768 shapes with the plain bf16 epilogue / with a separate residual buffer
+    # residual + LayerNorm fused into the epilogue (cluster of 4 CTA pairs x 192 columns)
+    "attn_out_ln": (768, 768, 5), "ffn2_ln": (768, 3072, 5),
     "attn_out_bf16": (768, 768, 0), "ffn2_bf16": (768, 3072, 0), "attn_out_sep": (768, 768, 12), "ffn2_sep": (768, 3072, 12),
 }
 
@@ -35,9 +37,20 @@ def run(M, N, K, epi, cg, bn, reps, n_buf):
     res = [torch.zeros(M, N, device="cuda") for _ in range(n_buf)] if separate else out
     s = torch.cuda.Stream()
 
+    ln = epi == 5
+    if ln:
+        out = [torch.zeros(M, N, device="cuda") for _ in range(n_buf)]
+        out16 = [torch.zeros(M, N, device="cuda", dtype=torch.bfloat16) for _ in range(n_buf)]
+        gamma, beta = torch.ones(N, device="cuda"), torch.zeros(N, device="cuda")
+
     def enqueue():
         for i in range(reps):
             o = out[i % n_buf]
+            if ln:
+                capi.check(L.spu_gemm_ln_bf16_async(capi.ptr(a[i % n_buf]), capi.ptr(w), capi.ptr(bias), capi.ptr(o),
+                                                    capi.ptr(gamma), capi.ptr(beta), 1e-12, capi.ptr(o),
+                                                    capi.ptr(out16[i % n_buf]), M, N, K, cg, bn, capi.stream_ptr(s)))
+                continue
             capi.check(L.spu_gemm_bf16_cfg_async(capi.ptr(a[i % n_buf]), capi.ptr(w), capi.ptr(bias),
                                                  capi.ptr(res[i % n_buf]) if epi == 2 else None, capi.ptr(o), M, N, K, epi,
                                                  cg, bn, capi.stream_ptr(s)))
@@ -60,25 +73,25 @@ def run(M, N, K, epi, cg, bn, reps, n_buf):
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--M", type=int, default=4096)
+    ap.add_argument("--M", default="4096", help="comma-separated row counts")
     ap.add_argument("--reps", type=int, default=40)
     ap.add_argument("--bufs", type=int, default=1, help="distinct A/out buffers rotated (1 = L2-warm, as in the forward)")
     ap.add_argument("--shapes", default="qkv,attn_out,ffn1,ffn2")
     ap.add_argument("--all", action="store_true", help="sweep every tile, not only the chosen one")
     args = ap.parse_args()
-    for name in args.shapes.split(","):
+    for name, M in ((n, int(m)) for n in args.shapes.split(",") for m in args.M.split(",")):
         N, K, epi = SHAPES[name]
         cfgs = [(0, 0)]
-        if args.all:
+        if args.all and epi != 5:
             cfgs += [(cg, bn) for cg in (2, 1) for bn in (256, 192, 128, 64) if N % bn == 0]
         for cg, bn in cfgs:
             try:
-                us = run(args.M, N, K, epi, cg, bn, args.reps, args.bufs)
+                us = run(M, N, K, epi, cg, bn, args.reps, args.bufs)
             except Exception as ex:  # keep sweeping
                 print(json.dumps({"shape": name, "cg": cg, "bn": bn, "error": str(ex)}), flush=True)
                 continue
-            tf = 2.0 * args.M * N * K / us / 1e6
-            print(json.dumps({"shape": name, "M": args.M, "N": N, "K": K, "epi": epi, "cg": cg, "bn": bn,
+            tf = 2.0 * M * N * K / us / 1e6
+            print(json.dumps({"shape": name, "M": M, "N": N, "K": K, "epi": epi, "cg": cg, "bn": bn,
                               "us": round(us, 2), "tflops": round(tf, 1)}), flush=True)
 
 
