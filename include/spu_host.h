@@ -80,6 +80,11 @@ typedef struct spu_server_cfg {
    * most length_bucket - 1 extra tokens per row instead of to the longest request in arrival order.  The oldest
    * queued request always opens the next batch, so no bucket starves.  0 = arrival order (the reference). */
   int32_t length_bucket;
+  /* gpu_model_replication (config_loader_device.hpp): 0 = per_device: replicas[i] serves device_ids[i];
+   * 1 = per_worker: one replica per CUDA worker, replicas[] ordered device by device then by StarPU worker id
+   * (n_devices x nworker_per_cuda entries), as build_gpu_replica_assignments orders them
+   * (src/core/inference_runner.cpp:128-183). */
+  int32_t gpu_model_replication;
 } spu_server_cfg;
 
 typedef struct spu_request {
@@ -143,6 +148,15 @@ int32_t spu_host_buffer_byte_size(int32_t interface_id, uint32_t nx, uint64_t el
  * returns the chosen index, or -1 on StarPUCodeletException (message in last_error). */
 int32_t spu_host_select_replica(const int32_t *device_ids, int32_t n_device_ids, const int32_t *worker_ids,
                                 int32_t n_worker_ids, int32_t n_models, int32_t worker_id, int32_t device_id);
+/* build_gpu_replica_assignments (inference_runner.cpp:128-183) + ReplicaRegistry::fill_model_pointers
+ * (inference_task.cpp:469-516) + select_gpu_module, without a runtime: the CUDA workers are described by
+ * worker_dev[w] = device of StarPU worker w.  Writes the assignments (device, worker or -1) and returns their
+ * count; `pick_*` (when >= 0) additionally selects the replica for that worker / device and stores its
+ * assignment index in *picked.  -1 on an exception (message in last_error). */
+int32_t spu_host_replica_assignments(const int32_t *device_ids, int32_t n_device_ids, int32_t per_worker,
+                                     const int32_t *worker_dev, int32_t n_workers, int32_t *out_device,
+                                     int32_t *out_worker, int32_t cap, int32_t pick_worker, int32_t pick_device,
+                                     int32_t *picked);
 /* copy_job_inputs_to_slot over one input: n_jobs host arrays back to back into a slot of
  * `capacity` bytes registered with elemsize; returns 0 ok / 1 exception.  nx_out = the
  * handle's nx afterwards on node 0. */

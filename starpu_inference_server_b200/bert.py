@@ -61,20 +61,6 @@ def config_from_state(state) -> BertConfig:
                       type_vocab=state["embeddings.token_type_embeddings.weight"].shape[0])
 
 
-def state_from_torchscript(path: str):
-    """Read the weights of a ``bert_libtorch.pt`` produced like
-    /root/reference/models/import_bert-base-uncased.py (keys carry a ``bert.`` prefix
-    from the wrapper module).  Start-up only."""
-    import torch
-
-    sd = torch.jit.load(path, map_location="cpu").state_dict()
-    out = {}
-    for k, v in sd.items():
-        k = k[5:] if k.startswith("bert.") else k
-        out[k] = v.detach().to(torch.float32).contiguous().numpy()
-    return out
-
-
 class BertReplica:
     """One weight replica on one GPU + ``n_workspaces`` worker-private arenas."""
 
@@ -91,6 +77,13 @@ class BertReplica:
         capi.check(capi.lib().spu_bert_replica_create(C.byref(desc), arr, len(keep), device, max_batch,
                                                       max_seq, n_workspaces, flags, C.byref(h)))
         self._h = h
+
+    @classmethod
+    def from_handle(cls, handle, cfg: BertConfig, device: int, max_batch: int, max_seq: int):
+        """Adopt a replica created elsewhere (the C++ TorchScript loader, loader.TorchScriptModule)."""
+        self = cls.__new__(cls)
+        self.cfg, self.device, self.max_batch, self.max_seq, self._h = cfg, device, max_batch, max_seq, handle
+        return self
 
     @property
     def launches_per_forward(self) -> int:

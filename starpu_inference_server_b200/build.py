@@ -4,7 +4,8 @@
 
 Produces, next to this file:
   libspu_b200.so        CUDA kernels + the C-ABI of include/spu_b200.h
-  libspu_host.so        C++ host layer (StarPU-shaped codelet, slot pools, mini runtime)
+  libspu_host.so        C++ host layer (StarPU-shaped codelet, slot pools, replica registry, mini runtime)
+  libspu_loader.so      start-up-only TorchScript weight loader (the one library that links LibTorch)
 nvcc cross-compiles without a GPU, so this runs in the CPU-only build container;
 the .so files travel to the GPU box with the repo snapshot.
 """
@@ -20,6 +21,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
 CORE = os.path.join(HERE, "core")
+LOADER = os.path.join(HERE, "loader")
 OBJ = os.path.join(HERE, "_obj")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 
@@ -29,8 +31,8 @@ NVCC_FLAGS = ARCH + ["-std=c++17", "-O3", "-lineinfo", "-Xcompiler", "-fPIC",
                      "-I", os.path.join(ROOT, "include")]
 
 CUDA_SOURCES = ["replica.cu", "gemm_sm100.cu", "attention.cu", "attention_sm100.cu", "rowops.cu", "vit.cu"]
-HOST_SOURCES = ["inference_codelet.cpp", "slot_pools.cpp", "task_runner.cpp", "mini_starpu.cpp", "host_capi.cpp",
-                "host_test_hooks.cpp"]
+HOST_SOURCES = ["inference_codelet.cpp", "slot_pools.cpp", "replica_registry.cpp", "task_runner.cpp",
+                "mini_starpu.cpp", "host_capi.cpp", "host_test_hooks.cpp"]
 CXX = os.environ.get("CXX", "g++")
 CUDA_HOME = os.environ.get("CUDA_HOME", "/usr/local/cuda")
 CXX_FLAGS = ["-std=c++20", "-O2", "-g", "-fPIC", "-Wall", "-Wextra", "-pthread",
@@ -85,6 +87,40 @@ def _build_lib(name, directory, sources, extra_link, force):
     return out, True
 
 
+def _torch_dir():
+    """site-packages/torch without importing it (its headers and libs ship in the wheel)."""
+    import importlib.util
+
+    spec = importlib.util.find_spec("torch")
+    if spec is None or not spec.submodule_search_locations:
+        return None
+    d = list(spec.submodule_search_locations)[0]
+    return d if os.path.isdir(os.path.join(d, "include", "torch")) else None
+
+
+def _build_loader(force):
+    """libspu_loader.so: plain g++ against the wheel's LibTorch (C++17, cxx11 ABI as torch >= 2.x wheels use)."""
+    out = os.path.join(HERE, "libspu_loader.so")
+    src = os.path.join(LOADER, "torchscript_loader.cpp")
+    tdir = _torch_dir()
+    if tdir is None or not os.path.exists(src):
+        return None, False
+    stamp = os.path.join(OBJ, "libspu_loader.so.sha256")
+    dig = _digest([src, os.path.join(ROOT, "include", "spu_loader.h"), os.path.join(ROOT, "include", "spu_b200.h")])
+    if not force and os.path.exists(out) and os.path.exists(stamp) and open(stamp).read() == dig:
+        return out, False
+    os.makedirs(OBJ, exist_ok=True)
+    tlib = os.path.join(tdir, "lib")
+    _run([CXX, "-std=c++17", "-O2", "-fPIC", "-shared", "-D_GLIBCXX_USE_CXX11_ABI=1",
+          "-I", os.path.join(ROOT, "include"), "-I", os.path.join(tdir, "include"),
+          "-I", os.path.join(tdir, "include", "torch", "csrc", "api", "include"), src, "-o", out,
+          "-L" + HERE, "-lspu_b200", "-L" + tlib, "-ltorch", "-ltorch_cpu", "-lc10",
+          "-Wl,-rpath,$ORIGIN", "-Wl,-rpath," + tlib])
+    with open(stamp, "w") as f:
+        f.write(dig)
+    return out, True
+
+
 def build(force: bool = False, verbose: bool = False):
     """Compile every CUDA/C++ source for sm_100a; returns the library paths."""
     libs = []
@@ -99,6 +135,11 @@ def build(force: bool = False, verbose: bool = False):
         libs.append(p2)
         if verbose:
             print(("built " if rebuilt2 else "up to date ") + p2)
+    p3, rebuilt3 = _build_loader(force or rebuilt)
+    if p3 is not None:
+        libs.append(p3)
+        if verbose:
+            print(("built " if rebuilt3 else "up to date ") + p3)
     return libs
 
 

@@ -55,7 +55,7 @@ struct Ticket {
 }  // namespace
 
 struct spu_server {
-  std::vector<std::unique_ptr<DeviceModel>> models;
+  ReplicaRegistry registry;  // device / worker -> replica; outlives the runner and the runtime
   std::unique_ptr<TaskRunner> runner;
   ModelConfig model;
   bool starpu_up = false;
@@ -282,25 +282,31 @@ int32_t spu_server_create(const spu_server_cfg *cfg, spu_server **out) {
       s->model.variable_length = cfg->variable_length != 0;
       s->length_bucket = cfg->length_bucket > 0 ? cfg->length_bucket : 0;
       s->coalesce_ms = cfg->batch_coalesce_timeout_ms;
-      std::vector<int> dev_ids;
-      std::vector<DeviceModel *> models;
-      for (int i = 0; i < cfg->n_devices; ++i) {
-        auto m = std::make_unique<DeviceModel>();
-        m->kind = cfg->model_kind == SPU_MODEL_BERT  ? DeviceModel::Kind::Bert
-                  : cfg->model_kind == SPU_MODEL_VIT ? DeviceModel::Kind::Vit
-                                                     : DeviceModel::Kind::Affine;
-        m->replica = cfg->replicas[i];
-        m->n_workspaces = cfg->n_workspaces;
-        m->scale = cfg->affine_scale;
-        m->shift = cfg->affine_shift;
-        m->device_id = cfg->device_ids[i];
-        if (m->kind != DeviceModel::Kind::Affine && m->replica == nullptr)
-          throw std::invalid_argument("missing replica for device " + std::to_string(cfg->device_ids[i]));
-        dev_ids.push_back(cfg->device_ids[i]);
-        models.push_back(m.get());
-        s->models.push_back(std::move(m));
+      // build_gpu_replica_assignments (inference_runner.cpp:128-183): one replica per device, or per CUDA worker
+      // (gpu_model_replication: per_worker); cfg->replicas[i] serves assignment i.  The caller created them
+      // (spu_bert_replica_create / libspu_loader.so) and keeps ownership.
+      std::vector<int> dev_ids(cfg->device_ids, cfg->device_ids + cfg->n_devices);
+      const auto policy = cfg->gpu_model_replication != 0 ? GpuModelReplicationPolicy::PerWorker
+                                                          : GpuModelReplicationPolicy::PerDevice;
+      const auto assignments = build_gpu_replica_assignments(dev_ids, policy);
+      if (assignments.size() > SPU_HOST_MAX_DEVICES) throw std::invalid_argument("too many replica assignments");
+      for (size_t i = 0; i < assignments.size(); ++i) {
+        DeviceModel m;
+        m.kind = cfg->model_kind == SPU_MODEL_BERT  ? DeviceModel::Kind::Bert
+                 : cfg->model_kind == SPU_MODEL_VIT ? DeviceModel::Kind::Vit
+                                                    : DeviceModel::Kind::Affine;
+        m.replica = cfg->replicas[i];
+        m.n_workspaces = cfg->n_workspaces;
+        m.scale = cfg->affine_scale;
+        m.shift = cfg->affine_shift;
+        if (m.kind != DeviceModel::Kind::Affine && m.replica == nullptr)
+          throw std::invalid_argument("missing replica for device " + std::to_string(assignments[i].device_id) +
+                                      (assignments[i].worker_id >= 0
+                                           ? " worker " + std::to_string(assignments[i].worker_id)
+                                           : std::string()));
+        s->registry.add(assignments[i], m, /*owned=*/false);
       }
-      s->runner = std::make_unique<TaskRunner>(s->model, dev_ids, models);
+      s->runner = std::make_unique<TaskRunner>(s->model, &s->registry);
       spu_server *raw = s.get();
       s->collector = std::thread([raw] { raw->collector_loop(); });
     } catch (...) {
@@ -325,8 +331,8 @@ void spu_server_destroy(spu_server *s) {
   s->qcv.notify_all();
   if (s->collector.joinable()) s->collector.join();
   if (s->runner) s->runner->wait_for_all();
-  for (auto &m : s->models)
-    if (m->replica) forget_replica_workspaces(m->replica);
+  for (size_t i = 0; i < s->registry.size(); ++i)
+    if (s->registry.model(i)->replica) forget_replica_workspaces(s->registry.model(i)->replica);
   s->runner.reset();  // unregisters the slot handles while the runtime is still up
   if (s->starpu_up) starpu_shutdown();
   delete s;

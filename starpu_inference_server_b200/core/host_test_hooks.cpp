@@ -2,7 +2,9 @@
 // single host-side function the way the reference's own unit tests do, so that
 // tests/test_host_*.py read like tests/unit/core/unit_starpu_setup.cpp and
 // tests/unit/starpu/unit_starpu_task_runner_*.cpp.
+#include <algorithm>
 #include <cstring>
+#include <map>
 
 #include "../../include/spu_host.h"
 #include "task_runner.hpp"
@@ -73,6 +75,41 @@ int32_t spu_host_select_replica(const int32_t *device_ids, int32_t n_device_ids,
     DeviceModel *m = select_gpu_module(p, worker_id, device_id);
     return static_cast<int32_t>(m - models.data());
   } catch (const StarPUCodeletException &e) {
+    fail(e);
+    return -1;
+  }
+}
+
+int32_t spu_host_replica_assignments(const int32_t *device_ids, int32_t n_device_ids, int32_t per_worker,
+                                     const int32_t *worker_dev, int32_t n_workers, int32_t *out_device,
+                                     int32_t *out_worker, int32_t cap, int32_t pick_worker, int32_t pick_device,
+                                     int32_t *picked) {
+  try {
+    std::vector<int> devs(device_ids, device_ids + n_device_ids);
+    auto workers = [&](const std::vector<int> &ids) {
+      std::map<int, std::vector<int>> by_dev;
+      for (int w = 0; w < n_workers; ++w)
+        if (std::find(ids.begin(), ids.end(), worker_dev[w]) != ids.end()) by_dev[worker_dev[w]].push_back(w);
+      return by_dev;
+    };
+    const auto assignments = build_gpu_replica_assignments(
+        devs, per_worker ? GpuModelReplicationPolicy::PerWorker : GpuModelReplicationPolicy::PerDevice, workers);
+    ReplicaRegistry reg;
+    for (const auto &a : assignments) reg.add(a, DeviceModel{}, false);
+    for (size_t i = 0; i < assignments.size() && static_cast<int32_t>(i) < cap; ++i) {
+      if (out_device) out_device[i] = assignments[i].device_id;
+      if (out_worker) out_worker[i] = assignments[i].worker_id;
+    }
+    if (picked != nullptr && (pick_worker >= 0 || pick_device >= 0)) {
+      InferenceParams p;
+      reg.fill_model_pointers(p.models);
+      DeviceModel *m = select_gpu_module(p, pick_worker, pick_device);
+      *picked = -1;
+      for (size_t i = 0; i < reg.size(); ++i)
+        if (reg.model(i) == m) *picked = static_cast<int32_t>(i);
+    }
+    return static_cast<int32_t>(assignments.size());
+  } catch (const std::exception &e) {
     fail(e);
     return -1;
   }

@@ -43,8 +43,8 @@ struct InferLimits {
   static constexpr size_t MaxDims = 8;
 };
 
-// What runs for `model->forward(...)` on a CUDA worker.  Owned by the replica registry
-// (core/replica_registry.hpp); the codelet only reads it.
+// What runs for `model->forward(...)` on a CUDA worker.  The entries live in the replica registry
+// (core/replica_registry.hpp: ReplicaRegistry); the codelet only reads them.
 struct DeviceModel {
   enum class Kind : uint8_t { Bert, Vit, Affine } kind = Kind::Affine;
   spu_replica *replica = nullptr;  // Bert / Vit: weights + per-worker workspaces on one GPU

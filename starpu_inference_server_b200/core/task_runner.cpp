@@ -181,13 +181,14 @@ struct TaskRunner::CallbackContext {
   std::vector<bool> acquired;
 };
 
-TaskRunner::TaskRunner(ModelConfig model, std::vector<int> device_ids, std::vector<DeviceModel *> models_gpu)
-    : model_(std::move(model)), device_ids_(std::move(device_ids)), models_gpu_(std::move(models_gpu)) {
-  if (models_gpu_.size() > InferLimits::MaxModelsGPU) throw std::invalid_argument("too many GPU replicas");
+TaskRunner::TaskRunner(ModelConfig model, const ReplicaRegistry *replicas)
+    : model_(std::move(model)), replicas_(replicas) {
+  if (replicas_ == nullptr) throw std::invalid_argument("TaskRunner needs a replica registry");
+  if (replicas_->size() > InferLimits::MaxModelsGPU) throw std::invalid_argument("too many GPU replicas");
   if (model_.inputs.empty() || model_.inputs.size() > InferLimits::MaxInputs)
     throw std::invalid_argument("model must declare 1..16 inputs");
   if (model_.outputs.empty()) throw std::invalid_argument("model must declare outputs");
-  const bool pinned = !device_ids_.empty();
+  const bool pinned = replicas_->size() > 0;
   input_pool_ = std::make_unique<InputSlotPool>(model_.inputs, model_.max_batch_size, model_.pool_size, pinned);
   output_pool_ = std::make_unique<OutputSlotPool>(model_.outputs, model_.max_batch_size, model_.pool_size, pinned);
   // Output slots are only ever consumed on the host (starpu_output_callback acquires them, inference_task.cpp:
@@ -285,8 +286,7 @@ void TaskRunner::submit_batch(const std::vector<std::shared_ptr<InferenceJob>> &
   }
 
   auto params = std::make_unique<InferenceParams>();
-  params->models.device_ids = device_ids_;
-  params->models.models_gpu = models_gpu_;
+  replicas_->fill_model_pointers(params->models);  // InferenceTask::fill_model_pointers
   params->num_inputs = model_.inputs.size();
   params->num_outputs = model_.outputs.size();
   params->batch_size = effective_batch;

@@ -20,6 +20,7 @@
 #include <vector>
 
 #include "inference_codelet.hpp"
+#include "replica_registry.hpp"
 #include "slot_pools.hpp"
 
 namespace starpu_server {
@@ -116,8 +117,9 @@ struct ModelConfig {  // the slice of models/*.yml the path needs (config_loader
 // slot pools, knows the per-device replicas, submits one StarPU task per batch.
 class TaskRunner {
  public:
-  // models_gpu[i] serves device_ids[i] (build_gpu_replica_assignments, inference_runner.cpp:128-183)
-  TaskRunner(ModelConfig model, std::vector<int> device_ids, std::vector<DeviceModel *> models_gpu);
+  // `replicas` says which replica serves which device / worker (core/replica_registry.hpp); it must outlive
+  // the runner.  Every task's InferenceParams::models is filled from it (fill_model_pointers).
+  TaskRunner(ModelConfig model, const ReplicaRegistry *replicas);
   ~TaskRunner();
 
   // One task from jobs[0] (master) + jobs[1..] (aggregated sub-jobs, in order).  Blocks while
@@ -137,8 +139,7 @@ class TaskRunner {
   static void finalize(CallbackContext *ctx);
 
   ModelConfig model_;
-  std::vector<int> device_ids_;
-  std::vector<DeviceModel *> models_gpu_;
+  const ReplicaRegistry *replicas_;
   InferenceCodelet codelet_;
   std::unique_ptr<InputSlotPool> input_pool_;
   std::unique_ptr<OutputSlotPool> output_pool_;

@@ -23,6 +23,7 @@ SYMBOLS = [
     "spu_server_wait_all", "spu_server_stats", "spu_host_last_error", "spu_host_codelet_fields",
     "spu_host_buffer_byte_size", "spu_host_select_replica", "spu_host_gather_to_slot", "spu_host_slice_rows",
     "spu_host_can_merge", "spu_host_call_cuda_func_affine", "spu_host_can_merge_varlen", "spu_host_gather_padded",
+    "spu_host_replica_assignments",
 ]
 
 
@@ -37,7 +38,7 @@ class ServerCfg(C.Structure):
                 ("inputs", TensorCfg * MAX_IO), ("outputs", TensorCfg * MAX_IO), ("model_kind", C.c_int32),
                 ("replicas", C.c_void_p * MAX_DEV), ("n_workspaces", C.c_int32), ("affine_scale", C.c_float),
                 ("affine_shift", C.c_float), ("variable_length", C.c_int32),
-                ("length_bucket", C.c_int32)]
+                ("length_bucket", C.c_int32), ("gpu_model_replication", C.c_int32)]
 
 
 class Request(C.Structure):
@@ -85,6 +86,9 @@ def lib():
     L.spu_host_buffer_byte_size.restype = i32
     L.spu_host_select_replica.argtypes = [C.POINTER(i32), i32, C.POINTER(i32), i32, i32, i32, i32]
     L.spu_host_select_replica.restype = i32
+    L.spu_host_replica_assignments.argtypes = [C.POINTER(i32), i32, i32, C.POINTER(i32), i32, C.POINTER(i32),
+                                               C.POINTER(i32), i32, i32, i32, C.POINTER(i32)]
+    L.spu_host_replica_assignments.restype = i32
     L.spu_host_gather_to_slot.argtypes = [C.POINTER(vp), C.POINTER(u64), i32, u64, vp, u64, C.POINTER(u64),
                                           C.POINTER(u64)]
     L.spu_host_gather_to_slot.restype = i32
@@ -125,13 +129,15 @@ class Server:
 
     ``inputs`` / ``outputs``: list of (name, dtype, dims) as models/<name>.yml declares them,
     dims[0] = per-request batch.  ``replicas``: list of replica handles (``BertReplica`` /
-    ``VitReplica`` objects or raw pointers), one per entry of ``device_ids``.
+    ``VitReplica`` objects or raw pointers), one per entry of ``device_ids`` -- or, with
+    ``per_worker_replicas`` (gpu_model_replication: per_worker), one per CUDA worker, device by device.
     """
 
     def __init__(self, inputs, outputs, device_ids=(0,), replicas=(), model_kind=MODEL_BERT, max_batch_size=32,
                  pool_size=12, nworker_per_cuda=1, cuda_pipeline=2, batch_coalesce_timeout_ms=0, n_workspaces=1,
-                 affine=(1.0, 0.0), variable_length=False, length_bucket=0):
+                 affine=(1.0, 0.0), variable_length=False, length_bucket=0, per_worker_replicas=False):
         cfg = ServerCfg()
+        cfg.gpu_model_replication = 1 if per_worker_replicas else 0
         cfg.variable_length = 1 if variable_length else 0
         cfg.length_bucket = int(length_bucket)
         self.variable_length = bool(variable_length)

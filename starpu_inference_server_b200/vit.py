@@ -55,13 +55,6 @@ def config_from_state(state, image: int = 224) -> VitConfig:
                      image=side * patch, channels=channels, classes=state["heads.head.weight"].shape[0])
 
 
-def state_from_torchscript(path: str):
-    import torch
-
-    sd = torch.jit.load(path, map_location="cpu").state_dict()
-    return {k: v.detach().to(torch.float32).contiguous().numpy() for k, v in sd.items()}
-
-
 class VitReplica:
     """One ViT weight replica on one GPU + ``n_workspaces`` worker-private arenas."""
 
@@ -77,6 +70,13 @@ class VitReplica:
         capi.check(capi.lib().spu_vit_replica_create(C.byref(desc), arr, len(keep), device, max_batch, n_workspaces,
                                                      flags, C.byref(h)))
         self._h = h
+
+    @classmethod
+    def from_handle(cls, handle, cfg: VitConfig, device: int, max_batch: int):
+        """Adopt a replica created elsewhere (the C++ TorchScript loader, loader.TorchScriptModule)."""
+        self = cls.__new__(cls)
+        self.cfg, self.device, self.max_batch, self._h = cfg, device, max_batch, handle
+        return self
 
     @property
     def launches_per_forward(self) -> int:

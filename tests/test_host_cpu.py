@@ -93,6 +93,34 @@ def test_select_gpu_module_throws_when_replica_missing(host):
     assert _select(host, [], [], 2, 0, -1) == -1
 
 
+def _assign(host, device_ids, per_worker, worker_dev, pick_worker=-1, pick_device=-1):
+    d = (C.c_int32 * max(1, len(device_ids)))(*device_ids)
+    wd = (C.c_int32 * max(1, len(worker_dev)))(*worker_dev)
+    od, ow, picked = (C.c_int32 * 32)(), (C.c_int32 * 32)(), C.c_int32(-2)
+    n = host.lib().spu_host_replica_assignments(d, len(device_ids), 1 if per_worker else 0, wd, len(worker_dev), od, ow,
+                                                32, pick_worker, pick_device, C.byref(picked))
+    return n, [(od[i], ow[i]) for i in range(max(n, 0))], picked.value
+
+
+def test_replica_registry_assignments_and_lookup(host):
+    """build_gpu_replica_assignments (inference_runner.cpp:128-183) -> ReplicaRegistry -> fill_model_pointers
+    (inference_task.cpp:469-516) -> select_gpu_module (starpu_setup.cpp:725-778)."""
+    # per_device: one replica per non-negative device id, in configuration order; the codelet finds it by device
+    n, a, picked = _assign(host, [2, 0, -1, 5], False, [], pick_device=5)
+    assert (n, a, picked) == (3, [(2, -1), (0, -1), (5, -1)], 2)
+    # per_worker: one per CUDA worker of every listed device, devices in order, workers in id order
+    worker_dev = [0, 0, 1, 1, 3]  # StarPU worker w runs on device worker_dev[w]
+    n, a, picked = _assign(host, [1, 0], True, worker_dev, pick_worker=1, pick_device=0)
+    assert (n, a) == (4, [(1, 2), (1, 3), (0, 0), (0, 1)]) and picked == 3
+    # a worker that has no replica is an error of the codelet, as in the reference
+    n, a, picked = _assign(host, [1], True, worker_dev, pick_worker=0, pick_device=0)
+    assert n == -1 and "No GPU model replica available for worker 0 on device 0" in host.last_error()
+    # a listed device without a CUDA worker cannot be served per worker
+    n, _, _ = _assign(host, [0, 2], True, worker_dev)
+    assert n == -1 and "No CUDA workers available for device 2" in host.last_error()
+    assert _assign(host, [], False, [])[0] == 0
+
+
 def _gather(host, arrays, elemsize, capacity):
     n = len(arrays)
     srcs = (C.c_void_p * max(1, n))(*[a.ctypes.data for a in arrays])
