@@ -350,12 +350,8 @@ spu_status spu_bert_embed_async(const int64_t *ids, const int64_t *mask,
 spu_status spu_affine_f32_async(const float *in, float *out, uint64_t n,
                                 float scale, float shift, void *stream);
 
-/* Debug (tools/gemm_trace.py): CTA `cta` of every following GEMM launch writes 65 u64
- * %globaltimer stamps of its pipeline to device_buf; NULL switches it off.  Not thread-safe. */
-void spu_debug_gemm_trace(void *device_buf, int32_t cta);
-/* Debug (tools/gemm_rates.py): 0 = normal, 1 = GEMM launches skip their TMA operand loads,
- * 2 = skip their MMAs.  Results are garbage; isolates the MMA rate from the feed rate. */
-void spu_debug_gemm_mode(int32_t mode);
+/* (The GEMM pipeline-trace / debug-mode hooks the measurement tools use are NOT part of this ABI: they exist
+ * only in libraries built with -DSPU_DEBUG_HOOKS and are declared in include/spu_b200_debug.h.) */
 
 /* ---- Misc ------------------------------------------------------------------ */
 const char *spu_last_error(void);       /* thread-local message of the last failure */

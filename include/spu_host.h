@@ -148,6 +148,9 @@ int32_t spu_host_buffer_byte_size(int32_t interface_id, uint32_t nx, uint64_t el
  * returns the chosen index, or -1 on StarPUCodeletException (message in last_error). */
 int32_t spu_host_select_replica(const int32_t *device_ids, int32_t n_device_ids, const int32_t *worker_ids,
                                 int32_t n_worker_ids, int32_t n_models, int32_t worker_id, int32_t device_id);
+/* NvtxRange around the codelet body (starpu_setup.cpp:817; src/utils/nvtx.hpp SetHooks): enable != 0 routes the
+ * ranges to a recorder instead of NVTX, 0 restores NVTX.  Reports the last label pushed and {pushes, pops}. */
+int32_t spu_host_nvtx_capture(int32_t enable, char *last_label, uint64_t cap, int64_t counts[2]);
 /* build_gpu_replica_assignments (inference_runner.cpp:128-183) + ReplicaRegistry::fill_model_pointers
  * (inference_task.cpp:469-516) + select_gpu_module, without a runtime: the CUDA workers are described by
  * worker_dev[w] = device of StarPU worker w.  Writes the assignments (device, worker or -1) and returns their

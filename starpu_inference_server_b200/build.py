@@ -29,6 +29,8 @@ ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 NVCC_FLAGS = ARCH + ["-std=c++17", "-O3", "-lineinfo", "-Xcompiler", "-fPIC",
                      "--expt-relaxed-constexpr",
                      "-I", os.path.join(ROOT, "include")]
+if os.environ.get("SPU_DEBUG_HOOKS") == "1":  # measurement builds only (include/spu_b200_debug.h)
+    NVCC_FLAGS.append("-DSPU_DEBUG_HOOKS=1")
 
 CUDA_SOURCES = ["replica.cu", "gemm_sm100.cu", "attention.cu", "attention_sm100.cu", "rowops.cu", "vit.cu"]
 HOST_SOURCES = ["inference_codelet.cpp", "slot_pools.cpp", "replica_registry.cpp", "task_runner.cpp",

@@ -34,8 +34,6 @@ SYMBOLS = [
     "spu_vit_output_bytes", "spu_bert_stage_chain_ms", "spu_bert_calibrate_fp8", "spu_bert_fp8_scales",
     "spu_gemm_fp8_async", "spu_quantize_e4m3_async", "spu_bert_set_fp8_mask", "spu_bert_get_fp8_mask",
     "spu_gemm_ln_bf16_async",
-    "spu_debug_gemm_trace",
-    "spu_debug_gemm_mode",
 ]
 
 
@@ -100,8 +98,11 @@ def lib():
     L.spu_bert_get_fp8_mask.argtypes = [vp, vp, i32]
     L.spu_gemm_fp8_async.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, i32, f32, f32, vp]
     L.spu_quantize_e4m3_async.argtypes = [vp, vp, u64, f32, vp]
-    L.spu_debug_gemm_trace.argtypes = [vp, i32]
-    L.spu_debug_gemm_mode.argtypes = [i32]
+    if hasattr(L, "spu_debug_gemm_trace"):  # only in SPU_DEBUG_HOOKS builds (include/spu_b200_debug.h)
+        L.spu_debug_gemm_trace.argtypes = [vp, i32]
+        L.spu_debug_gemm_trace.restype = None
+        L.spu_debug_gemm_mode.argtypes = [i32]
+        L.spu_debug_gemm_mode.restype = None
     L.spu_bert_output_bytes.argtypes = [vp, i32, i32]
     L.spu_vit_input_bytes.argtypes = [vp, i32]
     L.spu_vit_output_bytes.argtypes = [vp, i32]
@@ -110,11 +111,18 @@ def lib():
         fn = getattr(L, name)
         if name.endswith("_bytes"):
             fn.restype = u64
-        elif name in ("spu_debug_gemm_trace", "spu_debug_gemm_mode"):
-            fn.restype = None
         elif name not in ("spu_last_error",):
             fn.restype = i32
     _lib = L
+    return L
+
+
+def debug_hooks():
+    """The measurement hooks of include/spu_b200_debug.h; raises unless the library was built with them."""
+    L = lib()
+    if not hasattr(L, "spu_debug_gemm_trace"):
+        raise RuntimeError("libspu_b200.so was built without -DSPU_DEBUG_HOOKS: rebuild with "
+                           "`SPU_DEBUG_HOOKS=1 python -m starpu_inference_server_b200.build --force`")
     return L
 
 

@@ -5,8 +5,11 @@
 #include <algorithm>
 #include <cstring>
 #include <map>
+#include <mutex>
+#include <string>
 
 #include "../../include/spu_host.h"
+#include "nvtx_range.hpp"
 #include "task_runner.hpp"
 
 using namespace starpu_server;
@@ -78,6 +81,33 @@ int32_t spu_host_select_replica(const int32_t *device_ids, int32_t n_device_ids,
     fail(e);
     return -1;
   }
+}
+
+namespace {
+std::mutex g_nvtx_mu;
+std::string g_nvtx_last;
+int64_t g_nvtx_pushes = 0, g_nvtx_pops = 0;
+void nvtx_capture_push(const char *label) {
+  std::lock_guard<std::mutex> lk(g_nvtx_mu);
+  g_nvtx_last = label ? label : "";
+  ++g_nvtx_pushes;
+}
+void nvtx_capture_pop() {
+  std::lock_guard<std::mutex> lk(g_nvtx_mu);
+  ++g_nvtx_pops;
+}
+}  // namespace
+
+int32_t spu_host_nvtx_capture(int32_t enable, char *last_label, uint64_t cap, int64_t counts[2]) {
+  if (enable) NvtxRange::SetHooks(&nvtx_capture_push, &nvtx_capture_pop);
+  else NvtxRange::ResetHooks();
+  std::lock_guard<std::mutex> lk(g_nvtx_mu);
+  if (last_label && cap) std::snprintf(last_label, cap, "%s", g_nvtx_last.c_str());
+  if (counts) {
+    counts[0] = g_nvtx_pushes;
+    counts[1] = g_nvtx_pops;
+  }
+  return 0;
 }
 
 int32_t spu_host_replica_assignments(const int32_t *device_ids, int32_t n_device_ids, int32_t per_worker,

@@ -3,6 +3,8 @@
 // :807-846 (cuda_inference_func) -- restated without LibTorch on top of include/spu_b200.h.
 #include "inference_codelet.hpp"
 
+#include "nvtx_range.hpp"
+
 #include <cuda_runtime.h>
 
 #include <algorithm>
@@ -223,6 +225,10 @@ void run_codelet_inference(InferenceParams *params, StarpuBufferSpan buffers, in
   } guard{worker_id};
   set_gauge(worker_id, 1);
 
+  if (params->verbosity >= VerbosityLevel::Trace)  // log_trace (starpu_setup.cpp:685-692)
+    std::fprintf(stderr, "[TRACE] %s device id %d, worker id %d, job id %d\n",
+                 executed_on_type == DeviceType::CPU ? "CPU" : "GPU", device_id, worker_id, params->request_id);
+
   if (params->device.set_executed_on) params->device.set_executed_on(executed_on_type);
   else if (params->device.executed_on) *params->device.executed_on = executed_on_type;
   if (params->device.set_worker_id) params->device.set_worker_id(worker_id);
@@ -249,6 +255,9 @@ void InferenceCodelet::cuda_inference_func(void **buffers, void *cl_arg) {
   const StarpuBufferSpan span(typed, total_buffers);
   const int worker_id = ctx_worker_id();
   const int device_id = ctx_worker_devid(worker_id);
+  char label[64];
+  std::snprintf(label, sizeof(label), "codelet.cuda job %d dev %d", params->request_id, device_id);
+  const NvtxRange nvtx_scope(label);  // starpu_setup.cpp:817
   void *stream = ctx_stream();
   DeviceModel *model = select_gpu_module(*params, worker_id, device_id);
   // every kernel goes on StarPU's local stream and the function returns without

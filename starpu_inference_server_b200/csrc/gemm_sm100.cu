@@ -24,6 +24,7 @@
 // FFN projections of HF BertModel (oracle/bert_oracle.py).
 #include "gemm_sm100.cuh"
 
+#include <atomic>
 #include <cstdlib>
 #include <mutex>
 
@@ -930,17 +931,27 @@ spu_status launch_bn(const GemmPlan &plan, int block_n, const LaunchMaps &maps, 
 
 constexpr int kBlockNCands[4] = {256, 192, 128, 64};
 
-unsigned long long *g_trace_buf = nullptr;  // debug only, see KernelArgs::trace
-int g_trace_cta = 0;
-int g_dbg_mode = 0;
+#ifdef SPU_DEBUG_HOOKS
+// Measurement builds only (include/spu_b200_debug.h): process-wide switches every launch reads.
+std::atomic<unsigned long long *> g_trace_buf{nullptr};  // see KernelArgs::trace
+std::atomic<int> g_trace_cta{0};
+std::atomic<int> g_dbg_mode{0};
+#else
+// Product build: the hooks do not exist; the kernel's trace / debug branches are fed constants.
+constexpr unsigned long long *g_trace_buf = nullptr;
+constexpr int g_trace_cta = 0;
+constexpr int g_dbg_mode = 0;
+#endif
 
 }  // namespace
 
+#ifdef SPU_DEBUG_HOOKS
 void gemm_set_trace(unsigned long long *device_buf, int cta) {
   g_trace_buf = device_buf;
   g_trace_cta = cta;
 }
 void gemm_set_debug_mode(int mode) { g_dbg_mode = mode; }
+#endif
 
 // LayerNorm-fused epilogue: the widest column block whose count per row stays within the cluster.
 static GemmConfig choose_ln_config(int M, int N) {
@@ -1083,7 +1094,8 @@ spu_status gemm_launch(const GemmPlan &plan, int M, const GemmEpilogueArgs &args
     }
     maps.out2 = maps.out;
   }
-  KernelArgs a{M, plan.N, plan.K, args.bias, args.acc_scale, args.out_inv_scale, g_trace_buf, g_trace_cta, g_dbg_mode,
+  KernelArgs a{M, plan.N, plan.K, args.bias, args.acc_scale, args.out_inv_scale,
+               static_cast<unsigned long long *>(g_trace_buf), static_cast<int>(g_trace_cta), static_cast<int>(g_dbg_mode),
                args.gamma, args.beta, args.ln_eps, args.out != nullptr ? 1 : 0,
                args.out2 == nullptr ? 0 : (args.out2_e4m3 ? 2 : 1)};
   // residual == output: accumulate in place with a TMA reduce-add instead of load + add + store

@@ -793,11 +793,13 @@ extern "C" spu_status spu_attention_cfg_async(const void *qkv, const float *mask
   return attention_launch(qkv, mask_bias, ctx, batch, seq, heads, as_stream(stream), out_e4m3 != 0, q_inv_scale);
 }
 
+#ifdef SPU_DEBUG_HOOKS  // include/spu_b200_debug.h: measurement builds only
 extern "C" void spu_debug_gemm_trace(void *device_buf, int32_t cta) {
   gemm_set_trace(static_cast<unsigned long long *>(device_buf), cta);
 }
 
 extern "C" void spu_debug_gemm_mode(int32_t mode) { gemm_set_debug_mode(mode); }
+#endif
 
 extern "C" const char *spu_last_error(void) { return g_last_error.c_str(); }
 extern "C" int32_t spu_abi_version(void) { return SPU_ABI_VERSION; }

@@ -23,7 +23,7 @@ SYMBOLS = [
     "spu_server_wait_all", "spu_server_stats", "spu_host_last_error", "spu_host_codelet_fields",
     "spu_host_buffer_byte_size", "spu_host_select_replica", "spu_host_gather_to_slot", "spu_host_slice_rows",
     "spu_host_can_merge", "spu_host_call_cuda_func_affine", "spu_host_can_merge_varlen", "spu_host_gather_padded",
-    "spu_host_replica_assignments",
+    "spu_host_replica_assignments", "spu_host_nvtx_capture",
 ]
 
 
@@ -86,6 +86,8 @@ def lib():
     L.spu_host_buffer_byte_size.restype = i32
     L.spu_host_select_replica.argtypes = [C.POINTER(i32), i32, C.POINTER(i32), i32, i32, i32, i32]
     L.spu_host_select_replica.restype = i32
+    L.spu_host_nvtx_capture.argtypes = [i32, C.c_char_p, u64, C.POINTER(i64)]
+    L.spu_host_nvtx_capture.restype = i32
     L.spu_host_replica_assignments.argtypes = [C.POINTER(i32), i32, i32, C.POINTER(i32), i32, C.POINTER(i32),
                                                C.POINTER(i32), i32, i32, i32, C.POINTER(i32)]
     L.spu_host_replica_assignments.restype = i32

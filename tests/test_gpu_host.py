@@ -32,9 +32,15 @@ def test_cuda_func_copies_results_to_device_buffer(host, vector_iface):
     y = torch.zeros(3, device="cuda")
     s = torch.cuda.Stream()
     rec = (C.c_int64 * 6)()
+    label, counts = C.create_string_buffer(96), (C.c_int64 * 2)()
+    host.lib().spu_host_nvtx_capture(1, label, 96, counts)
+    before = list(counts)
     rc = host.lib().spu_host_call_cuda_func_affine(x.data_ptr(), y.data_ptr(), 3, 1.0, 1.5, 0, 77, s.cuda_stream, 1,
                                                    vector_iface, rec)
+    host.lib().spu_host_nvtx_capture(0, label, 96, counts)  # back to the real NVTX calls
     assert rc == 0, host.last_error()
+    # one NVTX range around the codelet body, named like the reference's (starpu_setup.cpp:817)
+    assert label.value == b"codelet.cuda job 0 dev 0" and [counts[0] - before[0], counts[1] - before[1]] == [1, 1]
     s.synchronize()
     assert y.cpu().tolist() == [2.5, 3.5, 4.5]
     device_id, worker_id, executed_on, start_set, end_set, gauge = list(rec)

@@ -25,7 +25,7 @@ def main():
     ap.add_argument("--cfgs", default="1:256,2:256,1:192,1:128,2:128")
     ap.add_argument("--stages", default="0", help="comma list of ring-stage limits (0 = all that fit)")
     args = ap.parse_args()
-    L = capi.lib()
+    L = capi.debug_hooks()  # SPU_DEBUG_HOOKS build only
     for name in args.shapes.split(","):
         N, K, epi = SHAPES[name]
         for cfg in args.cfgs.split(","):

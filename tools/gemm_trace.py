@@ -18,7 +18,7 @@ TILE = int(sys.argv[1]) if len(sys.argv) > 1 else 0  # local tile whose epilogue
 
 
 def main():
-    L = capi.lib()
+    L = capi.debug_hooks()  # SPU_DEBUG_HOOKS build only
     M = int(os.environ.get("TRACE_M", 4096))
     for name, (N, K, epi) in SHAPES.items():
         for cg, bn in ((2, 256 if N != 768 else 192),):
