@@ -27,7 +27,7 @@ NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 NVCC_FLAGS = ARCH + ["-std=c++17", "-O3", "-lineinfo", "-Xcompiler", "-fPIC",
-                     "--expt-relaxed-constexpr",
+                     "--expt-relaxed-constexpr", "-split-compile=0",
                      "-I", os.path.join(ROOT, "include")]
 if os.environ.get("SPU_DEBUG_HOOKS") == "1":  # measurement builds only (include/spu_b200_debug.h)
     NVCC_FLAGS.append("-DSPU_DEBUG_HOOKS=1")

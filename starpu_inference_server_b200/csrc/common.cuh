@@ -70,7 +70,10 @@ inline cudaError_t ensure_dynamic_smem(int bytes) {
   cudaGetDevice(&dev);
   const unsigned long long bit = 1ull << (dev & 63);
   if (__atomic_load_n(&done, __ATOMIC_ACQUIRE) & bit) return cudaSuccess;
-  const cudaError_t e = cudaFuncSetAttribute(Kern, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  cudaError_t e = cudaFuncSetAttribute(Kern, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  // largest shared-memory carve-out: kernels sized for two CTAs per SM must not be cut to one by a smaller split
+  if (e == cudaSuccess)
+    e = cudaFuncSetAttribute(Kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
   if (e == cudaSuccess) __atomic_fetch_or(&done, bit, __ATOMIC_RELEASE);
   return e;
 }

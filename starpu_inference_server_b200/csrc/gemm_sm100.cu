@@ -36,10 +36,22 @@ constexpr int kRowsPerCta = 128;
 constexpr int kTileKBytes = 128;  // one SWIZZLE_128B row: 64 bf16 or 128 e4m3
 constexpr int kUmmaKBytes = 32;   // K=16 bf16 / K=32 e4m3 per tcgen05.mma
 constexpr int kEpiWarp0 = 4;
-constexpr int kNumEpiWarps = 8;
-constexpr int kThreads = (kEpiWarp0 + kNumEpiWarps) * 32;  // 384
+constexpr int kMaxEpiWarps = 8;
 constexpr int kABytes = kRowsPerCta * kTileKBytes;          // 16 KiB
-constexpr int kSmemMax = 227 * 1024;
+
+// Footprint of one CTA.  HF = 0: the whole SM (227 KB of shared memory, all 512 TMEM columns, 8 epilogue
+// warps).  HF = 1 ("half footprint"): at most half of everything (113 KB, 256 TMEM columns, 4 epilogue
+// warps, <= 128 registers x 256 threads), so that TWO CTAs are resident per SM -- the second one is a CTA of
+// the kernel the other CUDA worker's stream runs (or this stream's next kernel under programmatic dependent
+// launch): its main loop keeps the tensor pipe busy through this CTA's pipeline fill, epilogue and store drain.
+template <int HF>
+struct Foot {
+  static constexpr int kNumEpiWarps = HF ? 4 : 8;
+  static constexpr int kThreads = (kEpiWarp0 + kNumEpiWarps) * 32;  // 256 | 384
+  static constexpr int kSmemMax = HF ? 113 * 1024 : 227 * 1024;
+  static constexpr int kTmemBudget = HF ? 256 : 512;
+  static constexpr int kMinCtas = HF ? 2 : 1;
+};
 constexpr int kBarrierBytes = 512;
 constexpr int kMaxStages = 8;
 
@@ -53,8 +65,10 @@ struct EpiTraits {
       (EPI == kEpiBiasResid || EPI == kEpiBiasAccum || EPI == kEpiBiasResidLN) ? 4
                                                                                : (EPI == kEpiBiasGeluE4m3 ? 1 : 2);
   static constexpr int kChunkBytes = 32 * 32 * kElemBytes;
-  // double-buffered per warp; the LayerNorm epilogue adds two slots for its second (bf16 / e4m3) output
-  static constexpr int kWarpBytes = 2 * kChunkBytes + (EPI == kEpiBiasResidLN ? 2 * kLnChunk2Bytes : 0);
+  // kSlots staging slots per warp (2 = double-buffered); the LayerNorm epilogue adds two slots for its second
+  // (bf16 / e4m3) output
+  template <int kSlots>
+  static constexpr int warp_bytes() { return kSlots * kChunkBytes + (EPI == kEpiBiasResidLN ? 2 * kLnChunk2Bytes : 0); }
   // LayerNorm epilogue: per-row (mean, M2) contributions of every column half of every column block,
   // double-buffered across tiles: [2][2 * kLnMaxNBlocks][128 rows] float2
   static constexpr int kLnStatsOnly = 2 * 2 * kLnMaxNBlocks * kRowsPerCta * 8;
@@ -63,23 +77,35 @@ struct EpiTraits {
   static constexpr int kStatsBytes = EPI == kEpiBiasResidLN ? kLnStatsOnly + kLnVecBytes : 0;
 };
 
-template <int BLOCK_N, int CG, int EPI>
+template <int BLOCK_N, int CG, int EPI, int HF = 0>
 struct TileCfg {
+  using F = Foot<HF>;
+  static constexpr int kNumEpiWarps = F::kNumEpiWarps;
+  static constexpr int kColSplit = kNumEpiWarps / 4;  // epilogue warps sharing one TMEM lane quarter split the columns
   static constexpr int kBRows = BLOCK_N / CG;  // B rows staged by one CTA
   static constexpr int kBBytes = kBRows * kTileKBytes;
   static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kStagingBytes = kNumEpiWarps * EpiTraits<EPI>::kWarpBytes;
   static constexpr int kStatsBytes = EpiTraits<EPI>::kStatsBytes;
-  static constexpr int kStagesRaw = (kSmemMax - 1024 - kStagingBytes - kStatsBytes - kBarrierBytes) / kStageBytes;
+  template <int kS>
+  static constexpr int stages_with() {
+    return (F::kSmemMax - 1024 - kNumEpiWarps * EpiTraits<EPI>::template warp_bytes<kS>() - kStatsBytes - kBarrierBytes) /
+           kStageBytes;
+  }
+  // operand-ring depth comes first: a half-footprint CTA gives up the second staging slot when that buys a stage
+  static constexpr int kSlots = (HF && stages_with<1>() > stages_with<2>() && stages_with<2>() < kMaxStages) ? 1 : 2;
+  static constexpr int kWarpBytes = EpiTraits<EPI>::template warp_bytes<kSlots>();
+  static constexpr int kStagingBytes = kNumEpiWarps * kWarpBytes;
+  static constexpr int kStagesRaw = stages_with<kSlots>();
   static constexpr int kStages = kStagesRaw > kMaxStages ? kMaxStages : kStagesRaw;
-  static constexpr int kTmemCols = (2 * BLOCK_N <= 32)    ? 32
-                                   : (2 * BLOCK_N <= 64)  ? 64
-                                   : (2 * BLOCK_N <= 128) ? 128
-                                   : (2 * BLOCK_N <= 256) ? 256
-                                                          : 512;
+  // two accumulator buffers (the epilogue of tile i overlaps the main loop of tile i+1) when the TMEM budget allows
+  static constexpr int kAccBufs = 2 * BLOCK_N <= F::kTmemBudget ? 2 : 1;
+  static constexpr int kAccCols = kAccBufs * BLOCK_N;
+  static constexpr int kTmemCols = kAccCols <= 32 ? 32 : kAccCols <= 64 ? 64 : kAccCols <= 128 ? 128 : kAccCols <= 256 ? 256 : 512;
   static constexpr int kSmemBytes = 1024 + kStages * kStageBytes + kStagingBytes + kStatsBytes + kBarrierBytes;
-  static_assert(kStages >= 3, "pipeline too shallow");
-  static_assert((BLOCK_N / 2) % 32 == 0, "each epilogue warp half must be whole 32-column chunks");
+  // does the tile fit the footprint with a ring deep enough to cover the TMA latency?
+  static constexpr bool kFits = kStages >= 3 && kTmemCols <= F::kTmemBudget && kSmemBytes <= F::kSmemMax;
+  static_assert((BLOCK_N / kColSplit) % 32 == 0, "each epilogue warp must own whole 32-column chunks");
+  static_assert(!(HF && EPI == kEpiBiasResidLN), "the LayerNorm-fused epilogue is a full-footprint kernel");
 };
 
 struct KernelArgs {
@@ -125,21 +151,26 @@ __device__ __forceinline__ uint32_t pack_e4m3x4(float a, float b, float c, float
   return static_cast<uint32_t>(lo) | (static_cast<uint32_t>(hi) << 16);
 }
 
-template <int BLOCK_N, int CG, int EPI, int IN_FP8>
-__global__ void __launch_bounds__(kThreads, 1)
+template <int BLOCK_N, int CG, int EPI, int IN_FP8, int HF>
+__global__ void __launch_bounds__(Foot<HF>::kThreads, Foot<HF>::kMinCtas)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
                     const __grid_constant__ CUtensorMap tmap_b,
                     const __grid_constant__ CUtensorMap tmap_out,
                     const __grid_constant__ CUtensorMap tmap_resid,
                     const __grid_constant__ CUtensorMap tmap_out2, const KernelArgs args) {
-  using Cfg = TileCfg<BLOCK_N, CG, EPI>;
+  using Cfg = TileCfg<BLOCK_N, CG, EPI, HF>;
   using Epi = EpiTraits<EPI>;
+  static_assert(Cfg::kFits, "tile exceeds the CTA footprint or leaves too shallow a pipeline");
+  constexpr int kNumEpiWarps = Cfg::kNumEpiWarps;
+  constexpr int kSlots = Cfg::kSlots;
+  constexpr int kAccBufs = Cfg::kAccBufs;
   constexpr int kStages = Cfg::kStages;
   constexpr int kStageBytes = Cfg::kStageBytes;
   constexpr uint32_t kIdesc = make_idesc(IN_FP8 ? 0u : 1u, kRowsPerCta * CG, BLOCK_N);
   constexpr int kElemsPerKBlock = IN_FP8 ? 128 : 64;
   constexpr int kTileM = kRowsPerCta * CG;
-  constexpr int kChunksPerWarp = BLOCK_N / 2 / 32;
+  constexpr int kColsPerWarp = BLOCK_N / Cfg::kColSplit;
+  constexpr int kChunksPerWarp = kColsPerWarp / 32;
   // LayerNorm-fused epilogue: the CG * (N / BLOCK_N) CTAs holding one row block's columns form a cluster
   constexpr bool kLN = EPI == kEpiBiasResidLN;
   constexpr bool kClustered = CG == 2 || kLN;
@@ -154,8 +185,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
   uint64_t *empty_bar = full_bar + kMaxStages;
   uint64_t *tmem_full_bar = empty_bar + kMaxStages;
   uint64_t *tmem_empty_bar = tmem_full_bar + 2;
-  uint64_t *resid_bar = tmem_empty_bar + 2;  // [kNumEpiWarps][2]
-  uint64_t *stats_bar = resid_bar + 2 * kNumEpiWarps;  // [2], LayerNorm epilogue only
+  uint64_t *resid_bar = tmem_empty_bar + 2;  // [kMaxEpiWarps][2]
+  uint64_t *stats_bar = resid_bar + 2 * kMaxEpiWarps;  // [2], LayerNorm epilogue only
   uint32_t *tmem_ptr_smem = reinterpret_cast<uint32_t *>(stats_bar + 2);
 
   // warp-uniform by construction AND provably so for the compiler (shuffle from lane 0)
@@ -306,8 +337,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
       int local_tile = 0;
       const int dbg = dbg_mode;
       for (int tile = unit; tile < num_tiles; tile += num_units, ++local_tile) {
-        const int acc = local_tile & 1;
-        const uint32_t acc_phase = (local_tile >> 1) & 1u;
+        const int acc = local_tile % kAccBufs;
+        const uint32_t acc_phase = (local_tile / kAccBufs) & 1u;
         mbar_wait_warp(&tmem_empty_bar[acc], acc_phase ^ 1u);
         tcgen05_fence_after();
         const uint32_t tmem_d = tmem_base + static_cast<uint32_t>(acc * BLOCK_N);
@@ -366,7 +397,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
       const int e = warp_idx - kEpiWarp0;
       const int q = warp_idx & 3;
       const int half = e >> 2;
-      uint8_t *wstage = staging + e * Epi::kWarpBytes;  // [2][4096] fp32 slots, then [2][2048] second-output slots
+      uint8_t *wstage = staging + e * Cfg::kWarpBytes;  // [2][4096] fp32 slots, then [2][2048] second-output slots
       const uint32_t stg = smem_u32(wstage);
       const uint32_t stg2 = stg + 2 * Epi::kChunkBytes;
       uint64_t *my_resid_bar = resid_bar + 2 * e;
@@ -407,7 +438,6 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
           mbar_arrive_expect_tx(&stats_bar[buf], static_cast<uint32_t>(n_contrib * kRowsPerCta * 8));
         if (lane == 0) {
           tma_store_wait_read<0>();  // the previous tile's stores have read the staging slots
-#pragma unroll
           mbar_arrive_expect_tx(&my_resid_bar[0], kChunks * Epi::kChunkBytes);
 #pragma unroll
           for (int c = 0; c < kChunks; ++c)
@@ -563,18 +593,18 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
     pdl_wait_prior_grid();
     const int e = warp_idx - kEpiWarp0;
     const int q = warp_idx & 3;  // TMEM lane quarter this warp may read
-    const int half = e >> 2;     // which half of the tile's columns
-    const uint32_t stg = smem_u32(staging + e * Epi::kWarpBytes);
+    const int half = e >> 2;     // which part of the tile's columns (8 epilogue warps: halves; 4: all of them)
+    const uint32_t stg = smem_u32(staging + e * Cfg::kWarpBytes);
     uint64_t *my_resid_bar = resid_bar + 2 * e;
     uint32_t chunk_ctr = 0;      // live chunks this warp has staged so far (selects slot + parity)
     int local_tile = 0;
     for (int tile = unit; tile < num_tiles; tile += num_units, ++local_tile) {
       const int m_blk = tile / n_blocks;
       const int n_blk = tile % n_blocks;
-      const int acc = local_tile & 1;
-      const uint32_t acc_phase = (local_tile >> 1) & 1u;
+      const int acc = local_tile % kAccBufs;
+      const uint32_t acc_phase = (local_tile / kAccBufs) & 1u;
       const int row0 = m_blk * kTileM + static_cast<int>(cta_rank) * kRowsPerCta + q * 32;
-      const int colw = n_blk * BLOCK_N + half * (BLOCK_N / 2);  // first column of this warp
+      const int colw = n_blk * BLOCK_N + half * kColsPerWarp;  // first column of this warp
       const bool slab_live = row0 < args.M;  // TMA clips partial slabs; dead ones are skipped
       // Bias: warp-uniform 128-bit loads (one broadcast each).  Chunk c+1's bias is requested
       // into the same registers right after chunk c's FMAs consumed them, so its L2 latency
@@ -592,14 +622,14 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
       float4 bv[8];
       load_bias(bv, colw);  // chunk 0, while the main loop still runs
       if constexpr (EPI == kEpiBiasResid) {
-        // Residual chunks 0 and 1 of this tile: fetched while the main loop still runs.
+        // The first residual chunks of this tile (one per staging slot): fetched while the main loop still runs.
         if (lane == 0 && slab_live) {
-          tma_store_wait_read<0>();  // both staging slots are free again
+          tma_store_wait_read<0>();  // every staging slot is free again
 #pragma unroll
-          for (int c = 0; c < (kChunksPerWarp < 2 ? kChunksPerWarp : 2); ++c) {
-            const uint32_t b = (chunk_ctr + c) & 1u;
+          for (int c = 0; c < (kChunksPerWarp < kSlots ? kChunksPerWarp : kSlots); ++c) {
+            const uint32_t b = (chunk_ctr + c) % kSlots;
             mbar_arrive_expect_tx(&my_resid_bar[b], Epi::kChunkBytes);
-            tma_load_2d(staging + e * Epi::kWarpBytes + b * Epi::kChunkBytes, &tmap_resid,
+            tma_load_2d(staging + e * Cfg::kWarpBytes + b * Epi::kChunkBytes, &tmap_resid,
                         &my_resid_bar[b], colw + c * 32, row0);
           }
         }
@@ -609,7 +639,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
       tcgen05_fence_after();
       if (tracing && local_tile == kTraceTile && e == 0 && lane == 0) args.trace[62] = global_timer_ns();
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) +
-                             static_cast<uint32_t>(acc * BLOCK_N + half * (BLOCK_N / 2));
+                             static_cast<uint32_t>(acc * BLOCK_N + half * kColsPerWarp);
       // TMEM -> registers is software-pipelined: chunk c+1's tcgen05.ld is in flight while
       // chunk c is converted, staged and stored (fully unrolled: the two register sets are
       // named statically).
@@ -619,14 +649,14 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
       for (int c = 0; c < kChunksPerWarp; ++c) {
         uint32_t(&v)[32] = vv[c & 1];
         const int col0 = colw + c * 32;
-        const uint32_t b = chunk_ctr & 1u;
+        const uint32_t b = chunk_ctr % kSlots;
         const uint32_t sbuf = stg + b * Epi::kChunkBytes;
         const bool tr_chunk = tracing && local_tile == kTraceTile && e == 0 && lane == 0 && c < 4;
         if (tr_chunk) args.trace[66 + 8 * c] = global_timer_ns();
         if (tr_chunk) args.trace[67 + 8 * c] = global_timer_ns();
         if constexpr (EPI != kEpiBiasResid) {
-          // the store issued from this slot two chunks ago must have drained it
-          if (lane == 0) tma_store_wait_read<1>();
+          // the store issued from this slot kSlots chunks ago must have drained it
+          if (lane == 0) tma_store_wait_read<kSlots - 1>();
           __syncwarp();
         }
         if (tr_chunk) args.trace[68 + 8 * c] = global_timer_ns();
@@ -659,7 +689,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
           }
           if constexpr (EPI == kEpiBiasResid) {
             // 32 rows x 128 B, SWIZZLE_128B: 16-byte chunk j of row r sits at j ^ (r & 7)
-            mbar_wait(&my_resid_bar[b], (chunk_ctr >> 1) & 1u);
+            mbar_wait(&my_resid_bar[b], (chunk_ctr / kSlots) & 1u);
             const uint32_t rowa = sbuf + static_cast<uint32_t>(lane) * 128u;
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
@@ -707,23 +737,23 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_a,
           if (tr_chunk) args.trace[71 + 8 * c] = global_timer_ns();
           if (lane == 0) {
             if constexpr (EPI == kEpiBiasAccum)
-              tma_reduce_add_2d(&tmap_out, staging + e * Epi::kWarpBytes + b * Epi::kChunkBytes, col0, row0);
+              tma_reduce_add_2d(&tmap_out, staging + e * Cfg::kWarpBytes + b * Epi::kChunkBytes, col0, row0);
             else
-              tma_store_2d(&tmap_out, staging + e * Epi::kWarpBytes + b * Epi::kChunkBytes, col0, row0);
+              tma_store_2d(&tmap_out, staging + e * Cfg::kWarpBytes + b * Epi::kChunkBytes, col0, row0);
             tma_store_commit();
             if constexpr (EPI == kEpiBiasResid) {
-              if (c + 2 < kChunksPerWarp) {
-                // refill this slot with the residual chunk two ahead once the store has read it
+              if (c + kSlots < kChunksPerWarp) {
+                // refill this slot with the residual chunk kSlots ahead once the store has read it
                 tma_store_wait_read<0>();
                 mbar_arrive_expect_tx(&my_resid_bar[b], Epi::kChunkBytes);
-                tma_load_2d(staging + e * Epi::kWarpBytes + b * Epi::kChunkBytes, &tmap_resid,
-                            &my_resid_bar[b], col0 + 64, row0);
+                tma_load_2d(staging + e * Cfg::kWarpBytes + b * Epi::kChunkBytes, &tmap_resid,
+                            &my_resid_bar[b], col0 + 32 * kSlots, row0);
               }
             }
           }
           __syncwarp();
           if (tr_chunk) args.trace[72 + 8 * c] = global_timer_ns();
-          ++chunk_ctr;  // counts live chunks only: slot = ctr & 1, residual-barrier parity = ctr >> 1
+          ++chunk_ctr;  // counts live chunks only: slot = ctr % kSlots, residual-barrier parity = ctr / kSlots
         }
       }
       if (tracing && local_tile == kTraceTile && e == 0 && lane == 0) args.trace[63] = global_timer_ns();
@@ -814,12 +844,16 @@ struct LaunchMaps {
   CUtensorMap a, out, resid, out2;
 };
 
-template <int BLOCK_N, int CG, int EPI, int IN_FP8>
+template <int BLOCK_N, int CG, int EPI, int IN_FP8, int HF = 0>
 spu_status launch_cfg(const GemmPlan &plan, const LaunchMaps &maps, const KernelArgs &a,
                       cudaStream_t stream) {
-  using Cfg = TileCfg<BLOCK_N, CG, EPI>;
-  auto kern = gemm_tcgen05_kernel<BLOCK_N, CG, EPI, IN_FP8>;
-  SPU_CUDA_TRY((ensure_dynamic_smem<gemm_tcgen05_kernel<BLOCK_N, CG, EPI, IN_FP8>>(Cfg::kSmemBytes)));
+  using Cfg = TileCfg<BLOCK_N, CG, EPI, HF>;
+  if constexpr (!Cfg::kFits) {
+    set_error("gemm: this tile / epilogue does not fit the requested CTA footprint");
+    return SPU_ERR_UNSUPPORTED;
+  } else {
+  auto kern = gemm_tcgen05_kernel<BLOCK_N, CG, EPI, IN_FP8, HF>;
+  SPU_CUDA_TRY((ensure_dynamic_smem<gemm_tcgen05_kernel<BLOCK_N, CG, EPI, IN_FP8, HF>>(Cfg::kSmemBytes)));
   constexpr bool kLN = EPI == kEpiBiasResidLN;
   const int n_blocks = plan.N / BLOCK_N;
   const int m_blocks = (a.M + kRowsPerCta * CG - 1) / (kRowsPerCta * CG);
@@ -827,7 +861,7 @@ spu_status launch_cfg(const GemmPlan &plan, const LaunchMaps &maps, const Kernel
   int dev = 0;
   cudaGetDevice(&dev);
   cudaLaunchConfig_t cfg{};
-  cfg.blockDim = dim3(kThreads, 1, 1);
+  cfg.blockDim = dim3(Foot<HF>::kThreads, 1, 1);
   cfg.dynamicSmemBytes = Cfg::kSmemBytes;
   cfg.stream = stream;
   cudaLaunchAttribute attrs[2];
@@ -880,39 +914,40 @@ spu_status launch_cfg(const GemmPlan &plan, const LaunchMaps &maps, const Kernel
   SPU_CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, maps.a, plan.tmap_b[BLOCK_N / CG / 32 - 1], maps.out,
                                   maps.resid, maps.out2, a));
   return SPU_OK;
+  }
 }
 
-template <int BLOCK_N, int CG>
+template <int BLOCK_N, int CG, int HF = 0>
 spu_status launch_epi(const GemmPlan &plan, const LaunchMaps &maps, const KernelArgs &a,
                       cudaStream_t stream, bool inplace) {
   if (plan.epilogue == kEpiBiasResidLN) {
     // BLOCK_N / 2 values of a row live in registers per thread; a lone CTA stages all of B (3 stages need <= 128)
-    if constexpr (BLOCK_N <= 192 && (CG == 2 || BLOCK_N <= 128)) {
+    if constexpr (HF == 0 && BLOCK_N <= 192 && (CG == 2 || BLOCK_N <= 128)) {
       return plan.in == GemmIn::FP8_E4M3 ? launch_cfg<BLOCK_N, CG, kEpiBiasResidLN, 1>(plan, maps, a, stream)
                                          : launch_cfg<BLOCK_N, CG, kEpiBiasResidLN, 0>(plan, maps, a, stream);
     } else {
-      set_error("gemm: the LayerNorm-fused epilogue needs BLOCK_N <= 192 (<= 128 without a CTA pair)");
+      set_error("gemm: the LayerNorm-fused epilogue needs BLOCK_N <= 192 (<= 128 without a CTA pair), full footprint");
       return SPU_ERR_UNSUPPORTED;
     }
   }
   if (plan.in == GemmIn::FP8_E4M3) {
     switch (plan.epilogue) {
-      case kEpiBias: return launch_cfg<BLOCK_N, CG, kEpiBias, 1>(plan, maps, a, stream);
+      case kEpiBias: return launch_cfg<BLOCK_N, CG, kEpiBias, 1, HF>(plan, maps, a, stream);
       case kEpiBiasResid:
-        return inplace ? launch_cfg<BLOCK_N, CG, kEpiBiasAccum, 1>(plan, maps, a, stream)
-                       : launch_cfg<BLOCK_N, CG, kEpiBiasResid, 1>(plan, maps, a, stream);
-      case kEpiBiasGeluE4m3: return launch_cfg<BLOCK_N, CG, kEpiBiasGeluE4m3, 1>(plan, maps, a, stream);
-      case kEpiBiasGelu: return launch_cfg<BLOCK_N, CG, kEpiBiasGelu, 1>(plan, maps, a, stream);
+        return inplace ? launch_cfg<BLOCK_N, CG, kEpiBiasAccum, 1, HF>(plan, maps, a, stream)
+                       : launch_cfg<BLOCK_N, CG, kEpiBiasResid, 1, HF>(plan, maps, a, stream);
+      case kEpiBiasGeluE4m3: return launch_cfg<BLOCK_N, CG, kEpiBiasGeluE4m3, 1, HF>(plan, maps, a, stream);
+      case kEpiBiasGelu: return launch_cfg<BLOCK_N, CG, kEpiBiasGelu, 1, HF>(plan, maps, a, stream);
       default: set_error("fp8 gemm: unsupported epilogue"); return SPU_ERR_INVALID;
     }
   }
   switch (plan.epilogue) {
-    case kEpiBias: return launch_cfg<BLOCK_N, CG, kEpiBias, 0>(plan, maps, a, stream);
-    case kEpiBiasGelu: return launch_cfg<BLOCK_N, CG, kEpiBiasGelu, 0>(plan, maps, a, stream);
-    case kEpiBiasGeluE4m3: return launch_cfg<BLOCK_N, CG, kEpiBiasGeluE4m3, 0>(plan, maps, a, stream);
+    case kEpiBias: return launch_cfg<BLOCK_N, CG, kEpiBias, 0, HF>(plan, maps, a, stream);
+    case kEpiBiasGelu: return launch_cfg<BLOCK_N, CG, kEpiBiasGelu, 0, HF>(plan, maps, a, stream);
+    case kEpiBiasGeluE4m3: return launch_cfg<BLOCK_N, CG, kEpiBiasGeluE4m3, 0, HF>(plan, maps, a, stream);
     case kEpiBiasResid:
-      return inplace ? launch_cfg<BLOCK_N, CG, kEpiBiasAccum, 0>(plan, maps, a, stream)
-                     : launch_cfg<BLOCK_N, CG, kEpiBiasResid, 0>(plan, maps, a, stream);
+      return inplace ? launch_cfg<BLOCK_N, CG, kEpiBiasAccum, 0, HF>(plan, maps, a, stream)
+                     : launch_cfg<BLOCK_N, CG, kEpiBiasResid, 0, HF>(plan, maps, a, stream);
     default: set_error("bf16 gemm: unsupported epilogue"); return SPU_ERR_INVALID;
   }
 }
@@ -926,6 +961,17 @@ spu_status launch_bn(const GemmPlan &plan, int block_n, const LaunchMaps &maps, 
     case 192: return launch_epi<192, CG>(plan, maps, a, stream, inplace);
     case 256: return launch_epi<256, CG>(plan, maps, a, stream, inplace);
     default: set_error("unsupported BLOCK_N"); return SPU_ERR_INVALID;
+  }
+}
+
+// Half-footprint CTAs exist for CTA pairs only (a lone CTA staging all of B would be left with two ring stages).
+spu_status launch_bn_half(const GemmPlan &plan, int block_n, const LaunchMaps &maps, const KernelArgs &a,
+                          cudaStream_t stream, bool inplace) {
+  switch (block_n) {
+    case 128: return launch_epi<128, 2, 1>(plan, maps, a, stream, inplace);
+    case 192: return launch_epi<192, 2, 1>(plan, maps, a, stream, inplace);
+    case 256: return launch_epi<256, 2, 1>(plan, maps, a, stream, inplace);
+    default: set_error("gemm: half-footprint tiles are 128, 192 or 256 columns wide"); return SPU_ERR_INVALID;
   }
 }
 
@@ -1012,14 +1058,14 @@ spu_status gemm_make_plan(GemmPlan *plan, const void *A, int rows_a, const void 
   plan->force_bn = force_bn;
   if (const char *env = std::getenv("SPU_GEMM_CFG")) {  // "cg:bn", experiments only
     int cg = 0, bn = 0;
-    if (std::sscanf(env, "%d:%d", &cg, &bn) == 2 && (cg == 1 || cg == 2) && bn > 0 && N % bn == 0) {
+    if (std::sscanf(env, "%d:%d", &cg, &bn) == 2 && cg >= 1 && cg <= 3 && bn > 0 && N % bn == 0) {
       plan->force_cg = cg;
       plan->force_bn = bn;
     }
   }
   if (plan->force_bn)
-    SPU_REQUIRE((plan->force_cg == 1 || plan->force_cg == 2) && N % plan->force_bn == 0 &&
-                    plan->force_bn % 64 == 0 && plan->force_bn <= 256,
+    SPU_REQUIRE(plan->force_cg >= 1 && plan->force_cg <= 3 && N % plan->force_bn == 0 &&
+                    plan->force_bn % 64 == 0 && plan->force_bn <= 256 && (plan->force_cg != 3 || plan->force_bn >= 128),
                 SPU_ERR_UNSUPPORTED, "gemm: forced tile does not fit N");
   if (epilogue == kEpiBiasResidLN) {
     SPU_REQUIRE(gemm_ln_supported(N), SPU_ERR_UNSUPPORTED,
@@ -1033,7 +1079,7 @@ spu_status gemm_make_plan(GemmPlan *plan, const void *A, int rows_a, const void 
     plan->b_ok[i] = false;
     bool wanted = false;
     for (int bn : kBlockNCands)
-      if (N % bn == 0 && (bn == box_rows || bn / 2 == box_rows)) wanted = true;
+      if (N % bn == 0 && (bn == box_rows || bn / 2 == box_rows)) wanted = true;  // lone CTA | CTA pair
     if (!wanted) continue;
     spu_status st = make_kmajor_tmap(&plan->tmap_b[i], W, N, K, box_rows, in);
     if (st != SPU_OK) return st;
@@ -1057,10 +1103,18 @@ spu_status gemm_launch(const GemmPlan &plan, int M, const GemmEpilogueArgs &args
                     (reinterpret_cast<uintptr_t>(args.out2) & 15u) == 0,
                 SPU_ERR_INVALID, "gemm: the LayerNorm-fused epilogue needs bias, gamma, beta and aligned outputs");
   const int esize = plan.in == GemmIn::FP8_E4M3 ? 1 : 2;
-  GemmConfig cfg = plan.force_bn ? GemmConfig{plan.force_cg, plan.force_bn}
+  GemmConfig cfg = plan.force_bn ? GemmConfig{plan.force_cg == 3 ? 2 : plan.force_cg, plan.force_bn, plan.force_cg == 3 ? 1 : 0}
                    : ln          ? choose_ln_config(M, plan.N)
                                  : choose_config(M, plan.N, plan.K, esize);
   SPU_REQUIRE(cfg.block_n > 0, SPU_ERR_UNSUPPORTED, "gemm: no BLOCK_N divides N");
+  if (!plan.force_bn && !ln) {
+    static const int hf_env = [] { const char *e = std::getenv("SPU_GEMM_HF"); return e ? std::atoi(e) : 0; }();
+    const int tiles_hf = ((M + 255) / 256) * (plan.N / cfg.block_n);
+    const bool one_round = tiles_hf <= kNumSMsB200 / 2;  // every CTA pair owns a single tile
+    if (cfg.cta_group == 2 && cfg.block_n >= 128 && (cfg.block_n < 256 || plan.epilogue != kEpiBiasResid) &&
+        (hf_env == 1 || (hf_env == 2 && one_round) || (hf_env == 3 && one_round && plan.K * esize <= 2048)))
+      cfg.half = 1;
+  }
   SPU_REQUIRE(plan.b_ok[cfg.block_n / cfg.cta_group / 32 - 1], SPU_ERR_UNSUPPORTED,
               "gemm: no weight tensor map for this tile");
   // Activation-side maps carry the live row count: TMA zero-fills A rows >= M and
@@ -1100,6 +1154,7 @@ spu_status gemm_launch(const GemmPlan &plan, int M, const GemmEpilogueArgs &args
                args.out2 == nullptr ? 0 : (args.out2_e4m3 ? 2 : 1)};
   // residual == output: accumulate in place with a TMA reduce-add instead of load + add + store
   const bool inplace = plan.epilogue == kEpiBiasResid && args.resid == args.out;
+  if (cfg.half) return launch_bn_half(plan, cfg.block_n, maps, a, stream, inplace);
   return cfg.cta_group == 2 ? launch_bn<2>(plan, cfg.block_n, maps, a, stream, inplace)
                             : launch_bn<1>(plan, cfg.block_n, maps, a, stream, inplace);
 }

@@ -50,12 +50,13 @@ struct GemmPlan {
   int N, K;
   int epilogue;
   GemmIn in;
-  int force_cg, force_bn;          // 0 = choose per launch from M
+  int force_cg, force_bn;          // 0 = choose per launch from M; force_cg 3 = CTA pair with half-footprint CTAs
 };
 
 struct GemmConfig {
   int cta_group;  // 1: 128 x BLOCK_N tile per CTA; 2: 256 x BLOCK_N per CTA pair
   int block_n;
+  int half = 0;   // CTA pairs only: half-footprint CTAs (<= 113 KB smem, 256 TMEM columns), two resident per SM
 };
 
 // Pick (cta_group, BLOCK_N) for an [M,N,K] problem: BLOCK_N must divide N; minimise

@@ -78,6 +78,33 @@ def test_gemm_every_tile_shape(spu, M, epi, bn, cg):
     _check_gemm(spu, M, 768, 320 if M != 4096 else 768, epi, cg, bn, M + 13 * bn + cg + epi)
 
 
+@pytest.mark.parametrize("bn", [128, 192, 256])
+@pytest.mark.parametrize("epi", [0, 1, 2])
+@pytest.mark.parametrize("M,K", [(4096, 768), (4096, 3072), (333, 320), (31, 320), (8192, 768)])
+def test_gemm_half_footprint_tiles(spu, M, K, epi, bn):
+    """cta_group 3 = CTA pair of half-footprint CTAs (two resident per SM: 3-4 ring stages, 4 epilogue warps, one
+    accumulator buffer above 128 columns).  K=3072 wraps the short ring 16 times, M=8192 gives CTAs several tiles."""
+    if bn == 256 and epi == 2:  # 3 x 32 KB stages + fp32 staging exceed 113 KB
+        with pytest.raises(Exception, match="footprint"):
+            _check_gemm(spu, M, 768, K, epi, 3, bn, 1)
+        return
+    _check_gemm(spu, M, 768, K, epi, 3, bn, M + 13 * bn + 3 + epi + K)
+
+
+def test_gemm_half_footprint_inplace_residual(spu):
+    M, N, K = 4096, 768, 3072
+    g = torch.Generator().manual_seed(6)
+    a = torch.randn(M, K, generator=g).to(torch.bfloat16).cuda()
+    w = (torch.randn(N, K, generator=g) * 0.02).to(torch.bfloat16).cuda()
+    bias = torch.randn(N, generator=g).cuda()
+    x = torch.randn(M, N, generator=g).cuda()
+    ref = _gemm_ref(a, w, bias, x, 2)
+    spu.check(spu.lib().spu_gemm_bf16_cfg_async(spu.ptr(a), spu.ptr(w), spu.ptr(bias), spu.ptr(x), spu.ptr(x),
+                                                M, N, K, 2, 3, 192, spu.stream_ptr()))
+    _sync()
+    assert torch.allclose(x.cpu(), ref, rtol=2e-3, atol=2e-3)
+
+
 def test_gelu_epilogue_tracks_erf(spu):
     """The 2^p(|x|) GELU of the epilogue against exact erf over a wide input range
     (identity weights route A straight into the activation)."""

@@ -26,7 +26,9 @@ SHAPES = {  # name: (N, K, epilogue)
 }
 
 
-def run(M, N, K, epi, cg, bn, reps, n_buf):
+def run(M, N, K, epi, cg, bn, reps, n_buf, n_streams=1):
+    if n_streams > 1:
+        return run_streams(M, N, K, epi, cg, bn, reps, n_streams)
     L = capi.lib()
     separate = epi == 12  # BIAS_RESID reading the residual from a different buffer (no in-place reduce-add)
     epi = 2 if separate else epi
@@ -71,6 +73,52 @@ def run(M, N, K, epi, cg, bn, reps, n_buf):
     return best
 
 
+def run_streams(M, N, K, epi, cg, bn, reps, n_streams):
+    """`n_streams` CUDA workers, each replaying its own graph of `reps` launches on private buffers, all at once:
+    microseconds per launch of the whole device (elapsed / (reps * n_streams)) -- what co-resident CTAs of two
+    in-flight batches buy.  epi 2 = in-place residual accumulate as in the forward."""
+    L = capi.lib()
+    main_s = torch.cuda.Stream()
+    graphs, streams, keep = [], [], []
+    for _ in range(n_streams):
+        a = (torch.randn(M, K, device="cuda") * 0.5).to(torch.bfloat16)
+        w = (torch.randn(N, K, device="cuda") * 0.05).to(torch.bfloat16)
+        bias = torch.randn(N, device="cuda")
+        out = torch.zeros(M, N, device="cuda", dtype=torch.float32 if epi == 2 else torch.bfloat16)
+        keep += [a, w, bias, out]
+        s = torch.cuda.Stream()
+
+        def enqueue(a=a, w=w, bias=bias, out=out, s=s):
+            for _ in range(reps):
+                capi.check(L.spu_gemm_bf16_cfg_async(capi.ptr(a), capi.ptr(w), capi.ptr(bias),
+                                                     capi.ptr(out) if epi == 2 else None, capi.ptr(out), M, N, K, epi,
+                                                     cg, bn, capi.stream_ptr(s)))
+        with torch.cuda.stream(s):
+            enqueue()
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=s):
+            enqueue()
+        graphs.append(g)
+        streams.append(s)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    best = 1e9
+    for _ in range(5):
+        with torch.cuda.stream(main_s):
+            e0.record(main_s)
+            for g, s in zip(graphs, streams):
+                s.wait_event(e0)
+                with torch.cuda.stream(s):
+                    g.replay()
+                ev = torch.cuda.Event()
+                ev.record(s)
+                main_s.wait_event(ev)
+            e1.record(main_s)
+        torch.cuda.synchronize()
+        best = min(best, e0.elapsed_time(e1) / (reps * n_streams) * 1e3)
+    return best
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--M", default="4096", help="comma-separated row counts")
@@ -78,21 +126,25 @@ def main():
     ap.add_argument("--bufs", type=int, default=1, help="distinct A/out buffers rotated (1 = L2-warm, as in the forward)")
     ap.add_argument("--shapes", default="qkv,attn_out,ffn1,ffn2")
     ap.add_argument("--all", action="store_true", help="sweep every tile, not only the chosen one")
+    ap.add_argument("--cfgs", default="", help="explicit tiles 'cg:bn,...' (cg 3 = CTA pair of half-footprint CTAs)")
+    ap.add_argument("--streams", type=int, default=1, help="concurrent CUDA workers, each with its own graph + buffers")
     args = ap.parse_args()
     for name, M in ((n, int(m)) for n in args.shapes.split(",") for m in args.M.split(",")):
         N, K, epi = SHAPES[name]
         cfgs = [(0, 0)]
         if args.all and epi != 5:
             cfgs += [(cg, bn) for cg in (2, 1) for bn in (256, 192, 128, 64) if N % bn == 0]
+        if args.cfgs:
+            cfgs = [tuple(int(v) for v in c.split(":")) for c in args.cfgs.split(",")]
         for cg, bn in cfgs:
             try:
-                us = run(M, N, K, epi, cg, bn, args.reps, args.bufs)
+                us = run(M, N, K, epi, cg, bn, args.reps, args.bufs, args.streams)
             except Exception as ex:  # keep sweeping
                 print(json.dumps({"shape": name, "cg": cg, "bn": bn, "error": str(ex)}), flush=True)
                 continue
             tf = 2.0 * M * N * K / us / 1e6
             print(json.dumps({"shape": name, "M": M, "N": N, "K": K, "epi": epi, "cg": cg, "bn": bn,
-                              "us": round(us, 2), "tflops": round(tf, 1)}), flush=True)
+                              "streams": args.streams, "us": round(us, 2), "tflops": round(tf, 1)}), flush=True)
 
 
 if __name__ == "__main__":
