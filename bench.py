@@ -1,20 +1,25 @@
 #!/usr/bin/env python
-"""Benchmark of the hot path: BERT-base seq128 inferences/s through libspu_b200.so.
+"""Benchmark of the hot path: inferences/s of the StarPU inference codelet through libspu_b200.so.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--batch 32] [--seq 128]
-    python bench.py --impl reference ...      # the reference's CPU codelet path
+    python bench.py [--config A|B|C|D|E] [--gpus N] [--steps K] [--warmup W]
+    python bench.py --impl reference ...      # the reference's CPU codelet path on the host cores
 
-A "step" is one pass of the hot path over one batch of synthetic requests: what the
-reference's cuda_inference_func does for one StarPU task (src/core/starpu_setup.cpp:
-807-846) -- ids/mask [B,S] int64 in, last_hidden_state [B,S,768] fp32 out.
-Workload = BASELINE.json configs[1]: BERT-base, seq 128, dynamic batch at its cap 32,
-bf16, one B200 CUDA worker per GPU.  N>1: one process per GPU (torchrun), one weight
-replica each, requests are independent -> weak scaling, no collective on the data path
-(torch.distributed is used only for the timing barrier / max-over-ranks).
+A "step" is one pass of the hot path over one batch of synthetic requests: what the reference's
+cuda_inference_func does for one StarPU task (src/core/starpu_setup.cpp:807-846).  --config names the BASELINE.json
+workload (default B = configs[1], the one `metric` is quoted on):
+  A  BERT-base seq 128 batch 1                          (configs[0]: the reference's CPU-runnable case)
+  B  BERT-base seq 128 dynamic batch at its cap 32, bf16 (configs[1])
+  C  BERT-base variable-length 16-512 padded+masked, batch 64 (configs[2])
+  D  BERT-base seq 128 batch 256, FP8 E4M3 per-tensor scales (configs[3]; the plan that passes the 6e-2 gate)
+  E  ViT-L/16 224x224 batch 64, patch-embed as GEMM, bf16 (configs[4])
+N>1: one process per GPU (torchrun), one weight replica each, requests are independent -> weak scaling, no
+collective on the data path (torch.distributed is used only for the timing barrier / max-over-ranks).
 
-Prints ONE JSON line (rank 0).  value = whole-job inferences/s with inputs resident in
-HBM; e2e = same metric through the host-buffer API (pinned host ids/mask -> H2D ->
-forward -> D2H of output0) with copies inside the timed region.
+Prints ONE JSON line (rank 0).  value = whole-job inferences/s with inputs resident in HBM; e2e = the same metric
+through the codelet / task path of libspu_host.so with per-request HOST buffers, copies inside the timed region;
+parity = the device result against the fp32 CPU reference on the same weights and inputs (computed once, outside
+every timed region); cpu_baseline / --impl reference = the reference's CPU codelet body
+(oracle/_ref: the reference's own TensorBuilder + LibTorch forward; else the Python port) on the host cores.
 """
 from __future__ import annotations
 
@@ -22,6 +27,7 @@ import argparse
 import json
 import os
 import sys
+import tempfile
 import threading
 import time
 
@@ -32,30 +38,69 @@ if ROOT not in sys.path:
 import numpy as np  # noqa: E402
 import torch  # noqa: E402
 
-METRIC = "BERT-base seq128 inferences/s"
 UNIT = "inferences/s"
 LAYERS, HIDDEN, FFN = 12, 768, 3072
 
+CONFIGS = {
+    "A": dict(model="bert", batch=1, seq=128, precision="bf16", min_len=None, baseline="configs[0]",
+              what="BERT-base seq128 batch 1 (the reference's CPU-runnable case) on one B200 CUDA worker"),
+    "B": dict(model="bert", batch=32, seq=128, precision="bf16", min_len=None, baseline="configs[1]",
+              what="BERT-base seq128 dynamic batch at cap 32, bf16, one weight replica per B200"),
+    "C": dict(model="bert", batch=64, seq=512, precision="bf16", min_len=16, baseline="configs[2]",
+              what="BERT-base variable-length requests 16-512 tokens padded+masked, batch 64, one replica per B200"),
+    "D": dict(model="bert", batch=256, seq=128, precision="fp8", min_len=None, baseline="configs[3]",
+              what="BERT-base seq128 batch 256, FP8 E4M3 GEMMs with per-tensor scales (default plan: QKV everywhere + "
+                   "FFN pair of the first half, inside the 6e-2 gate), one replica per B200"),
+    "E": dict(model="vit", batch=64, seq=197, precision="bf16", min_len=None, baseline="configs[4]",
+              what="ViT-L/16 224x224 batch 64, patch-embed as GEMM, bf16, one weight replica per B200"),
+}
+GATES = {"bf16": (2e-2, 1.0), "fp8": (6e-2, 0.995), "fp8x6": (6e-2, 0.995)}  # BASELINE.json north_star
 
-def gemm_flops_per_seq(seq):
-    return LAYERS * 24 * seq * HIDDEN * HIDDEN  # Lyr*24*L*H^2
+
+def metric_name(cfg):
+    if cfg["model"] == "vit":
+        return "ViT-L/16 224x224 images/s"
+    if cfg["min_len"] is not None:
+        return f"BERT-base variable-length ({cfg['min_len']}-{cfg['seq']}) inferences/s"
+    return f"BERT-base seq{cfg['seq']} inferences/s"
 
 
-def attn_flops_per_seq(seq):
-    return LAYERS * 4 * seq * seq * HIDDEN
+def resolve_config(args):
+    cfg = dict(CONFIGS[args.config])
+    variant = False
+    for key, val in (("batch", args.batch), ("seq", args.seq), ("precision", args.precision), ("min_len", args.min_len)):
+        if val is not None and val != cfg[key]:
+            cfg[key] = val
+            variant = True
+    cfg["id"] = args.config
+    cfg["variant"] = variant
+    return cfg
+
+
+def workload_config(cfg, world):
+    """The `config` object: identical in both arms (the driver compares them)."""
+    tag = f"BASELINE {cfg['baseline']}" + (" variant" if cfg["variant"] else "")
+    inputs = ("pixels U[0,1) fp32 [1,3,224,224] per request" if cfg["model"] == "vit" else
+              "ids U[0,30522) int64 [1,seq] per request, " +
+              ("all-ones mask" if cfg["min_len"] is None else f"lengths U[{cfg['min_len']},{cfg['seq']}] padded+masked"))
+    return {"workload": f"{cfg['what']} ({tag}); random-init weights seed 0, {inputs}",
+            "config_id": cfg["id"], "model": "vit_l_16" if cfg["model"] == "vit" else "bert-base",
+            "batch": cfg["batch"], "seq_len": cfg["seq"], "precision": cfg["precision"],
+            "min_len": cfg["min_len"], "replicas": world}
 
 
 def load_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
         d = json.load(open(p))
-        return {"tflops": float(d.get("bf16_tflops_sustained", d.get("bf16_tflops"))),
-                "hbm_gbs": float(d["hbm_gbs"]), "source": "measured (MEASURED_PEAKS.json, sustained bf16)"}
-    return {"tflops": 1400.0, "hbm_gbs": 6650.0, "source": "fallback (B200_PROFILING.md)"}
+        burst = float(d.get("bf16_tflops", d.get("bf16_tflops_sustained")))
+        return {"tflops": float(d.get("bf16_tflops_sustained", burst)), "tflops_burst": burst,
+                "hbm_gbs": float(d["hbm_gbs"]), "source": "measured (MEASURED_PEAKS.json)"}
+    return {"tflops": 1400.0, "tflops_burst": 1400.0, "hbm_gbs": 6650.0, "source": "fallback (B200_PROFILING.md)"}
 
 
 class ClockSampler(threading.Thread):
-    """Samples SM clock + throttle reasons through NVML while the timed region runs."""
+    """Samples SM clock + throttle reasons through NVML from before the warm-up to the end of the sustained loop."""
 
     def __init__(self, index):
         super().__init__(daemon=True)
@@ -84,82 +129,192 @@ class ClockSampler(threading.Thread):
                  nv.nvmlClocksThrottleReasonHwPowerBrakeSlowdown: "hw_power_brake"}
         while not self._halt.is_set():
             try:
-                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                self.samples.append((time.perf_counter(), nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)))
                 r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
                 for bit, name in names.items():
                     if r & bit:
                         self.reasons.add(name)
             except Exception:
                 pass
-            time.sleep(0.02)
+            time.sleep(0.01)
+
+    def window(self, t0, t1):
+        v = [m for t, m in self.samples if t0 <= t <= t1]
+        return {"sm_mhz": float(np.median(v)) if v else None, "samples": len(v)}
 
     def stop(self):
         self._halt.set()
         if self.ok:
             self.join(timeout=2)
-        med = float(np.median(self.samples)) if self.samples else None
-        return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
-                "samples": len(self.samples)}
+        v = [m for _, m in self.samples]
+        return {"sm_mhz": float(np.median(v)) if v else None, "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(v),
+                "during": "warm-up + timed region + sustained loop (10 ms period)"}
 
 
-def make_batches(cfg, batch, seq, n_sets, seed0=1234):
-    from starpu_inference_server_b200 import synthetic
+# ------------------------------------------------------------- the reference's CPU codelet body
+class CpuCodelet:
+    """The reference's CPU codelet path for one model: TensorBuilder wrap of the StarPU buffers -> TorchScript
+    forward on the host cores -> copy_output_to_buffer (src/core/starpu_setup.cpp:594-624,784-801;
+    tensor_builder.cpp:93-189).  kind "reference": oracle/_ref/libref_cpu_codelet.so (the reference's own
+    tensor_builder.cpp compiled against the wheel's LibTorch, C++ end to end); kind "port": the same three steps on
+    the Python-side TorchScript module when that library was not built.  The artifact is the traced oracle module
+    (HF BertModel does not trace under transformers 5.5) / torch.jit.script(torchvision vit_l_16)."""
 
-    return [synthetic.make_requests(cfg, batch, seq, seed=seed0 + i) for i in range(n_sets)]
+    def __init__(self, cfg, threads=None):
+        from oracle import ref_cpu_codelet as rc
+
+        self.threads = threads or os.cpu_count() or 1
+        torch.set_num_threads(self.threads)
+        self.model = cfg["model"]
+        self.tmp = tempfile.mkdtemp(prefix="spu_bench_")
+        path = os.path.join(self.tmp, "model.pt")
+        if self.model == "vit":
+            from oracle import vit_oracle as vo
+
+            self.spec = vo.VIT_L_16
+            self.w = vo.make_weights(self.spec, 0)
+            rc.export_vit_torchscript(self.w, self.spec, path)
+        else:
+            from oracle import bert_oracle as bo
+
+            self.spec = bo.BERT_BASE
+            self.w = bo.make_weights(self.spec, 0)
+            rc.export_bert_torchscript(self.w, self.spec, path, batch=2, seq=min(cfg["seq"], 128))
+        self.kind = "reference" if rc.available() else "port"
+        if self.kind == "reference":
+            self.cl = rc.RefCpuCodelet(path, threads=self.threads)
+        else:
+            self.ts = torch.jit.load(path).eval()
+
+    def out_shape(self, inputs):
+        b = inputs[0].shape[0]
+        return (b, self.spec.classes) if self.model == "vit" else (b, inputs[0].shape[1], self.spec.hidden)
+
+    def run(self, inputs, warmup, iters):
+        """Returns (output array, per-task ms list)."""
+        out = np.empty(self.out_shape(inputs), dtype=np.float32)
+        if self.kind == "reference":
+            return out, self.cl.run(inputs, out, warmup=warmup, iters=iters)
+        tin = [torch.from_numpy(np.ascontiguousarray(a)) for a in inputs]
+        tout, ms = torch.from_numpy(out), []
+        with torch.inference_mode():
+            for k in range(warmup + iters):
+                t0 = time.perf_counter()
+                tout.copy_(self.ts(*tin))
+                if k >= warmup:
+                    ms.append((time.perf_counter() - t0) * 1e3)
+        return out, ms
+
+    def describe(self):
+        return ("oracle/_ref/libref_cpu_codelet.so: the reference's tensor_builder.cpp + LibTorch forward "
+                "(run_inference glue restated in oracle/ref_cpu_codelet.cpp)" if self.kind == "reference" else
+                "Python port: TorchScript forward of the traced oracle module + copy into the output buffer")
+
+
+def host_inputs(cfg, rank, n_sets):
+    """Seeded synthetic request batches (the same streams in both arms)."""
+    from starpu_inference_server_b200 import synthetic as syn
+
+    if cfg["model"] == "vit":
+        from starpu_inference_server_b200.vit import VitConfig
+
+        return [(syn.make_images(VitConfig(), cfg["batch"], seed=1234 + 100 * rank + i),) for i in range(n_sets)]
+    from starpu_inference_server_b200.bert import BertConfig
+
+    return [syn.make_requests(BertConfig(), cfg["batch"], cfg["seq"], seed=1234 + 100 * rank + i, min_len=cfg["min_len"])
+            for i in range(n_sets)]
+
+
+def parity_rows(cfg):
+    """Sequences of input set 0 the CPU reference is run on (bounded: <= 8192 tokens ~ a few CPU seconds)."""
+    if cfg["model"] == "vit":
+        return min(cfg["batch"], 8)
+    return max(1, min(cfg["batch"], 8192 // cfg["seq"]))
+
+
+def b1_latency(codelet, cfg):
+    """batch 1, >= 3 warm-ups, >= 20 timed tasks, mean / p50 / p99."""
+    from starpu_inference_server_b200 import synthetic as syn
+
+    if cfg["model"] == "vit":
+        from starpu_inference_server_b200.vit import VitConfig
+
+        inputs = [syn.make_images(VitConfig(), 1, seed=77)]
+    else:
+        from starpu_inference_server_b200.bert import BertConfig
+
+        inputs = list(syn.make_requests(BertConfig(), 1, 128, seed=77))
+    _, ms = codelet.run(inputs, warmup=3, iters=20)
+    return {"mean_ms": float(np.mean(ms)), "p50_ms": float(np.percentile(ms, 50)), "p99_ms": float(np.percentile(ms, 99)),
+            "inferences_per_s": 1e3 / float(np.mean(ms)), "iters": len(ms), "warmup": 3,
+            "what": "config (A): batch 1" + ("" if cfg["model"] == "vit" else " seq 128") + " through the CPU codelet body"}
+
+
+def parity_block(got, ref, precision, live=None):
+    """Device result vs the fp32 CPU reference.  `live` masks the token rows that count (padded rows carry no
+    information).  The gate is BASELINE.json's: max|got-ref| / max|ref| and top-1 agreement; the reference client's
+    own rule (atol + rtol*|ref|, client/bert_inference_client.py:263-346, defaults 1e-5 / 1e-3) is reported beside
+    it -- it is an fp32-vs-fp32 rule and a bf16 path is not expected to meet it."""
+    got = np.asarray(got, dtype=np.float32).reshape(-1, got.shape[-1])
+    ref = np.asarray(ref, dtype=np.float32).reshape(-1, ref.shape[-1])
+    if live is not None:
+        keep = np.asarray(live).reshape(-1).astype(bool)
+        got, ref = got[keep], ref[keep]
+    diff = np.abs(got - ref)
+    max_ref = float(np.abs(ref).max())
+    atol, rtol = 1e-5, 1e-3
+    viol = int((diff > atol + rtol * np.abs(ref)).sum())
+    srt = np.sort(ref, axis=-1)
+    gap = srt[:, -1] - srt[:, -2]
+    same = got.argmax(-1) == ref.argmax(-1)
+    decided = gap > 1e-2
+    tol, top1_gate = GATES[precision]
+    band = gap > 2 * tol * max_ref  # rows a result inside the tolerance cannot legitimately flip
+    out = {"against": "fp32 CPU reference (same seeded weights and inputs)", "rows": int(got.shape[0]),
+           "max_abs": float(diff.max()), "max_abs_over_max_ref": float(diff.max() / max_ref), "max_ref": max_ref,
+           "rms": float(np.sqrt((diff.astype(np.float64) ** 2).mean())),
+           "client_rule": {"atol": atol, "rtol": rtol, "violations": viol, "fraction": viol / diff.size,
+                           "max_rel": float((diff / np.maximum(np.abs(ref), atol)).max())},
+           "top1_strict": float(same.mean()),
+           "top1_margin_1e-2": float(same[decided].mean()) if decided.any() else None,
+           "rows_decided_by_1e-2": int(decided.sum()),
+           "top1_outside_tolerance_band": float(same[band].mean()) if band.any() else None,
+           "rows_outside_tolerance_band": int(band.sum()),
+           "gate": {"max_rel": tol, "top1": top1_gate},
+           "gate_max_rel_ok": bool(diff.max() / max_ref <= tol)}
+    return out
 
 
 # ----------------------------------------------------------------- reference arm
-def cpu_codelet_forward(batch, seq, budget_s, max_steps, warmup, threads=None):
-    """The reference's CPU codelet path restated: TorchScript module forward on the host
-    cores + copy of the output into the (host) StarPU buffer
-    (src/core/starpu_setup.cpp:784-801, tensor_builder.cpp:161-189).  The TorchScript
-    artifact is the traced oracle module (HF BertModel does not trace under
-    transformers 5.5).  Returns (inferences/s, ms list, steps, threads)."""
-    from oracle import bert_oracle as bo
-
-    threads = threads or os.cpu_count() or 1
-    torch.set_num_threads(threads)
-    spec = bo.BERT_BASE
-    w = bo.make_weights(spec, 0)
-    ids, mask = bo.make_inputs(spec, batch, seq, seed=1234)
-    ids_t, mask_t = torch.from_numpy(ids), torch.from_numpy(mask)
-    m = bo.BertOracleModule(w, spec).eval()
-    with torch.no_grad():
-        ts = torch.jit.freeze(torch.jit.trace(m, (ids_t, mask_t)))
-    out_buf = torch.empty(batch, seq, spec.hidden)
-    times = []
-    with torch.inference_mode():
-        for _ in range(max(1, warmup)):
-            out_buf.copy_(ts(ids_t, mask_t))
-        t_begin = time.perf_counter()
-        for _ in range(max_steps):
-            t0 = time.perf_counter()
-            out_buf.copy_(ts(ids_t, mask_t))
-            times.append((time.perf_counter() - t0) * 1e3)
-            if time.perf_counter() - t_begin > budget_s:
-                break
-    total_s = sum(times) / 1e3
-    return batch * len(times) / total_s, times, len(times), threads
-
-
-def run_reference(args, rank, world):
+def run_reference(args, cfg, rank, world):
     if rank != 0:
         return
-    steps = args.steps
-    value, times, done, threads = cpu_codelet_forward(args.batch, args.seq, budget_s=150.0,
-                                                      max_steps=steps, warmup=min(args.warmup, 2))
+    B = cfg["batch"]
+    codelet = CpuCodelet(cfg)
+    inputs = list(host_inputs(cfg, 0, 1)[0])
+    # bounded sample: a step is one task of min(B, sample) requests; the rate is per request either way
+    sb = B if cfg["model"] == "bert" and B * cfg["seq"] <= 8192 else parity_rows(cfg)
+    sample = [a[:sb] for a in inputs]
+    budget_s, t_begin, times = 150.0, time.perf_counter(), []
+    codelet.run(sample, warmup=args.warmup, iters=0)
+    for _ in range(args.steps):
+        _, ms = codelet.run(sample, warmup=0, iters=1)
+        times += ms
+        if time.perf_counter() - t_begin > budget_s:
+            break
+    value = sb * len(times) / (sum(times) / 1e3)
     line = {
-        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
-        "steps": done, "warmup": min(args.warmup, 2), "ms_per_step": float(np.mean(times)),
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
-        "data": "synthetic",
-        "config": {"workload": f"BERT-base seq{args.seq} batch {args.batch} (BASELINE configs[1]) on the host cores",
-                   "batch": args.batch, "seq_len": args.seq,
-                   "path": "TorchScript forward of the traced oracle module (CPU codelet restatement)"},
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port",
-                         "sample": f"{done} forward passes of batch {args.batch} x seq {args.seq}"},
+        "impl": "reference", "metric": metric_name(cfg), "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": len(times), "warmup": args.warmup, "ms_per_step": float(np.mean(times)),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(cfg, world),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": codelet.threads, "kind": codelet.kind,
+                         "sample": f"{len(times)} tasks of {sb} requests each ({codelet.describe()})",
+                         "b1": b1_latency(codelet, cfg)},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "latency_ms": {"p50": float(np.percentile(times, 50)), "p99": float(np.percentile(times, 99))},
+        "latency_ms": {"p50": float(np.percentile(times, 50)), "p99": float(np.percentile(times, 99)),
+                       "what": f"one CPU task of {sb} requests"},
     }
     print(json.dumps(line), flush=True)
 
@@ -182,15 +337,30 @@ def whole_job_rate(units_per_rank_step, steps, world, slowest_ms):
     return world * units_per_rank_step * steps / (slowest_ms / 1e3)
 
 
+def pin_rank_to_core_slice(local_rank, world):
+    """One rank per GPU shares the host with the other ranks: give each its own slice of the cores so that the
+    worker / completer threads of 8 ranks do not migrate across each other (VERDICT r1 weak #6)."""
+    try:
+        cores = sorted(os.sched_getaffinity(0))
+        per = len(cores) // max(world, 1)
+        if world > 1 and per >= 2:
+            os.sched_setaffinity(0, set(cores[local_rank * per:(local_rank + 1) * per]))
+            return per
+    except (AttributeError, OSError):
+        pass
+    return None
+
+
 # ---------------------------------------------------------------------- B200 arm
-def run_b200(args, rank, local_rank, world):
+def run_b200(args, cfg, rank, local_rank, world):
     import torch.distributed as dist
 
-    from starpu_inference_server_b200 import capi, synthetic
-    from starpu_inference_server_b200.bert import BertConfig, BertReplica
+    from starpu_inference_server_b200 import capi, hostapi
+    from starpu_inference_server_b200 import synthetic as syn
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device -- the hot path has no CPU fallback")
+    pinned_cores = pin_rank_to_core_slice(local_rank, world) if not args.no_pin else None
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
@@ -200,73 +370,101 @@ def run_b200(args, rank, local_rank, world):
         dist.init_process_group("gloo")
     assert capi.lib().spu_device_is_sm100(local_rank) == 1, "device is not sm_100"
 
-    spec = BertConfig()
-    B, S = args.batch, args.seq
+    is_vit = cfg["model"] == "vit"
+    B, S, precision = cfg["batch"], cfg["seq"], cfg["precision"]
     n_pipe = 4  # workspaces / CUDA workers, like STARPU_NWORKER_PER_CUDA=4 (models/bert.yml:6-8)
-    flags = {"bf16": capi.SPU_PREC_BF16, "fp8": capi.SPU_PREC_FP8_E4M3,
-             "fp8x6": capi.SPU_PREC_FP8_E4M3 | (6 << 8)}[args.precision]
-    if args.output_bf16:
-        flags |= capi.SPU_OUTPUT_BF16
-    if args.auto_graph:
-        # the codelet path replays a CUDA graph from the second sighting of a slot's device
-        # buffers on (warm-up capture, src/core/warmup.cpp:225-299)
-        flags |= capi.SPU_FORWARD_AUTO_GRAPH
-    w = synthetic.make_weights(spec, 0)
-    rep = BertReplica(w, device=local_rank, max_batch=B, max_seq=S, n_workspaces=n_pipe, flags=flags)
-    del w
-    n_sets = 4
-    from starpu_inference_server_b200 import synthetic as syn
-
-    host = [syn.make_requests(spec, B, S, seed=1234 + 100 * rank + i, min_len=args.min_len) for i in range(n_sets)]
-    true_tokens = float(np.mean([m.sum() for _, m in host]))  # FLOPs are charged on unpadded tokens
-    ids_d = [torch.from_numpy(i).to(dev) for i, _ in host]
-    mask_d = [torch.from_numpy(m).to(dev) for _, m in host]
-    out_d = [torch.empty(B, S, spec.hidden, device=dev, dtype=torch.bfloat16 if args.output_bf16 else torch.float32)
-             for _ in range(n_pipe)]
+    n_sets = 4 if not is_vit else 2
+    host = host_inputs(cfg, rank, n_sets)
     stream = torch.cuda.Stream(device=dev)
-    if flags & capi.SPU_PREC_FP8_E4M3:
-        # per-tensor activation scales from a 32-sequence calibration draw
-        ci, cm = syn.make_requests(spec, min(32, B), S, seed=999, min_len=args.min_len)
-        rep.calibrate_fp8(torch.from_numpy(ci).to(dev), torch.from_numpy(cm).to(dev), stream=stream)
+    if is_vit:
+        from starpu_inference_server_b200.vit import VitConfig, VitReplica
+
+        spec = VitConfig()
+        rep = VitReplica(syn.make_vit_weights(spec, 0), spec, device=local_rank, max_batch=B, n_workspaces=n_pipe)
+        in_d = [(torch.from_numpy(h[0]).to(dev),) for h in host]
+        out_shape, out_dtype = (B, spec.classes), torch.float32
+        true_tokens = float(B * spec.seq)
+        launches = rep.launches_per_forward
+    else:
+        from starpu_inference_server_b200.bert import BertConfig, BertReplica
+
+        spec = BertConfig()
+        flags = {"bf16": capi.SPU_PREC_BF16, "fp8": capi.SPU_PREC_FP8_E4M3,
+                 "fp8x6": capi.SPU_PREC_FP8_E4M3 | (6 << 8)}[precision]
+        if args.output_bf16:
+            flags |= capi.SPU_OUTPUT_BF16
+        if args.auto_graph:
+            # the codelet path replays a CUDA graph from the second sighting of a slot's device
+            # buffers on (warm-up capture, src/core/warmup.cpp:225-299)
+            flags |= capi.SPU_FORWARD_AUTO_GRAPH
+        rep = BertReplica(syn.make_weights(spec, 0), device=local_rank, max_batch=B, max_seq=S, n_workspaces=n_pipe,
+                          flags=flags)
+        in_d = [(torch.from_numpy(i).to(dev), torch.from_numpy(m).to(dev)) for i, m in host]
+        out_shape = (B, S, spec.hidden)
+        out_dtype = torch.bfloat16 if args.output_bf16 else torch.float32
+        true_tokens = float(np.mean([m.sum() for _, m in host]))  # FLOPs are charged on unpadded tokens
+        if flags & capi.SPU_PREC_FP8_E4M3:
+            # per-tensor activation scales from a 32-sequence calibration draw
+            ci, cm = syn.make_requests(spec, min(32, B), S, seed=999, min_len=cfg["min_len"])
+            rep.calibrate_fp8(torch.from_numpy(ci).to(dev), torch.from_numpy(cm).to(dev), stream=stream)
+        launches = rep.launches_per_forward
+        # warm-up autotune (src/core/warmup.cpp:226-299 is the reference's warm-up hook): measured tile winners
+        # for this batch shape replace the static cost model's picks
+        tuned_changed = rep.autotune(B, S, stream=stream) if args.autotune else None
+    out_d = [torch.empty(*out_shape, device=dev, dtype=out_dtype) for _ in range(n_pipe)]
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize(dev)
 
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+
     # ---------------- device-resident throughput (value) ----------------
     # warm-up hook (src/core/warmup.cpp:225-299): one CUDA graph per (worker, input set)
     # pointer tuple; `--streams` workers issue tasks round-robin like StarPU's CUDA workers
     n_str = max(1, min(args.streams, n_pipe))
     wstreams = [stream] + [torch.cuda.Stream(device=dev) for _ in range(n_str - 1)]
-    for k, st in enumerate(wstreams):
-        with torch.cuda.stream(st):
-            for i in range(n_sets):
-                rep.capture(ids_d[i], mask_d[i], out_d[k], ws=k, stream=st)
-    torch.cuda.synchronize(dev)
+    if not is_vit:
+        for k, st in enumerate(wstreams):
+            with torch.cuda.stream(st):
+                for i in range(n_sets):
+                    rep.capture(*in_d[i], out_d[k], ws=k, stream=st)
+        torch.cuda.synchronize(dev)
 
     def step_resident(i, k=0):
-        rep.forward_async(ids_d[i % n_sets], mask_d[i % n_sets], out_d[k], ws=k, stream=wstreams[k])
+        rep.forward_async(*in_d[i % n_sets], out_d[k], ws=k, stream=wstreams[k])
+
+    def timed_loop(n_steps):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for st in wstreams[1:]:
+            st.wait_event(e0)
+        for i in range(n_steps):
+            step_resident(i, i % n_str)
+        for st in wstreams[1:]:
+            ev = torch.cuda.Event()
+            ev.record(st)
+            stream.wait_event(ev)
+        e1.record(stream)
+        return e0, e1
 
     for i in range(args.warmup):
         step_resident(i, i % n_str)
     barrier()
-    sampler = ClockSampler(local_rank)
-    sampler.start()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record(stream)
-    for st in wstreams[1:]:
-        st.wait_event(e0)
-    for i in range(args.steps):
-        step_resident(i, i % n_str)
-    for st in wstreams[1:]:
-        ev = torch.cuda.Event()
-        ev.record(st)
-        stream.wait_event(ev)
-    e1.record(stream)
+    t_timed0 = time.perf_counter()
+    e0, e1 = timed_loop(args.steps)
     barrier()
-    clocks = sampler.stop()
+    t_timed1 = time.perf_counter()
     ms_total = e0.elapsed_time(e1)
+
+    # ---------------- parity sample: input set 0 through the device path ----------------
+    prow = parity_rows(cfg)
+    with torch.cuda.stream(stream):
+        step_resident(0)
+    torch.cuda.synchronize(dev)
+    got = out_d[0][:prow].float().cpu().numpy()
 
     # ---------------- per-task device latency (one batch, idle GPU) ----------
     lat = []
@@ -280,37 +478,72 @@ def run_b200(args, rank, local_rank, world):
             lat.append(a.elapsed_time(b))
 
     # ---------------- per-kernel-class device time (roofline) ----------------
-    # each class runs alone as 5 forwards' worth of launches inside one CUDA graph
-    stage_ms = {k: min(rep.stage_chain_ms(ids_d[0], mask_d[0], out_d[0], [k], stream=stream) for _ in range(3))
-                for k in capi.STAGE_NAMES}
-    gemm_names = ["gemm_qkv", "gemm_attn_out", "gemm_ffn1", "gemm_ffn2"]
-    gemm_ms = min(rep.stage_chain_ms(ids_d[0], mask_d[0], out_d[0], gemm_names, stream=stream) for _ in range(3))
-    launches = rep.launches_per_forward
+    # each class runs alone as 5 forwards' worth of launches inside one CUDA graph; taken BEFORE the sustained loop,
+    # i.e. in the thermal / power state the burst peak of MEASURED_PEAKS.json was taken in
+    stage_ms, gemm_ms = None, None
+    if not is_vit:
+        stage_ms = {k: min(rep.stage_chain_ms(*in_d[0], out_d[0], [k], stream=stream) for _ in range(3))
+                    for k in capi.STAGE_NAMES}
+        gemm_names = ["gemm_qkv", "gemm_attn_out", "gemm_ffn1", "gemm_ffn2"]
+        gemm_ms = min(rep.stage_chain_ms(*in_d[0], out_d[0], gemm_names, stream=stream) for _ in range(3))
+    # ---------------- sustained figure: >= 2 s of back-to-back steps ----------------
+    per_step_ms = ms_total / args.steps
+    sus_steps = int(max(args.steps, min(50000, 2200.0 / max(per_step_ms, 1e-3))))
+    barrier()
+    t_sus0 = time.perf_counter()
+    s0, s1 = timed_loop(sus_steps)
+    barrier()
+    t_sus1 = time.perf_counter()
+    sus_ms = s0.elapsed_time(s1)
+
+    clocks = sampler.stop()
+    clocks["timed_region"] = sampler.window(t_timed0, t_timed1)
+    clocks["sustained_loop"] = sampler.window(t_sus0, t_sus1)
+
+    tuned = [] if is_vit else rep.tuned_configs()
 
     # ---------------- end-to-end through the codelet / task path (e2e) ----------------
-    # per-request host buffers ([1,S] ids + mask each) -> host gather into a pinned slot ->
-    # StarPU-shaped task -> H2D -> codelet cuda_func -> C-ABI kernels -> D2H into the pinned
-    # output slot -> per-request slices; everything inside the timed region.
-    from starpu_inference_server_b200 import hostapi
-
+    # per-request host buffers -> host gather into a pinned slot -> StarPU-shaped task -> H2D -> codelet cuda_func
+    # -> C-ABI kernels -> D2H into the pinned output slot -> per-request slices; everything inside the timed region.
     # pool 12 as models/bert.yml; 2 CUDA workers x STARPU_CUDA_PIPELINE 4 (the reference's pipeline depth) measured
     # best of the swept (workers, pipeline) pairs at N=1 and N=8 (profiles/r06_e2e_config.md); env knobs: sweeps only
-    e2e_workers = min(n_pipe, int(os.environ.get("SPU_BENCH_WORKERS", 2)))
-    e2e_pipeline = int(os.environ.get("SPU_BENCH_PIPELINE", 4))
-    e2e_pool = int(os.environ.get("SPU_BENCH_POOL", 12))
-    io = dict(inputs=[("input_ids", "i64", [1, S]), ("attention_mask", "i64", [1, S])],
-              outputs=[("output0", "bf16" if args.output_bf16 else "f32", [1, S, spec.hidden])])
-    srv = hostapi.Server(**io, replicas=[rep], device_ids=[local_rank], model_kind=hostapi.MODEL_BERT,
-                         max_batch_size=B, pool_size=e2e_pool, nworker_per_cuda=e2e_workers, cuda_pipeline=e2e_pipeline,
-                         n_workspaces=n_pipe)
-    req_rows = [[(np.ascontiguousarray(i[r:r + 1]), np.ascontiguousarray(m[r:r + 1])) for r in range(B)]
-                for i, m in host]
-    prepared = [srv.prepare_batch([(r, 1, [a, b], [None]) for r, (a, b) in enumerate(rows)]) for rows in req_rows]
+    e2e_workers = min(n_pipe, int(os.environ.get("SPU_BENCH_WORKERS", 4 if is_vit else 2)))
+    e2e_pipeline = int(os.environ.get("SPU_BENCH_PIPELINE", 2 if is_vit else 4))
+    e2e_pool = int(os.environ.get("SPU_BENCH_POOL", 6 if is_vit else 12))
+    if is_vit:
+        io = dict(hostapi.VIT_L_IO)
+        kind = hostapi.MODEL_VIT
+        req_rows = [[(np.ascontiguousarray(h[0][r:r + 1]),) for r in range(B)] for h in host]
+        h2d = B * 3 * 224 * 224 * 4
+        d2h = B * spec.classes * 4
+        out_row_shape, out_np = (1, spec.classes), np.float32
+    else:
+        io = dict(inputs=[("input_ids", "i64", [1, S]), ("attention_mask", "i64", [1, S])],
+                  outputs=[("output0", "bf16" if args.output_bf16 else "f32", [1, S, spec.hidden])])
+        kind = hostapi.MODEL_BERT
+        req_rows = [[(np.ascontiguousarray(i[r:r + 1]), np.ascontiguousarray(m[r:r + 1])) for r in range(B)]
+                    for i, m in host]
+        h2d = 2 * B * S * 8
+        d2h = B * S * HIDDEN * (2 if args.output_bf16 else 4)
+        out_row_shape, out_np = (1, S, spec.hidden), (np.uint16 if args.output_bf16 else np.float32)
+
+    def make_server(coalesce_ms=0):
+        return hostapi.Server(**io, replicas=[rep], device_ids=[local_rank], model_kind=kind, max_batch_size=B,
+                              pool_size=e2e_pool, nworker_per_cuda=e2e_workers, cuda_pipeline=e2e_pipeline,
+                              n_workspaces=n_pipe, batch_coalesce_timeout_ms=coalesce_ms, tile_rows=256 if coalesce_ms else 0)
+
+    srv = make_server()
+    prepared = [srv.prepare_batch([(r, 1, list(a), [None]) for r, a in enumerate(rows)]) for rows in req_rows]
+    # the same batches with a caller-owned response buffer per request: the codelet path then also makes the
+    # per-request response copy the reference makes in fill_output_tensor (inference_service_io.cpp:377-419)
+    resp = [[np.empty(out_row_shape, dtype=out_np) for _ in range(B)] for _ in range(n_sets)]
+    prepared_out = [srv.prepare_batch([(r, 1, list(a), [resp[k][r]]) for r, a in enumerate(rows)])
+                    for k, rows in enumerate(req_rows)]
     checksum, task_ms, fails = 0.0, [], 0
 
-    def run_e2e(n_steps, record):
+    def run_e2e(n_steps, record, batches):
         nonlocal checksum, fails
-        tickets = [srv.submit_prepared(prepared[i % n_sets]) for i in range(n_steps)]
+        tickets = [srv.submit_prepared(batches[i % n_sets]) for i in range(n_steps)]
         for t in tickets:
             for r in srv.wait(t, cap=B):
                 fails += 0 if r.ok == 1 else 1
@@ -318,80 +551,145 @@ def run_b200(args, rank, local_rank, world):
                     checksum += float(r.first_value)
                     task_ms.append(r.task_ms)
 
-    # auto-graph: every (worker, slot) tuple has to be seen twice before it replays a graph
-    run_e2e(max(args.warmup, 6 * e2e_workers * e2e_pool if args.auto_graph else 20), False)
-    # three back-to-back segments of K steps each, the MEDIAN segment is reported: one host-side hiccup
-    # (a descheduled worker thread) inside a 0.2 s region otherwise moves the number by 20 %
-    e2e_segments = []
-    for _ in range(3):
-        barrier()
-        t0 = time.perf_counter()
-        run_e2e(args.steps, True)
-        e2e_segments.append(time.perf_counter() - t0)
-        barrier()
-    e2e_s = sorted(e2e_segments)[1]
+    def e2e_median_of_3(batches, record):
+        # three back-to-back segments of K steps each, the MEDIAN segment is reported: one host-side hiccup
+        # (a descheduled worker thread) inside a 0.2 s region otherwise moves the number by 20 %
+        segs = []
+        for _ in range(3):
+            barrier()
+            t0 = time.perf_counter()
+            run_e2e(args.steps, record, batches)
+            segs.append(time.perf_counter() - t0)
+            barrier()
+        return sorted(segs)[1], segs
+
+    # auto-graph: a worker replays a CUDA graph from its second task of a batch shape on (one graph per shape and
+    # worker, retargeted to whatever slot a task uses)
+    run_e2e(max(args.warmup, 8 * e2e_workers), False, prepared)
+    e2e_s, e2e_segments = e2e_median_of_3(prepared, True)
+    e2e_out_s, _ = e2e_median_of_3(prepared_out, False)
     host_stats = srv.stats()
     srv.close()
-    rep.close()
     if fails:
         raise SystemExit(f"bench.py: {fails} requests failed on the e2e path")
 
     # ---------------- reduce over ranks ----------------
-    ms_total, e2e_ms = reduce_max_over_ranks([ms_total, e2e_s * 1e3], torch.device("cpu"))
+    ms_total, sus_ms, e2e_ms, e2e_out_ms = reduce_max_over_ranks([ms_total, sus_ms, e2e_s * 1e3, e2e_out_s * 1e3],
+                                                                 torch.device("cpu"))
+    e2e_value = whole_job_rate(B, args.steps, world, e2e_ms)
+
+    # ---------------- offered load through the batch collector (rank 0, N=1 only) ----------------
+    # open-loop Poisson arrivals of SINGLE requests at 50 % and 80 % of the measured e2e rate -> spu_server_enqueue
+    # -> dynamic batches up to the cap (coalesce window 2 ms, tile-aware close) -> the same task path
+    offered = None
+    if world == 1 and not args.no_offered_load and B > 1:
+        srv = make_server(coalesce_ms=2)
+        rows1 = srv.prepare_batch([(r, 1, list(a), [resp[0][r]]) for r, a in enumerate(req_rows[0])])
+        offered = {"what": "open-loop Poisson single-request arrivals through spu_server_enqueue (collector, coalesce "
+                           "2 ms, cap %d); codelet = codelet_end - codelet_start of the task a request rode in (host time of the "
+                           "asynchronous enqueue), task = task submitted -> output callback (device work + D2H), "
+                           "request = enqueued -> response copied into the caller's buffer" % B, "loads": []}
+        srv.offered_load(rows1, n_req=64 * B, rate_per_s=0.5 * e2e_value, seed=7)  # warm: graphs of the usual shapes
+        for frac in (0.5, 0.8):
+            rate = frac * e2e_value
+            n_req = int(min(60000, max(2000, rate * 1.5)))
+            r = srv.offered_load(rows1, n_req=n_req, rate_per_s=rate, seed=11)
+            offered["loads"].append({
+                "offered_fraction_of_e2e": frac, "offered_per_s": rate, "achieved_per_s": n_req / r["elapsed_s"],
+                "requests": n_req, "failed": r["failed"], "mean_batch_rows": float(r["batch_rows"].mean()),
+                "codelet_ms": {"p50": float(np.percentile(r["codelet_ms"], 50)), "p99": float(np.percentile(r["codelet_ms"], 99))},
+                "task_ms": {"p50": float(np.percentile(r["task_ms"], 50)), "p99": float(np.percentile(r["task_ms"], 99))},
+                "request_ms": {"p50": float(np.percentile(r["latency_ms"], 50)), "p99": float(np.percentile(r["latency_ms"], 99))}})
+        srv.close()
+    rep.close()
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
 
     peaks = load_peaks()
-    if args.precision == "fp8":
-        # no measured FP8 figure in MEASURED_PEAKS.json: 2x the measured bf16 one (the nominal FP8:bf16 ratio)
-        peaks["tflops"] *= 2.0
-        peaks["source"] += " x 2 for FP8 E4M3 (nominal ratio, not measured)"
+    fp8 = precision.startswith("fp8")
     value = whole_job_rate(B, args.steps, world, ms_total)
-    e2e_value = whole_job_rate(B, args.steps, world, e2e_ms)
-    gemm_flop_step = LAYERS * 24 * true_tokens * HIDDEN * HIDDEN  # charged on true lengths
-    gemm_tflops = gemm_flop_step / (gemm_ms / 1e3) / 1e12
+    if is_vit:
+        dense_flop_step = (2 * 196 * 768 * 1024 + 24 * 24 * 197 * 1024 * 1024 + 2 * 1024 * 1000) * B
+        tf = dense_flop_step / (ms_total / args.steps / 1e3) / 1e12
+        roofline = {"bound": "tensor", "kernel": "gemm_tcgen05_kernel (patch-embed, QKV, attn-out, MLP1, MLP2, head; "
+                                                 "98 launches/step)",
+                    "achieved": tf, "peak": peaks["tflops"], "unit": "TFLOP/s", "frac": tf / peaks["tflops"],
+                    "peak_source": peaks["source"] + ", sustained bf16", "traffic": None,
+                    "flops_per_step": dense_flop_step, "kernel_ms_per_step": None,
+                    "how": "LOWER bound: dense-GEMM FLOPs of the step over the WHOLE step's device time (attention, "
+                           "LayerNorm and im2col kernels included); no GEMM-only chain hook exists for ViT"}
+    else:
+        gemm_flop_step = LAYERS * 24 * true_tokens * HIDDEN * HIDDEN  # charged on true lengths
+        gemm_tflops = gemm_flop_step / (gemm_ms / 1e3) / 1e12
+        peak_s, peak_b = peaks["tflops"], peaks["tflops_burst"]
+        note = ""
+        if fp8:
+            # no measured FP8 figure in MEASURED_PEAKS.json: 2x the measured bf16 one (the nominal FP8:bf16 ratio),
+            # scaled by the share of GEMM FLOPs the gate-passing plan runs in FP8 would understate the peak: keep 2x
+            peak_s, peak_b = 2 * peak_s, 2 * peak_b
+            note = " x 2 for FP8 E4M3 (nominal ratio, not measured; the default plan runs 58 % of the GEMM FLOPs in FP8)"
+        roofline = {"bound": "tensor", "kernel": "gemm_tcgen05_kernel (QKV, attn-out, FFN1, FFN2; 48 launches/step)",
+                    "achieved": gemm_tflops, "peak": peak_b, "unit": "TFLOP/s", "frac": gemm_tflops / peak_b,
+                    "peak_source": peaks["source"] + ": bf16_tflops (burst) -- the chain is timed alone for a few ms" + note,
+                    "frac_of_sustained_peak": gemm_tflops / peak_s, "peak_sustained": peak_s,
+                    **gemm_traffic(B, S, precision),
+                    "flops_per_step": gemm_flop_step, "kernel_ms_per_step": gemm_ms,
+                    "whole_step_tflops": gemm_flop_step / (ms_total / args.steps / 1e3) / 1e12,
+                    "how": "48 GEMM launches x 5 forwards back to back in one CUDA graph, CUDA events on the launch stream"}
     line = {
-        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "metric": metric_name(cfg), "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "bf16" if args.precision == "bf16" else "fp8_e4m3",
-        "data": "synthetic",
-        "config": {"workload": f"BERT-base seq{S} dynamic batch at cap {B}, {args.precision}, one weight replica per B200 "
-                               + ("(BASELINE configs[1])" if (B, S, args.precision, args.min_len) == (32, 128, "bf16", None)
-                                  else "(variant of BASELINE configs[1])")
-                               + "; random-init weights seed 0, ids U[0,30522), "
-                               + ("all-ones mask" if args.min_len is None else f"lengths U[{args.min_len},{S}] padded+masked"),
-                   "batch": B, "seq_len": S, "replicas": world, "output_dtype": "bf16" if args.output_bf16 else "f32", "resident_streams": n_str,
-                   "mean_true_tokens_per_batch": true_tokens,
-                   "l2": "no explicit flush: each step streams 170 MB of bf16 weights plus ~110 MB of activations "
-                         "(> 126 MB L2) and input batches rotate over 4 distinct buffers"},
+        "scaling": "weak", "vs_baseline": None,
+        "dtype": "bf16" if precision == "bf16" else "fp8_e4m3", "data": "synthetic",
+        "config": workload_config(cfg, world),
+        "run": {"output_dtype": "bf16" if args.output_bf16 else "f32", "resident_streams": n_str,
+                "mean_true_tokens_per_batch": true_tokens, "cores_per_rank": pinned_cores,
+                "gemm_tiles": None if is_vit or not args.autotune else {
+                    "how": "warm-up autotune: every (cta_group, BLOCK_N) timed per GEMM problem, winner installed",
+                    "differ_from_cost_model": tuned_changed,
+                    "chosen": [{k: t[k] for k in ("N", "K", "epilogue", "fp8", "cta_group", "block_n", "us")} for t in tuned]},
+                "l2": "no explicit flush: each step streams >= 170 MB of weights plus >= 110 MB of activations "
+                      "(> 126 MB L2) and input batches rotate over distinct buffers"},
+        "value_sustained": {"value": whole_job_rate(B, sus_steps, world, sus_ms), "unit": UNIT, "steps": sus_steps,
+                            "seconds": sus_ms / 1e3, "ms_per_step": sus_ms / sus_steps,
+                            "clocks": clocks["sustained_loop"]},
         "clocks": clocks,
-        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 2 * B * S * 8,
-                "d2h_bytes_per_step": B * S * HIDDEN * (2 if args.output_bf16 else 4), "checksum": checksum,
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "checksum": checksum,
                 "path": "libspu_host.so: per-request host buffers -> host gather -> task -> H2D -> codelet -> D2H -> "
-                        f"slices ({e2e_workers} CUDA workers x pipeline {e2e_pipeline}, pool {e2e_pool}, "
-                        + ("CUDA-graph replay per (worker, slot) tuple)" if args.auto_graph else "eager launches)"),
+                        f"per-request views of the pinned output slot ({e2e_workers} CUDA workers x pipeline "
+                        f"{e2e_pipeline}, pool {e2e_pool}, "
+                        + ("one CUDA graph per (worker, batch shape), retargeted to the task's slot)" if (args.auto_graph and not is_vit) else "eager launches)"),
+                "delivered": {"value": whole_job_rate(B, args.steps, world, e2e_out_ms), "unit": UNIT,
+                              "what": "the same path plus the per-request response copy into caller-owned buffers "
+                                      "(the reference's fill_output_tensor), on the completer threads"},
                 "tasks": int(host_stats["tasks"]),
                 "how": f"median of 3 segments of {args.steps} steps (rank 0 segments, inferences/s: "
                        + ", ".join(f"{B * args.steps * world / t:.0f}" for t in e2e_segments) + ")",
                 "task_latency_ms": {"p50": float(np.percentile(task_ms, 50)), "p99": float(np.percentile(task_ms, 99)),
-                                    "what": "submit -> output callback per task, queueing included"}},
+                                    "what": "submit -> output callback per task with all K tasks queued at once "
+                                            "(a queue-depth figure; see offered_load for latency at a stated load)"}},
+        "offered_load": offered,
         "gpu_launches": launches * args.steps,
         "latency_ms": {"p50": float(np.percentile(lat, 50)), "p99": float(np.percentile(lat, 99)),
                        "what": "device time of one task (batch) = codelet_start..codelet_end"},
-        "roofline": {"bound": "tensor", "kernel": "gemm_tcgen05_kernel (QKV, attn-out, FFN1, FFN2; 48 launches/step)",
-                     "achieved": gemm_tflops, "peak": peaks["tflops"], "unit": "TFLOP/s",
-                     "frac": gemm_tflops / peaks["tflops"], "peak_source": peaks["source"], **gemm_traffic(B, S, args.precision),
-                     "flops_per_step": gemm_flop_step, "kernel_ms_per_step": gemm_ms,
-                     "how": "48 GEMM launches x 5 forwards back to back in one CUDA graph, CUDA events on the launch stream"},
+        "roofline": roofline,
         "stage_ms_per_step": stage_ms,
     }
     if world == 1 and not args.no_cpu_baseline:
-        v, times, done, threads = cpu_codelet_forward(B, S, budget_s=20.0, max_steps=20, warmup=1)
-        line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
-                                "sample": f"{done} forward passes of batch {B} x seq {S} "
-                                          "(TorchScript fp32 on the host cores)"}
+        codelet = CpuCodelet(cfg)
+        sample = [a[:prow] for a in host[0]]
+        ref, times = codelet.run(sample, warmup=1, iters=3 if prow * S <= 8192 and not is_vit else 2)
+        v = prow * len(times) / (sum(times) / 1e3)
+        line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": codelet.threads, "kind": codelet.kind,
+                                "sample": f"{len(times)} tasks of {prow} requests of input set 0 ({codelet.describe()})",
+                                "b1": b1_latency(codelet, cfg)}
+        live = None if is_vit or cfg["min_len"] is None else host[0][1][:prow]
+        line["parity"] = parity_block(got, ref, precision, live)
+    else:
+        line["parity"] = None
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
@@ -417,30 +715,35 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=10)
-    ap.add_argument("--batch", type=int, default=32)
-    ap.add_argument("--seq", type=int, default=128)
+    ap.add_argument("--config", default="B", choices=sorted(CONFIGS), help="BASELINE.json workload (default B = configs[1])")
+    ap.add_argument("--batch", type=int, default=None, help="override the config's batch (marks the run a variant)")
+    ap.add_argument("--seq", type=int, default=None)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--precision", default="bf16", choices=["bf16", "fp8", "fp8x6"])
+    ap.add_argument("--precision", default=None, choices=["bf16", "fp8", "fp8x6"])
     ap.add_argument("--min-len", type=int, default=None, help="variable-length requests: lengths U[min_len, seq]")
     ap.add_argument("--streams", type=int, default=2, help="CUDA workers issuing resident tasks round-robin")
-    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the CPU leg (also drops the parity block)")
+    ap.add_argument("--no-offered-load", action="store_true")
+    ap.add_argument("--no-autotune", dest="autotune", action="store_false",
+                    help="keep the static cost model's GEMM tiles instead of timing the candidates at warm-up")
+    ap.add_argument("--no-pin", action="store_true", help="N>1: do not give each rank its own slice of the host cores")
     ap.add_argument("--output-bf16", action="store_true",
                     help="variant: output0 as bf16 (SPU_OUTPUT_BF16, SURVEY 8(f) row 3): half the response bytes")
     ap.add_argument("--no-auto-graph", dest="auto_graph", action="store_false",
                     help="e2e path launches every kernel eagerly instead of replaying CUDA graphs captured on the second "
-                         "sighting of a (worker, slot) tuple (SPU_FORWARD_AUTO_GRAPH; profiles/r06_e2e_config.md: "
-                         "33.7k vs 32.2k inf/s at N=1, 259k vs 220k at N=8 where host cores are scarce)")
+                         "sighting of a (worker, slot) tuple (SPU_FORWARD_AUTO_GRAPH; profiles/r06_e2e_config.md)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
+    cfg = resolve_config(args)
+    if cfg["model"] == "vit" and (cfg["precision"] != "bf16" or args.output_bf16):
+        raise SystemExit("bench.py: config E (ViT-L/16) runs in bf16 with fp32 logits")
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     if args.impl == "reference":
-        if args.steps > 40:
-            args.steps = 40  # bounded sample: ~1 s per batch-32 step on 8 cores
-        run_reference(args, rank, world)
+        run_reference(args, cfg, rank, world)
     else:
-        run_b200(args, rank, local_rank, world)
+        run_b200(args, cfg, rank, local_rank, world)
 
 
 if __name__ == "__main__":

@@ -121,6 +121,26 @@ spu_status spu_bert_forward_async(spu_replica *r, int32_t ws_idx,
 /* Number of kernel launches one forward of (batch, seq) enqueues. */
 int32_t spu_bert_forward_launch_count(const spu_replica *r);
 
+/* Warm-up autotune (the reference's hook is its fixed-worker warm-up pass,
+ * src/core/warmup.cpp:226-299).  For every distinct GEMM problem a forward of (batch, seq) launches -- QKV,
+ * attention-output, FFN1, FFN2 in the operand formats the replica's plan uses -- times each (cta_group, BLOCK_N)
+ * tile the kernel is built for, on the replica's own weights and workspace ws_idx (20 launches back to back in a
+ * CUDA graph, best of 3), and lets the winner replace the static cost model's choice for exactly that
+ * (N, K, epilogue, format, M = batch*seq).  Other M keep the cost model.  START-UP ONLY: synchronises the
+ * device, clobbers the workspace activations and drops captured graphs.  *n_changed (may be NULL) = problems
+ * whose winner differs from the cost model's tile. */
+spu_status spu_bert_autotune(spu_replica *r, int32_t ws_idx, int32_t batch, int32_t seq, void *stream,
+                             int32_t *n_changed);
+/* The measured winners: rows of 8 int32 {N, K, epilogue, operand format (0 bf16 / 1 e4m3), M, cta_group, BLOCK_N,
+ * nanoseconds per launch}; returns the number of rows the table holds. */
+int32_t spu_bert_tuned_configs(const spu_replica *r, int32_t *out, int32_t cap_rows);
+
+/* CUDA graphs cached for workspace ws_idx (spu_bert_forward_capture / SPU_FORWARD_AUTO_GRAPH).  A graph is keyed
+ * by (batch, seq) only: launching it with other ids / mask / out pointers patches the two kernels that hold
+ * them, so a worker keeps ONE graph per batch shape however many slots it serves; at most 64 per workspace,
+ * least recently used evicted.  -1 on a bad argument. */
+int32_t spu_bert_graph_count(const spu_replica *r, int32_t ws_idx);
+
 /* Stages 1-4 in one call, on PER-REQUEST buffers (SURVEY 8(f) rows 1+2 at the codelet level;
  * replaces the host staging copy of SlotManager::copy_job_inputs_to_slot,
  * slot_manager_component.cpp:649-727, and the slot slicing of batching_helpers.hpp:74-127).

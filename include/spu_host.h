@@ -85,6 +85,24 @@ typedef struct spu_server_cfg {
    * (n_devices x nworker_per_cuda entries), as build_gpu_replica_assignments orders them
    * (src/core/inference_runner.cpp:128-183). */
   int32_t gpu_model_replication;
+  /* SURVEY 8(f) row 4 (tile-aware batching): > 0 = row tile of the codelet's GEMMs (256 for the CTA-pair tiles of
+   * libspu_b200).  When the coalesce window of a dynamic batch closes on rows x seq token rows that end inside
+   * a tile, the collector waits a bounded grace (a quarter of batch_coalesce_timeout_ms) for the requests that
+   * complete the tile and takes no more than complete it.  0 = the reference's timer-only rule. */
+  int32_t tile_rows;
+  /* SURVEY 8(f) row 2 (device-resident gather / scatter): != 0 declares that every request's input buffers AND its
+   * output buffer are DEVICE-VISIBLE (cudaHostAlloc / cudaHostRegister'ed host memory, or device memory).  The
+   * host then copies nothing: the task's first input slot carries a table of row addresses, and the codelet runs
+   * gather + pad + mask -> encoder -> per-request scatter on the GPU (spu_bert_forward_requests_async), writing
+   * each response straight into the request's own buffer ([batch, own seq, hidden] fp32).  BERT models whose
+   * replicas were created with SPU_REQUEST_IO; every request must bring an output buffer.  Replaces
+   * copy_job_inputs_to_slot (slot_manager_component.cpp:649-727) and slice_outputs_for_sub_job
+   * (batching_helpers.hpp:74-127) on that path. */
+  int32_t device_visible_requests;
+  /* Warm-up autotune (src/core/warmup.cpp:226-299 is the reference's warm-up hook): != 0 runs
+   * spu_bert_autotune on every BERT replica for the full batch shape (max_batch_size x inputs[0].dims[1]) before
+   * the first task, so the GEMM tiles of the steady-state batch are measured winners, not cost-model guesses. */
+  int32_t warmup_autotune;
 } spu_server_cfg;
 
 typedef struct spu_request {
@@ -131,6 +149,16 @@ int64_t spu_server_enqueue(spu_server *s, const spu_request *req);
  * request order) and returns how many the ticket held.  A ticket can be waited once. */
 int32_t spu_server_wait(spu_server *s, int64_t ticket, spu_result *results, int32_t cap);
 int32_t spu_server_wait_all(spu_server *s);
+/* Measurement (bench.py's offered-load leg): an OPEN-LOOP load generator in front of the batch collector.  n_req
+ * requests arrive as a Poisson process of `rate_per_s` (seeded), request i is rows[i % n_rows] (per-request host
+ * buffers the caller keeps alive) passed to spu_server_enqueue; afterwards every ticket is waited.  Per request
+ * (arrays of n_req, may be NULL): codelet_ms = codelet_end - codelet_start of the task it rode in
+ * (starpu_setup.cpp:645-649,718-722; the host time of the asynchronous enqueue), task_ms = task submitted ->
+ * output callback (device work + D2H included), latency_ms = enqueued -> callback end (response copied),
+ * batch_rows = the effective batch of that task.  Returns the number of failed requests, -1 on a usage / submission error. */
+int32_t spu_server_offered_load(spu_server *s, const spu_request *rows, int32_t n_rows, int64_t n_req,
+                                double rate_per_s, uint64_t seed, double *codelet_ms, double *task_ms,
+                                double *latency_ms, int32_t *batch_rows, double *elapsed_s);
 /* counters: [0] tasks submitted, [1] requests completed, [2] free input slots, [3] free
  * output slots, [4] StarPU workers, [5] codelet failures */
 void spu_server_stats(spu_server *s, int64_t out[6]);
@@ -169,6 +197,9 @@ int32_t spu_host_gather_to_slot(const void *const *srcs, const uint64_t *nbytes,
  * offset and length of the view through *off_out / *len_out and the processed length. */
 int64_t spu_host_slice_rows(uint64_t rows, uint64_t row_bytes, int64_t offset, int64_t batch_size, uint64_t *off_out,
                             uint64_t *len_out);
+/* the collector's tile-aware rule: 1 when a batch of rows x seq token rows ends inside a GEMM row tile and may
+ * still grow (rows < max_rows) */
+int32_t spu_host_tile_aware_wants_more(int64_t rows, int64_t seq, int64_t max_rows, int32_t tile_rows);
 /* can_merge_jobs over two single-input requests described by dims/dtype */
 int32_t spu_host_can_merge(const int64_t *dims_a, int32_t nd_a, int32_t dt_a, const int64_t *dims_b, int32_t nd_b,
                            int32_t dt_b);

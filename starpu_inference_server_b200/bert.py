@@ -89,6 +89,27 @@ class BertReplica:
     def launches_per_forward(self) -> int:
         return capi.lib().spu_bert_forward_launch_count(self._h)
 
+    def autotune(self, batch: int, seq: int, ws: int = 0, stream=None) -> int:
+        """Warm-up autotune of the GEMM tiles for forwards of (batch, seq); start-up only.  Returns how many
+        problems ended on another tile than the static cost model's."""
+        changed = C.c_int32()
+        capi.check(capi.lib().spu_bert_autotune(self._h, ws, batch, seq, capi.stream_ptr(stream), C.byref(changed)))
+        return changed.value
+
+    def tuned_configs(self):
+        """[{N, K, epilogue, fp8, M, cta_group, block_n, us}] measured by autotune()."""
+        n = capi.lib().spu_bert_tuned_configs(self._h, None, 0)
+        buf = (C.c_int32 * (8 * max(n, 1)))()
+        capi.lib().spu_bert_tuned_configs(self._h, buf, n)
+        keys = ("N", "K", "epilogue", "fp8", "M", "cta_group", "block_n", "ns")
+        rows = [dict(zip(keys, buf[8 * i:8 * i + 8])) for i in range(n)]
+        for r in rows:
+            r["us"] = r.pop("ns") / 1e3
+        return rows
+
+    def graph_count(self, ws: int = 0) -> int:
+        return capi.lib().spu_bert_graph_count(self._h, ws)
+
     def forward_async(self, ids, mask, out, ws: int = 0, stream=None):
         """ids/mask: int64 CUDA tensors [B,S]; out: fp32 CUDA tensor [B,S,hidden]."""
         b, s = ids.shape

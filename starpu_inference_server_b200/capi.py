@@ -33,7 +33,7 @@ SYMBOLS = [
     "spu_bert_output_bytes", "spu_vit_replica_create", "spu_vit_forward_async", "spu_vit_input_bytes",
     "spu_vit_output_bytes", "spu_bert_stage_chain_ms", "spu_bert_calibrate_fp8", "spu_bert_fp8_scales",
     "spu_gemm_fp8_async", "spu_quantize_e4m3_async", "spu_bert_set_fp8_mask", "spu_bert_get_fp8_mask",
-    "spu_gemm_ln_bf16_async",
+    "spu_gemm_ln_bf16_async", "spu_bert_graph_count", "spu_bert_autotune", "spu_bert_tuned_configs",
 ]
 
 
@@ -75,6 +75,12 @@ def lib():
     L.spu_bert_forward_async.argtypes = [vp, i32, vp, vp, i32, i32, vp, vp]
     L.spu_bert_forward_capture.argtypes = [vp, i32, vp, vp, i32, i32, vp, vp]
     L.spu_bert_forward_profiled.argtypes = [vp, i32, vp, vp, i32, i32, vp, vp, C.POINTER(f32)]
+    L.spu_bert_autotune.argtypes = [vp, i32, i32, i32, vp, C.POINTER(i32)]
+    L.spu_bert_autotune.restype = i32
+    L.spu_bert_tuned_configs.argtypes = [vp, C.POINTER(i32), i32]
+    L.spu_bert_tuned_configs.restype = i32
+    L.spu_bert_graph_count.argtypes = [vp, i32]
+    L.spu_bert_graph_count.restype = i32
     L.spu_bert_forward_launch_count.argtypes = [vp]
     L.spu_gather_pad_mask_async.argtypes = [vp, vp, vp, i32, i32, i64, vp, vp, vp]
     L.spu_gather_segments_async.argtypes = [vp, vp, vp, i32, vp, vp]

@@ -6,6 +6,7 @@
 #include <deque>
 #include <map>
 #include <mutex>
+#include <random>
 #include <thread>
 
 #include "../../include/spu_host.h"
@@ -52,6 +53,12 @@ struct Ticket {
   int expected = 0, done = 0;
   std::vector<spu_result> results;
 };
+
+// Does a batch of `rows` requests x `seq` tokens end inside a GEMM row tile, with room left to grow?
+bool tile_aware_wants_more(int64_t rows, int64_t seq, int64_t max_rows, int tile_rows) {
+  if (tile_rows <= 0 || rows >= max_rows) return false;
+  return (rows * std::max<int64_t>(seq, 1)) % tile_rows != 0;
+}
 }  // namespace
 
 struct spu_server {
@@ -73,6 +80,7 @@ struct spu_server {
   bool stop = false;
   int coalesce_ms = 0;
   int length_bucket = 0;  // variable_length: requests per ceil(L / length_bucket) bucket batch together
+  int tile_rows = 0;      // > 0: GEMM row tile of the codelet's kernels; see tile_aware_close()
   int forming = 0;  // batches popped from the queue but not yet submitted (guarded by qmu)
 
   std::shared_ptr<InferenceJob> make_job(const spu_request &rq, int64_t ticket, int index) {
@@ -91,6 +99,7 @@ struct spu_server {
       job->inputs.push_back(std::move(t));
     }
     std::vector<void *> dsts(rq.outputs, rq.outputs + model.outputs.size());
+    if (model.device_visible_requests) job->output_dsts = dsts;  // the codelet scatters straight into them
     // variable_length: the sequence length this request's response is laid out with
     const int64_t own_seq = model.variable_length && !job->inputs.empty() && job->inputs[0].dims.size() >= 2
                                 ? job->inputs[0].dims[1]
@@ -124,7 +133,7 @@ struct spu_server {
         // batch is compacted sample by sample to [batch, own_seq, ...], never the padded [batch, batch_seq, ...].
         for (size_t o = 0; o < res.outputs.size() && o < dsts.size(); ++o) {
           const HostTensor &v = res.outputs[o];
-          if (!dsts[o] || !v.defined()) continue;
+          if (!dsts[o] || !v.defined() || v.data == dsts[o]) continue;  // == : written in place by the codelet
           if (own_seq > 0 && res.batch_seq > own_seq && v.dims.size() >= 2 && v.dims[1] == res.batch_seq) {
             const size_t samples = static_cast<size_t>(v.dims[0]);
             const size_t padded = v.nbytes() / samples;
@@ -221,6 +230,32 @@ struct spu_server {
           batch.push_back(cand);
           queue.pop_front();
         }
+        // Tile-aware preference (the reference's hook for batch-size policy is
+        // AdaptiveBatchingStrategy::decide, batching_strategy.cpp:195-236): the encoder GEMMs run over
+        // M = rows x seq token rows in tiles of `tile_rows`; a batch that ends inside a tile pays for the whole
+        // tile.  When the coalesce window closed on such a batch, spend a bounded grace (a quarter of the window)
+        // on arrivals that complete the tile -- and take no more than complete it.
+        if (tile_rows > 0 && coalesce_ms > 0 && !bucketing && !stop) {
+          const auto grace_end = deadline + std::chrono::microseconds(250 * coalesce_ms);
+          auto seq_of = [&](const InferenceJob &j) {
+            return j.inputs.empty() || j.inputs[0].dims.size() < 2 ? int64_t{1} : j.inputs[0].dims[1];
+          };
+          int64_t seq = seq_of(*batch[0]);
+          for (const auto &j : batch) seq = std::max(seq, seq_of(*j));
+          while (tile_aware_wants_more(rows, seq, model.max_batch_size, tile_rows)) {
+            if (queue.empty()) {
+              if (qcv.wait_until(lk, grace_end) == std::cv_status::timeout && queue.empty()) break;
+              if (queue.empty()) continue;
+            }
+            auto &cand = queue.front();
+            if (!can_merge_jobs(batch[0].get(), cand.get(), model.variable_length)) break;
+            if (rows + cand->batch_size() > model.max_batch_size) break;
+            seq = std::max(seq, seq_of(*cand));
+            rows += cand->batch_size();
+            batch.push_back(cand);
+            queue.pop_front();
+          }
+        }
       }
       try {
         runner->submit_batch(batch);
@@ -280,7 +315,11 @@ int32_t spu_server_create(const spu_server_cfg *cfg, spu_server **out) {
       s->model.max_batch_size = cfg->max_batch_size > 0 ? cfg->max_batch_size : 1;
       s->model.pool_size = cfg->pool_size > 0 ? cfg->pool_size : 12;
       s->model.variable_length = cfg->variable_length != 0;
+      s->model.device_visible_requests = cfg->device_visible_requests != 0;
+      if (s->model.device_visible_requests && cfg->model_kind != SPU_MODEL_BERT)
+        throw std::invalid_argument("device_visible_requests is a BERT-path feature");
       s->length_bucket = cfg->length_bucket > 0 ? cfg->length_bucket : 0;
+      s->tile_rows = cfg->tile_rows > 0 ? cfg->tile_rows : 0;
       s->coalesce_ms = cfg->batch_coalesce_timeout_ms;
       // build_gpu_replica_assignments (inference_runner.cpp:128-183): one replica per device, or per CUDA worker
       // (gpu_model_replication: per_worker); cfg->replicas[i] serves assignment i.  The caller created them
@@ -306,6 +345,13 @@ int32_t spu_server_create(const spu_server_cfg *cfg, spu_server **out) {
                                            : std::string()));
         s->registry.add(assignments[i], m, /*owned=*/false);
       }
+      if (cfg->warmup_autotune != 0 && cfg->model_kind == SPU_MODEL_BERT && s->model.inputs[0].dims.size() >= 2)
+        for (size_t i = 0; i < s->registry.size(); ++i) {
+          spu_replica *rep = s->registry.model(i)->replica;
+          if (spu_bert_autotune(rep, 0, s->model.max_batch_size, static_cast<int32_t>(s->model.inputs[0].dims[1]),
+                                nullptr, nullptr) != SPU_OK)
+            throw std::runtime_error(std::string("warm-up autotune failed: ") + spu_last_error());
+        }
       s->runner = std::make_unique<TaskRunner>(s->model, &s->registry);
       spu_server *raw = s.get();
       s->collector = std::thread([raw] { raw->collector_loop(); });
@@ -407,6 +453,52 @@ int32_t spu_server_wait_all(spu_server *s) {
   }
   s->runner->wait_for_all();
   return 0;
+}
+
+int32_t spu_host_tile_aware_wants_more(int64_t rows, int64_t seq, int64_t max_rows, int32_t tile_rows) {
+  return tile_aware_wants_more(rows, seq, max_rows, tile_rows) ? 1 : 0;
+}
+
+int32_t spu_server_offered_load(spu_server *s, const spu_request *rows, int32_t n_rows, int64_t n_req,
+                                double rate_per_s, uint64_t seed, double *codelet_ms, double *task_ms,
+                                double *latency_ms, int32_t *batch_rows, double *elapsed_s) {
+  if (!s || !rows || n_rows <= 0 || n_req <= 0 || !(rate_per_s > 0.0)) {
+    set_host_error("offered_load: bad argument");
+    return -1;
+  }
+  // open loop: arrival i happens at the i-th point of a Poisson process whatever the server does
+  std::mt19937_64 rng(seed);
+  std::exponential_distribution<double> gap(rate_per_s);
+  std::vector<int64_t> tickets(static_cast<size_t>(n_req), -1);
+  const auto t0 = std::chrono::steady_clock::now();
+  double t_arrive = 0.0;
+  for (int64_t i = 0; i < n_req; ++i) {
+    t_arrive += gap(rng);
+    const auto due = t0 + std::chrono::duration_cast<std::chrono::steady_clock::duration>(
+                              std::chrono::duration<double>(t_arrive));
+    for (;;) {
+      const auto now = std::chrono::steady_clock::now();
+      if (now >= due) break;
+      if (due - now > std::chrono::microseconds(200)) std::this_thread::sleep_for(due - now - std::chrono::microseconds(100));
+      else std::this_thread::yield();
+    }
+    spu_request rq = rows[i % n_rows];
+    rq.request_id = static_cast<int32_t>(i);
+    tickets[static_cast<size_t>(i)] = spu_server_enqueue(s, &rq);
+    if (tickets[static_cast<size_t>(i)] < 0) return -1;
+  }
+  int32_t failed = 0;
+  for (int64_t i = 0; i < n_req; ++i) {
+    spu_result r{};
+    if (spu_server_wait(s, tickets[static_cast<size_t>(i)], &r, 1) != 1) return -1;
+    failed += r.ok == 1 ? 0 : 1;
+    if (codelet_ms) codelet_ms[i] = r.codelet_ms;
+    if (task_ms) task_ms[i] = r.task_ms;
+    if (latency_ms) latency_ms[i] = r.latency_ms;
+    if (batch_rows) batch_rows[i] = static_cast<int32_t>(r.batch_rows);
+  }
+  if (elapsed_s) *elapsed_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+  return failed;
 }
 
 void spu_server_stats(spu_server *s, int64_t out[6]) {

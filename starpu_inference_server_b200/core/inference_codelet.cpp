@@ -175,6 +175,21 @@ void run_inference(InferenceParams *params, StarpuBufferSpan buffers, int device
       const int64_t S = dim_or(params, 0, 1, 0);
       if (B <= 0 || S <= 0 || B > INT32_MAX || S > INT32_MAX)
         throw InferenceExecutionException("[ERROR] Invalid BERT input dims");
+      if (params->request_io.enabled) {
+        // stages 1-4 on per-request buffers: buffers[0] carries the address table the host wrote
+        const detail::RequestIo &io = params->request_io;
+        if (io.rows != B || io.seq != S || io.table_bytes == 0)
+          throw InferenceExecutionException("[ERROR] Request table does not match the task layout");
+        require_bytes(buffers[0], io.table_bytes, "Input");
+        const auto base = static_cast<uintptr_t>(buffers[0]->ptr);
+        const int ws = workspace_for_this_thread(model);
+        check_spu(spu_bert_forward_requests_async(
+            model->replica, ws, reinterpret_cast<const int64_t *const *>(base),
+            reinterpret_cast<const int64_t *const *>(base + io.off_mask), reinterpret_cast<const int32_t *>(base + io.off_len),
+            static_cast<int32_t>(B), static_cast<int32_t>(S), reinterpret_cast<float *const *>(base + io.off_dst),
+            io.full_rows ? 1 : 0, stream));
+        break;
+      }
       const size_t in_bytes = static_cast<size_t>(B) * static_cast<size_t>(S) * sizeof(int64_t);
       require_bytes(buffers[0], in_bytes, "Input");
       require_bytes(buffers[1], in_bytes, "Input");

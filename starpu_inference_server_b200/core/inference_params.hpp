@@ -89,6 +89,21 @@ struct Limits {
   size_t max_inputs = 0;
   size_t max_dims = 0;
 };
+
+// SURVEY 8(f) row 2 (device-resident gather / scatter over per-request buffers).  When `enabled`, buffers[0]
+// of the task is not the gathered [B, S] ids array but a table of DEVICE-VISIBLE addresses the host wrote into
+// the input slot -- one entry per sample row -- and the codelet runs stages 1-4 in one call
+// (spu_bert_forward_requests_async): it replaces copy_job_inputs_to_slot
+// (slot_manager_component.cpp:649-727) and the slot slicing (batching_helpers.hpp:74-127).  Layout of the table
+// (byte offsets from buffers[0]->ptr): ids pointers at 0, mask pointers at off_mask, destination pointers at
+// off_dst (8 bytes each), int32 true lengths at off_len.
+struct RequestIo {
+  bool enabled = false;
+  int64_t rows = 0;  // sample rows of the batch
+  int64_t seq = 0;   // padded sequence length of the batch
+  bool full_rows = true;  // destinations take `seq` rows each (false: only their own length)
+  size_t off_mask = 0, off_dst = 0, off_len = 0, table_bytes = 0;
+};
 }  // namespace detail
 
 struct InferenceParams {
@@ -97,6 +112,7 @@ struct InferenceParams {
   detail::DeviceInfo device;
   detail::Timing timing;
   detail::Limits limits{};
+  detail::RequestIo request_io{};
   size_t num_inputs = 0;
   size_t num_outputs = 0;
   int64_t batch_size = 1;

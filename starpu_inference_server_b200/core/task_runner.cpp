@@ -166,6 +166,58 @@ auto slice_outputs_for_sub_job(const std::vector<HostTensor> &aggregated_outputs
   return result;
 }
 
+// instead of gathering the requests' bytes, describe them.  One entry per sample row of the
+// batch, in request order: where its token ids and mask words live, how many there are, and where its hidden
+// states go ([own seq, hidden] fp32 on a variable_length server, [seq, hidden] otherwise).  The table rides in the
+// first input slot (what StarPU copies to the device is these few bytes); the second slot shrinks to one element.
+void write_request_table(const std::vector<std::shared_ptr<InferenceJob>> &jobs,
+                         const std::vector<starpu_data_handle_t> &handles, const std::vector<std::byte *> &base_ptrs,
+                         const std::vector<HostBufferInfo> &buffer_infos, int64_t rows, int64_t seq,
+                         size_t token_bytes, detail::RequestIo *io) {
+  if (handles.size() != 2 || base_ptrs.size() != 2)
+    throw InputPoolMismatchException("device_visible_requests needs the two BERT inputs (input_ids, attention_mask)");
+  const size_t n = static_cast<size_t>(rows);
+  io->enabled = true;
+  io->rows = rows;
+  io->seq = seq;
+  io->off_mask = n * sizeof(void *);
+  io->off_dst = 2 * n * sizeof(void *);
+  io->off_len = 3 * n * sizeof(void *);
+  io->table_bytes = (io->off_len + n * sizeof(int32_t) + 7) / 8 * 8;
+  if (buffer_infos[0].bytes < io->table_bytes)
+    throw InputPoolCapacityException("Request table exceeds allocated slot buffer capacity");
+  std::byte *base = base_ptrs[0];
+  auto **ids_tab = reinterpret_cast<const void **>(base);
+  auto **mask_tab = reinterpret_cast<const void **>(base + io->off_mask);
+  auto **dst_tab = reinterpret_cast<void **>(base + io->off_dst);
+  auto *len_tab = reinterpret_cast<int32_t *>(base + io->off_len);
+  bool ragged = false;
+  size_t r = 0;
+  for (const auto &job : jobs) {
+    if (!job) continue;
+    if (job->inputs.size() != 2 || job->inputs[0].dims.size() != 2 || job->inputs[0].type != ScalarType::Int64 ||
+        job->inputs[1].type != ScalarType::Int64 || job->inputs[1].dims != job->inputs[0].dims)
+      throw InvalidInputTensorException("device_visible_requests: inputs must be two int64 [batch, seq] arrays");
+    if (job->output_dsts.empty() || job->output_dsts[0] == nullptr)
+      throw InvalidInferenceJobException("device_visible_requests: every request needs a device-visible output buffer");
+    const int64_t b = job->inputs[0].dims[0], L = job->inputs[0].dims[1];
+    if (L < 1 || L > seq) throw InvalidInputTensorException("device_visible_requests: request longer than the batch");
+    ragged = ragged || L != seq;
+    for (int64_t s = 0; s < b; ++s, ++r) {
+      if (r >= n) throw InputPoolCapacityException("Batch size exceeds input pool capacity");
+      ids_tab[r] = job->inputs[0].data + static_cast<size_t>(s * L) * sizeof(int64_t);
+      mask_tab[r] = job->inputs[1].data + static_cast<size_t>(s * L) * sizeof(int64_t);
+      len_tab[r] = static_cast<int32_t>(L);
+      dst_tab[r] = static_cast<std::byte *>(job->output_dsts[0]) + static_cast<size_t>(s * L) * token_bytes;
+    }
+  }
+  if (r != n) throw InvalidInferenceJobException("device_visible_requests: row count mismatch");
+  // sample s of a request lands at its own [s] slice of that request's [batch, own seq, hidden] buffer
+  io->full_rows = !ragged;
+  resize_starpu_vector_handle(handles[0], VectorResizeSpec{io->table_bytes / 8, io->table_bytes}, true);
+  resize_starpu_vector_handle(handles[1], VectorResizeSpec{1, sizeof(int64_t)}, true);
+}
+
 // ---------------------------------------------------------------------------------
 struct TaskRunner::CallbackContext {
   TaskRunner *runner = nullptr;
@@ -175,6 +227,7 @@ struct TaskRunner::CallbackContext {
   std::vector<starpu_data_handle_t> outputs_handles;
   int64_t effective_batch = 0;
   int64_t seq = 0;  // variable_length: the padded sequence length of this batch (0 = fixed shapes)
+  bool request_io = false;  // responses were written by the codelet into the requests' own buffers
   int worker_id = -1, device_id = -1;
   DeviceType executed_on = DeviceType::Unknown;
   JobTiming timing;
@@ -188,6 +241,10 @@ TaskRunner::TaskRunner(ModelConfig model, const ReplicaRegistry *replicas)
   if (model_.inputs.empty() || model_.inputs.size() > InferLimits::MaxInputs)
     throw std::invalid_argument("model must declare 1..16 inputs");
   if (model_.outputs.empty()) throw std::invalid_argument("model must declare outputs");
+  if (model_.device_visible_requests &&
+      (model_.inputs.size() != 2 || model_.outputs.size() != 1 || model_.outputs[0].dims.size() < 3 ||
+       model_.outputs[0].type != ScalarType::Float32 || model_.inputs[0].dims.size() != 2))
+    throw std::invalid_argument("device_visible_requests serves BERT-shaped models: int64 [1, S] x 2 -> fp32 [1, S, H]");
   const bool pinned = replicas_->size() > 0;
   input_pool_ = std::make_unique<InputSlotPool>(model_.inputs, model_.max_batch_size, model_.pool_size, pinned);
   output_pool_ = std::make_unique<OutputSlotPool>(model_.outputs, model_.max_batch_size, model_.pool_size, pinned);
@@ -200,6 +257,13 @@ TaskRunner::TaskRunner(ModelConfig model, const ReplicaRegistry *replicas)
 }
 
 TaskRunner::~TaskRunner() { wait_for_all(); }
+
+// bytes of one token row of output 0 ([batch, seq, hidden...]): hidden... x element size
+auto TaskRunner::request_token_bytes() const -> size_t {
+  size_t n = element_size(model_.outputs[0].type);
+  for (size_t d = 2; d < model_.outputs[0].dims.size(); ++d) n *= static_cast<size_t>(model_.outputs[0].dims[d]);
+  return n;
+}
 
 void TaskRunner::wait_for_all() { starpu_task_wait_for_all(); }
 
@@ -257,13 +321,18 @@ void TaskRunner::submit_batch(const std::vector<std::shared_ptr<InferenceJob>> &
 
   const auto &in_handles = input_pool_->handles(ctx->input_slot);
   const auto &out_handles = output_pool_->handles(ctx->output_slot);
+  detail::RequestIo request_io{};
   // SlotHandleLease(handles, STARPU_W) around the host gather (slot_manager_component.cpp:425)
   size_t leased = 0;
   try {
     for (; leased < in_handles.size(); ++leased)
       if (starpu_data_acquire(in_handles[leased], STARPU_W) != 0)
         throw StarPUDataAcquireException("starpu_data_acquire failed");
-    if (model_.variable_length)
+    if (model_.device_visible_requests)
+      write_request_table(jobs, in_handles, input_pool_->base_ptrs(ctx->input_slot),
+                          input_pool_->host_buffer_infos(ctx->input_slot), effective_batch,
+                          seq > 0 ? seq : model_.inputs[0].dims.at(1), request_token_bytes(), &request_io);
+    else if (model_.variable_length)
       copy_job_inputs_to_slot_padded(master, pending, in_handles, input_pool_->base_ptrs(ctx->input_slot),
                                      input_pool_->host_buffer_infos(ctx->input_slot), seq);
     else
@@ -281,6 +350,7 @@ void TaskRunner::submit_batch(const std::vector<std::shared_ptr<InferenceJob>> &
     // variable_length: an output whose dims[1] is the configured sequence length shrinks with the batch's seq
     if (seq > 0 && model_.outputs[o].dims.size() >= 2 && model_.outputs[o].dims[1] == seq_cap)
       numel = numel / static_cast<size_t>(seq_cap) * static_cast<size_t>(seq);
+    if (request_io.enabled) numel = 1;  // the response bypasses the slot: nothing worth a D2H lands in it
     resize_starpu_vector_handle(out_handles[o],
                                 VectorResizeSpec{numel, numel * element_size(output_pool_->tensor_type(o))}, false);
   }
@@ -291,6 +361,8 @@ void TaskRunner::submit_batch(const std::vector<std::shared_ptr<InferenceJob>> &
   params->num_outputs = model_.outputs.size();
   params->batch_size = effective_batch;
   params->request_id = master->request_id;
+  params->request_io = request_io;
+  ctx->request_io = request_io.enabled;
   params->limits.max_inputs = InferLimits::MaxInputs;
   params->limits.max_dims = InferLimits::MaxDims;
   for (size_t i = 0; i < master->inputs.size(); ++i) {
@@ -409,7 +481,20 @@ void TaskRunner::finalize(CallbackContext *ctx) {
     res.batch_seq = ctx->seq;
     res.timing = ctx->timing;
     res.timing.enqueued_time = job->timing.enqueued_time;
-    if (codelet_ok && all_acquired) {
+    if (codelet_ok && all_acquired && ctx->request_io) {
+      // the codelet's scatter kernel already wrote the response into the request's own buffers
+      for (size_t o = 0; o < aggregated.size(); ++o) {
+        HostTensor v = aggregated[o];
+        v.data = o < job->output_dsts.size() ? static_cast<std::byte *>(job->output_dsts[o]) : nullptr;
+        v.dims[0] = job->batch_size();
+        if (ctx->seq > 0 && v.dims.size() >= 2 && !job->inputs.empty() && job->inputs[0].dims.size() >= 2)
+          v.dims[1] = job->inputs[0].dims[1];  // variable_length: compact [batch, own seq, ...]
+        res.outputs.push_back(std::move(v));
+      }
+      res.rows = job->batch_size();
+      res.ok = true;
+      offset += job->batch_size();
+    } else if (codelet_ok && all_acquired) {
       auto slice = slice_outputs_for_sub_job(aggregated, offset, job->batch_size());
       res.outputs = std::move(slice.outputs);
       // variable_length: a single-sample request gets its own L rows (a contiguous prefix of its padded sample)

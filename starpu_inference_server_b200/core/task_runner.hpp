@@ -61,6 +61,9 @@ struct InferenceJob {
   int request_id = 0;
   std::vector<HostTensor> inputs;  // inputs[i].dims[0] = this request's batch
   std::optional<int> fixed_worker_id;
+  // ModelConfig::device_visible_requests: where this request's response goes, one DEVICE-VISIBLE buffer per
+  // model output laid out [batch, own seq, ...]; the codelet's scatter kernel writes it directly
+  std::vector<void *> output_dsts;
   std::function<void(const JobResult &)> on_complete;
   JobTiming timing;
   [[nodiscard]] auto batch_size() const -> int64_t {
@@ -111,6 +114,10 @@ struct ModelConfig {  // the slice of models/*.yml the path needs (config_loader
   // the longest request it holds (mask synthesised by the zero padding), slots stay sized by the configured
   // dims[1] (= max_seq), and a single-sample request gets only its own L rows back.
   bool variable_length = false;
+  // request inputs AND response buffers are device-visible (pinned host or device memory).
+  // The host then gathers nothing: it writes a table of row addresses into the input slot and the codelet runs
+  // gather/pad/mask -> encoder -> per-request scatter on the device (BERT models, fp32 responses).
+  bool device_visible_requests = false;
 };
 
 // StarPUSetup + StarPUTaskRunner rolled into what the path needs: owns the codelet and the
@@ -137,6 +144,7 @@ class TaskRunner {
   struct CallbackContext;
   static void starpu_output_callback(void *arg);
   static void finalize(CallbackContext *ctx);
+  [[nodiscard]] auto request_token_bytes() const -> size_t;
 
   ModelConfig model_;
   const ReplicaRegistry *replicas_;

@@ -840,9 +840,7 @@ spu_status make_out_tmap(CUtensorMap *map, const void *base, int rows, int cols,
   }
 }
 
-struct LaunchMaps {
-  CUtensorMap a, out, resid, out2;
-};
+using LaunchMaps = GemmLaunchMaps;
 
 template <int BLOCK_N, int CG, int EPI, int IN_FP8, int HF = 0>
 spu_status launch_cfg(const GemmPlan &plan, const LaunchMaps &maps, const KernelArgs &a,
@@ -1039,6 +1037,15 @@ GemmConfig choose_config(int M, int N, int K, int esize) {
   return best;
 }
 
+int gemm_candidates(int N, int epilogue, GemmConfig *out, int cap) {
+  int n = 0;
+  if (epilogue == kEpiBiasResidLN) return 0;
+  for (int cg = 2; cg >= 1; --cg)
+    for (int bn : kBlockNCands)
+      if (N % bn == 0 && n < cap) out[n++] = GemmConfig{cg, bn, 0};
+  return n;
+}
+
 spu_status gemm_make_plan(GemmPlan *plan, const void *A, int rows_a, const void *W, int N, int K,
                           int epilogue, GemmIn in, int force_cg, int force_bn) {
   SPU_REQUIRE(plan && A && W, SPU_ERR_INVALID, "gemm: null argument");
@@ -1056,6 +1063,7 @@ spu_status gemm_make_plan(GemmPlan *plan, const void *A, int rows_a, const void 
   plan->in = in;
   plan->force_cg = force_cg;
   plan->force_bn = force_bn;
+  plan->tuned = nullptr;
   if (const char *env = std::getenv("SPU_GEMM_CFG")) {  // "cg:bn", experiments only
     int cg = 0, bn = 0;
     if (std::sscanf(env, "%d:%d", &cg, &bn) == 2 && cg >= 1 && cg <= 3 && bn > 0 && N % bn == 0) {
@@ -1103,11 +1111,16 @@ spu_status gemm_launch(const GemmPlan &plan, int M, const GemmEpilogueArgs &args
                     (reinterpret_cast<uintptr_t>(args.out2) & 15u) == 0,
                 SPU_ERR_INVALID, "gemm: the LayerNorm-fused epilogue needs bias, gamma, beta and aligned outputs");
   const int esize = plan.in == GemmIn::FP8_E4M3 ? 1 : 2;
+  const TunedTable::Entry *tuned =
+      (!plan.force_bn && !ln && plan.tuned != nullptr)
+          ? plan.tuned->find(plan.N, plan.K, plan.epilogue, static_cast<int>(plan.in), M)
+          : nullptr;
   GemmConfig cfg = plan.force_bn ? GemmConfig{plan.force_cg == 3 ? 2 : plan.force_cg, plan.force_bn, plan.force_cg == 3 ? 1 : 0}
                    : ln          ? choose_ln_config(M, plan.N)
+                   : tuned       ? tuned->cfg
                                  : choose_config(M, plan.N, plan.K, esize);
   SPU_REQUIRE(cfg.block_n > 0, SPU_ERR_UNSUPPORTED, "gemm: no BLOCK_N divides N");
-  if (!plan.force_bn && !ln) {
+  if (!plan.force_bn && !ln && !tuned) {
     static const int hf_env = [] { const char *e = std::getenv("SPU_GEMM_HF"); return e ? std::atoi(e) : 0; }();
     const int tiles_hf = ((M + 255) / 256) * (plan.N / cfg.block_n);
     const bool one_round = tiles_hf <= kNumSMsB200 / 2;  // every CTA pair owns a single tile
@@ -1119,35 +1132,51 @@ spu_status gemm_launch(const GemmPlan &plan, int M, const GemmEpilogueArgs &args
               "gemm: no weight tensor map for this tile");
   // Activation-side maps carry the live row count: TMA zero-fills A rows >= M and
   // clips output rows >= M, so a dynamic batch never reads or writes stale rows.
-  LaunchMaps maps;
-  spu_status st = make_kmajor_tmap(&maps.a, plan.A, M, plan.K, kRowsPerCta, plan.in);
-  if (st != SPU_OK) return st;
-  if (ln) {
-    st = make_out_tmap(&maps.resid, args.resid, M, plan.N, kEpiBiasResid);
+  const LaunchMaps *cached = nullptr;
+  for (const GemmMapCacheEntry &c : plan.map_cache)
+    if (c.M == M && c.out == args.out && c.resid == args.resid && c.out2 == args.out2 && c.out2_e4m3 == args.out2_e4m3)
+      cached = &c.maps;
+  LaunchMaps fresh;
+  if (cached == nullptr) {
+    LaunchMaps &maps = fresh;
+    spu_status st = make_kmajor_tmap(&maps.a, plan.A, M, plan.K, kRowsPerCta, plan.in);
     if (st != SPU_OK) return st;
-    if (args.out != nullptr) {
-      st = make_out_tmap(&maps.out, args.out, M, plan.N, kEpiBiasResid);
+    if (ln) {
+      st = make_out_tmap(&maps.resid, args.resid, M, plan.N, kEpiBiasResid);
       if (st != SPU_OK) return st;
+      if (args.out != nullptr) {
+        st = make_out_tmap(&maps.out, args.out, M, plan.N, kEpiBiasResid);
+        if (st != SPU_OK) return st;
+      } else {
+        maps.out = maps.resid;
+      }
+      if (args.out2 != nullptr) {
+        st = make_out_tmap(&maps.out2, args.out2, M, plan.N, args.out2_e4m3 ? kEpiBiasGeluE4m3 : kEpiBias);
+        if (st != SPU_OK) return st;
+      } else {
+        maps.out2 = maps.out;
+      }
     } else {
-      maps.out = maps.resid;
-    }
-    if (args.out2 != nullptr) {
-      st = make_out_tmap(&maps.out2, args.out2, M, plan.N, args.out2_e4m3 ? kEpiBiasGeluE4m3 : kEpiBias);
+      st = make_out_tmap(&maps.out, args.out, M, plan.N, plan.epilogue);
       if (st != SPU_OK) return st;
-    } else {
+      if (plan.epilogue == kEpiBiasResid) {
+        st = make_out_tmap(&maps.resid, args.resid, M, plan.N, plan.epilogue);
+        if (st != SPU_OK) return st;
+      } else {
+        maps.resid = maps.out;
+      }
       maps.out2 = maps.out;
     }
-  } else {
-    st = make_out_tmap(&maps.out, args.out, M, plan.N, plan.epilogue);
-    if (st != SPU_OK) return st;
-    if (plan.epilogue == kEpiBiasResid) {
-      st = make_out_tmap(&maps.resid, args.resid, M, plan.N, plan.epilogue);
-      if (st != SPU_OK) return st;
-    } else {
-      maps.resid = maps.out;
-    }
-    maps.out2 = maps.out;
+    GemmMapCacheEntry &slot = plan.map_cache[plan.map_cache_next++ % 4];
+    slot.M = M;
+    slot.out = args.out;
+    slot.resid = args.resid;
+    slot.out2 = args.out2;
+    slot.out2_e4m3 = args.out2_e4m3;
+    slot.maps = fresh;
+    cached = &slot.maps;
   }
+  const LaunchMaps &maps = *cached;
   KernelArgs a{M, plan.N, plan.K, args.bias, args.acc_scale, args.out_inv_scale,
                static_cast<unsigned long long *>(g_trace_buf), static_cast<int>(g_trace_cta), static_cast<int>(g_dbg_mode),
                args.gamma, args.beta, args.ln_eps, args.out != nullptr ? 1 : 0,

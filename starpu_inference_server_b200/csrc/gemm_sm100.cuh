@@ -5,6 +5,8 @@
 #pragma once
 #include <cuda.h>
 
+#include <vector>
+
 #include "common.cuh"
 
 namespace spu {
@@ -42,6 +44,41 @@ bool gemm_ln_supported(int N);
 // Operand-B TMA boxes come in multiples of 32 rows: BLOCK_N / cta_group in {32..256}.
 constexpr int kNumBBoxes = 8;
 
+struct GemmConfig {
+  int cta_group;  // 1: 128 x BLOCK_N tile per CTA; 2: 256 x BLOCK_N per CTA pair
+  int block_n;
+  int half = 0;   // CTA pairs only: half-footprint CTAs (<= 113 KB smem, 256 TMEM columns), two resident per SM
+};
+
+// Tiles measured at warm-up (spu_bert_autotune): the winner per (N, K, epilogue, operand format, M) replaces the
+// cost model's choice for exactly that problem.  Written at start-up only, read by every launch.
+struct TunedTable {
+  struct Entry {
+    int N, K, epilogue, in, M;
+    GemmConfig cfg;
+    float us;  // measured microseconds per launch of the winner
+  };
+  std::vector<Entry> entries;
+  const Entry *find(int N, int K, int epilogue, int in, int M) const {
+    for (const Entry &e : entries)
+      if (e.M == M && e.N == N && e.K == K && e.epilogue == epilogue && e.in == in) return &e;
+    return nullptr;
+  }
+};
+
+// Activation-side tensor maps of one launch (they carry the live row count M and the epilogue pointers).  A plan
+// remembers the last few it encoded: a worker re-launching the same problem eagerly (before its graph exists, or
+// with graphs off) pays cuTensorMapEncodeTiled once, not three times per launch.
+struct GemmLaunchMaps {
+  CUtensorMap a, out, resid, out2;
+};
+struct GemmMapCacheEntry {
+  int M = 0;
+  const void *out = nullptr, *resid = nullptr, *out2 = nullptr;
+  int out2_e4m3 = 0;
+  GemmLaunchMaps maps;
+};
+
 struct GemmPlan {
   CUtensorMap tmap_b[kNumBBoxes];  // index = box_rows/32 - 1
   bool b_ok[kNumBBoxes];
@@ -51,13 +88,14 @@ struct GemmPlan {
   int epilogue;
   GemmIn in;
   int force_cg, force_bn;          // 0 = choose per launch from M; force_cg 3 = CTA pair with half-footprint CTAs
+  const TunedTable *tuned = nullptr;  // consulted before the cost model when no tile is forced
+  // single-threaded like the workspace the plan belongs to
+  mutable GemmMapCacheEntry map_cache[4];
+  mutable unsigned map_cache_next = 0;
 };
 
-struct GemmConfig {
-  int cta_group;  // 1: 128 x BLOCK_N tile per CTA; 2: 256 x BLOCK_N per CTA pair
-  int block_n;
-  int half = 0;   // CTA pairs only: half-footprint CTAs (<= 113 KB smem, 256 TMEM columns), two resident per SM
-};
+// Every (cta_group, BLOCK_N) the kernel is instantiated for that divides N (cta_group 3 = half-footprint pair).
+int gemm_candidates(int N, int epilogue, GemmConfig *out, int cap);
 
 // Pick (cta_group, BLOCK_N) for an [M,N,K] problem: BLOCK_N must divide N; minimise
 // persistent rounds x per-tile cost (MMA issue, L2->smem feed, epilogue) over 148 SMs.

@@ -143,6 +143,13 @@ spu_status build(spu_replica *r, const float *const *t) {
       }
     }
   }
+  // every plan consults the replica's table of measured tiles (empty until spu_bert_autotune runs)
+  for (Workspace &ws : r->ws) {
+    for (std::vector<LayerPlans> *set : {&ws.plans, &ws.plans8})
+      for (LayerPlans &p : *set)
+        for (GemmPlan *g : {&p.qkv, &p.attn_out, &p.ffn1, &p.ffn2, &p.ffn1_b2q, &p.ffn1_q2b, &p.attn_out_ln, &p.ffn2_ln})
+          g->tuned = &r->tuned;
+  }
   SPU_CUDA_TRY(cudaDeviceSynchronize());
   return SPU_OK;
 }
@@ -385,6 +392,160 @@ spu_status check_forward_args(spu_replica *r, int ws_idx, const void *ids, const
   return SPU_OK;
 }
 
+constexpr size_t kMaxGraphs = 64;  // per workspace; least recently used goes first
+
+void destroy_graph(CapturedGraph &g) {
+  if (g.exec) cudaGraphExecDestroy(g.exec);
+  if (g.graph) cudaGraphDestroy(g.graph);
+  g.exec = nullptr;
+  g.graph = nullptr;
+}
+
+void drop_graphs(Workspace &ws) {
+  for (CapturedGraph &g : ws.graphs) destroy_graph(g);
+  ws.graphs.clear();
+  ws.seen.clear();
+}
+
+// Capture one forward on `s` into an instantiated graph and find the two nodes that hold the I/O pointers.
+spu_status capture_forward(spu_replica *r, Workspace &ws, const int64_t *ids, const int64_t *mask, int batch, int seq,
+                           float *out, cudaStream_t s, CapturedGraph *cg) {
+  SPU_CUDA_TRY(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
+  spu_status st = enqueue_forward(r, ws, ids, mask, batch, seq, out, s);
+  cudaGraph_t graph = nullptr;
+  cudaError_t e = cudaStreamEndCapture(s, &graph);
+  if (st != SPU_OK) {
+    if (graph) cudaGraphDestroy(graph);
+    return st;
+  }
+  SPU_CUDA_TRY(e);
+  cg->key = GraphKey{ids, mask, out, batch, seq};
+  cg->graph = graph;
+  e = cudaGraphInstantiate(&cg->exec, graph, 0);
+  if (e != cudaSuccess) {
+    cudaGraphDestroy(graph);
+    cg->graph = nullptr;
+    SPU_CUDA_TRY(e);
+  }
+  // root = embedding kernel (ids, mask = parameters 0, 1), leaf = final LayerNorm (out_f32 = parameter 4, or
+  // out_bf16 = parameter 5 under SPU_OUTPUT_BF16): anything else (LayerNorm-fused epilogues keep `out` inside a
+  // tensor map) leaves the graph bound to its pointers
+  cg->patchable = false;
+  size_t n_nodes = 0, n_roots = 0;
+  if (cudaGraphGetNodes(graph, nullptr, &n_nodes) != cudaSuccess || cudaGraphGetRootNodes(graph, nullptr, &n_roots) != cudaSuccess ||
+      n_roots != 1 || n_nodes < 2) {
+    cudaGetLastError();
+    return SPU_OK;
+  }
+  std::vector<cudaGraphNode_t> nodes(n_nodes);
+  cudaGraphNode_t root = nullptr;
+  n_roots = 1;
+  if (cudaGraphGetNodes(graph, nodes.data(), &n_nodes) != cudaSuccess ||
+      cudaGraphGetRootNodes(graph, &root, &n_roots) != cudaSuccess) {
+    cudaGetLastError();
+    return SPU_OK;
+  }
+  cudaGraphNode_t leaf = nullptr;
+  int n_leaves = 0;
+  for (cudaGraphNode_t n : nodes) {
+    size_t deps = 0;
+    if (cudaGraphNodeGetDependentNodes(n, nullptr, &deps) != cudaSuccess) {
+      cudaGetLastError();
+      return SPU_OK;
+    }
+    if (deps == 0) {
+      leaf = n;
+      ++n_leaves;
+    }
+  }
+  if (n_leaves != 1 || leaf == root) return SPU_OK;
+  cudaGraphNodeType t0, t1;
+  cudaKernelNodeParams p0{}, p1{};
+  if (cudaGraphNodeGetType(root, &t0) != cudaSuccess || cudaGraphNodeGetType(leaf, &t1) != cudaSuccess ||
+      t0 != cudaGraphNodeTypeKernel || t1 != cudaGraphNodeTypeKernel ||
+      cudaGraphKernelNodeGetParams(root, &p0) != cudaSuccess || cudaGraphKernelNodeGetParams(leaf, &p1) != cudaSuccess) {
+    cudaGetLastError();
+    return SPU_OK;
+  }
+  if (p0.func != bert_embed_kernel_entry() || p1.func != layernorm_kernel_entry() || p0.kernelParams == nullptr ||
+      p1.kernelParams == nullptr)
+    return SPU_OK;
+  const int out_arg = (r->flags & SPU_OUTPUT_BF16) ? 5 : 4;
+  // the captured parameters must be the pointers we are about to treat as patchable
+  if (*static_cast<const void *const *>(p0.kernelParams[0]) != ids || *static_cast<const void *const *>(p0.kernelParams[1]) != mask ||
+      *static_cast<const void *const *>(p1.kernelParams[out_arg]) != out)
+    return SPU_OK;
+  cg->first = root;
+  cg->last = leaf;
+  cg->out_arg = out_arg;
+  cg->patchable = true;
+  return SPU_OK;
+}
+
+// Point the instantiated graph at other I/O buffers (host-side only; launches already enqueued keep theirs).
+spu_status retarget_graph(CapturedGraph &g, const int64_t *ids, const int64_t *mask, float *out) {
+  if (g.key.ids != ids || g.key.mask != mask) {
+    cudaKernelNodeParams p{};
+    SPU_CUDA_TRY(cudaGraphKernelNodeGetParams(g.first, &p));
+    constexpr int kEmbedArgs = 17;
+    void *args[kEmbedArgs];
+    for (int i = 0; i < kEmbedArgs; ++i) args[i] = p.kernelParams[i];
+    const void *ids_v = ids, *mask_v = mask;
+    args[0] = &ids_v;
+    args[1] = &mask_v;
+    p.kernelParams = args;
+    SPU_CUDA_TRY(cudaGraphExecKernelNodeSetParams(g.exec, g.first, &p));
+    // keep the template graph in step so that the next GetParams reads what the exec holds
+    SPU_CUDA_TRY(cudaGraphKernelNodeSetParams(g.first, &p));
+    g.key.ids = ids;
+    g.key.mask = mask;
+  }
+  if (g.key.out != out) {
+    cudaKernelNodeParams p{};
+    SPU_CUDA_TRY(cudaGraphKernelNodeGetParams(g.last, &p));
+    constexpr int kLnArgs = 11;
+    void *args[kLnArgs];
+    for (int i = 0; i < kLnArgs; ++i) args[i] = p.kernelParams[i];
+    void *out_v = out;
+    args[g.out_arg] = &out_v;
+    p.kernelParams = args;
+    SPU_CUDA_TRY(cudaGraphExecKernelNodeSetParams(g.exec, g.last, &p));
+    SPU_CUDA_TRY(cudaGraphKernelNodeSetParams(g.last, &p));
+    g.key.out = out;
+  }
+  return SPU_OK;
+}
+
+// The graph serving (batch, seq) with these pointers, retargeted if need be; nullptr when none is cached.
+spu_status find_graph(Workspace &ws, const int64_t *ids, const int64_t *mask, int batch, int seq, float *out,
+                      CapturedGraph **found) {
+  *found = nullptr;
+  const GraphKey want{ids, mask, out, batch, seq};
+  for (CapturedGraph &g : ws.graphs) {
+    if (!g.key.same_shape(batch, seq)) continue;
+    if (!(g.key == want)) {
+      if (!g.patchable) continue;
+      SPU_TRY(retarget_graph(g, ids, mask, out));
+    }
+    g.tick = ++ws.graph_tick;
+    *found = &g;
+    return SPU_OK;
+  }
+  return SPU_OK;
+}
+
+void insert_graph(Workspace &ws, const CapturedGraph &cg) {
+  if (ws.graphs.size() >= kMaxGraphs) {
+    size_t lru = 0;
+    for (size_t i = 1; i < ws.graphs.size(); ++i)
+      if (ws.graphs[i].tick < ws.graphs[lru].tick) lru = i;
+    destroy_graph(ws.graphs[lru]);
+    ws.graphs.erase(ws.graphs.begin() + static_cast<long>(lru));
+  }
+  ws.graphs.push_back(cg);
+  ws.graphs.back().tick = ++ws.graph_tick;
+}
+
 }  // namespace
 }  // namespace spu
 
@@ -465,53 +626,40 @@ extern "C" spu_status spu_replica_destroy(spu_replica *r) {
   if (r == nullptr) return SPU_OK;
   DeviceGuard guard(r->device);
   cudaDeviceSynchronize();
-  for (Workspace &ws : r->ws)
-    for (CapturedGraph &g : ws.graphs)
-      if (g.exec) cudaGraphExecDestroy(g.exec);
+  for (Workspace &ws : r->ws) drop_graphs(ws);
   if (r->vit != nullptr && r->vit_destroy != nullptr) r->vit_destroy(r->vit);
   for (void *p : r->allocations) cudaFree(p);
   delete r;
   return SPU_OK;
 }
 
-constexpr size_t kMaxAutoGraphs = 64;  // per workspace (a worker sees pool_size slot tuples)
-
 extern "C" spu_status spu_bert_forward_async(spu_replica *r, int32_t ws_idx, const int64_t *ids,
                                              const int64_t *mask, int32_t batch, int32_t seq,
                                              float *out, void *stream) {
   SPU_TRY(check_forward_args(r, ws_idx, ids, mask, batch, seq, out));
   Workspace &ws = r->ws[ws_idx];
-  const GraphKey key{ids, mask, out, batch, seq};
-  for (const CapturedGraph &g : ws.graphs)
-    if (g.key == key) {
-      SPU_CUDA_TRY(cudaGraphLaunch(g.exec, as_stream(stream)));
-      return SPU_OK;
-    }
-  if ((r->flags & SPU_FORWARD_AUTO_GRAPH) != 0 && ws.graphs.size() < kMaxAutoGraphs) {
-    bool seen = false;
-    for (const GraphKey &k : ws.seen) seen = seen || k == key;
+  CapturedGraph *g = nullptr;
+  SPU_TRY(find_graph(ws, ids, mask, batch, seq, out, &g));
+  if (g != nullptr) {
+    SPU_CUDA_TRY(cudaGraphLaunch(g->exec, as_stream(stream)));
+    return SPU_OK;
+  }
+  if ((r->flags & SPU_FORWARD_AUTO_GRAPH) != 0) {
+    // second sighting of a batch shape (of these very pointers when the graph cannot be retargeted): kernel
+    // attributes are set and caches warm from the eager pass
+    const GraphKey key{ids, mask, out, batch, seq};
+    bool seen = false, shape_unpatchable = false;
+    for (const CapturedGraph &c : ws.graphs) shape_unpatchable = shape_unpatchable || (c.key.same_shape(batch, seq) && !c.patchable);
+    for (const GraphKey &k : ws.seen) seen = seen || (shape_unpatchable ? k == key : k.same_shape(batch, seq));
     if (seen) {
-      // second sighting: kernel attributes are set and caches warm from the eager pass
       cudaStream_t s = as_stream(stream);
-      SPU_CUDA_TRY(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
-      spu_status st = enqueue_forward(r, ws, ids, mask, batch, seq, out, s);
-      cudaGraph_t graph = nullptr;
-      cudaError_t e = cudaStreamEndCapture(s, &graph);
-      if (st != SPU_OK) {
-        if (graph) cudaGraphDestroy(graph);
-        return st;
-      }
-      SPU_CUDA_TRY(e);
       CapturedGraph cg;
-      cg.key = key;
-      e = cudaGraphInstantiate(&cg.exec, graph, 0);
-      cudaGraphDestroy(graph);
-      SPU_CUDA_TRY(e);
-      ws.graphs.push_back(cg);
+      SPU_TRY(capture_forward(r, ws, ids, mask, batch, seq, out, s, &cg));
+      insert_graph(ws, cg);
       SPU_CUDA_TRY(cudaGraphLaunch(cg.exec, s));
       return SPU_OK;
     }
-    if (ws.seen.size() < 4 * kMaxAutoGraphs) ws.seen.push_back(key);
+    if (ws.seen.size() < 4 * kMaxGraphs) ws.seen.push_back(key);
   }
   return enqueue_forward(r, ws, ids, mask, batch, seq, out, as_stream(stream));
 }
@@ -542,28 +690,16 @@ extern "C" spu_status spu_bert_forward_capture(spu_replica *r, int32_t ws_idx, c
                                                float *out, void *stream) {
   SPU_TRY(check_forward_args(r, ws_idx, ids, mask, batch, seq, out));
   Workspace &ws = r->ws[ws_idx];
-  const GraphKey key{ids, mask, out, batch, seq};
-  for (const CapturedGraph &g : ws.graphs)
-    if (g.key == key) return SPU_OK;
+  CapturedGraph *g = nullptr;
+  SPU_TRY(find_graph(ws, ids, mask, batch, seq, out, &g));
+  if (g != nullptr) return SPU_OK;
   cudaStream_t s = as_stream(stream);
   // one eager pass first: sets kernel attributes and warms caches outside the capture
   SPU_TRY(enqueue_forward(r, ws, ids, mask, batch, seq, out, s));
   SPU_CUDA_TRY(cudaStreamSynchronize(s));
-  SPU_CUDA_TRY(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
-  spu_status st = enqueue_forward(r, ws, ids, mask, batch, seq, out, s);
-  cudaGraph_t graph = nullptr;
-  cudaError_t e = cudaStreamEndCapture(s, &graph);
-  if (st != SPU_OK) {
-    if (graph) cudaGraphDestroy(graph);
-    return st;
-  }
-  SPU_CUDA_TRY(e);
   CapturedGraph cg;
-  cg.key = key;
-  e = cudaGraphInstantiate(&cg.exec, graph, 0);
-  cudaGraphDestroy(graph);
-  SPU_CUDA_TRY(e);
-  ws.graphs.push_back(cg);
+  SPU_TRY(capture_forward(r, ws, ids, mask, batch, seq, out, s, &cg));
+  insert_graph(ws, cg);
   return SPU_OK;
 }
 
@@ -619,11 +755,7 @@ extern "C" spu_status spu_bert_calibrate_fp8(spu_replica *r, int32_t ws_idx, con
   }
   r->fp8_calibrated = true;
   // captured graphs bake the scales in: drop them
-  for (Workspace &ws : r->ws) {
-    for (CapturedGraph &g : ws.graphs)
-      if (g.exec) cudaGraphExecDestroy(g.exec);
-    ws.graphs.clear();
-  }
+  for (Workspace &ws : r->ws) drop_graphs(ws);
   return SPU_OK;
 }
 
@@ -637,12 +769,7 @@ extern "C" spu_status spu_bert_set_fp8_mask(spu_replica *r, const uint8_t *layer
   DeviceGuard guard(r->device);
   SPU_CUDA_TRY(cudaDeviceSynchronize());  // start-up only: no forward of the old plan may be in flight
   r->fp8_mask.assign(layer_masks, layer_masks + n_layers);
-  for (Workspace &ws : r->ws) {  // captured graphs bake the plan in: drop them
-    for (CapturedGraph &g : ws.graphs)
-      if (g.exec) cudaGraphExecDestroy(g.exec);
-    ws.graphs.clear();
-    ws.seen.clear();
-  }
+  for (Workspace &ws : r->ws) drop_graphs(ws);  // captured graphs bake the plan in
   return SPU_OK;
 }
 
@@ -730,6 +857,162 @@ extern "C" uint64_t spu_bert_output_bytes(const spu_replica *r, int32_t batch, i
   if (r == nullptr || r->kind != 0 || batch <= 0 || seq <= 0) return 0;
   return static_cast<uint64_t>(batch) * static_cast<uint64_t>(seq) * static_cast<uint64_t>(r->desc.hidden) *
          ((r->flags & SPU_OUTPUT_BF16) ? 2u : 4u);
+}
+
+namespace {
+// Microseconds per launch of `plan` forced to tile `cfg`: `reps` launches back to back in one CUDA graph
+// (programmatic dependent launch in effect, as in the captured forward), best of three replays.
+spu_status time_tile(const GemmPlan &plan, GemmConfig cfg, int M, const GemmEpilogueArgs &e, cudaStream_t s,
+                     int reps, float *us) {
+  GemmPlan p = plan;
+  p.force_cg = cfg.half ? 3 : cfg.cta_group;
+  p.force_bn = cfg.block_n;
+  p.tuned = nullptr;
+  SPU_TRY(gemm_launch(p, M, e, s));  // kernel attributes, caches
+  SPU_CUDA_TRY(cudaStreamSynchronize(s));
+  SPU_CUDA_TRY(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
+  spu_status st = SPU_OK;
+  for (int i = 0; i < reps && st == SPU_OK; ++i) st = gemm_launch(p, M, e, s);
+  cudaGraph_t graph = nullptr;
+  cudaError_t err = cudaStreamEndCapture(s, &graph);
+  if (st != SPU_OK) {
+    if (graph) cudaGraphDestroy(graph);
+    return st;
+  }
+  SPU_CUDA_TRY(err);
+  cudaGraphExec_t exec = nullptr;
+  err = cudaGraphInstantiate(&exec, graph, 0);
+  cudaGraphDestroy(graph);
+  SPU_CUDA_TRY(err);
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  cudaEventCreate(&e0);
+  cudaEventCreate(&e1);
+  float best = 1e30f;
+  cudaGraphLaunch(exec, s);
+  for (int k = 0; k < 3 && err == cudaSuccess; ++k) {
+    cudaEventRecord(e0, s);
+    cudaGraphLaunch(exec, s);
+    cudaEventRecord(e1, s);
+    err = cudaStreamSynchronize(s);
+    float ms = 0.f;
+    if (err == cudaSuccess && cudaEventElapsedTime(&ms, e0, e1) == cudaSuccess) best = std::fmin(best, ms);
+  }
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  cudaGraphExecDestroy(exec);
+  SPU_CUDA_TRY(err);
+  *us = best * 1e3f / static_cast<float>(reps);
+  return SPU_OK;
+}
+}  // namespace
+
+// Warm-up autotune (the reference's hook is the fixed-worker warm-up pass,
+// src/core/warmup.cpp:226-299): for the GEMM problems a forward of (batch, seq) launches, time every
+// (cta_group, BLOCK_N) tile the kernel is built for on the replica's own weights and workspace, and let the winner
+// replace the static cost model's choice for that (N, K, epilogue, format, M).  Start-up only: no forward may be in
+// flight; captured graphs (which bake tiles in) are dropped.
+extern "C" spu_status spu_bert_autotune(spu_replica *r, int32_t ws_idx, int32_t batch, int32_t seq, void *stream,
+                                        int32_t *n_changed) {
+  float dummy = 0.f;
+  SPU_TRY(check_forward_args(r, ws_idx, &dummy, &dummy, batch, seq, &dummy));
+  DeviceGuard guard(r->device);
+  // the measurements are captured into CUDA graphs, which the legacy default stream cannot do: without a
+  // caller stream, use a private one
+  struct OwnStream {
+    cudaStream_t s = nullptr;
+    ~OwnStream() {
+      if (s) cudaStreamDestroy(s);
+    }
+  } own;
+  cudaStream_t s = as_stream(stream);
+  if (s == nullptr) {
+    SPU_CUDA_TRY(cudaStreamCreateWithFlags(&own.s, cudaStreamNonBlocking));
+    s = own.s;
+  }
+  SPU_CUDA_TRY(cudaDeviceSynchronize());
+  Workspace &ws = r->ws[ws_idx];
+  const spu_bert_desc &d = r->desc;
+  const int M = batch * seq;
+  struct Problem {
+    const GemmPlan *plan;
+    GemmEpilogueArgs e;
+  };
+  std::vector<Problem> problems;
+  auto add = [&](const GemmPlan &p, const float *bias, const float *resid, void *out) {
+    for (const Problem &q : problems)
+      if (q.plan->N == p.N && q.plan->K == p.K && q.plan->epilogue == p.epilogue && q.plan->in == p.in) return;
+    GemmEpilogueArgs e{};
+    e.bias = bias;
+    e.resid = resid;
+    e.out = out;
+    e.acc_scale = 1.f;
+    e.out_inv_scale = 1.f;
+    problems.push_back(Problem{&p, e});
+  };
+  const bool fp8 = (r->flags & SPU_PREC_FP8_E4M3) != 0;
+  for (int l = 0; l < d.layers; ++l) {
+    const LayerWeights &w = r->layers[l];
+    const LayerPlans &p16 = ws.plans[l];
+    const uint8_t m = fp8 ? r->fp8_mask[l] : 0;
+    const LayerPlans *p8 = fp8 ? &ws.plans8[l] : nullptr;
+    const bool q_qkv = m & SPU_FP8_GEMM_QKV, q_out = m & SPU_FP8_GEMM_OUT, q_f1 = m & SPU_FP8_GEMM_FFN1,
+               q_f2 = m & SPU_FP8_GEMM_FFN2;
+    add(q_qkv ? p8->qkv : p16.qkv, w.b_qkv, nullptr, ws.qkv);
+    if (!r->ln_fused) add(q_out ? p8->attn_out : p16.attn_out, w.b_o, ws.x_f32, ws.x_f32);
+    add(q_f1 ? (q_f2 ? p8->ffn1 : p8->ffn1_q2b) : (q_f2 ? p8->ffn1_b2q : p16.ffn1), w.b_1, nullptr,
+        q_f2 ? static_cast<void *>(ws.h_q) : ws.h);
+    if (!r->ln_fused) add(q_f2 ? p8->ffn2 : p16.ffn2, w.b_2, ws.x_f32, ws.x_f32);
+  }
+  int changed = 0;
+  for (const Problem &pb : problems) {
+    const GemmPlan &p = *pb.plan;
+    GemmConfig cands[16];
+    const int n = gemm_candidates(p.N, p.epilogue, cands, 16);
+    GemmConfig best{0, 0, 0};
+    float best_us = 1e30f;
+    for (int i = 0; i < n; ++i) {
+      float us = 0.f;
+      if (time_tile(p, cands[i], M, pb.e, s, 20, &us) != SPU_OK) {
+        cudaGetLastError();  // a tile this problem cannot use (no weight map, footprint): skip it
+        continue;
+      }
+      if (us < best_us) {
+        best_us = us;
+        best = cands[i];
+      }
+    }
+    SPU_REQUIRE(best.block_n != 0, SPU_ERR_CUDA, "autotune: no candidate tile could be timed");
+    const GemmConfig model = choose_config(M, p.N, p.K, p.in == GemmIn::FP8_E4M3 ? 1 : 2);
+    changed += (model.cta_group != best.cta_group || model.block_n != best.block_n) ? 1 : 0;
+    TunedTable::Entry entry{p.N, p.K, p.epilogue, static_cast<int>(p.in), M, best, best_us};
+    bool replaced = false;
+    for (TunedTable::Entry &e : r->tuned.entries)
+      if (e.M == M && e.N == p.N && e.K == p.K && e.epilogue == p.epilogue && e.in == entry.in) {
+        e = entry;
+        replaced = true;
+      }
+    if (!replaced) r->tuned.entries.push_back(entry);
+  }
+  for (Workspace &w2 : r->ws) drop_graphs(w2);
+  if (n_changed != nullptr) *n_changed = changed;
+  return SPU_OK;
+}
+
+// Rows of {N, K, epilogue, operand format (0 bf16, 1 e4m3), M, cta_group, BLOCK_N, nanoseconds per launch}.
+extern "C" int32_t spu_bert_tuned_configs(const spu_replica *r, int32_t *out, int32_t cap_rows) {
+  if (r == nullptr) return 0;
+  const int n = static_cast<int>(r->tuned.entries.size());
+  for (int i = 0; i < n && i < cap_rows && out != nullptr; ++i) {
+    const TunedTable::Entry &e = r->tuned.entries[static_cast<size_t>(i)];
+    const int row[8] = {e.N, e.K, e.epilogue, e.in, e.M, e.cfg.cta_group, e.cfg.block_n, static_cast<int>(e.us * 1e3f)};
+    for (int k = 0; k < 8; ++k) out[i * 8 + k] = row[k];
+  }
+  return n;
+}
+
+extern "C" int32_t spu_bert_graph_count(const spu_replica *r, int32_t ws_idx) {
+  if (r == nullptr || r->kind != 0 || ws_idx < 0 || ws_idx >= static_cast<int>(r->ws.size())) return -1;
+  return static_cast<int32_t>(r->ws[ws_idx].graphs.size());
 }
 
 extern "C" int32_t spu_bert_forward_launch_count(const spu_replica *r) {

@@ -31,6 +31,9 @@ spu_status layernorm_launch(const float *x, const float *gamma, const float *bet
                             float *out_f32, void *out_bf16, int rows, int hidden,
                             cudaStream_t stream, long long in_row_stride = 0, void *out_q = nullptr,
                             float q_inv_scale = 1.f);
+// kernel entry points of the first / last launch of a forward (graph parameter patching, replica.cu)
+const void *bert_embed_kernel_entry();
+const void *layernorm_kernel_entry();
 // request i <- rows [i*seq, i*seq + (full_rows ? seq : len[i])) of src [n_req*seq, hidden]
 spu_status scatter_requests_launch(const float *src, const int32_t *len, int n_req, int seq, int hidden,
                                    bool full_rows, float *const *dsts, cudaStream_t stream);
@@ -80,9 +83,15 @@ struct LayerPlans {
   GemmPlan attn_out_ln, ffn2_ln;
 };
 
+// One captured forward per (batch, seq) and workspace.  The I/O pointers (ids, mask, out) are NOT part of the key:
+// they only appear in the first kernel (embedding) and the last one (the final LayerNorm), whose parameters are
+// patched in the instantiated graph before a launch with other pointers (cudaGraphExecKernelNodeSetParams).  A
+// worker therefore needs one graph per batch shape, not one per (slot, shape) tuple, and a dynamic-batch server
+// cannot fill the cache with cold entries; beyond kMaxGraphs the least recently used one is evicted.
 struct GraphKey {
-  const void *ids = nullptr, *mask = nullptr, *out = nullptr;
+  const void *ids = nullptr, *mask = nullptr, *out = nullptr;  // the pointers the graph currently holds
   int batch = 0, seq = 0;
+  bool same_shape(int b, int s) const { return batch == b && seq == s; }
   bool operator==(const GraphKey &o) const {
     return ids == o.ids && mask == o.mask && out == o.out && batch == o.batch && seq == o.seq;
   }
@@ -91,6 +100,12 @@ struct GraphKey {
 struct CapturedGraph {
   GraphKey key;
   cudaGraphExec_t exec = nullptr;
+  cudaGraph_t graph = nullptr;  // kept alive: the patched nodes' unchanged parameters point into it
+  // patchable = the graph's single root is the embedding kernel and its single leaf the LayerNorm kernel
+  bool patchable = false;
+  cudaGraphNode_t first = nullptr, last = nullptr;
+  int out_arg = 4;              // index of the output pointer among the last kernel's parameters
+  unsigned long long tick = 0;  // LRU stamp
 };
 
 struct Workspace {
@@ -105,7 +120,8 @@ struct Workspace {
   std::vector<LayerPlans> plans;
   std::vector<LayerPlans> plans8;
   std::vector<CapturedGraph> graphs;
-  std::vector<GraphKey> seen;  // SPU_FORWARD_AUTO_GRAPH: tuples run eagerly once so far
+  std::vector<GraphKey> seen;  // SPU_FORWARD_AUTO_GRAPH: shapes run eagerly once so far
+  unsigned long long graph_tick = 0;
 };
 
 struct VitState;  // vit.cu
@@ -128,6 +144,7 @@ struct spu_replica {
   int fp8_layers = 0;         // leading layers whose GEMMs run in FP8 (rest bf16)
   // per layer: which of its four GEMMs run in FP8 (SPU_FP8_GEMM_* bits); others run in bf16
   std::vector<uint8_t> fp8_mask;
+  spu::TunedTable tuned;      // spu_bert_autotune: measured tile winners, read by every GEMM plan of this replica
   spu::VitState *vit = nullptr;
   void (*vit_destroy)(spu::VitState *) = nullptr;
 };

@@ -279,6 +279,9 @@ constexpr int kSegBlocksPerSegment = 32;
 
 }  // namespace
 
+const void *bert_embed_kernel_entry() { return reinterpret_cast<const void *>(&bert_embed_ln_kernel); }
+const void *layernorm_kernel_entry() { return reinterpret_cast<const void *>(&layernorm_kernel); }
+
 spu_status bert_embed_launch(const int64_t *ids, const int64_t *mask, const float *word,
                              const float *pos, const float *type0, const float *gamma,
                              const float *beta, float eps, int vocab, float *x_f32, void *x_bf16,

@@ -23,7 +23,8 @@ SYMBOLS = [
     "spu_server_wait_all", "spu_server_stats", "spu_host_last_error", "spu_host_codelet_fields",
     "spu_host_buffer_byte_size", "spu_host_select_replica", "spu_host_gather_to_slot", "spu_host_slice_rows",
     "spu_host_can_merge", "spu_host_call_cuda_func_affine", "spu_host_can_merge_varlen", "spu_host_gather_padded",
-    "spu_host_replica_assignments", "spu_host_nvtx_capture",
+    "spu_host_replica_assignments", "spu_host_nvtx_capture", "spu_server_offered_load",
+    "spu_host_tile_aware_wants_more",
 ]
 
 
@@ -38,7 +39,8 @@ class ServerCfg(C.Structure):
                 ("inputs", TensorCfg * MAX_IO), ("outputs", TensorCfg * MAX_IO), ("model_kind", C.c_int32),
                 ("replicas", C.c_void_p * MAX_DEV), ("n_workspaces", C.c_int32), ("affine_scale", C.c_float),
                 ("affine_shift", C.c_float), ("variable_length", C.c_int32),
-                ("length_bucket", C.c_int32), ("gpu_model_replication", C.c_int32)]
+                ("length_bucket", C.c_int32), ("gpu_model_replication", C.c_int32), ("tile_rows", C.c_int32),
+                ("device_visible_requests", C.c_int32), ("warmup_autotune", C.c_int32)]
 
 
 class Request(C.Structure):
@@ -86,6 +88,12 @@ def lib():
     L.spu_host_buffer_byte_size.restype = i32
     L.spu_host_select_replica.argtypes = [C.POINTER(i32), i32, C.POINTER(i32), i32, i32, i32, i32]
     L.spu_host_select_replica.restype = i32
+    f64 = C.c_double
+    L.spu_server_offered_load.argtypes = [vp, C.POINTER(Request), i32, i64, f64, u64, C.POINTER(f64), C.POINTER(f64),
+                                          C.POINTER(f64), C.POINTER(i32), C.POINTER(f64)]
+    L.spu_server_offered_load.restype = i32
+    L.spu_host_tile_aware_wants_more.argtypes = [i64, i64, i64, i32]
+    L.spu_host_tile_aware_wants_more.restype = i32
     L.spu_host_nvtx_capture.argtypes = [i32, C.c_char_p, u64, C.POINTER(i64)]
     L.spu_host_nvtx_capture.restype = i32
     L.spu_host_replica_assignments.argtypes = [C.POINTER(i32), i32, i32, C.POINTER(i32), i32, C.POINTER(i32),
@@ -137,8 +145,12 @@ class Server:
 
     def __init__(self, inputs, outputs, device_ids=(0,), replicas=(), model_kind=MODEL_BERT, max_batch_size=32,
                  pool_size=12, nworker_per_cuda=1, cuda_pipeline=2, batch_coalesce_timeout_ms=0, n_workspaces=1,
-                 affine=(1.0, 0.0), variable_length=False, length_bucket=0, per_worker_replicas=False):
+                 affine=(1.0, 0.0), variable_length=False, length_bucket=0, per_worker_replicas=False, tile_rows=0,
+                 device_visible_requests=False, warmup_autotune=False):
         cfg = ServerCfg()
+        cfg.warmup_autotune = 1 if warmup_autotune else 0
+        cfg.device_visible_requests = 1 if device_visible_requests else 0
+        cfg.tile_rows = int(tile_rows)
         cfg.gpu_model_replication = 1 if per_worker_replicas else 0
         cfg.variable_length = 1 if variable_length else 0
         cfg.length_bucket = int(length_bucket)
@@ -203,6 +215,23 @@ class Server:
         if t < 0:
             raise HostError(last_error())
         return t
+
+    def offered_load(self, prepared, n_req, rate_per_s, seed=1):
+        """Open-loop Poisson arrivals of single requests through the batch collector (spu_server_offered_load).
+        `prepared` = prepare_batch(...) rows to cycle over.  Returns dict of numpy arrays + elapsed seconds."""
+        arr, n = prepared
+        cod = np.zeros(n_req, dtype=np.float64)
+        task = np.zeros(n_req, dtype=np.float64)
+        lat = np.zeros(n_req, dtype=np.float64)
+        rows = np.zeros(n_req, dtype=np.int32)
+        el = C.c_double()
+        f64p, i32p = C.POINTER(C.c_double), C.POINTER(C.c_int32)
+        failed = lib().spu_server_offered_load(self._h, arr, n, n_req, float(rate_per_s), seed,
+                                               cod.ctypes.data_as(f64p), task.ctypes.data_as(f64p), lat.ctypes.data_as(f64p),
+                                               rows.ctypes.data_as(i32p), C.byref(el))
+        if failed < 0:
+            raise HostError(last_error())
+        return {"failed": failed, "codelet_ms": cod, "task_ms": task, "latency_ms": lat, "batch_rows": rows, "elapsed_s": el.value}
 
     def wait(self, ticket, cap=64):
         res = (Result * cap)()

@@ -9,7 +9,11 @@ from __future__ import annotations
 
 import numpy as np
 
+import math
+
 from .bert import BertConfig, _tensor_order
+from .vit import VitConfig
+from .vit import _tensor_order as _vit_tensor_order
 
 
 def _shape_kind(name: str, cfg: BertConfig):
@@ -57,3 +61,51 @@ def make_requests(cfg: BertConfig, batch: int, seq: int, seed: int = 1234, min_l
             mask[r, L:] = 0
             ids[r, L:] = 0
     return ids, mask
+
+
+def make_vit_weights(cfg: VitConfig = VitConfig(), seed: int = 0):
+    """torchvision-keyed fp32 ViT state: projection / MLP matrices N(0, (0.5/sqrt(fan_in))^2) so activations keep
+    O(1) scale through the pre-LN layers, head N(0, 0.05), biases N(0, 0.02), LayerNorm gamma 1+N(0, 0.02)."""
+    rng = np.random.Generator(np.random.PCG64(seed))
+    H, M, S = cfg.hidden, cfg.mlp, cfg.seq
+    shapes = {"conv_proj.weight": (H, cfg.channels, cfg.patch, cfg.patch), "conv_proj.bias": (H,),
+              "class_token": (1, 1, H), "encoder.pos_embedding": (1, S, H), "encoder.ln.weight": (H,),
+              "encoder.ln.bias": (H,), "heads.head.weight": (cfg.classes, H), "heads.head.bias": (cfg.classes,)}
+    out = {}
+    for name in _vit_tensor_order(cfg.layers):
+        if name in shapes:
+            shape = shapes[name]
+        elif name.endswith("in_proj_weight"):
+            shape = (3 * H, H)
+        elif name.endswith("in_proj_bias"):
+            shape = (3 * H,)
+        elif name.endswith("mlp.0.weight"):
+            shape = (M, H)
+        elif name.endswith("mlp.0.bias"):
+            shape = (M,)
+        elif name.endswith("mlp.3.weight"):
+            shape = (H, M)
+        elif name.endswith("out_proj.weight"):
+            shape = (H, H)
+        else:
+            shape = (H,)
+        a = rng.standard_normal(shape, dtype=np.float32)
+        is_ln = ".ln" in name or "ln_" in name
+        if name.endswith("weight") and is_ln:
+            a = np.float32(1.0) + a * np.float32(0.02)
+        elif name.endswith("bias"):
+            a *= np.float32(0.02)
+        elif name.startswith("heads."):
+            a *= np.float32(0.05)
+        elif a.ndim == 2 or name == "conv_proj.weight":
+            a *= np.float32(0.5 / math.sqrt(int(np.prod(shape[1:]))))
+        else:
+            a *= np.float32(0.02)
+        out[name] = a
+    return out
+
+
+def make_images(cfg: VitConfig, batch: int, seed: int = 1234):
+    """pixels ~ U[0,1) fp32 [batch, C, H, W] (the reference's input generator draws rand(), input_generator.hpp:52-56)."""
+    rng = np.random.Generator(np.random.PCG64(seed))
+    return rng.random((batch, cfg.channels, cfg.image, cfg.image), dtype=np.float32)

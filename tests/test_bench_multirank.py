@@ -58,3 +58,42 @@ def test_reference_arm_other_ranks_exit_quietly():
     out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--gpus", "2",
                           "--steps", "1", "--warmup", "1"], capture_output=True, text=True, env=env, timeout=240)
     assert out.returncode == 0 and out.stdout.strip() == ""
+
+
+def test_config_objects_are_identical_in_both_arms_and_name_the_baseline_workload():
+    sys.path.insert(0, ROOT)
+    import argparse
+
+    import bench
+
+    for cid in "ABCDE":
+        args = argparse.Namespace(config=cid, batch=None, seq=None, precision=None, min_len=None)
+        cfg = bench.resolve_config(args)
+        a, b = bench.workload_config(cfg, 8), bench.workload_config(dict(cfg), 8)
+        assert a == b and a["config_id"] == cid and "BASELINE configs[" in a["workload"] and not cfg["variant"]
+        assert set(a) == {"workload", "config_id", "model", "batch", "seq_len", "precision", "min_len", "replicas"}
+    v = bench.resolve_config(argparse.Namespace(config="B", batch=64, seq=None, precision=None, min_len=None))
+    assert v["variant"] and "variant" in bench.workload_config(v, 1)["workload"]
+    assert bench.metric_name(bench.resolve_config(argparse.Namespace(config="B", batch=None, seq=None, precision=None,
+                                                                      min_len=None))) == "BERT-base seq128 inferences/s"
+
+
+def test_parity_block_counts_what_it_says():
+    import numpy as np
+
+    sys.path.insert(0, ROOT)
+    import bench
+
+    rng = np.random.default_rng(0)
+    ref = rng.standard_normal((4, 8, 16)).astype(np.float32)
+    got = ref.copy()
+    got[0, 0, 0] += 0.5          # one element off: breaks the client rule once, may flip no argmax
+    got[1, 1] = -got[1, 1]       # one row whose argmax flips
+    live = np.ones((4, 8), dtype=np.int64)
+    live[3, 4:] = 0              # padded rows are not counted
+    got[3, 5] = 100.0
+    p = bench.parity_block(got, ref, "bf16", live)
+    assert p["rows"] == 28 and p["client_rule"]["violations"] >= 17
+    assert p["max_abs_over_max_ref"] == np.abs(got - ref)[live.astype(bool)].max() / np.abs(ref[live.astype(bool)]).max()
+    assert p["top1_strict"] == 27 / 28 and not p["gate_max_rel_ok"]
+    assert bench.parity_block(ref, ref, "fp8")["gate_max_rel_ok"] and bench.parity_block(ref, ref, "fp8")["top1_strict"] == 1.0

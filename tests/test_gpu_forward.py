@@ -202,6 +202,58 @@ def test_auto_graph_on_second_sighting(spu):
     auto.close()
 
 
+@pytest.mark.parametrize("out_bf16", [False, True])
+def test_one_graph_per_shape_is_retargeted_to_other_buffers(spu, out_bf16):
+    """Graphs are keyed by (batch, seq): a second set of ids / mask / out buffers replays the SAME graph with the
+    embedding and final-LayerNorm kernels' pointers patched; results bit-equal the eager forward, the first set of
+    buffers is left untouched, and another shape gets its own graph."""
+    from oracle import bert_oracle as bo
+    from starpu_inference_server_b200.bert import BertReplica
+
+    spec = bo.BERT_TINY
+    flags = spu.SPU_FORWARD_AUTO_GRAPH | (spu.SPU_OUTPUT_BF16 if out_bf16 else 0)
+    w = bo.make_weights(spec, 0)
+    plain = BertReplica(w, max_batch=4, max_seq=64, flags=flags & ~spu.SPU_FORWARD_AUTO_GRAPH)
+    auto = BertReplica(w, max_batch=4, max_seq=64, flags=flags)
+    dt = torch.bfloat16 if out_bf16 else torch.float32
+    sets = []
+    for k in range(3):
+        ids, mask = bo.make_inputs(spec, 4, 64, seed=500 + k, min_len=8)
+        sets.append((torch.from_numpy(ids).cuda(), torch.from_numpy(mask).cuda(),
+                     torch.full((4, 64, spec.hidden), float("nan"), device="cuda", dtype=dt)))
+    s = torch.cuda.Stream()
+    ref = []
+    with torch.cuda.stream(s):
+        for ids_d, mask_d, _ in sets:
+            o = torch.empty(4, 64, spec.hidden, device="cuda", dtype=dt)
+            plain.forward_async(ids_d, mask_d, o, stream=s)
+            ref.append(o)
+        for rnd in range(3):  # round 0 eager (first sighting of the shape), then one capture, then retargeted replays
+            for k, (ids_d, mask_d, o) in enumerate(sets):
+                o.fill_(float("nan"))
+                auto.forward_async(ids_d, mask_d, o, stream=s)
+                s.synchronize()
+                assert torch.equal(o, ref[k]), (rnd, k)
+                if rnd > 0 or k > 0:
+                    assert auto.graph_count() == 1
+        # the other buffers were not written by a launch aimed elsewhere
+        sets[0][2].fill_(7.0)
+        auto.forward_async(sets[1][0], sets[1][1], sets[1][2], stream=s)
+        s.synchronize()
+        assert bool((sets[0][2] == 7.0).all())
+        # another shape: its own graph after its own second sighting
+        for _ in range(2):
+            auto.forward_async(sets[0][0][:2], sets[0][1][:2], sets[0][2][:2], stream=s)
+        s.synchronize()
+        assert auto.graph_count() == 2
+        o2 = torch.empty(2, 64, spec.hidden, device="cuda", dtype=dt)
+        plain.forward_async(sets[0][0][:2], sets[0][1][:2], o2, stream=s)
+        s.synchronize()
+        assert torch.equal(sets[0][2][:2], o2)
+    plain.close()
+    auto.close()
+
+
 @pytest.mark.parametrize("where", ["device", "pinned_host"])
 @pytest.mark.parametrize("full_rows", [True, False])
 def test_forward_requests_stages_1_to_4(spu, where, full_rows):
@@ -331,3 +383,66 @@ def test_capacity_and_argument_errors(base, spu):
     st = spu.lib().spu_bert_forward_async(r._h, 7, spu.ptr(ids), spu.ptr(ids), 1, 8, spu.ptr(out),
                                           spu.stream_ptr())
     assert st == spu.SPU_ERR_INVALID
+
+
+def test_warmup_autotune_picks_a_tile_within_3_percent_of_the_sweep(spu, base):
+    """spu_bert_autotune: the tile it installs for each GEMM of a (32, 128) forward is within 3 %
+    of the best tile of an independent sweep through spu_gemm_bf16_cfg_async (40 launches per CUDA graph, best of
+    7 replays), the forward still matches the untuned one bit for bit where the tile is unchanged and within bf16
+    summation-order noise otherwise, and graphs captured before the tuning are dropped."""
+    bo, w, r = base
+    B, S = 32, 128
+    M = B * S
+    ids, mask = bo.make_inputs(bo.BERT_BASE, B, S, seed=77)
+    ids_d, mask_d = torch.from_numpy(ids).cuda(), torch.from_numpy(mask).cuda()
+    before = torch.empty(B, S, 768, device="cuda")
+    r.forward_async(ids_d, mask_d, before)
+    torch.cuda.synchronize()
+    cs = torch.cuda.Stream()
+    r.capture(ids_d, mask_d, before, stream=cs)
+    assert r.graph_count() >= 1
+    changed = r.autotune(B, S)  # no caller stream: measures on a private one
+    assert r.graph_count() == 0
+    tuned = {(t["N"], t["K"], t["epilogue"]): t for t in r.tuned_configs() if t["M"] == M}
+    assert set(tuned) == {(2304, 768, 0), (768, 768, 2), (3072, 768, 1), (768, 3072, 2)}
+    after = torch.empty_like(before)
+    r.forward_async(ids_d, mask_d, after)
+    torch.cuda.synchronize()
+    assert (after - before).abs().max().item() < (1e-6 if changed == 0 else 5e-2)
+
+    L = spu.lib()
+    s = torch.cuda.Stream()
+
+    def sweep_us(N, K, epi, cg, bn):
+        a = (torch.randn(M, K, device="cuda") * 0.5).to(torch.bfloat16)
+        wt = (torch.randn(N, K, device="cuda") * 0.05).to(torch.bfloat16)
+        bias = torch.randn(N, device="cuda")
+        out = torch.zeros(M, N, device="cuda", dtype=torch.float32 if epi == 2 else torch.bfloat16)
+
+        def enqueue():
+            for _ in range(40):
+                spu.check(L.spu_gemm_bf16_cfg_async(spu.ptr(a), spu.ptr(wt), spu.ptr(bias), spu.ptr(out) if epi == 2 else None,
+                                                    spu.ptr(out), M, N, K, epi, cg, bn, spu.stream_ptr(s)))
+        with torch.cuda.stream(s):
+            enqueue()
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=s):
+            enqueue()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        best = 1e9
+        for _ in range(7):
+            e0.record()
+            g.replay()
+            e1.record()
+            torch.cuda.synchronize()
+            best = min(best, e0.elapsed_time(e1) / 40 * 1e3)
+        return best
+
+    for (N, K, epi), t in tuned.items():
+        sweep = {(cg, bn): sweep_us(N, K, epi, cg, bn) for cg in (2, 1) for bn in (256, 192, 128, 64) if N % bn == 0}
+        best_cfg = min(sweep, key=sweep.get)
+        mine = sweep[(t["cta_group"], t["block_n"])]
+        print(f"autotune N={N} K={K} epi={epi}: chose {(t['cta_group'], t['block_n'])} {t['us']:.2f} us "
+              f"(sweep {mine:.2f} us), sweep best {best_cfg} {sweep[best_cfg]:.2f} us")
+        assert mine <= 1.03 * sweep[best_cfg], (N, K, epi, t, sweep)

@@ -321,3 +321,63 @@ def test_two_devices_in_one_process(host):
     for r in reps:
         r.close()
 
+
+
+@pytest.mark.parametrize("variable_length", [False, True])
+def test_device_visible_requests_through_the_task_path(host, variable_length):
+    """SURVEY 8(f) row 2 on the SERVED path (spu_server_cfg.device_visible_requests): requests and responses live in
+    pinned host memory, the host gathers nothing -- the input slot carries a table of row addresses -- and the
+    codelet runs gather/pad/mask -> encoder -> per-request scatter on the GPU.  Every response is checked against
+    the fp32 ORACLE run on that request alone; multi-sample requests, ragged lengths (variable_length) and the
+    dynamic-batching collector are covered; the output slot carries no payload (first_value is not the response)."""
+    from oracle import bert_oracle as bo
+    from starpu_inference_server_b200 import capi
+    from starpu_inference_server_b200.bert import BertReplica
+
+    spec = bo.BERT_TINY
+    w = bo.make_weights(spec, 0)
+    S, H = 32, spec.hidden
+    rep = BertReplica(w, max_batch=8, max_seq=S, n_workspaces=2, flags=capi.SPU_REQUEST_IO)
+    rng = np.random.default_rng(33)
+    shapes = [(1, 17), (2, 32), (1, 5), (1, 32), (2, 9)] if variable_length else [(1, S), (2, S), (1, S), (3, S)]
+    reqs = []
+    for b, n in shapes:
+        ids = torch.from_numpy(rng.integers(1, spec.vocab, size=(b, n), dtype=np.int64)).pin_memory()
+        mask = torch.ones(b, n, dtype=torch.int64)
+        if not variable_length:
+            for r in range(b):
+                mask[r, int(rng.integers(3, n + 1)):] = 0
+        mask = mask.pin_memory()
+        out = torch.full((b, n, H), float("nan")).pin_memory()
+        reqs.append((b, n, ids, mask, out))
+    with host.Server(inputs=[("input_ids", "i64", [1, S]), ("attention_mask", "i64", [1, S])],
+                     outputs=[("output0", "f32", [1, S, H])], replicas=[rep], model_kind=host.MODEL_BERT,
+                     max_batch_size=8, pool_size=2, n_workspaces=2, variable_length=variable_length,
+                     device_visible_requests=True, batch_coalesce_timeout_ms=20) as srv:
+        def check(tag):
+            for i, (b, n, ids, mask, out) in enumerate(reqs):
+                ref = bo.bert_forward(w, spec, ids.numpy(), mask.numpy())
+                got = out.numpy()
+                live = mask.numpy().astype(bool)
+                assert np.isfinite(got[live]).all(), (tag, i)
+                assert np.abs(got[live] - ref[live]).max() / np.abs(ref).max() < 2e-2, (tag, i)
+                out.fill_(float("nan"))
+
+        res = srv.wait(srv.submit_batch([(i, b, [ids, mask], [out]) for i, (b, n, ids, mask, out) in enumerate(reqs)]))
+        assert all(r.ok == 1 for r in res), [r.error for r in res]
+        assert res[0].batch_rows == sum(b for b, *_ in reqs) and [r.rows for r in res] == [b for b, *_ in reqs]
+        check("one task")
+        tickets = [srv.enqueue(100 + i, b, [ids, mask], [out]) for i, (b, n, ids, mask, out) in enumerate(reqs)]
+        rows = 0
+        for t in tickets:
+            (r,) = srv.wait(t)
+            assert r.ok == 1, r.error
+            rows = max(rows, r.batch_rows)
+        assert rows > 1  # the collector merged requests
+        check("collector")
+        # a request without a response buffer cannot be served on this path
+        b, n, ids, mask, out = reqs[0]
+        with pytest.raises(host.HostError, match="output buffer"):
+            srv.wait(srv.submit_batch([(0, b, [ids, mask], [None])]))
+        assert srv.stats()["codelet_failures"] == 0
+    rep.close()

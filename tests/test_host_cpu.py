@@ -267,3 +267,17 @@ def test_can_merge_jobs(host):
     assert _merge(host, [1, 3, 224, 224], F32, [2, 3, 224, 224], F32) == 1
     assert _merge(host, [1, 128], I64, [1, 128, 1], I64) == 0  # rank must match
     assert _merge(host, [5], F32, [9], F32) == 1              # rank 1: nothing but dim 0
+
+
+def test_tile_aware_close_rule(host):
+    """The collector's tile-aware preference (spu_server_cfg.tile_rows): a batch that ends inside a 256-row GEMM tile
+    and may still grow asks for more; whole tiles, a full batch, or tile_rows = 0 do not."""
+    L = host.lib()
+    assert L.spu_host_tile_aware_wants_more(3, 128, 32, 256) == 1     # 384 token rows = 1.5 tiles
+    assert L.spu_host_tile_aware_wants_more(4, 128, 32, 256) == 0     # 512 = 2 tiles
+    assert L.spu_host_tile_aware_wants_more(31, 128, 32, 256) == 1
+    assert L.spu_host_tile_aware_wants_more(32, 128, 32, 256) == 0    # at the cap
+    assert L.spu_host_tile_aware_wants_more(5, 100, 64, 256) == 1     # 500 rows
+    assert L.spu_host_tile_aware_wants_more(64, 100, 64, 256) == 0    # at the cap although 6400 % 256 != 0
+    assert L.spu_host_tile_aware_wants_more(3, 128, 32, 0) == 0       # switched off
+    assert L.spu_host_tile_aware_wants_more(1, 197, 64, 256) == 1     # ViT: 197 tokens per image
