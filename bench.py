@@ -393,6 +393,8 @@ def run_b200(args, cfg, rank, local_rank, world):
                  "fp8x6": capi.SPU_PREC_FP8_E4M3 | (6 << 8)}[precision]
         if args.output_bf16:
             flags |= capi.SPU_OUTPUT_BF16
+        if not args.output_bf16:
+            flags |= capi.SPU_REQUEST_IO  # the device-visible-requests e2e leg needs its arenas
         if args.auto_graph:
             # the codelet path replays a CUDA graph from the second sighting of a slot's device
             # buffers on (warm-up capture, src/core/warmup.cpp:225-299)
@@ -426,15 +428,23 @@ def run_b200(args, cfg, rank, local_rank, world):
     # pointer tuple; `--streams` workers issue tasks round-robin like StarPU's CUDA workers
     n_str = max(1, min(args.streams, n_pipe))
     wstreams = [stream] + [torch.cuda.Stream(device=dev) for _ in range(n_str - 1)]
-    if not is_vit:
+    if not is_vit and not (cfg["min_len"] is not None and precision == "bf16" and not args.no_packed):
         for k, st in enumerate(wstreams):
             with torch.cuda.stream(st):
                 for i in range(n_sets):
                     rep.capture(*in_d[i], out_d[k], ws=k, stream=st)
         torch.cuda.synchronize(dev)
 
+    # variable-length config: the host knows every request's length, so the codelet runs the packed forward (the
+    # encoder skips the padding rows; what the variable_length served path does)
+    packed = (not is_vit) and cfg["min_len"] is not None and precision == "bf16" and not args.no_packed
+    lens_h = [m.sum(1).astype(np.int32) for _, m in host] if packed else None
+
     def step_resident(i, k=0):
-        rep.forward_async(*in_d[i % n_sets], out_d[k], ws=k, stream=wstreams[k])
+        if packed:
+            rep.forward_packed_async(in_d[i % n_sets][0], lens_h[i % n_sets], out_d[k], ws=k, stream=wstreams[k])
+        else:
+            rep.forward_async(*in_d[i % n_sets], out_d[k], ws=k, stream=wstreams[k])
 
     def timed_loop(n_steps):
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -481,11 +491,20 @@ def run_b200(args, cfg, rank, local_rank, world):
     # each class runs alone as 5 forwards' worth of launches inside one CUDA graph; taken BEFORE the sustained loop,
     # i.e. in the thermal / power state the burst peak of MEASURED_PEAKS.json was taken in
     stage_ms, gemm_ms = None, None
+    gemm_rows = B * S
     if not is_vit:
-        stage_ms = {k: min(rep.stage_chain_ms(*in_d[0], out_d[0], [k], stream=stream) for _ in range(3))
+        chain_in = in_d[0]
+        if packed:
+            # the packed forward's GEMMs see M = true tokens: time the chain on a dense batch of that many rows
+            b2 = max(1, int(round(true_tokens / 128)))
+            gemm_rows = b2 * 128
+            chain_in = (in_d[0][0].reshape(-1)[:gemm_rows].reshape(b2, 128).contiguous(),
+                        torch.ones(b2, 128, dtype=torch.int64, device=dev))
+        chain_out = out_d[0].reshape(-1)[:gemm_rows * spec.hidden].reshape(-1, 128, spec.hidden) if packed else out_d[0]
+        stage_ms = {k: min(rep.stage_chain_ms(*chain_in, chain_out, [k], stream=stream) for _ in range(3))
                     for k in capi.STAGE_NAMES}
         gemm_names = ["gemm_qkv", "gemm_attn_out", "gemm_ffn1", "gemm_ffn2"]
-        gemm_ms = min(rep.stage_chain_ms(*in_d[0], out_d[0], gemm_names, stream=stream) for _ in range(3))
+        gemm_ms = min(rep.stage_chain_ms(*chain_in, chain_out, gemm_names, stream=stream) for _ in range(3))
     # ---------------- sustained figure: >= 2 s of back-to-back steps ----------------
     per_step_ms = ms_total / args.steps
     sus_steps = int(max(args.steps, min(50000, 2200.0 / max(per_step_ms, 1e-3))))
@@ -521,16 +540,24 @@ def run_b200(args, cfg, rank, local_rank, world):
         io = dict(inputs=[("input_ids", "i64", [1, S]), ("attention_mask", "i64", [1, S])],
                   outputs=[("output0", "bf16" if args.output_bf16 else "f32", [1, S, spec.hidden])])
         kind = hostapi.MODEL_BERT
-        req_rows = [[(np.ascontiguousarray(i[r:r + 1]), np.ascontiguousarray(m[r:r + 1])) for r in range(B)]
-                    for i, m in host]
-        h2d = 2 * B * S * 8
-        d2h = B * S * HIDDEN * (2 if args.output_bf16 else 4)
+        if packed:
+            # requests arrive with their OWN length ([1, L] ids + all-ones mask): variable-length admission pads
+            # them in the host gather and hands the lengths to the codelet
+            req_rows = [[(np.ascontiguousarray(i[r:r + 1, :lens_h[k][r]]), np.ones((1, int(lens_h[k][r])), np.int64))
+                         for r in range(B)] for k, (i, m) in enumerate(host)]
+        else:
+            req_rows = [[(np.ascontiguousarray(i[r:r + 1]), np.ascontiguousarray(m[r:r + 1])) for r in range(B)]
+                        for i, m in host]
+        s_batch = [int(l.max()) for l in lens_h] if packed else [S] * n_sets
+        h2d = int(np.mean([2 * B * sb * 8 for sb in s_batch]))
+        d2h = int(np.mean([B * sb * HIDDEN * (2 if args.output_bf16 else 4) for sb in s_batch]))
         out_row_shape, out_np = (1, S, spec.hidden), (np.uint16 if args.output_bf16 else np.float32)
 
-    def make_server(coalesce_ms=0):
+    def make_server(coalesce_ms=0, device_visible=False):
         return hostapi.Server(**io, replicas=[rep], device_ids=[local_rank], model_kind=kind, max_batch_size=B,
                               pool_size=e2e_pool, nworker_per_cuda=e2e_workers, cuda_pipeline=e2e_pipeline,
-                              n_workspaces=n_pipe, batch_coalesce_timeout_ms=coalesce_ms, tile_rows=256 if coalesce_ms else 0)
+                              n_workspaces=n_pipe, batch_coalesce_timeout_ms=coalesce_ms, tile_rows=256 if coalesce_ms else 0,
+                              device_visible_requests=device_visible, variable_length=bool(packed))
 
     srv = make_server()
     prepared = [srv.prepare_batch([(r, 1, list(a), [None]) for r, a in enumerate(rows)]) for rows in req_rows]
@@ -570,12 +597,26 @@ def run_b200(args, cfg, rank, local_rank, world):
     e2e_out_s, _ = e2e_median_of_3(prepared_out, False)
     host_stats = srv.stats()
     srv.close()
+    # SURVEY 8(f) row 2 on the served path: requests and responses in PINNED host memory, no host gather and no
+    # response copy -- the input slot carries a table of row addresses, the codelet gathers / pads / masks on the
+    # device and its scatter kernel writes every response straight into the caller's buffer
+    e2e_dv_s = None
+    if not is_vit and not args.output_bf16:
+        pin = [[(torch.from_numpy(a).pin_memory(), torch.from_numpy(m).pin_memory(),
+                 torch.empty(out_row_shape, dtype=torch.float32).pin_memory()) for a, m in rows] for rows in req_rows]
+        srv = make_server(device_visible=True)
+        prepared_dv = [srv.prepare_batch([(r, 1, [a, m], [o]) for r, (a, m, o) in enumerate(rows)]) for rows in pin]
+        run_e2e(max(args.warmup, 8 * e2e_workers), False, prepared_dv)
+        e2e_dv_s, _ = e2e_median_of_3(prepared_dv, False)
+        srv.close()
+        n_live = int(lens_h[0][0]) if packed else S  # rows of request 0 the path delivers
+        dv_err = float(np.abs(pin[0][0][2].numpy()[0, :n_live] - got[0, :n_live]).max()) if prow >= 1 else None
     if fails:
         raise SystemExit(f"bench.py: {fails} requests failed on the e2e path")
 
     # ---------------- reduce over ranks ----------------
-    ms_total, sus_ms, e2e_ms, e2e_out_ms = reduce_max_over_ranks([ms_total, sus_ms, e2e_s * 1e3, e2e_out_s * 1e3],
-                                                                 torch.device("cpu"))
+    ms_total, sus_ms, e2e_ms, e2e_out_ms, e2e_dv_ms = reduce_max_over_ranks(
+        [ms_total, sus_ms, e2e_s * 1e3, e2e_out_s * 1e3, (e2e_dv_s or 0.0) * 1e3], torch.device("cpu"))
     e2e_value = whole_job_rate(B, args.steps, world, e2e_ms)
 
     # ---------------- offered load through the batch collector (rank 0, N=1 only) ----------------
@@ -622,7 +663,8 @@ def run_b200(args, cfg, rank, local_rank, world):
                            "LayerNorm and im2col kernels included); no GEMM-only chain hook exists for ViT"}
     else:
         gemm_flop_step = LAYERS * 24 * true_tokens * HIDDEN * HIDDEN  # charged on true lengths
-        gemm_tflops = gemm_flop_step / (gemm_ms / 1e3) / 1e12
+        # the timed chain ran `gemm_rows` rows (= the padded batch, or ~the true tokens on the packed path)
+        gemm_tflops = LAYERS * 24 * (true_tokens if not packed else gemm_rows) * HIDDEN * HIDDEN / (gemm_ms / 1e3) / 1e12
         peak_s, peak_b = peaks["tflops"], peaks["tflops_burst"]
         note = ""
         if fp8:
@@ -646,6 +688,8 @@ def run_b200(args, cfg, rank, local_rank, world):
         "config": workload_config(cfg, world),
         "run": {"output_dtype": "bf16" if args.output_bf16 else "f32", "resident_streams": n_str,
                 "mean_true_tokens_per_batch": true_tokens, "cores_per_rank": pinned_cores,
+                "forward": ("packed: the encoder runs on the true tokens of each right-padded batch (lengths known to the "
+                            "host), eager launches" if packed else "padded [batch, seq] with mask, CUDA-graph replay"),
                 "gemm_tiles": None if is_vit or not args.autotune else {
                     "how": "warm-up autotune: every (cta_group, BLOCK_N) timed per GEMM problem, winner installed",
                     "differ_from_cost_model": tuned_changed,
@@ -665,6 +709,12 @@ def run_b200(args, cfg, rank, local_rank, world):
                 "delivered": {"value": whole_job_rate(B, args.steps, world, e2e_out_ms), "unit": UNIT,
                               "what": "the same path plus the per-request response copy into caller-owned buffers "
                                       "(the reference's fill_output_tensor), on the completer threads"},
+                "device_visible": None if not e2e_dv_ms else {
+                    "value": whole_job_rate(B, args.steps, world, e2e_dv_ms), "unit": UNIT,
+                    "max_abs_vs_resident_path": dv_err,
+                    "what": "spu_server_cfg.device_visible_requests: requests and responses in pinned host memory, "
+                            "the slot carries a table of row addresses, gather/pad/mask and the per-request scatter run "
+                            "on the GPU (no host gather, no D2H of a slot, no response copy)"},
                 "tasks": int(host_stats["tasks"]),
                 "how": f"median of 3 segments of {args.steps} steps (rank 0 segments, inferences/s: "
                        + ", ".join(f"{B * args.steps * world / t:.0f}" for t in e2e_segments) + ")",
@@ -677,6 +727,9 @@ def run_b200(args, cfg, rank, local_rank, world):
                        "what": "device time of one task (batch) = codelet_start..codelet_end"},
         "roofline": roofline,
         "stage_ms_per_step": stage_ms,
+        "stage_ms_note": ("kernel classes timed alone on a DENSE batch of %d rows at seq 128 (the packed forward's GEMM / LayerNorm "
+                          "row count); the attention entry is therefore not this workload's ragged attention" % gemm_rows)
+                         if packed else None,
     }
     if world == 1 and not args.no_cpu_baseline:
         codelet = CpuCodelet(cfg)
@@ -724,6 +777,8 @@ def main():
     ap.add_argument("--streams", type=int, default=2, help="CUDA workers issuing resident tasks round-robin")
     ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the CPU leg (also drops the parity block)")
     ap.add_argument("--no-offered-load", action="store_true")
+    ap.add_argument("--no-packed", action="store_true",
+                    help="variable-length configs: run the padded forward (mask) instead of the packed one (lengths)")
     ap.add_argument("--no-autotune", dest="autotune", action="store_false",
                     help="keep the static cost model's GEMM tiles instead of timing the candidates at warm-up")
     ap.add_argument("--no-pin", action="store_true", help="N>1: do not give each rank its own slice of the host cores")

@@ -118,6 +118,19 @@ spu_status spu_bert_forward_async(spu_replica *r, int32_t ws_idx,
                                   int32_t batch, int32_t seq, float *out,
                                   void *stream);
 
+/* The same forward for RIGHT-PADDED batches whose true lengths the host knows (a variable-length
+ * batch padded by the host gather): lens[b] in [1, seq] (HOST array, read before the call returns) is the number of
+ * real tokens of sequence b; ids is the padded [batch, seq] DEVICE array; no mask is needed.  The encoder runs on
+ * the sum(lens) real tokens only -- GEMMs, LayerNorms and attention skip the padding instead of multiplying it --
+ * and `out` receives the padded [batch, seq, hidden] layout with rows t >= lens[b] set to ZERO (the reference
+ * leaves the model's values for [PAD] tokens there; no consumer reads them).  Rows t < lens[b] are bit-identical
+ * to spu_bert_forward_async with the equivalent mask.  bf16 replicas, batch <= 256; launches eagerly (the token
+ * count changes from batch to batch, so there is no graph to replay). */
+spu_status spu_bert_forward_packed_async(spu_replica *r, int32_t ws_idx, const int64_t *ids, const int32_t *lens,
+                                         int32_t batch, int32_t seq, float *out, void *stream);
+/* 1 when spu_bert_forward_packed_async serves this replica for batches of `batch` sequences. */
+int32_t spu_bert_packed_supported(const spu_replica *r, int32_t batch);
+
 /* Number of kernel launches one forward of (batch, seq) enqueues. */
 int32_t spu_bert_forward_launch_count(const spu_replica *r);
 

@@ -117,6 +117,16 @@ class BertReplica:
                                                      capi.ptr(out), capi.stream_ptr(stream)))
         return out
 
+    def forward_packed_async(self, ids, lens, out, ws: int = 0, stream=None):
+        """Right-padded batch whose true lengths are known on the host: ids int64 CUDA [B,S], lens = B host ints.
+        The encoder runs on sum(lens) tokens; out [B,S,hidden] gets zeros behind each length."""
+        b, s = ids.shape
+        lens = np.ascontiguousarray(np.asarray(lens, dtype=np.int32))
+        assert lens.shape == (b,)
+        capi.check(capi.lib().spu_bert_forward_packed_async(self._h, ws, capi.ptr(ids), lens.ctypes.data, b, s,
+                                                            capi.ptr(out), capi.stream_ptr(stream)))
+        return out
+
     def forward_requests_async(self, src_ids_table, src_mask_table, len_dev, n_req: int, seq: int, dst_table,
                                full_rows: bool = True, ws: int = 0, stream=None):
         """Stages 1-4 on per-request buffers (replica created with capi.SPU_REQUEST_IO).  The tables are int64 CUDA

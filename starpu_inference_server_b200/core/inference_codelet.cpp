@@ -196,6 +196,15 @@ void run_inference(InferenceParams *params, StarpuBufferSpan buffers, int device
       require_bytes(buffers[2], spu_bert_output_bytes(model->replica, static_cast<int32_t>(B), static_cast<int32_t>(S)),
                     "Output");
       const int ws = workspace_for_this_thread(model);
+      if (params->layout.seq_lens.size() == static_cast<size_t>(B) &&
+          spu_bert_packed_supported(model->replica, static_cast<int32_t>(B)) == 1) {
+        // right-padded batch with host-known lengths: skip the padding instead of multiplying it
+        check_spu(spu_bert_forward_packed_async(model->replica, ws, reinterpret_cast<const int64_t *>(buffers[0]->ptr),
+                                                params->layout.seq_lens.data(), static_cast<int32_t>(B),
+                                                static_cast<int32_t>(S), reinterpret_cast<float *>(buffers[2]->ptr),
+                                                stream));
+        break;
+      }
       check_spu(spu_bert_forward_async(model->replica, ws, reinterpret_cast<const int64_t *>(buffers[0]->ptr),
                                        reinterpret_cast<const int64_t *>(buffers[1]->ptr), static_cast<int32_t>(B),
                                        static_cast<int32_t>(S), reinterpret_cast<float *>(buffers[2]->ptr), stream));

@@ -83,6 +83,10 @@ struct TensorLayout {
   std::vector<std::vector<int64_t>> dims;  // dims[i][0] = effective batch (inference_task.cpp:606-613)
   std::vector<int64_t> num_dims;
   std::vector<ScalarType> input_types;
+  // variable_length batches whose every request mask is all ones (the usual case: the padding is the host
+  // gather's own): true token count of each sample row.  Lets the codelet run the encoder on the real tokens
+  // only (spu_bert_forward_packed_async).  Empty = unknown, the padded forward runs.
+  std::vector<int32_t> seq_lens;
 };
 
 struct Limits {

@@ -166,6 +166,20 @@ auto slice_outputs_for_sub_job(const std::vector<HostTensor> &aggregated_outputs
   return result;
 }
 
+// Is every request's second input (attention_mask, int64 [batch, L]) all non-zero?  Then the only padding of the
+// batch is the host gather's own and the rows' true lengths are the requests' L.
+auto masks_all_ones(const std::vector<std::shared_ptr<InferenceJob>> &jobs) -> bool {
+  for (const auto &j : jobs) {
+    if (!j) continue;
+    if (j->inputs.size() != 2 || j->inputs[1].type != ScalarType::Int64 || !j->inputs[1].defined()) return false;
+    const auto *m = reinterpret_cast<const int64_t *>(j->inputs[1].data);
+    const size_t n = j->inputs[1].numel();
+    for (size_t i = 0; i < n; ++i)
+      if (m[i] == 0) return false;
+  }
+  return true;
+}
+
 // instead of gathering the requests' bytes, describe them.  One entry per sample row of the
 // batch, in request order: where its token ids and mask words live, how many there are, and where its hidden
 // states go ([own seq, hidden] fp32 on a variable_length server, [seq, hidden] otherwise).  The table rides in the
@@ -362,6 +376,13 @@ void TaskRunner::submit_batch(const std::vector<std::shared_ptr<InferenceJob>> &
   params->batch_size = effective_batch;
   params->request_id = master->request_id;
   params->request_io = request_io;
+  // variable_length + every mask all ones: hand the true lengths to the codelet (packed forward)
+  if (model_.variable_length && !request_io.enabled && model_.inputs.size() == 2 && masks_all_ones(jobs)) {
+    for (const auto &j : jobs)
+      if (j)
+        for (int64_t s = 0; s < j->batch_size(); ++s)
+          params->layout.seq_lens.push_back(static_cast<int32_t>(j->inputs[0].dims[1]));
+  }
   ctx->request_io = request_io.enabled;
   params->limits.max_inputs = InferLimits::MaxInputs;
   params->limits.max_dims = InferLimits::MaxDims;

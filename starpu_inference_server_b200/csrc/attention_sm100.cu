@@ -16,6 +16,10 @@
 //          collected one tile late; V single-buffered so that a CTA needs 97 KB -> 2 CTAs per SM.
 // Chunks / KV tiles behind the last live key of a hard-masked (padded) sequence are skipped: they add
 // exactly 0 to every row sum and to O.
+// PACKED mode (cu_seqlens != nullptr): qkv holds the sequences back to back ([total_tokens, 3H], no padding rows),
+// sequence b owns rows cu_seqlens[b] .. cu_seqlens[b+1]; a CTA reads its own length, tiles that start behind it exit
+// at once, a tile that runs past it sees the next sequence's rows as keys -- masked with -inf like any key past the
+// end -- and as query rows that are computed and never stored.
 //
 // Restates the attention block of HF BertSelfAttention / torchvision MultiheadAttention that
 // LibTorch executes inside Module::forward (/root/reference/src/core/starpu_setup.cpp:610);
@@ -196,7 +200,8 @@ __device__ __forceinline__ float row_exp(uint32_t tmem_row, int nch, int c0, con
 template <bool MULTI, bool OUT_E4M3>
 __global__ void __launch_bounds__(AttnCfg<MULTI>::kThreads, MULTI ? 2 : 4)
 attention_tc_kernel(const __grid_constant__ CUtensorMap tm_qkv, const float *__restrict__ mask_bias,
-                    void *__restrict__ ctx_out, int seq, int heads, float q_inv_scale) {
+                    void *__restrict__ ctx_out, int seq, int heads, float q_inv_scale,
+                    const int32_t *__restrict__ cu_seqlens) {
   using Cfg = AttnCfg<MULTI>;
   constexpr int kOCols = Cfg::kOCols;
   extern __shared__ uint8_t smem_raw[];
@@ -217,6 +222,19 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm_qkv, const float *__r
   const int half = MULTI ? (tid >> 7) : 0;    // which half of the key / output columns (MULTI)
   const int qt = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
   const int hidden = heads * kHeadDim;
+  // PACKED: this sequence's rows start at row0 of the [total_tokens, 3H] array (TMA batch coordinate 0) and there are
+  // `seq` of them; cu_seqlens was written by an earlier kernel of the chain (stream order, no PDL overlap with it)
+  int row0 = 0, bz = b;
+  if (cu_seqlens != nullptr) {
+    pdl_wait_prior_grid();
+    row0 = __ldg(cu_seqlens + b);
+    seq = __ldg(cu_seqlens + b + 1) - row0;
+    bz = 0;
+    if (qt * kTile >= seq) {  // block-uniform: nothing of this tile is live
+      pdl_launch_dependents();
+      return;
+    }
+  }
 
   // thread 0 gets the first loads in flight before anything else; warp 1 allocates TMEM meanwhile
   if (tid == 0) {
@@ -225,10 +243,10 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm_qkv, const float *__r
     fence_barrier_init();
     pdl_wait_prior_grid();  // qkv is written by the preceding GEMM
     mbar_arrive_expect_tx(&bar_k[0], 2 * kTileBytes);
-    tma_load_3d(s_q, &tm_qkv, &bar_k[0], h * kHeadDim, qt * kTile, b);
-    tma_load_3d(s_k, &tm_qkv, &bar_k[0], hidden + h * kHeadDim, 0, b);
+    tma_load_3d(s_q, &tm_qkv, &bar_k[0], h * kHeadDim, row0 + qt * kTile, bz);
+    tma_load_3d(s_k, &tm_qkv, &bar_k[0], hidden + h * kHeadDim, row0, bz);
     mbar_arrive_expect_tx(&bar_v[0], kTileBytes);
-    tma_load_3d(s_v, &tm_qkv, &bar_v[0], 2 * hidden + h * kHeadDim, 0, b);
+    tma_load_3d(s_v, &tm_qkv, &bar_v[0], 2 * hidden + h * kHeadDim, row0, bz);
   }
   if (warp == 1) {
     tmem_alloc(tmem_slot, Cfg::kTmemCols);
@@ -303,7 +321,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm_qkv, const float *__r
   if (tid == 0) {
     if (MULTI && n_kv > 1) {  // second K tile: in flight before the first softmax starts
       mbar_arrive_expect_tx(&bar_k[1], kTileBytes);
-      tma_load_3d(s_k + kTileBytes, &tm_qkv, &bar_k[1], hidden + h * kHeadDim, kTile, b);
+      tma_load_3d(s_k + kTileBytes, &tm_qkv, &bar_k[1], hidden + h * kHeadDim, row0 + kTile, bz);
     }
     issue_qk(0);
   }
@@ -339,7 +357,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm_qkv, const float *__r
     tcgen05_fence_after();
     if (MULTI && tid == 0 && j + 2 < n_kv) {  // S_j done: its K buffer takes tile j+2
       mbar_arrive_expect_tx(&bar_k[buf], kTileBytes);
-      tma_load_3d(s_k + buf * kTileBytes, &tm_qkv, &bar_k[buf], hidden + h * kHeadDim, (j + 2) * kTile, b);
+      tma_load_3d(s_k + buf * kTileBytes, &tm_qkv, &bar_k[buf], hidden + h * kHeadDim, row0 + (j + 2) * kTile, bz);
     }
 
     // ---- pass 1: max of s' = s*scale + bias over this thread's columns of query row `row` ----
@@ -358,7 +376,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm_qkv, const float *__r
       if (tid == 0) {
         if (j > 0) {  // P V of tile j-1 has completed: the V buffer takes tile j
           mbar_arrive_expect_tx(&bar_v[0], kTileBytes);
-          tma_load_3d(s_v, &tm_qkv, &bar_v[0], 2 * hidden + h * kHeadDim, j * kTile, b);
+          tma_load_3d(s_v, &tm_qkv, &bar_v[0], 2 * hidden + h * kHeadDim, row0 + j * kTile, bz);
         }
         if (j + 1 < n_kv) issue_qk(j + 1);  // runs under pass 2 of tile j
       }
@@ -402,7 +420,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tm_qkv, const float *__r
   // ---- normalise and store: this thread holds kOCols columns of query row `row` ----
   const float inv = 1.f / l_run;
   const int q_row = qt * kTile + row;
-  const size_t tok0 = static_cast<size_t>(b) * seq;
+  const size_t tok0 = cu_seqlens != nullptr ? static_cast<size_t>(row0) : static_cast<size_t>(b) * seq;
   if constexpr (OUT_E4M3) {
     // per-tensor scaled e4m3 operand of the attention-output GEMM: 64 contiguous bytes per row
     if (q_row < seq) {
@@ -477,13 +495,13 @@ EncodeTiledFn attn_encode_fn() {
 
 template <bool MULTI, bool OUT_E4M3>
 spu_status launch_tc(const CUtensorMap &map, const float *mask_bias, void *ctx, int batch, int seq, int heads,
-                     cudaStream_t stream, float q_inv_scale) {
+                     cudaStream_t stream, float q_inv_scale, const int32_t *cu_seqlens) {
   using Cfg = AttnCfg<MULTI>;
   auto kern = attention_tc_kernel<MULTI, OUT_E4M3>;
   SPU_CUDA_TRY((ensure_dynamic_smem<attention_tc_kernel<MULTI, OUT_E4M3>>(Cfg::kSmemBytes)));
   dim3 grid((seq + kTile - 1) / kTile, heads, batch);
   SPU_CUDA_TRY(launch_pdl(kern, grid, dim3(Cfg::kThreads), Cfg::kSmemBytes, stream, map, mask_bias, ctx, seq, heads,
-                          q_inv_scale));
+                          q_inv_scale, cu_seqlens));
   SPU_CUDA_TRY(cudaGetLastError());
   return SPU_OK;
 }
@@ -491,9 +509,14 @@ spu_status launch_tc(const CUtensorMap &map, const float *mask_bias, void *ctx, 
 }  // namespace
 
 // qkv: bf16 [batch*seq, 3*heads*64] (Q | K | V column blocks), ctx: bf16 or e4m3 [batch*seq, heads*64].
+// PACKED (cu_seqlens != nullptr, DEVICE int32 [batch + 1]): qkv / ctx hold total_tokens rows, `seq` is the longest
+// sequence (it sizes the grid and picks the kernel variant), mask_bias must be null.
 spu_status attention_tc_launch(const void *qkv, const float *mask_bias, void *ctx, int batch, int seq, int heads,
-                               cudaStream_t stream, bool out_e4m3, float q_inv_scale) {
+                               cudaStream_t stream, bool out_e4m3, float q_inv_scale, const int32_t *cu_seqlens,
+                               int total_tokens) {
   SPU_REQUIRE(qkv && ctx, SPU_ERR_INVALID, "attention: null argument");  // mask_bias may be null (no mask)
+  SPU_REQUIRE(cu_seqlens == nullptr || (mask_bias == nullptr && total_tokens > 0), SPU_ERR_INVALID,
+              "attention: packed sequences carry no mask and need their total row count");
   SPU_REQUIRE(batch > 0 && seq > 0 && heads > 0, SPU_ERR_INVALID, "attention: empty shape");
   SPU_REQUIRE(batch <= 65535 && heads <= 65535, SPU_ERR_CAPACITY, "attention: grid too large");
   SPU_REQUIRE((reinterpret_cast<uintptr_t>(qkv) & 15) == 0, SPU_ERR_INVALID, "attention: qkv must be 16-byte aligned");
@@ -501,8 +524,10 @@ spu_status attention_tc_launch(const void *qkv, const float *mask_bias, void *ct
   SPU_REQUIRE(enc != nullptr, SPU_ERR_CUDA, "cuTensorMapEncodeTiled entry point unavailable");
   // qkv viewed as [batch, seq, 3H]: a 128-row box that runs past a sequence end is zero-filled
   const cuuint64_t ld = static_cast<cuuint64_t>(3) * heads * kHeadDim;
-  cuuint64_t gdim[3] = {ld, static_cast<cuuint64_t>(seq), static_cast<cuuint64_t>(batch)};
-  cuuint64_t gstride[2] = {ld * 2, ld * 2 * static_cast<cuuint64_t>(seq)};
+  // packed: ONE "batch" of total_tokens rows (rows past the end are zero-filled, rows of the next sequence masked)
+  const cuuint64_t rows = cu_seqlens != nullptr ? static_cast<cuuint64_t>(total_tokens) : static_cast<cuuint64_t>(seq);
+  cuuint64_t gdim[3] = {ld, rows, cu_seqlens != nullptr ? 1u : static_cast<cuuint64_t>(batch)};
+  cuuint64_t gstride[2] = {ld * 2, ld * 2 * rows};
   cuuint32_t box[3] = {kHeadDim, kTile, 1};
   cuuint32_t estride[3] = {1, 1, 1};
   CUtensorMap map;
@@ -514,10 +539,10 @@ spu_status attention_tc_launch(const void *qkv, const float *mask_bias, void *ct
     return SPU_ERR_CUDA;
   }
   if (seq <= kTile)
-    return out_e4m3 ? launch_tc<false, true>(map, mask_bias, ctx, batch, seq, heads, stream, q_inv_scale)
-                    : launch_tc<false, false>(map, mask_bias, ctx, batch, seq, heads, stream, 1.f);
-  return out_e4m3 ? launch_tc<true, true>(map, mask_bias, ctx, batch, seq, heads, stream, q_inv_scale)
-                  : launch_tc<true, false>(map, mask_bias, ctx, batch, seq, heads, stream, 1.f);
+    return out_e4m3 ? launch_tc<false, true>(map, mask_bias, ctx, batch, seq, heads, stream, q_inv_scale, cu_seqlens)
+                    : launch_tc<false, false>(map, mask_bias, ctx, batch, seq, heads, stream, 1.f, cu_seqlens);
+  return out_e4m3 ? launch_tc<true, true>(map, mask_bias, ctx, batch, seq, heads, stream, q_inv_scale, cu_seqlens)
+                  : launch_tc<true, false>(map, mask_bias, ctx, batch, seq, heads, stream, 1.f, cu_seqlens);
 }
 
 }  // namespace spu

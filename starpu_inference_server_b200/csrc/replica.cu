@@ -90,6 +90,7 @@ spu_status build(spu_replica *r, const float *const *t) {
     SPU_TRY(dev_alloc(r, &ws.ctx, rows * H));
     SPU_TRY(dev_alloc(r, &ws.h, rows * F));
     SPU_TRY(dev_alloc(r, &ws.mask_bias, rows));
+    SPU_TRY(dev_alloc(r, &ws.cu_seqlens, static_cast<size_t>(kMaxPackedBatch) + 1));
     if (r->flags & SPU_REQUEST_IO) {
       SPU_TRY(dev_alloc(r, &ws.req_ids, rows));
       SPU_TRY(dev_alloc(r, &ws.req_mask, rows));
@@ -243,6 +244,57 @@ spu_status enqueue_forward(spu_replica *r, Workspace &ws, const int64_t *ids, co
                              out16 ? nullptr : (last ? out : ws.x_f32),
                              out16 ? static_cast<void *>(out) : (last ? nullptr : ws.x_bf16), M, d.hidden, stream));
     SPU_MARK(SPU_STAGE_LN2);
+  }
+  return SPU_OK;
+}
+
+// Packed forward (bf16): the encoder runs on the batch's TRUE tokens only.  `lens` (host) gives each sequence's
+// length; ids is still the padded [batch, seq] array the host gather produced.  Rows of all sequences sit back to
+// back in the workspace (T = sum of lengths), so the GEMMs and LayerNorms do T rows of work instead of
+// batch * seq, attention reads per-sequence extents from cu_seqlens, and the last LayerNorm writes the padded
+// [batch, seq, hidden] output the StarPU handle expects (zeros behind each length).  Every live row equals the
+// padded forward's bit for bit: a row's GEMM / LayerNorm result does not depend on its neighbours, and keys past a
+// sequence's end get probability exactly 0 either way.
+spu_status enqueue_forward_packed(spu_replica *r, Workspace &ws, const int64_t *ids, const int32_t *lens, int batch,
+                                  int seq, float *out, cudaStream_t stream) {
+  const spu_bert_desc &d = r->desc;
+  int T = 0;
+  SPU_TRY(write_cu_seqlens_launch(lens, batch, ws.cu_seqlens, &T, stream));
+  SPU_REQUIRE(T > 0 && T <= r->cap_rows, SPU_ERR_CAPACITY, "packed forward: token count out of range");
+  SPU_TRY(bert_embed_packed_launch(ids, ws.cu_seqlens, batch, seq, T, r->word, r->pos, r->type0, r->emb_g, r->emb_b,
+                                   d.ln_eps, d.vocab, ws.x_f32, ws.x_bf16, d.hidden, stream));
+  int max_len = 0;
+  for (int b = 0; b < batch; ++b) max_len = lens[b] > max_len ? lens[b] : max_len;
+  for (int l = 0; l < d.layers; ++l) {
+    const LayerWeights &w = r->layers[l];
+    const LayerPlans &p = ws.plans[l];
+    const bool last = l == d.layers - 1;
+    GemmEpilogueArgs e{};
+    e.acc_scale = 1.f;
+    e.bias = w.b_qkv;
+    e.out = ws.qkv;
+    SPU_TRY(gemm_launch(p.qkv, T, e, stream));
+    SPU_TRY(attention_tc_launch(ws.qkv, nullptr, ws.ctx, batch, max_len, d.heads, stream, false, 1.f, ws.cu_seqlens, T));
+    e.bias = w.b_o;
+    e.resid = ws.x_f32;
+    e.out = ws.x_f32;
+    SPU_TRY(gemm_launch(p.attn_out, T, e, stream));
+    SPU_TRY(layernorm_launch(ws.x_f32, w.ln1_g, w.ln1_b, d.ln_eps, ws.x_f32, ws.x_bf16, T, d.hidden, stream));
+    e.bias = w.b_1;
+    e.resid = nullptr;
+    e.out = ws.h;
+    SPU_TRY(gemm_launch(p.ffn1, T, e, stream));
+    e.bias = w.b_2;
+    e.resid = ws.x_f32;
+    e.out = ws.x_f32;
+    SPU_TRY(gemm_launch(p.ffn2, T, e, stream));
+    if (!last) {
+      SPU_TRY(layernorm_launch(ws.x_f32, w.ln2_g, w.ln2_b, d.ln_eps, ws.x_f32, ws.x_bf16, T, d.hidden, stream));
+    } else {
+      const bool out16 = (r->flags & SPU_OUTPUT_BF16) != 0;
+      SPU_TRY(layernorm_unpad_launch(ws.x_f32, ws.cu_seqlens, batch, seq, w.ln2_g, w.ln2_b, d.ln_eps,
+                                     out16 ? nullptr : out, out16 ? static_cast<void *>(out) : nullptr, d.hidden, stream));
+    }
   }
   return SPU_OK;
 }
@@ -403,8 +455,68 @@ void destroy_graph(CapturedGraph &g) {
 
 void drop_graphs(Workspace &ws) {
   for (CapturedGraph &g : ws.graphs) destroy_graph(g);
+  for (CapturedGraph &g : ws.req_graphs) destroy_graph(g);
   ws.graphs.clear();
   ws.seen.clear();
+  ws.req_graphs.clear();
+  ws.req_seen.clear();
+}
+
+// Replace 8-byte parameters of one kernel node in the instantiated graph (and in its template, so the next
+// read-back sees what the exec holds).  Launches already enqueued keep their parameters.
+spu_status patch_node(CapturedGraph &g, cudaGraphNode_t node, int n_args, std::initializer_list<std::pair<int, const void *>> changes) {
+  cudaKernelNodeParams p{};
+  SPU_CUDA_TRY(cudaGraphKernelNodeGetParams(node, &p));
+  void *args[24];
+  const void *vals[24];
+  SPU_REQUIRE(n_args <= 24, SPU_ERR_INVALID, "graph patch: too many kernel parameters");
+  for (int i = 0; i < n_args; ++i) args[i] = p.kernelParams[i];
+  for (const auto &c : changes) {
+    vals[c.first] = c.second;
+    args[c.first] = &vals[c.first];
+  }
+  p.kernelParams = args;
+  SPU_CUDA_TRY(cudaGraphExecKernelNodeSetParams(g.exec, node, &p));
+  SPU_CUDA_TRY(cudaGraphKernelNodeSetParams(node, &p));
+  return SPU_OK;
+}
+
+// Find the single root and the single leaf of a captured chain; both must be kernel nodes.
+bool chain_ends(cudaGraph_t graph, cudaGraphNode_t *root, cudaGraphNode_t *leaf, cudaKernelNodeParams *p0,
+                cudaKernelNodeParams *p1) {
+  size_t n_nodes = 0, n_roots = 0;
+  if (cudaGraphGetNodes(graph, nullptr, &n_nodes) != cudaSuccess || cudaGraphGetRootNodes(graph, nullptr, &n_roots) != cudaSuccess ||
+      n_roots != 1 || n_nodes < 2) {
+    cudaGetLastError();
+    return false;
+  }
+  std::vector<cudaGraphNode_t> nodes(n_nodes);
+  n_roots = 1;
+  if (cudaGraphGetNodes(graph, nodes.data(), &n_nodes) != cudaSuccess || cudaGraphGetRootNodes(graph, root, &n_roots) != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  int n_leaves = 0;
+  for (cudaGraphNode_t n : nodes) {
+    size_t deps = 0;
+    if (cudaGraphNodeGetDependentNodes(n, nullptr, &deps) != cudaSuccess) {
+      cudaGetLastError();
+      return false;
+    }
+    if (deps == 0) {
+      *leaf = n;
+      ++n_leaves;
+    }
+  }
+  if (n_leaves != 1 || *leaf == *root) return false;
+  cudaGraphNodeType t0, t1;
+  if (cudaGraphNodeGetType(*root, &t0) != cudaSuccess || cudaGraphNodeGetType(*leaf, &t1) != cudaSuccess ||
+      t0 != cudaGraphNodeTypeKernel || t1 != cudaGraphNodeTypeKernel ||
+      cudaGraphKernelNodeGetParams(*root, p0) != cudaSuccess || cudaGraphKernelNodeGetParams(*leaf, p1) != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  return p0->kernelParams != nullptr && p1->kernelParams != nullptr;
 }
 
 // Capture one forward on `s` into an instantiated graph and find the two nodes that hold the I/O pointers.
@@ -431,45 +543,10 @@ spu_status capture_forward(spu_replica *r, Workspace &ws, const int64_t *ids, co
   // out_bf16 = parameter 5 under SPU_OUTPUT_BF16): anything else (LayerNorm-fused epilogues keep `out` inside a
   // tensor map) leaves the graph bound to its pointers
   cg->patchable = false;
-  size_t n_nodes = 0, n_roots = 0;
-  if (cudaGraphGetNodes(graph, nullptr, &n_nodes) != cudaSuccess || cudaGraphGetRootNodes(graph, nullptr, &n_roots) != cudaSuccess ||
-      n_roots != 1 || n_nodes < 2) {
-    cudaGetLastError();
-    return SPU_OK;
-  }
-  std::vector<cudaGraphNode_t> nodes(n_nodes);
-  cudaGraphNode_t root = nullptr;
-  n_roots = 1;
-  if (cudaGraphGetNodes(graph, nodes.data(), &n_nodes) != cudaSuccess ||
-      cudaGraphGetRootNodes(graph, &root, &n_roots) != cudaSuccess) {
-    cudaGetLastError();
-    return SPU_OK;
-  }
-  cudaGraphNode_t leaf = nullptr;
-  int n_leaves = 0;
-  for (cudaGraphNode_t n : nodes) {
-    size_t deps = 0;
-    if (cudaGraphNodeGetDependentNodes(n, nullptr, &deps) != cudaSuccess) {
-      cudaGetLastError();
-      return SPU_OK;
-    }
-    if (deps == 0) {
-      leaf = n;
-      ++n_leaves;
-    }
-  }
-  if (n_leaves != 1 || leaf == root) return SPU_OK;
-  cudaGraphNodeType t0, t1;
+  cudaGraphNode_t root = nullptr, leaf = nullptr;
   cudaKernelNodeParams p0{}, p1{};
-  if (cudaGraphNodeGetType(root, &t0) != cudaSuccess || cudaGraphNodeGetType(leaf, &t1) != cudaSuccess ||
-      t0 != cudaGraphNodeTypeKernel || t1 != cudaGraphNodeTypeKernel ||
-      cudaGraphKernelNodeGetParams(root, &p0) != cudaSuccess || cudaGraphKernelNodeGetParams(leaf, &p1) != cudaSuccess) {
-    cudaGetLastError();
-    return SPU_OK;
-  }
-  if (p0.func != bert_embed_kernel_entry() || p1.func != layernorm_kernel_entry() || p0.kernelParams == nullptr ||
-      p1.kernelParams == nullptr)
-    return SPU_OK;
+  if (!chain_ends(graph, &root, &leaf, &p0, &p1)) return SPU_OK;
+  if (p0.func != bert_embed_kernel_entry() || p1.func != layernorm_kernel_entry()) return SPU_OK;
   const int out_arg = (r->flags & SPU_OUTPUT_BF16) ? 5 : 4;
   // the captured parameters must be the pointers we are about to treat as patchable
   if (*static_cast<const void *const *>(p0.kernelParams[0]) != ids || *static_cast<const void *const *>(p0.kernelParams[1]) != mask ||
@@ -485,32 +562,12 @@ spu_status capture_forward(spu_replica *r, Workspace &ws, const int64_t *ids, co
 // Point the instantiated graph at other I/O buffers (host-side only; launches already enqueued keep theirs).
 spu_status retarget_graph(CapturedGraph &g, const int64_t *ids, const int64_t *mask, float *out) {
   if (g.key.ids != ids || g.key.mask != mask) {
-    cudaKernelNodeParams p{};
-    SPU_CUDA_TRY(cudaGraphKernelNodeGetParams(g.first, &p));
-    constexpr int kEmbedArgs = 17;
-    void *args[kEmbedArgs];
-    for (int i = 0; i < kEmbedArgs; ++i) args[i] = p.kernelParams[i];
-    const void *ids_v = ids, *mask_v = mask;
-    args[0] = &ids_v;
-    args[1] = &mask_v;
-    p.kernelParams = args;
-    SPU_CUDA_TRY(cudaGraphExecKernelNodeSetParams(g.exec, g.first, &p));
-    // keep the template graph in step so that the next GetParams reads what the exec holds
-    SPU_CUDA_TRY(cudaGraphKernelNodeSetParams(g.first, &p));
+    SPU_TRY(patch_node(g, g.first, 17, {{0, ids}, {1, mask}}));  // bert_embed_ln_kernel(ids, mask, ...)
     g.key.ids = ids;
     g.key.mask = mask;
   }
   if (g.key.out != out) {
-    cudaKernelNodeParams p{};
-    SPU_CUDA_TRY(cudaGraphKernelNodeGetParams(g.last, &p));
-    constexpr int kLnArgs = 11;
-    void *args[kLnArgs];
-    for (int i = 0; i < kLnArgs; ++i) args[i] = p.kernelParams[i];
-    void *out_v = out;
-    args[g.out_arg] = &out_v;
-    p.kernelParams = args;
-    SPU_CUDA_TRY(cudaGraphExecKernelNodeSetParams(g.exec, g.last, &p));
-    SPU_CUDA_TRY(cudaGraphKernelNodeSetParams(g.last, &p));
+    SPU_TRY(patch_node(g, g.last, 11, {{g.out_arg, out}}));  // layernorm_kernel(..., out_f32 [4], out_bf16 [5], ...)
     g.key.out = out;
   }
   return SPU_OK;
@@ -664,6 +721,25 @@ extern "C" spu_status spu_bert_forward_async(spu_replica *r, int32_t ws_idx, con
   return enqueue_forward(r, ws, ids, mask, batch, seq, out, as_stream(stream));
 }
 
+extern "C" int32_t spu_bert_packed_supported(const spu_replica *r, int32_t batch) {
+  return (r != nullptr && r->kind == 0 && (r->flags & SPU_PREC_FP8_E4M3) == 0 && !r->ln_fused && batch >= 1 &&
+          batch <= kMaxPackedBatch)
+             ? 1
+             : 0;
+}
+
+extern "C" spu_status spu_bert_forward_packed_async(spu_replica *r, int32_t ws_idx, const int64_t *ids,
+                                                    const int32_t *lens, int32_t batch, int32_t seq, float *out,
+                                                    void *stream) {
+  SPU_TRY(check_forward_args(r, ws_idx, ids, lens, batch, seq, out));
+  SPU_REQUIRE((r->flags & SPU_PREC_FP8_E4M3) == 0 && !r->ln_fused, SPU_ERR_UNSUPPORTED,
+              "forward_packed: bf16 replicas with the separate LayerNorm kernel only");
+  SPU_REQUIRE(batch <= kMaxPackedBatch, SPU_ERR_CAPACITY, "forward_packed: at most 256 sequences per batch");
+  for (int b = 0; b < batch; ++b)
+    SPU_REQUIRE(lens[b] >= 1 && lens[b] <= seq, SPU_ERR_INVALID, "forward_packed: every length must be in [1, seq]");
+  return enqueue_forward_packed(r, r->ws[ws_idx], ids, lens, batch, seq, out, as_stream(stream));
+}
+
 extern "C" spu_status spu_bert_forward_requests_async(spu_replica *r, int32_t ws_idx,
                                                       const int64_t *const *src_ids,
                                                       const int64_t *const *src_mask, const int32_t *len,
@@ -680,9 +756,77 @@ extern "C" spu_status spu_bert_forward_requests_async(spu_replica *r, int32_t ws
   Workspace &ws = r->ws[ws_idx];
   SPU_TRY(check_forward_args(r, ws_idx, ws.req_ids, ws.req_mask, n_req, seq, ws.req_out));
   cudaStream_t s = as_stream(stream);
-  SPU_TRY(spu_gather_pad_mask_async(src_ids, src_mask, len, n_req, seq, 0, ws.req_ids, ws.req_mask, stream));
-  SPU_TRY(enqueue_forward(r, ws, ws.req_ids, ws.req_mask, n_req, seq, ws.req_out, s));
-  return scatter_requests_launch(ws.req_out, len, n_req, seq, r->desc.hidden, full_rows != 0, dsts, s);
+  auto enqueue = [&]() -> spu_status {
+    SPU_TRY(spu_gather_pad_mask_async(src_ids, src_mask, len, n_req, seq, 0, ws.req_ids, ws.req_mask, stream));
+    SPU_TRY(enqueue_forward(r, ws, ws.req_ids, ws.req_mask, n_req, seq, ws.req_out, s));
+    return scatter_requests_launch(ws.req_out, len, n_req, seq, r->desc.hidden, full_rows != 0, dsts, s);
+  };
+  // one graph per (n_req, seq, full_rows): the tables' addresses (they live in whatever slot the task uses) are
+  // parameters of the first kernel (gather) and the last one (scatter), patched per launch
+  GraphKey want{src_ids, len, dsts, n_req, seq};
+  want.aux = src_mask;
+  want.full_rows = full_rows != 0 ? 1 : 0;
+  auto same = [&](const GraphKey &k) { return k.same_shape(n_req, seq) && k.full_rows == want.full_rows; };
+  for (CapturedGraph &g : ws.req_graphs) {
+    if (!same(g.key) || !g.patchable) continue;
+    if (g.key.ids != want.ids || g.key.aux != want.aux || g.key.mask != want.mask) {
+      // gather_pad_mask_kernel(src_ids, src_mask, len, ...)
+      SPU_TRY(patch_node(g, g.first, 7, {{0, want.ids}, {1, want.aux}, {2, want.mask}}));
+    }
+    if (g.key.out != want.out || g.key.mask != want.mask) {
+      // scatter_requests_kernel(src, len, seq, hidden, full_rows, dsts)
+      SPU_TRY(patch_node(g, g.last, 6, {{1, want.mask}, {5, want.out}}));
+    }
+    g.key = want;
+    g.tick = ++ws.graph_tick;
+    SPU_CUDA_TRY(cudaGraphLaunch(g.exec, s));
+    return SPU_OK;
+  }
+  if ((r->flags & SPU_FORWARD_AUTO_GRAPH) != 0 && s != nullptr) {
+    bool seen = false;
+    for (const GraphKey &k : ws.req_seen) seen = seen || same(k);
+    if (seen) {
+      SPU_CUDA_TRY(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
+      spu_status st = enqueue();
+      cudaGraph_t graph = nullptr;
+      cudaError_t e = cudaStreamEndCapture(s, &graph);
+      if (st != SPU_OK) {
+        if (graph) cudaGraphDestroy(graph);
+        return st;
+      }
+      SPU_CUDA_TRY(e);
+      CapturedGraph cg;
+      cg.key = want;
+      cg.graph = graph;
+      e = cudaGraphInstantiate(&cg.exec, graph, 0);
+      if (e != cudaSuccess) {
+        cudaGraphDestroy(graph);
+        SPU_CUDA_TRY(e);
+      }
+      cudaKernelNodeParams p0{}, p1{};
+      cg.patchable = chain_ends(graph, &cg.first, &cg.last, &p0, &p1) &&
+                     p0.func == gather_pad_mask_kernel_entry() && p1.func == scatter_requests_kernel_entry();
+      if (!cg.patchable) {  // cannot be retargeted: useless for a slot-cycling server
+        SPU_CUDA_TRY(cudaGraphLaunch(cg.exec, s));
+        cudaStreamSynchronize(s);
+        destroy_graph(cg);
+        return SPU_OK;
+      }
+      if (ws.req_graphs.size() >= kMaxGraphs) {
+        size_t lru = 0;
+        for (size_t i = 1; i < ws.req_graphs.size(); ++i)
+          if (ws.req_graphs[i].tick < ws.req_graphs[lru].tick) lru = i;
+        destroy_graph(ws.req_graphs[lru]);
+        ws.req_graphs.erase(ws.req_graphs.begin() + static_cast<long>(lru));
+      }
+      cg.tick = ++ws.graph_tick;
+      ws.req_graphs.push_back(cg);
+      SPU_CUDA_TRY(cudaGraphLaunch(cg.exec, s));
+      return SPU_OK;
+    }
+    if (ws.req_seen.size() < 4 * kMaxGraphs) ws.req_seen.push_back(want);
+  }
+  return enqueue();
 }
 
 extern "C" spu_status spu_bert_forward_capture(spu_replica *r, int32_t ws_idx, const int64_t *ids,

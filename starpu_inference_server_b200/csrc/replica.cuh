@@ -18,7 +18,8 @@ spu_status attention_launch(const void *qkv, const float *mask_bias, void *ctx, 
                             float q_inv_scale = 1.f);
 // the two implementations behind attention_launch (attention_sm100.cu: tcgen05; attention.cu: mma.sync)
 spu_status attention_tc_launch(const void *qkv, const float *mask_bias, void *ctx, int batch, int seq,
-                               int heads, cudaStream_t stream, bool out_e4m3, float q_inv_scale);
+                               int heads, cudaStream_t stream, bool out_e4m3, float q_inv_scale,
+                               const int32_t *cu_seqlens = nullptr, int total_tokens = 0);
 spu_status attention_mma_launch(const void *qkv, const float *mask_bias, void *ctx, int batch, int seq,
                                 int heads, cudaStream_t stream, bool out_e4m3, float q_inv_scale);
 spu_status bert_embed_launch(const int64_t *ids, const int64_t *mask, const float *word,
@@ -31,7 +32,22 @@ spu_status layernorm_launch(const float *x, const float *gamma, const float *bet
                             float *out_f32, void *out_bf16, int rows, int hidden,
                             cudaStream_t stream, long long in_row_stride = 0, void *out_q = nullptr,
                             float q_inv_scale = 1.f);
+// ---- packed (unpadded) forward: sequences back to back, cu_seqlens[b] = first row of sequence b ----
+constexpr int kMaxPackedBatch = 256;  // cu_seqlens rides in a kernel parameter
+// host lengths -> device cu_seqlens [batch + 1] (as a kernel parameter: no staging buffer to race on); *total = sum
+spu_status write_cu_seqlens_launch(const int32_t *lens_host, int batch, int32_t *cu_dev, int *total,
+                                   cudaStream_t stream);
+spu_status bert_embed_packed_launch(const int64_t *ids, const int32_t *cu, int batch, int seq, int total,
+                                    const float *word, const float *pos, const float *type0, const float *gamma,
+                                    const float *beta, float eps, int vocab, float *x_f32, void *x_bf16, int hidden,
+                                    cudaStream_t stream);
+// final LayerNorm reading packed rows and writing the padded [batch, seq, hidden] output (zeros behind each length)
+spu_status layernorm_unpad_launch(const float *x, const int32_t *cu, int batch, int seq, const float *gamma,
+                                  const float *beta, float eps, float *out_f32, void *out_bf16, int hidden,
+                                  cudaStream_t stream);
 // kernel entry points of the first / last launch of a forward (graph parameter patching, replica.cu)
+const void *gather_pad_mask_kernel_entry();
+const void *scatter_requests_kernel_entry();
 const void *bert_embed_kernel_entry();
 const void *layernorm_kernel_entry();
 // request i <- rows [i*seq, i*seq + (full_rows ? seq : len[i])) of src [n_req*seq, hidden]
@@ -91,6 +107,8 @@ struct LayerPlans {
 struct GraphKey {
   const void *ids = nullptr, *mask = nullptr, *out = nullptr;  // the pointers the graph currently holds
   int batch = 0, seq = 0;
+  const void *aux = nullptr;  // requests path: the source-mask table
+  int full_rows = 0;          // requests path
   bool same_shape(int b, int s) const { return batch == b && seq == s; }
   bool operator==(const GraphKey &o) const {
     return ids == o.ids && mask == o.mask && out == o.out && batch == o.batch && seq == o.seq;
@@ -117,10 +135,15 @@ struct Workspace {
   // spu_bert_forward_requests_async (stage 1 writes, stage 4 reads)
   int64_t *req_ids = nullptr, *req_mask = nullptr;
   float *req_out = nullptr;
+  int32_t *cu_seqlens = nullptr;  // packed forward: [kMaxPackedBatch + 1]
   std::vector<LayerPlans> plans;
   std::vector<LayerPlans> plans8;
   std::vector<CapturedGraph> graphs;
   std::vector<GraphKey> seen;  // SPU_FORWARD_AUTO_GRAPH: shapes run eagerly once so far
+  // spu_bert_forward_requests_async (gather -> forward -> scatter): one graph per (n_req, seq, full_rows); the
+  // key's ids / mask / out fields hold the source-id table, the length array and the destination table
+  std::vector<CapturedGraph> req_graphs;
+  std::vector<GraphKey> req_seen;
   unsigned long long graph_tick = 0;
 };
 

@@ -106,6 +106,100 @@ bert_embed_ln_kernel(const int64_t *__restrict__ ids, const int64_t *__restrict_
   if (lane == 0) mask_bias[row] = mask[row] != 0 ? 0.f : -1e30f;
 }
 
+// ---- packed (unpadded) sequences: rows of all sequences back to back, cu[b] = first row of sequence b ----
+struct CuSeqlensArg {
+  int32_t v[kMaxPackedBatch + 1];
+};
+
+// cu_seqlens travels as a kernel parameter (1 KB): no staging buffer whose reuse a pipelined worker could race
+__global__ void write_cu_seqlens_kernel(const CuSeqlensArg cu, int n, int32_t *out) {
+  pdl_wait_prior_grid();
+  pdl_launch_dependents();
+  for (int i = threadIdx.x; i < n; i += blockDim.x) out[i] = cu.v[i];
+}
+
+// sequence that owns packed row `row`: last b with cu[b] <= row
+__device__ __forceinline__ int seq_of_row(const int32_t *__restrict__ cu, int batch, int row) {
+  int lo = 0, hi = batch - 1;
+  while (lo < hi) {
+    const int mid = (lo + hi + 1) >> 1;
+    if (__ldg(cu + mid) <= row) lo = mid;
+    else hi = mid - 1;
+  }
+  return lo;
+}
+
+// Packed embedding: row r of the output is token t = r - cu[b] of sequence b; its id sits at ids[b*seq + t] of the
+// padded [batch, seq] array the host gather produced.  No mask bias: packed attention needs none.
+__global__ void __launch_bounds__(kRowThreads)
+bert_embed_packed_kernel(const int64_t *__restrict__ ids, const int32_t *__restrict__ cu, int batch, int seq,
+                         const float *__restrict__ word, const float *__restrict__ pos,
+                         const float *__restrict__ type0, const float *__restrict__ gamma,
+                         const float *__restrict__ beta, float eps, int vocab, float *x_f32, __nv_bfloat16 *x_bf16,
+                         int rows, int hidden) {
+  pdl_wait_prior_grid();
+  pdl_launch_dependents();
+  const int row = blockIdx.x * (kRowThreads / 32) + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const int lane = threadIdx.x & 31;
+  const int nchunk = hidden >> 2;
+  const int nchunk_lane = (nchunk - lane + 31) >> 5;
+  const int b = seq_of_row(cu, batch, row);
+  const int t = row - __ldg(cu + b);
+  int64_t id = ids[static_cast<size_t>(b) * seq + t];
+  id = id < 0 ? 0 : (id >= vocab ? vocab - 1 : id);
+  const float4 *w4 = reinterpret_cast<const float4 *>(word + static_cast<size_t>(id) * hidden);
+  const float4 *p4 = reinterpret_cast<const float4 *>(pos + static_cast<size_t>(t) * hidden);
+  const float4 *t4 = reinterpret_cast<const float4 *>(type0);
+  float4 v[kMaxChunksPerLane];
+#pragma unroll
+  for (int i = 0; i < kMaxChunksPerLane; ++i) {
+    if (i < nchunk_lane) {
+      const int c = lane + i * 32;
+      const float4 a = __ldg(w4 + c), q = __ldg(p4 + c), d = __ldg(t4 + c);
+      v[i] = make_float4(a.x + q.x + d.x, a.y + q.y + d.y, a.z + q.z + d.z, a.w + q.w + d.w);
+    }
+  }
+  const RowStats st = row_stats(v, nchunk_lane, hidden, eps);
+  row_normalise_store(v, nchunk_lane, st, gamma, beta, x_f32, x_bf16, static_cast<size_t>(row) * hidden);
+}
+
+// Final LayerNorm of the packed forward: reads packed row r, writes the PADDED output row b*seq + t; one warp per
+// padded row, rows behind a sequence's length are zero-filled (the reference leaves whatever the model computes
+// for [PAD] tokens there; nothing reads them).
+__global__ void __launch_bounds__(kRowThreads)
+layernorm_unpad_kernel(const float *__restrict__ x, const int32_t *__restrict__ cu, int batch, int seq,
+                       const float *__restrict__ gamma, const float *__restrict__ beta, float eps, float *out_f32,
+                       __nv_bfloat16 *out_bf16, int hidden) {
+  pdl_wait_prior_grid();
+  pdl_launch_dependents();
+  const int prow = blockIdx.x * (kRowThreads / 32) + (threadIdx.x >> 5);  // padded row
+  if (prow >= batch * seq) return;
+  const int lane = threadIdx.x & 31;
+  const int nchunk = hidden >> 2;
+  const int nchunk_lane = (nchunk - lane + 31) >> 5;
+  const int b = prow / seq, t = prow - b * seq;
+  const int start = __ldg(cu + b), len = __ldg(cu + b + 1) - start;
+  const size_t off = static_cast<size_t>(prow) * hidden;
+  if (t >= len) {
+#pragma unroll
+    for (int i = 0; i < kMaxChunksPerLane; ++i) {
+      if (i >= nchunk_lane) break;
+      const int c = lane + i * 32;
+      if (out_f32 != nullptr) reinterpret_cast<float4 *>(out_f32 + off)[c] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (out_bf16 != nullptr) reinterpret_cast<uint2 *>(out_bf16 + off)[c] = make_uint2(0u, 0u);
+    }
+    return;
+  }
+  const size_t in_off = static_cast<size_t>(start + t) * hidden;
+  float4 v[kMaxChunksPerLane];
+#pragma unroll
+  for (int i = 0; i < kMaxChunksPerLane; ++i)
+    if (i < nchunk_lane) v[i] = reinterpret_cast<const float4 *>(x + in_off)[lane + i * 32];
+  const RowStats st = row_stats(v, nchunk_lane, hidden, eps);
+  row_normalise_store(v, nchunk_lane, st, gamma, beta, out_f32, out_bf16, off);
+}
+
 __global__ void __launch_bounds__(kRowThreads)
 layernorm_kernel(const float *__restrict__ x, const float *__restrict__ gamma,
                  const float *__restrict__ beta, float eps, float *out_f32,
@@ -279,6 +373,47 @@ constexpr int kSegBlocksPerSegment = 32;
 
 }  // namespace
 
+spu_status write_cu_seqlens_launch(const int32_t *lens_host, int batch, int32_t *cu_dev, int *total,
+                                   cudaStream_t stream) {
+  SPU_REQUIRE(lens_host && cu_dev && total, SPU_ERR_INVALID, "cu_seqlens: null argument");
+  SPU_REQUIRE(batch > 0 && batch <= kMaxPackedBatch, SPU_ERR_CAPACITY, "cu_seqlens: batch exceeds the packed-path cap");
+  CuSeqlensArg cu;
+  cu.v[0] = 0;
+  for (int b = 0; b < batch; ++b) {
+    SPU_REQUIRE(lens_host[b] >= 0, SPU_ERR_INVALID, "cu_seqlens: negative length");
+    cu.v[b + 1] = cu.v[b] + lens_host[b];
+  }
+  *total = cu.v[batch];
+  SPU_CUDA_TRY(launch_pdl(write_cu_seqlens_kernel, dim3(1), dim3(256), 0, stream, cu, batch + 1, cu_dev));
+  return SPU_OK;
+}
+
+spu_status bert_embed_packed_launch(const int64_t *ids, const int32_t *cu, int batch, int seq, int total,
+                                    const float *word, const float *pos, const float *type0, const float *gamma,
+                                    const float *beta, float eps, int vocab, float *x_f32, void *x_bf16, int hidden,
+                                    cudaStream_t stream) {
+  SPU_REQUIRE(ids && cu && word && pos && type0 && gamma && beta, SPU_ERR_INVALID, "embed: null argument");
+  SPU_REQUIRE(hidden % 4 == 0 && hidden <= 128 * kMaxChunksPerLane && total > 0, SPU_ERR_UNSUPPORTED, "embed: bad shape");
+  const int grid = (total + kRowThreads / 32 - 1) / (kRowThreads / 32);
+  SPU_CUDA_TRY(launch_pdl(bert_embed_packed_kernel, dim3(grid), dim3(kRowThreads), 0, stream, ids, cu, batch, seq, word,
+                          pos, type0, gamma, beta, eps, vocab, x_f32, static_cast<__nv_bfloat16 *>(x_bf16), total, hidden));
+  return SPU_OK;
+}
+
+spu_status layernorm_unpad_launch(const float *x, const int32_t *cu, int batch, int seq, const float *gamma,
+                                  const float *beta, float eps, float *out_f32, void *out_bf16, int hidden,
+                                  cudaStream_t stream) {
+  SPU_REQUIRE(x && cu && gamma && beta && (out_f32 || out_bf16), SPU_ERR_INVALID, "layernorm: null argument");
+  SPU_REQUIRE(hidden % 4 == 0 && hidden <= 128 * kMaxChunksPerLane, SPU_ERR_UNSUPPORTED, "layernorm: bad hidden size");
+  const int rows = batch * seq;
+  const int grid = (rows + kRowThreads / 32 - 1) / (kRowThreads / 32);
+  SPU_CUDA_TRY(launch_pdl(layernorm_unpad_kernel, dim3(grid), dim3(kRowThreads), 0, stream, x, cu, batch, seq, gamma,
+                          beta, eps, out_f32, static_cast<__nv_bfloat16 *>(out_bf16), hidden));
+  return SPU_OK;
+}
+
+const void *gather_pad_mask_kernel_entry() { return reinterpret_cast<const void *>(&gather_pad_mask_kernel); }
+const void *scatter_requests_kernel_entry() { return reinterpret_cast<const void *>(&scatter_requests_kernel); }
 const void *bert_embed_kernel_entry() { return reinterpret_cast<const void *>(&bert_embed_ln_kernel); }
 const void *layernorm_kernel_entry() { return reinterpret_cast<const void *>(&layernorm_kernel); }
 
@@ -342,7 +477,16 @@ spu_status scatter_requests_launch(const float *src, const int32_t *len, int n_r
   SPU_REQUIRE(src && len && dsts, SPU_ERR_INVALID, "scatter_requests: null argument");
   SPU_REQUIRE(n_req > 0 && n_req <= 65535 && seq > 0 && hidden > 0 && hidden % 4 == 0, SPU_ERR_INVALID,
               "scatter_requests: bad shape");
-  dim3 grid(kSegBlocksPerSegment, n_req);
+  // ~64 CTAs in all, not 32 per request: the destinations are usually pinned HOST buffers, the stores drain at the
+  // PCIe rate (a few hundred KB in flight saturate it) and every resident CTA of this kernel holds thread slots
+  // the other worker's GEMM CTAs are waiting for; 64 CTAs x 16 KB in flight still move 12.6 MB into HBM in ~6 us
+  static const int total = [] {
+    const char *e = std::getenv("SPU_SCATTER_CTAS");
+    const int t = e ? std::atoi(e) : 0;
+    return t > 0 ? t : 64;
+  }();
+  const int per_req = total / n_req > 0 ? (total / n_req > kSegBlocksPerSegment ? kSegBlocksPerSegment : total / n_req) : 1;
+  dim3 grid(per_req, n_req);
   scatter_requests_kernel<<<grid, 256, 0, stream>>>(src, len, seq, hidden, full_rows ? 1 : 0, dsts);
   SPU_CUDA_TRY(cudaGetLastError());
   return SPU_OK;

@@ -446,3 +446,42 @@ def test_warmup_autotune_picks_a_tile_within_3_percent_of_the_sweep(spu, base):
         print(f"autotune N={N} K={K} epi={epi}: chose {(t['cta_group'], t['block_n'])} {t['us']:.2f} us "
               f"(sweep {mine:.2f} us), sweep best {best_cfg} {sweep[best_cfg]:.2f} us")
         assert mine <= 1.03 * sweep[best_cfg], (N, K, epi, t, sweep)
+
+
+@pytest.mark.parametrize("B,S,min_len", [(8, 128, 5), (16, 512, 16), (5, 200, 1), (3, 64, 64)])
+def test_packed_forward_equals_the_padded_one_on_live_rows(base, B, S, min_len):
+    """spu_bert_forward_packed_async: the encoder runs on the true tokens of a right-padded batch only.  Every live row
+    is BIT-IDENTICAL to spu_bert_forward_async with the equivalent mask (a row's GEMM / LayerNorm result does not
+    depend on its neighbours; keys past a sequence's end get probability 0 either way), rows behind a length are
+    zero, and each sequence matches the fp32 oracle run on it alone."""
+    bo, w, r = base
+    ids, mask = bo.make_inputs(bo.BERT_BASE, B, S, seed=900 + B, min_len=min_len)
+    lens = mask.sum(1).astype(np.int32)
+    lens[0] = S  # one full-length sequence, one of the minimum length
+    lens[-1] = min_len
+    for b in range(B):
+        mask[b] = 0
+        mask[b, :lens[b]] = 1
+    ids_d, mask_d = torch.from_numpy(ids).cuda(), torch.from_numpy(mask).cuda()
+    padded = torch.empty(B, S, 768, device="cuda")
+    packed = torch.full((B, S, 768), float("nan"), device="cuda")
+    r.forward_async(ids_d, mask_d, padded)
+    r.forward_packed_async(ids_d, lens, packed, ws=1)
+    torch.cuda.synchronize()
+    live = torch.from_numpy(mask.astype(bool)).cuda()
+    assert torch.equal(packed[live], padded[live])
+    assert bool((packed[~live] == 0).all())
+    for b in (0, B - 1):
+        n = int(lens[b])
+        alone = bo.bert_forward(w, bo.BERT_BASE, ids[b:b + 1, :n], np.ones((1, n), np.int64))
+        got = packed[b, :n].cpu().numpy()
+        assert np.abs(got - alone[0]).max() / np.abs(alone).max() < 2e-2, b
+
+
+def test_packed_forward_rejects_bad_lengths(spu, base):
+    bo, w, r = base
+    ids = torch.zeros(2, 16, dtype=torch.int64, device="cuda")
+    out = torch.empty(2, 16, 768, device="cuda")
+    for lens in ([0, 4], [17, 4]):
+        with pytest.raises(spu.SpuError):
+            r.forward_packed_async(ids, lens, out)
