@@ -630,7 +630,8 @@ def run_b200(args, cfg, rank, local_rank, world):
                            "2 ms, cap %d); codelet = codelet_end - codelet_start of the task a request rode in (host time of the "
                            "asynchronous enqueue), task = task submitted -> output callback (device work + D2H), "
                            "request = enqueued -> response copied into the caller's buffer" % B, "loads": []}
-        srv.offered_load(rows1, n_req=64 * B, rate_per_s=0.5 * e2e_value, seed=7)  # warm: graphs of the usual shapes
+        for frac in (0.5, 0.8):  # warm: a second of each load, so every batch shape it forms has its graph
+            srv.offered_load(rows1, n_req=int(min(40000, max(1000, frac * e2e_value))), rate_per_s=frac * e2e_value, seed=7)
         for frac in (0.5, 0.8):
             rate = frac * e2e_value
             n_req = int(min(60000, max(2000, rate * 1.5)))

@@ -128,6 +128,10 @@ spu_status spu_bert_forward_async(spu_replica *r, int32_t ws_idx,
  * count changes from batch to batch, so there is no graph to replay). */
 spu_status spu_bert_forward_packed_async(spu_replica *r, int32_t ws_idx, const int64_t *ids, const int32_t *lens,
                                          int32_t batch, int32_t seq, float *out, void *stream);
+/* Rows of the replica's word-embedding table (0 for a non-BERT replica).  The embedding kernel clamps ids into
+ * [0, vocab) for memory safety where LibTorch's embedding would raise; a host layer that wants the reference's
+ * failure instead validates ids against this before submitting (core/task_runner.cpp does). */
+int32_t spu_bert_vocab_size(const spu_replica *r);
 /* 1 when spu_bert_forward_packed_async serves this replica for batches of `batch` sequences. */
 int32_t spu_bert_packed_supported(const spu_replica *r, int32_t batch);
 

@@ -2,8 +2,10 @@
 // + TaskRunner + BatchCollector; tickets instead of foreign-thread callbacks into Python.
 #include <chrono>
 #include <condition_variable>
+#include <cstdlib>
 #include <cstring>
 #include <deque>
+#include <functional>
 #include <map>
 #include <mutex>
 #include <random>
@@ -82,6 +84,54 @@ struct spu_server {
   int length_bucket = 0;  // variable_length: requests per ceil(L / length_bucket) bucket batch together
   int tile_rows = 0;      // > 0: GEMM row tile of the codelet's kernels; see tile_aware_close()
   int forming = 0;  // batches popped from the queue but not yet submitted (guarded by qmu)
+  // Response-copy helpers (the per-request copy into caller buffers, fill_output_tensor in the reference,
+  // must not serialise on the one completer thread of a worker): a finished task's on_complete calls are spread
+  // over these threads plus the calling one.
+  std::vector<std::thread> helpers;
+  std::mutex hmu;
+  std::condition_variable hcv;
+  std::deque<std::function<void()>> hq;
+  bool hstop = false;
+
+  void helper_loop() {
+    for (;;) {
+      std::function<void()> fn;
+      {
+        std::unique_lock<std::mutex> lk(hmu);
+        hcv.wait(lk, [&] { return hstop || !hq.empty(); });
+        if (hq.empty()) return;
+        fn = std::move(hq.front());
+        hq.pop_front();
+      }
+      fn();
+    }
+  }
+
+  void run_completions(std::vector<std::function<void()>> &fns) {
+    struct Sync {
+      std::mutex m;
+      std::condition_variable cv;
+      size_t left;
+    } sync;
+    const size_t n = fns.size(), parts = std::min(n, helpers.size() + 1);
+    sync.left = parts - 1;
+    auto run_part = [&fns, n, parts](size_t p) {
+      for (size_t i = p * n / parts; i < (p + 1) * n / parts; ++i) fns[i]();
+    };
+    {
+      std::lock_guard<std::mutex> lk(hmu);
+      for (size_t p = 1; p < parts; ++p)
+        hq.emplace_back([&sync, run_part, p] {
+          run_part(p);
+          std::lock_guard<std::mutex> l2(sync.m);
+          if (--sync.left == 0) sync.cv.notify_one();
+        });
+    }
+    hcv.notify_all();
+    run_part(0);
+    std::unique_lock<std::mutex> lk(sync.m);
+    sync.cv.wait(lk, [&] { return sync.left == 0; });
+  }
 
   std::shared_ptr<InferenceJob> make_job(const spu_request &rq, int64_t ticket, int index) {
     auto job = std::make_shared<InferenceJob>();
@@ -352,8 +402,17 @@ int32_t spu_server_create(const spu_server_cfg *cfg, spu_server **out) {
                                 nullptr, nullptr) != SPU_OK)
             throw std::runtime_error(std::string("warm-up autotune failed: ") + spu_last_error());
         }
+      if (cfg->model_kind == SPU_MODEL_BERT && s->registry.size() > 0)
+        s->model.id_vocab = spu_bert_vocab_size(s->registry.model(0)->replica);
       s->runner = std::make_unique<TaskRunner>(s->model, &s->registry);
       spu_server *raw = s.get();
+      {
+        const char *env = std::getenv("SPU_RESPONSE_THREADS");
+        const int n_helpers = env ? std::atoi(env) : 3;
+        for (int i = 0; i < n_helpers; ++i) s->helpers.emplace_back([raw] { raw->helper_loop(); });
+        if (n_helpers > 0)
+          s->runner->set_completion_executor([raw](std::vector<std::function<void()>> &fns) { raw->run_completions(fns); });
+      }
       s->collector = std::thread([raw] { raw->collector_loop(); });
     } catch (...) {
       s->runner.reset();
@@ -377,6 +436,13 @@ void spu_server_destroy(spu_server *s) {
   s->qcv.notify_all();
   if (s->collector.joinable()) s->collector.join();
   if (s->runner) s->runner->wait_for_all();
+  {
+    std::lock_guard<std::mutex> lk(s->hmu);
+    s->hstop = true;
+  }
+  s->hcv.notify_all();
+  for (auto &t : s->helpers)
+    if (t.joinable()) t.join();
   for (size_t i = 0; i < s->registry.size(); ++i)
     if (s->registry.model(i)->replica) forget_replica_workspaces(s->registry.model(i)->replica);
   s->runner.reset();  // unregisters the slot handles while the runtime is still up

@@ -352,6 +352,17 @@ void TaskRunner::submit_batch(const std::vector<std::shared_ptr<InferenceJob>> &
     else
       copy_job_inputs_to_slot(master, pending, in_handles, input_pool_->base_ptrs(ctx->input_slot),
                               input_pool_->host_buffer_infos(ctx->input_slot));
+    if (model_.id_vocab > 0 && !model_.device_visible_requests && model_.inputs[0].type == ScalarType::Int64)
+      for (const auto &j : jobs) {
+        if (!j) continue;
+        const auto *ids = reinterpret_cast<const int64_t *>(j->inputs[0].data);
+        const size_t n = j->inputs[0].numel();
+        for (size_t i = 0; i < n; ++i)
+          if (ids[i] < 0 || ids[i] >= model_.id_vocab)
+            throw InvalidInputTensorException("token id " + std::to_string(ids[i]) + " of request " +
+                                              std::to_string(j->request_id) + " is outside the embedding table [0, " +
+                                              std::to_string(model_.id_vocab) + ")");
+      }
   } catch (...) {
     for (size_t i = 0; i < leased; ++i) starpu_data_release(in_handles[i]);
     throw;
@@ -491,6 +502,8 @@ void TaskRunner::finalize(CallbackContext *ctx) {
   ctx->timing.callback_end_time = MonotonicClock::now();
   // propagate_completion_to_sub_jobs (result_dispatcher_component.cpp:678-739)
   int64_t offset = 0;
+  std::vector<std::function<void()>> completions;
+  completions.reserve(ctx->jobs.size());
   for (const auto &job : ctx->jobs) {
     if (!job) continue;
     JobResult res;
@@ -530,8 +543,12 @@ void TaskRunner::finalize(CallbackContext *ctx) {
       res.error = codelet_ok ? "Failed to acquire output data handle from StarPU." : "Inference failed";
       offset += job->batch_size();
     }
-    if (job->on_complete) job->on_complete(res);
+    if (job->on_complete)
+      completions.emplace_back([cb = &job->on_complete, res = std::move(res)] { (*cb)(res); });
   }
+  if (r->completion_executor_ && completions.size() > 1) r->completion_executor_(completions);
+  else
+    for (auto &c : completions) c();
   for (size_t i = 0; i < ctx->outputs_handles.size(); ++i)
     if (ctx->acquired[i]) starpu_data_release(ctx->outputs_handles[i]);
   r->input_pool_->release(ctx->input_slot);

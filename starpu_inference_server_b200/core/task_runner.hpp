@@ -118,6 +118,10 @@ struct ModelConfig {  // the slice of models/*.yml the path needs (config_loader
   // The host then gathers nothing: it writes a table of row addresses into the input slot and the codelet runs
   // gather/pad/mask -> encoder -> per-request scatter on the device (BERT models, fp32 responses).
   bool device_visible_requests = false;
+  // > 0: input 0 holds int64 token ids that must lie in [0, id_vocab).  LibTorch's embedding raises on an id outside
+  // its table and the reference turns that into a failed job; the device kernel clamps for memory safety, so the
+  // host gather (which touches every id anyway) refuses the batch instead.
+  int64_t id_vocab = 0;
 };
 
 // StarPUSetup + StarPUTaskRunner rolled into what the path needs: owns the codelet and the
@@ -139,6 +143,11 @@ class TaskRunner {
   [[nodiscard]] auto output_pool() -> OutputSlotPool & { return *output_pool_; }
   [[nodiscard]] auto model() const -> const ModelConfig & { return model_; }
   [[nodiscard]] auto tasks_submitted() const -> long { return submitted_.load(); }
+  // Completion fan-out: the per-request on_complete calls of one finished task (each makes that request's response
+  // copy) are independent; an executor may run them on several threads.  It must return only when all have run --
+  // the output slot is released right after.  Default: the callback thread runs them one after the other.
+  using CompletionExecutor = std::function<void(std::vector<std::function<void()>> &)>;
+  void set_completion_executor(CompletionExecutor ex) { completion_executor_ = std::move(ex); }
 
  private:
   struct CallbackContext;
@@ -152,6 +161,7 @@ class TaskRunner {
   std::unique_ptr<InputSlotPool> input_pool_;
   std::unique_ptr<OutputSlotPool> output_pool_;
   std::atomic<long> submitted_{0};
+  CompletionExecutor completion_executor_;
 };
 
 }  // namespace starpu_server

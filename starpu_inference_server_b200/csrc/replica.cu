@@ -721,6 +721,10 @@ extern "C" spu_status spu_bert_forward_async(spu_replica *r, int32_t ws_idx, con
   return enqueue_forward(r, ws, ids, mask, batch, seq, out, as_stream(stream));
 }
 
+extern "C" int32_t spu_bert_vocab_size(const spu_replica *r) {
+  return (r != nullptr && r->kind == 0) ? r->desc.vocab : 0;
+}
+
 extern "C" int32_t spu_bert_packed_supported(const spu_replica *r, int32_t batch) {
   return (r != nullptr && r->kind == 0 && (r->flags & SPU_PREC_FP8_E4M3) == 0 && !r->ln_fused && batch >= 1 &&
           batch <= kMaxPackedBatch)

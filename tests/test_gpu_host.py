@@ -385,3 +385,22 @@ def test_device_visible_requests_through_the_task_path(host, variable_length):
             srv.wait(srv.submit_batch([(0, b, [ids, mask], [None])]))
         assert srv.stats()["codelet_failures"] == 0
     rep.close()
+
+
+def test_out_of_range_token_id_fails_the_batch_like_the_reference(host, bert_tiny):
+    """LibTorch's embedding raises on an id outside the table and the reference's job fails; the kernel clamps (memory
+    safety), so the host gather refuses the batch before anything is submitted."""
+    bo, spec, w, rep = bert_tiny
+    S, H = 32, spec.hidden
+    ids, mask = bo.make_inputs(spec, 2, S, seed=3)
+    with host.Server(inputs=[("input_ids", "i64", [1, S]), ("attention_mask", "i64", [1, S])],
+                     outputs=[("output0", "f32", [1, S, H])], replicas=[rep], model_kind=host.MODEL_BERT,
+                     max_batch_size=4, pool_size=2, n_workspaces=2) as srv:
+        for bad in (spec.vocab, -1):
+            b = ids[1:2].copy()
+            b[0, 7] = bad
+            with pytest.raises(host.HostError, match="outside the embedding table"):
+                srv.submit_batch([(0, 1, [ids[:1].copy(), mask[:1].copy()], [None]), (1, 1, [b, mask[1:2].copy()], [None])])
+        out = np.zeros((1, S, H), np.float32)
+        (r,) = srv.wait(srv.submit_batch([(0, 1, [ids[:1].copy(), mask[:1].copy()], [out])]))
+        assert r.ok == 1 and srv.stats()["free_in"] == 2  # the refused batches gave their slots back
