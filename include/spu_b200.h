@@ -132,6 +132,13 @@ spu_status spu_bert_forward_packed_async(spu_replica *r, int32_t ws_idx, const i
  * [0, vocab) for memory safety where LibTorch's embedding would raise; a host layer that wants the reference's
  * failure instead validates ids against this before submitting (core/task_runner.cpp does). */
 int32_t spu_bert_vocab_size(const spu_replica *r);
+/* The same with a COMPACT output: `out` receives the packed rows only, [sum(lens), hidden] with sequence b at row
+ * lens[0] + ... + lens[b-1], nothing for the padding.  A host layer that knows the lengths slices its responses
+ * from that (core/task_runner.cpp does on variable_length servers): the device-to-host copy of the output shrinks
+ * by the padding fraction, which is what bounds 8 GPUs feeding one host. */
+spu_status spu_bert_forward_packed_compact_async(spu_replica *r, int32_t ws_idx, const int64_t *ids,
+                                                 const int32_t *lens, int32_t batch, int32_t seq, float *out,
+                                                 void *stream);
 /* 1 when spu_bert_forward_packed_async serves this replica for batches of `batch` sequences. */
 int32_t spu_bert_packed_supported(const spu_replica *r, int32_t batch);
 

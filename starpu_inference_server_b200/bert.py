@@ -117,14 +117,15 @@ class BertReplica:
                                                      capi.ptr(out), capi.stream_ptr(stream)))
         return out
 
-    def forward_packed_async(self, ids, lens, out, ws: int = 0, stream=None):
+    def forward_packed_async(self, ids, lens, out, ws: int = 0, stream=None, compact: bool = False):
         """Right-padded batch whose true lengths are known on the host: ids int64 CUDA [B,S], lens = B host ints.
-        The encoder runs on sum(lens) tokens; out [B,S,hidden] gets zeros behind each length."""
+        The encoder runs on sum(lens) tokens; out [B,S,hidden] gets zeros behind each length -- or, with
+        `compact`, out is [sum(lens), hidden]: the packed rows only."""
         b, s = ids.shape
         lens = np.ascontiguousarray(np.asarray(lens, dtype=np.int32))
         assert lens.shape == (b,)
-        capi.check(capi.lib().spu_bert_forward_packed_async(self._h, ws, capi.ptr(ids), lens.ctypes.data, b, s,
-                                                            capi.ptr(out), capi.stream_ptr(stream)))
+        fn = capi.lib().spu_bert_forward_packed_compact_async if compact else capi.lib().spu_bert_forward_packed_async
+        capi.check(fn(self._h, ws, capi.ptr(ids), lens.ctypes.data, b, s, capi.ptr(out), capi.stream_ptr(stream)))
         return out
 
     def forward_requests_async(self, src_ids_table, src_mask_table, len_dev, n_req: int, seq: int, dst_table,

@@ -193,18 +193,29 @@ void run_inference(InferenceParams *params, StarpuBufferSpan buffers, int device
       const size_t in_bytes = static_cast<size_t>(B) * static_cast<size_t>(S) * sizeof(int64_t);
       require_bytes(buffers[0], in_bytes, "Input");
       require_bytes(buffers[1], in_bytes, "Input");
-      require_bytes(buffers[2], spu_bert_output_bytes(model->replica, static_cast<int32_t>(B), static_cast<int32_t>(S)),
-                    "Output");
       const int ws = workspace_for_this_thread(model);
-      if (params->layout.seq_lens.size() == static_cast<size_t>(B) &&
-          spu_bert_packed_supported(model->replica, static_cast<int32_t>(B)) == 1) {
+      if (params->layout.seq_lens.size() == static_cast<size_t>(B)) {
         // right-padded batch with host-known lengths: skip the padding instead of multiplying it
-        check_spu(spu_bert_forward_packed_async(model->replica, ws, reinterpret_cast<const int64_t *>(buffers[0]->ptr),
-                                                params->layout.seq_lens.data(), static_cast<int32_t>(B),
-                                                static_cast<int32_t>(S), reinterpret_cast<float *>(buffers[2]->ptr),
-                                                stream));
+        if (spu_bert_packed_supported(model->replica, static_cast<int32_t>(B)) != 1)
+          throw InferenceExecutionException("[ERROR] Replica has no packed forward for a task laid out with seq_lens");
+        int64_t tokens = 0;
+        for (int32_t l : params->layout.seq_lens) tokens += l;
+        const size_t token_bytes = spu_bert_output_bytes(model->replica, 1, 1);
+        auto *ids = reinterpret_cast<const int64_t *>(buffers[0]->ptr);
+        auto *out = reinterpret_cast<float *>(buffers[2]->ptr);
+        if (params->layout.compact_output) {
+          require_bytes(buffers[2], static_cast<size_t>(tokens) * token_bytes, "Output");
+          check_spu(spu_bert_forward_packed_compact_async(model->replica, ws, ids, params->layout.seq_lens.data(),
+                                                          static_cast<int32_t>(B), static_cast<int32_t>(S), out, stream));
+        } else {
+          require_bytes(buffers[2], static_cast<size_t>(B) * static_cast<size_t>(S) * token_bytes, "Output");
+          check_spu(spu_bert_forward_packed_async(model->replica, ws, ids, params->layout.seq_lens.data(),
+                                                  static_cast<int32_t>(B), static_cast<int32_t>(S), out, stream));
+        }
         break;
       }
+      require_bytes(buffers[2], spu_bert_output_bytes(model->replica, static_cast<int32_t>(B), static_cast<int32_t>(S)),
+                    "Output");
       check_spu(spu_bert_forward_async(model->replica, ws, reinterpret_cast<const int64_t *>(buffers[0]->ptr),
                                        reinterpret_cast<const int64_t *>(buffers[1]->ptr), static_cast<int32_t>(B),
                                        static_cast<int32_t>(S), reinterpret_cast<float *>(buffers[2]->ptr), stream));

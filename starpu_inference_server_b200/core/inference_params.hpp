@@ -87,6 +87,9 @@ struct TensorLayout {
   // gather's own): true token count of each sample row.  Lets the codelet run the encoder on the real tokens
   // only (spu_bert_forward_packed_async).  Empty = unknown, the padded forward runs.
   std::vector<int32_t> seq_lens;
+  // with seq_lens: output 0 is laid out COMPACT, [sum(seq_lens), hidden...] (sample row r at token offset
+  // seq_lens[0] + ... + seq_lens[r-1]) instead of padded [batch, seq, hidden...]: no padding crosses PCIe
+  bool compact_output = false;
 };
 
 struct Limits {

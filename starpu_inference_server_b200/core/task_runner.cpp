@@ -242,6 +242,7 @@ struct TaskRunner::CallbackContext {
   int64_t effective_batch = 0;
   int64_t seq = 0;  // variable_length: the padded sequence length of this batch (0 = fixed shapes)
   bool request_io = false;  // responses were written by the codelet into the requests' own buffers
+  bool compact = false;     // output 0 holds the batch's true tokens back to back (packed forward)
   int worker_id = -1, device_id = -1;
   DeviceType executed_on = DeviceType::Unknown;
   JobTiming timing;
@@ -271,6 +272,19 @@ TaskRunner::TaskRunner(ModelConfig model, const ReplicaRegistry *replicas)
 }
 
 TaskRunner::~TaskRunner() { wait_for_all(); }
+
+// Does every replica a task may land on implement the packed forward for this batch size?  (The host decides the
+// output layout before it knows which worker takes the task.)
+auto TaskRunner::packed_forward_everywhere(int64_t batch) const -> bool {
+  if (replicas_->size() == 0 || batch > INT32_MAX) return false;
+  for (size_t i = 0; i < replicas_->size(); ++i) {
+    const DeviceModel *m = replicas_->model(i);
+    if (m == nullptr || m->kind != DeviceModel::Kind::Bert ||
+        spu_bert_packed_supported(m->replica, static_cast<int32_t>(batch)) != 1)
+      return false;
+  }
+  return true;
+}
 
 // bytes of one token row of output 0 ([batch, seq, hidden...]): hidden... x element size
 auto TaskRunner::request_token_bytes() const -> size_t {
@@ -369,9 +383,24 @@ void TaskRunner::submit_batch(const std::vector<std::shared_ptr<InferenceJob>> &
   }
   for (size_t i = 0; i < leased; ++i) starpu_data_release(in_handles[i]);
 
+  // variable_length + every mask all ones + replicas that have the packed forward: the codelet gets the true
+  // lengths and returns output 0 in the compact layout
+  std::vector<int32_t> seq_lens;
+  if (model_.variable_length && !request_io.enabled && model_.inputs.size() == 2 && model_.outputs.size() == 1 &&
+      model_.outputs[0].dims.size() >= 2 && model_.outputs[0].dims[1] == seq_cap && packed_forward_everywhere(effective_batch) &&
+      masks_all_ones(jobs))
+    for (const auto &j : jobs)
+      if (j)
+        for (int64_t s = 0; s < j->batch_size(); ++s) seq_lens.push_back(static_cast<int32_t>(j->inputs[0].dims[1]));
+  size_t total_tokens = 0;
+  for (int32_t l : seq_lens) total_tokens += static_cast<size_t>(l);
+
   // outputs: prototype resized to [effective_batch, ...] (resize_outputs_for_batch)
   for (size_t o = 0; o < out_handles.size(); ++o) {
     size_t numel = output_pool_->per_sample_numel(o) * static_cast<size_t>(effective_batch);
+    if (!seq_lens.empty())  // compact: one row of hidden... per true token
+      numel = output_pool_->per_sample_numel(o) / static_cast<size_t>(seq_cap) * total_tokens;
+    else
     // variable_length: an output whose dims[1] is the configured sequence length shrinks with the batch's seq
     if (seq > 0 && model_.outputs[o].dims.size() >= 2 && model_.outputs[o].dims[1] == seq_cap)
       numel = numel / static_cast<size_t>(seq_cap) * static_cast<size_t>(seq);
@@ -387,13 +416,9 @@ void TaskRunner::submit_batch(const std::vector<std::shared_ptr<InferenceJob>> &
   params->batch_size = effective_batch;
   params->request_id = master->request_id;
   params->request_io = request_io;
-  // variable_length + every mask all ones: hand the true lengths to the codelet (packed forward)
-  if (model_.variable_length && !request_io.enabled && model_.inputs.size() == 2 && masks_all_ones(jobs)) {
-    for (const auto &j : jobs)
-      if (j)
-        for (int64_t s = 0; s < j->batch_size(); ++s)
-          params->layout.seq_lens.push_back(static_cast<int32_t>(j->inputs[0].dims[1]));
-  }
+  params->layout.compact_output = !seq_lens.empty();
+  ctx->compact = !seq_lens.empty();
+  params->layout.seq_lens = std::move(seq_lens);
   ctx->request_io = request_io.enabled;
   params->limits.max_inputs = InferLimits::MaxInputs;
   params->limits.max_dims = InferLimits::MaxDims;
@@ -515,7 +540,19 @@ void TaskRunner::finalize(CallbackContext *ctx) {
     res.batch_seq = ctx->seq;
     res.timing = ctx->timing;
     res.timing.enqueued_time = job->timing.enqueued_time;
-    if (codelet_ok && all_acquired && ctx->request_io) {
+    if (codelet_ok && all_acquired && ctx->compact) {
+      // compact output: this request's [batch, own seq, hidden...] block starts at its token offset
+      const int64_t L = job->inputs[0].dims[1], b = job->batch_size();
+      HostTensor v = aggregated[0];
+      v.dims[0] = b;
+      v.dims[1] = L;
+      const size_t token_bytes = r->request_token_bytes();
+      v.data = aggregated[0].data + static_cast<size_t>(offset) * token_bytes;
+      res.outputs.push_back(std::move(v));
+      res.rows = b;
+      res.ok = true;
+      offset += b * L;  // `offset` counts TOKENS on this path
+    } else if (codelet_ok && all_acquired && ctx->request_io) {
       // the codelet's scatter kernel already wrote the response into the request's own buffers
       for (size_t o = 0; o < aggregated.size(); ++o) {
         HostTensor v = aggregated[o];

@@ -154,6 +154,7 @@ class TaskRunner {
   static void starpu_output_callback(void *arg);
   static void finalize(CallbackContext *ctx);
   [[nodiscard]] auto request_token_bytes() const -> size_t;
+  [[nodiscard]] auto packed_forward_everywhere(int64_t batch) const -> bool;
 
   ModelConfig model_;
   const ReplicaRegistry *replicas_;

@@ -256,7 +256,7 @@ spu_status enqueue_forward(spu_replica *r, Workspace &ws, const int64_t *ids, co
 // padded forward's bit for bit: a row's GEMM / LayerNorm result does not depend on its neighbours, and keys past a
 // sequence's end get probability exactly 0 either way.
 spu_status enqueue_forward_packed(spu_replica *r, Workspace &ws, const int64_t *ids, const int32_t *lens, int batch,
-                                  int seq, float *out, cudaStream_t stream) {
+                                  int seq, float *out, cudaStream_t stream, bool compact_out = false) {
   const spu_bert_desc &d = r->desc;
   int T = 0;
   SPU_TRY(write_cu_seqlens_launch(lens, batch, ws.cu_seqlens, &T, stream));
@@ -292,8 +292,12 @@ spu_status enqueue_forward_packed(spu_replica *r, Workspace &ws, const int64_t *
       SPU_TRY(layernorm_launch(ws.x_f32, w.ln2_g, w.ln2_b, d.ln_eps, ws.x_f32, ws.x_bf16, T, d.hidden, stream));
     } else {
       const bool out16 = (r->flags & SPU_OUTPUT_BF16) != 0;
-      SPU_TRY(layernorm_unpad_launch(ws.x_f32, ws.cu_seqlens, batch, seq, w.ln2_g, w.ln2_b, d.ln_eps,
-                                     out16 ? nullptr : out, out16 ? static_cast<void *>(out) : nullptr, d.hidden, stream));
+      if (compact_out)  // the output keeps the packed layout: [T, hidden], sequence b at row cu_seqlens[b]
+        SPU_TRY(layernorm_launch(ws.x_f32, w.ln2_g, w.ln2_b, d.ln_eps, out16 ? nullptr : out,
+                                 out16 ? static_cast<void *>(out) : nullptr, T, d.hidden, stream));
+      else
+        SPU_TRY(layernorm_unpad_launch(ws.x_f32, ws.cu_seqlens, batch, seq, w.ln2_g, w.ln2_b, d.ln_eps,
+                                       out16 ? nullptr : out, out16 ? static_cast<void *>(out) : nullptr, d.hidden, stream));
     }
   }
   return SPU_OK;
@@ -732,16 +736,30 @@ extern "C" int32_t spu_bert_packed_supported(const spu_replica *r, int32_t batch
              : 0;
 }
 
+static spu_status forward_packed(spu_replica *r, int32_t ws_idx, const int64_t *ids, const int32_t *lens, int32_t batch,
+                                 int32_t seq, float *out, void *stream, bool compact_out);
+
 extern "C" spu_status spu_bert_forward_packed_async(spu_replica *r, int32_t ws_idx, const int64_t *ids,
                                                     const int32_t *lens, int32_t batch, int32_t seq, float *out,
                                                     void *stream) {
+  return forward_packed(r, ws_idx, ids, lens, batch, seq, out, stream, false);
+}
+
+extern "C" spu_status spu_bert_forward_packed_compact_async(spu_replica *r, int32_t ws_idx, const int64_t *ids,
+                                                            const int32_t *lens, int32_t batch, int32_t seq,
+                                                            float *out, void *stream) {
+  return forward_packed(r, ws_idx, ids, lens, batch, seq, out, stream, true);
+}
+
+static spu_status forward_packed(spu_replica *r, int32_t ws_idx, const int64_t *ids, const int32_t *lens, int32_t batch,
+                                 int32_t seq, float *out, void *stream, bool compact_out) {
   SPU_TRY(check_forward_args(r, ws_idx, ids, lens, batch, seq, out));
   SPU_REQUIRE((r->flags & SPU_PREC_FP8_E4M3) == 0 && !r->ln_fused, SPU_ERR_UNSUPPORTED,
               "forward_packed: bf16 replicas with the separate LayerNorm kernel only");
   SPU_REQUIRE(batch <= kMaxPackedBatch, SPU_ERR_CAPACITY, "forward_packed: at most 256 sequences per batch");
   for (int b = 0; b < batch; ++b)
     SPU_REQUIRE(lens[b] >= 1 && lens[b] <= seq, SPU_ERR_INVALID, "forward_packed: every length must be in [1, seq]");
-  return enqueue_forward_packed(r, r->ws[ws_idx], ids, lens, batch, seq, out, as_stream(stream));
+  return enqueue_forward_packed(r, r->ws[ws_idx], ids, lens, batch, seq, out, as_stream(stream), compact_out);
 }
 
 extern "C" spu_status spu_bert_forward_requests_async(spu_replica *r, int32_t ws_idx,

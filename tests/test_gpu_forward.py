@@ -485,3 +485,25 @@ def test_packed_forward_rejects_bad_lengths(spu, base):
     for lens in ([0, 4], [17, 4]):
         with pytest.raises(spu.SpuError):
             r.forward_packed_async(ids, lens, out)
+
+
+def test_packed_forward_compact_output(base):
+    """spu_bert_forward_packed_compact_async: the output holds the true tokens back to back, bit-identical to the
+    live rows of the padded layout, and nothing is written behind the last token."""
+    bo, w, r = base
+    B, S = 6, 96
+    ids, mask = bo.make_inputs(bo.BERT_BASE, B, S, seed=41, min_len=3)
+    lens = mask.sum(1).astype(np.int32)
+    ids_d = torch.from_numpy(ids).cuda()
+    padded = torch.empty(B, S, 768, device="cuda")
+    T = int(lens.sum())
+    compact = torch.full((T + 2, 768), float("nan"), device="cuda")
+    r.forward_packed_async(ids_d, lens, padded)
+    r.forward_packed_async(ids_d, lens, compact, ws=1, compact=True)
+    torch.cuda.synchronize()
+    off = 0
+    for b in range(B):
+        n = int(lens[b])
+        assert torch.equal(compact[off:off + n], padded[b, :n]), b
+        off += n
+    assert bool(torch.isnan(compact[T:]).all())
