@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define SPU_ABI_VERSION 1
+#define SPU_ABI_VERSION 2 /* 2: packed / compact forward, autotune, graph count, vocab size */
 
 typedef enum spu_status {
   SPU_OK = 0,

@@ -25,7 +25,7 @@ def test_header_symbols_all_exported(built_libs):
     for name in declared:
         assert hasattr(L, name), f"{name} declared in spu_b200.h but not exported"
     assert sorted(capi.SYMBOLS) == declared
-    assert L.spu_abi_version() == 1
+    assert L.spu_abi_version() == 2
 
 
 def test_library_is_sm100a_only(built_libs):
