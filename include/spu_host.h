@@ -200,6 +200,15 @@ int64_t spu_host_slice_rows(uint64_t rows, uint64_t row_bytes, int64_t offset, i
 /* the collector's tile-aware rule: 1 when a batch of rows x seq token rows ends inside a GEMM row tile and may
  * still grow (rows < max_rows) */
 int32_t spu_host_tile_aware_wants_more(int64_t rows, int64_t seq, int64_t max_rows, int32_t tile_rows);
+/* write_request_table (spu_server_cfg.device_visible_requests) over n_jobs requests of batch[j] samples x len[j]
+ * tokens whose ids / mask / response buffers live at the given addresses (dst 0 = no response buffer): writes the
+ * table into `slot`; out = {rows, off_mask, off_dst, off_len, table_bytes, full_rows, nx of the table handle, nx of
+ * the second input handle}.  0 ok / 1 exception (message in last_error). */
+int32_t spu_host_request_table(const uint64_t *ids_ptrs, const uint64_t *mask_ptrs, const uint64_t *dst_ptrs,
+                               const int64_t *batch, const int64_t *len, int32_t n_jobs, int64_t seq,
+                               uint64_t token_bytes, void *slot, uint64_t capacity_bytes, int64_t out[8]);
+/* masks_all_ones over n_jobs int64 mask arrays: 1 when the packed forward may be used for the batch */
+int32_t spu_host_masks_all_ones(const int64_t *const *masks, const int64_t *numel, int32_t n_jobs);
 /* can_merge_jobs over two single-input requests described by dims/dtype */
 int32_t spu_host_can_merge(const int64_t *dims_a, int32_t nd_a, int32_t dt_a, const int64_t *dims_b, int32_t nd_b,
                            int32_t dt_b);

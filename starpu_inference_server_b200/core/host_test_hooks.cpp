@@ -258,6 +258,71 @@ int32_t spu_host_gather_padded(const int64_t *const *srcs, const int64_t *len, i
   return rc;
 }
 
+int32_t spu_host_request_table(const uint64_t *ids_ptrs, const uint64_t *mask_ptrs, const uint64_t *dst_ptrs,
+                               const int64_t *batch, const int64_t *len, int32_t n_jobs, int64_t seq,
+                               uint64_t token_bytes, void *slot, uint64_t capacity_bytes, int64_t out[8]) {
+  starpu_data_handle_t h0 = nullptr, h1 = nullptr;
+  std::vector<int64_t> second(8, 0);
+  starpu_vector_data_register(&h0, STARPU_MAIN_RAM, reinterpret_cast<uintptr_t>(slot),
+                              static_cast<uint32_t>(capacity_bytes / 8), 8);
+  starpu_vector_data_register(&h1, STARPU_MAIN_RAM, reinterpret_cast<uintptr_t>(second.data()), 8, 8);
+  std::vector<std::shared_ptr<InferenceJob>> jobs;
+  int64_t rows = 0;
+  for (int j = 0; j < n_jobs; ++j) {
+    auto job = std::make_shared<InferenceJob>();
+    job->request_id = j;
+    for (const uint64_t *tab : {ids_ptrs, mask_ptrs}) {
+      HostTensor t;
+      t.data = reinterpret_cast<std::byte *>(static_cast<uintptr_t>(tab[j]));
+      t.type = ScalarType::Int64;
+      t.dims = {batch[j], len[j]};
+      job->inputs.push_back(std::move(t));
+    }
+    if (dst_ptrs[j] != 0) job->output_dsts.push_back(reinterpret_cast<void *>(static_cast<uintptr_t>(dst_ptrs[j])));
+    rows += batch[j];
+    jobs.push_back(std::move(job));
+  }
+  int32_t rc = 0;
+  try {
+    HostBufferInfo i0, i1;
+    i0.bytes = static_cast<size_t>(capacity_bytes);
+    i1.bytes = 64;
+    detail::RequestIo io;
+    write_request_table(jobs, {h0, h1}, {reinterpret_cast<std::byte *>(slot), reinterpret_cast<std::byte *>(second.data())},
+                        {i0, i1}, rows, seq, static_cast<size_t>(token_bytes), &io);
+    out[0] = io.rows;
+    out[1] = static_cast<int64_t>(io.off_mask);
+    out[2] = static_cast<int64_t>(io.off_dst);
+    out[3] = static_cast<int64_t>(io.off_len);
+    out[4] = static_cast<int64_t>(io.table_bytes);
+    out[5] = io.full_rows ? 1 : 0;
+    out[6] = static_cast<starpu_vector_interface *>(starpu_data_get_interface_on_node(h0, 0))->nx;
+    out[7] = static_cast<starpu_vector_interface *>(starpu_data_get_interface_on_node(h1, 0))->nx;
+  } catch (const std::exception &e) {
+    fail(e);
+    rc = 1;
+  }
+  starpu_data_unregister(h0);
+  starpu_data_unregister(h1);
+  return rc;
+}
+
+int32_t spu_host_masks_all_ones(const int64_t *const *masks, const int64_t *numel, int32_t n_jobs) {
+  std::vector<std::shared_ptr<InferenceJob>> jobs;
+  for (int j = 0; j < n_jobs; ++j) {
+    auto job = std::make_shared<InferenceJob>();
+    for (int k = 0; k < 2; ++k) {
+      HostTensor t;
+      t.data = reinterpret_cast<std::byte *>(const_cast<int64_t *>(masks[j]));
+      t.type = ScalarType::Int64;
+      t.dims = {1, numel[j]};
+      job->inputs.push_back(std::move(t));
+    }
+    jobs.push_back(std::move(job));
+  }
+  return masks_all_ones(jobs) ? 1 : 0;
+}
+
 int32_t spu_host_call_cuda_func_affine(const float *in_dev, float *out_dev, uint64_t n, float scale, float shift,
                                        int32_t device, int32_t worker_id, void *stream, int32_t n_models,
                                        int32_t use_vector_iface, int64_t rec[6]) {

@@ -97,6 +97,18 @@ auto copy_job_inputs_to_slot_padded(const InferenceJob *job, const std::vector<c
                                     const std::vector<std::byte *> &base_ptrs,
                                     const std::vector<HostBufferInfo> &buffer_infos, int64_t seq) -> std::size_t;
 
+// SURVEY 8(f) row 2 (ModelConfig::device_visible_requests): describe the requests instead of gathering them.
+// Writes into the first input slot one entry per sample row, in request order: address of its token ids, of its
+// mask words, of its destination block ([own seq, hidden...] of that request's output buffer) and its length;
+// resizes the two input handles to the table / to one element.  `io` receives the layout the codelet needs.
+void write_request_table(const std::vector<std::shared_ptr<InferenceJob>> &jobs,
+                         const std::vector<starpu_data_handle_t> &handles, const std::vector<std::byte *> &base_ptrs,
+                         const std::vector<HostBufferInfo> &buffer_infos, int64_t rows, int64_t seq,
+                         size_t token_bytes, detail::RequestIo *io);
+// Is every request's attention_mask (input 1, int64) all non-zero?  Then the batch's only padding is the host
+// gather's own and the rows' true lengths are the requests' dims[1] (packed forward, compact output).
+auto masks_all_ones(const std::vector<std::shared_ptr<InferenceJob>> &jobs) -> bool;
+
 struct SubJobSliceResult {
   std::vector<HostTensor> outputs;
   int64_t processed_length = 0;

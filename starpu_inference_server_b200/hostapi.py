@@ -24,7 +24,7 @@ SYMBOLS = [
     "spu_host_buffer_byte_size", "spu_host_select_replica", "spu_host_gather_to_slot", "spu_host_slice_rows",
     "spu_host_can_merge", "spu_host_call_cuda_func_affine", "spu_host_can_merge_varlen", "spu_host_gather_padded",
     "spu_host_replica_assignments", "spu_host_nvtx_capture", "spu_server_offered_load",
-    "spu_host_tile_aware_wants_more",
+    "spu_host_tile_aware_wants_more", "spu_host_request_table", "spu_host_masks_all_ones",
 ]
 
 
@@ -92,6 +92,11 @@ def lib():
     L.spu_server_offered_load.argtypes = [vp, C.POINTER(Request), i32, i64, f64, u64, C.POINTER(f64), C.POINTER(f64),
                                           C.POINTER(f64), C.POINTER(i32), C.POINTER(f64)]
     L.spu_server_offered_load.restype = i32
+    L.spu_host_request_table.argtypes = [C.POINTER(u64), C.POINTER(u64), C.POINTER(u64), C.POINTER(i64), C.POINTER(i64),
+                                         i32, i64, u64, vp, u64, C.POINTER(i64)]
+    L.spu_host_request_table.restype = i32
+    L.spu_host_masks_all_ones.argtypes = [C.POINTER(vp), C.POINTER(i64), i32]
+    L.spu_host_masks_all_ones.restype = i32
     L.spu_host_tile_aware_wants_more.argtypes = [i64, i64, i64, i32]
     L.spu_host_tile_aware_wants_more.restype = i32
     L.spu_host_nvtx_capture.argtypes = [i32, C.c_char_p, u64, C.POINTER(i64)]

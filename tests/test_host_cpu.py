@@ -281,3 +281,58 @@ def test_tile_aware_close_rule(host):
     assert L.spu_host_tile_aware_wants_more(64, 100, 64, 256) == 0    # at the cap although 6400 % 256 != 0
     assert L.spu_host_tile_aware_wants_more(3, 128, 32, 0) == 0       # switched off
     assert L.spu_host_tile_aware_wants_more(1, 197, 64, 256) == 1     # ViT: 197 tokens per image
+
+
+def test_request_table_layout_for_device_visible_requests(host):
+    """write_request_table: one entry per SAMPLE ROW in request order -- ids / mask addresses stride
+    by the request's own length, the destination by length x token bytes -- int32 lengths behind the three pointer
+    arrays, the table handle resized to the table, the second input to one element; ragged batches scatter live rows."""
+    import ctypes as C
+
+    L = host.lib()
+    u64, i64 = C.c_uint64, C.c_int64
+    batch, lens = [1, 2, 1], [5, 9, 9]
+    ids, mask, dst = [0x1000, 0x2000, 0x3000], [0x11000, 0x12000, 0x13000], [0x100000, 0x200000, 0x300000]
+    slot = np.zeros(64, dtype=np.int64)
+    out = (i64 * 8)()
+    tb = 768 * 4
+    rc = L.spu_host_request_table((u64 * 3)(*ids), (u64 * 3)(*mask), (u64 * 3)(*dst), (i64 * 3)(*batch), (i64 * 3)(*lens),
+                                  3, 9, tb, slot.ctypes.data, slot.nbytes, out)
+    assert rc == 0, host.last_error()
+    rows, off_mask, off_dst, off_len, table_bytes, full_rows, nx0, nx1 = list(out)
+    assert (rows, off_mask, off_dst, off_len) == (4, 32, 64, 96) and table_bytes == 112 and full_rows == 0
+    assert nx0 == table_bytes // 8 and nx1 == 1
+    raw = slot.view(np.uint8)
+    tab = lambda off: raw[off:off + 32].view(np.uint64).tolist()
+    assert tab(0) == [0x1000, 0x2000, 0x2000 + 9 * 8, 0x3000]
+    assert tab(off_mask) == [0x11000, 0x12000, 0x12000 + 9 * 8, 0x13000]
+    assert tab(off_dst) == [0x100000, 0x200000, 0x200000 + 9 * tb, 0x300000]
+    assert raw[off_len:off_len + 16].view(np.int32).tolist() == [5, 9, 9, 9]
+    # equal lengths = the batch's seq: full-row scatter
+    rc = L.spu_host_request_table((u64 * 2)(*ids[:2]), (u64 * 2)(*mask[:2]), (u64 * 2)(*dst[:2]), (i64 * 2)(1, 1),
+                                  (i64 * 2)(9, 9), 2, 9, tb, slot.ctypes.data, slot.nbytes, out)
+    assert rc == 0 and out[5] == 1
+    # a request without a response buffer, a request longer than the batch, a slot too small for the table
+    rc = L.spu_host_request_table((u64 * 1)(ids[0]), (u64 * 1)(mask[0]), (u64 * 1)(0), (i64 * 1)(1), (i64 * 1)(5), 1, 9, tb,
+                                  slot.ctypes.data, slot.nbytes, out)
+    assert rc == 1 and "output buffer" in host.last_error()
+    rc = L.spu_host_request_table((u64 * 1)(ids[0]), (u64 * 1)(mask[0]), (u64 * 1)(dst[0]), (i64 * 1)(1), (i64 * 1)(10), 1, 9,
+                                  tb, slot.ctypes.data, slot.nbytes, out)
+    assert rc == 1 and "longer than the batch" in host.last_error()
+    rc = L.spu_host_request_table((u64 * 3)(*ids), (u64 * 3)(*mask), (u64 * 3)(*dst), (i64 * 3)(*batch), (i64 * 3)(*lens),
+                                  3, 9, tb, slot.ctypes.data, 64, out)
+    assert rc == 1 and "capacity" in host.last_error()
+
+
+def test_masks_all_ones_decides_the_packed_forward(host):
+    import ctypes as C
+
+    L = host.lib()
+    a, b = np.ones(7, dtype=np.int64), np.ones(12, dtype=np.int64)
+    ptrs = (C.c_void_p * 2)(a.ctypes.data, b.ctypes.data)
+    n = (C.c_int64 * 2)(7, 12)
+    assert L.spu_host_masks_all_ones(ptrs, n, 2) == 1
+    b[11] = 0  # a client-side padded mask: lengths are not the requests' dims[1] any more
+    assert L.spu_host_masks_all_ones(ptrs, n, 2) == 0
+    b[11], a[0] = 3, -1  # any non-zero word keeps a token
+    assert L.spu_host_masks_all_ones(ptrs, n, 2) == 1
