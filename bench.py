@@ -508,6 +508,10 @@ def run_b200(args, cfg, rank, local_rank, world):
         gemm_ms = min(rep.stage_chain_ms(*chain_in, chain_out, gemm_names, stream=stream) for _ in range(3))
         stage_ms = {k: min(rep.stage_chain_ms(*chain_in, chain_out, [k], stream=stream) for _ in range(3))
                     for k in capi.STAGE_NAMES}
+    else:
+        torch.cuda.synchronize(dev)
+        time.sleep(1.0)
+        gemm_ms = min(rep.gemm_chain_ms(in_d[0][0], out_d[0], stream=stream) for _ in range(3))
     # ---------------- sustained figure: >= 2 s of back-to-back steps ----------------
     per_step_ms = ms_total / args.steps
     sus_steps = int(max(args.steps, min(50000, 2200.0 / max(per_step_ms, 1e-3))))
@@ -520,6 +524,8 @@ def run_b200(args, cfg, rank, local_rank, world):
     if not is_vit:
         # the same GEMM chain right after >= 2 s of load: the state the SUSTAINED peak was measured in
         gemm_ms_hot = min(rep.stage_chain_ms(*chain_in, chain_out, gemm_names, stream=stream) for _ in range(3))
+    else:
+        gemm_ms_hot = min(rep.gemm_chain_ms(in_d[0][0], out_d[0], stream=stream) for _ in range(3))
 
     clocks = sampler.stop()
     clocks["timed_region"] = sampler.window(t_timed0, t_timed1)
@@ -662,14 +668,17 @@ def run_b200(args, cfg, rank, local_rank, world):
     value = whole_job_rate(B, args.steps, world, ms_total)
     if is_vit:
         dense_flop_step = (2 * 196 * 768 * 1024 + 24 * 24 * 197 * 1024 * 1024 + 2 * 1024 * 1000) * B
-        tf = dense_flop_step / (ms_total / args.steps / 1e3) / 1e12
+        tf = dense_flop_step / (gemm_ms / 1e3) / 1e12
         roofline = {"bound": "tensor", "kernel": "gemm_tcgen05_kernel (patch-embed, QKV, attn-out, MLP1, MLP2, head; "
                                                  "98 launches/step)",
-                    "achieved": tf, "peak": peaks["tflops"], "unit": "TFLOP/s", "frac": tf / peaks["tflops"],
-                    "peak_source": peaks["source"] + ", sustained bf16", "traffic": None,
-                    "flops_per_step": dense_flop_step, "kernel_ms_per_step": None,
-                    "how": "LOWER bound: dense-GEMM FLOPs of the step over the WHOLE step's device time (attention, "
-                           "LayerNorm and im2col kernels included); no GEMM-only chain hook exists for ViT"}
+                    "achieved": tf, "peak": peaks["tflops_burst"], "unit": "TFLOP/s", "frac": tf / peaks["tflops_burst"],
+                    "peak_source": peaks["source"] + ": bf16_tflops (burst) -- the chain is timed alone after 1 s of idle",
+                    "frac_of_sustained_peak": dense_flop_step / (gemm_ms_hot / 1e3) / 1e12 / peaks["tflops"],
+                    "peak_sustained": peaks["tflops"], "kernel_ms_per_step_after_sustained_load": gemm_ms_hot,
+                    "traffic": None, "flops_per_step": dense_flop_step, "kernel_ms_per_step": gemm_ms,
+                    "whole_step_tflops": dense_flop_step / (ms_total / args.steps / 1e3) / 1e12,
+                    "how": "the 98 GEMM launches of 3 forwards back to back in one CUDA graph (spu_vit_gemm_chain_ms), "
+                           "CUDA events on the launch stream"}
     else:
         gemm_flop_step = LAYERS * 24 * true_tokens * HIDDEN * HIDDEN  # charged on true lengths
         # the timed chain ran `gemm_rows` rows (= the padded batch, or ~the true tokens on the packed path)

@@ -272,6 +272,11 @@ spu_status spu_vit_replica_create(const spu_vit_desc *desc, const float *const *
  * buffers[0]->ptr); logits: DEVICE fp32 [batch, classes]. */
 spu_status spu_vit_forward_async(spu_replica *r, int32_t ws_idx, const float *pixels,
                                  int32_t batch, float *logits, void *stream);
+/* Measurement hook: device ms per forward of the ViT's dense GEMMs alone (patch embedding, QKV, attention-output,
+ * MLP1, MLP2 of every layer, head): `reps` forwards' worth back to back in one CUDA graph, CUDA events on `stream`
+ * (non-default).  Clobbers the workspace. */
+spu_status spu_vit_gemm_chain_ms(spu_replica *r, int32_t ws_idx, const float *pixels, int32_t batch, float *logits,
+                                 int32_t reps, void *stream, float *ms_per_forward);
 uint64_t spu_vit_input_bytes(const spu_replica *r, int32_t batch);
 uint64_t spu_vit_output_bytes(const spu_replica *r, int32_t batch);
 

@@ -35,7 +35,7 @@ SYMBOLS = [
     "spu_gemm_fp8_async", "spu_quantize_e4m3_async", "spu_bert_set_fp8_mask", "spu_bert_get_fp8_mask",
     "spu_gemm_ln_bf16_async", "spu_bert_graph_count", "spu_bert_autotune", "spu_bert_tuned_configs",
     "spu_bert_forward_packed_async", "spu_bert_packed_supported", "spu_bert_vocab_size",
-    "spu_bert_forward_packed_compact_async",
+    "spu_bert_forward_packed_compact_async", "spu_vit_gemm_chain_ms",
 ]
 
 
@@ -81,6 +81,8 @@ def lib():
     L.spu_bert_forward_packed_async.restype = i32
     L.spu_bert_forward_packed_compact_async.argtypes = [vp, i32, vp, vp, i32, i32, vp, vp]
     L.spu_bert_forward_packed_compact_async.restype = i32
+    L.spu_vit_gemm_chain_ms.argtypes = [vp, i32, vp, i32, vp, i32, vp, C.POINTER(f32)]
+    L.spu_vit_gemm_chain_ms.restype = i32
     L.spu_bert_vocab_size.argtypes = [vp]
     L.spu_bert_vocab_size.restype = i32
     L.spu_bert_packed_supported.argtypes = [vp, i32]

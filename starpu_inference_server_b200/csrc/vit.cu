@@ -212,11 +212,13 @@ spu_status vit_build(spu_replica *r, VitState *v, const float *const *t, int max
   return SPU_OK;
 }
 
+// gemm_only (measurement hook, spu_vit_gemm_chain_ms): enqueue the dense GEMMs only -- patch embedding, QKV,
+// attention-output, MLP1, MLP2, head -- on whatever the workspace holds
 spu_status vit_enqueue(spu_replica *r, VitState *v, VitWorkspace &ws, const float *pixels, int batch,
-                       float *logits, cudaStream_t stream) {
+                       float *logits, cudaStream_t stream, bool gemm_only = false) {
   const spu_vit_desc &d = v->d;
   const int S = v->seq, M = batch * S, MP = batch * v->n_patches;
-  {
+  if (!gemm_only) {
     const long long total = static_cast<long long>(batch) * d.channels * d.image * (d.image / 4);
     const long long blocks = (total + 255) / 256;
     const int grid = static_cast<int>(blocks > 148LL * 16 ? 148LL * 16 : blocks);
@@ -229,7 +231,7 @@ spu_status vit_enqueue(spu_replica *r, VitState *v, VitWorkspace &ws, const floa
   e.resid = v->pos_tiled;
   e.out = ws.patch_out;
   SPU_TRY(gemm_launch(ws.patch_plan, MP, e, stream));
-  {
+  if (!gemm_only) {
     const int grid = (M + kRowThreads / 32 - 1) / (kRowThreads / 32);
     SPU_CUDA_TRY(launch_pdl(vit_assemble_ln_kernel, dim3(grid), dim3(kRowThreads), 0, stream, ws.patch_out,
                             v->cls_pos0, v->layers[0].ln1_g, v->layers[0].ln1_b, d.ln_eps, ws.x_f32, ws.y_bf16, M, S,
@@ -242,12 +244,12 @@ spu_status vit_enqueue(spu_replica *r, VitState *v, VitWorkspace &ws, const floa
     e.resid = nullptr;
     e.out = ws.qkv;
     SPU_TRY(gemm_launch(p.qkv, M, e, stream));
-    SPU_TRY(attention_launch(ws.qkv, nullptr, ws.ctx, batch, S, d.heads, stream));
+    if (!gemm_only) SPU_TRY(attention_launch(ws.qkv, nullptr, ws.ctx, batch, S, d.heads, stream));
     e.bias = w.b_o;
     e.resid = ws.x_f32;
     e.out = ws.x_f32;
     SPU_TRY(gemm_launch(p.attn_out, M, e, stream));
-    SPU_TRY(layernorm_launch(ws.x_f32, w.ln2_g, w.ln2_b, d.ln_eps, nullptr, ws.y_bf16, M, d.hidden, stream));
+    if (!gemm_only) SPU_TRY(layernorm_launch(ws.x_f32, w.ln2_g, w.ln2_b, d.ln_eps, nullptr, ws.y_bf16, M, d.hidden, stream));
     e.bias = w.b_1;
     e.resid = nullptr;
     e.out = ws.h;
@@ -256,19 +258,20 @@ spu_status vit_enqueue(spu_replica *r, VitState *v, VitWorkspace &ws, const floa
     e.resid = ws.x_f32;
     e.out = ws.x_f32;
     SPU_TRY(gemm_launch(p.mlp2, M, e, stream));
-    if (l + 1 < d.layers) {
+    if (l + 1 < d.layers && !gemm_only) {
       const LayerWeights &n = v->layers[l + 1];
       SPU_TRY(layernorm_launch(ws.x_f32, n.ln1_g, n.ln1_b, d.ln_eps, nullptr, ws.y_bf16, M, d.hidden, stream));
     }
   }
   // encoder.ln on the class tokens only (rows b*S), then the classification head
-  SPU_TRY(layernorm_launch(ws.x_f32, v->lnf_g, v->lnf_b, d.ln_eps, nullptr, ws.cls_bf16, batch, d.hidden, stream,
-                           static_cast<long long>(S) * d.hidden));
+  if (!gemm_only)
+    SPU_TRY(layernorm_launch(ws.x_f32, v->lnf_g, v->lnf_b, d.ln_eps, nullptr, ws.cls_bf16, batch, d.hidden, stream,
+                             static_cast<long long>(S) * d.hidden));
   e.bias = v->b_head;
   e.resid = v->zeros;
   e.out = ws.logits_pad;
   SPU_TRY(gemm_launch(ws.head_plan, batch, e, stream));
-  {
+  if (!gemm_only) {
     const int total = batch * d.classes;
     vit_slice_logits_kernel<<<(total + 255) / 256, 256, 0, stream>>>(ws.logits_pad, logits, batch, d.classes,
                                                                     v->classes_pad);
@@ -343,6 +346,51 @@ extern "C" spu_status spu_vit_forward_async(spu_replica *r, int32_t ws_idx, cons
               "vit_forward: batch exceeds the workspace the replica was created with");
   SPU_REQUIRE((reinterpret_cast<uintptr_t>(pixels) & 15u) == 0, SPU_ERR_INVALID, "vit_forward: pixels must be 16-byte aligned");
   return vit_enqueue(r, r->vit, r->vit->ws[ws_idx], pixels, batch, logits, as_stream(stream));
+}
+
+// Measurement hook (bench.py's roofline of config E): device ms per forward of the dense GEMMs alone -- `reps`
+// forwards' worth of them back to back in one CUDA graph, CUDA events on `stream`.  Clobbers the workspace.
+extern "C" spu_status spu_vit_gemm_chain_ms(spu_replica *r, int32_t ws_idx, const float *pixels, int32_t batch,
+                                            float *logits, int32_t reps, void *stream, float *ms_per_forward) {
+  SPU_REQUIRE(r != nullptr && r->kind == 1 && r->vit != nullptr, SPU_ERR_INVALID, "vit_gemm_chain: not a ViT replica");
+  SPU_REQUIRE(pixels && logits && ms_per_forward && reps > 0 && stream != nullptr, SPU_ERR_INVALID,
+              "vit_gemm_chain: bad argument (a non-default stream is needed for the capture)");
+  SPU_REQUIRE(ws_idx >= 0 && ws_idx < static_cast<int>(r->vit->ws.size()) && batch >= 1 && batch <= r->max_batch,
+              SPU_ERR_INVALID, "vit_gemm_chain: bad workspace or batch");
+  cudaStream_t s = as_stream(stream);
+  VitWorkspace &ws = r->vit->ws[ws_idx];
+  SPU_TRY(vit_enqueue(r, r->vit, ws, pixels, batch, logits, s, true));  // warm-up, kernel attributes
+  SPU_CUDA_TRY(cudaStreamSynchronize(s));
+  SPU_CUDA_TRY(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
+  spu_status st = SPU_OK;
+  for (int i = 0; i < reps && st == SPU_OK; ++i) st = vit_enqueue(r, r->vit, ws, pixels, batch, logits, s, true);
+  cudaGraph_t graph = nullptr;
+  cudaError_t e = cudaStreamEndCapture(s, &graph);
+  if (st != SPU_OK) {
+    if (graph) cudaGraphDestroy(graph);
+    return st;
+  }
+  SPU_CUDA_TRY(e);
+  cudaGraphExec_t exec = nullptr;
+  e = cudaGraphInstantiate(&exec, graph, 0);
+  cudaGraphDestroy(graph);
+  SPU_CUDA_TRY(e);
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  cudaEventCreate(&e0);
+  cudaEventCreate(&e1);
+  cudaGraphLaunch(exec, s);
+  cudaEventRecord(e0, s);
+  cudaGraphLaunch(exec, s);
+  cudaEventRecord(e1, s);
+  e = cudaStreamSynchronize(s);
+  float ms = 0.f;
+  if (e == cudaSuccess) cudaEventElapsedTime(&ms, e0, e1);
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  cudaGraphExecDestroy(exec);
+  SPU_CUDA_TRY(e);
+  *ms_per_forward = ms / static_cast<float>(reps);
+  return SPU_OK;
 }
 
 extern "C" uint64_t spu_vit_input_bytes(const spu_replica *r, int32_t batch) {

@@ -88,6 +88,13 @@ class VitReplica:
                                                     capi.stream_ptr(stream)))
         return logits
 
+    def gemm_chain_ms(self, pixels, logits, reps: int = 3, ws: int = 0, stream=None) -> float:
+        """Device ms per forward of the dense GEMMs alone (measurement hook; needs a non-default stream)."""
+        ms = C.c_float()
+        capi.check(capi.lib().spu_vit_gemm_chain_ms(self._h, ws, capi.ptr(pixels), pixels.shape[0], capi.ptr(logits), reps,
+                                                    capi.stream_ptr(stream), C.byref(ms)))
+        return ms.value
+
     def close(self):
         if getattr(self, "_h", None):
             capi.lib().spu_replica_destroy(self._h)

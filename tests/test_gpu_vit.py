@@ -118,3 +118,18 @@ def test_vit_through_the_task_path(tiny):
         res = srv.wait(srv.submit_batch([(i, 1, [x[i:i + 1].copy()], [outs[i]]) for i in range(5)]))
         assert all(q.ok == 1 and q.batch_rows == 5 for q in res), [q.error for q in res]
         assert (np.concatenate(outs, 0) == direct).all()
+
+
+def test_gemm_chain_hook_times_the_gemms_and_leaves_the_replica_usable(tiny):
+    """spu_vit_gemm_chain_ms (bench.py's roofline of config E) runs the GEMMs alone on whatever the workspace holds;
+    the next real forward is unaffected."""
+    vo, w, r = tiny
+    x = vo.make_inputs(vo.VIT_TINY, 4, 11)
+    before = _run(r, x, 10)
+    s = torch.cuda.Stream()
+    out = torch.empty(4, 10, device="cuda")
+    ms = r.gemm_chain_ms(torch.from_numpy(x).cuda(), out, reps=2, stream=s)
+    assert 0.0 < ms < 50.0
+    with pytest.raises(Exception):
+        r.gemm_chain_ms(torch.from_numpy(x).cuda(), out, reps=2, stream=None)  # the default stream cannot capture
+    assert np.array_equal(_run(r, x, 10), before)
