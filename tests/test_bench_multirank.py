@@ -71,7 +71,7 @@ def test_config_objects_are_identical_in_both_arms_and_name_the_baseline_workloa
         cfg = bench.resolve_config(args)
         a, b = bench.workload_config(cfg, 8), bench.workload_config(dict(cfg), 8)
         assert a == b and a["config_id"] == cid and "BASELINE configs[" in a["workload"] and not cfg["variant"]
-        assert set(a) == {"workload", "config_id", "model", "batch", "seq_len", "precision", "min_len", "replicas"}
+        assert set(a) == {"workload", "config_id", "model", "batch", "seq_len", "precision", "min_len", "replicas", "l2"}
     v = bench.resolve_config(argparse.Namespace(config="B", batch=64, seq=None, precision=None, min_len=None))
     assert v["variant"] and "variant" in bench.workload_config(v, 1)["workload"]
     assert bench.metric_name(bench.resolve_config(argparse.Namespace(config="B", batch=None, seq=None, precision=None,
