@@ -382,7 +382,8 @@ def run_b200(args, cfg, rank, local_rank, world):
         from starpu_inference_server_b200.vit import VitConfig, VitReplica
 
         spec = VitConfig()
-        rep = VitReplica(syn.make_vit_weights(spec, 0), spec, device=local_rank, max_batch=B, n_workspaces=n_pipe)
+        rep = VitReplica(syn.make_vit_weights(spec, 0), spec, device=local_rank, max_batch=B, n_workspaces=n_pipe,
+                         flags=capi.SPU_PREC_BF16 | (capi.SPU_FORWARD_AUTO_GRAPH if args.auto_graph else 0))
         in_d = [(torch.from_numpy(h[0]).to(dev),) for h in host]
         out_shape, out_dtype = (B, spec.classes), torch.float32
         true_tokens = float(B * spec.seq)
@@ -713,7 +714,7 @@ def run_b200(args, cfg, rank, local_rank, world):
                 "mean_true_tokens_per_batch": true_tokens, "cores_per_rank": pinned_cores,
                 "forward": ("packed: the encoder runs on the true tokens of each right-padded batch (lengths known to the "
                             "host), eager launches" if packed else
-                            ("[batch, 3, 224, 224] pixels, eager launches" if is_vit else
+                            ("[batch, 3, 224, 224] pixels, " + ("CUDA-graph replay" if args.auto_graph else "eager launches") if is_vit else
                              "padded [batch, seq] with mask, CUDA-graph replay")),
                 "gemm_tiles": None if is_vit or not args.autotune else {
                     "how": "warm-up autotune: every (cta_group, BLOCK_N) timed per GEMM problem, winner installed",
@@ -729,7 +730,7 @@ def run_b200(args, cfg, rank, local_rank, world):
                 "path": "libspu_host.so: per-request host buffers -> host gather -> task -> H2D -> codelet -> D2H -> "
                         f"per-request views of the pinned output slot ({e2e_workers} CUDA workers x pipeline "
                         f"{e2e_pipeline}, pool {e2e_pool}, "
-                        + ("one CUDA graph per (worker, batch shape), retargeted to the task's slot)" if (args.auto_graph and not is_vit) else "eager launches)"),
+                        + ("one CUDA graph per (worker, batch shape), retargeted to the task's slot)" if args.auto_graph else "eager launches)"),
                 "delivered": {"value": whole_job_rate(B, args.steps, world, e2e_out_ms), "unit": UNIT,
                               "what": "the same path plus the per-request response copy into caller-owned buffers "
                                       "(the reference's fill_output_tensor), on the completer threads"},

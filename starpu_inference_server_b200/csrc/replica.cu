@@ -448,7 +448,9 @@ spu_status check_forward_args(spu_replica *r, int ws_idx, const void *ids, const
   return SPU_OK;
 }
 
-constexpr size_t kMaxGraphs = 64;  // per workspace; least recently used goes first
+}  // namespace
+
+// ---- CUDA-graph helpers shared with vit.cu (declared in replica.cuh) ----
 
 void destroy_graph(CapturedGraph &g) {
   if (g.exec) cudaGraphExecDestroy(g.exec);
@@ -457,18 +459,9 @@ void destroy_graph(CapturedGraph &g) {
   g.graph = nullptr;
 }
 
-void drop_graphs(Workspace &ws) {
-  for (CapturedGraph &g : ws.graphs) destroy_graph(g);
-  for (CapturedGraph &g : ws.req_graphs) destroy_graph(g);
-  ws.graphs.clear();
-  ws.seen.clear();
-  ws.req_graphs.clear();
-  ws.req_seen.clear();
-}
-
 // Replace 8-byte parameters of one kernel node in the instantiated graph (and in its template, so the next
 // read-back sees what the exec holds).  Launches already enqueued keep their parameters.
-spu_status patch_node(CapturedGraph &g, cudaGraphNode_t node, int n_args, std::initializer_list<std::pair<int, const void *>> changes) {
+spu_status graph_patch_node(CapturedGraph &g, cudaGraphNode_t node, int n_args, std::initializer_list<std::pair<int, const void *>> changes) {
   cudaKernelNodeParams p{};
   SPU_CUDA_TRY(cudaGraphKernelNodeGetParams(node, &p));
   void *args[24];
@@ -486,7 +479,7 @@ spu_status patch_node(CapturedGraph &g, cudaGraphNode_t node, int n_args, std::i
 }
 
 // Find the single root and the single leaf of a captured chain; both must be kernel nodes.
-bool chain_ends(cudaGraph_t graph, cudaGraphNode_t *root, cudaGraphNode_t *leaf, cudaKernelNodeParams *p0,
+bool graph_chain_ends(cudaGraph_t graph, cudaGraphNode_t *root, cudaGraphNode_t *leaf, cudaKernelNodeParams *p0,
                 cudaKernelNodeParams *p1) {
   size_t n_nodes = 0, n_roots = 0;
   if (cudaGraphGetNodes(graph, nullptr, &n_nodes) != cudaSuccess || cudaGraphGetRootNodes(graph, nullptr, &n_roots) != cudaSuccess ||
@@ -523,6 +516,18 @@ bool chain_ends(cudaGraph_t graph, cudaGraphNode_t *root, cudaGraphNode_t *leaf,
   return p0->kernelParams != nullptr && p1->kernelParams != nullptr;
 }
 
+
+namespace {
+
+void drop_graphs(Workspace &ws) {
+  for (CapturedGraph &g : ws.graphs) destroy_graph(g);
+  for (CapturedGraph &g : ws.req_graphs) destroy_graph(g);
+  ws.graphs.clear();
+  ws.seen.clear();
+  ws.req_graphs.clear();
+  ws.req_seen.clear();
+}
+
 // Capture one forward on `s` into an instantiated graph and find the two nodes that hold the I/O pointers.
 spu_status capture_forward(spu_replica *r, Workspace &ws, const int64_t *ids, const int64_t *mask, int batch, int seq,
                            float *out, cudaStream_t s, CapturedGraph *cg) {
@@ -549,7 +554,7 @@ spu_status capture_forward(spu_replica *r, Workspace &ws, const int64_t *ids, co
   cg->patchable = false;
   cudaGraphNode_t root = nullptr, leaf = nullptr;
   cudaKernelNodeParams p0{}, p1{};
-  if (!chain_ends(graph, &root, &leaf, &p0, &p1)) return SPU_OK;
+  if (!graph_chain_ends(graph, &root, &leaf, &p0, &p1)) return SPU_OK;
   if (p0.func != bert_embed_kernel_entry() || p1.func != layernorm_kernel_entry()) return SPU_OK;
   const int out_arg = (r->flags & SPU_OUTPUT_BF16) ? 5 : 4;
   // the captured parameters must be the pointers we are about to treat as patchable
@@ -566,12 +571,12 @@ spu_status capture_forward(spu_replica *r, Workspace &ws, const int64_t *ids, co
 // Point the instantiated graph at other I/O buffers (host-side only; launches already enqueued keep theirs).
 spu_status retarget_graph(CapturedGraph &g, const int64_t *ids, const int64_t *mask, float *out) {
   if (g.key.ids != ids || g.key.mask != mask) {
-    SPU_TRY(patch_node(g, g.first, 17, {{0, ids}, {1, mask}}));  // bert_embed_ln_kernel(ids, mask, ...)
+    SPU_TRY(graph_patch_node(g, g.first, 17, {{0, ids}, {1, mask}}));  // bert_embed_ln_kernel(ids, mask, ...)
     g.key.ids = ids;
     g.key.mask = mask;
   }
   if (g.key.out != out) {
-    SPU_TRY(patch_node(g, g.last, 11, {{g.out_arg, out}}));  // layernorm_kernel(..., out_f32 [4], out_bf16 [5], ...)
+    SPU_TRY(graph_patch_node(g, g.last, 11, {{g.out_arg, out}}));  // layernorm_kernel(..., out_f32 [4], out_bf16 [5], ...)
     g.key.out = out;
   }
   return SPU_OK;
@@ -793,11 +798,11 @@ extern "C" spu_status spu_bert_forward_requests_async(spu_replica *r, int32_t ws
     if (!same(g.key) || !g.patchable) continue;
     if (g.key.ids != want.ids || g.key.aux != want.aux || g.key.mask != want.mask) {
       // gather_pad_mask_kernel(src_ids, src_mask, len, ...)
-      SPU_TRY(patch_node(g, g.first, 7, {{0, want.ids}, {1, want.aux}, {2, want.mask}}));
+      SPU_TRY(graph_patch_node(g, g.first, 7, {{0, want.ids}, {1, want.aux}, {2, want.mask}}));
     }
     if (g.key.out != want.out || g.key.mask != want.mask) {
       // scatter_requests_kernel(src, len, seq, hidden, full_rows, dsts)
-      SPU_TRY(patch_node(g, g.last, 6, {{1, want.mask}, {5, want.out}}));
+      SPU_TRY(graph_patch_node(g, g.last, 6, {{1, want.mask}, {5, want.out}}));
     }
     g.key = want;
     g.tick = ++ws.graph_tick;
@@ -826,7 +831,7 @@ extern "C" spu_status spu_bert_forward_requests_async(spu_replica *r, int32_t ws
         SPU_CUDA_TRY(e);
       }
       cudaKernelNodeParams p0{}, p1{};
-      cg.patchable = chain_ends(graph, &cg.first, &cg.last, &p0, &p1) &&
+      cg.patchable = graph_chain_ends(graph, &cg.first, &cg.last, &p0, &p1) &&
                      p0.func == gather_pad_mask_kernel_entry() && p1.func == scatter_requests_kernel_entry();
       if (!cg.patchable) {  // cannot be retargeted: useless for a slot-cycling server
         SPU_CUDA_TRY(cudaGraphLaunch(cg.exec, s));

@@ -126,6 +126,15 @@ struct CapturedGraph {
   unsigned long long tick = 0;  // LRU stamp
 };
 
+// CUDA-graph helpers (replica.cu): find the single root / leaf kernel nodes of a captured chain; replace 8-byte
+// parameters of one of them in the instantiated graph (and its template); free a captured graph.
+constexpr size_t kMaxGraphs = 64;  // per workspace; least recently used goes first
+bool graph_chain_ends(cudaGraph_t graph, cudaGraphNode_t *root, cudaGraphNode_t *leaf, cudaKernelNodeParams *p0,
+                      cudaKernelNodeParams *p1);
+spu_status graph_patch_node(CapturedGraph &g, cudaGraphNode_t node, int n_args,
+                            std::initializer_list<std::pair<int, const void *>> changes);
+void destroy_graph(CapturedGraph &g);
+
 struct Workspace {
   float *x_f32 = nullptr;
   __nv_bfloat16 *x_bf16 = nullptr, *qkv = nullptr, *ctx = nullptr, *h = nullptr;

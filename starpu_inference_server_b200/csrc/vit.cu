@@ -23,6 +23,11 @@ struct VitWorkspace {
   float *logits_pad = nullptr;        // [B, classes_pad]
   GemmPlan patch_plan, head_plan;
   std::vector<VitLayerPlans> plans;
+  // SPU_FORWARD_AUTO_GRAPH: one captured forward per batch size; pixels / logits are parameters of the first
+  // (im2col) and last (logit slice) kernel and are patched per launch (key.ids = pixels, key.out = logits)
+  std::vector<CapturedGraph> graphs;
+  std::vector<int> seen_batches;
+  unsigned long long graph_tick = 0;
 };
 
 struct VitState {
@@ -130,7 +135,12 @@ vit_slice_logits_kernel(const float *__restrict__ padded, float *__restrict__ lo
   }
 }
 
-void vit_destroy(VitState *v) { delete v; }
+void vit_destroy(VitState *v) {
+  if (v != nullptr)
+    for (VitWorkspace &ws : v->ws)
+      for (CapturedGraph &g : ws.graphs) destroy_graph(g);
+  delete v;
+}
 
 spu_status vit_build(spu_replica *r, VitState *v, const float *const *t, int max_batch, int n_workspaces) {
   const spu_vit_desc &d = v->d;
@@ -304,7 +314,8 @@ extern "C" spu_status spu_vit_replica_create(const spu_vit_desc *desc, const flo
   SPU_REQUIRE((desc->channels * desc->patch * desc->patch) % 64 == 0, SPU_ERR_UNSUPPORTED,
               "vit_replica_create: C*P*P must be a multiple of 64");
   SPU_REQUIRE(max_batch > 0 && n_workspaces > 0, SPU_ERR_INVALID, "vit_replica_create: bad capacity");
-  SPU_REQUIRE(flags == SPU_PREC_BF16, SPU_ERR_UNSUPPORTED, "vit_replica_create: unsupported precision flag");
+  SPU_REQUIRE((flags & ~SPU_FORWARD_AUTO_GRAPH) == SPU_PREC_BF16, SPU_ERR_UNSUPPORTED,
+              "vit_replica_create: unsupported precision flag");
   for (int i = 0; i < n_tensors; ++i)
     SPU_REQUIRE(tensors[i] != nullptr, SPU_ERR_INVALID, "vit_replica_create: null weight tensor");
   SPU_REQUIRE(spu_device_is_sm100(device) == 1, SPU_ERR_UNSUPPORTED,
@@ -345,7 +356,69 @@ extern "C" spu_status spu_vit_forward_async(spu_replica *r, int32_t ws_idx, cons
   SPU_REQUIRE(batch <= r->max_batch, SPU_ERR_CAPACITY,
               "vit_forward: batch exceeds the workspace the replica was created with");
   SPU_REQUIRE((reinterpret_cast<uintptr_t>(pixels) & 15u) == 0, SPU_ERR_INVALID, "vit_forward: pixels must be 16-byte aligned");
-  return vit_enqueue(r, r->vit, r->vit->ws[ws_idx], pixels, batch, logits, as_stream(stream));
+  VitWorkspace &ws = r->vit->ws[ws_idx];
+  cudaStream_t s = as_stream(stream);
+  if ((r->flags & SPU_FORWARD_AUTO_GRAPH) == 0 || s == nullptr) return vit_enqueue(r, r->vit, ws, pixels, batch, logits, s);
+  // one graph per batch size, retargeted to the task's buffers (as the BERT forward, replica.cu)
+  for (CapturedGraph &g : ws.graphs) {
+    if (g.key.batch != batch) continue;
+    if (g.key.ids != pixels) {
+      SPU_TRY(graph_patch_node(g, g.first, 6, {{0, pixels}}));  // vit_im2col_kernel(pixels, ...)
+      g.key.ids = pixels;
+    }
+    if (g.key.out != logits) {
+      SPU_TRY(graph_patch_node(g, g.last, 5, {{1, logits}}));  // vit_slice_logits_kernel(logits_pad, logits, ...)
+      g.key.out = logits;
+    }
+    g.tick = ++ws.graph_tick;
+    SPU_CUDA_TRY(cudaGraphLaunch(g.exec, s));
+    return SPU_OK;
+  }
+  bool seen = false;
+  for (int b : ws.seen_batches) seen = seen || b == batch;
+  if (!seen) {  // first sighting: eager (sets kernel attributes, warms caches)
+    if (ws.seen_batches.size() < 4 * kMaxGraphs) ws.seen_batches.push_back(batch);
+    return vit_enqueue(r, r->vit, ws, pixels, batch, logits, s);
+  }
+  SPU_CUDA_TRY(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal));
+  spu_status st = vit_enqueue(r, r->vit, ws, pixels, batch, logits, s);
+  cudaGraph_t graph = nullptr;
+  cudaError_t e = cudaStreamEndCapture(s, &graph);
+  if (st != SPU_OK) {
+    if (graph) cudaGraphDestroy(graph);
+    return st;
+  }
+  SPU_CUDA_TRY(e);
+  CapturedGraph cg;
+  cg.key.ids = pixels;
+  cg.key.out = logits;
+  cg.key.batch = batch;
+  cg.graph = graph;
+  e = cudaGraphInstantiate(&cg.exec, graph, 0);
+  if (e != cudaSuccess) {
+    cudaGraphDestroy(graph);
+    SPU_CUDA_TRY(e);
+  }
+  cudaKernelNodeParams p0{}, p1{};
+  cg.patchable = graph_chain_ends(graph, &cg.first, &cg.last, &p0, &p1) &&
+                 p0.func == reinterpret_cast<const void *>(&vit_im2col_kernel) &&
+                 p1.func == reinterpret_cast<const void *>(&vit_slice_logits_kernel);
+  SPU_CUDA_TRY(cudaGraphLaunch(cg.exec, s));
+  if (!cg.patchable) {  // cannot follow the task's buffers: not worth keeping
+    cudaStreamSynchronize(s);
+    destroy_graph(cg);
+    return SPU_OK;
+  }
+  if (ws.graphs.size() >= kMaxGraphs) {
+    size_t lru = 0;
+    for (size_t i = 1; i < ws.graphs.size(); ++i)
+      if (ws.graphs[i].tick < ws.graphs[lru].tick) lru = i;
+    destroy_graph(ws.graphs[lru]);
+    ws.graphs.erase(ws.graphs.begin() + static_cast<long>(lru));
+  }
+  cg.tick = ++ws.graph_tick;
+  ws.graphs.push_back(cg);
+  return SPU_OK;
 }
 
 // Measurement hook (bench.py's roofline of config E): device ms per forward of the dense GEMMs alone -- `reps`

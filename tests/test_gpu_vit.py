@@ -133,3 +133,37 @@ def test_gemm_chain_hook_times_the_gemms_and_leaves_the_replica_usable(tiny):
     with pytest.raises(Exception):
         r.gemm_chain_ms(torch.from_numpy(x).cuda(), out, reps=2, stream=None)  # the default stream cannot capture
     assert np.array_equal(_run(r, x, 10), before)
+
+
+def test_vit_auto_graph_replays_and_follows_the_buffers(spu):
+    """SPU_FORWARD_AUTO_GRAPH on a ViT replica: eager on the first sighting of a batch size, captured on the second,
+    afterwards one graph per batch size whose pixel / logit pointers are patched per launch; bit-equal to eager."""
+    from oracle import vit_oracle as vo
+    from starpu_inference_server_b200.vit import VitReplica
+
+    w = vo.make_weights(vo.VIT_TINY, 0)
+    plain = VitReplica(w, max_batch=6, n_workspaces=1)
+    auto = VitReplica(w, max_batch=6, n_workspaces=1, flags=spu.SPU_PREC_BF16 | spu.SPU_FORWARD_AUTO_GRAPH)
+    s = torch.cuda.Stream()
+    xs = [torch.from_numpy(vo.make_inputs(vo.VIT_TINY, 6, 20 + k)).cuda() for k in range(3)]
+    outs = [torch.full((6, 10), float("nan"), device="cuda") for _ in range(3)]
+    ref = []
+    for x in xs:
+        o = torch.empty(6, 10, device="cuda")
+        plain.forward_async(x, o, stream=s)
+        ref.append(o)
+    for rnd in range(3):
+        for k in range(3):
+            outs[k].fill_(float("nan"))
+            auto.forward_async(xs[k], outs[k], stream=s)
+            s.synchronize()
+            assert torch.equal(outs[k], ref[k]), (rnd, k)
+    o4 = torch.empty(4, 10, device="cuda")  # another batch size: its own eager pass, then its own graph
+    r4 = torch.empty(4, 10, device="cuda")
+    plain.forward_async(xs[0][:4], r4, stream=s)
+    for _ in range(3):
+        auto.forward_async(xs[0][:4], o4, stream=s)
+        s.synchronize()
+        assert torch.equal(o4, r4)
+    plain.close()
+    auto.close()
