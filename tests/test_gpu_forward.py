@@ -32,7 +32,7 @@ def rel_err(got, ref):
 def check_top1(got, ref):
     # 100 % agreement on every token the fp32 reference decides by more than the margin;
     # the remaining near-ties (top-2 gap <= 1e-2, i.e. ~2 rms errors of ANY bf16-operand
-    # evaluation of this graph, tools/diag_forward.py) flip as often in a CPU bf16 emulation
+    # evaluation of this graph, tests/sweeps/diag_forward.py) flip as often in a CPU bf16 emulation
     # as here, so the strict figure is only bounded loosely.
     assert top1_agreement(got, ref, TOP1_MARGIN) == 1.0
     assert top1_agreement(got, ref, 0.0) >= 0.97
