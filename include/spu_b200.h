@@ -128,6 +128,41 @@ spu_status spu_bert_forward_async(spu_replica *r, int32_t ws_idx,
  * count changes from batch to batch, so there is no graph to replay). */
 spu_status spu_bert_forward_packed_async(spu_replica *r, int32_t ws_idx, const int64_t *ids, const int32_t *lens,
                                          int32_t batch, int32_t seq, float *out, void *stream);
+/* The same forward as spu_bert_forward_async, for a caller that has no workspace to name and no way to get one.
+ * (No counterpart in the reference: LibTorch allocates its activations from the caching allocator inside
+ * model->forward, and the reference never needed a path that cannot.)
+ *
+ * Who this is for.  spu_bert_replica_create sizes its workspaces once, at start-up, for the CUDA workers it was
+ * told about; after that, code running on the serving path must not obtain device memory any more: inside a
+ * StarPU codelet body a cudaMalloc / cudaFree stalls every stream of the device (all other workers wait) and takes
+ * memory StarPU's own accounting (STARPU_LIMIT_CUDA_MEM, its allocation cache) does not know about, and while any
+ * thread is capturing a stream into a CUDA graph an allocation call fails and breaks that capture.  A worker the
+ * replica was not sized for, a health probe, or a late warm-up of one more shape is in exactly that position: it
+ * holds a replica, input and output buffers, and nothing else.  This entry point gives it the forward anyway.
+ *
+ * How.  The activations live in ONE array of SPU_STATIC_SCRATCH_BYTES that is compiled into the library as a
+ * device global: every GPU that loads libspu_b200.so sets that much memory aside until the process exits, whether
+ * or not this function is ever called.  The call itself performs no cudaMalloc, cudaFree or any other allocating
+ * CUDA / library routine; it only enqueues the same kernels, with the same tiles, as spu_bert_forward_async, so
+ * `out` is bit-identical to that call's.  ids / mask / out are the caller's DEVICE buffers, as there.
+ *
+ * Limits.  bf16 replicas only (SPU_ERR_UNSUPPORTED for an FP8 replica).  With rows = batch*seq rounded up to a
+ * multiple of 128, the forward needs rows * (14*hidden + 2*ffn + 4) bytes; more than SPU_STATIC_SCRATCH_BYTES
+ * returns SPU_ERR_CAPACITY with the numbers in spu_last_error() and enqueues nothing.  For BERT-base that is 512
+ * tokens (e.g. 4 x 128 or 1 x 512).
+ *
+ * Sharing.  There is one array per GPU and every call on that GPU uses it, from any thread, stream or replica:
+ * two calls whose kernels can overlap on the device (different streams, or no ordering between them) race on the
+ * activations and both results are garbage -- order them on one stream or with events.  The array keeps whatever
+ * the previous call left in it; the forward does not depend on that (every buffer is written by its producer
+ * kernel before any consumer reads it; nothing is accumulated across calls), so no clearing pass is needed or run.
+ *
+ * First call.  The first call on each device looks the array's device address up (cudaGetSymbolAddress, with
+ * that device current) and remembers it; make that first call outside any stream capture, e.g. during warm-up. */
+#define SPU_STATIC_SCRATCH_BYTES (9u << 20) /* 9 MiB per GPU */
+spu_status spu_bert_forward_static_async(spu_replica *r, const int64_t *ids, const int64_t *mask, int32_t batch,
+                                         int32_t seq, float *out, void *stream);
+
 /* Rows of the replica's word-embedding table (0 for a non-BERT replica).  The embedding kernel clamps ids into
  * [0, vocab) for memory safety where LibTorch's embedding would raise; a host layer that wants the reference's
  * failure instead validates ids against this before submitting (core/task_runner.cpp does). */

@@ -117,6 +117,15 @@ class BertReplica:
                                                      capi.ptr(out), capi.stream_ptr(stream)))
         return out
 
+    def forward_static_async(self, ids, mask, out, stream=None):
+        """forward_async for a caller without a workspace: the activations go to the scratch array the library
+        holds on every GPU (capi.SPU_STATIC_SCRATCH_BYTES; BERT-base: batch*seq <= 512), nothing is allocated.
+        Calls on one GPU share that array: keep them ordered on the device."""
+        b, s = ids.shape
+        capi.check(capi.lib().spu_bert_forward_static_async(self._h, capi.ptr(ids), capi.ptr(mask), b, s,
+                                                            capi.ptr(out), capi.stream_ptr(stream)))
+        return out
+
     def forward_packed_async(self, ids, lens, out, ws: int = 0, stream=None, compact: bool = False):
         """Right-padded batch whose true lengths are known on the host: ids int64 CUDA [B,S], lens = B host ints.
         The encoder runs on sum(lens) tokens; out [B,S,hidden] gets zeros behind each length -- or, with

@@ -20,12 +20,13 @@ SPU_FORWARD_AUTO_GRAPH = 1 << 16  # capture a CUDA graph on the second sighting 
 SPU_OUTPUT_BF16 = 1 << 18  # output0 is bf16 [B,S,H] (response path)
 SPU_LN_FUSED = 1 << 19  # residual + LayerNorm in the N = hidden GEMM epilogues
 SPU_REQUEST_IO = 1 << 17  # allocate the staging spu_bert_forward_requests_async needs
+SPU_STATIC_SCRATCH_BYTES = 9 << 20  # per-GPU scratch array of spu_bert_forward_static_async
 FP8_GEMM_QKV, FP8_GEMM_OUT, FP8_GEMM_FFN1, FP8_GEMM_FFN2, FP8_GEMM_ALL = 1, 2, 4, 8, 15
 STAGE_NAMES = ["embed_ln", "gemm_qkv", "attention", "gemm_attn_out", "ln1", "gemm_ffn1", "gemm_ffn2", "ln2"]
 
 # every symbol include/spu_b200.h declares (checked by tests/test_capi_symbols.py)
 SYMBOLS = [
-    "spu_bert_replica_create", "spu_replica_destroy", "spu_bert_forward_async",
+    "spu_bert_replica_create", "spu_replica_destroy", "spu_bert_forward_async", "spu_bert_forward_static_async",
     "spu_bert_forward_launch_count", "spu_bert_forward_requests_async", "spu_bert_forward_capture", "spu_bert_forward_profiled", "spu_gather_pad_mask_async",
     "spu_gather_segments_async", "spu_scatter_segments_async", "spu_gemm_bf16_async", "spu_gemm_bf16_cfg_async",
     "spu_attention_async", "spu_attention_cfg_async", "spu_layernorm_async", "spu_bert_embed_async", "spu_affine_f32_async",
@@ -76,6 +77,8 @@ def lib():
     L.spu_replica_destroy.argtypes = [vp]
     L.spu_bert_forward_async.argtypes = [vp, i32, vp, vp, i32, i32, vp, vp]
     L.spu_bert_forward_capture.argtypes = [vp, i32, vp, vp, i32, i32, vp, vp]
+    L.spu_bert_forward_static_async.argtypes = [vp, vp, vp, i32, i32, vp, vp]
+    L.spu_bert_forward_static_async.restype = i32
     L.spu_bert_forward_profiled.argtypes = [vp, i32, vp, vp, i32, i32, vp, vp, C.POINTER(f32)]
     L.spu_bert_forward_packed_async.argtypes = [vp, i32, vp, vp, i32, i32, vp, vp]
     L.spu_bert_forward_packed_async.restype = i32

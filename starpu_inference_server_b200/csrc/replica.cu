@@ -730,6 +730,109 @@ extern "C" spu_status spu_bert_forward_async(spu_replica *r, int32_t ws_idx, con
   return enqueue_forward(r, ws, ids, mask, batch, seq, out, as_stream(stream));
 }
 
+// ---- Forward on scratch the library itself holds (no device allocation anywhere on the path) --------------------
+// The activations of one forward (residual stream, QKV, attention context, FFN intermediate, mask bias) normally
+// live in a workspace that spu_bert_replica_create cudaMalloc-ed.  This variant lays the same six buffers out in
+// the array below, which is part of the loaded module on every GPU from the first CUDA call of the process until
+// exit.  On the host, `g_static_scratch` is only the handle cudaGetSymbolAddress understands -- never a device
+// address -- so static_scratch_base() asks the runtime for the real address once per device and caches it.
+static __device__ __align__(256) unsigned char g_static_scratch[SPU_STATIC_SCRATCH_BYTES];
+
+namespace {
+constexpr int kStaticMaxDevices = 64;
+std::mutex g_static_mu;
+unsigned char *g_static_base[kStaticMaxDevices] = {};  // device address of g_static_scratch, per CUDA device
+
+// Caller has made `device` current.
+spu_status static_scratch_base(int device, unsigned char **base) {
+  SPU_REQUIRE(device >= 0 && device < kStaticMaxDevices, SPU_ERR_INVALID, "forward_static: device index out of range");
+  std::lock_guard<std::mutex> lock(g_static_mu);
+  if (g_static_base[device] == nullptr) {
+    void *p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&p, g_static_scratch);
+    if (e != cudaSuccess || p == nullptr) {
+      set_error(std::string("forward_static: cudaGetSymbolAddress(g_static_scratch): ") +
+                (e != cudaSuccess ? cudaGetErrorString(e) : "null address"));
+      return SPU_ERR_CUDA;
+    }
+    SPU_REQUIRE((reinterpret_cast<uintptr_t>(p) & 255u) == 0, SPU_ERR_CUDA, "forward_static: scratch is not 256-byte aligned");
+    g_static_base[device] = static_cast<unsigned char *>(p);
+  }
+  *base = g_static_base[device];
+  return SPU_OK;
+}
+
+// rows is a multiple of 128, so every buffer below is a whole number of 256-byte units
+size_t static_scratch_need(size_t rows, size_t H, size_t F) { return rows * (14 * H + 2 * F + 4); }
+
+template <typename T>
+T *carve(unsigned char *base, size_t *off, size_t count) {
+  T *p = reinterpret_cast<T *>(base + *off);
+  *off += (count * sizeof(T) + 255u) & ~static_cast<size_t>(255u);
+  return p;
+}
+}  // namespace
+
+extern "C" spu_status spu_bert_forward_static_async(spu_replica *r, const int64_t *ids, const int64_t *mask,
+                                                    int32_t batch, int32_t seq, float *out, void *stream) {
+  SPU_REQUIRE(r != nullptr, SPU_ERR_INVALID, "forward_static: null replica");
+  SPU_REQUIRE(r->kind == 0, SPU_ERR_INVALID, "forward_static: not a BERT replica");
+  SPU_REQUIRE(ids && mask && out, SPU_ERR_INVALID, "forward_static: null buffer");
+  SPU_REQUIRE((r->flags & SPU_PREC_FP8_E4M3) == 0, SPU_ERR_UNSUPPORTED,
+              "forward_static: bf16 replicas only (the FP8 operand buffers are not part of the static scratch)");
+  SPU_REQUIRE(batch >= 1 && seq >= 1, SPU_ERR_INVALID, "forward_static: empty batch");
+  SPU_REQUIRE(seq <= r->desc.max_pos, SPU_ERR_CAPACITY, "forward_static: seq exceeds max_position_embeddings");
+  const spu_bert_desc &d = r->desc;
+  const size_t H = d.hidden, F = d.ffn;
+  // same row rounding as a replica workspace (cap_rows): whole 128-row tiles
+  const size_t rows = (static_cast<size_t>(batch) * static_cast<size_t>(seq) + 127u) / 128u * 128u;
+  const size_t need = static_scratch_need(rows, H, F);
+  if (need > SPU_STATIC_SCRATCH_BYTES) {
+    set_error("forward_static: batch*seq = " + std::to_string(static_cast<long long>(batch) * seq) + " tokens of hidden " +
+              std::to_string(d.hidden) + " / ffn " + std::to_string(d.ffn) + " need " + std::to_string(need) +
+              " bytes of scratch, the static array holds SPU_STATIC_SCRATCH_BYTES = " +
+              std::to_string(static_cast<size_t>(SPU_STATIC_SCRATCH_BYTES)) +
+              " (use spu_bert_forward_async on a replica workspace for larger batches)");
+    return SPU_ERR_CAPACITY;
+  }
+  DeviceGuard guard(r->device);
+  unsigned char *base = nullptr;
+  SPU_TRY(static_scratch_base(r->device, &base));
+
+  // A workspace whose buffers are slices of the static array.  Its GEMM plans (host-side tensor-map encodes of the
+  // weight matrices; the kernels take them by value) are rebuilt on every call: this path trades ~100 us of host
+  // time for holding no per-replica state, so a destroyed replica can never leave a stale plan behind.
+  Workspace ws;
+  size_t off = 0;
+  ws.x_f32 = carve<float>(base, &off, rows * H);
+  ws.x_bf16 = carve<__nv_bfloat16>(base, &off, rows * H);
+  ws.qkv = carve<__nv_bfloat16>(base, &off, rows * 3 * H);
+  ws.ctx = carve<__nv_bfloat16>(base, &off, rows * H);
+  ws.h = carve<__nv_bfloat16>(base, &off, rows * F);
+  ws.mask_bias = carve<float>(base, &off, rows);
+  SPU_REQUIRE(off == need && off <= SPU_STATIC_SCRATCH_BYTES, SPU_ERR_INVALID, "forward_static: layout does not match its size formula");
+  ws.plans.resize(d.layers);
+  const int R = static_cast<int>(rows);
+  for (int l = 0; l < d.layers; ++l) {
+    const LayerWeights &w = r->layers[l];
+    LayerPlans &p = ws.plans[l];
+    SPU_TRY(gemm_make_plan(&p.qkv, ws.x_bf16, R, w.w_qkv, 3 * d.hidden, d.hidden, SPU_EPI_BIAS, GemmIn::BF16));
+    SPU_TRY(gemm_make_plan(&p.attn_out, ws.ctx, R, w.w_o, d.hidden, d.hidden, SPU_EPI_BIAS_RESID, GemmIn::BF16));
+    SPU_TRY(gemm_make_plan(&p.ffn1, ws.x_bf16, R, w.w_1, d.ffn, d.hidden, SPU_EPI_BIAS_GELU, GemmIn::BF16));
+    SPU_TRY(gemm_make_plan(&p.ffn2, ws.h, R, w.w_2, d.hidden, d.ffn, SPU_EPI_BIAS_RESID, GemmIn::BF16));
+    if (r->ln_fused) {
+      SPU_TRY(gemm_make_plan(&p.attn_out_ln, ws.ctx, R, w.w_o, d.hidden, d.hidden, kEpiBiasResidLN, GemmIn::BF16));
+      SPU_TRY(gemm_make_plan(&p.ffn2_ln, ws.h, R, w.w_2, d.hidden, d.ffn, kEpiBiasResidLN, GemmIn::BF16));
+    }
+    // the same measured tiles a replica workspace would use, so both paths launch identical kernels
+    for (GemmPlan *g : {&p.qkv, &p.attn_out, &p.ffn1, &p.ffn2, &p.attn_out_ln, &p.ffn2_ln}) g->tuned = &r->tuned;
+  }
+  // Nothing in the forward relies on scratch that starts at zero: the embedding kernel writes x / mask_bias before
+  // anything reads them and every later buffer is fully produced by the kernel ahead of its consumer, so what the
+  // previous call left behind is overwritten, never accumulated into.
+  return enqueue_forward(r, ws, ids, mask, batch, seq, out, as_stream(stream));
+}
+
 extern "C" int32_t spu_bert_vocab_size(const spu_replica *r) {
   return (r != nullptr && r->kind == 0) ? r->desc.vocab : 0;
 }
