@@ -10,7 +10,7 @@ workload (default B = configs[1], the one `metric` is quoted on):
   A  BERT-base seq 128 batch 1                          (configs[0]: the reference's CPU-runnable case)
   B  BERT-base seq 128 dynamic batch at its cap 32, bf16 (configs[1])
   C  BERT-base variable-length 16-512 padded+masked, batch 64 (configs[2])
-  D  BERT-base seq 128 batch 256, FP8 E4M3 per-tensor scales (configs[3]; the plan that passes the 6e-2 gate)
+  D  BERT-base seq 128 batch 256, FP8 E4M3 per-tensor scales (configs[3]; default plan: inside the 6e-2 max-rel gate, strict top-1 below the 99.5 % gate -> parity.gate_ok false)
   E  ViT-L/16 224x224 batch 64, patch-embed as GEMM, bf16 (configs[4])
 N>1: one process per GPU (torchrun), one weight replica each, requests are independent -> weak scaling, no
 collective on the data path (torch.distributed is used only for the timing barrier / max-over-ranks).
@@ -285,6 +285,13 @@ def parity_block(got, ref, precision, live=None):
            "rows_outside_tolerance_band": int(band.sum()),
            "gate": {"max_rel": tol, "top1": top1_gate},
            "gate_max_rel_ok": bool(diff.max() / max_ref <= tol)}
+    # per-row normalisation beside the global one: ||d_row||inf / ||ref_row||inf, max over rows
+    row_ref = np.maximum(np.abs(ref).max(axis=-1), 1e-30)
+    out["max_rel_per_row"] = float((diff.max(axis=-1) / row_ref).max())
+    # BASELINE's gate as written: BOTH halves, top-1 on the STRICT figure (no margin, no band).  The band / margin
+    # figures above explain a miss; they do not turn it into a pass.
+    out["gate_top1_ok"] = bool(out["top1_strict"] >= top1_gate)
+    out["gate_ok"] = bool(out["gate_max_rel_ok"] and out["gate_top1_ok"])
     return out
 
 
