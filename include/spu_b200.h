@@ -219,6 +219,21 @@ spu_status spu_bert_forward_requests_async(spu_replica *r, int32_t ws_idx,
                                            float *const *dsts, int32_t full_rows,
                                            void *stream);
 
+/* The same call with the token ids CHECKED against the embedding table, which is what LibTorch's embedding does on
+ * the reference path (an id outside [0, vocab) raises inside model->forward, src/core/starpu_setup.cpp:610, and the
+ * whole job fails).  The host cannot do that check here without reading every request (the point of this path is
+ * that it does not), so the gather kernel does: `status` is a DEVICE int32 the caller reads once the stream has
+ * reached this call's end -- 0 when every live id was inside the table, else 1 + the index of a request row that
+ * carried one outside (the largest such row).  The forward still runs (the embedding clamps, nothing reads out
+ * of bounds) and the responses of such a batch are written but meaningless: fail the batch.  status == NULL is
+ * spu_bert_forward_requests_async. */
+spu_status spu_bert_forward_requests_checked_async(spu_replica *r, int32_t ws_idx,
+                                                   const int64_t *const *src_ids,
+                                                   const int64_t *const *src_mask,
+                                                   const int32_t *len, int32_t n_req, int32_t seq,
+                                                   float *const *dsts, int32_t full_rows, int32_t *status,
+                                                   void *stream);
+
 /* Capture the forward of (batch, seq) on ws_idx into a CUDA graph (warm-up hook,
  * src/core/warmup.cpp:225-299) so later spu_bert_forward_async calls with the
  * same (ws_idx, batch, seq, ids, mask, out) pointers replay it. */

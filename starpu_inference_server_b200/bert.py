@@ -138,11 +138,19 @@ class BertReplica:
         return out
 
     def forward_requests_async(self, src_ids_table, src_mask_table, len_dev, n_req: int, seq: int, dst_table,
-                               full_rows: bool = True, ws: int = 0, stream=None):
+                               full_rows: bool = True, ws: int = 0, stream=None, status=None):
         """Stages 1-4 on per-request buffers (replica created with capi.SPU_REQUEST_IO).  The tables are int64 CUDA
-        tensors of device-visible addresses (src_mask_table may be None), len_dev an int32 CUDA tensor."""
+        tensors of device-visible addresses (src_mask_table may be None), len_dev an int32 CUDA tensor.  `status`:
+        optional int32 CUDA tensor of one element that receives 0, or 1 + a request row whose token ids leave the
+        embedding table (spu_bert_forward_requests_checked_async)."""
+        mask_tab = None if src_mask_table is None else capi.ptr(src_mask_table)
+        if status is not None:
+            capi.check(capi.lib().spu_bert_forward_requests_checked_async(
+                self._h, ws, capi.ptr(src_ids_table), mask_tab, capi.ptr(len_dev), n_req, seq, capi.ptr(dst_table),
+                1 if full_rows else 0, capi.ptr(status), capi.stream_ptr(stream)))
+            return
         capi.check(capi.lib().spu_bert_forward_requests_async(
-            self._h, ws, capi.ptr(src_ids_table), None if src_mask_table is None else capi.ptr(src_mask_table),
+            self._h, ws, capi.ptr(src_ids_table), mask_tab,
             capi.ptr(len_dev), n_req, seq, capi.ptr(dst_table), 1 if full_rows else 0, capi.stream_ptr(stream)))
 
     def forward_profiled(self, ids, mask, out, ws: int = 0, stream=None):

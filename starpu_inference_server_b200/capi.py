@@ -27,7 +27,7 @@ STAGE_NAMES = ["embed_ln", "gemm_qkv", "attention", "gemm_attn_out", "ln1", "gem
 # every symbol include/spu_b200.h declares (checked by tests/test_capi_symbols.py)
 SYMBOLS = [
     "spu_bert_replica_create", "spu_replica_destroy", "spu_bert_forward_async", "spu_bert_forward_static_async",
-    "spu_bert_forward_launch_count", "spu_bert_forward_requests_async", "spu_bert_forward_capture", "spu_bert_forward_profiled", "spu_gather_pad_mask_async",
+    "spu_bert_forward_launch_count", "spu_bert_forward_requests_async", "spu_bert_forward_requests_checked_async", "spu_bert_forward_capture", "spu_bert_forward_profiled", "spu_gather_pad_mask_async",
     "spu_gather_segments_async", "spu_scatter_segments_async", "spu_gemm_bf16_async", "spu_gemm_bf16_cfg_async",
     "spu_attention_async", "spu_attention_cfg_async", "spu_layernorm_async", "spu_bert_embed_async", "spu_affine_f32_async",
     "spu_last_error", "spu_abi_version", "spu_device_count", "spu_device_is_sm100",
@@ -105,6 +105,8 @@ def lib():
     L.spu_gemm_bf16_cfg_async.argtypes = [vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, vp]
     L.spu_attention_async.argtypes = [vp, vp, vp, i32, i32, i32, vp]
     L.spu_bert_forward_requests_async.argtypes = [vp, i32, vp, vp, vp, i32, i32, vp, i32, vp]
+    L.spu_bert_forward_requests_checked_async.argtypes = [vp, i32, vp, vp, vp, i32, i32, vp, i32, vp, vp]
+    L.spu_bert_forward_requests_checked_async.restype = i32
     L.spu_attention_cfg_async.argtypes = [vp, vp, vp, i32, i32, i32, i32, i32, f32, vp]
     L.spu_layernorm_async.argtypes = [vp, vp, vp, f32, vp, vp, i32, i32, vp]
     L.spu_bert_embed_async.argtypes = [vp, vp, vp, vp, vp, vp, vp, f32, i32, vp, vp, vp, i32, i32, i32, vp]

@@ -183,11 +183,16 @@ void run_inference(InferenceParams *params, StarpuBufferSpan buffers, int device
         require_bytes(buffers[0], io.table_bytes, "Input");
         const auto base = static_cast<uintptr_t>(buffers[0]->ptr);
         const int ws = workspace_for_this_thread(model);
-        check_spu(spu_bert_forward_requests_async(
+        // The responses bypass the STARPU_W buffer on this path; its first word carries the task's verdict on the
+        // token ids instead (0 = all inside the embedding table).  StarPU brings it to the host with the handle
+        // like any output, and the output callback fails the batch on a non-zero word, as the reference's job
+        // fails when LibTorch's embedding raises (task_runner.cpp: finalize).
+        int32_t *status = buffer_byte_size(buffers[2]) >= sizeof(int32_t) ? reinterpret_cast<int32_t *>(buffers[2]->ptr) : nullptr;
+        check_spu(spu_bert_forward_requests_checked_async(
             model->replica, ws, reinterpret_cast<const int64_t *const *>(base),
             reinterpret_cast<const int64_t *const *>(base + io.off_mask), reinterpret_cast<const int32_t *>(base + io.off_len),
             static_cast<int32_t>(B), static_cast<int32_t>(S), reinterpret_cast<float *const *>(base + io.off_dst),
-            io.full_rows ? 1 : 0, stream));
+            io.full_rows ? 1 : 0, status, stream));
         break;
       }
       const size_t in_bytes = static_cast<size_t>(B) * static_cast<size_t>(S) * sizeof(int64_t);

@@ -525,6 +525,13 @@ void TaskRunner::finalize(CallbackContext *ctx) {
     aggregated.push_back(std::move(t));
   }
   ctx->timing.callback_end_time = MonotonicClock::now();
+  // device_visible_requests: nobody on the host read the token ids, the gather kernel checked them against the
+  // embedding table and the codelet routed its finding into the first word of output 0 (inference_codelet.cpp).
+  // A non-zero word fails the whole batch, which is what the reference does when LibTorch's embedding raises.
+  int32_t bad_id_row = 0;
+  if (codelet_ok && all_acquired && ctx->request_io && !bases.empty() && bases[0] != nullptr &&
+      r->output_pool_->per_sample_numel(0) * element_size(r->output_pool_->tensor_type(0)) >= sizeof(int32_t))
+    std::memcpy(&bad_id_row, bases[0], sizeof(int32_t));
   // propagate_completion_to_sub_jobs (result_dispatcher_component.cpp:678-739)
   int64_t offset = 0;
   std::vector<std::function<void()>> completions;
@@ -552,6 +559,11 @@ void TaskRunner::finalize(CallbackContext *ctx) {
       res.rows = b;
       res.ok = true;
       offset += b * L;  // `offset` counts TOKENS on this path
+    } else if (codelet_ok && all_acquired && ctx->request_io && bad_id_row != 0) {
+      res.ok = false;
+      res.error = "token id of batch row " + std::to_string(bad_id_row - 1) + " is outside the embedding table" +
+                  (r->model_.id_vocab > 0 ? " [0, " + std::to_string(r->model_.id_vocab) + ")" : std::string());
+      offset += job->batch_size();
     } else if (codelet_ok && all_acquired && ctx->request_io) {
       // the codelet's scatter kernel already wrote the response into the request's own buffers
       for (size_t o = 0; o < aggregated.size(); ++o) {

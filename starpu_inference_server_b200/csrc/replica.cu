@@ -95,6 +95,8 @@ spu_status build(spu_replica *r, const float *const *t) {
       SPU_TRY(dev_alloc(r, &ws.req_ids, rows));
       SPU_TRY(dev_alloc(r, &ws.req_mask, rows));
       SPU_TRY(dev_alloc(r, &ws.req_out, rows * H));
+      SPU_TRY(dev_alloc(r, &ws.req_err, 1));
+      SPU_CUDA_TRY(cudaMemset(ws.req_err, 0, sizeof(int32_t)));
     }
     if (r->flags & SPU_PREC_FP8_E4M3) {
       SPU_TRY(dev_alloc(r, &ws.x_q, rows * H));
@@ -875,6 +877,15 @@ extern "C" spu_status spu_bert_forward_requests_async(spu_replica *r, int32_t ws
                                                       const int64_t *const *src_mask, const int32_t *len,
                                                       int32_t n_req, int32_t seq, float *const *dsts,
                                                       int32_t full_rows, void *stream) {
+  return spu_bert_forward_requests_checked_async(r, ws_idx, src_ids, src_mask, len, n_req, seq, dsts, full_rows, nullptr,
+                                                 stream);
+}
+
+extern "C" spu_status spu_bert_forward_requests_checked_async(spu_replica *r, int32_t ws_idx,
+                                                              const int64_t *const *src_ids,
+                                                              const int64_t *const *src_mask, const int32_t *len,
+                                                              int32_t n_req, int32_t seq, float *const *dsts,
+                                                              int32_t full_rows, int32_t *status, void *stream) {
   SPU_REQUIRE(r != nullptr && r->kind == 0, SPU_ERR_INVALID, "forward_requests: not a BERT replica");
   SPU_REQUIRE((r->flags & SPU_REQUEST_IO) != 0, SPU_ERR_UNSUPPORTED,
               "forward_requests: replica was created without SPU_REQUEST_IO");
@@ -887,25 +898,33 @@ extern "C" spu_status spu_bert_forward_requests_async(spu_replica *r, int32_t ws
   SPU_TRY(check_forward_args(r, ws_idx, ws.req_ids, ws.req_mask, n_req, seq, ws.req_out));
   cudaStream_t s = as_stream(stream);
   auto enqueue = [&]() -> spu_status {
-    SPU_TRY(spu_gather_pad_mask_async(src_ids, src_mask, len, n_req, seq, 0, ws.req_ids, ws.req_mask, stream));
+    // without a status word nobody would read (or re-arm) the error word: the gather then skips the id check
+    SPU_TRY(gather_pad_mask_launch(src_ids, src_mask, len, n_req, seq, 0, ws.req_ids, ws.req_mask, r->desc.vocab,
+                                   status != nullptr ? ws.req_err : nullptr, s));
     SPU_TRY(enqueue_forward(r, ws, ws.req_ids, ws.req_mask, n_req, seq, ws.req_out, s));
-    return scatter_requests_launch(ws.req_out, len, n_req, seq, r->desc.hidden, full_rows != 0, dsts, s);
+    return scatter_requests_launch(ws.req_out, len, n_req, seq, r->desc.hidden, full_rows != 0, dsts, s,
+                                   status != nullptr ? ws.req_err : nullptr, status);
   };
   // one graph per (n_req, seq, full_rows): the tables' addresses (they live in whatever slot the task uses) are
   // parameters of the first kernel (gather) and the last one (scatter), patched per launch
   GraphKey want{src_ids, len, dsts, n_req, seq};
   want.aux = src_mask;
   want.full_rows = full_rows != 0 ? 1 : 0;
-  auto same = [&](const GraphKey &k) { return k.same_shape(n_req, seq) && k.full_rows == want.full_rows; };
+  want.status = status;
+  // a graph captured with the id check serves only checked calls (its gather node holds the error word) and vice versa
+  auto same = [&](const GraphKey &k) {
+    return k.same_shape(n_req, seq) && k.full_rows == want.full_rows && (k.status != nullptr) == (status != nullptr);
+  };
   for (CapturedGraph &g : ws.req_graphs) {
     if (!same(g.key) || !g.patchable) continue;
     if (g.key.ids != want.ids || g.key.aux != want.aux || g.key.mask != want.mask) {
       // gather_pad_mask_kernel(src_ids, src_mask, len, ...)
-      SPU_TRY(graph_patch_node(g, g.first, 7, {{0, want.ids}, {1, want.aux}, {2, want.mask}}));
+      SPU_TRY(graph_patch_node(g, g.first, kGatherKernelArgs, {{0, want.ids}, {1, want.aux}, {2, want.mask}}));
     }
-    if (g.key.out != want.out || g.key.mask != want.mask) {
-      // scatter_requests_kernel(src, len, seq, hidden, full_rows, dsts)
-      SPU_TRY(graph_patch_node(g, g.last, 6, {{1, want.mask}, {5, want.out}}));
+    if (g.key.out != want.out || g.key.mask != want.mask || g.key.status != want.status) {
+      // scatter_requests_kernel(src, len, seq, hidden, full_rows, dsts, err, status)
+      SPU_TRY(graph_patch_node(g, g.last, kScatterKernelArgs,
+                               {{kScatterArgLen, want.mask}, {kScatterArgDsts, want.out}, {kScatterArgStatus, want.status}}));
     }
     g.key = want;
     g.tick = ++ws.graph_tick;

@@ -51,8 +51,20 @@ const void *scatter_requests_kernel_entry();
 const void *bert_embed_kernel_entry();
 const void *layernorm_kernel_entry();
 // request i <- rows [i*seq, i*seq + (full_rows ? seq : len[i])) of src [n_req*seq, hidden]
+// err (may be null): the word the gather kernel reported into; status (may be null): where this task's finding
+// goes (0 = every token id inside the embedding table, else 1 + a row that carried one outside); err is re-armed
 spu_status scatter_requests_launch(const float *src, const int32_t *len, int n_req, int seq, int hidden,
-                                   bool full_rows, float *const *dsts, cudaStream_t stream);
+                                   bool full_rows, float *const *dsts, cudaStream_t stream, int32_t *err = nullptr,
+                                   int32_t *status = nullptr);
+// spu_gather_pad_mask_async plus the id check: err != null -> atomicMax(err, row + 1) for a live id outside [0, vocab)
+spu_status gather_pad_mask_launch(const int64_t *const *src_ids, const int64_t *const *src_mask, const int32_t *len,
+                                  int n_req, int seq, int64_t pad_id, int64_t *ids_out, int64_t *mask_out,
+                                  int64_t vocab, int32_t *err, cudaStream_t stream);
+// parameter counts / positions of the two kernels whose arguments replica.cu patches in instantiated graphs
+// (rowops.cu: gather_pad_mask_kernel(src_ids, src_mask, len, seq, pad_id, ids_out, mask_out, vocab, err);
+//  scatter_requests_kernel(src, len, seq, hidden, full_rows, dsts, err, status))
+constexpr int kGatherKernelArgs = 9, kScatterKernelArgs = 8;
+constexpr int kScatterArgLen = 1, kScatterArgDsts = 5, kScatterArgStatus = 7;
 // e4m3 = sat(in * inv_scale); exactly one of in_f32 / in_bf16 is non-null; n % 4 == 0
 spu_status quantize_e4m3_launch(const float *in_f32, const void *in_bf16, void *out, uint64_t n,
                                 float inv_scale, cudaStream_t stream);
@@ -108,6 +120,7 @@ struct GraphKey {
   const void *ids = nullptr, *mask = nullptr, *out = nullptr;  // the pointers the graph currently holds
   int batch = 0, seq = 0;
   const void *aux = nullptr;  // requests path: the source-mask table
+  const void *status = nullptr;  // requests path: the task's status word
   int full_rows = 0;          // requests path
   bool same_shape(int b, int s) const { return batch == b && seq == s; }
   bool operator==(const GraphKey &o) const {
@@ -144,6 +157,7 @@ struct Workspace {
   // spu_bert_forward_requests_async (stage 1 writes, stage 4 reads)
   int64_t *req_ids = nullptr, *req_mask = nullptr;
   float *req_out = nullptr;
+  int32_t *req_err = nullptr;  // requests path: 1 + a row whose token id lies outside the table (0 = none), per task
   int32_t *cu_seqlens = nullptr;  // packed forward: [kMaxPackedBatch + 1]
   std::vector<LayerPlans> plans;
   std::vector<LayerPlans> plans8;

@@ -262,7 +262,8 @@ __global__ void __launch_bounds__(256)
 gather_pad_mask_kernel(const int64_t *const *__restrict__ src_ids,
                        const int64_t *const *__restrict__ src_mask,
                        const int32_t *__restrict__ len, int seq, int64_t pad_id,
-                       int64_t *__restrict__ ids_out, int64_t *__restrict__ mask_out) {
+                       int64_t *__restrict__ ids_out, int64_t *__restrict__ mask_out, int64_t vocab,
+                       int32_t *__restrict__ err) {
   const int r = blockIdx.y;
   const int L = len[r];
   const int64_t *sid = src_ids[r];
@@ -275,6 +276,9 @@ gather_pad_mask_kernel(const int64_t *const *__restrict__ src_ids,
     const int64_t i1 = in1 ? sid[t + 1] : pad_id;
     const int64_t m0 = in0 ? (smk != nullptr ? smk[t] : 1) : 0;
     const int64_t m1 = in1 ? (smk != nullptr ? smk[t + 1] : 1) : 0;
+    // err != nullptr: a token id outside the embedding table is REPORTED (row + 1, largest such row wins), where
+    // LibTorch's embedding would raise; the embedding kernel still clamps it, so nothing reads out of bounds
+    if (err != nullptr && ((in0 && (i0 < 0 || i0 >= vocab)) || (in1 && (i1 < 0 || i1 >= vocab)))) atomicMax(err, r + 1);
     if (vec) {
       *reinterpret_cast<longlong2 *>(ids_out + row + t) = make_longlong2(i0, i1);
       *reinterpret_cast<longlong2 *>(mask_out + row + t) = make_longlong2(m0, m1);
@@ -332,8 +336,15 @@ segcopy_kernel(const void *const *__restrict__ srcs, const uint8_t *src_base,
 // 16-byte streaming loads in flight per thread (the output is read once, written once).
 __global__ void __launch_bounds__(256)
 scatter_requests_kernel(const float *__restrict__ src, const int32_t *__restrict__ len, int seq, int hidden,
-                        int full_rows, float *const *__restrict__ dsts) {
+                        int full_rows, float *const *__restrict__ dsts, int32_t *__restrict__ err,
+                        int32_t *__restrict__ status) {
   const int i = blockIdx.y;
+  // hand the gather kernel's finding (0 = every id inside the table) to this task's status word and re-arm the
+  // workspace's error word for the next task on this stream
+  if (status != nullptr && blockIdx.x == 0 && i == 0 && threadIdx.x == 0) {
+    *status = err != nullptr ? *err : 0;
+    if (err != nullptr) *err = 0;
+  }
   const int rows = full_rows ? seq : min(max(len[i], 0), seq);
   const float *s = src + static_cast<size_t>(i) * seq * hidden;
   float *d = dsts[i];
@@ -473,7 +484,8 @@ spu_status quantize_e4m3_launch(const float *in_f32, const void *in_bf16, void *
 }
 
 spu_status scatter_requests_launch(const float *src, const int32_t *len, int n_req, int seq, int hidden,
-                                   bool full_rows, float *const *dsts, cudaStream_t stream) {
+                                   bool full_rows, float *const *dsts, cudaStream_t stream, int32_t *err,
+                                   int32_t *status) {
   SPU_REQUIRE(src && len && dsts, SPU_ERR_INVALID, "scatter_requests: null argument");
   SPU_REQUIRE(n_req > 0 && n_req <= 65535 && seq > 0 && hidden > 0 && hidden % 4 == 0, SPU_ERR_INVALID,
               "scatter_requests: bad shape");
@@ -487,7 +499,7 @@ spu_status scatter_requests_launch(const float *src, const int32_t *len, int n_r
   }();
   const int per_req = total / n_req > 0 ? (total / n_req > kSegBlocksPerSegment ? kSegBlocksPerSegment : total / n_req) : 1;
   dim3 grid(per_req, n_req);
-  scatter_requests_kernel<<<grid, 256, 0, stream>>>(src, len, seq, hidden, full_rows ? 1 : 0, dsts);
+  scatter_requests_kernel<<<grid, 256, 0, stream>>>(src, len, seq, hidden, full_rows ? 1 : 0, dsts, err, status);
   SPU_CUDA_TRY(cudaGetLastError());
   return SPU_OK;
 }
@@ -508,19 +520,27 @@ spu_status amax_launch(const float *in_f32, const void *in_bf16, uint64_t n, flo
 
 using namespace spu;
 
+namespace spu {
+spu_status gather_pad_mask_launch(const int64_t *const *src_ids, const int64_t *const *src_mask, const int32_t *len,
+                                  int n_req, int seq, int64_t pad_id, int64_t *ids_out, int64_t *mask_out,
+                                  int64_t vocab, int32_t *err, cudaStream_t stream) {
+  if (n_req == 0 || seq == 0) return SPU_OK;  // empty batch: nothing to move
+  SPU_REQUIRE(src_ids && len && ids_out && mask_out, SPU_ERR_INVALID, "gather: null argument");
+  SPU_REQUIRE(n_req > 0 && seq > 0 && n_req <= 65535, SPU_ERR_INVALID, "gather: bad shape");
+  dim3 grid((seq + 511) / 512 > 8 ? 8 : (seq + 511) / 512, n_req);
+  gather_pad_mask_kernel<<<grid, 256, 0, stream>>>(src_ids, src_mask, len, seq, pad_id, ids_out, mask_out, vocab, err);
+  SPU_CUDA_TRY(cudaGetLastError());
+  return SPU_OK;
+}
+}  // namespace spu
+
 extern "C" spu_status spu_gather_pad_mask_async(const int64_t *const *src_ids,
                                                 const int64_t *const *src_mask,
                                                 const int32_t *len, int32_t n_req, int32_t seq,
                                                 int64_t pad_id, int64_t *ids_out,
                                                 int64_t *mask_out, void *stream) {
-  if (n_req == 0 || seq == 0) return SPU_OK;  // empty batch: nothing to move
-  SPU_REQUIRE(src_ids && len && ids_out && mask_out, SPU_ERR_INVALID, "gather: null argument");
-  SPU_REQUIRE(n_req > 0 && seq > 0 && n_req <= 65535, SPU_ERR_INVALID, "gather: bad shape");
-  dim3 grid((seq + 511) / 512 > 8 ? 8 : (seq + 511) / 512, n_req);
-  gather_pad_mask_kernel<<<grid, 256, 0, as_stream(stream)>>>(src_ids, src_mask, len, seq, pad_id,
-                                                              ids_out, mask_out);
-  SPU_CUDA_TRY(cudaGetLastError());
-  return SPU_OK;
+  return gather_pad_mask_launch(src_ids, src_mask, len, n_req, seq, pad_id, ids_out, mask_out, 0, nullptr,
+                                as_stream(stream));
 }
 
 extern "C" spu_status spu_gather_segments_async(const void *const *srcs, const uint64_t *dst_off,

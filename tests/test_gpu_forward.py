@@ -309,6 +309,58 @@ def test_forward_requests_stages_1_to_4(spu, where, full_rows):
     rep.close()
 
 
+def test_forward_requests_checked_reports_ids_outside_the_table(spu):
+    """spu_bert_forward_requests_checked_async: the gather kernel checks every live token id against the embedding
+    table and the status word says which request row broke it (LibTorch's embedding raises there and the reference's
+    job fails; on this path no host code ever reads the ids).  Ids in the PADDING of a request buffer do not count.
+    Eager, captured and replayed launches (SPU_FORWARD_AUTO_GRAPH) agree, the word re-arms itself between tasks,
+    and a clean batch gives 0 and the same bits as the unchecked call."""
+    from oracle import bert_oracle as bo
+    from starpu_inference_server_b200.bert import BertReplica
+
+    cfg = bo.BERT_TINY
+    w = bo.make_weights(cfg, 0)
+    n_req, seq, H = 5, 32, cfg.hidden
+    rep = BertReplica(w, max_batch=8, max_seq=32, flags=spu.SPU_REQUEST_IO | spu.SPU_FORWARD_AUTO_GRAPH)
+    rng = np.random.default_rng(5)
+    lens = np.array([32, 7, 19, 1, 32], np.int32)
+    ids = [torch.from_numpy(rng.integers(0, cfg.vocab, size=seq).astype(np.int64)).cuda() for _ in range(n_req)]
+    outs = [torch.zeros(seq, H, device="cuda") for _ in range(n_req)]
+    table = lambda ts: torch.tensor([t.data_ptr() for t in ts], dtype=torch.int64, device="cuda")  # noqa: E731
+    ids_tab, out_tab, len_dev = table(ids), table(outs), torch.from_numpy(lens).cuda()
+
+    def run(status):
+        rep.forward_requests_async(ids_tab, None, len_dev, n_req, seq, out_tab, status=status)
+        torch.cuda.synchronize()
+        return None if status is None else int(status.item())
+
+    plain = None
+    for rnd in range(4):  # eager, eager (second sighting captures), replay, replay
+        status = torch.full((1,), -7, dtype=torch.int32, device="cuda")
+        assert run(status) == 0, rnd
+        got = torch.stack(outs).clone()
+        if plain is None:
+            run(None)
+            plain = torch.stack(outs).clone()
+        assert torch.equal(got, plain)
+        # an id past the table inside request 2's live tokens, another one in request 1's padding (not live)
+        good2, good1 = ids[2][18].item(), ids[1][20].item()
+        ids[2][18] = cfg.vocab
+        ids[1][20] = -5
+        status.fill_(-7)
+        assert run(status) == 3, rnd  # 1 + row 2
+        ids[2][18] = good2
+        good3, good0 = ids[3][0].item(), ids[0][31].item()
+        ids[3][0] = -1  # two bad rows: the larger index is reported
+        ids[0][31] = cfg.vocab + 100
+        status.fill_(-7)
+        assert run(status) == 4, rnd
+        ids[3][0], ids[0][31], ids[1][20] = good3, good0, good1
+    status = torch.full((1,), -7, dtype=torch.int32, device="cuda")
+    assert run(status) == 0  # nothing left over from the failed tasks
+    rep.close()
+
+
 def test_bf16_output_option(spu):
     """SPU_OUTPUT_BF16: output0 is the fp32 last_hidden_state rounded to bf16 by the last
     LayerNorm -- bit-identical to rounding the fp32 output, half the bytes."""

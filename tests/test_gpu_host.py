@@ -387,6 +387,46 @@ def test_device_visible_requests_through_the_task_path(host, variable_length):
     rep.close()
 
 
+def test_device_visible_requests_with_a_token_id_outside_the_table_fail_the_batch(host):
+    """on the device_visible_requests path the host never reads the ids, so the gather kernel checks them
+    and the output callback fails the batch (ok = 0 for every request of it, as the reference's job fails when
+    LibTorch's embedding raises) instead of returning a plausible response computed from a clamped id.  The next
+    clean batch on the same worker succeeds: the error word does not stick."""
+    from oracle import bert_oracle as bo
+    from starpu_inference_server_b200 import capi
+    from starpu_inference_server_b200.bert import BertReplica
+
+    spec = bo.BERT_TINY
+    w = bo.make_weights(spec, 0)
+    S, H = 32, spec.hidden
+    rep = BertReplica(w, max_batch=8, max_seq=S, n_workspaces=2, flags=capi.SPU_REQUEST_IO | capi.SPU_FORWARD_AUTO_GRAPH)
+    rng = np.random.default_rng(34)
+    reqs = []
+    for b in (1, 2, 1):
+        ids = torch.from_numpy(rng.integers(1, spec.vocab, size=(b, S), dtype=np.int64)).pin_memory()
+        mask = torch.ones(b, S, dtype=torch.int64).pin_memory()
+        out = torch.full((b, S, H), float("nan")).pin_memory()
+        reqs.append((b, ids, mask, out))
+    batch = lambda: [(i, b, [ids, mask], [out]) for i, (b, ids, mask, out) in enumerate(reqs)]  # noqa: E731
+    with host.Server(inputs=[("input_ids", "i64", [1, S]), ("attention_mask", "i64", [1, S])],
+                     outputs=[("output0", "f32", [1, S, H])], replicas=[rep], model_kind=host.MODEL_BERT,
+                     max_batch_size=8, pool_size=2, n_workspaces=2, device_visible_requests=True) as srv:
+        for rnd in range(4):  # eager, captured, replayed: the verdict follows the task, not the graph
+            res = srv.wait(srv.submit_batch(batch(), fixed_worker=0))
+            assert all(r.ok == 1 for r in res), [r.error for r in res]
+            keep = reqs[1][1][1, 5].item()
+            reqs[1][1][1, 5] = spec.vocab  # second sample of request 1 = batch row 2
+            res = srv.wait(srv.submit_batch(batch(), fixed_worker=0))
+            assert all(r.ok == 0 for r in res)
+            assert all(b"outside the embedding table" in r.error and b"row 2" in r.error for r in res), [r.error for r in res]
+            reqs[1][1][1, 5] = keep
+        res = srv.wait(srv.submit_batch(batch(), fixed_worker=0))
+        assert all(r.ok == 1 for r in res)
+        ref = bo.bert_forward(w, spec, reqs[1][1].numpy(), reqs[1][2].numpy())
+        assert np.abs(reqs[1][3].numpy() - ref).max() / np.abs(ref).max() < 2e-2
+    rep.close()
+
+
 def test_out_of_range_token_id_fails_the_batch_like_the_reference(host, bert_tiny):
     """LibTorch's embedding raises on an id outside the table and the reference's job fails; the kernel clamps (memory
     safety), so the host gather refuses the batch before anything is submitted."""
