@@ -558,9 +558,10 @@ spu_status capture_forward(spu_replica *r, Workspace &ws, const int64_t *ids, co
   cudaKernelNodeParams p0{}, p1{};
   if (!graph_chain_ends(graph, &root, &leaf, &p0, &p1)) return SPU_OK;
   if (p0.func != bert_embed_kernel_entry() || p1.func != layernorm_kernel_entry()) return SPU_OK;
-  const int out_arg = (r->flags & SPU_OUTPUT_BF16) ? 5 : 4;
+  const int out_arg = (r->flags & SPU_OUTPUT_BF16) ? kLayerNormArgOutBf16 : kLayerNormArgOutF32;
   // the captured parameters must be the pointers we are about to treat as patchable
-  if (*static_cast<const void *const *>(p0.kernelParams[0]) != ids || *static_cast<const void *const *>(p0.kernelParams[1]) != mask ||
+  if (*static_cast<const void *const *>(p0.kernelParams[kEmbedArgIds]) != ids ||
+      *static_cast<const void *const *>(p0.kernelParams[kEmbedArgMask]) != mask ||
       *static_cast<const void *const *>(p1.kernelParams[out_arg]) != out)
     return SPU_OK;
   cg->first = root;
@@ -573,12 +574,12 @@ spu_status capture_forward(spu_replica *r, Workspace &ws, const int64_t *ids, co
 // Point the instantiated graph at other I/O buffers (host-side only; launches already enqueued keep theirs).
 spu_status retarget_graph(CapturedGraph &g, const int64_t *ids, const int64_t *mask, float *out) {
   if (g.key.ids != ids || g.key.mask != mask) {
-    SPU_TRY(graph_patch_node(g, g.first, 17, {{0, ids}, {1, mask}}));  // bert_embed_ln_kernel(ids, mask, ...)
+    SPU_TRY(graph_patch_node(g, g.first, kEmbedKernelArgs, {{kEmbedArgIds, ids}, {kEmbedArgMask, mask}}));
     g.key.ids = ids;
     g.key.mask = mask;
   }
   if (g.key.out != out) {
-    SPU_TRY(graph_patch_node(g, g.last, 11, {{g.out_arg, out}}));  // layernorm_kernel(..., out_f32 [4], out_bf16 [5], ...)
+    SPU_TRY(graph_patch_node(g, g.last, kLayerNormKernelArgs, {{g.out_arg, out}}));
     g.key.out = out;
   }
   return SPU_OK;
@@ -955,6 +956,11 @@ extern "C" spu_status spu_bert_forward_requests_checked_async(spu_replica *r, in
       cudaKernelNodeParams p0{}, p1{};
       cg.patchable = graph_chain_ends(graph, &cg.first, &cg.last, &p0, &p1) &&
                      p0.func == gather_pad_mask_kernel_entry() && p1.func == scatter_requests_kernel_entry();
+      // the captured parameters must be the very pointers that will be treated as patchable
+      auto held = [](const cudaKernelNodeParams &p, int i) { return *static_cast<const void *const *>(p.kernelParams[i]); };
+      cg.patchable = cg.patchable && held(p0, 0) == want.ids && held(p0, 1) == want.aux && held(p0, 2) == want.mask &&
+                     held(p1, kScatterArgLen) == want.mask && held(p1, kScatterArgDsts) == want.out &&
+                     held(p1, kScatterArgStatus) == want.status;
       if (!cg.patchable) {  // cannot be retargeted: useless for a slot-cycling server
         SPU_CUDA_TRY(cudaGraphLaunch(cg.exec, s));
         cudaStreamSynchronize(s);

@@ -5,6 +5,8 @@
 #include <initializer_list>
 #include <memory>
 #include <string>
+#include <tuple>
+#include <type_traits>
 #include <vector>
 
 #include "common.cuh"
@@ -65,6 +67,22 @@ spu_status gather_pad_mask_launch(const int64_t *const *src_ids, const int64_t *
 //  scatter_requests_kernel(src, len, seq, hidden, full_rows, dsts, err, status))
 constexpr int kGatherKernelArgs = 9, kScatterKernelArgs = 8;
 constexpr int kScatterArgLen = 1, kScatterArgDsts = 5, kScatterArgStatus = 7;
+// bert_embed_ln_kernel(ids, mask, ...17 in all); layernorm_kernel(x, gamma, beta, eps, out_f32 [4], out_bf16 [5], ...11)
+constexpr int kEmbedKernelArgs = 17, kEmbedArgIds = 0, kEmbedArgMask = 1;
+constexpr int kLayerNormKernelArgs = 11, kLayerNormArgOutF32 = 4, kLayerNormArgOutBf16 = 5;
+
+// The file that defines a patched kernel pins those numbers to its real signature (static_assert beside the kernel),
+// so a changed parameter list fails the build instead of patching the wrong argument of an instantiated graph.
+template <typename F>
+struct KernelSig;
+template <typename... A>
+struct KernelSig<void(A...)> {
+  static constexpr int count = static_cast<int>(sizeof...(A));
+  template <int I>
+  static constexpr bool pointer_at = std::is_pointer<typename std::tuple_element<I, std::tuple<A...>>::type>::value;
+};
+#define SPU_PIN_KERNEL_ARGS(kernel, n) static_assert(::spu::KernelSig<decltype(kernel)>::count == (n), #kernel ": parameter count changed; update the graph-patching constants")
+#define SPU_PIN_KERNEL_PTR_ARG(kernel, i) static_assert(::spu::KernelSig<decltype(kernel)>::pointer_at<(i)>, #kernel ": patched parameter is not a pointer")
 // e4m3 = sat(in * inv_scale); exactly one of in_f32 / in_bf16 is non-null; n % 4 == 0
 spu_status quantize_e4m3_launch(const float *in_f32, const void *in_bf16, void *out, uint64_t n,
                                 float inv_scale, cudaStream_t stream);

@@ -423,6 +423,21 @@ spu_status layernorm_unpad_launch(const float *x, const int32_t *cu, int batch, 
   return SPU_OK;
 }
 
+SPU_PIN_KERNEL_ARGS(gather_pad_mask_kernel, kGatherKernelArgs);
+SPU_PIN_KERNEL_PTR_ARG(gather_pad_mask_kernel, 0);
+SPU_PIN_KERNEL_PTR_ARG(gather_pad_mask_kernel, 1);
+SPU_PIN_KERNEL_PTR_ARG(gather_pad_mask_kernel, 2);
+SPU_PIN_KERNEL_ARGS(scatter_requests_kernel, kScatterKernelArgs);
+SPU_PIN_KERNEL_PTR_ARG(scatter_requests_kernel, kScatterArgLen);
+SPU_PIN_KERNEL_PTR_ARG(scatter_requests_kernel, kScatterArgDsts);
+SPU_PIN_KERNEL_PTR_ARG(scatter_requests_kernel, kScatterArgStatus);
+SPU_PIN_KERNEL_ARGS(bert_embed_ln_kernel, kEmbedKernelArgs);
+SPU_PIN_KERNEL_PTR_ARG(bert_embed_ln_kernel, kEmbedArgIds);
+SPU_PIN_KERNEL_PTR_ARG(bert_embed_ln_kernel, kEmbedArgMask);
+SPU_PIN_KERNEL_ARGS(layernorm_kernel, kLayerNormKernelArgs);
+SPU_PIN_KERNEL_PTR_ARG(layernorm_kernel, kLayerNormArgOutF32);
+SPU_PIN_KERNEL_PTR_ARG(layernorm_kernel, kLayerNormArgOutBf16);
+
 const void *gather_pad_mask_kernel_entry() { return reinterpret_cast<const void *>(&gather_pad_mask_kernel); }
 const void *scatter_requests_kernel_entry() { return reinterpret_cast<const void *>(&scatter_requests_kernel); }
 const void *bert_embed_kernel_entry() { return reinterpret_cast<const void *>(&bert_embed_ln_kernel); }

@@ -135,6 +135,13 @@ vit_slice_logits_kernel(const float *__restrict__ padded, float *__restrict__ lo
   }
 }
 
+// the two kernels whose parameters spu_vit_forward_async patches in an instantiated graph
+constexpr int kIm2colKernelArgs = 6, kIm2colArgPixels = 0, kSliceLogitsKernelArgs = 5, kSliceLogitsArgLogits = 1;
+SPU_PIN_KERNEL_ARGS(vit_im2col_kernel, kIm2colKernelArgs);
+SPU_PIN_KERNEL_PTR_ARG(vit_im2col_kernel, kIm2colArgPixels);
+SPU_PIN_KERNEL_ARGS(vit_slice_logits_kernel, kSliceLogitsKernelArgs);
+SPU_PIN_KERNEL_PTR_ARG(vit_slice_logits_kernel, kSliceLogitsArgLogits);
+
 void vit_destroy(VitState *v) {
   if (v != nullptr)
     for (VitWorkspace &ws : v->ws)
@@ -363,11 +370,11 @@ extern "C" spu_status spu_vit_forward_async(spu_replica *r, int32_t ws_idx, cons
   for (CapturedGraph &g : ws.graphs) {
     if (g.key.batch != batch) continue;
     if (g.key.ids != pixels) {
-      SPU_TRY(graph_patch_node(g, g.first, 6, {{0, pixels}}));  // vit_im2col_kernel(pixels, ...)
+      SPU_TRY(graph_patch_node(g, g.first, kIm2colKernelArgs, {{kIm2colArgPixels, pixels}}));
       g.key.ids = pixels;
     }
     if (g.key.out != logits) {
-      SPU_TRY(graph_patch_node(g, g.last, 5, {{1, logits}}));  // vit_slice_logits_kernel(logits_pad, logits, ...)
+      SPU_TRY(graph_patch_node(g, g.last, kSliceLogitsKernelArgs, {{kSliceLogitsArgLogits, logits}}));
       g.key.out = logits;
     }
     g.tick = ++ws.graph_tick;
@@ -403,6 +410,10 @@ extern "C" spu_status spu_vit_forward_async(spu_replica *r, int32_t ws_idx, cons
   cg.patchable = graph_chain_ends(graph, &cg.first, &cg.last, &p0, &p1) &&
                  p0.func == reinterpret_cast<const void *>(&vit_im2col_kernel) &&
                  p1.func == reinterpret_cast<const void *>(&vit_slice_logits_kernel);
+  // ... and the parameters captured there must be the very pointers that will be patched later (as
+  // replica.cu's capture_forward checks for the BERT chain)
+  cg.patchable = cg.patchable && *static_cast<const void *const *>(p0.kernelParams[kIm2colArgPixels]) == pixels &&
+                 *static_cast<const void *const *>(p1.kernelParams[kSliceLogitsArgLogits]) == logits;
   SPU_CUDA_TRY(cudaGraphLaunch(cg.exec, s));
   if (!cg.patchable) {  // cannot follow the task's buffers: not worth keeping
     cudaStreamSynchronize(s);
