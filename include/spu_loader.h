@@ -33,9 +33,17 @@ typedef struct spu_module spu_module;
 
 /* torch::jit::load(path, CPU) + eval(); collects the fp32 host copy of every tensor the
  * replica needs, in SPU_BERT_NUM_TENSORS / SPU_VIT_NUM_TENSORS order, and infers the
- * architecture from their shapes (heads = hidden / 64).  Returns 0, or non-zero with
+ * architecture from their shapes (heads and the LayerNorm epsilon are read from the artifact, see spu_loader_open_ex).  Returns 0, or non-zero with
  * spu_loader_last_error() set (missing file, missing parameter, unsupported shape). */
 int32_t spu_loader_open(const char *path, int32_t kind, spu_module **out);
+/* The same with the two facts the tensor shapes do not carry supplied by the caller (models/*.yml): heads > 0 and
+ * ln_eps > 0 override what the loader reads from the artifact; 0 = read it.  The loader reads the LayerNorm epsilon
+ * from the constant eps input of the forward graph's aten::layer_norm nodes (else the `eps` attribute of the first
+ * LayerNorm) and the head count from the `num_heads` / `num_attention_heads` attribute of the first attention
+ * module (else the constant trailing dims of the [B, S, heads, head_dim] view in the forward graph).  It never
+ * guesses: when neither source has them, or when head_dim is not the 64 the attention kernels are built for
+ * (e.g. ViT-H/14: 16 heads of 80), the call fails with the reason in spu_loader_last_error(). */
+int32_t spu_loader_open_ex(const char *path, int32_t kind, int32_t heads, float ln_eps, spu_module **out);
 void spu_loader_close(spu_module *m);
 
 int32_t spu_loader_kind(const spu_module *m);

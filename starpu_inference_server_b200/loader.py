@@ -13,7 +13,7 @@ from . import capi
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libspu_loader.so")
 KIND_BERT, KIND_VIT = 0, 1
-SYMBOLS = ["spu_loader_open", "spu_loader_close", "spu_loader_kind", "spu_loader_num_tensors", "spu_loader_tensor",
+SYMBOLS = ["spu_loader_open", "spu_loader_open_ex", "spu_loader_close", "spu_loader_kind", "spu_loader_num_tensors", "spu_loader_tensor",
            "spu_loader_bert_desc", "spu_loader_vit_desc", "spu_loader_create_replica", "spu_loader_last_error"]
 
 _lib = None
@@ -33,6 +33,7 @@ def lib():
     L = C.CDLL(LIB_PATH)
     vp, i32 = C.c_void_p, C.c_int32
     L.spu_loader_open.argtypes = [C.c_char_p, i32, C.POINTER(vp)]
+    L.spu_loader_open_ex.argtypes = [C.c_char_p, i32, i32, C.c_float, C.POINTER(vp)]
     L.spu_loader_close.argtypes = [vp]
     L.spu_loader_close.restype = None
     L.spu_loader_kind.argtypes = [vp]
@@ -49,9 +50,11 @@ def lib():
 class TorchScriptModule:
     """`torch::jit::load` + `eval()` of a served artifact, done in C++ (load_model, inference_runner.cpp:243-249)."""
 
-    def __init__(self, path: str, kind: int):
+    def __init__(self, path: str, kind: int, heads: int = 0, ln_eps: float = 0.0):
+        """heads / ln_eps: 0 = read them from the artifact (the loader refuses rather than guess); a positive value,
+        e.g. from models/*.yml, overrides."""
         h = C.c_void_p()
-        if lib().spu_loader_open(os.fsencode(path), kind, C.byref(h)) != 0:
+        if lib().spu_loader_open_ex(os.fsencode(path), kind, heads, ln_eps, C.byref(h)) != 0:
             raise LoaderError(lib().spu_loader_last_error().decode(errors="replace"))
         self._h, self.kind = h, kind
 

@@ -106,3 +106,47 @@ def test_loader_errors(ld, tmp_path):
         ld.TorchScriptModule(p, ld.KIND_BERT)
     with pytest.raises(ld.LoaderError, match="not a torchvision ViT"):
         ld.TorchScriptModule(p, ld.KIND_VIT)
+
+
+def test_heads_and_eps_come_from_the_artifact_not_from_a_guess(ld, tmp_path):
+    """hidden / 64 heads and a per-family eps constant are right for BERT-base / ViT-B/L and silently
+    wrong otherwise.  The loader reads both from the TorchScript artifact (graph constants, module attributes), a
+    caller may override them (models/*.yml), and a model the attention kernels cannot serve (head_dim != 64) is
+    refused at load time -- the reference's torch::jit::load serves such a module, this path must not pretend to."""
+    import dataclasses
+
+    import torchvision
+
+    import hf_keyed
+    from oracle import bert_oracle as bo
+
+    # traced BERT with a non-default epsilon: read from the aten::layer_norm constants of the forward graph
+    spec = dataclasses.replace(bo.BERT_TINY, ln_eps=1e-5)
+    path = str(tmp_path / "bert_eps.pt")
+    hf_keyed.export_bert_torchscript(spec, bo.make_weights(spec, 4), path)
+    with ld.TorchScriptModule(path, ld.KIND_BERT) as m:
+        d = m.desc()
+        assert d.heads == spec.heads and d.ln_eps == pytest.approx(1e-5, rel=1e-6)
+    with ld.TorchScriptModule(path, ld.KIND_BERT, ln_eps=3e-6) as m:  # explicit value wins
+        assert m.desc().ln_eps == pytest.approx(3e-6, rel=1e-6)
+    # same hidden size split into 4 heads of 32: hidden / 64 would have said 2 and computed the wrong attention
+    spec32 = dataclasses.replace(bo.BERT_TINY, heads=4)
+    path32 = str(tmp_path / "bert_h32.pt")
+    hf_keyed.export_bert_torchscript(spec32, bo.make_weights(spec32, 4), path32)
+    with pytest.raises(ld.LoaderError, match="4 heads of 32"):
+        ld.TorchScriptModule(path32, ld.KIND_BERT)
+    # scripted torchvision ViT with 2 heads of 80 (the ViT-H/14 head size): `num_heads` attribute, refused
+    vit = torchvision.models.vision_transformer.VisionTransformer(
+        image_size=32, patch_size=16, num_layers=1, num_heads=2, hidden_dim=160, mlp_dim=320, num_classes=10).eval()
+    pv = str(tmp_path / "vit_h80.pt")
+    torch.jit.script(vit).save(pv)
+    with pytest.raises(ld.LoaderError, match="2 heads of 80.*head_dim 64"):
+        ld.TorchScriptModule(pv, ld.KIND_VIT)
+    # the family default is read, not assumed
+    vit64 = torchvision.models.vision_transformer.VisionTransformer(
+        image_size=32, patch_size=16, num_layers=1, num_heads=2, hidden_dim=128, mlp_dim=256, num_classes=10).eval()
+    p64 = str(tmp_path / "vit_h64.pt")
+    torch.jit.script(vit64).save(p64)
+    with ld.TorchScriptModule(p64, ld.KIND_VIT) as m:
+        d = m.desc()
+        assert d.heads == 2 and d.ln_eps == pytest.approx(1e-6, rel=1e-6)
